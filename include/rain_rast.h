@@ -1,0 +1,101 @@
+/* rain_rast.h — C ABI of librainrast.so, the sm_100a replacement for the two CUDA extensions of sharonal10/rain:
+ *   submodules/diff_gaussian_rasterization  (pybind module `_C`, ext.cpp:4-8)
+ *   submodules/simple-knn                   (pybind module `simple_knn._C`, ext.cpp:4-6)
+ *
+ * Conventions
+ *  - every pointer is a raw DEVICE pointer (tensor.data_ptr()) unless its name ends in `_host`;
+ *  - `stream` is a cudaStream_t passed as void* (torch.cuda.current_stream().cuda_stream); the reference always
+ *    used the legacy default stream (forward.cu:386,428; rasterizer_impl.cu:281,306);
+ *  - the library never allocates: the caller owns outputs and the three opaque scratch blobs (geometry / binning /
+ *    image) that the reference grew through std::function<char*(size_t)> callbacks (rasterizer.h:21-23,
+ *    rasterize_points.cu:16-22); their sizes come from the rr_*_bytes functions;
+ *  - functions return 0 on success and a negative value on error; rr_last_error() gives the message
+ *    (the reference threw std::runtime_error / AT_ERROR through pybind, rasterize_points.cu:47-49,
+ *    rasterizer_impl.cu:233-236, auxiliary.h:155-162);
+ *  - null `shs` / `colors_precomp` and null `scales`+`rotations` / `cov3D_precomp` select the modes exactly like the
+ *    nullptr tests of the reference (forward.cu:195,231; backward.cu:380,384);
+ *  - `debug != 0` makes each entry synchronise the stream and report asynchronous CUDA errors (CHECK_CUDA semantics,
+ *    auxiliary.h:155-162);
+ *  - `variant`: 1 = TMA bulk-copy staging in the tile renderers (default), 0 = cooperative float4 loads.
+ */
+#ifndef RAIN_RAST_H
+#define RAIN_RAST_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* rr_last_error(void);
+int rr_version(void);
+
+/* scratch sizes: replace required<GeometryState>(P), required<ImageState>(W*H), required<BinningState>(N)
+ * (rasterizer_impl.h:55-62, rasterizer_impl.cu:144-183) */
+size_t rr_geom_bytes(int P);
+size_t rr_image_bytes(int W, int H);
+size_t rr_binning_bytes(int64_t N, int W, int H);
+size_t rr_backward_ws_bytes(int64_t N);
+
+/* Forward, first half — replaces FORWARD::preprocess + cub InclusiveSum + the blocking cudaMemcpy of num_rendered
+ * (Rasterizer::forward, rasterizer_impl.cu:187-273).  Writes radii[P] and the geometry blob, and enqueues an async
+ * copy of num_rendered into *num_rendered_host (pinned host memory); the caller synchronises the stream before
+ * reading it and sizing the binning blob. */
+int rr_forward_geom(void* stream, int P, int D, int M, int W, int H,
+	const float* means3D, const float* shs, const float* colors_precomp, const float* opacities,
+	const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+	const float* viewmatrix, const float* projmatrix, const float* campos,
+	float tan_fovx, float tan_fovy, float low_pass, int prefiltered, int debug,
+	int* radii, void* geom, size_t geom_bytes, int64_t* num_rendered_host);
+
+/* Forward, second half — replaces duplicateWithKeys + cub SortPairs + identifyTileRanges + FORWARD::render
+ * (rasterizer_impl.cu:275-328).  out_color[3,H,W], out_depth[1,H,W]. */
+int rr_forward_raster(void* stream, int P, int W, int H, int64_t N, const float* background,
+	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes,
+	float* out_color, float* out_depth, int variant, int debug);
+
+/* Backward — replaces Rasterizer::backward (rasterizer_impl.cu:334-430) and the torch::zeros fills of
+ * RasterizeGaussiansBackwardCUDA (rasterize_points.cu:145-153): every element of every gradient buffer is written.
+ * dL_dconic may be null (the reference keeps it internal).  dL_dsh is [P,M,3] (unused when shs is null),
+ * dL_dscale / dL_drot may be null when cov3D_precomp is given.  ws: rr_backward_ws_bytes(N) of scratch. */
+int rr_backward(void* stream, int P, int D, int M, int W, int H, int64_t N, const float* background,
+	const float* means3D, const float* shs, const float* colors_precomp,
+	const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+	const float* viewmatrix, const float* projmatrix, const float* campos,
+	float tan_fovx, float tan_fovy, float low_pass, const int* radii,
+	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes,
+	const float* dL_dpix, void* ws, size_t ws_bytes,
+	float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+	float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+	int variant, int debug);
+
+/* replaces Rasterizer::markVisible / checkFrustum (rasterizer_impl.cu:43-55,130-142); present is uint8/bool [P] */
+int rr_mark_visible(void* stream, int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present);
+
+/* replaces distCUDA2 / SimpleKNN::knn (simple-knn/spatial.cu:4-15, simple_knn.cu:174-210); points f32[P,3] -> out f32[P] */
+size_t rr_dist2_ws_bytes(int P);
+int rr_dist2(void* stream, int P, const float* points, float* out, void* ws, size_t ws_bytes);
+
+/* ---- stage-level entry points used by the parity tests ---- */
+/* stable ascending sort of (key,value) pairs on key bits [begin_bit,end_bit); result is written to keys_out/vals_out;
+ * keys_in/vals_in are clobbered (they are the ping-pong partners).  vals_in == NULL sorts the identity 0..n-1. */
+size_t rr_sort_ws_bytes(int64_t n, int key_bytes, int begin_bit, int end_bit);
+int rr_sort_pairs_u32(void* stream, int64_t n, uint32_t* keys_in, uint32_t* keys_out, uint32_t* vals_in, uint32_t* vals_out,
+	int begin_bit, int end_bit, void* ws);
+int rr_sort_pairs_u64(void* stream, int64_t n, uint64_t* keys_in, uint64_t* keys_out, uint32_t* vals_in, uint32_t* vals_out,
+	int begin_bit, int end_bit, void* ws);
+
+/* byte offsets of the arrays inside the opaque blobs (for stage-wise diffing against the oracle / reference).
+ * geom:    [0] rec f32[P,12]  [1] cov3D f32[P,6]  [2] clamped u8[P]  [3] tiles_touched u32[P]  [4] rect u32[P,2]
+ *          [5] depth_order u32[P]  [6] offsets u32[P] (inclusive, in depth order)  [7] dup_off u32[P]  [8] num_rendered u32
+ * binning: [0] tile_keys_sorted u32[N]  [1] emit_sorted u32[N]  [2] owner u32[N]  [3] point_list u32[N]  [4] packed f32[N,12]
+ * image:   [0] final_T f32[H*W]  [1] n_contrib u32[H*W]  [2] ranges u32[T,2]  [3] tile_max_contrib u32[T] */
+int rr_geom_layout(int P, int64_t offsets_host[9]);
+int rr_binning_layout(int64_t N, int W, int H, int64_t offsets_host[5]);
+int rr_image_layout(int W, int H, int64_t offsets_host[4]);
+/* the 64-bit (tile<<32 | depth bits) key of every sorted duplicate, as the reference's point_list_keys holds them */
+int rr_export_sorted_keys(void* stream, int P, int64_t N, int W, int H, void* geom, void* binning, uint64_t* keys_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,159 @@
+"""Drop-in for the reference's pybind module ``diff_gaussian_rasterization._C`` (ext.cpp:4-8): the three ops
+``rasterize_gaussians``, ``rasterize_gaussians_backward`` and ``mark_visible`` with the argument order, return order,
+shapes and dtypes of rasterize_points.h:7-58, implemented on top of the C ABI of librainrast.so.
+
+PyTorch is only plumbing here: it owns device memory (outputs, gradients, the three opaque scratch blobs) and the
+current stream.  All compute happens in the hand-written sm_100a kernels.
+"""
+import os
+
+import torch
+
+from . import _lib
+
+NUM_CHANNELS = 3  # config.h:4
+
+_pinned = {}
+
+
+def _variant():
+    return int(os.environ.get("RAIN_RAST_VARIANT", "1"))
+
+
+def _ptr(t):
+    """device pointer or NULL for the empty tensors the reference API uses for 'not provided' (__init__.py:189-199)"""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def _f32c(t, dev):
+    if t is None or t.numel() == 0:
+        return None
+    if t.device != dev:
+        raise RuntimeError(f"expected a tensor on {dev}, got {t.device}")
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"expected float32, got {t.dtype}")
+    return t.contiguous()
+
+
+def _pinned_i64(dev):
+    key = dev.index
+    if key not in _pinned:
+        _pinned[key] = torch.zeros(1, dtype=torch.int64).pin_memory()
+    return _pinned[key]
+
+
+def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                        viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
+                        prefiltered, debug, low_pass):
+    """RasterizeGaussiansCUDA (rasterize_points.cu:24-108).
+    Returns (num_rendered, out_color[3,H,W], radii i32[P], out_depth[1,H,W], geomBuffer, binningBuffer, imgBuffer)."""
+    lib = _lib.load()
+    if means3D.dim() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")  # rasterize_points.cu:47-49
+    if not means3D.is_cuda:
+        raise RuntimeError("rain_b200 has no CPU path: means3D must be a CUDA tensor")
+    dev = means3D.device
+    P, H, W = means3D.size(0), int(image_height), int(image_width)
+    byte = dict(dtype=torch.uint8, device=dev)
+    if P == 0:  # rasterize_points.cu:72
+        z = torch.zeros
+        return (0, z((NUM_CHANNELS, H, W), dtype=torch.float32, device=dev), z((0,), dtype=torch.int32, device=dev),
+                z((1, H, W), dtype=torch.float32, device=dev), torch.empty(0, **byte), torch.empty(0, **byte), torch.empty(0, **byte))
+    means3D_c = _f32c(means3D, dev)
+    bg, colors_c, opac, scales_c, rots, cov_c = (_f32c(t, dev) for t in (background, colors, opacity, scales, rotations, cov3D_precomp))
+    view, proj, cam, sh_c = (_f32c(t, dev) for t in (viewmatrix, projmatrix, campos, sh))
+    M = sh.size(1) if (sh is not None and sh.numel() != 0) else 0  # rasterize_points.cu:75-78
+    out_color = torch.empty((NUM_CHANNELS, H, W), dtype=torch.float32, device=dev)
+    out_depth = torch.empty((1, H, W), dtype=torch.float32, device=dev)
+    radii = torch.empty((P,), dtype=torch.int32, device=dev)
+    geom = torch.empty(lib.rr_geom_bytes(P), **byte)
+    img = torch.empty(lib.rr_image_bytes(W, H), **byte)
+    nr = _pinned_i64(dev)
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream()
+        _lib.check(lib.rr_forward_geom(stream.cuda_stream, P, int(degree), M, W, H,
+                                       _ptr(means3D_c), _ptr(sh_c), _ptr(colors_c), _ptr(opac),
+                                       _ptr(scales_c), float(scale_modifier), _ptr(rots), _ptr(cov_c),
+                                       _ptr(view), _ptr(proj), _ptr(cam),
+                                       float(tan_fovx), float(tan_fovy), float(low_pass), int(bool(prefiltered)), int(bool(debug)),
+                                       radii.data_ptr(), geom.data_ptr(), geom.numel(), nr.data_ptr()), "rr_forward_geom")
+        stream.synchronize()  # num_rendered sizes the binning blob (reference: blocking cudaMemcpy, rasterizer_impl.cu:273)
+        N = int(nr.item())
+        binning = torch.empty(lib.rr_binning_bytes(N, W, H), **byte)
+        _lib.check(lib.rr_forward_raster(stream.cuda_stream, P, W, H, N, _ptr(bg),
+                                         geom.data_ptr(), geom.numel(), binning.data_ptr(), binning.numel(), img.data_ptr(), img.numel(),
+                                         out_color.data_ptr(), out_depth.data_ptr(), _variant(), int(bool(debug))), "rr_forward_raster")
+    return N, out_color, radii, out_depth, geom, binning, img
+
+
+def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
+                                 viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
+                                 geomBuffer, R, binningBuffer, imageBuffer, debug, low_pass, return_conic=False):
+    """RasterizeGaussiansBackwardCUDA (rasterize_points.cu:110-191).
+    Returns (dL_dmeans2D[P,3], dL_dcolors[P,3], dL_dopacity[P,1], dL_dmeans3D[P,3], dL_dcov3D[P,6], dL_dsh[P,M,3],
+    dL_dscales[P,3], dL_drotations[P,4])."""
+    lib = _lib.load()
+    dev = means3D.device
+    P, H, W = means3D.size(0), dL_dout_color.size(1), dL_dout_color.size(2)
+    M = sh.size(1) if (sh is not None and sh.numel() != 0) else 0
+    f32 = dict(dtype=torch.float32, device=dev)
+    new = torch.zeros if P == 0 else torch.empty
+    dL_dmeans3D, dL_dmeans2D, dL_dcolors = new((P, 3), **f32), new((P, 3), **f32), new((P, NUM_CHANNELS), **f32)
+    dL_dconic, dL_dopacity, dL_dcov3D = new((P, 2, 2), **f32), new((P, 1), **f32), new((P, 6), **f32)
+    dL_dsh, dL_dscales, dL_drotations = new((P, M, 3), **f32), new((P, 3), **f32), new((P, 4), **f32)
+    if P != 0:
+        means3D_c = _f32c(means3D, dev)
+        bg, colors_c, scales_c, rots, cov_c = (_f32c(t, dev) for t in (background, colors, scales, rotations, cov3D_precomp))
+        view, proj, cam, sh_c, dpix = (_f32c(t, dev) for t in (viewmatrix, projmatrix, campos, sh, dL_dout_color))
+        radii_c = radii.contiguous()
+        ws = torch.empty(lib.rr_backward_ws_bytes(int(R)), dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            stream = torch.cuda.current_stream()
+            _lib.check(lib.rr_backward(stream.cuda_stream, P, int(degree), M, W, H, int(R), _ptr(bg),
+                                       _ptr(means3D_c), _ptr(sh_c), _ptr(colors_c),
+                                       _ptr(scales_c), float(scale_modifier), _ptr(rots), _ptr(cov_c),
+                                       _ptr(view), _ptr(proj), _ptr(cam),
+                                       float(tan_fovx), float(tan_fovy), float(low_pass), radii_c.data_ptr(),
+                                       geomBuffer.data_ptr(), geomBuffer.numel(), binningBuffer.data_ptr(), binningBuffer.numel(),
+                                       imageBuffer.data_ptr(), imageBuffer.numel(),
+                                       dpix.data_ptr(), ws.data_ptr(), ws.numel(),
+                                       dL_dmeans2D.data_ptr(), dL_dconic.data_ptr(), dL_dopacity.data_ptr(), dL_dcolors.data_ptr(),
+                                       dL_dmeans3D.data_ptr(), dL_dcov3D.data_ptr(), _ptr(dL_dsh), dL_dscales.data_ptr(), dL_drotations.data_ptr(),
+                                       _variant(), int(bool(debug))), "rr_backward")
+    out = (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)
+    return out + (dL_dconic,) if return_conic else out
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    """markVisible (rasterize_points.cu:193-212): bool[P], view-space z > 0.2."""
+    lib = _lib.load()
+    if not means3D.is_cuda:
+        raise RuntimeError("rain_b200 has no CPU path: means3D must be a CUDA tensor")
+    dev = means3D.device
+    P = means3D.size(0)
+    present = torch.zeros((P,), dtype=torch.bool, device=dev)
+    if P != 0:
+        m, v, p = _f32c(means3D, dev), _f32c(viewmatrix, dev), _f32c(projmatrix, dev)
+        with torch.cuda.device(dev):
+            _lib.check(lib.rr_mark_visible(torch.cuda.current_stream().cuda_stream, P, m.data_ptr(), v.data_ptr(), p.data_ptr(),
+                                           present.data_ptr()), "rr_mark_visible")
+    return present
+
+
+def distCUDA2(points):
+    """simple_knn._C.distCUDA2 (simple-knn/spatial.cu:4-15): f32[P,3] cuda -> f32[P] mean squared distance to the 3 nearest
+    other points."""
+    lib = _lib.load()
+    if not points.is_cuda:
+        raise RuntimeError("rain_b200 has no CPU path: points must be a CUDA tensor")
+    dev = points.device
+    P = points.size(0)
+    pts = _f32c(points, dev) if P else points
+    means = torch.zeros((P,), dtype=torch.float32, device=dev)
+    if P != 0:
+        ws = torch.empty(lib.rr_dist2_ws_bytes(P), dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            _lib.check(lib.rr_dist2(torch.cuda.current_stream().cuda_stream, P, pts.data_ptr(), means.data_ptr(), ws.data_ptr(), ws.numel()), "rr_dist2")
+    return means

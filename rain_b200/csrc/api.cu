@@ -1,0 +1,316 @@
+// C ABI of librainrast.so (include/rain_rast.h): host orchestration of the forward / backward pipelines.
+// Replaces CudaRasterizer::Rasterizer::forward/backward/markVisible (reference rasterizer_impl.cu:187-430) and the
+// torch binding RasterizeGaussiansCUDA / RasterizeGaussiansBackwardCUDA / markVisible (rasterize_points.cu) minus
+// tensor allocation, which stays in Python.
+#include <cstdarg>
+#include <cstring>
+#include <string>
+#include "../../include/rain_rast.h"
+#include "common.cuh"
+#include "kernels.cuh"
+#include "radix_sort.cuh"
+
+namespace rr {
+
+static thread_local std::string g_error;
+
+void set_error(const char* fmt, ...)
+{
+	char buf[512];
+	va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof(buf), fmt, ap); va_end(ap);
+	g_error = buf;
+}
+
+int check_launch(const char* what, cudaStream_t stream, bool sync)
+{
+	cudaError_t e = cudaGetLastError();
+	if (e == cudaSuccess && sync) e = cudaStreamSynchronize(stream);
+	if (e != cudaSuccess) { set_error("%s: %s", what, cudaGetErrorString(e)); return -1; }
+	return 0;
+}
+
+namespace {
+
+// bit length, the reference's getHigherMsb (rasterizer_impl.cu:24-39)
+int tile_bits(int num_tiles) { int b = 0; while ((num_tiles >> b) != 0) b++; return b < 1 ? 1 : b; }
+
+struct GeomLayout {
+	SplatRec* rec; float* cov3D; uint8_t* clamped; uint32_t* tiles_touched; uint2* rect;
+	uint32_t *key_a, *key_b, *val_a, *val_b, *offsets, *dup_off, *block_sums, *num_rendered; void* sort_ws;
+	size_t total;
+	int64_t off[9];
+};
+GeomLayout geom_layout(void* blob, int P)
+{
+	GeomLayout L; Carver c(blob);
+	const size_t Pz = (size_t)(P < 1 ? 1 : P);
+	L.rec = c.take<SplatRec>(Pz);
+	L.cov3D = c.take<float>(6 * Pz);
+	L.clamped = c.take<uint8_t>(Pz);
+	L.tiles_touched = c.take<uint32_t>(Pz);
+	L.rect = c.take<uint2>(Pz);
+	L.key_a = c.take<uint32_t>(Pz); L.key_b = c.take<uint32_t>(Pz);
+	L.val_a = c.take<uint32_t>(Pz); L.val_b = c.take<uint32_t>(Pz);
+	L.offsets = c.take<uint32_t>(Pz);
+	L.dup_off = c.take<uint32_t>(Pz);
+	L.block_sums = c.take<uint32_t>(scan_ws_elems((int)Pz));
+	L.num_rendered = c.take<uint32_t>(4);
+	L.sort_ws = c.take<char>(sort_ws_bytes<uint32_t>(Pz, 0, 32));
+	L.total = c.used();
+	char* b = reinterpret_cast<char*>(blob);
+	// depth sort: 4 passes -> result back in the *_a buffers
+	L.off[0] = (char*)L.rec - b; L.off[1] = (char*)L.cov3D - b; L.off[2] = (char*)L.clamped - b; L.off[3] = (char*)L.tiles_touched - b;
+	L.off[4] = (char*)L.rect - b; L.off[5] = (char*)L.val_a - b; L.off[6] = (char*)L.offsets - b; L.off[7] = (char*)L.dup_off - b;
+	L.off[8] = (char*)L.num_rendered - b;
+	return L;
+}
+
+struct BinLayout {
+	uint32_t *key_a, *key_b, *emit_a, *emit_b, *owner, *point_list; SplatRec* packed; void* sort_ws;
+	uint32_t *keys_sorted, *emit_sorted;
+	int bits; size_t total; int64_t off[5];
+};
+BinLayout bin_layout(void* blob, int64_t N, int W, int H)
+{
+	BinLayout L; Carver c(blob);
+	const size_t Nz = (size_t)(N < 1 ? 1 : N);
+	const int tiles = ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+	L.bits = tile_bits(tiles);
+	L.key_a = c.take<uint32_t>(Nz); L.key_b = c.take<uint32_t>(Nz);
+	L.emit_a = c.take<uint32_t>(Nz); L.emit_b = c.take<uint32_t>(Nz);
+	L.owner = c.take<uint32_t>(Nz);
+	L.point_list = c.take<uint32_t>(Nz);
+	L.packed = c.take<SplatRec>(Nz);
+	L.sort_ws = c.take<char>(sort_ws_bytes<uint32_t>(Nz, 0, L.bits));
+	L.total = c.used();
+	const bool in_b = (((L.bits + 7) / 8) & 1) != 0;
+	L.keys_sorted = in_b ? L.key_b : L.key_a;
+	L.emit_sorted = in_b ? L.emit_b : L.emit_a;
+	char* b = reinterpret_cast<char*>(blob);
+	L.off[0] = (char*)L.keys_sorted - b; L.off[1] = (char*)L.emit_sorted - b; L.off[2] = (char*)L.owner - b;
+	L.off[3] = (char*)L.point_list - b; L.off[4] = (char*)L.packed - b;
+	return L;
+}
+
+struct ImgLayout { float* final_T; uint32_t* n_contrib; uint2* ranges; uint32_t* tile_max; size_t total; int64_t off[4]; };
+ImgLayout img_layout(void* blob, int W, int H)
+{
+	ImgLayout L; Carver c(blob);
+	const size_t X = (size_t)W * H;
+	const size_t tiles = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+	L.final_T = c.take<float>(X < 1 ? 1 : X);
+	L.n_contrib = c.take<uint32_t>(X < 1 ? 1 : X);
+	L.ranges = c.take<uint2>(tiles < 1 ? 1 : tiles);
+	L.tile_max = c.take<uint32_t>(tiles < 1 ? 1 : tiles);
+	L.total = c.used();
+	char* b = reinterpret_cast<char*>(blob);
+	L.off[0] = (char*)L.final_T - b; L.off[1] = (char*)L.n_contrib - b; L.off[2] = (char*)L.ranges - b; L.off[3] = (char*)L.tile_max - b;
+	return L;
+}
+
+bool bad_ptr(const void* p, const char* name) { if (!p) { set_error("%s must not be null", name); return true; } return false; }
+
+}  // namespace
+}  // namespace rr
+
+using namespace rr;
+
+extern "C" {
+
+const char* rr_last_error(void) { return g_error.c_str(); }
+int rr_version(void) { return 1; }
+
+size_t rr_geom_bytes(int P) { return geom_layout(nullptr, P).total + 256; }
+size_t rr_image_bytes(int W, int H) { return img_layout(nullptr, W, H).total + 256; }
+size_t rr_binning_bytes(int64_t N, int W, int H) { return bin_layout(nullptr, N, W, H).total + 256; }
+size_t rr_backward_ws_bytes(int64_t N) { return (size_t)(N < 1 ? 1 : N) * PARTIAL_FLOATS * sizeof(float) + 256; }
+
+int rr_geom_layout(int P, int64_t o[9]) { const GeomLayout L = geom_layout(nullptr, P); memcpy(o, L.off, sizeof(L.off)); return 0; }
+int rr_binning_layout(int64_t N, int W, int H, int64_t o[5]) { const BinLayout L = bin_layout(nullptr, N, W, H); memcpy(o, L.off, sizeof(L.off)); return 0; }
+int rr_image_layout(int W, int H, int64_t o[4]) { const ImgLayout L = img_layout(nullptr, W, H); memcpy(o, L.off, sizeof(L.off)); return 0; }
+
+int rr_forward_geom(void* stream_, int P, int D, int M, int W, int H,
+	const float* means3D, const float* shs, const float* colors_precomp, const float* opacities,
+	const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+	const float* viewmatrix, const float* projmatrix, const float* campos,
+	float tan_fovx, float tan_fovy, float low_pass, int prefiltered, int debug,
+	int* radii, void* geom, size_t geom_bytes, int64_t* num_rendered_host)
+{
+	(void)prefiltered;   // the reference only uses it to trap on an inconsistent caller (auxiliary.h:145-149)
+	cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+	if (bad_ptr(num_rendered_host, "num_rendered_host")) return -1;
+	*num_rendered_host = 0;
+	if (P == 0) return 0;                                                  // rasterize_points.cu:72
+	if (P < 0 || W <= 0 || H <= 0) { set_error("bad sizes P=%d W=%d H=%d", P, W, H); return -1; }
+	if (bad_ptr(means3D, "means3D") || bad_ptr(opacities, "opacities") || bad_ptr(viewmatrix, "viewmatrix") || bad_ptr(projmatrix, "projmatrix") ||
+		bad_ptr(campos, "campos") || bad_ptr(radii, "radii") || bad_ptr(geom, "geom")) return -1;
+	if (!shs && !colors_precomp) { set_error("For non-RGB, provide precomputed Gaussian colors!"); return -1; }   // rasterizer_impl.cu:233-236
+	if (!cov3D_precomp && !(scales && rotations)) { set_error("provide scales+rotations or cov3D_precomp"); return -1; }
+	if (shs && !colors_precomp && (D < 0 || D > 3 || (D + 1) * (D + 1) > M)) { set_error("SH degree %d needs %d coefficients, M=%d", D, (D + 1) * (D + 1), M); return -1; }
+	const GeomLayout L = geom_layout(geom, P);
+	if (L.total > geom_bytes) { set_error("geometry blob too small: %zu < %zu", geom_bytes, L.total); return -1; }
+
+	PreprocessArgs a;
+	a.P = P; a.D = D; a.M = M; a.W = W; a.H = H;
+	a.grid_x = (W + TILE_X - 1) / TILE_X; a.grid_y = (H + TILE_Y - 1) / TILE_Y;
+	a.tan_fovx = tan_fovx; a.tan_fovy = tan_fovy;
+	a.focal_y = H / (2.0f * tan_fovy); a.focal_x = W / (2.0f * tan_fovx);       // rasterizer_impl.cu:213-214
+	a.scale_modifier = scale_modifier; a.low_pass = low_pass;
+	a.means3D = means3D; a.scales = scales; a.rotations = rotations; a.opacities = opacities; a.shs = colors_precomp ? nullptr : shs;
+	a.cov3D_precomp = cov3D_precomp; a.colors_precomp = colors_precomp; a.view = viewmatrix; a.proj = projmatrix; a.campos = campos;
+	a.radii = radii; a.rec = L.rec; a.cov3D = L.cov3D; a.clamped = L.clamped; a.tiles_touched = L.tiles_touched; a.depth_key = L.key_a; a.rect = L.rect;
+	if (launch_preprocess_fwd(stream, a)) return -1;
+	if (debug && check_launch("preprocess_fwd", stream, true)) return -1;
+	// depth order of the Gaussians: 32-bit keys, 4 passes, result in the *_a buffers
+	const int which = sort_pairs<uint32_t>(stream, L.key_a, L.key_b, L.val_a, L.val_b, (size_t)P, 0, 32, L.sort_ws, true);
+	if (which != 0) { if (which > 0) set_error("internal: depth sort landed in the wrong buffer"); return -1; }
+	if (debug && check_launch("depth sort", stream, true)) return -1;
+	if (launch_scan_tiles(stream, P, L.val_a, L.tiles_touched, L.offsets, L.block_sums, L.num_rendered)) return -1;
+	// num_rendered: u32 on the device, widened on the host side of the copy (the upper half was zeroed above)
+	cudaMemcpyAsync(num_rendered_host, L.num_rendered, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream);
+	return check_launch("forward_geom", stream, debug != 0);
+}
+
+int rr_forward_raster(void* stream_, int P, int W, int H, int64_t N, const float* background,
+	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes,
+	float* out_color, float* out_depth, int variant, int debug)
+{
+	cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+	if (P == 0) return 0;
+	if (bad_ptr(background, "background") || bad_ptr(geom, "geom") || bad_ptr(binning, "binning") || bad_ptr(image, "image") ||
+		bad_ptr(out_color, "out_color") || bad_ptr(out_depth, "out_depth")) return -1;
+	if (N < 0 || N >= (1ll << 30)) { set_error("num_rendered=%lld out of range", (long long)N); return -1; }
+	const GeomLayout G = geom_layout(geom, P);
+	const BinLayout B = bin_layout(binning, N, W, H);
+	const ImgLayout I = img_layout(image, W, H);
+	if (G.total > geom_bytes || B.total > binning_bytes || I.total > image_bytes) { set_error("scratch blob too small"); return -1; }
+	const int grid_x = (W + TILE_X - 1) / TILE_X, grid_y = (H + TILE_Y - 1) / TILE_Y;
+
+	if (N > 0) {
+		if (launch_duplicate(stream, P, G.val_a, G.offsets, G.rect, grid_x, B.key_a, B.owner, G.dup_off)) return -1;
+		if (debug && check_launch("duplicate", stream, true)) return -1;
+		const int which = sort_pairs<uint32_t>(stream, B.key_a, B.key_b, B.emit_a, B.emit_b, (size_t)N, 0, B.bits, B.sort_ws, true);
+		if (which < 0) return -1;
+		if ((which ? B.key_b : B.key_a) != B.keys_sorted) { set_error("internal: tile sort landed in the wrong buffer"); return -1; }
+		if (debug && check_launch("tile sort", stream, true)) return -1;
+	}
+	if (launch_tile_ranges(stream, (size_t)N, B.keys_sorted, I.ranges, grid_x * grid_y)) return -1;
+	if (launch_pack(stream, (size_t)N, B.emit_sorted, B.owner, G.rec, B.packed, B.point_list)) return -1;
+	if (debug && check_launch("ranges/pack", stream, true)) return -1;
+
+	RenderArgs r; memset(&r, 0, sizeof(r));
+	r.W = W; r.H = H; r.grid_x = grid_x; r.grid_y = grid_y;
+	r.ranges = I.ranges; r.packed = B.packed; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.tile_max_contrib = I.tile_max;
+	r.out_color = out_color; r.out_depth = out_depth; r.variant = variant;
+	if (launch_render_fwd(stream, r)) return -1;
+	return check_launch("forward_raster", stream, debug != 0);
+}
+
+int rr_backward(void* stream_, int P, int D, int M, int W, int H, int64_t N, const float* background,
+	const float* means3D, const float* shs, const float* colors_precomp,
+	const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+	const float* viewmatrix, const float* projmatrix, const float* campos,
+	float tan_fovx, float tan_fovy, float low_pass, const int* radii,
+	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes,
+	const float* dL_dpix, void* ws, size_t ws_bytes,
+	float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+	float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+	int variant, int debug)
+{
+	cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+	if (P == 0) return 0;                                                  // rasterize_points.cu:155
+	if (bad_ptr(background, "background") || bad_ptr(means3D, "means3D") || bad_ptr(radii, "radii") || bad_ptr(geom, "geom") ||
+		bad_ptr(binning, "binning") || bad_ptr(image, "image") || bad_ptr(dL_dpix, "dL_dpix") || bad_ptr(ws, "ws") ||
+		bad_ptr(dL_dmean2D, "dL_dmean2D") || bad_ptr(dL_dopacity, "dL_dopacity") || bad_ptr(dL_dcolor, "dL_dcolor") ||
+		bad_ptr(dL_dmean3D, "dL_dmean3D") || bad_ptr(dL_dcov3D, "dL_dcov3D")) return -1;
+	const bool use_sh = shs && !colors_precomp;
+	if (use_sh && bad_ptr(dL_dsh, "dL_dsh")) return -1;
+	const GeomLayout G = geom_layout(geom, P);
+	const BinLayout B = bin_layout(binning, N, W, H);
+	const ImgLayout I = img_layout(image, W, H);
+	if (G.total > geom_bytes || B.total > binning_bytes || I.total > image_bytes || rr_backward_ws_bytes(N) > ws_bytes + 256) { set_error("scratch blob too small"); return -1; }
+	const int grid_x = (W + TILE_X - 1) / TILE_X, grid_y = (H + TILE_Y - 1) / TILE_Y;
+	float* partial = reinterpret_cast<float*>(ws);
+
+	RenderArgs r; memset(&r, 0, sizeof(r));
+	r.W = W; r.H = H; r.grid_x = grid_x; r.grid_y = grid_y;
+	r.ranges = I.ranges; r.packed = B.packed; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.tile_max_contrib = I.tile_max;
+	r.dL_dpix = dL_dpix; r.sorted_emit = B.emit_sorted; r.partial = partial; r.variant = variant;
+	if (N > 0) {
+		if (launch_render_bwd(stream, r)) return -1;
+		if (debug && check_launch("render_bwd", stream, true)) return -1;
+	}
+
+	PreprocessBwdArgs a; memset(&a, 0, sizeof(a));
+	a.P = P; a.D = D; a.M = M; a.W = W; a.H = H;
+	a.tan_fovx = tan_fovx; a.tan_fovy = tan_fovy; a.focal_y = H / (2.0f * tan_fovy); a.focal_x = W / (2.0f * tan_fovx);
+	a.scale_modifier = scale_modifier; a.low_pass = low_pass;
+	a.means3D = means3D; a.scales = cov3D_precomp ? nullptr : scales; a.rotations = cov3D_precomp ? nullptr : rotations;
+	a.shs = use_sh ? shs : nullptr; a.cov3D = cov3D_precomp ? cov3D_precomp : G.cov3D;        // rasterizer_impl.cu:406
+	a.view = viewmatrix; a.proj = projmatrix; a.campos = campos; a.has_colors_precomp = colors_precomp != nullptr;
+	a.radii = radii; a.clamped = G.clamped; a.tiles_touched = G.tiles_touched; a.dup_off = G.dup_off; a.partial = partial;
+	a.dL_dmean2D = dL_dmean2D; a.dL_dconic = dL_dconic; a.dL_dopacity = dL_dopacity; a.dL_dcolor = dL_dcolor; a.dL_dmean3D = dL_dmean3D;
+	a.dL_dcov3D = dL_dcov3D; a.dL_dsh = dL_dsh; a.dL_dscale = dL_dscale; a.dL_drot = dL_drot;
+	if (launch_preprocess_bwd(stream, a)) return -1;
+	return check_launch("backward", stream, debug != 0);
+}
+
+int rr_mark_visible(void* stream_, int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present)
+{
+	(void)projmatrix;   // in_frustum computes p_proj but only tests view-space z (auxiliary.h:137-143)
+	if (P == 0) return 0;
+	if (bad_ptr(means3D, "means3D") || bad_ptr(viewmatrix, "viewmatrix") || bad_ptr(present, "present")) return -1;
+	return launch_mark_visible(reinterpret_cast<cudaStream_t>(stream_), P, means3D, viewmatrix, present);
+}
+
+size_t rr_dist2_ws_bytes(int P) { return knn_ws_bytes(P); }
+int rr_dist2(void* stream_, int P, const float* points, float* out, void* ws, size_t ws_bytes)
+{
+	if (P == 0) return 0;
+	if (bad_ptr(points, "points") || bad_ptr(out, "out") || bad_ptr(ws, "ws")) return -1;
+	return launch_dist2(reinterpret_cast<cudaStream_t>(stream_), P, points, out, ws, ws_bytes);
+}
+
+size_t rr_sort_ws_bytes(int64_t n, int key_bytes, int begin_bit, int end_bit)
+{
+	return key_bytes == 8 ? sort_ws_bytes<uint64_t>((size_t)n, begin_bit, end_bit) : sort_ws_bytes<uint32_t>((size_t)n, begin_bit, end_bit);
+}
+
+}  // extern "C"
+
+template <class K>
+static int sort_entry(void* stream_, int64_t n, K* keys_in, K* keys_out, uint32_t* vals_in, uint32_t* vals_out, int begin_bit, int end_bit, void* ws)
+{
+	cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+	if (n == 0) return 0;
+	if (bad_ptr(keys_in, "keys_in") || bad_ptr(keys_out, "keys_out") || bad_ptr(vals_out, "vals_out") || bad_ptr(ws, "ws")) return -1;
+	uint32_t* va = vals_in;
+	const bool iota = vals_in == nullptr;
+	if (iota) { set_error("vals_in must be a scratch buffer even for identity values"); return -1; }
+	const int which = sort_pairs<K>(stream, keys_in, keys_out, va, vals_out, (size_t)n, begin_bit, end_bit, ws, false);
+	if (which < 0) return -1;
+	if (which == 0) {
+		cudaMemcpyAsync(keys_out, keys_in, sizeof(K) * (size_t)n, cudaMemcpyDeviceToDevice, stream);
+		cudaMemcpyAsync(vals_out, va, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToDevice, stream);
+	}
+	return check_launch("sort_pairs", stream, false);
+}
+
+extern "C" {
+
+int rr_sort_pairs_u32(void* stream, int64_t n, uint32_t* keys_in, uint32_t* keys_out, uint32_t* vals_in, uint32_t* vals_out, int begin_bit, int end_bit, void* ws)
+{ return sort_entry<uint32_t>(stream, n, keys_in, keys_out, vals_in, vals_out, begin_bit, end_bit, ws); }
+int rr_sort_pairs_u64(void* stream, int64_t n, uint64_t* keys_in, uint64_t* keys_out, uint32_t* vals_in, uint32_t* vals_out, int begin_bit, int end_bit, void* ws)
+{ return sort_entry<uint64_t>(stream, n, keys_in, keys_out, vals_in, vals_out, begin_bit, end_bit, ws); }
+
+int rr_export_sorted_keys(void* stream_, int P, int64_t N, int W, int H, void* geom, void* binning, uint64_t* keys_out)
+{
+	if (N == 0) return 0;
+	const GeomLayout G = geom_layout(geom, P);
+	const BinLayout B = bin_layout(binning, N, W, H);
+	// depth bits live in rec.c.y (float index 9 of the 12-float record)
+	return launch_export_keys(reinterpret_cast<cudaStream_t>(stream_), (size_t)N, B.keys_sorted, B.point_list,
+		reinterpret_cast<const uint32_t*>(G.rec), keys_out);
+}
+
+}  // extern "C"

@@ -1,0 +1,217 @@
+// Tile binning: prefix sum of tiles_touched, (tile, Gaussian) duplicate emission, tile ranges, record packing.
+// Replaces cub::DeviceScan::InclusiveSum (reference rasterizer_impl.cu:269), duplicateWithKeys (:59-100),
+// identifyTileRanges (:105-127) and the cudaMemset of ranges (:302).
+//
+// Ordering.  The reference sorts N (tile<<32 | depth_bits) keys with 6 radix passes.  Here the P Gaussians are first
+// sorted by depth bits (4 passes over P items), duplicates are then emitted in that depth order, and a stable sort
+// on the tile id alone (ceil(bits/8) = 2 passes over N at every supported resolution) yields exactly the same
+// (tile, depth, index) order: ties in (tile, depth) keep ascending Gaussian index in both schemes, because both
+// sorts are stable and the depth sort starts from index order.  The 64-bit key list the reference would hold is
+// reconstructed on demand by export_keys_kernel for the parity tests.
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace rr {
+
+namespace {
+
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 4;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* s_warp /*[8]*/, uint32_t& block_total)
+{
+	const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
+	uint32_t inc = v;
+	#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(FULL, inc, o); if (lane >= (unsigned)o) inc += t; }
+	if (lane == 31) s_warp[warp] = inc;
+	__syncthreads();
+	uint32_t pre = 0, tot = 0;
+	#pragma unroll
+	for (int w = 0; w < SCAN_THREADS / 32; w++) { const uint32_t t = s_warp[w]; if (w < (int)warp) pre += t; tot += t; }
+	block_total = tot;
+	__syncthreads();
+	return pre + inc - v;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_reduce_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ tt, uint32_t* __restrict__ block_sums)
+{
+	__shared__ uint32_t s_warp[SCAN_THREADS / 32];
+	uint32_t sum = 0;
+	#pragma unroll
+	for (int k = 0; k < SCAN_ITEMS; k++) {
+		const int i = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS + k;
+		if (i < P) sum += tt[order[i]];
+	}
+	uint32_t tot;
+	block_exclusive_scan(sum, s_warp, tot);
+	if (threadIdx.x == 0) block_sums[blockIdx.x] = tot;
+}
+
+// single CTA: exclusive scan of the block sums in place, grand total to *total
+__global__ void __launch_bounds__(SCAN_THREADS) scan_blocksums_kernel(int nb, uint32_t* __restrict__ block_sums, uint32_t* __restrict__ total)
+{
+	__shared__ uint32_t s_warp[SCAN_THREADS / 32];
+	uint32_t carry = 0;
+	for (int base = 0; base < nb; base += SCAN_THREADS) {
+		const int i = base + threadIdx.x;
+		const uint32_t v = i < nb ? block_sums[i] : 0;
+		uint32_t tot;
+		const uint32_t ex = block_exclusive_scan(v, s_warp, tot);
+		if (i < nb) block_sums[i] = carry + ex;
+		carry += tot;
+	}
+	if (threadIdx.x == 0) *total = carry;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_final_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ tt,
+	const uint32_t* __restrict__ block_excl, uint32_t* __restrict__ offsets)
+{
+	__shared__ uint32_t s_warp[SCAN_THREADS / 32];
+	uint32_t v[SCAN_ITEMS], sum = 0;
+	#pragma unroll
+	for (int k = 0; k < SCAN_ITEMS; k++) {
+		const int i = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS + k;
+		v[k] = i < P ? tt[order[i]] : 0;
+		sum += v[k];
+	}
+	uint32_t tot;
+	uint32_t run = block_excl[blockIdx.x] + block_exclusive_scan(sum, s_warp, tot);
+	#pragma unroll
+	for (int k = 0; k < SCAN_ITEMS; k++) {
+		const int i = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS + k;
+		run += v[k];
+		if (i < P) offsets[i] = run;
+	}
+}
+
+// One warp emits the duplicates of 32 consecutive depth-sorted Gaussians cooperatively: output slot s of the warp's
+// contiguous span is owned by the last lane whose exclusive offset is <= s (binary search over 32 shared values),
+// so writes are coalesced and a large splat does not serialise on one thread (reference: one thread per rect).
+__global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ offsets,
+	const uint2* __restrict__ rect, int grid_x, uint32_t* __restrict__ tile_keys, uint32_t* __restrict__ owner, uint32_t* __restrict__ dup_off)
+{
+	__shared__ uint32_t s_excl[8][32];
+	__shared__ uint32_t s_g[8][32];
+	__shared__ uint32_t s_xw[8][32];   // x0 | width<<16
+	__shared__ uint32_t s_y0[8][32];
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const int i = blockIdx.x * 256 + threadIdx.x;
+	uint32_t g = 0, excl = 0, incl = 0;
+	if (i < P) {
+		g = order[i];
+		incl = offsets[i];
+		excl = i == 0 ? 0u : offsets[i - 1];
+	}
+	const int last_valid = min(31, P - 1 - (blockIdx.x * 256 + warp * 32));   // >= 0 for any warp that has work
+	if (last_valid < 0) return;                                                 // warp-uniform
+	const uint32_t base = __shfl_sync(FULL, excl, 0);
+	const uint32_t end = __shfl_sync(FULL, incl, last_valid);
+	const uint32_t total = end - base;
+	const uint32_t tt = i < P ? incl - excl : 0u;
+	uint32_t x0 = 0, wdt = 1, y0 = 0;
+	if (tt > 0) {
+		const uint2 r = rect[g];
+		x0 = r.x & 0xffffu; wdt = (r.x >> 16) - x0; y0 = r.y & 0xffffu;
+		dup_off[g] = excl;
+	}
+	s_excl[warp][lane] = i < P ? excl - base : total;
+	s_g[warp][lane] = g;
+	s_xw[warp][lane] = x0 | (wdt << 16);
+	s_y0[warp][lane] = y0;
+	__syncwarp();
+	for (uint32_t s = lane; s < total; s += 32) {
+		// last j with s_excl[j] <= s
+		int lo = 0;
+		#pragma unroll
+		for (int step = 16; step >= 1; step >>= 1) if (s_excl[warp][lo + step] <= s) lo += step;
+		const uint32_t local = s - s_excl[warp][lo];
+		const uint32_t xw = s_xw[warp][lo];
+		const uint32_t w = xw >> 16, xx0 = xw & 0xffffu;
+		const uint32_t ry = local / w, rx = local - ry * w;
+		tile_keys[base + s] = (s_y0[warp][lo] + ry) * (uint32_t)grid_x + xx0 + rx;
+		owner[base + s] = s_g[warp][lo];
+	}
+}
+
+__global__ void __launch_bounds__(256) tile_ranges_kernel(uint32_t N, const uint32_t* __restrict__ keys, uint2* __restrict__ ranges)
+{
+	const uint32_t idx = blockIdx.x * 256 + threadIdx.x;
+	if (idx >= N) return;
+	const uint32_t cur = keys[idx];
+	if (idx == 0) ranges[cur].x = 0;
+	else {
+		const uint32_t prev = keys[idx - 1];
+		if (cur != prev) { ranges[prev].y = idx; ranges[cur].x = idx; }
+	}
+	if (idx == N - 1) ranges[cur].y = N;
+}
+
+// packed[j] = rec[owner[sorted_emit[j]]]; three threads move one 48-byte record (one float4 each)
+__global__ void __launch_bounds__(256) pack_kernel(uint32_t N, const uint32_t* __restrict__ sorted_emit, const uint32_t* __restrict__ owner,
+	const float4* __restrict__ rec, float4* __restrict__ packed, uint32_t* __restrict__ point_list)
+{
+	const size_t t = (size_t)blockIdx.x * 256 + threadIdx.x;
+	if (t >= (size_t)N * 3) return;
+	const uint32_t j = (uint32_t)(t / 3), part = (uint32_t)(t - (size_t)j * 3);
+	const uint32_t g = owner[sorted_emit[j]];
+	packed[t] = __ldg(&rec[(size_t)g * 3 + part]);
+	if (part == 0) point_list[j] = g;
+}
+
+__global__ void __launch_bounds__(256) export_keys_kernel(uint32_t N, const uint32_t* __restrict__ tile_keys, const uint32_t* __restrict__ point_list,
+	const uint32_t* __restrict__ rec_words, uint64_t* __restrict__ out)
+{
+	const uint32_t j = blockIdx.x * 256 + threadIdx.x;
+	if (j >= N) return;
+	// depth bits = float index 9 (c.y) of the Gaussian's 12-float record
+	out[j] = ((uint64_t)tile_keys[j] << 32) | rec_words[(size_t)point_list[j] * 12 + 9];
+}
+
+}  // namespace
+
+size_t scan_ws_elems(int P) { return (size_t)(P + SCAN_TILE - 1) / SCAN_TILE + 1; }
+
+int launch_scan_tiles(cudaStream_t stream, int P, const uint32_t* order, const uint32_t* tt, uint32_t* offsets, uint32_t* block_sums, uint32_t* num_rendered_dev)
+{
+	if (P == 0) { cudaMemsetAsync(num_rendered_dev, 0, sizeof(uint32_t), stream); return 0; }
+	const int nb = (P + SCAN_TILE - 1) / SCAN_TILE;
+	scan_reduce_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, order, tt, block_sums);
+	scan_blocksums_kernel<<<1, SCAN_THREADS, 0, stream>>>(nb, block_sums, num_rendered_dev);
+	scan_final_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, order, tt, block_sums, offsets);
+	return check_launch("scan_tiles", stream, false);
+}
+
+int launch_duplicate(cudaStream_t stream, int P, const uint32_t* order, const uint32_t* offsets, const uint2* rect, int grid_x,
+	uint32_t* tile_keys, uint32_t* owner, uint32_t* dup_off)
+{
+	if (P == 0) return 0;
+	duplicate_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, order, offsets, rect, grid_x, tile_keys, owner, dup_off);
+	return check_launch("duplicate", stream, false);
+}
+
+int launch_tile_ranges(cudaStream_t stream, size_t N, const uint32_t* keys, uint2* ranges, int num_tiles)
+{
+	cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)num_tiles, stream);
+	if (N == 0) return 0;
+	tile_ranges_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>((uint32_t)N, keys, ranges);
+	return check_launch("tile_ranges", stream, false);
+}
+
+int launch_pack(cudaStream_t stream, size_t N, const uint32_t* sorted_emit, const uint32_t* owner, const SplatRec* rec, SplatRec* packed, uint32_t* point_list)
+{
+	if (N == 0) return 0;
+	pack_kernel<<<(unsigned)((N * 3 + 255) / 256), 256, 0, stream>>>((uint32_t)N, sorted_emit, owner, reinterpret_cast<const float4*>(rec),
+		reinterpret_cast<float4*>(packed), point_list);
+	return check_launch("pack", stream, false);
+}
+
+int launch_export_keys(cudaStream_t stream, size_t N, const uint32_t* tile_keys, const uint32_t* point_list, const uint32_t* rec_words, uint64_t* out)
+{
+	if (N == 0) return 0;
+	export_keys_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>((uint32_t)N, tile_keys, point_list, rec_words, out);
+	return check_launch("export_keys", stream, false);
+}
+
+}  // namespace rr

@@ -1,0 +1,73 @@
+// Launcher interfaces between the C-ABI layer (api.cu) and the kernel translation units.
+#pragma once
+#include "common.cuh"
+
+namespace rr {
+
+struct PreprocessArgs {
+	int P, D, M, W, H, grid_x, grid_y;
+	float tan_fovx, tan_fovy, focal_x, focal_y, scale_modifier, low_pass;
+	const float *means3D, *scales, *rotations, *opacities, *shs, *cov3D_precomp, *colors_precomp, *view, *proj, *campos;
+	int* radii;               // [P] user-visible output
+	SplatRec* rec;            // [P] projected record (valid where radii > 0)
+	float* cov3D;             // [P,6]
+	uint8_t* clamped;         // [P] bit ch set if colour channel ch was clamped at 0
+	uint32_t* tiles_touched;  // [P]
+	uint32_t* depth_key;      // [P] float bits of view-space depth, 0xFFFFFFFF when culled
+	uint2* rect;              // [P] x0 | x1<<16, y0 | y1<<16
+};
+int launch_preprocess_fwd(cudaStream_t, const PreprocessArgs&);
+int launch_mark_visible(cudaStream_t, int P, const float* means3D, const float* view, uint8_t* present);
+
+// binning.cu
+size_t scan_ws_elems(int P);
+int launch_scan_tiles(cudaStream_t, int P, const uint32_t* order, const uint32_t* tiles_touched, uint32_t* offsets /*inclusive, sorted order*/,
+	uint32_t* block_sums, uint32_t* num_rendered_dev);
+int launch_duplicate(cudaStream_t, int P, const uint32_t* order, const uint32_t* offsets, const uint2* rect, int grid_x,
+	uint32_t* tile_keys /*[N]*/, uint32_t* owner /*[N]*/, uint32_t* dup_off /*[P]*/);
+int launch_tile_ranges(cudaStream_t, size_t N, const uint32_t* sorted_tile_keys, uint2* ranges, int num_tiles);
+int launch_pack(cudaStream_t, size_t N, const uint32_t* sorted_emit, const uint32_t* owner, const SplatRec* rec,
+	SplatRec* packed, uint32_t* point_list);
+int launch_export_keys(cudaStream_t, size_t N, const uint32_t* sorted_tile_keys, const uint32_t* point_list, const uint32_t* rec_words, uint64_t* out);
+
+// render_fwd.cu / render_bwd.cu
+struct RenderArgs {
+	int W, H, grid_x, grid_y;
+	const uint2* ranges;        // [tiles]
+	const SplatRec* packed;     // [N] in sorted (tile, depth) order
+	const float* bg;            // [3]
+	float* final_T;             // [H*W]
+	uint32_t* n_contrib;        // [H*W]
+	uint32_t* tile_max_contrib; // [tiles] max n_contrib over the tile's pixels (written by forward, read by backward)
+	float* out_color;           // [3,H,W]
+	float* out_depth;           // [H,W]
+	// backward only
+	const float* dL_dpix;       // [3,H,W]
+	const uint32_t* sorted_emit;// [N] emission index of each sorted entry
+	float* partial;             // [N, PARTIAL_FLOATS] indexed by emission index
+	int variant;                // 0 = cooperative loads, 1 = TMA bulk staging
+};
+int launch_render_fwd(cudaStream_t, const RenderArgs&);
+int launch_render_bwd(cudaStream_t, const RenderArgs&);
+
+// preprocess_bwd.cu
+struct PreprocessBwdArgs {
+	int P, D, M, W, H;
+	float tan_fovx, tan_fovy, focal_x, focal_y, scale_modifier, low_pass;
+	const float *means3D, *scales, *rotations, *shs, *cov3D /*precomp or geom*/, *view, *proj, *campos;
+	int has_colors_precomp;
+	const int* radii;
+	const uint8_t* clamped;
+	const uint32_t* tiles_touched;
+	const uint32_t* dup_off;
+	const float* partial;
+	float *dL_dmean2D /*[P,3]*/, *dL_dconic /*[P,4] or null*/, *dL_dopacity /*[P]*/, *dL_dcolor /*[P,3]*/, *dL_dmean3D /*[P,3]*/,
+		*dL_dcov3D /*[P,6]*/, *dL_dsh /*[P,M,3]*/, *dL_dscale /*[P,3]*/, *dL_drot /*[P,4]*/;
+};
+int launch_preprocess_bwd(cudaStream_t, const PreprocessBwdArgs&);
+
+// knn.cu
+size_t knn_ws_bytes(int P);
+int launch_dist2(cudaStream_t, int P, const float* points, float* out, void* ws, size_t ws_bytes);
+
+}  // namespace rr

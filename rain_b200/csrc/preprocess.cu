@@ -1,0 +1,273 @@
+// Forward preprocess: per-Gaussian cull, 3D covariance, EWA projection to a 2D conic, SH colour, radius / tile rect.
+// Replaces preprocessCUDA<3> (reference forward.cu:144-246, with computeCov3D :107-141, computeCov2D :63-102,
+// computeColorFromSH :9-60, in_frustum auxiliary.h:128-153, ndc2Pix :30-33, getRect :35-45) and checkFrustum
+// (rasterizer_impl.cu:43-55).
+//
+// Integer outputs (radii, tile rects, depth key bits) must be bit-identical to the reference build, so every
+// rounding step on the path to them is written with explicit round-to-nearest intrinsics (__fmaf_rn / __fmul_rn /
+// __fadd_rn / __fdiv_rn / __fsqrt_rn) in the order the reference's nvcc build performs them ("FMA
+// contract"); the compiler can neither contract nor reassociate these.
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace rr {
+
+namespace {
+
+#define FMA(a, b, c) __fmaf_rn((a), (b), (c))
+#define MUL(a, b) __fmul_rn((a), (b))
+#define ADD(a, b) __fadd_rn((a), (b))
+#define SUB(a, b) __fsub_rn((a), (b))
+#define DIV(a, b) __fdiv_rn((a), (b))
+
+__device__ __forceinline__ float sop3(float a, float b, float c, float d, float e, float f) { return FMA(e, f, FMA(a, b, MUL(c, d))); }
+// column `col` of the row-vector transform: m[col]*x + m[4+col]*y + m[8+col]*z + m[12+col]
+__device__ __forceinline__ float xform(const float* __restrict__ m, int col, float x, float y, float z) {
+	return ADD(m[12 + col], sop3(x, m[col], y, m[4 + col], z, m[8 + col]));
+}
+
+__constant__ float c_SH_C2[5] = { 1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f, -1.0925484305920792f, 0.5462742152960396f };
+__constant__ float c_SH_C3[7] = { -0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f, 0.3731763325901154f, -0.4570457994644658f, 1.445305721320277f, -0.5900435899266435f };
+constexpr float kSH_C0 = 0.28209479177387814f;
+constexpr float kSH_C1 = 0.4886025119029199f;
+
+__device__ __forceinline__ void cov3d_from_scale_rot(float s0, float s1, float s2, float mod, float4 q, float* c)
+{
+	const float sx = MUL(mod, s0), sy = MUL(mod, s1), sz = MUL(mod, s2);
+	const float r = q.x, x = q.y, y = q.z, z = q.w;
+	const float xz = MUL(x, z), A = FMA(r, y, xz), B = FMA(-r, y, xz);
+	const float rx = MUL(r, x), C = FMA(y, z, -rx), Dd = FMA(y, z, rx);
+	const float rz = MUL(r, z), E = FMA(x, y, -rz), F = FMA(x, y, rz);
+	const float yy = MUL(y, y), zz = MUL(z, z), G = FMA(x, x, yy), Hh = ADD(yy, zz), I = FMA(x, x, zz);
+	const float R00 = SUB(1.f, ADD(Hh, Hh)), R01 = ADD(E, E), R02 = ADD(A, A);
+	const float R10 = ADD(F, F), R11 = SUB(1.f, ADD(I, I)), R12 = ADD(C, C);
+	const float R20 = ADD(B, B), R21 = ADD(Dd, Dd), R22 = SUB(1.f, ADD(G, G));
+	const float z0 = 0.0f;
+	const float M00 = FMA(R02, z0, FMA(R01, z0, MUL(sx, R00)));
+	const float t0 = MUL(R00, z0);
+	const float M01 = FMA(R02, z0, FMA(sy, R01, t0));
+	const float M02 = FMA(sz, R02, FMA(R01, z0, t0));
+	const float t1 = MUL(R11, z0);
+	const float M10 = FMA(R12, z0, FMA(sx, R10, t1));
+	const float M11 = FMA(R12, z0, FMA(R10, z0, MUL(sy, R11)));
+	const float M12 = FMA(sz, R12, FMA(R10, z0, t1));
+	const float t2 = MUL(R21, z0);
+	const float M20 = FMA(R22, z0, FMA(sx, R20, t2));
+	const float M21 = FMA(R22, z0, FMA(R20, z0, MUL(sy, R21)));
+	const float M22 = FMA(sz, R22, FMA(R20, z0, t2));
+	c[0] = sop3(M00, M00, M01, M01, M02, M02);
+	c[1] = sop3(M10, M00, M11, M01, M12, M02);
+	c[2] = sop3(M20, M00, M21, M01, M22, M02);
+	c[3] = sop3(M10, M10, M11, M11, M12, M12);
+	c[4] = sop3(M20, M10, M21, M11, M22, M12);
+	c[5] = sop3(M20, M20, M21, M21, M22, M22);
+}
+
+__global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreprocessArgs a)
+{
+	const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+	if (idx >= a.P) return;
+	const float* __restrict__ V = a.view;
+	const float* __restrict__ Pm = a.proj;
+
+	const float px = a.means3D[3 * (size_t)idx], py = a.means3D[3 * (size_t)idx + 1], pz = a.means3D[3 * (size_t)idx + 2];
+	const float view_z = xform(V, 2, px, py, pz);
+
+	int radius = 0;
+	uint32_t tiles = 0, depth_key = 0xFFFFFFFFu;
+	uint2 rect = make_uint2(0u, 0u);
+	bool visible = false;
+	float conx = 0, cony = 0, conz = 0, pix_x = 0, pix_y = 0;
+
+	if (!(view_z <= 0.2f)) {
+		const float hx = xform(Pm, 0, px, py, pz), hy = xform(Pm, 1, px, py, pz), hw = xform(Pm, 3, px, py, pz);
+		const float p_w = DIV(1.0f, ADD(hw, 0.0000001f));
+		const float projx = MUL(hx, p_w), projy = MUL(hy, p_w);
+		float c3[6];
+		if (a.cov3D_precomp) {
+			#pragma unroll
+			for (int k = 0; k < 6; k++) c3[k] = a.cov3D_precomp[6 * (size_t)idx + k];
+		} else {
+			const float4 q = reinterpret_cast<const float4*>(a.rotations)[idx];
+			cov3d_from_scale_rot(a.scales[3 * (size_t)idx], a.scales[3 * (size_t)idx + 1], a.scales[3 * (size_t)idx + 2], a.scale_modifier, q, c3);
+			#pragma unroll
+			for (int k = 0; k < 6; k++) a.cov3D[6 * (size_t)idx + k] = c3[k];     // written even if culled below (forward.cu:201)
+		}
+		// computeCov2D
+		const float tx0 = xform(V, 0, px, py, pz), ty0 = xform(V, 1, px, py, pz), tz = view_z;
+		const float limx = MUL(a.tan_fovx, 1.3f), limy = MUL(a.tan_fovy, 1.3f);
+		const float cx = fminf(limx, fmaxf(-limx, DIV(tx0, tz)));
+		const float cy = fminf(limy, fmaxf(-limy, DIV(ty0, tz)));
+		const float tz2 = MUL(tz, tz);
+		const float J00 = DIV(a.focal_x, tz);
+		const float J02 = DIV(MUL(a.focal_x, MUL(cx, -tz)), tz2);
+		const float J11 = DIV(a.focal_y, tz);
+		const float J12 = DIV(MUL(a.focal_y, MUL(cy, -tz)), tz2);
+		const float z0 = 0.0f;
+		const float T00 = FMA(V[2], J02, FMA(V[0], J00, MUL(V[1], z0)));
+		const float T01 = FMA(V[6], J02, FMA(V[4], J00, MUL(V[5], z0)));
+		const float T02 = FMA(J02, V[10], FMA(V[8], J00, MUL(V[9], z0)));
+		const float T10 = FMA(V[2], J12, FMA(V[0], z0, MUL(J11, V[1])));
+		const float T11 = FMA(V[6], J12, FMA(V[4], z0, MUL(J11, V[5])));
+		const float T12 = FMA(J12, V[10], FMA(V[8], z0, MUL(J11, V[9])));
+		const float A00 = sop3(T00, c3[0], T01, c3[1], T02, c3[2]);
+		const float A01 = sop3(T10, c3[0], T11, c3[1], T12, c3[2]);
+		const float A10 = sop3(T00, c3[1], T01, c3[3], T02, c3[4]);
+		const float A11 = sop3(T10, c3[1], T11, c3[3], T12, c3[4]);
+		const float A20 = sop3(T00, c3[2], T01, c3[4], T02, c3[5]);
+		const float A21 = sop3(T10, c3[2], T11, c3[4], T12, c3[5]);
+		const float covx = ADD(a.low_pass, sop3(T00, A00, T01, A10, T02, A20));
+		const float covy = sop3(T00, A01, T01, A11, T02, A21);
+		const float covz = ADD(a.low_pass, sop3(T10, A01, T11, A11, T12, A21));
+
+		const float det = FMA(covx, covz, -MUL(covy, covy));
+		if (det != 0.0f) {
+			const float det_inv = DIV(1.f, det);
+			conx = MUL(covz, det_inv); cony = MUL(det_inv, -covy); conz = MUL(covx, det_inv);
+			const float mid = MUL(ADD(covx, covz), 0.5f);
+			const float sq = __fsqrt_rn(fmaxf(FMA(mid, mid, -det), 0.1f));
+			const float lam = fmaxf(ADD(mid, sq), SUB(mid, sq));
+			const float my_radius = ceilf(MUL(__fsqrt_rn(lam), 3.f));
+			// ndc2Pix in double, as the reference's 1.0 / 0.5 literals force it (auxiliary.h:30-33)
+			pix_x = (float)__dmul_rn(__fma_rn(__dadd_rn((double)projx, 1.0), (double)a.W, -1.0), 0.5);
+			pix_y = (float)__dmul_rn(__fma_rn(__dadd_rn((double)projy, 1.0), (double)a.H, -1.0), 0.5);
+			const int r_i = (int)my_radius;
+			const float r_f = (float)r_i;
+			// getRect
+			const uint32_t x0 = min((uint32_t)a.grid_x, (uint32_t)max(0, (int)MUL(SUB(pix_x, r_f), 0.0625f)));
+			const uint32_t y0 = min((uint32_t)a.grid_y, (uint32_t)max(0, (int)MUL(SUB(pix_y, r_f), 0.0625f)));
+			const uint32_t x1 = min((uint32_t)a.grid_x, (uint32_t)max(0, (int)MUL(ADD(ADD(ADD(pix_x, r_f), 16.0f), -1.0f), 0.0625f)));
+			const uint32_t y1 = min((uint32_t)a.grid_y, (uint32_t)max(0, (int)MUL(ADD(ADD(ADD(pix_y, r_f), 16.0f), -1.0f), 0.0625f)));
+			const uint32_t area = (x1 - x0) * (y1 - y0);
+			if (area != 0) {
+				visible = true;
+				radius = r_i;
+				tiles = area;
+				rect = make_uint2(x0 | (x1 << 16), y0 | (y1 << 16));
+				depth_key = __float_as_uint(view_z);
+			}
+		}
+	}
+
+	a.radii[idx] = radius;
+	a.tiles_touched[idx] = tiles;
+	a.depth_key[idx] = depth_key;
+	if (!visible) return;
+	a.rect[idx] = rect;
+
+	// colour
+	float rgb0, rgb1, rgb2;
+	uint8_t clamped = 0;
+	if (a.colors_precomp) {
+		rgb0 = a.colors_precomp[3 * (size_t)idx]; rgb1 = a.colors_precomp[3 * (size_t)idx + 1]; rgb2 = a.colors_precomp[3 * (size_t)idx + 2];
+	} else {
+		const float dx = SUB(px, a.campos[0]), dy = SUB(py, a.campos[1]), dz = SUB(pz, a.campos[2]);
+		const float len = __fsqrt_rn(sop3(dx, dx, dy, dy, dz, dz));
+		const float x = DIV(dx, len), y = DIV(dy, len), z = DIV(dz, len);
+		// SH coefficients of the active degree only: (D+1)^2 x 3 floats, fetched as float4 when the row is the usual
+		// 16 x 3 = 192-byte aligned row, scalar otherwise
+		float sh[48];
+		{
+			const int nfl = (a.D + 1) * (a.D + 1) * 3;
+			const float* __restrict__ row = a.shs + (size_t)idx * a.M * 3;
+			if (a.M == 16 && (reinterpret_cast<uintptr_t>(a.shs) & 15) == 0) {
+				const float4* __restrict__ row4 = reinterpret_cast<const float4*>(row);
+				#pragma unroll
+				for (int i = 0; i < 12; i++) {
+					if (4 * i < nfl) { const float4 v = __ldg(row4 + i); sh[4 * i] = v.x; sh[4 * i + 1] = v.y; sh[4 * i + 2] = v.z; sh[4 * i + 3] = v.w; }
+				}
+			} else {
+				#pragma unroll
+				for (int i = 0; i < 48; i++) if (i < nfl && i < a.M * 3) sh[i] = row[i];
+			}
+		}
+		float res[3];
+		#pragma unroll
+		for (int ch = 0; ch < 3; ch++) res[ch] = MUL(sh[ch], kSH_C0);
+		if (a.D > 0) {
+			const float ca = MUL(y, kSH_C1), cb = MUL(z, kSH_C1), cc = MUL(x, kSH_C1);
+			#pragma unroll
+			for (int ch = 0; ch < 3; ch++) {
+				float r = FMA(-ca, sh[3 + ch], res[ch]);
+				r = FMA(cb, sh[6 + ch], r);
+				res[ch] = FMA(-cc, sh[9 + ch], r);
+			}
+			if (a.D > 1) {
+				const float xx = MUL(x, x), yy = MUL(y, y), zz = MUL(z, z), xy = MUL(x, y), yz = MUL(y, z), xz = MUL(x, z);
+				const float zz2 = ADD(zz, zz);
+				const float t4 = MUL(xy, c_SH_C2[0]), t5 = MUL(yz, c_SH_C2[1]), t6 = MUL(SUB(SUB(zz2, xx), yy), c_SH_C2[2]), t7 = MUL(xz, c_SH_C2[3]);
+				const float xx_yy = SUB(xx, yy), t8 = MUL(xx_yy, c_SH_C2[4]);
+				#pragma unroll
+				for (int ch = 0; ch < 3; ch++) {
+					float r = FMA(t4, sh[12 + ch], res[ch]);
+					r = FMA(t5, sh[15 + ch], r);
+					r = FMA(t6, sh[18 + ch], r);
+					r = FMA(t7, sh[21 + ch], r);
+					res[ch] = FMA(t8, sh[24 + ch], r);
+				}
+				if (a.D > 2) {
+					const float t9 = MUL(MUL(y, c_SH_C3[0]), FMA(xx, 3.0f, -yy));
+					const float t10 = MUL(z, MUL(xy, c_SH_C3[1]));
+					const float q4 = SUB(FMA(zz, 4.0f, -xx), yy);
+					const float t11 = MUL(MUL(y, c_SH_C3[2]), q4);
+					const float t12 = MUL(MUL(z, c_SH_C3[3]), FMA(yy, -3.0f, FMA(xx, -3.0f, zz2)));
+					const float t13 = MUL(MUL(x, c_SH_C3[4]), q4);
+					const float t14 = MUL(MUL(z, c_SH_C3[5]), xx_yy);
+					const float t15 = MUL(MUL(x, c_SH_C3[6]), FMA(yy, -3.0f, xx));
+					#pragma unroll
+					for (int ch = 0; ch < 3; ch++) {
+						float r = FMA(t9, sh[27 + ch], res[ch]);
+						r = FMA(t10, sh[30 + ch], r);
+						r = FMA(t11, sh[33 + ch], r);
+						r = FMA(t12, sh[36 + ch], r);
+						r = FMA(t13, sh[39 + ch], r);
+						r = FMA(t14, sh[42 + ch], r);
+						res[ch] = FMA(t15, sh[45 + ch], r);
+					}
+				}
+			}
+		}
+		const float v0 = ADD(res[0], 0.5f), v1 = ADD(res[1], 0.5f), v2 = ADD(res[2], 0.5f);
+		clamped = (v0 < 0.0f ? 1 : 0) | (v1 < 0.0f ? 2 : 0) | (v2 < 0.0f ? 4 : 0);
+		rgb0 = v0 < 0.0f ? 0.0f : v0; rgb1 = v1 < 0.0f ? 0.0f : v1; rgb2 = v2 < 0.0f ? 0.0f : v2;
+	}
+	a.clamped[idx] = clamped;
+
+	// cull threshold for the render kernels: a pair can only reach alpha >= 1/255 if power >= thr (conservative
+	// margin; -inf disables culling for a conic that is not positive definite or an opacity outside (0, inf))
+	const float opacity = a.opacities[idx];
+	float thr = -__logf(255.0f * opacity) - 1e-3f;
+	if (!(conx > 0.0f && conz > 0.0f && conx * conz - cony * cony > 0.0f) || !(opacity > 0.0f) || !(thr == thr)) thr = -INFINITY;
+
+	SplatRec rec;
+	rec.a = make_float4(pix_x, pix_y, conx, cony);
+	rec.b = make_float4(conz, opacity, rgb0, rgb1);
+	rec.c = make_float4(rgb2, view_z, thr, 0.0f);
+	a.rec[idx] = rec;
+}
+
+__global__ void __launch_bounds__(256) mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view, uint8_t* __restrict__ present)
+{
+	const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+	if (idx >= P) return;
+	const float z = xform(view, 2, means3D[3 * (size_t)idx], means3D[3 * (size_t)idx + 1], means3D[3 * (size_t)idx + 2]);
+	present[idx] = z > 0.2f ? 1 : 0;
+}
+
+}  // namespace
+
+int launch_preprocess_fwd(cudaStream_t stream, const PreprocessArgs& a)
+{
+	if (a.P == 0) return 0;
+	preprocess_fwd_kernel<<<(a.P + 255) / 256, 256, 0, stream>>>(a);
+	return check_launch("preprocess_fwd", stream, false);
+}
+
+int launch_mark_visible(cudaStream_t stream, int P, const float* means3D, const float* view, uint8_t* present)
+{
+	if (P == 0) return 0;
+	mark_visible_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, means3D, view, present);
+	return check_launch("mark_visible", stream, false);
+}
+
+}  // namespace rr

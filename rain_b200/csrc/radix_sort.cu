@@ -1,0 +1,272 @@
+// Hand-written onesweep LSD radix sort (key/value pairs, stable, ascending) for sm_100a.
+//
+// Replaces the reference's cub::DeviceRadixSort::SortPairs calls (rasterizer_impl.cu:295-300 — u64 tile|depth keys,
+// u32 Gaussian index values, bits [0, 32+bit); simple_knn.cu:199-202 — u32 Morton keys).  Structure:
+//   1. one histogram kernel builds the 256-bin digit histograms of ALL passes in a single read of the keys;
+//   2. a tiny kernel turns them into exclusive digit bases;
+//   3. one kernel per 8-bit pass ("onesweep"): every CTA takes a tile of keys (tile ids are handed out by an atomic
+//      ticket so a CTA's predecessors are always already running), ranks its keys per warp with
+//      __match_any_sync + popc (stable: items are visited in memory order), combines the warp histograms,
+//      resolves its global digit offsets by DECOUPLED LOOK-BACK over per-tile status words (aggregate / inclusive
+//      flags in the top two bits), reorders the tile through shared memory so the global scatter is written in runs,
+//      and writes keys and values to the other buffer.
+// Memory traffic per pass: read 1x + write 1x of (key,value); histogram: read keys once.
+#include "common.cuh"
+#include "radix_sort.cuh"
+
+namespace rr {
+
+namespace {
+
+constexpr int RADIX_BITS = 8;
+constexpr int RADIX = 1 << RADIX_BITS;
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_WARPS = SORT_THREADS / 32;
+constexpr int MAX_PASSES = 8;
+constexpr uint32_t FLAG_SHIFT = 30;
+constexpr uint32_t FLAG_AGG = 1u << FLAG_SHIFT;      // tile aggregate available
+constexpr uint32_t FLAG_INC = 2u << FLAG_SHIFT;      // inclusive prefix available
+constexpr uint32_t VALUE_MASK = (1u << FLAG_SHIFT) - 1;
+
+template <class K> struct Cfg;
+template <> struct Cfg<uint32_t> { static constexpr int IPT = 16; };
+template <> struct Cfg<uint64_t> { static constexpr int IPT = 12; };
+
+template <class K> __device__ __forceinline__ uint32_t digit_of(K key, int shift, uint32_t mask) {
+	return (uint32_t)(key >> shift) & mask;
+}
+
+struct PassDesc { int shift[MAX_PASSES]; uint32_t mask[MAX_PASSES]; int npass; };
+
+// ---- 1. histograms of all passes ------------------------------------------------------------------------------
+template <class K>
+__global__ void __launch_bounds__(SORT_THREADS) histogram_kernel(const K* __restrict__ keys, uint32_t n, PassDesc pd, uint32_t* __restrict__ ghist)
+{
+	__shared__ uint32_t sh[MAX_PASSES * RADIX];
+	for (int i = threadIdx.x; i < pd.npass * RADIX; i += SORT_THREADS) sh[i] = 0;
+	__syncthreads();
+	const uint32_t stride = gridDim.x * SORT_THREADS;
+	// uniform trip count so the warp-wide match below always sees all 32 lanes
+	for (uint32_t base = blockIdx.x * SORT_THREADS; base < n; base += stride) {
+		const uint32_t i = base + threadIdx.x;
+		const bool valid = i < n;
+		const K key = valid ? keys[i] : (K)0;
+		#pragma unroll 1
+		for (int p = 0; p < pd.npass; p++) {
+			const uint32_t d = valid ? digit_of(key, pd.shift[p], pd.mask[p]) : RADIX;   // RADIX = "no item"
+			const unsigned peers = __match_any_sync(FULL, d);
+			if (valid && (peers & lanemask_lt()) == 0) atomicAdd(&sh[p * RADIX + d], (uint32_t)__popc(peers));
+		}
+	}
+	__syncthreads();
+	for (int i = threadIdx.x; i < pd.npass * RADIX; i += SORT_THREADS) {
+		const uint32_t v = sh[i];
+		if (v) atomicAdd(&ghist[i], v);
+	}
+}
+
+// ---- 2. exclusive scan of each 256-bin histogram (one CTA per pass) ---------------------------------------------
+__global__ void __launch_bounds__(RADIX) digit_base_kernel(uint32_t* __restrict__ ghist)
+{
+	__shared__ uint32_t warp_tot[RADIX / 32];
+	uint32_t* h = ghist + blockIdx.x * RADIX;
+	const uint32_t v = h[threadIdx.x];
+	uint32_t inc = v;
+	#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(FULL, inc, o); if (lane_id() >= (unsigned)o) inc += t; }
+	if (lane_id() == 31) warp_tot[threadIdx.x >> 5] = inc;
+	__syncthreads();
+	uint32_t pre = 0;
+	for (int w = 0; w < (int)(threadIdx.x >> 5); w++) pre += warp_tot[w];
+	h[threadIdx.x] = pre + inc - v;
+}
+
+// ---- 3. one onesweep pass ---------------------------------------------------------------------------------------
+template <class K, int IPT>
+__global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(
+	const K* __restrict__ keys_in, K* __restrict__ keys_out,
+	const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
+	uint32_t n, int shift, uint32_t mask,
+	const uint32_t* __restrict__ digit_base,   // [RADIX] exclusive global base of each digit
+	uint32_t* __restrict__ ticket,             // dynamic tile id
+	volatile uint32_t* __restrict__ status)    // [ntiles][RADIX]
+{
+	constexpr int TILE = SORT_THREADS * IPT;
+	constexpr int WARP_ITEMS = 32 * IPT;
+	__shared__ uint32_t s_tile;
+	__shared__ uint32_t s_whist[SORT_WARPS][RADIX];
+	__shared__ uint32_t s_dstart[RADIX];
+	__shared__ uint32_t s_goff[RADIX];
+	__shared__ uint32_t s_wtot[SORT_WARPS];
+	__shared__ K s_keys[TILE];
+	__shared__ uint32_t s_vals[TILE];
+
+	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+	if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+	for (int i = tid; i < SORT_WARPS * RADIX; i += SORT_THREADS) (&s_whist[0][0])[i] = 0;
+	__syncthreads();
+	const uint32_t tile = s_tile;
+	const uint32_t tile_base = tile * (uint32_t)TILE;
+	const uint32_t tile_count = min((uint32_t)TILE, n - tile_base);
+
+	// load (warp-striped: item k of lane l of warp w sits at w*WARP_ITEMS + k*32 + l, i.e. memory order within the warp)
+	K key[IPT];
+	uint32_t pos[IPT];
+	#pragma unroll
+	for (int k = 0; k < IPT; k++) {
+		const uint32_t li = warp * WARP_ITEMS + k * 32 + lane;
+		key[k] = (li < tile_count) ? keys_in[tile_base + li] : (K)0;
+	}
+	// per-warp stable ranking
+	#pragma unroll
+	for (int k = 0; k < IPT; k++) {
+		const uint32_t li = warp * WARP_ITEMS + k * 32 + lane;
+		const bool valid = li < tile_count;
+		const uint32_t d = valid ? digit_of(key[k], shift, mask) : RADIX;
+		const unsigned peers = __match_any_sync(FULL, d);
+		const int leader = __ffs(peers) - 1;
+		uint32_t old = 0;
+		if (valid && lane == leader) { old = s_whist[warp][d]; s_whist[warp][d] = old + __popc(peers); }
+		__syncwarp();
+		old = __shfl_sync(FULL, old, leader);
+		pos[k] = old + __popc(peers & lanemask_lt());
+	}
+	__syncthreads();
+
+	// thread d owns digit d: warp-exclusive offsets, tile count, look-back
+	{
+		const int d = tid;
+		uint32_t sum = 0;
+		#pragma unroll
+		for (int w = 0; w < SORT_WARPS; w++) { const uint32_t t = s_whist[w][d]; s_whist[w][d] = sum; sum += t; }
+		status[(size_t)tile * RADIX + d] = sum | (tile == 0 ? FLAG_INC : FLAG_AGG);
+		// exclusive scan of the tile's digit counts -> start of each digit in tile-local sorted order
+		uint32_t inc = sum;
+		#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(FULL, inc, o); if (lane >= o) inc += t; }
+		if (lane == 31) s_wtot[warp] = inc;
+		__syncthreads();
+		uint32_t pre = 0;
+		for (int w = 0; w < warp; w++) pre += s_wtot[w];
+		const uint32_t dstart = pre + inc - sum;
+		s_dstart[d] = dstart;
+		// decoupled look-back
+		uint32_t excl = 0;
+		if (tile > 0) {
+			int64_t t = (int64_t)tile - 1;
+			while (true) {
+				const uint32_t v = status[(size_t)t * RADIX + d];
+				const uint32_t f = v >> FLAG_SHIFT;
+				if (f == 0) continue;               // predecessor has not published yet
+				excl += v & VALUE_MASK;
+				if (f == 2) break;
+				t--;
+			}
+			status[(size_t)tile * RADIX + d] = (excl + sum) | FLAG_INC;
+		}
+		s_goff[d] = digit_base[d] + excl - dstart;
+	}
+	__syncthreads();
+
+	// values are fetched only now so they do not occupy registers during the ranking
+	uint32_t val[IPT];
+	#pragma unroll
+	for (int k = 0; k < IPT; k++) {
+		const uint32_t li = warp * WARP_ITEMS + k * 32 + lane;
+		val[k] = 0;
+		if (li < tile_count) val[k] = vals_in ? vals_in[tile_base + li] : tile_base + li;
+	}
+	// reorder through shared memory into tile-local sorted order
+	#pragma unroll
+	for (int k = 0; k < IPT; k++) {
+		const uint32_t li = warp * WARP_ITEMS + k * 32 + lane;
+		if (li < tile_count) {
+			const uint32_t d = digit_of(key[k], shift, mask);
+			const uint32_t p = s_dstart[d] + s_whist[warp][d] + pos[k];
+			s_keys[p] = key[k];
+			s_vals[p] = val[k];
+		}
+	}
+	__syncthreads();
+	#pragma unroll
+	for (int k = 0; k < IPT; k++) {
+		const uint32_t p = k * SORT_THREADS + tid;
+		if (p < tile_count) {
+			const K kk = s_keys[p];
+			const uint32_t g = s_goff[digit_of(kk, shift, mask)] + p;
+			keys_out[g] = kk;
+			vals_out[g] = s_vals[p];
+		}
+	}
+}
+
+struct WsLayout { uint32_t* ghist; uint32_t* tickets; uint32_t* status; size_t zero_bytes; size_t total; uint32_t ntiles; };
+
+template <class K>
+WsLayout ws_layout(void* ws, size_t n, int npass) {
+	constexpr int TILE = SORT_THREADS * Cfg<K>::IPT;
+	WsLayout L;
+	L.ntiles = (uint32_t)((n + TILE - 1) / TILE);
+	Carver c(ws);
+	L.ghist = c.take<uint32_t>((size_t)MAX_PASSES * RADIX);
+	L.tickets = c.take<uint32_t>(MAX_PASSES);
+	L.status = c.take<uint32_t>((size_t)npass * L.ntiles * RADIX);
+	L.zero_bytes = c.off;
+	L.total = c.used();
+	return L;
+}
+
+PassDesc make_passes(int begin_bit, int end_bit) {
+	PassDesc pd;
+	pd.npass = 0;
+	for (int b = begin_bit; b < end_bit && pd.npass < MAX_PASSES; b += RADIX_BITS) {
+		const int nb = (end_bit - b) < RADIX_BITS ? (end_bit - b) : RADIX_BITS;
+		pd.shift[pd.npass] = b;
+		pd.mask[pd.npass] = (1u << nb) - 1;
+		pd.npass++;
+	}
+	return pd;
+}
+
+}  // namespace
+
+template <class K>
+size_t sort_ws_bytes(size_t n, int begin_bit, int end_bit) {
+	const PassDesc pd = make_passes(begin_bit, end_bit);
+	return ws_layout<K>(nullptr, n, pd.npass).total + 256;
+}
+
+template <class K>
+int sort_pairs(cudaStream_t stream, K* keys_a, K* keys_b, uint32_t* vals_a, uint32_t* vals_b, size_t n,
+	int begin_bit, int end_bit, void* ws, bool iota_vals)
+{
+	if (n == 0) return 0;
+	if (n >= (size_t)VALUE_MASK) { set_error("sort_pairs: n=%zu exceeds the 2^30-1 item limit of the look-back status word", n); return -1; }
+	if (end_bit <= begin_bit || end_bit > (int)sizeof(K) * 8 || (end_bit - begin_bit + RADIX_BITS - 1) / RADIX_BITS > MAX_PASSES) {
+		set_error("sort_pairs: bad bit range [%d,%d)", begin_bit, end_bit); return -1;
+	}
+	constexpr int IPT = Cfg<K>::IPT;
+	const PassDesc pd = make_passes(begin_bit, end_bit);
+	const WsLayout L = ws_layout<K>(ws, n, pd.npass);
+	cudaMemsetAsync(ws, 0, L.zero_bytes, stream);
+	const uint32_t hgrid = (uint32_t)((n + SORT_THREADS * 16 - 1) / (SORT_THREADS * 16));
+	histogram_kernel<K><<<hgrid < 1184u ? hgrid : 1184u, SORT_THREADS, 0, stream>>>(keys_a, (uint32_t)n, pd, L.ghist);
+	digit_base_kernel<<<pd.npass, RADIX, 0, stream>>>(L.ghist);
+	K* kin = keys_a; K* kout = keys_b;
+	uint32_t* vin = vals_a; uint32_t* vout = vals_b;
+	for (int p = 0; p < pd.npass; p++) {
+		onesweep_kernel<K, IPT><<<L.ntiles, SORT_THREADS, 0, stream>>>(kin, kout, (p == 0 && iota_vals) ? nullptr : vin, vout,
+			(uint32_t)n, pd.shift[p], pd.mask[p], L.ghist + p * RADIX, L.tickets + p, L.status + (size_t)p * L.ntiles * RADIX);
+		K* tk = kin; kin = kout; kout = tk;
+		uint32_t* tv = vin; vin = vout; vout = tv;
+	}
+	if (check_launch("sort_pairs", stream, false)) return -1;
+	return pd.npass & 1;   // odd number of passes -> result sits in the *_b buffers
+}
+
+template size_t sort_ws_bytes<uint32_t>(size_t, int, int);
+template size_t sort_ws_bytes<uint64_t>(size_t, int, int);
+template int sort_pairs<uint32_t>(cudaStream_t, uint32_t*, uint32_t*, uint32_t*, uint32_t*, size_t, int, int, void*, bool);
+template int sort_pairs<uint64_t>(cudaStream_t, uint64_t*, uint64_t*, uint32_t*, uint32_t*, size_t, int, int, void*, bool);
+
+}  // namespace rr

@@ -1,0 +1,220 @@
+// Backward tile renderer: back-to-front replay of each tile's list, producing one gradient partial per
+// (tile, Gaussian) duplicate.  Replaces renderCUDA<3> backward (reference backward.cu:389-547), whose 9 global float
+// atomics per contributing (pixel, Gaussian) pair serialise in L2 on a single address per Gaussian.
+//
+// B200 design:
+//  * same TMA-staged, per-warp-culled list walk as the forward (render_fwd.cu), in reverse order, starting at the
+//    tile's deepest contributor (tile_max_contrib, recorded by the forward) instead of the end of the list;
+//  * each lane forms the 9 per-pair terms for its pixel exactly as the reference does; the warp then reduces them with
+//    a halving butterfly (8 values in 4+2+1+1+1 shuffles, the 9th in 5) — skipped when no lane contributed;
+//  * the 8 warps' sums meet in a shared-memory slab (plain stores, a per-warp bitmask says which rows are live) and
+//    ONE 40-byte partial per (tile, Gaussian) is stored to global memory at the duplicate's emission index, so the
+//    partials of one Gaussian are contiguous for the per-Gaussian gather in preprocess_bwd.cu.
+//  No atomics anywhere: the backward is deterministic (bit-reproducible run to run), unlike the reference.
+#include "common.cuh"
+#include "kernels.cuh"
+#include "render_common.cuh"
+
+namespace rr {
+
+namespace {
+
+constexpr int BWD_BATCH = 64;
+constexpr int NV = 9;
+
+// Sum v[0..8] over the 32 lanes.  On return lane L with (L & 3) == 0 holds in `y` the total of value
+// k = 4*bit4(L) + 2*bit3(L) + bit2(L); every lane holds the total of v[8] in `z`.
+__device__ __forceinline__ void warp_reduce9(const float (&v)[NV], int lane, float& y, float& z)
+{
+	float w[4], x[2];
+	const bool h4 = lane & 16, h3 = lane & 8, h2 = lane & 4;
+	#pragma unroll
+	for (int i = 0; i < 4; i++) {
+		const float send = h4 ? v[i] : v[i + 4], keep = h4 ? v[i + 4] : v[i];
+		w[i] = keep + __shfl_xor_sync(FULL, send, 16);
+	}
+	#pragma unroll
+	for (int i = 0; i < 2; i++) {
+		const float send = h3 ? w[i] : w[i + 2], keep = h3 ? w[i + 2] : w[i];
+		x[i] = keep + __shfl_xor_sync(FULL, send, 8);
+	}
+	{
+		const float send = h2 ? x[0] : x[1], keep = h2 ? x[1] : x[0];
+		y = keep + __shfl_xor_sync(FULL, send, 4);
+	}
+	y += __shfl_xor_sync(FULL, y, 2);
+	y += __shfl_xor_sync(FULL, y, 1);
+	z = v[8];
+	#pragma unroll
+	for (int o = 16; o >= 1; o >>= 1) z += __shfl_xor_sync(FULL, z, o);
+}
+
+template <bool USE_TMA>
+__global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a)
+{
+	__shared__ __align__(128) float4 s_rec[STAGES][BWD_BATCH * 3];
+	__shared__ __align__(8) uint64_t s_full[STAGES];
+	__shared__ float s_slab[RENDER_WARPS][BWD_BATCH * NV];
+	__shared__ uint64_t s_mask[RENDER_WARPS];
+	__shared__ uint8_t s_list[RENDER_WARPS][BWD_BATCH];
+
+	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+	const int tile = blockIdx.y * a.grid_x + blockIdx.x;
+	int wx, wy, lx, ly;
+	warp_footprint(warp, lane, wx, wy, lx, ly);
+	const int pix_x = blockIdx.x * TILE_X + wx + lx, pix_y = blockIdx.y * TILE_Y + wy + ly;
+	const bool inside = pix_x < a.W && pix_y < a.H;
+	const float pxf = (float)pix_x, pyf = (float)pix_y;
+	const float X0 = (float)(blockIdx.x * TILE_X + wx), X1 = X0 + 7.0f;
+	const float Y0 = (float)(blockIdx.y * TILE_Y + wy), Y1 = Y0 + 3.0f;
+
+	const uint2 range = a.ranges[tile];
+	const int n = (int)(range.y - range.x);
+	const int m = min(n, (int)a.tile_max_contrib[tile]);        // entries [m, n) contributed to no pixel
+	const int nbatches = (m + BWD_BATCH - 1) / BWD_BATCH;
+	const float4* __restrict__ src = reinterpret_cast<const float4*>(a.packed + range.x);
+	const uint32_t* __restrict__ emit = a.sorted_emit + range.x;
+
+	// batch b covers local indices [lo_b, hi_b), hi_b = m - b*BWD_BATCH
+	if (tid == 0 && USE_TMA) {
+		for (int s = 0; s < STAGES; s++) mbar_init(&s_full[s], 1);
+		mbar_fence_init();
+	}
+	__syncthreads();
+	if (USE_TMA && tid == 0) {
+		for (int b = 0; b < STAGES && b < nbatches; b++) {
+			const int hi = m - b * BWD_BATCH, lo = max(0, hi - BWD_BATCH);
+			const uint32_t bytes = (uint32_t)(hi - lo) * (uint32_t)sizeof(SplatRec);
+			mbar_arrive_expect_tx(&s_full[b], bytes);
+			bulk_g2s(&s_rec[b][0], src + (size_t)lo * 3, bytes, &s_full[b]);
+		}
+	}
+
+	// duplicates behind the deepest contributor get zero partials
+	for (int t = tid; t < (n - m) * PARTIAL_FLOATS; t += RENDER_THREADS) {
+		const int e = m + t / PARTIAL_FLOATS, k = t % PARTIAL_FLOATS;
+		a.partial[(size_t)emit[e] * PARTIAL_FLOATS + k] = 0.0f;
+	}
+
+	const size_t pid = (size_t)a.W * pix_y + pix_x, HW = (size_t)a.H * a.W;
+	const float T_final = inside ? a.final_T[pid] : 0.0f;
+	float T = T_final;
+	const int last_contributor = inside ? (int)a.n_contrib[pid] : 0;
+	float dLp0 = 0, dLp1 = 0, dLp2 = 0;
+	if (inside) { dLp0 = a.dL_dpix[pid]; dLp1 = a.dL_dpix[HW + pid]; dLp2 = a.dL_dpix[2 * HW + pid]; }
+	float bg_dot_dpixel = 0;
+	bg_dot_dpixel += a.bg[0] * dLp0; bg_dot_dpixel += a.bg[1] * dLp1; bg_dot_dpixel += a.bg[2] * dLp2;
+	float ar0 = 0, ar1 = 0, ar2 = 0, lc0 = 0, lc1 = 0, lc2 = 0, last_alpha = 0;
+	const float ddelx_dx = 0.5f * a.W, ddely_dy = 0.5f * a.H;
+	const int warp_max = (int)__reduce_max_sync(FULL, (unsigned)last_contributor);
+
+	for (int b = 0; b < nbatches; b++) {
+		const int s = b % STAGES;
+		const int hi = m - b * BWD_BATCH, lo = max(0, hi - BWD_BATCH), cnt = hi - lo;
+		if (USE_TMA) {
+			mbar_wait(&s_full[s], (uint32_t)(b / STAGES) & 1u);
+		} else {
+			for (int i = tid; i < cnt * 3; i += RENDER_THREADS) s_rec[s][i] = __ldg(src + (size_t)lo * 3 + i);
+			__syncthreads();
+		}
+		const float4* __restrict__ rec = s_rec[s];
+		uint64_t live = 0;
+		if (lo < warp_max) {
+			int nsurv = 0;
+			for (int c = 0; c < cnt; c += 32) {
+				const int e = c + lane;
+				bool pass = false;
+				if (e < cnt && lo + e < warp_max) {
+					const float4 ra = rec[e * 3];
+					pass = rect_may_contribute(ra.x, ra.y, ra.z, ra.w, rec[e * 3 + 1].x, rec[e * 3 + 2].z, X0, X1, Y0, Y1);
+				}
+				const unsigned mk = __ballot_sync(FULL, pass);
+				if (pass) s_list[warp][nsurv + __popc(mk & lanemask_lt())] = (uint8_t)e;
+				nsurv += __popc(mk);
+			}
+			__syncwarp();
+			for (int k = nsurv - 1; k >= 0; k--) {
+				const int e = s_list[warp][k];
+				const float4 ra = rec[e * 3], rb = rec[e * 3 + 1], rc = rec[e * 3 + 2];
+				float v[NV];
+				#pragma unroll
+				for (int i = 0; i < NV; i++) v[i] = 0.0f;
+				bool contributed = false;
+				if (lo + e < last_contributor) {
+					const float dx = __fsub_rn(ra.x, pxf), dy = __fsub_rn(ra.y, pyf);
+					const float q = __fmaf_rn(dx, __fmul_rn(dx, ra.z), __fmul_rn(dy, __fmul_rn(dy, rb.x)));
+					const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(dy, __fmul_rn(dx, ra.w)));
+					if (!(power > 0.0f) && !(power < rc.z)) {
+						const float G = expf(power);
+						const float alpha = fminf(0.99f, __fmul_rn(rb.y, G));
+						if (!(alpha < 1.0f / 255.0f)) {
+							contributed = true;
+							const float one_m_a = 1.f - alpha;
+							T = T / one_m_a;
+							const float dchannel_dcolor = alpha * T;
+							const float one_m_la = 1.f - last_alpha;
+							ar0 = last_alpha * lc0 + one_m_la * ar0; lc0 = rb.z;
+							ar1 = last_alpha * lc1 + one_m_la * ar1; lc1 = rb.w;
+							ar2 = last_alpha * lc2 + one_m_la * ar2; lc2 = rc.x;
+							float dL_dalpha = (rb.z - ar0) * dLp0;
+							dL_dalpha += (rb.w - ar1) * dLp1;
+							dL_dalpha += (rc.x - ar2) * dLp2;
+							v[0] = dchannel_dcolor * dLp0; v[1] = dchannel_dcolor * dLp1; v[2] = dchannel_dcolor * dLp2;
+							dL_dalpha *= T;
+							last_alpha = alpha;
+							dL_dalpha += (-T_final / one_m_a) * bg_dot_dpixel;
+							const float dL_dG = rb.y * dL_dalpha;
+							const float gdx = G * dx, gdy = G * dy;
+							const float dG_ddelx = -gdx * ra.z - gdy * ra.w;
+							const float dG_ddely = -gdy * rb.x - gdx * ra.w;
+							v[3] = dL_dG * dG_ddelx * ddelx_dx;
+							v[4] = dL_dG * dG_ddely * ddely_dy;
+							v[5] = -0.5f * gdx * dx * dL_dG;
+							v[6] = -0.5f * gdx * dy * dL_dG;
+							v[7] = -0.5f * gdy * dy * dL_dG;
+							v[8] = G * dL_dalpha;
+						}
+					}
+				}
+				if (__ballot_sync(FULL, contributed) == 0) continue;
+				float y, z;
+				warp_reduce9(v, lane, y, z);
+				if ((lane & 3) == 0) s_slab[warp][e * NV + ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1)] = y;
+				if (lane == 1) s_slab[warp][e * NV + 8] = z;
+				live |= 1ull << e;
+			}
+		}
+		if (lane == 0) s_mask[warp] = live;
+		__syncthreads();
+		// combine the 8 warps and store one partial per (tile, Gaussian) at its emission index
+		for (int t = tid; t < cnt * PARTIAL_FLOATS; t += RENDER_THREADS) {
+			const int e = t / PARTIAL_FLOATS, k = t - e * PARTIAL_FLOATS;
+			float sum = 0.0f;
+			if (k < NV) {
+				#pragma unroll
+				for (int w = 0; w < RENDER_WARPS; w++) if ((s_mask[w] >> e) & 1ull) sum += s_slab[w][e * NV + k];
+			}
+			a.partial[(size_t)emit[lo + e] * PARTIAL_FLOATS + k] = sum;
+		}
+		__syncthreads();
+		if (USE_TMA && tid == 0 && b + STAGES < nbatches) {
+			const int nb = b + STAGES;
+			const int nhi = m - nb * BWD_BATCH, nlo = max(0, nhi - BWD_BATCH);
+			const uint32_t bytes = (uint32_t)(nhi - nlo) * (uint32_t)sizeof(SplatRec);
+			mbar_arrive_expect_tx(&s_full[s], bytes);
+			bulk_g2s(&s_rec[s][0], src + (size_t)nlo * 3, bytes, &s_full[s]);
+		}
+	}
+}
+
+}  // namespace
+
+int launch_render_bwd(cudaStream_t stream, const RenderArgs& a)
+{
+	const dim3 grid(a.grid_x, a.grid_y);
+	if (a.variant == 0) render_bwd_kernel<false><<<grid, RENDER_THREADS, 0, stream>>>(a);
+	else render_bwd_kernel<true><<<grid, RENDER_THREADS, 0, stream>>>(a);
+	return check_launch("render_bwd", stream, false);
+}
+
+}  // namespace rr

@@ -1,0 +1,165 @@
+// Forward tile renderer: front-to-back alpha blending of each 16x16 tile's depth-sorted splat list.
+// Replaces renderCUDA<3> forward (reference forward.cu:251-369).
+//
+// B200 design:
+//  * the tile's list is a contiguous span of 48-byte records (packed by pack_kernel), so each batch of 128 splats
+//    is staged into shared memory with ONE cp.async.bulk (TMA) issued by one thread and tracked by an mbarrier,
+//    3 stages deep — no per-thread gathers, no register staging (variant 1; variant 0 uses plain cooperative
+//    float4 loads and exists as a cross-check);
+//  * each warp owns an 8x4 pixel block and first culls the staged batch against that block (one splat per lane,
+//    exact concave-maximum test, see render_common.cuh) and compacts the survivors with ballot/popc, so the blend
+//    loop only visits splats that can reach alpha >= 1/255 somewhere in the warp's pixels;
+//  * warps stop individually once their 32 pixels are saturated; the CTA stops when all 8 warps have.
+// The per-pair arithmetic (power, exp, alpha, T test, accumulation) is spelled with explicit-rounding intrinsics in
+// exactly the order of the reference build so final_T, n_contrib and the colours are reproduced bit for bit.
+#include "common.cuh"
+#include "kernels.cuh"
+#include "render_common.cuh"
+
+namespace rr {
+
+namespace {
+
+template <bool USE_TMA>
+__global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a)
+{
+	__shared__ __align__(128) float4 s_rec[STAGES][BATCH * 3];
+	__shared__ __align__(8) uint64_t s_full[STAGES];
+	__shared__ uint8_t s_list[RENDER_WARPS][BATCH];
+	__shared__ uint32_t s_max_contrib;
+
+	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+	const int tile = blockIdx.y * a.grid_x + blockIdx.x;
+	int wx, wy, lx, ly;
+	warp_footprint(warp, lane, wx, wy, lx, ly);
+	const int pix_x = blockIdx.x * TILE_X + wx + lx, pix_y = blockIdx.y * TILE_Y + wy + ly;
+	const bool inside = pix_x < a.W && pix_y < a.H;
+	const float pxf = (float)pix_x, pyf = (float)pix_y;
+	// rectangle of the warp's pixel centres
+	const float X0 = (float)(blockIdx.x * TILE_X + wx), X1 = X0 + 7.0f;
+	const float Y0 = (float)(blockIdx.y * TILE_Y + wy), Y1 = Y0 + 3.0f;
+
+	const uint2 range = a.ranges[tile];
+	const int n = (int)(range.y - range.x);
+	const int nbatches = (n + BATCH - 1) / BATCH;
+	const float4* __restrict__ src = reinterpret_cast<const float4*>(a.packed + range.x);
+
+	if (tid == 0) {
+		s_max_contrib = 0;
+		if (USE_TMA) {
+			for (int s = 0; s < STAGES; s++) mbar_init(&s_full[s], 1);
+			mbar_fence_init();
+		}
+	}
+	__syncthreads();
+	if (USE_TMA && tid == 0) {
+		for (int b = 0; b < STAGES && b < nbatches; b++) {
+			const uint32_t bytes = (uint32_t)min(BATCH, n - b * BATCH) * (uint32_t)sizeof(SplatRec);
+			mbar_arrive_expect_tx(&s_full[b], bytes);
+			bulk_g2s(&s_rec[b][0], src + (size_t)b * BATCH * 3, bytes, &s_full[b]);
+		}
+	}
+
+	float T = 1.0f, C0 = 0.0f, C1 = 0.0f, C2 = 0.0f, Dp = 0.0f;
+	uint32_t last_contributor = 0;
+	bool done = !inside;
+	int b_exit = nbatches;   // first batch index whose stage was never consumed
+
+	for (int b = 0; b < nbatches; b++) {
+		const int s = b % STAGES;
+		const int cnt = min(BATCH, n - b * BATCH);
+		if (USE_TMA) {
+			mbar_wait(&s_full[s], (uint32_t)(b / STAGES) & 1u);
+		} else {
+			__syncthreads();
+			for (int i = tid; i < cnt * 3; i += RENDER_THREADS) s_rec[s][i] = __ldg(src + (size_t)b * BATCH * 3 + i);
+			__syncthreads();
+		}
+		const float4* __restrict__ rec = s_rec[s];
+		bool warp_done = __all_sync(FULL, done);
+		if (!warp_done) {
+			// cull the batch against this warp's 8x4 pixels, one splat per lane, and compact the survivors
+			int nsurv = 0;
+			for (int c = 0; c < cnt; c += 32) {
+				const int e = c + lane;
+				bool pass = false;
+				if (e < cnt) {
+					const float4 ra = rec[e * 3];
+					const float conz = rec[e * 3 + 1].x;
+					const float thr = rec[e * 3 + 2].z;
+					pass = rect_may_contribute(ra.x, ra.y, ra.z, ra.w, conz, thr, X0, X1, Y0, Y1);
+				}
+				const unsigned m = __ballot_sync(FULL, pass);
+				if (pass) s_list[warp][nsurv + __popc(m & lanemask_lt())] = (uint8_t)e;
+				nsurv += __popc(m);
+			}
+			__syncwarp();
+			for (int k = 0; k < nsurv; k++) {
+				const int e = s_list[warp][k];
+				const float4 ra = rec[e * 3], rb = rec[e * 3 + 1], rc = rec[e * 3 + 2];
+				if (!done) {
+					const float dx = __fsub_rn(ra.x, pxf), dy = __fsub_rn(ra.y, pyf);
+					const float q = __fmaf_rn(dx, __fmul_rn(dx, ra.z), __fmul_rn(dy, __fmul_rn(dy, rb.x)));
+					const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(dy, __fmul_rn(dx, ra.w)));
+					if (!(power > 0.0f) && !(power < rc.z)) {
+						const float alpha = fminf(0.99f, __fmul_rn(rb.y, expf(power)));
+						if (!(alpha < 1.0f / 255.0f)) {
+							const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
+							if (test_T < 0.0001f) {
+								done = true;
+							} else {
+								C0 = __fmaf_rn(T, __fmul_rn(alpha, rb.z), C0);
+								C1 = __fmaf_rn(T, __fmul_rn(alpha, rb.w), C1);
+								C2 = __fmaf_rn(T, __fmul_rn(alpha, rc.x), C2);
+								Dp = __fmaf_rn(T, __fmul_rn(alpha, rc.y), Dp);
+								T = test_T;
+								last_contributor = (uint32_t)(b * BATCH + e + 1);
+							}
+						}
+					}
+				}
+				if (__all_sync(FULL, done)) break;
+			}
+		}
+		// every warp is past this stage: it can be refilled; stop early when all 256 pixels are saturated
+		const int all_done = __syncthreads_and(done);
+		if (all_done) { b_exit = b + 1; break; }
+		if (USE_TMA && tid == 0 && b + STAGES < nbatches) {
+			const int nb = b + STAGES;
+			const uint32_t bytes = (uint32_t)min(BATCH, n - nb * BATCH) * (uint32_t)sizeof(SplatRec);
+			mbar_arrive_expect_tx(&s_full[s], bytes);
+			bulk_g2s(&s_rec[s][0], src + (size_t)nb * BATCH * 3, bytes, &s_full[s]);
+		}
+	}
+
+	if (USE_TMA && tid == 0) {
+		// bulk copies already in flight for later stages must land before the CTA (and its shared memory) retires
+		for (int bb = b_exit; bb < nbatches && bb < b_exit + STAGES - 1; bb++) mbar_wait(&s_full[bb % STAGES], (uint32_t)(bb / STAGES) & 1u);
+	}
+
+	if (inside) {
+		const size_t pid = (size_t)a.W * pix_y + pix_x, HW = (size_t)a.H * a.W;
+		a.final_T[pid] = T;
+		a.n_contrib[pid] = last_contributor;
+		a.out_color[pid] = __fmaf_rn(T, a.bg[0], C0);
+		a.out_color[HW + pid] = __fmaf_rn(T, a.bg[1], C1);
+		a.out_color[2 * HW + pid] = __fmaf_rn(T, a.bg[2], C2);
+		a.out_depth[pid] = Dp;
+	}
+	const uint32_t wmax = __reduce_max_sync(FULL, inside ? last_contributor : 0u);
+	if (lane == 0) atomicMax(&s_max_contrib, wmax);
+	__syncthreads();
+	if (tid == 0) a.tile_max_contrib[tile] = s_max_contrib;
+}
+
+}  // namespace
+
+int launch_render_fwd(cudaStream_t stream, const RenderArgs& a)
+{
+	const dim3 grid(a.grid_x, a.grid_y);
+	if (a.variant == 0) render_fwd_kernel<false><<<grid, RENDER_THREADS, 0, stream>>>(a);
+	else render_fwd_kernel<true><<<grid, RENDER_THREADS, 0, stream>>>(a);
+	return check_launch("render_fwd", stream, false);
+}
+
+}  // namespace rr
