@@ -64,7 +64,7 @@ for name in names:
                 a = a.reshape(-1, 4)[:, [0, 1, 3]]; b = b.reshape(-1, 4)[:, [0, 1, 3]]
             e = rel_err(a, b); fr = elem_rel_err_frac(a, b, 1e-4)
             e_rr = rel_err(gr2[k], gr[k]); det = bool((g2[k] == g[k]).all())
-            rep[f"v{variant}_{k}"] = dict(max_rel=e[0], l2_rel=e[1], frac_gt_1e-4=fr, ref_vs_ref_max=e_rr[0], deterministic=det)
+            rep[f"v{variant}_{k}"] = dict(max_rel=e[0], l2_rel=e[1], frac_gt_1e_4=fr, ref_vs_ref_max=e_rr[0], deterministic=det)
             print(f"   {k:12s} mine-vs-ref max {e[0]:.2e} l2 {e[1]:.2e} frac>1e-4 {fr:.2e} | ref-vs-ref max {e_rr[0]:.2e} | mine deterministic {det}")
     # oracle comparison (CPU)
     if cfg["P"] <= 300_000:
