@@ -212,12 +212,14 @@ class RefCuda:
         if self.lib.ref_state_ptrs(ptrs) != 0:
             raise RuntimeError("ref_state_ptrs failed")
         torch.cuda.synchronize()
-        rt = torch.cuda.cudart()
+        rt = C.CDLL("libcudart.so.12")      # already in the process (libref_rast.so links it); same soname -> same handle
+        rt.cudaMemcpy.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]
 
         def grab(i, shape, dtype):
             t = torch.empty(shape, dtype=dtype, device=dev)
             if t.numel():
-                rt.cudaMemcpy(t.data_ptr(), ptrs[i], t.numel() * t.element_size(), 3)
+                if rt.cudaMemcpy(t.data_ptr(), ptrs[i], t.numel() * t.element_size(), 3) != 0:
+                    raise RuntimeError("cudaMemcpy of reference state failed")
             return t
         st = dict(depths=grab(0, (P,), torch.float32), clamped=grab(1, (P, 3), torch.uint8), means2D=grab(2, (P, 2), torch.float32),
                   cov3D=grab(3, (P, 6), torch.float32), conic_opacity=grab(4, (P, 4), torch.float32), rgb=grab(5, (P, 3), torch.float32),

@@ -1,9 +1,10 @@
 """GPU diagnostic: stage-by-stage comparison of rain_b200 against the rebuilt reference CUDA and the CPU oracle, with
 mismatch statistics (not just pass/fail), plus rough per-call timings.  Usage: python tools/gpu_diag.py [C1 C2 C3] """
 import sys, os, time, json
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, 'tests'))
 import numpy as np, torch
-from tests.harness import mine_forward, mine_backward, rel_err, elem_rel_err_frac
+from harness import mine_forward, mine_backward, rel_err, elem_rel_err_frac
 from rain_b200.synthetic import make_scene, make_camera, make_grad, CONFIGS
 from oracle.oracle_py import Oracle, RefCuda
 
