@@ -1,0 +1,392 @@
+"""bench.py — fwd+bwd renders/sec of the splat rasterizer on B200 (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload C3|C2|C1]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
+
+A "step": every rank renders VIEWS_PER_STEP different camera views of the same synthetic scene forward + backward
+(default workload C3 = BASELINE.json configs[2], the one the metric is quoted on: 1M Gaussians, 1920x1080, SH degree 3),
+accumulating the parameter gradients of its views into one flat bucket (59 floats per Gaussian), followed — for N > 1 — by
+ONE NCCL all-reduce of that bucket (view-sharded data parallelism).  Scaling is weak: per-GPU work is fixed.
+`value` = views rendered by all ranks / max-over-ranks device time, inputs resident in HBM.
+`e2e`   = the same step driven from HOST buffers through the public API: per view the camera matrices and the target
+          image are copied from pinned host memory, the loss gradient is formed on the device, and the loss scalar and
+          num_rendered are read back.
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+from rain_b200.synthetic import CONFIGS, make_camera, make_grad, make_scene  # noqa: E402
+
+VIEWS_PER_STEP = 4          # views each rank renders per step
+NUM_CAMERAS = 64            # the view pool (BASELINE.json config 4 uses a 64-view batch)
+METRIC = "fwd+bwd renders/sec (1M Gaussians, 1920x1080) at 1/2/4/8 B200"
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p)), "measured"
+    return {"hbm_gbs": 6650.0}, "fallback"
+
+
+class ClockSampler:
+    """samples nvidia-smi clocks / throttle reasons of one GPU during the timed region"""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50", "-i", str(self.index)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.12)
+        self.proc.terminate()
+        rows = [r for t, r in self.rows if t0 - 0.05 <= t <= t1 + 0.1 and len(r) >= 7] or [r for _, r in self.rows if len(r) >= 7]
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm = sorted(float(r[0]) for r in rows)
+        reasons = [n for i, n in ((3, "hw_slowdown"), (4, "hw_thermal_slowdown"), (5, "sw_thermal_slowdown"), (6, "sw_power_cap"))
+                   if any(r[i].lower().startswith("active") for r in rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][1]), "power_w_max": max(float(r[2]) for r in rows),
+                "samples": len(rows), "reasons": reasons}
+
+
+def stage_bytes(name, P, V, N, X, M=16):
+    """ALGORITHMIC bytes of one launch group per render (SURVEY.md §8(d) per-unit figures adapted to this
+    library's data layout).  P Gaussians, V visible, N (tile, Gaussian) pairs, X pixels."""
+    return {
+        "preprocess_fwd": 52 * P + (12 * M + 67) * V,                 # 44 in + 8 out always; SH row in + projected record out if visible
+        "depth_sort": (4 + 4 * 16) * P,                                # histogram read + 4 passes x (key+value read, key+value write)
+        "scan": 12 * P,                                                # order + tiles_touched in, offsets out
+        "duplicate": 20 * P + 8 * N,                                   # order/offsets/rect in, tile key + owner out
+        "tile_sort": (4 + 2 * 16) * N,                                 # histogram read + 2 passes x 16 B
+        "ranges_pack": 4 * N + (8 + 48 + 48 + 4) * N,                  # key read; (emit, owner, record) in, record + point_list out
+        "render_fwd": 48 * N + 24 * X,                                 # staged records; colour 12 + depth 4 + final_T 4 + n_contrib 4 out
+        "render_bwd": 52 * N + 40 * N + 20 * X,                        # records + emission index in, one 40-B partial per pair out, dL_dpix/T/n in
+        "preprocess_bwd": 40 * N + (12 * M + 111) * V + (12 * M + 56) * P,   # partials + inputs in, every gradient element out
+    }.get(name)
+
+
+def dist_setup(n_gpus):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    elif n_gpus > 1:
+        raise SystemExit("--gpus N > 1 must be launched with torch.distributed.run (one process per GPU)")
+    return rank, world, local
+
+
+def barrier_sync(world):
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def max_over_ranks(x, world, dev):
+    if world == 1:
+        return x
+    t = torch.tensor([x], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def build_workload(name, dev, rank):
+    cfg = CONFIGS[name]
+    sc_h = make_scene(cfg["P"], cfg["D"], seed=0)
+    cams_h = [make_camera(v, NUM_CAMERAS, cfg["W"], cfg["H"]) for v in range(NUM_CAMERAS)]
+    # per-view target images: upstream gradient = colour - target (L2 loss); seeded, pinned on the host for the e2e arm
+    targets_h = [make_grad(cfg["W"], cfg["H"], seed=100 + v).mul_(0.1).add_(0.5).pin_memory() for v in range(VIEWS_PER_STEP)]
+    return cfg, sc_h, cams_h, targets_h
+
+
+def run_ours(args, rank, world, local):
+    from rain_b200 import _lib, multiview as mv
+    dev = torch.device("cuda", local)
+    lib = _lib.load()
+    cfg, sc_h, cams_h, targets_h = build_workload(args.workload, dev, rank)
+    P, W, H, D = cfg["P"], cfg["W"], cfg["H"], cfg["D"]
+    sc = sc_h.to(dev)
+    params = dict(means3D=sc.means3D, opacities=sc.opacities, shs=sc.shs, scales=sc.scales, rotations=sc.rotations)
+    bg = torch.zeros(3, device=dev)
+    bucket = mv.GradientBucket(P, 16, dev)
+    kw = dict(bg=bg, sh_degree=D, keep_outputs=False)
+
+    def views_of(step):   # a different slice of the 64-camera pool for every (step, rank)
+        return [(step * world * VIEWS_PER_STEP + rank * VIEWS_PER_STEP + i) % NUM_CAMERAS for i in range(VIEWS_PER_STEP)]
+
+    # ---------------- device-resident arm (`value`) ----------------
+    cams_d = [c.to(dev) for c in cams_h]
+    targets_d = [t.to(dev) for t in targets_h]
+    slot = {}
+
+    def grad_resident(v, color, depth):
+        return torch.sub(color, targets_d[slot[v]])
+
+    def step_resident(s):
+        ids = views_of(s)
+        slot.clear(); slot.update({v: i for i, v in enumerate(ids)})
+        bucket.filled = False
+        res = mv.render_views_fwd_bwd(params, cams_d, ids, bucket, grad_resident, **kw)
+        mv.allreduce_bucket(bucket)
+        return res
+
+    for s in range(args.warmup):
+        step_resident(s)
+    sampler = ClockSampler(local)
+    barrier_sync(world)
+    if rank == 0:
+        sampler.start()
+    launches0 = lib.rr_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.time()
+    e0.record()
+    N_last = 0
+    for s in range(args.steps):
+        res = step_resident(args.warmup + s)
+        N_last = res[-1].num_rendered
+    e1.record()
+    barrier_sync(world)
+    t1 = time.time()
+    launches = lib.rr_launch_count() - launches0
+    ms = max_over_ranks(e0.elapsed_time(e1), world, dev)
+    clocks = sampler.stop(t0, t1) if rank == 0 else None
+    renders = world * VIEWS_PER_STEP * args.steps
+    value = renders / (ms * 1e-3)
+
+    # ---------------- per-stage device times (CUDA events on the launch stream, same steps) ----------------
+    lib.rr_prof_enable(1)
+    _lib.stage_times(reset=True)
+    torch.cuda.synchronize()
+    for s in range(args.steps):
+        step_resident(args.warmup + s)
+    torch.cuda.synchronize()
+    st = _lib.stage_times(reset=True)
+    lib.rr_prof_enable(0)
+
+    # ---------------- end-to-end arm (host buffers -> public API -> host scalar) ----------------
+    pinned = [dict(view=c.viewmatrix.pin_memory(), proj=c.projmatrix.pin_memory(), campos=c.campos.pin_memory()) for c in cams_h]
+    dev_cam = [dict(view=torch.empty(4, 4, device=dev), proj=torch.empty(4, 4, device=dev), campos=torch.empty(3, device=dev)) for _ in range(VIEWS_PER_STEP)]
+    dev_tgt = [torch.empty(3, H, W, device=dev) for _ in range(VIEWS_PER_STEP)]
+    loss_dev = torch.zeros(1, device=dev)
+    loss_host = torch.zeros(1).pin_memory()
+    h2d = VIEWS_PER_STEP * ((16 + 16 + 3) * 4 + 3 * H * W * 4)
+    d2h = 4 + VIEWS_PER_STEP * 8          # loss scalar + num_rendered (8 B, read inside the forward) per view
+    from rain_b200.synthetic import Camera
+
+    def step_e2e(s):
+        ids = views_of(s)
+        cams_step = {}
+        for i, v in enumerate(ids):
+            for k in ("view", "proj", "campos"):
+                dev_cam[i][k].copy_(pinned[v][k], non_blocking=True)
+            dev_tgt[i].copy_(targets_h[i], non_blocking=True)
+            cams_step[v] = Camera(W, H, cams_h[v].tanfovx, cams_h[v].tanfovy, dev_cam[i]["view"], dev_cam[i]["proj"], dev_cam[i]["campos"])
+        slot.clear(); slot.update({v: i for i, v in enumerate(ids)})
+        loss_dev.zero_()
+
+        def grad_e2e(v, color, depth):
+            d = torch.sub(color, dev_tgt[slot[v]])
+            loss_dev.add_(0.5 * (d * d).sum())
+            return d
+        bucket.filled = False
+        mv.render_views_fwd_bwd(params, cams_step, ids, bucket, grad_e2e, **kw)
+        mv.allreduce_bucket(bucket)
+        loss_host.copy_(loss_dev, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return float(loss_host.item())
+
+    for s in range(args.warmup):
+        step_e2e(s)
+    barrier_sync(world)
+    e0.record()
+    for s in range(args.steps):
+        loss = step_e2e(args.warmup + s)
+    e1.record()
+    barrier_sync(world)
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1), world, dev)
+    e2e_value = renders / (ms_e2e * 1e-3)
+
+    if rank != 0:
+        return None
+    return dict(cfg=cfg, value=value, ms=ms, e2e_value=e2e_value, ms_e2e=ms_e2e, h2d=h2d, d2h=d2h, launches=launches, stage=st, clocks=clocks,
+                N=N_last, loss=loss, bucket_bytes=bucket.nbytes())
+
+
+def cpu_oracle_sample(workload, renders):
+    """The CPU baseline: the oracle port (scalar C++/OpenMP restatement of forward.cu / backward.cu, all host threads) timed
+    on `renders` fwd+bwd renders of the same workload.  Test infrastructure used here only as the measured baseline."""
+    from oracle.oracle_py import Oracle
+    orc = Oracle()
+    cfg = CONFIGS[workload]
+    sc = make_scene(cfg["P"], cfg["D"], seed=0)
+    bg = np.zeros(3, np.float32)
+    arrs = [sc.means3D.numpy(), sc.opacities.numpy(), sc.scales.numpy(), sc.rotations.numpy()]
+    t = time.time()
+    for v in range(renders):
+        cam = make_camera(v, NUM_CAMERAS, cfg["W"], cfg["H"])
+        N, color, radii, depth = orc.forward(bg, *arrs, cam.viewmatrix.numpy(), cam.projmatrix.numpy(), cam.campos.numpy(), cam.tanfovx, cam.tanfovy,
+                                             cam.height, cam.width, shs=sc.shs.numpy(), sh_degree=cfg["D"])
+        orc.backward(color - (make_grad(cfg["W"], cfg["H"], seed=100 + v % VIEWS_PER_STEP).numpy() * 0.1 + 0.5))
+    dt = time.time() - t
+    return dict(value=renders / dt, unit="renders/s", cores=orc.num_threads(), kind="port",
+                sample=f"{renders} fwd+bwd renders of {workload} ({cfg['P']} Gaussians, {cfg['W']}x{cfg['H']}, SH degree {cfg['D']}) in {dt:.1f} s, "
+                       f"oracle/liboracle.so (g++ -O2 -fopenmp), host threads = {orc.num_threads()} of {os.cpu_count()} cores")
+
+
+def run_reference(args, rank, world, local):
+    """Reference arm: the UNMODIFIED reference CUDA rasterizer (oracle/_ref/libref_rast.so, compiled from /root/reference for
+    sm_100a by oracle/Makefile) on the same GPU, same workload, same step — the reference has no CPU implementation of this
+    path, so its own CUDA build is 'the reference' here; the scalar host port is reported beside it as cpu_baseline."""
+    if rank != 0:
+        return None
+    from oracle.oracle_py import REF_SO, RefCuda
+    cfg = CONFIGS[args.workload]
+    base = {"metric": METRIC, "unit": "renders/s", "impl": "reference", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic"}
+    if not os.path.exists(REF_SO) or not torch.cuda.is_available():
+        # fall back to timing the host port, as the tier contract allows
+        cb = cpu_oracle_sample(args.workload, max(1, min(3, args.steps)))
+        base.update(value=cb["value"], ms_per_step=1e3 * VIEWS_PER_STEP / cb["value"], cpu_baseline=cb,
+                    config={"workload": f"{args.workload}: {cfg['P']} Gaussians, {cfg['W']}x{cfg['H']}, SH degree {cfg['D']}", "arm": "host port (oracle)"},
+                    e2e={"value": cb["value"], "unit": "renders/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
+        return base
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    ref = RefCuda()
+    sc = make_scene(cfg["P"], cfg["D"], seed=0).to(dev)
+    cams = [make_camera(v, NUM_CAMERAS, cfg["W"], cfg["H"]).to(dev) for v in range(NUM_CAMERAS)]
+    targets = [make_grad(cfg["W"], cfg["H"], seed=100 + v).mul_(0.1).add_(0.5).to(dev) for v in range(VIEWS_PER_STEP)]
+    bg = torch.zeros(3, device=dev)
+
+    def step(s):
+        for i in range(VIEWS_PER_STEP):
+            cam = cams[(s * VIEWS_PER_STEP + i) % NUM_CAMERAS]
+            N, color, radii, depth = ref.forward(bg, sc.means3D, sc.opacities, sc.scales, sc.rotations, cam.viewmatrix, cam.projmatrix, cam.campos,
+                                                 cam.tanfovx, cam.tanfovy, cam.height, cam.width, shs=sc.shs, sh_degree=cfg["D"], sync=False)
+            ref.backward(torch.sub(color, targets[i]), sync=False)
+    for s in range(args.warmup):
+        step(s)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for s in range(args.steps):
+        step(args.warmup + s)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    value = VIEWS_PER_STEP * args.steps / (ms * 1e-3)
+    base.update(value=value, ms_per_step=ms / args.steps, n_gpus=1,
+                config={"workload": f"{args.workload}: {cfg['P']} Gaussians, {cfg['W']}x{cfg['H']}, SH degree {cfg['D']}, {VIEWS_PER_STEP} views per step",
+                        "arm": "reference CUDA (unmodified sources, rebuilt for sm_100a) on the same B200, one GPU; no gradient accumulation or all-reduce"},
+                cpu_baseline={"value": value, "unit": "renders/s", "cores": 0, "kind": "reference",
+                              "sample": f"{args.steps} steps x {VIEWS_PER_STEP} views, oracle/_ref/libref_rast.so on cuda:{local} (the reference has no CPU path)"},
+                e2e={"value": value, "unit": "renders/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 4 * VIEWS_PER_STEP})
+    return base
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="C3", choices=["C1", "C2", "C3"])
+    ap.add_argument("--cpu-renders", type=int, default=2, help="renders of the workload timed on the host for cpu_baseline (0 = skip)")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    if args.impl == "reference":
+        rank = int(os.environ.get("RANK", "0"))
+        line = run_reference(args, rank, int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0")))
+        if line is not None:
+            print(json.dumps(line), flush=True)
+        return
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl ours needs a CUDA device: rain_b200 has no CPU path")
+    rank, world, local = dist_setup(args.gpus)
+    torch.cuda.set_device(local)
+    r = run_ours(args, rank, world, local)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank != 0:
+        return
+    cfg = r["cfg"]
+    P, X, N = cfg["P"], cfg["W"] * cfg["H"], r["N"]
+    peaks, peak_kind = load_peaks()
+    peak = float(peaks["hbm_gbs"])
+    calls = max(1, r["stage"]["render_fwd"][1])
+    stages = {}
+    for name, (ms, n) in r["stage"].items():
+        if n == 0:
+            continue
+        b = stage_bytes(name, P, P, N, X)
+        per = ms / n
+        stages[name] = {"ms": round(per, 4), "share": None, "alg_bytes": b, "gbs": round(b / per / 1e6, 1) if b else None,
+                        "frac_of_hbm": round(b / per / 1e6 / peak, 4) if b else None}
+    tot = sum(v["ms"] for v in stages.values())
+    for v in stages.values():
+        v["share"] = round(v["ms"] / tot, 4)
+    top = max(stages, key=lambda k: stages[k]["ms"])
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.exists(tp):
+        traffic = json.load(open(tp)).get(args.workload, {}).get(top)
+    line = {
+        "metric": METRIC, "value": round(r["value"], 2), "unit": "renders/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": round(r["ms"] / args.steps, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": f"{args.workload}: {P} random Gaussians, {cfg['W']}x{cfg['H']}, SH degree {cfg['D']} (BASELINE.json configs[2])",
+                   "views_per_step_per_gpu": VIEWS_PER_STEP, "global_views_per_step": VIEWS_PER_STEP * world, "num_rendered_per_view": N,
+                   "parallelism": f"view-sharded dp{world}, one f32 all-reduce of {r['bucket_bytes']} B per step" if world > 1 else "single GPU",
+                   "l2": "inputs larger than L2: 236 MB of Gaussian parameters + 236 MB gradient bucket per render, different cameras every step"},
+        "e2e": {"value": round(r["e2e_value"], 2), "unit": "renders/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
+                "ms_per_step": round(r["ms_e2e"] / args.steps, 4), "loss": r["loss"]},
+        "gpu_launches": int(r["launches"]),
+        "clocks": r["clocks"],
+        "roofline": {"kernel": top, "bound": "hbm", "achieved": stages[top]["gbs"], "peak": peak, "unit": "GB/s", "frac": stages[top]["frac_of_hbm"],
+                     "traffic": traffic, "peak_source": f"{peak_kind} (MEASURED_PEAKS.json hbm_gbs)" if peak_kind == "measured" else "fallback",
+                     "ms_per_launch": stages[top]["ms"], "share_of_step": stages[top]["share"],
+                     "note": "render kernels are FP32/SFU-issue bound, not HBM bound; see stages[] and DESIGN.md"},
+        "stages": stages,
+    }
+    if world == 1 and args.cpu_renders > 0:
+        line["cpu_baseline"] = cpu_oracle_sample(args.workload, args.cpu_renders)
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()

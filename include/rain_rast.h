@@ -26,8 +26,21 @@
 extern "C" {
 #endif
 
+#define RR_BWD_ACCUMULATE 1
+
 const char* rr_last_error(void);
 int rr_version(void);
+
+/* Optional per-stage device timing: when enabled every entry point brackets each of its stages with CUDA events on the
+ * caller's stream (no reference counterpart; the reference only has CHECK_CUDA syncs, auxiliary.h:155-162).
+ * rr_prof_read synchronises the recorded events and returns accumulated milliseconds and call counts per stage
+ * (arrays of rr_prof_num_stages() entries; either may be null), optionally resetting the accumulators. */
+/* number of CUDA kernels this library has launched in this process so far */
+int64_t rr_launch_count(void);
+int rr_prof_enable(int on);
+int rr_prof_num_stages(void);
+const char* rr_prof_stage_name(int i);
+int rr_prof_read(double* ms, int64_t* calls, int reset);
 
 /* scratch sizes: replace required<GeometryState>(P), required<ImageState>(W*H), required<BinningState>(N)
  * (rasterizer_impl.h:55-62, rasterizer_impl.cu:144-183) */
@@ -55,6 +68,9 @@ int rr_forward_raster(void* stream, int P, int W, int H, int64_t N, const float*
 
 /* Backward — replaces Rasterizer::backward (rasterizer_impl.cu:334-430) and the torch::zeros fills of
  * RasterizeGaussiansBackwardCUDA (rasterize_points.cu:145-153): every element of every gradient buffer is written.
+ * flags & RR_BWD_ACCUMULATE (view-sharded batches, no reference counterpart): the parameter gradients (dL_dmean3D,
+ * dL_dsh / dL_dcolor, dL_dopacity, dL_dscale, dL_drot / dL_dcov3D) are ADDED to the buffers' contents and Gaussians
+ * with radii == 0 are left untouched; the per-view outputs dL_dmean2D and dL_dconic are still overwritten.
  * dL_dconic may be null (the reference keeps it internal).  dL_dsh is [P,M,3] (unused when shs is null),
  * dL_dscale / dL_drot may be null when cov3D_precomp is given.  ws: rr_backward_ws_bytes(N) of scratch. */
 int rr_backward(void* stream, int P, int D, int M, int W, int H, int64_t N, const float* background,
@@ -66,7 +82,7 @@ int rr_backward(void* stream, int P, int D, int M, int W, int H, int64_t N, cons
 	const float* dL_dpix, void* ws, size_t ws_bytes,
 	float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
 	float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
-	int variant, int debug);
+	int variant, int debug, int flags);
 
 /* replaces Rasterizer::markVisible / checkFrustum (rasterizer_impl.cu:43-55,130-142); present is uint8/bool [P] */
 int rr_mark_visible(void* stream, int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present);

@@ -163,7 +163,7 @@ class RefCuda:
         return None if (t is None or t.numel() == 0) else t.data_ptr()
 
     def forward(self, bg, means3D, opacities, scales, rotations, viewmatrix, projmatrix, campos, tanfovx, tanfovy, H, W,
-                shs=None, sh_degree=0, colors_precomp=None, cov3D_precomp=None, scale_modifier=1.0, low_pass=0.3, debug=False):
+                shs=None, sh_degree=0, colors_precomp=None, cov3D_precomp=None, scale_modifier=1.0, low_pass=0.3, debug=False, sync=True):
         torch = self.torch
         P = means3D.shape[0]
         dev = means3D.device
@@ -171,7 +171,8 @@ class RefCuda:
         out_color = torch.full((3, H, W), 0.0, dtype=torch.float32, device=dev)   # rasterize_points.cu:58-60
         radii = torch.full((P,), 0, dtype=torch.int32, device=dev)
         out_depth = torch.full((1, H, W), 0.0, dtype=torch.float32, device=dev)
-        torch.cuda.current_stream().synchronize()
+        if sync:    # only needed when the caller is not on torch's default stream (== the legacy stream the reference uses)
+            torch.cuda.current_stream().synchronize()
         N = self.lib.ref_forward(P, int(sh_degree), M, self._p(bg), W, H, self._p(means3D), self._p(shs), self._p(colors_precomp),
                                  self._p(opacities), self._p(scales), float(scale_modifier), self._p(rotations), self._p(cov3D_precomp),
                                  self._p(viewmatrix), self._p(projmatrix), self._p(campos), float(tanfovx), float(tanfovy), 0,
@@ -183,14 +184,15 @@ class RefCuda:
                           tanfovx=tanfovx, tanfovy=tanfovy, scale_modifier=scale_modifier, low_pass=low_pass, radii=radii, dev=dev)
         return int(N), out_color, radii, out_depth
 
-    def backward(self, dL_dpix, debug=False):
+    def backward(self, dL_dpix, debug=False, sync=True):
         torch = self.torch
         s = self._last
         P, M, dev = s["P"], s["M"], s["dev"]
         z = lambda *sh: torch.zeros(sh, dtype=torch.float32, device=dev)                # rasterize_points.cu:145-153
         g = dict(dL_dmean3D=z(P, 3), dL_dmean2D=z(P, 3), dL_dcolor=z(P, 3), dL_dconic=z(P, 2, 2), dL_dopacity=z(P, 1), dL_dcov3D=z(P, 6),
                  dL_dsh=z(P, M, 3), dL_dscale=z(P, 3), dL_drot=z(P, 4))
-        torch.cuda.current_stream().synchronize()
+        if sync:
+            torch.cuda.current_stream().synchronize()
         r = self.lib.ref_backward(P, s["D"], M, s["N"], self._p(s["bg"]), s["W"], s["H"], self._p(s["means3D"]), self._p(s["shs"]),
                                   self._p(s["colors_precomp"]), self._p(s["scales"]), float(s["scale_modifier"]), self._p(s["rotations"]),
                                   self._p(s["cov3D_precomp"]), self._p(s["view"]), self._p(s["proj"]), self._p(s["campos"]),

@@ -15,6 +15,11 @@ _vp, _i, _i64, _f, _sz = _c.c_void_p, _c.c_int, _c.c_int64, _c.c_float, _c.c_siz
 SIGNATURES = {
     "rr_last_error": (_c.c_char_p, []),
     "rr_version": (_i, []),
+    "rr_launch_count": (_i64, []),
+    "rr_prof_enable": (_i, [_i]),
+    "rr_prof_num_stages": (_i, []),
+    "rr_prof_stage_name": (_c.c_char_p, [_i]),
+    "rr_prof_read": (_i, [_c.POINTER(_c.c_double), _c.POINTER(_i64), _i]),
     "rr_geom_bytes": (_sz, [_i]),
     "rr_image_bytes": (_sz, [_i, _i]),
     "rr_binning_bytes": (_sz, [_i64, _i, _i]),
@@ -37,7 +42,7 @@ SIGNATURES = {
                          _vp, _vp, _sz,
                          _vp, _vp, _vp, _vp,
                          _vp, _vp, _vp, _vp, _vp,
-                         _i, _i]),
+                         _i, _i, _i]),
     "rr_mark_visible": (_i, [_vp, _i, _vp, _vp, _vp, _vp]),
     "rr_dist2_ws_bytes": (_sz, [_i]),
     "rr_dist2": (_i, [_vp, _i, _vp, _vp, _vp, _sz]),
@@ -75,6 +80,16 @@ def load():
 def last_error():
     msg = load().rr_last_error()
     return msg.decode() if msg else ""
+
+
+def stage_times(reset=True):
+    """{stage name: (total ms, calls)} accumulated since the last reset by rr_prof_enable(1) runs."""
+    lib = load()
+    n = lib.rr_prof_num_stages()
+    ms = (_c.c_double * n)()
+    calls = (_i64 * n)()
+    lib.rr_prof_read(ms, calls, 1 if reset else 0)
+    return {lib.rr_prof_stage_name(i).decode(): (ms[i], calls[i]) for i in range(n)}
 
 
 def check(status, what):

@@ -4,7 +4,10 @@
 // tensor allocation, which stays in Python.
 #include <cstdarg>
 #include <cstring>
+#include <atomic>
+#include <mutex>
 #include <string>
+#include <vector>
 #include "../../include/rain_rast.h"
 #include "common.cuh"
 #include "kernels.cuh"
@@ -13,6 +16,8 @@
 namespace rr {
 
 static thread_local std::string g_error;
+static std::atomic<long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 void set_error(const char* fmt, ...)
 {
@@ -30,6 +35,50 @@ int check_launch(const char* what, cudaStream_t stream, bool sync)
 }
 
 namespace {
+
+// ---- per-stage device timing (CUDA events on the caller's stream), off by default; used by bench.py -----------------
+enum StageId { ST_PREPROCESS = 0, ST_DEPTH_SORT, ST_SCAN, ST_DUPLICATE, ST_TILE_SORT, ST_RANGES_PACK, ST_RENDER_FWD,
+	ST_RENDER_BWD, ST_PREPROCESS_BWD, ST_DIST2, ST_COUNT };
+const char* const kStageNames[ST_COUNT] = { "preprocess_fwd", "depth_sort", "scan", "duplicate", "tile_sort", "ranges_pack",
+	"render_fwd", "render_bwd", "preprocess_bwd", "dist2" };
+struct Pending { int stage; cudaEvent_t a, b; };
+struct Prof {
+	std::mutex mu;
+	bool on = false;
+	std::vector<cudaEvent_t> pool;
+	std::vector<Pending> pending;
+	double ms[ST_COUNT] = {};
+	int64_t calls[ST_COUNT] = {};
+	cudaEvent_t get() {
+		if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+		cudaEvent_t e; cudaEventCreate(&e); return e;
+	}
+	void drain() {   // caller holds mu
+		for (const Pending& p : pending) {
+			float t = 0.f;
+			if (cudaEventSynchronize(p.b) == cudaSuccess && cudaEventElapsedTime(&t, p.a, p.b) == cudaSuccess) { ms[p.stage] += t; calls[p.stage]++; }
+			pool.push_back(p.a); pool.push_back(p.b);
+		}
+		pending.clear();
+	}
+};
+Prof g_prof;
+struct Stage {
+	cudaStream_t stream; int id; cudaEvent_t a = nullptr; bool live = false;
+	Stage(cudaStream_t s, int id_) : stream(s), id(id_) {
+		if (!g_prof.on) return;
+		std::lock_guard<std::mutex> lk(g_prof.mu);
+		a = g_prof.get(); live = true;
+		cudaEventRecord(a, stream);
+	}
+	~Stage() {
+		if (!live) return;
+		std::lock_guard<std::mutex> lk(g_prof.mu);
+		cudaEvent_t b = g_prof.get();
+		cudaEventRecord(b, stream);
+		g_prof.pending.push_back({ id, a, b });
+	}
+};
 
 // bit length, the reference's getHigherMsb (rasterizer_impl.cu:24-39)
 int tile_bits(int num_tiles) { int b = 0; while ((num_tiles >> b) != 0) b++; return b < 1 ? 1 : b; }
@@ -118,7 +167,26 @@ using namespace rr;
 extern "C" {
 
 const char* rr_last_error(void) { return g_error.c_str(); }
-int rr_version(void) { return 1; }
+int rr_version(void) { return 2; }
+
+int64_t rr_launch_count(void) { return (int64_t)g_launches.load(); }
+
+int rr_prof_enable(int on)
+{
+	std::lock_guard<std::mutex> lk(g_prof.mu);
+	g_prof.on = on != 0;
+	return 0;
+}
+int rr_prof_num_stages(void) { return ST_COUNT; }
+const char* rr_prof_stage_name(int i) { return (i >= 0 && i < ST_COUNT) ? kStageNames[i] : ""; }
+int rr_prof_read(double* ms, int64_t* calls, int reset)
+{
+	std::lock_guard<std::mutex> lk(g_prof.mu);
+	g_prof.drain();
+	for (int i = 0; i < ST_COUNT; i++) { if (ms) ms[i] = g_prof.ms[i]; if (calls) calls[i] = g_prof.calls[i]; }
+	if (reset) for (int i = 0; i < ST_COUNT; i++) { g_prof.ms[i] = 0; g_prof.calls[i] = 0; }
+	return 0;
+}
 
 size_t rr_geom_bytes(int P) { return geom_layout(nullptr, P).total + 256; }
 size_t rr_image_bytes(int W, int H) { return img_layout(nullptr, W, H).total + 256; }
@@ -159,13 +227,14 @@ int rr_forward_geom(void* stream_, int P, int D, int M, int W, int H,
 	a.means3D = means3D; a.scales = scales; a.rotations = rotations; a.opacities = opacities; a.shs = colors_precomp ? nullptr : shs;
 	a.cov3D_precomp = cov3D_precomp; a.colors_precomp = colors_precomp; a.view = viewmatrix; a.proj = projmatrix; a.campos = campos;
 	a.radii = radii; a.rec = L.rec; a.cov3D = L.cov3D; a.clamped = L.clamped; a.tiles_touched = L.tiles_touched; a.depth_key = L.key_a; a.rect = L.rect;
-	if (launch_preprocess_fwd(stream, a)) return -1;
+	{ Stage st(stream, ST_PREPROCESS); if (launch_preprocess_fwd(stream, a)) return -1; }
 	if (debug && check_launch("preprocess_fwd", stream, true)) return -1;
 	// depth order of the Gaussians: 32-bit keys, 4 passes, result in the *_a buffers
-	const int which = sort_pairs<uint32_t>(stream, L.key_a, L.key_b, L.val_a, L.val_b, (size_t)P, 0, 32, L.sort_ws, true);
+	int which;
+	{ Stage st(stream, ST_DEPTH_SORT); which = sort_pairs<uint32_t>(stream, L.key_a, L.key_b, L.val_a, L.val_b, (size_t)P, 0, 32, L.sort_ws, true); }
 	if (which != 0) { if (which > 0) set_error("internal: depth sort landed in the wrong buffer"); return -1; }
 	if (debug && check_launch("depth sort", stream, true)) return -1;
-	if (launch_scan_tiles(stream, P, L.val_a, L.tiles_touched, L.offsets, L.block_sums, L.num_rendered)) return -1;
+	{ Stage st(stream, ST_SCAN); if (launch_scan_tiles(stream, P, L.val_a, L.tiles_touched, L.offsets, L.block_sums, L.num_rendered)) return -1; }
 	// num_rendered: u32 on the device, widened on the host side of the copy (the upper half was zeroed above)
 	cudaMemcpyAsync(num_rendered_host, L.num_rendered, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream);
 	return check_launch("forward_geom", stream, debug != 0);
@@ -187,22 +256,26 @@ int rr_forward_raster(void* stream_, int P, int W, int H, int64_t N, const float
 	const int grid_x = (W + TILE_X - 1) / TILE_X, grid_y = (H + TILE_Y - 1) / TILE_Y;
 
 	if (N > 0) {
-		if (launch_duplicate(stream, P, G.val_a, G.offsets, G.rect, grid_x, B.key_a, B.owner, G.dup_off)) return -1;
+		{ Stage st(stream, ST_DUPLICATE); if (launch_duplicate(stream, P, G.val_a, G.offsets, G.rect, grid_x, B.key_a, B.owner, G.dup_off)) return -1; }
 		if (debug && check_launch("duplicate", stream, true)) return -1;
-		const int which = sort_pairs<uint32_t>(stream, B.key_a, B.key_b, B.emit_a, B.emit_b, (size_t)N, 0, B.bits, B.sort_ws, true);
+		int which;
+		{ Stage st(stream, ST_TILE_SORT); which = sort_pairs<uint32_t>(stream, B.key_a, B.key_b, B.emit_a, B.emit_b, (size_t)N, 0, B.bits, B.sort_ws, true); }
 		if (which < 0) return -1;
 		if ((which ? B.key_b : B.key_a) != B.keys_sorted) { set_error("internal: tile sort landed in the wrong buffer"); return -1; }
 		if (debug && check_launch("tile sort", stream, true)) return -1;
 	}
-	if (launch_tile_ranges(stream, (size_t)N, B.keys_sorted, I.ranges, grid_x * grid_y)) return -1;
-	if (launch_pack(stream, (size_t)N, B.emit_sorted, B.owner, G.rec, B.packed, B.point_list)) return -1;
+	{
+		Stage st(stream, ST_RANGES_PACK);
+		if (launch_tile_ranges(stream, (size_t)N, B.keys_sorted, I.ranges, grid_x * grid_y)) return -1;
+		if (launch_pack(stream, (size_t)N, B.emit_sorted, B.owner, G.rec, B.packed, B.point_list)) return -1;
+	}
 	if (debug && check_launch("ranges/pack", stream, true)) return -1;
 
 	RenderArgs r; memset(&r, 0, sizeof(r));
 	r.W = W; r.H = H; r.grid_x = grid_x; r.grid_y = grid_y;
 	r.ranges = I.ranges; r.packed = B.packed; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.tile_max_contrib = I.tile_max;
 	r.out_color = out_color; r.out_depth = out_depth; r.variant = variant;
-	if (launch_render_fwd(stream, r)) return -1;
+	{ Stage st(stream, ST_RENDER_FWD); if (launch_render_fwd(stream, r)) return -1; }
 	return check_launch("forward_raster", stream, debug != 0);
 }
 
@@ -215,7 +288,7 @@ int rr_backward(void* stream_, int P, int D, int M, int W, int H, int64_t N, con
 	const float* dL_dpix, void* ws, size_t ws_bytes,
 	float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
 	float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
-	int variant, int debug)
+	int variant, int debug, int flags)
 {
 	cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
 	if (P == 0) return 0;                                                  // rasterize_points.cu:155
@@ -237,7 +310,7 @@ int rr_backward(void* stream_, int P, int D, int M, int W, int H, int64_t N, con
 	r.ranges = I.ranges; r.packed = B.packed; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.tile_max_contrib = I.tile_max;
 	r.dL_dpix = dL_dpix; r.sorted_emit = B.emit_sorted; r.partial = partial; r.variant = variant;
 	if (N > 0) {
-		if (launch_render_bwd(stream, r)) return -1;
+		{ Stage st(stream, ST_RENDER_BWD); if (launch_render_bwd(stream, r)) return -1; }
 		if (debug && check_launch("render_bwd", stream, true)) return -1;
 	}
 
@@ -247,11 +320,11 @@ int rr_backward(void* stream_, int P, int D, int M, int W, int H, int64_t N, con
 	a.scale_modifier = scale_modifier; a.low_pass = low_pass;
 	a.means3D = means3D; a.scales = cov3D_precomp ? nullptr : scales; a.rotations = cov3D_precomp ? nullptr : rotations;
 	a.shs = use_sh ? shs : nullptr; a.cov3D = cov3D_precomp ? cov3D_precomp : G.cov3D;        // rasterizer_impl.cu:406
-	a.view = viewmatrix; a.proj = projmatrix; a.campos = campos; a.has_colors_precomp = colors_precomp != nullptr;
+	a.view = viewmatrix; a.proj = projmatrix; a.campos = campos; a.has_colors_precomp = colors_precomp != nullptr; a.accumulate = (flags & RR_BWD_ACCUMULATE) ? 1 : 0;
 	a.radii = radii; a.clamped = G.clamped; a.tiles_touched = G.tiles_touched; a.dup_off = G.dup_off; a.partial = partial;
 	a.dL_dmean2D = dL_dmean2D; a.dL_dconic = dL_dconic; a.dL_dopacity = dL_dopacity; a.dL_dcolor = dL_dcolor; a.dL_dmean3D = dL_dmean3D;
 	a.dL_dcov3D = dL_dcov3D; a.dL_dsh = dL_dsh; a.dL_dscale = dL_dscale; a.dL_drot = dL_drot;
-	if (launch_preprocess_bwd(stream, a)) return -1;
+	{ Stage st(stream, ST_PREPROCESS_BWD); if (launch_preprocess_bwd(stream, a)) return -1; }
 	return check_launch("backward", stream, debug != 0);
 }
 
@@ -268,6 +341,7 @@ int rr_dist2(void* stream_, int P, const float* points, float* out, void* ws, si
 {
 	if (P == 0) return 0;
 	if (bad_ptr(points, "points") || bad_ptr(out, "out") || bad_ptr(ws, "ws")) return -1;
+	Stage st(reinterpret_cast<cudaStream_t>(stream_), ST_DIST2);
 	return launch_dist2(reinterpret_cast<cudaStream_t>(stream_), P, points, out, ws, ws_bytes);
 }
 

@@ -177,9 +177,9 @@ int launch_scan_tiles(cudaStream_t stream, int P, const uint32_t* order, const u
 {
 	if (P == 0) { cudaMemsetAsync(num_rendered_dev, 0, sizeof(uint32_t), stream); return 0; }
 	const int nb = (P + SCAN_TILE - 1) / SCAN_TILE;
-	scan_reduce_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, order, tt, block_sums);
-	scan_blocksums_kernel<<<1, SCAN_THREADS, 0, stream>>>(nb, block_sums, num_rendered_dev);
-	scan_final_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, order, tt, block_sums, offsets);
+	count_launch(), scan_reduce_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, order, tt, block_sums);
+	count_launch(), scan_blocksums_kernel<<<1, SCAN_THREADS, 0, stream>>>(nb, block_sums, num_rendered_dev);
+	count_launch(), scan_final_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, order, tt, block_sums, offsets);
 	return check_launch("scan_tiles", stream, false);
 }
 
@@ -187,7 +187,7 @@ int launch_duplicate(cudaStream_t stream, int P, const uint32_t* order, const ui
 	uint32_t* tile_keys, uint32_t* owner, uint32_t* dup_off)
 {
 	if (P == 0) return 0;
-	duplicate_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, order, offsets, rect, grid_x, tile_keys, owner, dup_off);
+	count_launch(), duplicate_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, order, offsets, rect, grid_x, tile_keys, owner, dup_off);
 	return check_launch("duplicate", stream, false);
 }
 
@@ -195,14 +195,14 @@ int launch_tile_ranges(cudaStream_t stream, size_t N, const uint32_t* keys, uint
 {
 	cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)num_tiles, stream);
 	if (N == 0) return 0;
-	tile_ranges_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>((uint32_t)N, keys, ranges);
+	count_launch(), tile_ranges_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>((uint32_t)N, keys, ranges);
 	return check_launch("tile_ranges", stream, false);
 }
 
 int launch_pack(cudaStream_t stream, size_t N, const uint32_t* sorted_emit, const uint32_t* owner, const SplatRec* rec, SplatRec* packed, uint32_t* point_list)
 {
 	if (N == 0) return 0;
-	pack_kernel<<<(unsigned)((N * 3 + 255) / 256), 256, 0, stream>>>((uint32_t)N, sorted_emit, owner, reinterpret_cast<const float4*>(rec),
+	count_launch(), pack_kernel<<<(unsigned)((N * 3 + 255) / 256), 256, 0, stream>>>((uint32_t)N, sorted_emit, owner, reinterpret_cast<const float4*>(rec),
 		reinterpret_cast<float4*>(packed), point_list);
 	return check_launch("pack", stream, false);
 }
@@ -210,7 +210,7 @@ int launch_pack(cudaStream_t stream, size_t N, const uint32_t* sorted_emit, cons
 int launch_export_keys(cudaStream_t stream, size_t N, const uint32_t* tile_keys, const uint32_t* point_list, const uint32_t* rec_words, uint64_t* out)
 {
 	if (N == 0) return 0;
-	export_keys_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>((uint32_t)N, tile_keys, point_list, rec_words, out);
+	count_launch(), export_keys_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>((uint32_t)N, tile_keys, point_list, rec_words, out);
 	return check_launch("export_keys", stream, false);
 }
 

@@ -41,6 +41,7 @@ struct Carver {
 
 void set_error(const char* fmt, ...);
 int check_launch(const char* what, cudaStream_t stream, bool sync);
+void count_launch();   // every kernel launch of the library is counted (rr_launch_count), bench.py reports it
 
 __device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31u; }
 __device__ __forceinline__ unsigned lanemask_lt() { unsigned m; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m)); return m; }

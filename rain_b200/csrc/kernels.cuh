@@ -56,6 +56,7 @@ struct PreprocessBwdArgs {
 	float tan_fovx, tan_fovy, focal_x, focal_y, scale_modifier, low_pass;
 	const float *means3D, *scales, *rotations, *shs, *cov3D /*precomp or geom*/, *view, *proj, *campos;
 	int has_colors_precomp;
+	int accumulate;           // 1: += into the parameter-gradient buffers, untouched where radii == 0
 	const int* radii;
 	const uint8_t* clamped;
 	const uint32_t* tiles_touched;

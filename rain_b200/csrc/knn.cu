@@ -211,17 +211,17 @@ int launch_dist2(cudaStream_t stream, int P, const float* points, float* out, vo
 	const KnnWs L = knn_layout(ws, P);
 	if (L.total > ws_bytes) { set_error("dist2: workspace too small (%zu < %zu)", ws_bytes, L.total); return -1; }
 	const int rb = min(1024, (P + 255) / 256);
-	minmax_partial_kernel<<<rb, 256, 0, stream>>>(P, points, L.mm_partial);
-	minmax_final_kernel<<<1, 32, 0, stream>>>(rb, L.mm_partial, L.mm);
-	morton_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, points, L.mm, L.keys_a);
+	count_launch(), minmax_partial_kernel<<<rb, 256, 0, stream>>>(P, points, L.mm_partial);
+	count_launch(), minmax_final_kernel<<<1, 32, 0, stream>>>(rb, L.mm_partial, L.mm);
+	count_launch(), morton_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, points, L.mm, L.keys_a);
 	const int which = sort_pairs<uint32_t>(stream, L.keys_a, L.keys_b, L.vals_a, L.vals_b, (size_t)P, 0, 30, L.sort_ws, true);
 	if (which < 0) return -1;
 	const uint32_t* order = which ? L.vals_b : L.vals_a;
-	gather_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, points, order, L.sorted);
-	box_aabb_kernel<<<(L.nboxes + 7) / 8, 256, 0, stream>>>(P, L.nboxes, L.sorted, L.boxes);
-	merge_aabb_kernel<<<(L.ngroups + 7) / 8, 256, 0, stream>>>(L.nboxes, L.ngroups, L.boxes, L.groups);
-	merge_aabb_kernel<<<(L.nsuper + 7) / 8, 256, 0, stream>>>(L.ngroups, L.nsuper, L.groups, L.supers);
-	knn_search_kernel<<<L.nboxes, BOX, 0, stream>>>(P, L.nboxes, L.ngroups, L.nsuper, L.sorted, L.boxes, L.groups, L.supers, out);
+	count_launch(), gather_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, points, order, L.sorted);
+	count_launch(), box_aabb_kernel<<<(L.nboxes + 7) / 8, 256, 0, stream>>>(P, L.nboxes, L.sorted, L.boxes);
+	count_launch(), merge_aabb_kernel<<<(L.ngroups + 7) / 8, 256, 0, stream>>>(L.nboxes, L.ngroups, L.boxes, L.groups);
+	count_launch(), merge_aabb_kernel<<<(L.nsuper + 7) / 8, 256, 0, stream>>>(L.ngroups, L.nsuper, L.groups, L.supers);
+	count_launch(), knn_search_kernel<<<L.nboxes, BOX, 0, stream>>>(P, L.nboxes, L.ngroups, L.nsuper, L.sorted, L.boxes, L.groups, L.supers, out);
 	return check_launch("dist2", stream, false);
 }
 

@@ -259,14 +259,14 @@ __global__ void __launch_bounds__(256) mark_visible_kernel(int P, const float* _
 int launch_preprocess_fwd(cudaStream_t stream, const PreprocessArgs& a)
 {
 	if (a.P == 0) return 0;
-	preprocess_fwd_kernel<<<(a.P + 255) / 256, 256, 0, stream>>>(a);
+	count_launch(), preprocess_fwd_kernel<<<(a.P + 255) / 256, 256, 0, stream>>>(a);
 	return check_launch("preprocess_fwd", stream, false);
 }
 
 int launch_mark_visible(cudaStream_t stream, int P, const float* means3D, const float* view, uint8_t* present)
 {
 	if (P == 0) return 0;
-	mark_visible_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, means3D, view, present);
+	count_launch(), mark_visible_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, means3D, view, present);
 	return check_launch("mark_visible", stream, false);
 }
 

@@ -25,6 +25,10 @@ __global__ void __launch_bounds__(128) preprocess_bwd_kernel(PreprocessBwdArgs a
 	if (idx >= a.P) return;
 	const size_t i3 = 3 * (size_t)idx;
 	const bool visible = a.radii[idx] > 0;
+	// accumulate mode (multi-view batches, see rr_backward flags): parameter gradients are added to what the buffers
+	// hold and a Gaussian this view does not see is not touched at all; otherwise every element is overwritten.
+	const bool acc = a.accumulate != 0;
+	auto put1 = [acc](float* p, float v) { *p = acc ? *p + v : v; };
 
 	// ---- gather the (tile, Gaussian) partials ----
 	float g[9];
@@ -39,9 +43,10 @@ __global__ void __launch_bounds__(128) preprocess_bwd_kernel(PreprocessBwdArgs a
 		}
 	}
 	a.dL_dmean2D[i3] = g[3]; a.dL_dmean2D[i3 + 1] = g[4]; a.dL_dmean2D[i3 + 2] = 0.0f;
-	a.dL_dopacity[idx] = g[8];
-	a.dL_dcolor[i3] = g[0]; a.dL_dcolor[i3 + 1] = g[1]; a.dL_dcolor[i3 + 2] = g[2];
 	if (a.dL_dconic) reinterpret_cast<float4*>(a.dL_dconic)[idx] = make_float4(g[5], g[6], 0.0f, g[7]);
+	if (acc && !visible) return;
+	put1(a.dL_dopacity + idx, g[8]);
+	put1(a.dL_dcolor + i3, g[0]); put1(a.dL_dcolor + i3 + 1, g[1]); put1(a.dL_dcolor + i3 + 2, g[2]);
 
 	float dmean[3] = { 0, 0, 0 }, dcov[6] = { 0, 0, 0, 0, 0, 0 };
 	const float mx = a.means3D[i3], my = a.means3D[i3 + 1], mz = a.means3D[i3 + 2];
@@ -114,7 +119,7 @@ __global__ void __launch_bounds__(128) preprocess_bwd_kernel(PreprocessBwdArgs a
 		dmean[2] += (Pj[8] * m_w - Pj[11] * mul1) * g[3] + (Pj[9] * m_w - Pj[11] * mul2) * g[4];
 	}
 	#pragma unroll
-	for (int k = 0; k < 6; k++) a.dL_dcov3D[6 * (size_t)idx + k] = dcov[k];
+	for (int k = 0; k < 6; k++) put1(a.dL_dcov3D + 6 * (size_t)idx + k, dcov[k]);
 
 	// ---- SH colour gradient (reference backward.cu:9-128) ----
 	if (a.shs) {
@@ -128,7 +133,7 @@ __global__ void __launch_bounds__(128) preprocess_bwd_kernel(PreprocessBwdArgs a
 			const float inv_len = 1.0f / sqrtf(ox * ox + oy * oy + oz * oz);
 			const float x = ox * inv_len, y = oy * inv_len, z = oz * inv_len;
 			float ddx = 0, ddy = 0, ddz = 0;   // dL/d(dir)
-			auto put = [&](int k, float wgt) { dsh[3 * k] = wgt * dR[0]; dsh[3 * k + 1] = wgt * dR[1]; dsh[3 * k + 2] = wgt * dR[2]; };
+			auto put = [&](int k, float wgt) { put1(dsh + 3 * k, wgt * dR[0]); put1(dsh + 3 * k + 1, wgt * dR[1]); put1(dsh + 3 * k + 2, wgt * dR[2]); };
 			auto dot = [&](int k) { return sh[3 * k] * dR[0] + sh[3 * k + 1] * dR[1] + sh[3 * k + 2] * dR[2]; };
 			put(0, kC0);
 			if (a.D > 0) {
@@ -162,9 +167,9 @@ __global__ void __launch_bounds__(128) preprocess_bwd_kernel(PreprocessBwdArgs a
 			dmean[1] += (-ox * oy * ddx + (sum2 - oy * oy) * ddy - oz * oy * ddz) * invsum32;
 			dmean[2] += (-ox * oz * ddx - oy * oz * ddy + (sum2 - oz * oz) * ddz) * invsum32;
 		}
-		for (int k = nact; k < a.M; k++) { dsh[3 * k] = 0.0f; dsh[3 * k + 1] = 0.0f; dsh[3 * k + 2] = 0.0f; }
+		if (!acc) for (int k = nact; k < a.M; k++) { dsh[3 * k] = 0.0f; dsh[3 * k + 1] = 0.0f; dsh[3 * k + 2] = 0.0f; }
 	}
-	a.dL_dmean3D[i3] = dmean[0]; a.dL_dmean3D[i3 + 1] = dmean[1]; a.dL_dmean3D[i3 + 2] = dmean[2];
+	put1(a.dL_dmean3D + i3, dmean[0]); put1(a.dL_dmean3D + i3 + 1, dmean[1]); put1(a.dL_dmean3D + i3 + 2, dmean[2]);
 
 	// ---- 3D covariance -> scale, rotation (reference backward.cu:268-331) ----
 	float ds[3] = { 0, 0, 0 };
@@ -196,8 +201,12 @@ __global__ void __launch_bounds__(128) preprocess_bwd_kernel(PreprocessBwdArgs a
 		dq.z = 2 * x * (dMt[1][0] + dMt[0][1]) + 2 * r * (dMt[2][0] - dMt[0][2]) + 2 * z * (dMt[1][2] + dMt[2][1]) - 4 * y * (dMt[2][2] + dMt[0][0]);
 		dq.w = 2 * r * (dMt[0][1] - dMt[1][0]) + 2 * x * (dMt[2][0] + dMt[0][2]) + 2 * y * (dMt[1][2] + dMt[2][1]) - 4 * z * (dMt[1][1] + dMt[0][0]);
 	}
-	if (a.dL_dscale) { a.dL_dscale[i3] = ds[0]; a.dL_dscale[i3 + 1] = ds[1]; a.dL_dscale[i3 + 2] = ds[2]; }
-	if (a.dL_drot) reinterpret_cast<float4*>(a.dL_drot)[idx] = dq;
+	if (a.dL_dscale) { put1(a.dL_dscale + i3, ds[0]); put1(a.dL_dscale + i3 + 1, ds[1]); put1(a.dL_dscale + i3 + 2, ds[2]); }
+	if (a.dL_drot) {
+		float4* o = reinterpret_cast<float4*>(a.dL_drot) + idx;
+		if (acc) { const float4 c = *o; dq.x += c.x; dq.y += c.y; dq.z += c.z; dq.w += c.w; }
+		*o = dq;
+	}
 }
 
 }  // namespace
@@ -205,7 +214,7 @@ __global__ void __launch_bounds__(128) preprocess_bwd_kernel(PreprocessBwdArgs a
 int launch_preprocess_bwd(cudaStream_t stream, const PreprocessBwdArgs& a)
 {
 	if (a.P == 0) return 0;
-	preprocess_bwd_kernel<<<(a.P + 127) / 128, 128, 0, stream>>>(a);
+	count_launch(), preprocess_bwd_kernel<<<(a.P + 127) / 128, 128, 0, stream>>>(a);
 	return check_launch("preprocess_bwd", stream, false);
 }
 

@@ -250,12 +250,12 @@ int sort_pairs(cudaStream_t stream, K* keys_a, K* keys_b, uint32_t* vals_a, uint
 	const WsLayout L = ws_layout<K>(ws, n, pd.npass);
 	cudaMemsetAsync(ws, 0, L.zero_bytes, stream);
 	const uint32_t hgrid = (uint32_t)((n + SORT_THREADS * 16 - 1) / (SORT_THREADS * 16));
-	histogram_kernel<K><<<hgrid < 1184u ? hgrid : 1184u, SORT_THREADS, 0, stream>>>(keys_a, (uint32_t)n, pd, L.ghist);
-	digit_base_kernel<<<pd.npass, RADIX, 0, stream>>>(L.ghist);
+	count_launch(), histogram_kernel<K><<<hgrid < 1184u ? hgrid : 1184u, SORT_THREADS, 0, stream>>>(keys_a, (uint32_t)n, pd, L.ghist);
+	count_launch(), digit_base_kernel<<<pd.npass, RADIX, 0, stream>>>(L.ghist);
 	K* kin = keys_a; K* kout = keys_b;
 	uint32_t* vin = vals_a; uint32_t* vout = vals_b;
 	for (int p = 0; p < pd.npass; p++) {
-		onesweep_kernel<K, IPT><<<L.ntiles, SORT_THREADS, 0, stream>>>(kin, kout, (p == 0 && iota_vals) ? nullptr : vin, vout,
+		count_launch(), onesweep_kernel<K, IPT><<<L.ntiles, SORT_THREADS, 0, stream>>>(kin, kout, (p == 0 && iota_vals) ? nullptr : vin, vout,
 			(uint32_t)n, pd.shift[p], pd.mask[p], L.ghist + p * RADIX, L.tickets + p, L.status + (size_t)p * L.ntiles * RADIX);
 		K* tk = kin; kin = kout; kout = tk;
 		uint32_t* tv = vin; vin = vout; vout = tv;

@@ -212,8 +212,8 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 int launch_render_bwd(cudaStream_t stream, const RenderArgs& a)
 {
 	const dim3 grid(a.grid_x, a.grid_y);
-	if (a.variant == 0) render_bwd_kernel<false><<<grid, RENDER_THREADS, 0, stream>>>(a);
-	else render_bwd_kernel<true><<<grid, RENDER_THREADS, 0, stream>>>(a);
+	if (a.variant == 0) count_launch(), render_bwd_kernel<false><<<grid, RENDER_THREADS, 0, stream>>>(a);
+	else count_launch(), render_bwd_kernel<true><<<grid, RENDER_THREADS, 0, stream>>>(a);
 	return check_launch("render_bwd", stream, false);
 }
 

@@ -1,0 +1,128 @@
+"""View-sharded data parallelism for the rasterizer — the one component with no reference
+counterpart: sharonal10/rain is single-process, single-GPU (utils/general_utils.py:90).
+
+The path shards across camera views: every rank (one process per GPU) holds a full replica of the Gaussian parameters
+and renders its slice of the view batch.  The backward-preprocess kernel ADDS each view's parameter gradients straight
+into one flat per-rank bucket (RR_BWD_ACCUMULATE, no zero-fill pass, Gaussians a view does not see are not touched),
+and ONE all-reduce (NCCL over NVLink/NVSwitch, sum, f32, 59 floats per Gaussian with 16 SH coefficients) combines the
+ranks per step.  No other exchange is needed; Gaussians and tiles are not partitioned.
+
+Bucket layout (floats, contiguous, so that each segment is directly usable as the .grad of the matching tensor):
+    means3D [P,3] | sh [P,M,3] | opacity [P,1] | scales [P,3] | rotations [P,4]
+"""
+from dataclasses import dataclass
+from typing import Callable, List, Optional, Sequence
+
+import torch
+
+from . import _C as _native
+
+SEGMENTS = ("means3D", "sh", "opacity", "scales", "rotations")
+
+
+def shard_views(num_views: int, rank: int, world_size: int) -> List[int]:
+    """Contiguous block partition of view indices 0..num_views-1; block sizes differ by at most one and every view
+    belongs to exactly one rank."""
+    if world_size < 1 or not (0 <= rank < world_size):
+        raise ValueError(f"bad rank/world_size {rank}/{world_size}")
+    base, extra = divmod(num_views, world_size)
+    start = rank * base + min(rank, extra)
+    return list(range(start, start + base + (1 if rank < extra else 0)))
+
+
+class GradientBucket:
+    """One flat f32 buffer holding the per-Gaussian parameter gradients of a rank, plus typed views of its segments."""
+
+    def __init__(self, P: int, M: int, device):
+        self.P, self.M = int(P), int(M)
+        self.floats_per_gaussian = 3 + 3 * self.M + 1 + 3 + 4
+        self.flat = torch.zeros(self.P * self.floats_per_gaussian, dtype=torch.float32, device=device)
+        shapes = dict(means3D=(self.P, 3), sh=(self.P, self.M, 3), opacity=(self.P, 1), scales=(self.P, 3), rotations=(self.P, 4))
+        self.views, off = {}, 0
+        for name in SEGMENTS:
+            n = 1
+            for d in shapes[name]:
+                n *= d
+            self.views[name] = self.flat[off:off + n].view(shapes[name])
+            off += n
+        assert off == self.flat.numel()
+        self.filled = False
+
+    def grads_out(self):
+        return dict(self.views)
+
+    def zero_(self):
+        self.flat.zero_()
+        self.filled = False
+
+    def nbytes(self):
+        return self.flat.numel() * 4
+
+
+@dataclass
+class ViewResult:
+    view: int
+    color: torch.Tensor
+    depth: torch.Tensor
+    radii: torch.Tensor
+    num_rendered: int
+    dL_dmeans2D: Optional[torch.Tensor]
+
+
+def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int], bucket: GradientBucket,
+                         grad_fn: Callable[[int, torch.Tensor, torch.Tensor], torch.Tensor], *, bg: torch.Tensor, sh_degree: int,
+                         scale_modifier: float = 1.0, low_pass: float = 0.3, debug: bool = False, keep_outputs: bool = True,
+                         backend=_native) -> List[ViewResult]:
+    """Forward + backward of this rank's views; parameter gradients of all views are summed into ``bucket``.
+
+    params: dict(means3D[P,3], opacities[P,1], shs[P,M,3], scales[P,3], rotations[P,4]) — activated values, as
+    gaussian_renderer/__init__.py:37-60 passes them.  cameras[v] has width/height/tanfovx/tanfovy/viewmatrix/projmatrix/
+    campos (rain_b200.synthetic.Camera or the reference's scene.cameras.Camera fields).  grad_fn(view, color, depth)
+    returns dL/dcolor [3,H,W] (the loss backward of train.py:113-115).  The first view overwrites the bucket (no
+    zero-fill pass), later views accumulate."""
+    dev = params["means3D"].device
+    e = torch.empty(0, device=dev)
+    results = []
+    for v in view_ids:
+        cam = cameras[v]
+        N, color, radii, depth, geom, binning, img = backend.rasterize_gaussians(
+            bg, params["means3D"], e, params["opacities"], params["scales"], params["rotations"], scale_modifier, e,
+            cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, cam.height, cam.width, params["shs"], sh_degree, cam.campos,
+            False, debug, low_pass)
+        dpix = grad_fn(v, color, depth)
+        if not bucket.filled:
+            # slots are overwritten by the first view; culled Gaussians get explicit zeros from the kernel
+            grads = backend.rasterize_gaussians_backward(
+                bg, params["means3D"], radii, e, params["scales"], params["rotations"], scale_modifier, e, cam.viewmatrix, cam.projmatrix,
+                cam.tanfovx, cam.tanfovy, dpix, params["shs"], sh_degree, cam.campos, geom, N, binning, img, debug, low_pass,
+                grads_out=bucket.grads_out(), accumulate=False)
+            bucket.filled = True
+        else:
+            grads = backend.rasterize_gaussians_backward(
+                bg, params["means3D"], radii, e, params["scales"], params["rotations"], scale_modifier, e, cam.viewmatrix, cam.projmatrix,
+                cam.tanfovx, cam.tanfovy, dpix, params["shs"], sh_degree, cam.campos, geom, N, binning, img, debug, low_pass,
+                grads_out=bucket.grads_out(), accumulate=True)
+        results.append(ViewResult(v, color if keep_outputs else None, depth if keep_outputs else None, radii if keep_outputs else None,
+                                  int(N), grads[0] if keep_outputs else None))
+    return results
+
+
+def allreduce_bucket(bucket: GradientBucket, group=None, average: bool = False):
+    """The single collective of a step: sum (or mean) of the flat bucket over all ranks, in place."""
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(bucket.flat, op=dist.ReduceOp.SUM, group=group)
+        if average:
+            bucket.flat.div_(dist.get_world_size(group))
+    return bucket
+
+
+def train_step_views(params, cameras, num_views, bucket, grad_fn, *, rank=0, world_size=1, group=None, **kw):
+    """One data-parallel step: zero-copy accumulate the local views' gradients, then one all-reduce."""
+    bucket.filled = False
+    local = shard_views(num_views, rank, world_size)
+    res = render_views_fwd_bwd(params, cameras, local, bucket, grad_fn, **kw)
+    if not local:
+        bucket.zero_()
+    allreduce_bucket(bucket, group)
+    return res

@@ -1,0 +1,93 @@
+"""CPU tests of the host-side mirror of the reference's Python interface: same import paths, names, field order,
+keyword arguments and error behaviour as submodules/diff_gaussian_rasterization/diff_gaussian_rasterization/__init__.py
+and simple_knn._C of sharonal10/rain.  No kernel runs here."""
+import inspect
+
+import pytest
+import torch
+
+
+def test_reference_import_paths_resolve_to_this_package():
+    from submodules.diff_gaussian_rasterization.diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer  # noqa: F401  gaussian_renderer/__init__.py:5
+    from simple_knn._C import distCUDA2  # noqa: F401  scene/gaussian_model.py:9
+    import rain_b200
+    assert GaussianRasterizer is rain_b200.GaussianRasterizer
+    assert distCUDA2 is rain_b200.distCUDA2
+
+
+def test_settings_fields_match_reference_order():
+    from rain_b200 import GaussianRasterizationSettings as S
+    # reference __init__.py:148-161 (low_pass is this fork's addition, last)
+    assert S._fields == ("image_height", "image_width", "tanfovx", "tanfovy", "bg", "scale_modifier", "viewmatrix", "projmatrix",
+                         "sh_degree", "campos", "prefiltered", "debug", "low_pass")
+
+
+def test_forward_keyword_names_match_reference():
+    from rain_b200 import GaussianRasterizer
+    sig = inspect.signature(GaussianRasterizer.forward)
+    assert list(sig.parameters) == ["self", "means3D", "means2D", "opacities", "shs", "colors_precomp", "scales", "rotations", "cov3D_precomp"]
+    assert hasattr(GaussianRasterizer, "markVisible")
+
+
+def _settings():
+    from rain_b200 import GaussianRasterizationSettings
+    return GaussianRasterizationSettings(16, 16, 0.5, 0.5, torch.zeros(3), 1.0, torch.eye(4), torch.eye(4), 0, torch.zeros(3), False, False, 0.3)
+
+
+def test_argument_combination_errors_match_reference():
+    from rain_b200 import GaussianRasterizer
+    r = GaussianRasterizer(_settings())
+    m = torch.zeros(4, 3); o = torch.ones(4, 1); sh = torch.zeros(4, 16, 3); c = torch.zeros(4, 3); s = torch.ones(4, 3); q = torch.ones(4, 4); cov = torch.zeros(4, 6)
+    with pytest.raises(Exception, match="excatly one of either SHs or precomputed colors"):      # reference typo kept (__init__.py:184)
+        r(m, m, o, shs=None, colors_precomp=None, scales=s, rotations=q)
+    with pytest.raises(Exception, match="excatly one of either SHs or precomputed colors"):
+        r(m, m, o, shs=sh, colors_precomp=c, scales=s, rotations=q)
+    with pytest.raises(Exception, match="exactly one of either scale/rotation pair or precomputed 3D covariance"):
+        r(m, m, o, shs=sh, scales=s, rotations=None)
+    with pytest.raises(Exception, match="exactly one of either scale/rotation pair or precomputed 3D covariance"):
+        r(m, m, o, shs=sh, scales=s, rotations=q, cov3D_precomp=cov)
+
+
+def test_no_cpu_path_fails_loudly():
+    from rain_b200 import GaussianRasterizer, distCUDA2, mark_visible
+    r = GaussianRasterizer(_settings())
+    m = torch.zeros(4, 3)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        r(m, m, torch.ones(4, 1), shs=torch.zeros(4, 16, 3), scales=torch.ones(4, 3), rotations=torch.ones(4, 4))
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        distCUDA2(torch.zeros(5, 3))
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        mark_visible(m, torch.eye(4), torch.eye(4))
+    with pytest.raises(RuntimeError, match=r"\(num_points, 3\)"):                               # rasterize_points.cu:47-49
+        r(torch.zeros(4, 2), m, torch.ones(4, 1), shs=torch.zeros(4, 16, 3), scales=torch.ones(4, 3), rotations=torch.ones(4, 4))
+
+
+def test_missing_library_raises_instead_of_falling_back(monkeypatch):
+    from rain_b200 import _lib
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(_lib, "LIB_PATH", "/nonexistent/librainrast.so")
+    with pytest.raises(RuntimeError, match="no CPU or PyTorch fallback"):
+        _lib.load()
+
+
+def test_autograd_function_slot_order():
+    """backward returns one slot per forward input in input order (reference __init__.py:134-144)."""
+    from rain_b200.rasterizer import _RasterizeGaussians
+    src = inspect.getsource(_RasterizeGaussians.backward)
+    assert "grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities, grad_scales, grad_rotations" in src
+    fsig = list(inspect.signature(_RasterizeGaussians.forward).parameters)
+    assert fsig == ["ctx", "means3D", "means2D", "sh", "colors_precomp", "opacities", "scales", "rotations", "cov3Ds_precomp", "raster_settings"]
+
+
+def test_synthetic_camera_matches_reference_conventions():
+    """scene/cameras.py:43-46: world_view_transform = W2V^T, full_proj = wvt @ P^T, campos = inverse(wvt)[3,:3]."""
+    from rain_b200.synthetic import make_camera, SCENE_RADIUS
+    cam = make_camera(3, 8, 64, 48)
+    W2V = cam.viewmatrix.t()
+    c = torch.cat([cam.campos, torch.ones(1)])
+    assert torch.allclose(W2V @ c, torch.tensor([0.0, 0.0, 0.0, 1.0]), atol=1e-5)               # camera centre maps to the view origin
+    origin_view = W2V @ torch.tensor([0.0, 0.0, 0.0, 1.0])
+    assert abs(origin_view[2].item() - 3.0 * SCENE_RADIUS) < 1e-4 and origin_view[:2].abs().max() < 1e-4   # looks at the origin, +z forward
+    assert abs(cam.tanfovx / cam.tanfovy - 64 / 48) < 1e-6
+    hom = torch.tensor([0.3, -0.2, 0.1, 1.0]) @ cam.projmatrix
+    assert hom[3] > 0

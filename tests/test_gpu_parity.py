@@ -1,0 +1,326 @@
+"""GPU parity tests (run with -m gpu on a B200).  Everything goes through the C ABI of librainrast.so (ctypes), and is
+compared with
+  * the UNMODIFIED reference CUDA rebuilt for sm_100a (oracle/_ref/libref_rast.so, fixture `refcuda`) on the same
+    seeded inputs — bit-exact for integers/indices (num_rendered, radii, tiles_touched, sorted keys, point_list, ranges,
+    n_contrib), 1e-5 relative for colour/depth (in practice bit-identical), 1e-4 relative for gradients (the
+    reference's own backward is order-nondeterministic because of its float atomics);
+  * the CPU oracle (oracle/liboracle.so) at sizes it finishes in seconds;
+  * the golden vectors committed under tests/golden/ (reference CUDA outputs);
+  * size-independent properties at BASELINE.json's full sizes (linearity, determinism, sortedness, range partition).
+"""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from harness import mine_backward, mine_forward, rel_err
+from rain_b200 import _C, _lib
+from rain_b200.synthetic import CONFIGS, make_camera, make_grad, make_scene
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+GRAD_KEYS = ["dL_dmean2D", "dL_dopacity", "dL_dcolor", "dL_dmean3D", "dL_dcov3D", "dL_dsh", "dL_dscale", "dL_drot"]
+RTOL_COLOR = 1e-5     # north_star: rendered colour and depth within 1e-5 relative
+RTOL_GRAD = 1e-4      # north_star: input gradients within 1e-4 relative
+
+
+def eq(a, b):
+    return bool(torch.equal(torch.as_tensor(a).cpu(), torch.as_tensor(b).cpu()))
+
+
+def ref_forward(ref, sc, cam, bg, **kw):
+    return ref.forward(bg, sc.means3D, sc.opacities, sc.scales, sc.rotations, cam.viewmatrix, cam.projmatrix, cam.campos, cam.tanfovx, cam.tanfovy,
+                       cam.height, cam.width, shs=sc.shs, sh_degree=sc.sh_degree, **kw)
+
+
+def check_against_ref(fw, g, ref, N_r, color_r, radii_r, depth_r, g_r):
+    st = ref.state()
+    assert fw["N"] == N_r
+    assert eq(fw["radii"], radii_r)
+    assert eq(fw["tiles_touched"], st["tiles_touched"])
+    if N_r:
+        assert eq(fw["keys"], st["keys"])
+        assert eq(fw["point_list"], st["point_list"])
+    assert eq(fw["ranges"], st["ranges"])
+    assert eq(fw["n_contrib"], st["n_contrib"])
+    assert rel_err(fw["final_T"], st["final_T"])[0] <= RTOL_COLOR
+    assert rel_err(fw["color"], color_r)[0] <= RTOL_COLOR
+    assert rel_err(fw["depth"], depth_r)[0] <= RTOL_COLOR
+    if g is not None:
+        for k in GRAD_KEYS:
+            assert rel_err(g[k], g_r[k])[0] <= RTOL_GRAD, k
+        a = g["dL_dconic"].reshape(-1, 4)[:, [0, 1, 3]]; b = g_r["dL_dconic"].reshape(-1, 4)[:, [0, 1, 3]]
+        assert rel_err(a, b)[0] <= RTOL_GRAD
+
+
+@pytest.mark.parametrize("name", ["C1", "C2", "C3"])
+@pytest.mark.parametrize("variant", ["1", "0"])
+def test_configs_match_reference_cuda(device, refcuda, monkeypatch, name, variant):
+    """BASELINE.json configs 1-3 at full size against the reference CUDA on the same GPU."""
+    monkeypatch.setenv("RAIN_RAST_VARIANT", variant)
+    cfg = CONFIGS[name]
+    sc = make_scene(cfg["P"], cfg["D"]).to(device); cam = make_camera(0, 1, cfg["W"], cfg["H"]).to(device)
+    bg = torch.zeros(3, device=device); dpix = make_grad(cfg["W"], cfg["H"]).to(device)
+    fw = mine_forward(sc, cam, bg)
+    g = mine_backward(fw, sc, cam, bg, dpix)
+    N_r, color_r, radii_r, depth_r = ref_forward(refcuda, sc, cam, bg)
+    g_r = refcuda.backward(dpix)
+    assert N_r > cfg["P"]
+    check_against_ref(fw, g, refcuda, N_r, color_r, radii_r, depth_r, g_r)
+
+
+@pytest.mark.parametrize("P,W,H,D,seed,view,bgc,low_pass,smod,smult", [
+    (5000, 100, 70, 3, 1, 1, (0.3, 0.6, 0.9), 0.3, 1.0, 1.0),        # image not a multiple of 16, non-zero background
+    (3000, 64, 64, 2, 2, 2, (0.0, 0.0, 0.0), 30.0, 1.0, 1.0),         # large coarse-to-fine low_pass: huge rects, long tile lists
+    (2000, 160, 96, 1, 3, 3, (1.0, 1.0, 1.0), 0.3, 2.5, 3.0),         # scale_modifier, fat opaque splats: early termination
+    (50000, 48, 32, 0, 4, 0, (0.0, 0.0, 0.0), 0.3, 1.0, 4.0),         # > 128 entries in every tile: multi-batch staging, saturation
+    (1, 32, 32, 3, 5, 0, (0.5, 0.5, 0.5), 0.3, 1.0, 1.0),             # single Gaussian
+    (257, 17, 15, 3, 6, 1, (0.2, 0.2, 0.2), 0.3, 1.0, 2.0),           # image smaller than one tile row/column multiple
+])
+def test_shapes_and_settings_match_reference_cuda(device, refcuda, P, W, H, D, seed, view, bgc, low_pass, smod, smult):
+    sc = make_scene(P, D, seed, smult).to(device); cam = make_camera(view, 4, W, H).to(device)
+    if P == 1:
+        sc.means3D.zero_()
+    bg = torch.tensor(bgc, device=device); dpix = make_grad(W, H, seed).to(device)
+    fw = mine_forward(sc, cam, bg, low_pass=low_pass, scale_modifier=smod)
+    g = mine_backward(fw, sc, cam, bg, dpix)
+    N_r, color_r, radii_r, depth_r = ref_forward(refcuda, sc, cam, bg, low_pass=low_pass, scale_modifier=smod)
+    g_r = refcuda.backward(dpix)
+    check_against_ref(fw, g, refcuda, N_r, color_r, radii_r, depth_r, g_r)
+
+
+def test_precomputed_colour_and_covariance_modes(device, refcuda):
+    P, W, H = 4000, 96, 80
+    sc = make_scene(P, 0, 9, 1.5).to(device); cam = make_camera(1, 3, W, H).to(device)
+    gen = torch.Generator().manual_seed(1)
+    colors = torch.rand(P, 3, generator=gen).to(device)
+    A = torch.randn(P, 3, 3, generator=gen) * 0.05
+    S = A @ A.transpose(1, 2) + 0.0005 * torch.eye(3)
+    cov = torch.stack([S[:, 0, 0], S[:, 0, 1], S[:, 0, 2], S[:, 1, 1], S[:, 1, 2], S[:, 2, 2]], 1).contiguous().to(device)
+    bg = torch.tensor([0.1, 0.0, 0.2], device=device); dpix = make_grad(W, H, 2).to(device)
+    for cp, cv in ((colors, None), (None, cov), (colors, cov)):
+        fw = mine_forward(sc, cam, bg, colors_precomp=cp, cov3D_precomp=cv)
+        g = mine_backward(fw, sc, cam, bg, dpix)
+        N_r, color_r, radii_r, depth_r = refcuda.forward(bg, sc.means3D, sc.opacities, None if cv is not None else sc.scales,
+                                                         None if cv is not None else sc.rotations, cam.viewmatrix, cam.projmatrix, cam.campos,
+                                                         cam.tanfovx, cam.tanfovy, H, W, shs=None if cp is not None else sc.shs, sh_degree=0,
+                                                         colors_precomp=cp, cov3D_precomp=cv)
+        g_r = refcuda.backward(dpix)
+        if cp is not None:
+            g_r["dL_dsh"] = g["dL_dsh"]          # M = 0: nothing to compare
+        if cv is not None:
+            g_r["dL_dscale"], g_r["dL_drot"] = g["dL_dscale"], g["dL_drot"]   # the reference leaves them untouched (zeros)
+            assert not g["dL_dscale"].any() and not g["dL_drot"].any()
+        check_against_ref(fw, g, refcuda, N_r, color_r, radii_r, depth_r, g_r)
+
+
+def test_config1_matches_cpu_oracle(device, oracle):
+    """BASELINE.json config 1 (10k Gaussians, 256x256, SH degree 0) against the host restatement."""
+    cfg = CONFIGS["C1"]
+    sc_h = make_scene(cfg["P"], cfg["D"]); cam_h = make_camera(0, 1, cfg["W"], cfg["H"])
+    sc, cam = sc_h.to(device), cam_h.to(device)
+    bg = torch.zeros(3, device=device); dpix = make_grad(cfg["W"], cfg["H"])
+    fw = mine_forward(sc, cam, bg)
+    g = mine_backward(fw, sc, cam, bg, dpix.to(device))
+    N_o, color_o, radii_o, depth_o = oracle.forward(np.zeros(3, np.float32), sc_h.means3D.numpy(), sc_h.opacities.numpy(), sc_h.scales.numpy(),
+                                                    sc_h.rotations.numpy(), cam_h.viewmatrix.numpy(), cam_h.projmatrix.numpy(), cam_h.campos.numpy(),
+                                                    cam_h.tanfovx, cam_h.tanfovy, cam_h.height, cam_h.width, shs=sc_h.shs.numpy(), sh_degree=cfg["D"])
+    g_o = oracle.backward(dpix.numpy())
+    assert fw["N"] == N_o
+    assert np.array_equal(fw["radii"].cpu().numpy(), radii_o)
+    assert np.array_equal(fw["keys"].cpu().numpy().astype(np.uint64), oracle.get("keys"))
+    assert np.array_equal(fw["point_list"].cpu().numpy().astype(np.uint32), oracle.get("point_list"))
+    assert np.array_equal(fw["ranges"].cpu().numpy().astype(np.uint32).ravel(), oracle.get("ranges"))
+    assert np.array_equal(fw["n_contrib"].cpu().numpy().astype(np.uint32), oracle.get("n_contrib"))
+    assert rel_err(fw["color"], color_o)[0] <= RTOL_COLOR and rel_err(fw["depth"], depth_o)[0] <= RTOL_COLOR
+    for k in GRAD_KEYS:
+        assert rel_err(g[k], g_o[k].reshape(g[k].shape))[0] <= RTOL_GRAD, k
+
+
+GOLDEN_FILES = sorted(glob.glob(os.path.join(GOLDEN, "fwd_bwd_*.npz")))
+
+
+@pytest.mark.parametrize("path", GOLDEN_FILES or [None])
+def test_golden_vectors(device, path):
+    if path is None:
+        pytest.skip("no golden vectors committed yet")
+    z = np.load(path)
+    t = lambda k: torch.from_numpy(z[k]).to(device)
+    has = lambda k: z[k].size > 0
+    e = torch.empty(0, device=device)
+    args = (t("bg"), t("means3D"), t("colors_precomp") if has("colors_precomp") else e, t("opacities"), t("scales") if has("scales") else e,
+            t("rotations") if has("rotations") else e, float(z["scale_modifier"]), t("cov3D_precomp") if has("cov3D_precomp") else e, t("viewmatrix"),
+            t("projmatrix"), float(z["tanfovx"]), float(z["tanfovy"]), int(z["H"]), int(z["W"]), t("shs") if has("shs") else e, int(z["D"]), t("campos"),
+            False, False, float(z["low_pass"]))
+    N, color, radii, depth, geom, binning, img = _C.rasterize_gaussians(*args)
+    assert N == int(z["num_rendered"])
+    assert np.array_equal(radii.cpu().numpy(), z["radii"])
+    assert rel_err(color, z["color"])[0] <= RTOL_COLOR and rel_err(depth, z["depth"])[0] <= RTOL_COLOR
+    grads = _C.rasterize_gaussians_backward(args[0], args[1], radii, args[2], args[4], args[5], args[6], args[7], args[8], args[9], args[10], args[11],
+                                            t("dL_dpix"), args[14], args[15], args[16], geom, N, binning, img, False, args[19])
+    for k, gr in zip(["dL_dmean2D", "dL_dcolor", "dL_dopacity", "dL_dmean3D", "dL_dcov3D", "dL_dsh", "dL_dscale", "dL_drot"], grads):
+        if z[k].size and gr.numel():
+            assert rel_err(gr, z[k].reshape(gr.shape))[0] <= RTOL_GRAD, k
+
+
+def test_empty_and_fully_culled_inputs(device):
+    cam = make_camera(0, 1, 64, 48).to(device)
+    bg = torch.tensor([0.25, 0.5, 0.75], device=device)
+    e = torch.empty(0, device=device)
+    z3 = torch.zeros(0, 3, device=device)
+    N, color, radii, depth, *_ = _C.rasterize_gaussians(bg, z3, e, torch.zeros(0, 1, device=device), z3, torch.zeros(0, 4, device=device), 1.0, e, cam.viewmatrix,
+                                                        cam.projmatrix, cam.tanfovx, cam.tanfovy, 48, 64, torch.zeros(0, 16, 3, device=device), 3, cam.campos, False, False, 0.3)
+    assert N == 0 and radii.numel() == 0 and color.shape == (3, 48, 64) and not color.any()        # rasterize_points.cu:58-72: zeros, not bg
+    sc = make_scene(100, 3, 0).to(device)
+    sc.means3D[:] = cam.campos * 2.0                                                                # everything behind the camera
+    fw = mine_forward(sc, cam, bg)
+    assert fw["N"] == 0 and not fw["radii"].any() and not fw["depth"].any()
+    assert torch.allclose(fw["color"], bg[:, None, None].expand(3, 48, 64))
+    g = mine_backward(fw, sc, cam, bg, make_grad(64, 48).to(device))
+    assert all(not v.any() for v in g.values())
+    assert not _C.mark_visible(sc.means3D, cam.viewmatrix, cam.projmatrix).any()
+
+
+def test_mark_visible_matches_oracle(device, oracle):
+    sc_h = make_scene(20000, 0, 3, 1.0); cam_h = make_camera(2, 5, 64, 64, radius=1.0)               # camera inside the cloud
+    got = _C.mark_visible(sc_h.means3D.to(device), cam_h.viewmatrix.to(device), cam_h.projmatrix.to(device)).cpu().numpy()
+    exp = oracle.mark_visible(sc_h.means3D.numpy(), cam_h.viewmatrix.numpy(), cam_h.projmatrix.numpy())
+    assert 0 < exp.sum() < exp.size and np.array_equal(got, exp)
+
+
+def test_autograd_api_equals_direct_backward_and_is_deterministic(device):
+    from rain_b200 import GaussianRasterizationSettings, GaussianRasterizer
+    P, W, H, D = 20000, 200, 120, 3
+    sc = make_scene(P, D, 5).to(device); cam = make_camera(0, 2, W, H).to(device)
+    bg = torch.tensor([0.1, 0.2, 0.3], device=device); dpix = make_grad(W, H, 5).to(device)
+    rs = GaussianRasterizationSettings(H, W, cam.tanfovx, cam.tanfovy, bg, 1.0, cam.viewmatrix, cam.projmatrix, D, cam.campos, False, True, 0.3)
+    outs = []
+    for _ in range(2):
+        leaves = [t.clone().requires_grad_(True) for t in (sc.means3D, sc.opacities, sc.shs, sc.scales, sc.rotations)]
+        m2d = torch.zeros_like(sc.means3D, requires_grad=True)
+        color, radii, depth = GaussianRasterizer(rs)(means3D=leaves[0], means2D=m2d, opacities=leaves[1], shs=leaves[2], scales=leaves[3], rotations=leaves[4])
+        assert not radii.requires_grad and color.requires_grad
+        (color * dpix).sum().backward()
+        outs.append([color.detach(), radii, depth.detach(), m2d.grad] + [t.grad for t in leaves])
+    for a, b in zip(*outs):
+        assert eq(a, b)                                                    # no atomics anywhere: bit-reproducible
+    fw = mine_forward(sc, cam, bg)
+    g = mine_backward(fw, sc, cam, bg, dpix)
+    for a, k in zip(outs[0][3:], ["dL_dmean2D", "dL_dmean3D", "dL_dopacity", "dL_dsh", "dL_dscale", "dL_drot"]):
+        assert eq(a, g[k]), k
+
+
+def test_full_size_properties_config3(device):
+    """Size-independent properties at BASELINE.json's headline size (1M Gaussians, 1920x1080, SH degree 3)."""
+    cfg = CONFIGS["C3"]
+    sc = make_scene(cfg["P"], cfg["D"]).to(device); cam = make_camera(0, 1, cfg["W"], cfg["H"]).to(device)
+    bg = torch.tensor([0.3, 0.3, 0.3], device=device)
+    fw = mine_forward(sc, cam, bg)
+    N, keys, pl, ranges = fw["N"], fw["keys"], fw["point_list"].long(), fw["ranges"].long()
+    assert N == int(fw["tiles_touched"].long().sum()) and ((fw["radii"] > 0) == (fw["tiles_touched"] > 0)).all()
+    d = keys[1:] - keys[:-1]
+    assert (d >= 0).all()                                                  # sorted by (tile, depth)
+    assert (pl[1:][d == 0] > pl[:-1][d == 0]).all()                        # stable: ties keep ascending Gaussian index
+    assert eq(keys & 0xFFFFFFFF, fw["depths"].contiguous().view(torch.int32)[pl].long() & 0xFFFFFFFF)
+    cnt = torch.bincount(keys >> 32, minlength=ranges.shape[0])
+    assert eq(ranges[:, 1] - ranges[:, 0], cnt)
+    nz = cnt > 0
+    assert eq(ranges[nz, 0], (torch.cumsum(cnt, 0) - cnt)[nz]) and not ranges[~nz].any()
+    assert eq(torch.bincount(pl, minlength=cfg["P"]), fw["tiles_touched"].long())
+    assert (fw["final_T"] >= 0).all() and (fw["final_T"] <= 1).all() and torch.isfinite(fw["color"]).all()
+    # linearity of the backward in the upstream gradient
+    d1, d2 = make_grad(cfg["W"], cfg["H"], 1).to(device), make_grad(cfg["W"], cfg["H"], 2).to(device)
+    g1, g2, g12 = mine_backward(fw, sc, cam, bg, d1), mine_backward(fw, sc, cam, bg, d2), mine_backward(fw, sc, cam, bg, 2.0 * d1 - 0.5 * d2)
+    for k in GRAD_KEYS:
+        assert rel_err(g12[k], 2.0 * g1[k] - 0.5 * g2[k])[0] < 1e-4, k
+    # a zero upstream gradient gives exactly zero everywhere (every output element is written)
+    g0 = mine_backward(fw, sc, cam, bg, torch.zeros_like(d1))
+    assert all(not v.any() for v in g0.values())
+
+
+def test_accumulate_mode_and_multiview_bucket(device):
+    from rain_b200 import multiview as mv
+    P, W, H, D, V = 30000, 160, 96, 3, 3
+    sc = make_scene(P, D, 8).to(device)
+    cams = [make_camera(v, V, W, H).to(device) for v in range(V)]
+    bg = torch.zeros(3, device=device)
+    dp = [make_grad(W, H, 20 + v).to(device) for v in range(V)]
+    params = dict(means3D=sc.means3D, opacities=sc.opacities, shs=sc.shs, scales=sc.scales, rotations=sc.rotations)
+    bucket = mv.GradientBucket(P, 16, device)
+    bucket.flat.fill_(float("nan"))                                        # the first view must overwrite everything
+    res = mv.train_step_views(params, cams, V, bucket, lambda v, c, d: dp[v], bg=bg, sh_degree=D)
+    tot = None
+    for v in range(V):
+        fw = mine_forward(sc, cams[v], bg)
+        g = mine_backward(fw, sc, cams[v], bg, dp[v])
+        assert eq(res[v].color, fw["color"]) and eq(res[v].dL_dmeans2D, g["dL_dmean2D"])
+        cur = dict(means3D=g["dL_dmean3D"], sh=g["dL_dsh"], opacity=g["dL_dopacity"], scales=g["dL_dscale"], rotations=g["dL_drot"])
+        tot = cur if tot is None else {k: tot[k] + cur[k] for k in cur}
+    for k in mv.SEGMENTS:
+        assert torch.isfinite(bucket.views[k]).all()
+        assert rel_err(bucket.views[k], tot[k])[0] < 1e-6, k
+
+
+def _sort_case(device, n, key_bytes, b0, b1, seed, skew):
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(seed)
+    if key_bytes == 4:
+        keys = torch.randint(0, 2 ** 31 - 1, (n,), generator=g, dtype=torch.int64)
+        keys = keys % 7 if skew else keys
+        kd = keys.to(torch.int32).to(device)
+    else:
+        hi = torch.randint(0, 8160, (n,), generator=g, dtype=torch.int64)
+        lo = torch.randint(0, 2 ** 31 - 1, (n,), generator=g, dtype=torch.int64)
+        keys = (hi << 32) | (lo % 3 if skew else lo)
+        kd = keys.to(device)
+    mask = ((1 << b1) - 1) ^ ((1 << b0) - 1)
+    perm = torch.sort(keys & mask, stable=True).indices
+    ws = torch.empty(lib.rr_sort_ws_bytes(n, key_bytes, b0, b1), dtype=torch.uint8, device=device)
+    kout = torch.empty_like(kd); vin = torch.arange(n, dtype=torch.int32, device=device); vout = torch.empty_like(vin)
+    fn = lib.rr_sort_pairs_u32 if key_bytes == 4 else lib.rr_sort_pairs_u64
+    _lib.check(fn(torch.cuda.current_stream().cuda_stream, n, kd.data_ptr(), kout.data_ptr(), vin.data_ptr(), vout.data_ptr(), b0, b1, ws.data_ptr()), "sort")
+    torch.cuda.synchronize()
+    assert eq(vout.long(), perm) and eq(kout.long(), keys[perm])
+
+
+@pytest.mark.parametrize("n,key_bytes,b0,b1,skew", [
+    (1, 4, 0, 32, False), (2, 8, 0, 45, False), (1000, 4, 0, 32, False), (4096, 4, 0, 13, False), (4097, 4, 0, 13, True), (100_003, 4, 0, 32, False),
+    (3073, 8, 0, 45, False), (3071, 8, 0, 41, True), (1_000_000, 4, 0, 30, False), (8_400_000, 4, 0, 13, False), (2_000_000, 8, 0, 45, False),
+    (2_000_000, 8, 0, 45, True), (50_000, 4, 8, 24, False)])
+def test_onesweep_sort_is_a_stable_sort(device, n, key_bytes, b0, b1, skew):
+    """the hand-written onesweep (the replacement for cub::DeviceRadixSort::SortPairs, rasterizer_impl.cu:295-300 and
+    simple_knn.cu:199-202) against torch's stable sort — bit-exact keys and permutation"""
+    _sort_case(device, n, key_bytes, b0, b1, 1234 + n, skew)
+
+
+@pytest.mark.parametrize("P", [4, 7, 1000, 100_000])
+def test_dist2_exact_against_oracle_and_reference(device, oracle, refcuda, P):
+    g = torch.Generator().manual_seed(P)
+    pts = (torch.rand(P, 3, generator=g) * 2 - 1).float()
+    if P >= 1000:
+        pts[10] = pts[11]; pts[12] = pts[11]                               # coincident points count with distance 0
+        pts[: P // 4] = torch.randn(P // 4, 3, generator=g) * 0.01 + 0.3   # a dense cluster
+    got = _C.distCUDA2(pts.to(device)).cpu()
+    assert np.array_equal(got.numpy(), oracle.dist2(pts.numpy(), brute=P <= 1000))
+    assert eq(got, refcuda.dist2(pts.to(device)))
+
+
+def test_dist2_five_million_points_sampled_queries(device, oracle):
+    """BASELINE.json config 5: 5M uniform points; exactness checked on 10 000 sampled queries."""
+    P = CONFIGS["C5"]["P"]
+    pts = (torch.rand(P, 3, generator=torch.Generator().manual_seed(0)) * 2 - 1).float()
+    got = _C.distCUDA2(pts.to(device)).cpu().numpy()
+    idx = np.random.default_rng(0).choice(P, 10_000, replace=False).astype(np.int32)
+    assert np.array_equal(got[idx], oracle.dist2_queries(pts.numpy(), idx))
+    assert np.isfinite(got).all() and (got > 0).all()
+
+
+def test_golden_knn_vectors(device):
+    files = sorted(glob.glob(os.path.join(GOLDEN, "knn_*.npz")))
+    if not files:
+        pytest.skip("no golden vectors committed yet")
+    for f in files:
+        z = np.load(f)
+        assert np.array_equal(_C.distCUDA2(torch.from_numpy(z["points"]).to(device)).cpu().numpy(), z["dist2"]), f
