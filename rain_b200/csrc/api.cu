@@ -115,7 +115,7 @@ GeomLayout geom_layout(void* blob, int P)
 }
 
 struct BinLayout {
-	uint32_t *key_a, *key_b, *emit_a, *emit_b, *owner, *point_list; SplatRec* packed; void* sort_ws;
+	uint32_t *key_a, *key_b, *emit_a, *emit_b, *owner, *point_list; SplatRec* packed; uint8_t* flags; void* sort_ws;
 	uint32_t *keys_sorted, *emit_sorted;
 	int bits; size_t total; int64_t off[5];
 };
@@ -130,6 +130,7 @@ BinLayout bin_layout(void* blob, int64_t N, int W, int H)
 	L.owner = c.take<uint32_t>(Nz);
 	L.point_list = c.take<uint32_t>(Nz);
 	L.packed = c.take<SplatRec>(Nz);
+	L.flags = c.take<uint8_t>(Nz + 16);
 	L.sort_ws = c.take<char>(sort_ws_bytes<uint32_t>(Nz, 0, L.bits));
 	L.total = c.used();
 	const bool in_b = (((L.bits + 7) / 8) & 1) != 0;
@@ -234,7 +235,7 @@ int rr_forward_geom(void* stream_, int P, int D, int M, int W, int H,
 	{ Stage st(stream, ST_DEPTH_SORT); which = sort_pairs<uint32_t>(stream, L.key_a, L.key_b, L.val_a, L.val_b, (size_t)P, 0, 32, L.sort_ws, true); }
 	if (which != 0) { if (which > 0) set_error("internal: depth sort landed in the wrong buffer"); return -1; }
 	if (debug && check_launch("depth sort", stream, true)) return -1;
-	{ Stage st(stream, ST_SCAN); if (launch_scan_tiles(stream, P, L.val_a, L.tiles_touched, L.offsets, L.block_sums, L.num_rendered)) return -1; }
+	{ Stage st(stream, ST_SCAN); if (launch_scan_tiles(stream, P, L.val_a, L.tiles_touched, L.offsets, L.dup_off, L.block_sums, L.num_rendered)) return -1; }
 	// num_rendered: u32 on the device, widened on the host side of the copy (the upper half was zeroed above)
 	cudaMemcpyAsync(num_rendered_host, L.num_rendered, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream);
 	return check_launch("forward_geom", stream, debug != 0);
@@ -256,10 +257,10 @@ int rr_forward_raster(void* stream_, int P, int W, int H, int64_t N, const float
 	const int grid_x = (W + TILE_X - 1) / TILE_X, grid_y = (H + TILE_Y - 1) / TILE_Y;
 
 	if (N > 0) {
-		{ Stage st(stream, ST_DUPLICATE); if (launch_duplicate(stream, P, G.val_a, G.offsets, G.rect, grid_x, B.key_a, B.owner, G.dup_off)) return -1; }
+		{ Stage st(stream, ST_DUPLICATE); if (launch_duplicate(stream, P, G.val_a, G.offsets, G.rect, grid_x, B.key_a, B.emit_a, B.owner, G.dup_off)) return -1; }
 		if (debug && check_launch("duplicate", stream, true)) return -1;
 		int which;
-		{ Stage st(stream, ST_TILE_SORT); which = sort_pairs<uint32_t>(stream, B.key_a, B.key_b, B.emit_a, B.emit_b, (size_t)N, 0, B.bits, B.sort_ws, true); }
+		{ Stage st(stream, ST_TILE_SORT); which = sort_pairs<uint32_t>(stream, B.key_a, B.key_b, B.emit_a, B.emit_b, (size_t)N, 0, B.bits, B.sort_ws, false); }
 		if (which < 0) return -1;
 		if ((which ? B.key_b : B.key_a) != B.keys_sorted) { set_error("internal: tile sort landed in the wrong buffer"); return -1; }
 		if (debug && check_launch("tile sort", stream, true)) return -1;
@@ -273,7 +274,7 @@ int rr_forward_raster(void* stream_, int P, int W, int H, int64_t N, const float
 
 	RenderArgs r; memset(&r, 0, sizeof(r));
 	r.W = W; r.H = H; r.grid_x = grid_x; r.grid_y = grid_y;
-	r.ranges = I.ranges; r.packed = B.packed; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.tile_max_contrib = I.tile_max;
+	r.ranges = I.ranges; r.packed = B.packed; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.tile_max_contrib = I.tile_max; r.pair_flags = B.flags;
 	r.out_color = out_color; r.out_depth = out_depth; r.variant = variant;
 	{ Stage st(stream, ST_RENDER_FWD); if (launch_render_fwd(stream, r)) return -1; }
 	return check_launch("forward_raster", stream, debug != 0);
@@ -307,7 +308,7 @@ int rr_backward(void* stream_, int P, int D, int M, int W, int H, int64_t N, con
 
 	RenderArgs r; memset(&r, 0, sizeof(r));
 	r.W = W; r.H = H; r.grid_x = grid_x; r.grid_y = grid_y;
-	r.ranges = I.ranges; r.packed = B.packed; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.tile_max_contrib = I.tile_max;
+	r.ranges = I.ranges; r.packed = B.packed; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.tile_max_contrib = I.tile_max; r.pair_flags = B.flags;
 	r.dL_dpix = dL_dpix; r.sorted_emit = B.emit_sorted; r.partial = partial; r.variant = variant;
 	if (N > 0) {
 		{ Stage st(stream, ST_RENDER_BWD); if (launch_render_bwd(stream, r)) return -1; }

@@ -13,7 +13,8 @@ constexpr unsigned FULL = 0xffffffffu;
 // One projected Gaussian as the render kernels consume it: 48 bytes, 16-byte aligned so a tile's list is a
 // contiguous span a 1-D bulk copy (cp.async.bulk) can stage into shared memory.
 //   a = { pix.x, pix.y, conic.x, conic.y }   b = { conic.z, opacity, r, g }   c = { b, depth, ext.x, ext.y }
-// ext = conservative half-extent (in pixels) of the region where alpha can reach 1/255 (used only for culling).
+// ext = conservative half-extent (in pixels) of the region where alpha can reach 1/255 (used only for culling;
+// +inf = never cull, -inf = can never contribute).
 struct __align__(16) SplatRec {
 	float4 a, b, c;
 };

@@ -21,10 +21,10 @@ int launch_mark_visible(cudaStream_t, int P, const float* means3D, const float* 
 
 // binning.cu
 size_t scan_ws_elems(int P);
-int launch_scan_tiles(cudaStream_t, int P, const uint32_t* order, const uint32_t* tiles_touched, uint32_t* offsets /*inclusive, sorted order*/,
-	uint32_t* block_sums, uint32_t* num_rendered_dev);
+int launch_scan_tiles(cudaStream_t, int P, const uint32_t* order, const uint32_t* tiles_touched, uint32_t* offsets /*inclusive, depth order*/,
+	uint32_t* slot_off /*exclusive, index order*/, uint32_t* block_sums, uint32_t* num_rendered_dev);
 int launch_duplicate(cudaStream_t, int P, const uint32_t* order, const uint32_t* offsets, const uint2* rect, int grid_x,
-	uint32_t* tile_keys /*[N]*/, uint32_t* owner /*[N]*/, uint32_t* dup_off /*[P]*/);
+	uint32_t* tile_keys /*[N] emission order*/, uint32_t* slots /*[N] emission order*/, uint32_t* owner /*[N] by slot*/, const uint32_t* slot_off /*[P]*/);
 int launch_tile_ranges(cudaStream_t, size_t N, const uint32_t* sorted_tile_keys, uint2* ranges, int num_tiles);
 int launch_pack(cudaStream_t, size_t N, const uint32_t* sorted_emit, const uint32_t* owner, const SplatRec* rec,
 	SplatRec* packed, uint32_t* point_list);
@@ -39,6 +39,7 @@ struct RenderArgs {
 	float* final_T;             // [H*W]
 	uint32_t* n_contrib;        // [H*W]
 	uint32_t* tile_max_contrib; // [tiles] max n_contrib over the tile's pixels (written by forward, read by backward)
+	uint8_t* pair_flags;        // [N] sorted order: bit w set if warp w's 8x4 pixel block of the tile blended this pair (fwd writes, bwd reads)
 	float* out_color;           // [3,H,W]
 	float* out_depth;           // [H,W]
 	// backward only

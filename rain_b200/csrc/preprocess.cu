@@ -233,16 +233,36 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreprocessArgs a)
 	}
 	a.clamped[idx] = clamped;
 
-	// cull threshold for the render kernels: a pair can only reach alpha >= 1/255 if power >= thr (conservative
-	// margin; -inf disables culling for a conic that is not positive definite or an opacity outside (0, inf))
+	// Conservative half-extents (pixels) of the region where this splat can reach alpha >= 1/255, for the render
+	// kernels' per-warp culling: alpha = min(0.99, o * exp(power)) >= 1/255 needs power >= -t with t = ln(255 o), and
+	// {d : 0.5 d^T Q d <= t} (Q = the stored conic) has x-extent sqrt(2 t Q^-1_xx) = sqrt(2 t C / (AC - B^2)).
+	// Evaluated in double from the STORED conic; t is inflated for the fp32 rounding of `power` in the blend, which is
+	// relative to the magnitude of its terms, i.e. grows with the conditioning of Q.  +inf = never cull, -inf = the
+	// splat can never pass the alpha test (o < 1/255).
 	const float opacity = a.opacities[idx];
-	float thr = -__logf(255.0f * opacity) - 1e-3f;
-	if (!(conx > 0.0f && conz > 0.0f && conx * conz - cony * cony > 0.0f) || !(opacity > 0.0f) || !(thr == thr)) thr = -INFINITY;
+	float ext_x = INFINITY, ext_y = INFINITY;
+	{
+		const double A = conx, B = cony, C = conz;
+		const double dd = A * C - B * B;
+		const float t = __logf(255.0f * opacity) + 1e-3f;
+		if (opacity == opacity && t == t && A > 0.0 && C > 0.0 && dd > 0.0) {
+			if (!(t > 0.0f)) { ext_x = -INFINITY; ext_y = -INFINITY; }
+			else {
+				const double cond = (A + C) * (A + C) / dd;
+				const double shrink = 1.0 - 4e-6 * cond;
+				if (shrink > 0.5) {
+					const double t2 = 2.0 * ((double)t + 1e-3) / shrink;
+					ext_x = (float)(sqrt(t2 * C / dd) * 1.00001 + 1e-3);
+					ext_y = (float)(sqrt(t2 * A / dd) * 1.00001 + 1e-3);
+				}
+			}
+		}
+	}
 
 	SplatRec rec;
 	rec.a = make_float4(pix_x, pix_y, conx, cony);
 	rec.b = make_float4(conz, opacity, rgb0, rgb1);
-	rec.c = make_float4(rgb2, view_z, thr, 0.0f);
+	rec.c = make_float4(rgb2, view_z, ext_x, ext_y);
 	a.rec[idx] = rec;
 }
 

@@ -19,12 +19,32 @@ __constant__ float b_SH_C3[7] = { -0.5900435899266435f, 2.890611442640554f, -0.4
 constexpr float kC0 = 0.28209479177387814f;
 constexpr float kC1 = 0.4886025119029199f;
 
-__global__ void __launch_bounds__(128) preprocess_bwd_kernel(PreprocessBwdArgs a)
+constexpr int PB_THREADS = 128;
+constexpr int PB_WARPS = PB_THREADS / 32;
+constexpr int SH_FLOATS = 48;            // 16 coefficients x 3 channels (the staged fast path needs M == 16)
+constexpr int SH_STRIDE = SH_FLOATS + 1; // +1 float: a lane walking its own row is bank-conflict free
+constexpr int PCHUNK = 128;              // (tile, Gaussian) partials staged per warp and round: 128 * 40 B = 5 KB
+
+// One warp handles 32 consecutive Gaussians.  Everything that is wide per Gaussian moves through a per-warp shared
+// buffer with fully coalesced global accesses:
+//   * the gradient partials of the warp's Gaussians are ONE contiguous span (slots are assigned in index order), read
+//     in chunks of PCHUNK entries, each lane then sums its own entries in slot order (deterministic);
+//   * the 32 SH rows (6 KB contiguous) are read as float4, each lane works on its row in shared memory, and the 32
+//     dL_dsh rows go back as float4 (STAGED; the plain per-thread path remains for M != 16 or unaligned pointers).
+template <bool STAGED>
+__global__ void __launch_bounds__(PB_THREADS) preprocess_bwd_kernel(PreprocessBwdArgs a)
 {
-	const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-	if (idx >= a.P) return;
-	const size_t i3 = 3 * (size_t)idx;
-	const bool visible = a.radii[idx] > 0;
+	__shared__ __align__(16) float s_buf[PB_WARPS][32 * SH_STRIDE];
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const int warp_base = blockIdx.x * PB_THREADS + warp * 32;
+	if (warp_base >= a.P) return;                               // warp-uniform
+	float* __restrict__ sb = s_buf[warp];
+	const int idx = warp_base + lane;
+	const bool valid = idx < a.P;
+	const int nvalid = min(32, a.P - warp_base);
+	const size_t i3 = 3 * (size_t)(valid ? idx : 0);
+	const bool visible = valid && a.radii[idx] > 0;
+	const unsigned vismask = __ballot_sync(FULL, visible);
 	// accumulate mode (multi-view batches, see rr_backward flags): parameter gradients are added to what the buffers
 	// hold and a Gaussian this view does not see is not touched at all; otherwise every element is overwritten.
 	const bool acc = a.accumulate != 0;
@@ -34,19 +54,55 @@ __global__ void __launch_bounds__(128) preprocess_bwd_kernel(PreprocessBwdArgs a
 	float g[9];
 	#pragma unroll
 	for (int k = 0; k < 9; k++) g[k] = 0.0f;
-	if (visible) {
-		const uint32_t cnt = a.tiles_touched[idx];
-		const float2* __restrict__ p = reinterpret_cast<const float2*>(a.partial + (size_t)a.dup_off[idx] * PARTIAL_FLOATS);
-		for (uint32_t j = 0; j < cnt; j++, p += PARTIAL_FLOATS / 2) {
-			const float2 p0 = p[0], p1 = p[1], p2 = p[2], p3 = p[3], p4 = p[4];
-			g[0] += p0.x; g[1] += p0.y; g[2] += p1.x; g[3] += p1.y; g[4] += p2.x; g[5] += p2.y; g[6] += p3.x; g[7] += p3.y; g[8] += p4.x;
+	if (vismask != 0) {
+		const uint32_t off = valid ? a.dup_off[idx] : 0u;
+		const uint32_t cnt = visible ? a.tiles_touched[idx] : 0u;
+		const uint32_t span0 = __shfl_sync(FULL, off, 0);
+		const uint32_t span1 = __shfl_sync(FULL, off + cnt, nvalid - 1);   // slot offsets are an exclusive scan in index order
+		for (uint32_t c0 = span0; c0 < span1; c0 += PCHUNK) {
+			const uint32_t nent = min((uint32_t)PCHUNK, span1 - c0);
+			const float2* __restrict__ src = reinterpret_cast<const float2*>(a.partial + (size_t)c0 * PARTIAL_FLOATS);
+			for (uint32_t i = lane; i < nent * (PARTIAL_FLOATS / 2); i += 32) reinterpret_cast<float2*>(sb)[i] = __ldg(src + i);
+			__syncwarp();
+			const uint32_t lo = max(off, c0), hi = min(off + cnt, c0 + nent);
+			for (uint32_t k = lo; k < hi; k++) {
+				const float2* __restrict__ p = reinterpret_cast<const float2*>(sb + (k - c0) * PARTIAL_FLOATS);
+				const float2 p0 = p[0], p1 = p[1], p2 = p[2], p3 = p[3], p4 = p[4];
+				g[0] += p0.x; g[1] += p0.y; g[2] += p1.x; g[3] += p1.y; g[4] += p2.x; g[5] += p2.y; g[6] += p3.x; g[7] += p3.y; g[8] += p4.x;
+			}
+			__syncwarp();
 		}
 	}
-	a.dL_dmean2D[i3] = g[3]; a.dL_dmean2D[i3 + 1] = g[4]; a.dL_dmean2D[i3 + 2] = 0.0f;
-	if (a.dL_dconic) reinterpret_cast<float4*>(a.dL_dconic)[idx] = make_float4(g[5], g[6], 0.0f, g[7]);
-	if (acc && !visible) return;
-	put1(a.dL_dopacity + idx, g[8]);
-	put1(a.dL_dcolor + i3, g[0]); put1(a.dL_dcolor + i3 + 1, g[1]); put1(a.dL_dcolor + i3 + 2, g[2]);
+	if (valid) {
+		a.dL_dmean2D[i3] = g[3]; a.dL_dmean2D[i3 + 1] = g[4]; a.dL_dmean2D[i3 + 2] = 0.0f;
+		if (a.dL_dconic) reinterpret_cast<float4*>(a.dL_dconic)[idx] = make_float4(g[5], g[6], 0.0f, g[7]);
+	}
+	if (acc && vismask == 0) return;                            // warp-uniform: nothing to add anywhere
+	const bool wr = valid && !(acc && !visible);                // does this lane write its per-Gaussian parameter gradients?
+	if (wr) {
+		put1(a.dL_dopacity + idx, g[8]);
+		put1(a.dL_dcolor + i3, g[0]); put1(a.dL_dcolor + i3 + 1, g[1]); put1(a.dL_dcolor + i3 + 2, g[2]);
+	}
+
+	// ---- stage the warp's 32 SH rows (coalesced float4 reads) ----
+	const bool use_sh = a.shs != nullptr;
+	if (STAGED && use_sh && vismask != 0) {
+		const float4* __restrict__ src = reinterpret_cast<const float4*>(a.shs) + (size_t)warp_base * (SH_FLOATS / 4);
+		const int n4 = nvalid * (SH_FLOATS / 4);
+		#pragma unroll
+		for (int it = 0; it < SH_FLOATS / 4; it++) {
+			const int f4 = it * 32 + lane;
+			if (f4 < n4) {
+				const int row = f4 / (SH_FLOATS / 4), col = (f4 - row * (SH_FLOATS / 4)) * 4;
+				if ((vismask >> row) & 1u) {
+					const float4 v = __ldg(src + f4);
+					float* d = sb + row * SH_STRIDE + col;
+					d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+				}
+			}
+		}
+	}
+	__syncwarp();
 
 	float dmean[3] = { 0, 0, 0 }, dcov[6] = { 0, 0, 0, 0, 0, 0 };
 	const float mx = a.means3D[i3], my = a.means3D[i3 + 1], mz = a.means3D[i3 + 2];
@@ -119,38 +175,44 @@ __global__ void __launch_bounds__(128) preprocess_bwd_kernel(PreprocessBwdArgs a
 		dmean[2] += (Pj[8] * m_w - Pj[11] * mul1) * g[3] + (Pj[9] * m_w - Pj[11] * mul2) * g[4];
 	}
 	#pragma unroll
-	for (int k = 0; k < 6; k++) put1(a.dL_dcov3D + 6 * (size_t)idx + k, dcov[k]);
+	for (int k = 0; k < 6; k++) if (wr) put1(a.dL_dcov3D + 6 * (size_t)idx + k, dcov[k]);
 
 	// ---- SH colour gradient (reference backward.cu:9-128) ----
-	if (a.shs) {
-		float* __restrict__ dsh = a.dL_dsh + (size_t)idx * a.M * 3;
+	if (use_sh) {
+		// row pointers: shared-memory row (STAGED) or the Gaussian's own global rows
+		const float* __restrict__ sh = STAGED ? sb + lane * SH_STRIDE : a.shs + (size_t)(valid ? idx : 0) * a.M * 3;
+		float* __restrict__ dsh = STAGED ? sb + lane * SH_STRIDE : a.dL_dsh + (size_t)(valid ? idx : 0) * a.M * 3;
 		const int nact = visible ? (a.D + 1) * (a.D + 1) : 0;
 		if (visible) {
-			const float* __restrict__ sh = a.shs + (size_t)idx * a.M * 3;
 			const uint8_t cl = a.clamped[idx];
 			const float dR[3] = { (cl & 1) ? 0.f : g[0], (cl & 2) ? 0.f : g[1], (cl & 4) ? 0.f : g[2] };
 			const float ox = mx - a.campos[0], oy = my - a.campos[1], oz = mz - a.campos[2];
 			const float inv_len = 1.0f / sqrtf(ox * ox + oy * oy + oz * oz);
 			const float x = ox * inv_len, y = oy * inv_len, z = oz * inv_len;
 			float ddx = 0, ddy = 0, ddz = 0;   // dL/d(dir)
-			auto put = [&](int k, float wgt) { put1(dsh + 3 * k, wgt * dR[0]); put1(dsh + 3 * k + 1, wgt * dR[1]); put1(dsh + 3 * k + 2, wgt * dR[2]); };
 			auto dot = [&](int k) { return sh[3 * k] * dR[0] + sh[3 * k + 1] * dR[1] + sh[3 * k + 2] * dR[2]; };
+			// STAGED: the row is overwritten in place with the gradient, so every dot() of a band is taken before its put()s
+			auto put = [&](int k, float wgt) {
+				if (STAGED) { dsh[3 * k] = wgt * dR[0]; dsh[3 * k + 1] = wgt * dR[1]; dsh[3 * k + 2] = wgt * dR[2]; }
+				else { put1(dsh + 3 * k, wgt * dR[0]); put1(dsh + 3 * k + 1, wgt * dR[1]); put1(dsh + 3 * k + 2, wgt * dR[2]); }
+			};
 			put(0, kC0);
 			if (a.D > 0) {
+				const float s1 = dot(1), s2 = dot(2), s3 = dot(3);
 				put(1, -kC1 * y); put(2, kC1 * z); put(3, -kC1 * x);
-				ddx = -kC1 * dot(3); ddy = -kC1 * dot(1); ddz = kC1 * dot(2);
+				ddx = -kC1 * s3; ddy = -kC1 * s1; ddz = kC1 * s2;
 				if (a.D > 1) {
 					const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
-					put(4, b_SH_C2[0] * xy); put(5, b_SH_C2[1] * yz); put(6, b_SH_C2[2] * (2.f * zz - xx - yy)); put(7, b_SH_C2[3] * xz); put(8, b_SH_C2[4] * (xx - yy));
 					const float s4 = dot(4), s5 = dot(5), s6 = dot(6), s7 = dot(7), s8 = dot(8);
+					put(4, b_SH_C2[0] * xy); put(5, b_SH_C2[1] * yz); put(6, b_SH_C2[2] * (2.f * zz - xx - yy)); put(7, b_SH_C2[3] * xz); put(8, b_SH_C2[4] * (xx - yy));
 					ddx += b_SH_C2[0] * y * s4 + b_SH_C2[2] * 2.f * -x * s6 + b_SH_C2[3] * z * s7 + b_SH_C2[4] * 2.f * x * s8;
 					ddy += b_SH_C2[0] * x * s4 + b_SH_C2[1] * z * s5 + b_SH_C2[2] * 2.f * -y * s6 + b_SH_C2[4] * 2.f * -y * s8;
 					ddz += b_SH_C2[1] * y * s5 + b_SH_C2[2] * 2.f * 2.f * z * s6 + b_SH_C2[3] * x * s7;
 					if (a.D > 2) {
+						const float s9 = dot(9), s10 = dot(10), s11 = dot(11), s12 = dot(12), s13 = dot(13), s14 = dot(14), s15 = dot(15);
 						put(9, b_SH_C3[0] * y * (3.f * xx - yy)); put(10, b_SH_C3[1] * xy * z); put(11, b_SH_C3[2] * y * (4.f * zz - xx - yy));
 						put(12, b_SH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy)); put(13, b_SH_C3[4] * x * (4.f * zz - xx - yy));
 						put(14, b_SH_C3[5] * z * (xx - yy)); put(15, b_SH_C3[6] * x * (xx - 3.f * yy));
-						const float s9 = dot(9), s10 = dot(10), s11 = dot(11), s12 = dot(12), s13 = dot(13), s14 = dot(14), s15 = dot(15);
 						ddx += b_SH_C3[0] * s9 * 3.f * 2.f * xy + b_SH_C3[1] * s10 * yz + b_SH_C3[2] * s11 * -2.f * xy + b_SH_C3[3] * s12 * -3.f * 2.f * xz +
 							b_SH_C3[4] * s13 * (-3.f * xx + 4.f * zz - yy) + b_SH_C3[5] * s14 * 2.f * xz + b_SH_C3[6] * s15 * 3.f * (xx - yy);
 						ddy += b_SH_C3[0] * s9 * 3.f * (xx - yy) + b_SH_C3[1] * s10 * xz + b_SH_C3[2] * s11 * (-3.f * yy + 4.f * zz - xx) + b_SH_C3[3] * s12 * -3.f * 2.f * yz +
@@ -167,8 +229,33 @@ __global__ void __launch_bounds__(128) preprocess_bwd_kernel(PreprocessBwdArgs a
 			dmean[1] += (-ox * oy * ddx + (sum2 - oy * oy) * ddy - oz * oy * ddz) * invsum32;
 			dmean[2] += (-ox * oz * ddx - oy * oz * ddy + (sum2 - oz * oz) * ddz) * invsum32;
 		}
-		if (!acc) for (int k = nact; k < a.M; k++) { dsh[3 * k] = 0.0f; dsh[3 * k + 1] = 0.0f; dsh[3 * k + 2] = 0.0f; }
+		if (STAGED) {
+			// coefficients above the active degree (and whole rows of culled Gaussians) are zero; then the 32 rows go
+			// out as coalesced float4 (added to the buffer in accumulate mode, rows of culled Gaussians skipped there)
+			for (int k = nact; k < 16; k++) { dsh[3 * k] = 0.0f; dsh[3 * k + 1] = 0.0f; dsh[3 * k + 2] = 0.0f; }
+			__syncwarp();
+			float4* __restrict__ dst = reinterpret_cast<float4*>(a.dL_dsh) + (size_t)warp_base * (SH_FLOATS / 4);
+			const int n4 = nvalid * (SH_FLOATS / 4);
+			#pragma unroll
+			for (int it = 0; it < SH_FLOATS / 4; it++) {
+				const int f4 = it * 32 + lane;
+				if (f4 < n4) {
+					const int row = f4 / (SH_FLOATS / 4), col = (f4 - row * (SH_FLOATS / 4)) * 4;
+					const float* srow = sb + row * SH_STRIDE + col;
+					float4 v = make_float4(srow[0], srow[1], srow[2], srow[3]);
+					if (acc) {
+						if (!((vismask >> row) & 1u)) continue;
+						const float4 o = dst[f4];
+						v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+					}
+					dst[f4] = v;
+				}
+			}
+		} else if (!acc && valid) {
+			for (int k = nact; k < a.M; k++) { dsh[3 * k] = 0.0f; dsh[3 * k + 1] = 0.0f; dsh[3 * k + 2] = 0.0f; }
+		}
 	}
+	if (!wr) return;
 	put1(a.dL_dmean3D + i3, dmean[0]); put1(a.dL_dmean3D + i3 + 1, dmean[1]); put1(a.dL_dmean3D + i3 + 2, dmean[2]);
 
 	// ---- 3D covariance -> scale, rotation (reference backward.cu:268-331) ----
@@ -214,7 +301,10 @@ __global__ void __launch_bounds__(128) preprocess_bwd_kernel(PreprocessBwdArgs a
 int launch_preprocess_bwd(cudaStream_t stream, const PreprocessBwdArgs& a)
 {
 	if (a.P == 0) return 0;
-	count_launch(), preprocess_bwd_kernel<<<(a.P + 127) / 128, 128, 0, stream>>>(a);
+	const bool staged = a.shs && a.M == 16 && (reinterpret_cast<uintptr_t>(a.shs) & 15) == 0 && (reinterpret_cast<uintptr_t>(a.dL_dsh) & 15) == 0;
+	const unsigned grid = (unsigned)((a.P + PB_THREADS - 1) / PB_THREADS);
+	if (staged) count_launch(), preprocess_bwd_kernel<true><<<grid, PB_THREADS, 0, stream>>>(a);
+	else count_launch(), preprocess_bwd_kernel<false><<<grid, PB_THREADS, 0, stream>>>(a);
 	return check_launch("preprocess_bwd", stream, false);
 }
 

@@ -38,6 +38,23 @@ template <class K> __device__ __forceinline__ uint32_t digit_of(K key, int shift
 
 struct PassDesc { int shift[MAX_PASSES]; uint32_t mask[MAX_PASSES]; int npass; };
 
+// Lanes of the warp holding the same digit as this lane, built from one ballot per digit bit.  (match.any does this
+// in one instruction, but on sm_100a it is a slow MIO-queue operation: the first version of this kernel spent 58 % of
+// its stall samples waiting on MATCH results — profiles/r01_v0_ncu_full_summary.csv — whereas VOTE + LOP3 pipeline.)
+__device__ __forceinline__ unsigned same_digit_lanes(uint32_t d, bool valid, int nbits)
+{
+	unsigned peers = __ballot_sync(FULL, valid);
+	#pragma unroll
+	for (int b = 0; b < RADIX_BITS; b++) {
+		if (b < nbits) {
+			const bool bit = (d >> b) & 1u;
+			const unsigned bal = __ballot_sync(FULL, bit);
+			peers &= bit ? bal : ~bal;
+		}
+	}
+	return peers;
+}
+
 // ---- 1. histograms of all passes ------------------------------------------------------------------------------
 template <class K>
 __global__ void __launch_bounds__(SORT_THREADS) histogram_kernel(const K* __restrict__ keys, uint32_t n, PassDesc pd, uint32_t* __restrict__ ghist)
@@ -53,8 +70,8 @@ __global__ void __launch_bounds__(SORT_THREADS) histogram_kernel(const K* __rest
 		const K key = valid ? keys[i] : (K)0;
 		#pragma unroll 1
 		for (int p = 0; p < pd.npass; p++) {
-			const uint32_t d = valid ? digit_of(key, pd.shift[p], pd.mask[p]) : RADIX;   // RADIX = "no item"
-			const unsigned peers = __match_any_sync(FULL, d);
+			const uint32_t d = valid ? digit_of(key, pd.shift[p], pd.mask[p]) : 0u;
+			const unsigned peers = same_digit_lanes(d, valid, __popc(pd.mask[p]));
 			if (valid && (peers & lanemask_lt()) == 0) atomicAdd(&sh[p * RADIX + d], (uint32_t)__popc(peers));
 		}
 	}
@@ -102,6 +119,7 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(
 	__shared__ uint32_t s_vals[TILE];
 
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+	const int nbits = __popc(mask);
 	if (tid == 0) s_tile = atomicAdd(ticket, 1u);
 	for (int i = tid; i < SORT_WARPS * RADIX; i += SORT_THREADS) (&s_whist[0][0])[i] = 0;
 	__syncthreads();
@@ -122,9 +140,9 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(
 	for (int k = 0; k < IPT; k++) {
 		const uint32_t li = warp * WARP_ITEMS + k * 32 + lane;
 		const bool valid = li < tile_count;
-		const uint32_t d = valid ? digit_of(key[k], shift, mask) : RADIX;
-		const unsigned peers = __match_any_sync(FULL, d);
-		const int leader = __ffs(peers) - 1;
+		const uint32_t d = valid ? digit_of(key[k], shift, mask) : 0u;
+		const unsigned peers = same_digit_lanes(d, valid, nbits);
+		const int leader = valid ? __ffs(peers) - 1 : lane;
 		uint32_t old = 0;
 		if (valid && lane == leader) { old = s_whist[warp][d]; s_whist[warp][d] = old + __popc(peers); }
 		__syncwarp();

@@ -3,8 +3,9 @@
 // atomics per contributing (pixel, Gaussian) pair serialise in L2 on a single address per Gaussian.
 //
 // B200 design:
-//  * same TMA-staged, per-warp-culled list walk as the forward (render_fwd.cu), in reverse order, starting at the
-//    tile's deepest contributor (tile_max_contrib, recorded by the forward) instead of the end of the list;
+//  * same TMA-staged list walk as the forward (render_fwd.cu), in reverse order, starting at the tile's deepest
+//    contributor (tile_max_contrib, recorded by the forward); each warp visits exactly the pairs its 8x4 pixels blended
+//    in the forward (one flag byte per pair written by the forward) — no culling arithmetic, no wasted pairs;
 //  * each lane forms the 9 per-pair terms for its pixel exactly as the reference does; the warp then reduces them with
 //    a halving butterfly (8 values in 4+2+1+1+1 shuffles, the 9th in 5) — skipped when no lane contributed;
 //  * the 8 warps' sums meet in a shared-memory slab (plain stores, a per-warp bitmask says which rows are live) and
@@ -55,8 +56,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 	__shared__ __align__(128) float4 s_rec[STAGES][BWD_BATCH * 3];
 	__shared__ __align__(8) uint64_t s_full[STAGES];
 	__shared__ float s_slab[RENDER_WARPS][BWD_BATCH * NV];
-	__shared__ uint64_t s_mask[RENDER_WARPS];
-	__shared__ uint8_t s_list[RENDER_WARPS][BWD_BATCH];
+	__shared__ uint8_t s_flags[2][BWD_BATCH];     // [batch parity] the forward's "which warps blended this pair" byte
 
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 	const int tile = blockIdx.y * a.grid_x + blockIdx.x;
@@ -65,8 +65,6 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 	const int pix_x = blockIdx.x * TILE_X + wx + lx, pix_y = blockIdx.y * TILE_Y + wy + ly;
 	const bool inside = pix_x < a.W && pix_y < a.H;
 	const float pxf = (float)pix_x, pyf = (float)pix_y;
-	const float X0 = (float)(blockIdx.x * TILE_X + wx), X1 = X0 + 7.0f;
-	const float Y0 = (float)(blockIdx.y * TILE_Y + wy), Y1 = Y0 + 3.0f;
 
 	const uint2 range = a.ranges[tile];
 	const int n = (int)(range.y - range.x);
@@ -74,11 +72,16 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 	const int nbatches = (m + BWD_BATCH - 1) / BWD_BATCH;
 	const float4* __restrict__ src = reinterpret_cast<const float4*>(a.packed + range.x);
 	const uint32_t* __restrict__ emit = a.sorted_emit + range.x;
+	const uint8_t* __restrict__ flags = a.pair_flags + range.x;
 
-	// batch b covers local indices [lo_b, hi_b), hi_b = m - b*BWD_BATCH
+	// batch b covers local indices [lo_b, hi_b), hi_b = m - b*BWD_BATCH (back to front)
 	if (tid == 0 && USE_TMA) {
 		for (int s = 0; s < STAGES; s++) mbar_init(&s_full[s], 1);
 		mbar_fence_init();
+	}
+	if (tid < BWD_BATCH && nbatches > 0) {
+		const int lo0 = max(0, m - BWD_BATCH);
+		s_flags[0][tid] = (lo0 + tid < m) ? flags[lo0 + tid] : (uint8_t)0;
 	}
 	__syncthreads();
 	if (USE_TMA && tid == 0) {
@@ -106,7 +109,6 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 	bg_dot_dpixel += a.bg[0] * dLp0; bg_dot_dpixel += a.bg[1] * dLp1; bg_dot_dpixel += a.bg[2] * dLp2;
 	float ar0 = 0, ar1 = 0, ar2 = 0, lc0 = 0, lc1 = 0, lc2 = 0, last_alpha = 0;
 	const float ddelx_dx = 0.5f * a.W, ddely_dy = 0.5f * a.H;
-	const int warp_max = (int)__reduce_max_sync(FULL, (unsigned)last_contributor);
 
 	for (int b = 0; b < nbatches; b++) {
 		const int s = b % STAGES;
@@ -118,83 +120,72 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 			__syncthreads();
 		}
 		const float4* __restrict__ rec = s_rec[s];
-		uint64_t live = 0;
-		if (lo < warp_max) {
-			int nsurv = 0;
-			for (int c = 0; c < cnt; c += 32) {
-				const int e = c + lane;
-				bool pass = false;
-				if (e < cnt && lo + e < warp_max) {
-					const float4 ra = rec[e * 3];
-					pass = rect_may_contribute(ra.x, ra.y, ra.z, ra.w, rec[e * 3 + 1].x, rec[e * 3 + 2].z, X0, X1, Y0, Y1);
-				}
-				const unsigned mk = __ballot_sync(FULL, pass);
-				if (pass) s_list[warp][nsurv + __popc(mk & lanemask_lt())] = (uint8_t)e;
-				nsurv += __popc(mk);
-			}
-			__syncwarp();
-			for (int k = nsurv - 1; k >= 0; k--) {
-				const int e = s_list[warp][k];
-				const float4 ra = rec[e * 3], rb = rec[e * 3 + 1], rc = rec[e * 3 + 2];
-				float v[NV];
-				#pragma unroll
-				for (int i = 0; i < NV; i++) v[i] = 0.0f;
-				bool contributed = false;
-				if (lo + e < last_contributor) {
-					const float dx = __fsub_rn(ra.x, pxf), dy = __fsub_rn(ra.y, pyf);
-					const float q = __fmaf_rn(dx, __fmul_rn(dx, ra.z), __fmul_rn(dy, __fmul_rn(dy, rb.x)));
-					const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(dy, __fmul_rn(dx, ra.w)));
-					if (!(power > 0.0f) && !(power < rc.z)) {
-						const float G = expf(power);
-						const float alpha = fminf(0.99f, __fmul_rn(rb.y, G));
-						if (!(alpha < 1.0f / 255.0f)) {
-							contributed = true;
-							const float one_m_a = 1.f - alpha;
-							T = T / one_m_a;
-							const float dchannel_dcolor = alpha * T;
-							const float one_m_la = 1.f - last_alpha;
-							ar0 = last_alpha * lc0 + one_m_la * ar0; lc0 = rb.z;
-							ar1 = last_alpha * lc1 + one_m_la * ar1; lc1 = rb.w;
-							ar2 = last_alpha * lc2 + one_m_la * ar2; lc2 = rc.x;
-							float dL_dalpha = (rb.z - ar0) * dLp0;
-							dL_dalpha += (rb.w - ar1) * dLp1;
-							dL_dalpha += (rc.x - ar2) * dLp2;
-							v[0] = dchannel_dcolor * dLp0; v[1] = dchannel_dcolor * dLp1; v[2] = dchannel_dcolor * dLp2;
-							dL_dalpha *= T;
-							last_alpha = alpha;
-							dL_dalpha += (-T_final / one_m_a) * bg_dot_dpixel;
-							const float dL_dG = rb.y * dL_dalpha;
-							const float gdx = G * dx, gdy = G * dy;
-							const float dG_ddelx = -gdx * ra.z - gdy * ra.w;
-							const float dG_ddely = -gdy * rb.x - gdx * ra.w;
-							v[3] = dL_dG * dG_ddelx * ddelx_dx;
-							v[4] = dL_dG * dG_ddely * ddely_dy;
-							v[5] = -0.5f * gdx * dx * dL_dG;
-							v[6] = -0.5f * gdx * dy * dL_dG;
-							v[7] = -0.5f * gdy * dy * dL_dG;
-							v[8] = G * dL_dalpha;
-						}
+		// the pairs this warp's 8x4 pixels blended in the forward, as a 64-bit mask over the batch
+		const uint8_t* __restrict__ fl = s_flags[b & 1];
+		uint64_t surv = (uint64_t)__ballot_sync(FULL, (fl[lane] >> warp) & 1) | ((uint64_t)__ballot_sync(FULL, (fl[lane + 32] >> warp) & 1) << 32);
+		while (surv) {
+			const int e = 63 - __clzll((long long)surv);
+			surv ^= 1ull << e;
+			const float4 ra = rec[e * 3], rb = rec[e * 3 + 1], rc = rec[e * 3 + 2];
+			float v[NV];
+			#pragma unroll
+			for (int i = 0; i < NV; i++) v[i] = 0.0f;
+			if (lo + e < last_contributor) {
+				const float dx = __fsub_rn(ra.x, pxf), dy = __fsub_rn(ra.y, pyf);
+				const float q = __fmaf_rn(dx, __fmul_rn(dx, ra.z), __fmul_rn(dy, __fmul_rn(dy, rb.x)));
+				const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(dy, __fmul_rn(dx, ra.w)));
+				if (!(power > 0.0f)) {
+					const float G = expf(power);
+					const float alpha = fminf(0.99f, __fmul_rn(rb.y, G));
+					if (!(alpha < 1.0f / 255.0f)) {
+						const float inv_1ma = __frcp_rn(1.f - alpha);
+						T = T * inv_1ma;
+						const float dchannel_dcolor = alpha * T;
+						const float one_m_la = 1.f - last_alpha;
+						ar0 = last_alpha * lc0 + one_m_la * ar0; lc0 = rb.z;
+						ar1 = last_alpha * lc1 + one_m_la * ar1; lc1 = rb.w;
+						ar2 = last_alpha * lc2 + one_m_la * ar2; lc2 = rc.x;
+						float dL_dalpha = (rb.z - ar0) * dLp0;
+						dL_dalpha += (rb.w - ar1) * dLp1;
+						dL_dalpha += (rc.x - ar2) * dLp2;
+						v[0] = dchannel_dcolor * dLp0; v[1] = dchannel_dcolor * dLp1; v[2] = dchannel_dcolor * dLp2;
+						dL_dalpha *= T;
+						last_alpha = alpha;
+						dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
+						const float dL_dG = rb.y * dL_dalpha;
+						const float gdx = G * dx, gdy = G * dy;
+						const float dG_ddelx = -gdx * ra.z - gdy * ra.w;
+						const float dG_ddely = -gdy * rb.x - gdx * ra.w;
+						v[3] = dL_dG * dG_ddelx * ddelx_dx;
+						v[4] = dL_dG * dG_ddely * ddely_dy;
+						v[5] = -0.5f * gdx * dx * dL_dG;
+						v[6] = -0.5f * gdx * dy * dL_dG;
+						v[7] = -0.5f * gdy * dy * dL_dG;
+						v[8] = G * dL_dalpha;
 					}
 				}
-				if (__ballot_sync(FULL, contributed) == 0) continue;
-				float y, z;
-				warp_reduce9(v, lane, y, z);
-				if ((lane & 3) == 0) s_slab[warp][e * NV + ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1)] = y;
-				if (lane == 1) s_slab[warp][e * NV + 8] = z;
-				live |= 1ull << e;
 			}
+			float y, z;
+			warp_reduce9(v, lane, y, z);
+			if ((lane & 3) == 0) s_slab[warp][e * NV + ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1)] = y;
+			if (lane == 1) s_slab[warp][e * NV + 8] = z;
 		}
-		if (lane == 0) s_mask[warp] = live;
 		__syncthreads();
-		// combine the 8 warps and store one partial per (tile, Gaussian) at its emission index
+		// combine the warps that blended each pair and store one partial per (tile, Gaussian) at its slot
 		for (int t = tid; t < cnt * PARTIAL_FLOATS; t += RENDER_THREADS) {
 			const int e = t / PARTIAL_FLOATS, k = t - e * PARTIAL_FLOATS;
 			float sum = 0.0f;
 			if (k < NV) {
+				const uint32_t f = fl[e];
 				#pragma unroll
-				for (int w = 0; w < RENDER_WARPS; w++) if ((s_mask[w] >> e) & 1ull) sum += s_slab[w][e * NV + k];
+				for (int w = 0; w < RENDER_WARPS; w++) if ((f >> w) & 1u) sum += s_slab[w][e * NV + k];
 			}
 			a.partial[(size_t)emit[lo + e] * PARTIAL_FLOATS + k] = sum;
+		}
+		// flags of the next batch
+		if (b + 1 < nbatches && tid < BWD_BATCH) {
+			const int nhi = m - (b + 1) * BWD_BATCH, nlo = max(0, nhi - BWD_BATCH);
+			s_flags[(b + 1) & 1][tid] = (nlo + tid < nhi) ? flags[nlo + tid] : (uint8_t)0;
 		}
 		__syncthreads();
 		if (USE_TMA && tid == 0 && b + STAGES < nbatches) {

@@ -26,6 +26,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a
 	__shared__ __align__(128) float4 s_rec[STAGES][BATCH * 3];
 	__shared__ __align__(8) uint64_t s_full[STAGES];
 	__shared__ uint8_t s_list[RENDER_WARPS][BATCH];
+	__shared__ __align__(4) uint8_t s_used[2][RENDER_WARPS][BATCH];   // [batch parity]: 1 if the warp blended the entry into at least one pixel
 	__shared__ uint32_t s_max_contrib;
 
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -68,6 +69,10 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a
 	for (int b = 0; b < nbatches; b++) {
 		const int s = b % STAGES;
 		const int cnt = min(BATCH, n - b * BATCH);
+		// this warp's "used" row for the batch starts from zero (one 4-byte store per lane covers the 128 entries)
+		// (double-buffered by batch parity: the other warps read the previous batch's rows after the barrier below)
+		reinterpret_cast<uint32_t*>(s_used[b & 1][warp])[lane] = 0u;
+		__syncwarp();
 		if (USE_TMA) {
 			mbar_wait(&s_full[s], (uint32_t)(b / STAGES) & 1u);
 		} else {
@@ -76,20 +81,34 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a
 			__syncthreads();
 		}
 		const float4* __restrict__ rec = s_rec[s];
-		bool warp_done = __all_sync(FULL, done);
+		const bool warp_done = __all_sync(FULL, done);
 		if (!warp_done) {
-			// cull the batch against this warp's 8x4 pixels, one splat per lane, and compact the survivors
-			int nsurv = 0;
+			// stage 1: cheap AABB cull against this warp's 8x4 pixels, one splat per lane, survivors compacted
+			int n1 = 0;
 			for (int c = 0; c < cnt; c += 32) {
 				const int e = c + lane;
 				bool pass = false;
 				if (e < cnt) {
-					const float4 ra = rec[e * 3];
-					const float conz = rec[e * 3 + 1].x;
-					const float thr = rec[e * 3 + 2].z;
-					pass = rect_may_contribute(ra.x, ra.y, ra.z, ra.w, conz, thr, X0, X1, Y0, Y1);
+					const float4 ra = rec[e * 3], rc = rec[e * 3 + 2];
+					pass = aabb_may_contribute(ra.x, ra.y, rc.z, rc.w, X0, X1, Y0, Y1);
 				}
 				const unsigned m = __ballot_sync(FULL, pass);
+				if (pass) s_list[warp][n1 + __popc(m & lanemask_lt())] = (uint8_t)e;
+				n1 += __popc(m);
+			}
+			__syncwarp();
+			// stage 2: exact concave-maximum test on the (dense) survivors, compacted in place
+			int nsurv = 0;
+			for (int c = 0; c < n1; c += 32) {
+				const int k = c + lane;
+				bool pass = false;
+				int e = 0;
+				if (k < n1) {
+					e = s_list[warp][k];
+					const float4 ra = rec[e * 3], rb = rec[e * 3 + 1];
+					pass = rect_may_contribute(ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, X0, X1, Y0, Y1);
+				}
+				const unsigned m = __ballot_sync(FULL, pass);     // all lanes have consumed their s_list[k] by now
 				if (pass) s_list[warp][nsurv + __popc(m & lanemask_lt())] = (uint8_t)e;
 				nsurv += __popc(m);
 			}
@@ -97,11 +116,12 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a
 			for (int k = 0; k < nsurv; k++) {
 				const int e = s_list[warp][k];
 				const float4 ra = rec[e * 3], rb = rec[e * 3 + 1], rc = rec[e * 3 + 2];
+				bool used = false;
 				if (!done) {
 					const float dx = __fsub_rn(ra.x, pxf), dy = __fsub_rn(ra.y, pyf);
 					const float q = __fmaf_rn(dx, __fmul_rn(dx, ra.z), __fmul_rn(dy, __fmul_rn(dy, rb.x)));
 					const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(dy, __fmul_rn(dx, ra.w)));
-					if (!(power > 0.0f) && !(power < rc.z)) {
+					if (!(power > 0.0f)) {
 						const float alpha = fminf(0.99f, __fmul_rn(rb.y, expf(power)));
 						if (!(alpha < 1.0f / 255.0f)) {
 							const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
@@ -114,15 +134,24 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a
 								Dp = __fmaf_rn(T, __fmul_rn(alpha, rc.y), Dp);
 								T = test_T;
 								last_contributor = (uint32_t)(b * BATCH + e + 1);
+								used = true;
 							}
 						}
 					}
 				}
+				if (__any_sync(FULL, used) && lane == 0) s_used[b & 1][warp][e] = 1;
 				if (__all_sync(FULL, done)) break;
 			}
 		}
 		// every warp is past this stage: it can be refilled; stop early when all 256 pixels are saturated
 		const int all_done = __syncthreads_and(done);
+		// one flag byte per (tile, entry): bit w = warp w blended it.  The backward walks exactly these.
+		if (tid < cnt) {
+			uint32_t f = 0;
+			#pragma unroll
+			for (int w = 0; w < RENDER_WARPS; w++) f |= (uint32_t)s_used[b & 1][w][tid] << w;
+			a.pair_flags[(size_t)range.x + (size_t)b * BATCH + tid] = (uint8_t)f;
+		}
 		if (all_done) { b_exit = b + 1; break; }
 		if (USE_TMA && tid == 0 && b + STAGES < nbatches) {
 			const int nb = b + STAGES;
