@@ -17,7 +17,7 @@ _pinned = {}
 
 
 def _variant():
-    return int(os.environ.get("RAIN_RAST_VARIANT", "1"))
+    return int(os.environ.get("RAIN_RAST_VARIANT", "2"))
 
 
 def _ptr(t):

@@ -267,14 +267,16 @@ int rr_forward_raster(void* stream_, int P, int W, int H, int64_t N, const float
 	}
 	{
 		Stage st(stream, ST_RANGES_PACK);
-		if (launch_tile_ranges(stream, (size_t)N, B.keys_sorted, I.ranges, grid_x * grid_y)) return -1;
-		if (launch_pack(stream, (size_t)N, B.emit_sorted, B.owner, G.rec, B.packed, B.point_list)) return -1;
+		const bool packed = (variant == 0 || variant == 1);    // the gather modes read rec[] through point_list: no pack pass
+		if (launch_tile_ranges(stream, (size_t)N, B.keys_sorted, I.ranges, grid_x * grid_y, packed ? nullptr : B.emit_sorted, B.owner,
+			packed ? nullptr : B.point_list)) return -1;
+		if (packed && launch_pack(stream, (size_t)N, B.emit_sorted, B.owner, G.rec, B.packed, B.point_list)) return -1;
 	}
 	if (debug && check_launch("ranges/pack", stream, true)) return -1;
 
 	RenderArgs r; memset(&r, 0, sizeof(r));
 	r.W = W; r.H = H; r.grid_x = grid_x; r.grid_y = grid_y;
-	r.ranges = I.ranges; r.packed = B.packed; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.tile_max_contrib = I.tile_max; r.pair_flags = B.flags;
+	r.ranges = I.ranges; r.packed = B.packed; r.rec = G.rec; r.point_list = B.point_list; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.tile_max_contrib = I.tile_max; r.pair_flags = B.flags;
 	r.out_color = out_color; r.out_depth = out_depth; r.variant = variant;
 	{ Stage st(stream, ST_RENDER_FWD); if (launch_render_fwd(stream, r)) return -1; }
 	return check_launch("forward_raster", stream, debug != 0);
@@ -308,7 +310,7 @@ int rr_backward(void* stream_, int P, int D, int M, int W, int H, int64_t N, con
 
 	RenderArgs r; memset(&r, 0, sizeof(r));
 	r.W = W; r.H = H; r.grid_x = grid_x; r.grid_y = grid_y;
-	r.ranges = I.ranges; r.packed = B.packed; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.tile_max_contrib = I.tile_max; r.pair_flags = B.flags;
+	r.ranges = I.ranges; r.packed = B.packed; r.rec = G.rec; r.point_list = B.point_list; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.tile_max_contrib = I.tile_max; r.pair_flags = B.flags;
 	r.dL_dpix = dL_dpix; r.sorted_emit = B.emit_sorted; r.partial = partial; r.variant = variant;
 	if (N > 0) {
 		{ Stage st(stream, ST_RENDER_BWD); if (launch_render_bwd(stream, r)) return -1; }

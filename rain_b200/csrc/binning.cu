@@ -151,10 +151,13 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* _
 	}
 }
 
-__global__ void __launch_bounds__(256) tile_ranges_kernel(uint32_t N, const uint32_t* __restrict__ keys, uint2* __restrict__ ranges)
+// tile ranges from key changes; optionally also point_list[j] = owner[sorted_slot[j]] (the sorted Gaussian ids)
+__global__ void __launch_bounds__(256) tile_ranges_kernel(uint32_t N, const uint32_t* __restrict__ keys, uint2* __restrict__ ranges,
+	const uint32_t* __restrict__ sorted_slot, const uint32_t* __restrict__ owner, uint32_t* __restrict__ point_list)
 {
 	const uint32_t idx = blockIdx.x * 256 + threadIdx.x;
 	if (idx >= N) return;
+	if (point_list) point_list[idx] = __ldg(owner + __ldg(sorted_slot + idx));
 	const uint32_t cur = keys[idx];
 	if (idx == 0) ranges[cur].x = 0;
 	else {
@@ -207,11 +210,12 @@ int launch_duplicate(cudaStream_t stream, int P, const uint32_t* order, const ui
 	return check_launch("duplicate", stream, false);
 }
 
-int launch_tile_ranges(cudaStream_t stream, size_t N, const uint32_t* keys, uint2* ranges, int num_tiles)
+int launch_tile_ranges(cudaStream_t stream, size_t N, const uint32_t* keys, uint2* ranges, int num_tiles,
+	const uint32_t* sorted_slot, const uint32_t* owner, uint32_t* point_list)
 {
 	cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)num_tiles, stream);
 	if (N == 0) return 0;
-	count_launch(), tile_ranges_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>((uint32_t)N, keys, ranges);
+	count_launch(), tile_ranges_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>((uint32_t)N, keys, ranges, sorted_slot, owner, point_list);
 	return check_launch("tile_ranges", stream, false);
 }
 

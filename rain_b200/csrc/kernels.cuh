@@ -25,7 +25,8 @@ int launch_scan_tiles(cudaStream_t, int P, const uint32_t* order, const uint32_t
 	uint32_t* slot_off /*exclusive, index order*/, uint32_t* block_sums, uint32_t* num_rendered_dev);
 int launch_duplicate(cudaStream_t, int P, const uint32_t* order, const uint32_t* offsets, const uint2* rect, int grid_x,
 	uint32_t* tile_keys /*[N] emission order*/, uint32_t* slots /*[N] emission order*/, uint32_t* owner /*[N] by slot*/, const uint32_t* slot_off /*[P]*/);
-int launch_tile_ranges(cudaStream_t, size_t N, const uint32_t* sorted_tile_keys, uint2* ranges, int num_tiles);
+int launch_tile_ranges(cudaStream_t, size_t N, const uint32_t* sorted_tile_keys, uint2* ranges, int num_tiles,
+	const uint32_t* sorted_slot /*nullable with point_list*/, const uint32_t* owner, uint32_t* point_list);
 int launch_pack(cudaStream_t, size_t N, const uint32_t* sorted_emit, const uint32_t* owner, const SplatRec* rec,
 	SplatRec* packed, uint32_t* point_list);
 int launch_export_keys(cudaStream_t, size_t N, const uint32_t* sorted_tile_keys, const uint32_t* point_list, const uint32_t* rec_words, uint64_t* out);
@@ -34,7 +35,9 @@ int launch_export_keys(cudaStream_t, size_t N, const uint32_t* sorted_tile_keys,
 struct RenderArgs {
 	int W, H, grid_x, grid_y;
 	const uint2* ranges;        // [tiles]
-	const SplatRec* packed;     // [N] in sorted (tile, depth) order
+	const SplatRec* packed;     // [N] in sorted (tile, depth) order (variants 0/1 only)
+	const SplatRec* rec;        // [P] per-Gaussian records (variants 2/3 gather from here)
+	const uint32_t* point_list; // [N] sorted Gaussian ids
 	const float* bg;            // [3]
 	float* final_T;             // [H*W]
 	uint32_t* n_contrib;        // [H*W]
@@ -46,7 +49,7 @@ struct RenderArgs {
 	const float* dL_dpix;       // [3,H,W]
 	const uint32_t* sorted_emit;// [N] emission index of each sorted entry
 	float* partial;             // [N, PARTIAL_FLOATS] indexed by emission index
-	int variant;                // 0 = cooperative loads, 1 = TMA bulk staging
+	int variant;                // staging mode, see render_common.cuh
 };
 int launch_render_fwd(cudaStream_t, const RenderArgs&);
 int launch_render_bwd(cudaStream_t, const RenderArgs&);

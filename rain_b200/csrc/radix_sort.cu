@@ -70,9 +70,12 @@ __global__ void __launch_bounds__(SORT_THREADS) histogram_kernel(const K* __rest
 		const K key = valid ? keys[i] : (K)0;
 		#pragma unroll 1
 		for (int p = 0; p < pd.npass; p++) {
-			const uint32_t d = valid ? digit_of(key, pd.shift[p], pd.mask[p]) : 0u;
-			const unsigned peers = same_digit_lanes(d, valid, __popc(pd.mask[p]));
-			if (valid && (peers & lanemask_lt()) == 0) atomicAdd(&sh[p * RADIX + d], (uint32_t)__popc(peers));
+			// warp-uniform digit (the usual case for the high digits of tile ids / depth exponents): one add of 32;
+			// otherwise plain shared-memory atomics, which are conflict-light exactly when the digits differ
+			const uint32_t d = valid ? digit_of(key, pd.shift[p], pd.mask[p]) : RADIX;
+			const uint32_t d0 = __shfl_sync(FULL, d, 0);
+			if (__all_sync(FULL, d == d0)) { if (lane_id() == 0 && valid) atomicAdd(&sh[p * RADIX + d0], 32u); }
+			else if (valid) atomicAdd(&sh[p * RADIX + d], 1u);
 		}
 	}
 	__syncthreads();
@@ -168,17 +171,27 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(
 		for (int w = 0; w < warp; w++) pre += s_wtot[w];
 		const uint32_t dstart = pre + inc - sum;
 		s_dstart[d] = dstart;
-		// decoupled look-back
+		// decoupled look-back, LB predecessors per round: the status words of a round are loaded with independent loads
+		// (one L2 round trip per round instead of one per predecessor — a tile of the first wave has to walk over every
+		// tile in flight, ~3 per SM), then consumed in order; the walk restarts at the first word not yet published.
 		uint32_t excl = 0;
 		if (tile > 0) {
+			constexpr int LB = 8;
 			int64_t t = (int64_t)tile - 1;
-			while (true) {
-				const uint32_t v = status[(size_t)t * RADIX + d];
-				const uint32_t f = v >> FLAG_SHIFT;
-				if (f == 0) continue;               // predecessor has not published yet
-				excl += v & VALUE_MASK;
-				if (f == 2) break;
-				t--;
+			bool found = false;
+			while (!found) {
+				uint32_t v[LB];
+				#pragma unroll
+				for (int j = 0; j < LB; j++) { v[j] = 2u << FLAG_SHIFT; if (t - j >= 0) v[j] = status[(size_t)(t - j) * RADIX + d]; }   // before tile 0: inclusive 0
+				#pragma unroll
+				for (int j = 0; j < LB; j++) {
+					if (found) break;
+					const uint32_t f = v[j] >> FLAG_SHIFT;
+					if (f == 0) { t -= j; break; }          // not published yet: retry from here
+					excl += v[j] & VALUE_MASK;
+					if (f == 2) found = true;
+					else if (j == LB - 1) t -= LB;
+				}
 			}
 			status[(size_t)tile * RADIX + d] = (excl + sum) | FLAG_INC;
 		}

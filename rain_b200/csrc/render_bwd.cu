@@ -50,9 +50,10 @@ __device__ __forceinline__ void warp_reduce9(const float (&v)[NV], int lane, flo
 	for (int o = 16; o >= 1; o >>= 1) z += __shfl_xor_sync(FULL, z, o);
 }
 
-template <bool USE_TMA>
+template <int MODE>
 __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a)
 {
+	constexpr bool USE_TMA = StageMode<MODE>::tma;
 	__shared__ __align__(128) float4 s_rec[STAGES][BWD_BATCH * 3];
 	__shared__ __align__(8) uint64_t s_full[STAGES];
 	__shared__ float s_slab[RENDER_WARPS][BWD_BATCH * NV];
@@ -70,7 +71,9 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 	const int n = (int)(range.y - range.x);
 	const int m = min(n, (int)a.tile_max_contrib[tile]);        // entries [m, n) contributed to no pixel
 	const int nbatches = (m + BWD_BATCH - 1) / BWD_BATCH;
-	const float4* __restrict__ src = reinterpret_cast<const float4*>(a.packed + range.x);
+	const float4* __restrict__ src = reinterpret_cast<const float4*>(a.packed) + (size_t)range.x * 3;
+	const float4* __restrict__ grec = reinterpret_cast<const float4*>(a.rec);
+	const uint32_t* __restrict__ ids = a.point_list + range.x;
 	const uint32_t* __restrict__ emit = a.sorted_emit + range.x;
 	const uint8_t* __restrict__ flags = a.pair_flags + range.x;
 
@@ -84,19 +87,18 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 		s_flags[0][tid] = (lo0 + tid < m) ? flags[lo0 + tid] : (uint8_t)0;
 	}
 	__syncthreads();
-	if (USE_TMA && tid == 0) {
+	if (USE_TMA && warp == 0) {
 		for (int b = 0; b < STAGES && b < nbatches; b++) {
 			const int hi = m - b * BWD_BATCH, lo = max(0, hi - BWD_BATCH);
-			const uint32_t bytes = (uint32_t)(hi - lo) * (uint32_t)sizeof(SplatRec);
-			mbar_arrive_expect_tx(&s_full[b], bytes);
-			bulk_g2s(&s_rec[b][0], src + (size_t)lo * 3, bytes, &s_full[b]);
+			stage_fill_async<MODE>(&s_rec[b][0], &s_full[b], src, grec, ids, lo, hi - lo, lane);
 		}
 	}
 
-	// duplicates behind the deepest contributor get zero partials
-	for (int t = tid; t < (n - m) * PARTIAL_FLOATS; t += RENDER_THREADS) {
-		const int e = m + t / PARTIAL_FLOATS, k = t % PARTIAL_FLOATS;
-		a.partial[(size_t)emit[e] * PARTIAL_FLOATS + k] = 0.0f;
+	// duplicates behind the deepest contributor get zero partials (one thread per pair: one slot load, five 8-byte stores)
+	for (int e = m + tid; e < n; e += RENDER_THREADS) {
+		float2* __restrict__ p = reinterpret_cast<float2*>(a.partial + (size_t)__ldg(emit + e) * PARTIAL_FLOATS);
+		#pragma unroll
+		for (int k = 0; k < PARTIAL_FLOATS / 2; k++) p[k] = make_float2(0.0f, 0.0f);
 	}
 
 	const size_t pid = (size_t)a.W * pix_y + pix_x, HW = (size_t)a.H * a.W;
@@ -116,7 +118,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 		if (USE_TMA) {
 			mbar_wait(&s_full[s], (uint32_t)(b / STAGES) & 1u);
 		} else {
-			for (int i = tid; i < cnt * 3; i += RENDER_THREADS) s_rec[s][i] = __ldg(src + (size_t)lo * 3 + i);
+			stage_fill_sync<MODE>(&s_rec[s][0], src, grec, ids, lo, cnt, tid);
 			__syncthreads();
 		}
 		const float4* __restrict__ rec = s_rec[s];
@@ -138,7 +140,8 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 					const float G = expf(power);
 					const float alpha = fminf(0.99f, __fmul_rn(rb.y, G));
 					if (!(alpha < 1.0f / 255.0f)) {
-						const float inv_1ma = __frcp_rn(1.f - alpha);
+						float inv_1ma;      // 1/(1-alpha), 1-alpha in [0.01, 1): the approximate reciprocal (1 ulp) is ample for 1e-4 gradients
+						asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv_1ma) : "f"(1.f - alpha));
 						T = T * inv_1ma;
 						const float dchannel_dcolor = alpha * T;
 						const float one_m_la = 1.f - last_alpha;
@@ -188,12 +191,10 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 			s_flags[(b + 1) & 1][tid] = (nlo + tid < nhi) ? flags[nlo + tid] : (uint8_t)0;
 		}
 		__syncthreads();
-		if (USE_TMA && tid == 0 && b + STAGES < nbatches) {
+		if (USE_TMA && warp == 0 && b + STAGES < nbatches) {
 			const int nb = b + STAGES;
 			const int nhi = m - nb * BWD_BATCH, nlo = max(0, nhi - BWD_BATCH);
-			const uint32_t bytes = (uint32_t)(nhi - nlo) * (uint32_t)sizeof(SplatRec);
-			mbar_arrive_expect_tx(&s_full[s], bytes);
-			bulk_g2s(&s_rec[s][0], src + (size_t)nlo * 3, bytes, &s_full[s]);
+			stage_fill_async<MODE>(&s_rec[s][0], &s_full[s], src, grec, ids, nlo, nhi - nlo, lane);
 		}
 	}
 }
@@ -203,8 +204,12 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 int launch_render_bwd(cudaStream_t stream, const RenderArgs& a)
 {
 	const dim3 grid(a.grid_x, a.grid_y);
-	if (a.variant == 0) count_launch(), render_bwd_kernel<false><<<grid, RENDER_THREADS, 0, stream>>>(a);
-	else count_launch(), render_bwd_kernel<true><<<grid, RENDER_THREADS, 0, stream>>>(a);
+	switch (a.variant) {
+	case MODE_PACKED_LDG: count_launch(), render_bwd_kernel<MODE_PACKED_LDG><<<grid, RENDER_THREADS, 0, stream>>>(a); break;
+	case MODE_PACKED_TMA: count_launch(), render_bwd_kernel<MODE_PACKED_TMA><<<grid, RENDER_THREADS, 0, stream>>>(a); break;
+	case MODE_GATHER_LDG: count_launch(), render_bwd_kernel<MODE_GATHER_LDG><<<grid, RENDER_THREADS, 0, stream>>>(a); break;
+	default: count_launch(), render_bwd_kernel<MODE_GATHER_TMA><<<grid, RENDER_THREADS, 0, stream>>>(a); break;
+	}
 	return check_launch("render_bwd", stream, false);
 }
 

@@ -20,9 +20,10 @@ namespace rr {
 
 namespace {
 
-template <bool USE_TMA>
+template <int MODE>
 __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a)
 {
+	constexpr bool USE_TMA = StageMode<MODE>::tma;
 	__shared__ __align__(128) float4 s_rec[STAGES][BATCH * 3];
 	__shared__ __align__(8) uint64_t s_full[STAGES];
 	__shared__ uint8_t s_list[RENDER_WARPS][BATCH];
@@ -43,7 +44,9 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a
 	const uint2 range = a.ranges[tile];
 	const int n = (int)(range.y - range.x);
 	const int nbatches = (n + BATCH - 1) / BATCH;
-	const float4* __restrict__ src = reinterpret_cast<const float4*>(a.packed + range.x);
+	const float4* __restrict__ src = reinterpret_cast<const float4*>(a.packed) + (size_t)range.x * 3;
+	const float4* __restrict__ grec = reinterpret_cast<const float4*>(a.rec);
+	const uint32_t* __restrict__ ids = a.point_list + range.x;
 
 	if (tid == 0) {
 		s_max_contrib = 0;
@@ -53,12 +56,9 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a
 		}
 	}
 	__syncthreads();
-	if (USE_TMA && tid == 0) {
-		for (int b = 0; b < STAGES && b < nbatches; b++) {
-			const uint32_t bytes = (uint32_t)min(BATCH, n - b * BATCH) * (uint32_t)sizeof(SplatRec);
-			mbar_arrive_expect_tx(&s_full[b], bytes);
-			bulk_g2s(&s_rec[b][0], src + (size_t)b * BATCH * 3, bytes, &s_full[b]);
-		}
+	if (USE_TMA && warp == 0) {
+		for (int b = 0; b < STAGES && b < nbatches; b++)
+			stage_fill_async<MODE>(&s_rec[b][0], &s_full[b], src, grec, ids, b * BATCH, min(BATCH, n - b * BATCH), lane);
 	}
 
 	float T = 1.0f, C0 = 0.0f, C1 = 0.0f, C2 = 0.0f, Dp = 0.0f;
@@ -77,7 +77,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a
 			mbar_wait(&s_full[s], (uint32_t)(b / STAGES) & 1u);
 		} else {
 			__syncthreads();
-			for (int i = tid; i < cnt * 3; i += RENDER_THREADS) s_rec[s][i] = __ldg(src + (size_t)b * BATCH * 3 + i);
+			stage_fill_sync<MODE>(&s_rec[s][0], src, grec, ids, b * BATCH, cnt, tid);
 			__syncthreads();
 		}
 		const float4* __restrict__ rec = s_rec[s];
@@ -113,34 +113,42 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a
 				nsurv += __popc(m);
 			}
 			__syncwarp();
-			for (int k = 0; k < nsurv; k++) {
-				const int e = s_list[warp][k];
-				const float4 ra = rec[e * 3], rb = rec[e * 3 + 1], rc = rec[e * 3 + 2];
-				bool used = false;
-				if (!done) {
-					const float dx = __fsub_rn(ra.x, pxf), dy = __fsub_rn(ra.y, pyf);
-					const float q = __fmaf_rn(dx, __fmul_rn(dx, ra.z), __fmul_rn(dy, __fmul_rn(dy, rb.x)));
-					const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(dy, __fmul_rn(dx, ra.w)));
-					if (!(power > 0.0f)) {
-						const float alpha = fminf(0.99f, __fmul_rn(rb.y, expf(power)));
-						if (!(alpha < 1.0f / 255.0f)) {
-							const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
-							if (test_T < 0.0001f) {
-								done = true;
-							} else {
-								C0 = __fmaf_rn(T, __fmul_rn(alpha, rb.z), C0);
-								C1 = __fmaf_rn(T, __fmul_rn(alpha, rb.w), C1);
-								C2 = __fmaf_rn(T, __fmul_rn(alpha, rc.x), C2);
-								Dp = __fmaf_rn(T, __fmul_rn(alpha, rc.y), Dp);
-								T = test_T;
-								last_contributor = (uint32_t)(b * BATCH + e + 1);
-								used = true;
+			// blend the survivors, 32 at a time; each lane keeps one "I blended survivor kk" bit per chunk, OR-reduced once per
+			// chunk with redux.sync, and the saturation vote is taken every 8 survivors (a saturated pixel skips the math anyway)
+			for (int kc = 0; kc < nsurv; kc += 32) {
+				const int kn = min(32, nsurv - kc);
+				uint32_t usedbits = 0;
+				bool stop = false;
+				for (int kk = 0; kk < kn; kk++) {
+					const int e = s_list[warp][kc + kk];
+					const float4 ra = rec[e * 3], rb = rec[e * 3 + 1], rc = rec[e * 3 + 2];
+					if (!done) {
+						const float dx = __fsub_rn(ra.x, pxf), dy = __fsub_rn(ra.y, pyf);
+						const float q = __fmaf_rn(dx, __fmul_rn(dx, ra.z), __fmul_rn(dy, __fmul_rn(dy, rb.x)));
+						const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(dy, __fmul_rn(dx, ra.w)));
+						if (!(power > 0.0f)) {
+							const float alpha = fminf(0.99f, __fmul_rn(rb.y, expf(power)));
+							if (!(alpha < 1.0f / 255.0f)) {
+								const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
+								if (test_T < 0.0001f) {
+									done = true;
+								} else {
+									C0 = __fmaf_rn(T, __fmul_rn(alpha, rb.z), C0);
+									C1 = __fmaf_rn(T, __fmul_rn(alpha, rb.w), C1);
+									C2 = __fmaf_rn(T, __fmul_rn(alpha, rc.x), C2);
+									Dp = __fmaf_rn(T, __fmul_rn(alpha, rc.y), Dp);
+									T = test_T;
+									last_contributor = (uint32_t)(b * BATCH + e + 1);
+									usedbits |= 1u << kk;
+								}
 							}
 						}
 					}
+					if ((kk & 7) == 7 && __all_sync(FULL, done)) { stop = true; break; }
 				}
-				if (__any_sync(FULL, used) && lane == 0) s_used[b & 1][warp][e] = 1;
-				if (__all_sync(FULL, done)) break;
+				const unsigned wbits = __reduce_or_sync(FULL, usedbits);
+				if ((wbits >> lane) & 1u) s_used[b & 1][warp][s_list[warp][kc + lane]] = 1;
+				if (stop || __all_sync(FULL, done)) break;
 			}
 		}
 		// every warp is past this stage: it can be refilled; stop early when all 256 pixels are saturated
@@ -153,11 +161,9 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a
 			a.pair_flags[(size_t)range.x + (size_t)b * BATCH + tid] = (uint8_t)f;
 		}
 		if (all_done) { b_exit = b + 1; break; }
-		if (USE_TMA && tid == 0 && b + STAGES < nbatches) {
+		if (USE_TMA && warp == 0 && b + STAGES < nbatches) {
 			const int nb = b + STAGES;
-			const uint32_t bytes = (uint32_t)min(BATCH, n - nb * BATCH) * (uint32_t)sizeof(SplatRec);
-			mbar_arrive_expect_tx(&s_full[s], bytes);
-			bulk_g2s(&s_rec[s][0], src + (size_t)nb * BATCH * 3, bytes, &s_full[s]);
+			stage_fill_async<MODE>(&s_rec[s][0], &s_full[s], src, grec, ids, nb * BATCH, min(BATCH, n - nb * BATCH), lane);
 		}
 	}
 
@@ -186,8 +192,12 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a
 int launch_render_fwd(cudaStream_t stream, const RenderArgs& a)
 {
 	const dim3 grid(a.grid_x, a.grid_y);
-	if (a.variant == 0) count_launch(), render_fwd_kernel<false><<<grid, RENDER_THREADS, 0, stream>>>(a);
-	else count_launch(), render_fwd_kernel<true><<<grid, RENDER_THREADS, 0, stream>>>(a);
+	switch (a.variant) {
+	case MODE_PACKED_LDG: count_launch(), render_fwd_kernel<MODE_PACKED_LDG><<<grid, RENDER_THREADS, 0, stream>>>(a); break;
+	case MODE_PACKED_TMA: count_launch(), render_fwd_kernel<MODE_PACKED_TMA><<<grid, RENDER_THREADS, 0, stream>>>(a); break;
+	case MODE_GATHER_LDG: count_launch(), render_fwd_kernel<MODE_GATHER_LDG><<<grid, RENDER_THREADS, 0, stream>>>(a); break;
+	default: count_launch(), render_fwd_kernel<MODE_GATHER_TMA><<<grid, RENDER_THREADS, 0, stream>>>(a); break;
+	}
 	return check_launch("render_fwd", stream, false);
 }
 

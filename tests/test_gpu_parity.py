@@ -55,10 +55,11 @@ def check_against_ref(fw, g, ref, N_r, color_r, radii_r, depth_r, g_r):
         assert rel_err(a, b)[0] <= RTOL_GRAD
 
 
-@pytest.mark.parametrize("name", ["C1", "C2", "C3"])
-@pytest.mark.parametrize("variant", ["1", "0"])
+@pytest.mark.parametrize("name,variant", [("C1", "2"), ("C1", "1"), ("C1", "3"), ("C1", "0"), ("C2", "2"), ("C2", "1"), ("C2", "3"), ("C2", "0"),
+                                          ("C3", "2"), ("C3", "1")])
 def test_configs_match_reference_cuda(device, refcuda, monkeypatch, name, variant):
-    """BASELINE.json configs 1-3 at full size against the reference CUDA on the same GPU."""
+    """BASELINE.json configs 1-3 at full size against the reference CUDA on the same GPU, in every staging mode
+    (2 = TMA gather, the default; 1 = packed TMA; 3 / 0 = their plain-load cross-checks)."""
     monkeypatch.setenv("RAIN_RAST_VARIANT", variant)
     cfg = CONFIGS[name]
     sc = make_scene(cfg["P"], cfg["D"]).to(device); cam = make_camera(0, 1, cfg["W"], cfg["H"]).to(device)
