@@ -47,7 +47,7 @@ int rr_prof_read(double* ms, int64_t* calls, int reset);
 size_t rr_geom_bytes(int P);
 size_t rr_image_bytes(int W, int H);
 size_t rr_binning_bytes(int64_t N, int W, int H);
-size_t rr_backward_ws_bytes(int64_t N);
+size_t rr_backward_ws_bytes(int P);
 
 /* Forward, first half — replaces FORWARD::preprocess + cub InclusiveSum + the blocking cudaMemcpy of num_rendered
  * (Rasterizer::forward, rasterizer_impl.cu:187-273).  Writes radii[P] and the geometry blob, and enqueues an async
@@ -72,7 +72,8 @@ int rr_forward_raster(void* stream, int P, int W, int H, int64_t N, const float*
  * dL_dsh / dL_dcolor, dL_dopacity, dL_dscale, dL_drot / dL_dcov3D) are ADDED to the buffers' contents and Gaussians
  * with radii == 0 are left untouched; the per-view outputs dL_dmean2D and dL_dconic are still overwritten.
  * dL_dconic may be null (the reference keeps it internal).  dL_dsh is [P,M,3] (unused when shs is null),
- * dL_dscale / dL_drot may be null when cov3D_precomp is given.  ws: rr_backward_ws_bytes(N) of scratch. */
+ * dL_dscale / dL_drot may be null when cov3D_precomp is given.  ws: rr_backward_ws_bytes(P) of scratch
+ * (the per-Gaussian gradient accumulators the backward render adds into; zero-filled inside). */
 int rr_backward(void* stream, int P, int D, int M, int W, int H, int64_t N, const float* background,
 	const float* means3D, const float* shs, const float* colors_precomp,
 	const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
@@ -102,9 +103,10 @@ int rr_sort_pairs_u64(void* stream, int64_t n, uint64_t* keys_in, uint64_t* keys
 
 /* byte offsets of the arrays inside the opaque blobs (for stage-wise diffing against the oracle / reference).
  * geom:    [0] rec f32[P,12]  [1] cov3D f32[P,6]  [2] clamped u8[P]  [3] tiles_touched u32[P]  [4] rect u32[P,2]
- *          [5] depth_order u32[P]  [6] offsets u32[P] (inclusive, in depth order)  [7] dup_off u32[P]  [8] num_rendered u32
- * binning: [0] tile_keys_sorted u32[N]  [1] emit_sorted u32[N]  [2] owner u32[N]  [3] point_list u32[N]  [4] packed f32[N,12]
- * image:   [0] final_T f32[H*W]  [1] n_contrib u32[H*W]  [2] ranges u32[T,2]  [3] tile_max_contrib u32[T] */
+ *          [5] depth_order u32[P]  [6] offsets u32[P] (inclusive, in depth order)  [7] = [6]  [8] num_rendered u32
+ * binning: [0] tile_keys_sorted u32[N]  [1] point_list u32[N]  [2] warp_flags u32[8*(N/32+T+2)]  [3] = [1]  [4] packed f32[N,12]
+ *          (packed is only filled by the packed staging variants 0 / 1)
+ * image:   [0] final_T f32[H*W]  [1] n_contrib u32[H*W]  [2] ranges u32[T,2]  [3] reserved u32[T] */
 int rr_geom_layout(int P, int64_t offsets_host[9]);
 int rr_binning_layout(int64_t N, int W, int H, int64_t offsets_host[5]);
 int rr_image_layout(int W, int H, int64_t offsets_host[4]);

@@ -130,7 +130,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         bg, colors_c, scales_c, rots, cov_c = (_f32c(t, dev) for t in (background, colors, scales, rotations, cov3D_precomp))
         view, proj, cam, sh_c, dpix = (_f32c(t, dev) for t in (viewmatrix, projmatrix, campos, sh, dL_dout_color))
         radii_c = radii.contiguous()
-        ws = torch.empty(lib.rr_backward_ws_bytes(int(R)), dtype=torch.uint8, device=dev)
+        ws = torch.empty(lib.rr_backward_ws_bytes(P), dtype=torch.uint8, device=dev)
         with torch.cuda.device(dev):
             stream = torch.cuda.current_stream()
             _lib.check(lib.rr_backward(stream.cuda_stream, P, int(degree), M, W, H, int(R), _ptr(bg),

@@ -23,7 +23,7 @@ SIGNATURES = {
     "rr_geom_bytes": (_sz, [_i]),
     "rr_image_bytes": (_sz, [_i, _i]),
     "rr_binning_bytes": (_sz, [_i64, _i, _i]),
-    "rr_backward_ws_bytes": (_sz, [_i64]),
+    "rr_backward_ws_bytes": (_sz, [_i]),
     "rr_forward_geom": (_i, [_vp, _i, _i, _i, _i, _i,
                              _vp, _vp, _vp, _vp,
                              _vp, _f, _vp, _vp,

@@ -85,7 +85,7 @@ int tile_bits(int num_tiles) { int b = 0; while ((num_tiles >> b) != 0) b++; ret
 
 struct GeomLayout {
 	SplatRec* rec; float* cov3D; uint8_t* clamped; uint32_t* tiles_touched; uint2* rect;
-	uint32_t *key_a, *key_b, *val_a, *val_b, *offsets, *dup_off, *block_sums, *num_rendered; void* sort_ws;
+	uint32_t *key_a, *key_b, *val_a, *val_b, *offsets, *block_sums, *num_rendered; void* sort_ws;
 	size_t total;
 	int64_t off[9];
 };
@@ -101,7 +101,6 @@ GeomLayout geom_layout(void* blob, int P)
 	L.key_a = c.take<uint32_t>(Pz); L.key_b = c.take<uint32_t>(Pz);
 	L.val_a = c.take<uint32_t>(Pz); L.val_b = c.take<uint32_t>(Pz);
 	L.offsets = c.take<uint32_t>(Pz);
-	L.dup_off = c.take<uint32_t>(Pz);
 	L.block_sums = c.take<uint32_t>(scan_ws_elems((int)Pz));
 	L.num_rendered = c.take<uint32_t>(4);
 	L.sort_ws = c.take<char>(sort_ws_bytes<uint32_t>(Pz, 0, 32));
@@ -109,15 +108,15 @@ GeomLayout geom_layout(void* blob, int P)
 	char* b = reinterpret_cast<char*>(blob);
 	// depth sort: 4 passes -> result back in the *_a buffers
 	L.off[0] = (char*)L.rec - b; L.off[1] = (char*)L.cov3D - b; L.off[2] = (char*)L.clamped - b; L.off[3] = (char*)L.tiles_touched - b;
-	L.off[4] = (char*)L.rect - b; L.off[5] = (char*)L.val_a - b; L.off[6] = (char*)L.offsets - b; L.off[7] = (char*)L.dup_off - b;
+	L.off[4] = (char*)L.rect - b; L.off[5] = (char*)L.val_a - b; L.off[6] = (char*)L.offsets - b; L.off[7] = L.off[6];
 	L.off[8] = (char*)L.num_rendered - b;
 	return L;
 }
 
 struct BinLayout {
-	uint32_t *key_a, *key_b, *emit_a, *emit_b, *owner, *point_list; SplatRec* packed; uint8_t* flags; void* sort_ws;
-	uint32_t *keys_sorted, *emit_sorted;
-	int bits; size_t total; int64_t off[5];
+	uint32_t *key_a, *key_b, *val_a, *val_b, *warp_flags; SplatRec* packed; void* sort_ws;
+	uint32_t *keys_sorted, *point_list;
+	int bits; size_t flag_words; size_t total; int64_t off[5];
 };
 BinLayout bin_layout(void* blob, int64_t N, int W, int H)
 {
@@ -126,18 +125,19 @@ BinLayout bin_layout(void* blob, int64_t N, int W, int H)
 	const int tiles = ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
 	L.bits = tile_bits(tiles);
 	L.key_a = c.take<uint32_t>(Nz); L.key_b = c.take<uint32_t>(Nz);
-	L.emit_a = c.take<uint32_t>(Nz); L.emit_b = c.take<uint32_t>(Nz);
-	L.owner = c.take<uint32_t>(Nz);
-	L.point_list = c.take<uint32_t>(Nz);
-	L.packed = c.take<SplatRec>(Nz);
-	L.flags = c.take<uint8_t>(Nz + 16);
+	L.val_a = c.take<uint32_t>(Nz); L.val_b = c.take<uint32_t>(Nz);
+	L.flag_words = warp_flag_words(Nz, (size_t)tiles);
+	L.warp_flags = c.take<uint32_t>(L.flag_words);
 	L.sort_ws = c.take<char>(sort_ws_bytes<uint32_t>(Nz, 0, L.bits));
+	// the packed copy of the records in sorted order is only touched by the packed staging variants (0 / 1); it is carved
+	// last so that the working set of the gather variants stays compact
+	L.packed = c.take<SplatRec>(Nz);
 	L.total = c.used();
 	const bool in_b = (((L.bits + 7) / 8) & 1) != 0;
 	L.keys_sorted = in_b ? L.key_b : L.key_a;
-	L.emit_sorted = in_b ? L.emit_b : L.emit_a;
+	L.point_list = in_b ? L.val_b : L.val_a;
 	char* b = reinterpret_cast<char*>(blob);
-	L.off[0] = (char*)L.keys_sorted - b; L.off[1] = (char*)L.emit_sorted - b; L.off[2] = (char*)L.owner - b;
+	L.off[0] = (char*)L.keys_sorted - b; L.off[1] = (char*)L.point_list - b; L.off[2] = (char*)L.warp_flags - b;
 	L.off[3] = (char*)L.point_list - b; L.off[4] = (char*)L.packed - b;
 	return L;
 }
@@ -192,7 +192,7 @@ int rr_prof_read(double* ms, int64_t* calls, int reset)
 size_t rr_geom_bytes(int P) { return geom_layout(nullptr, P).total + 256; }
 size_t rr_image_bytes(int W, int H) { return img_layout(nullptr, W, H).total + 256; }
 size_t rr_binning_bytes(int64_t N, int W, int H) { return bin_layout(nullptr, N, W, H).total + 256; }
-size_t rr_backward_ws_bytes(int64_t N) { return (size_t)(N < 1 ? 1 : N) * PARTIAL_FLOATS * sizeof(float) + 256; }
+size_t rr_backward_ws_bytes(int P) { return (size_t)(P < 1 ? 1 : P) * ACC_FLOATS * sizeof(float) + 256; }
 
 int rr_geom_layout(int P, int64_t o[9]) { const GeomLayout L = geom_layout(nullptr, P); memcpy(o, L.off, sizeof(L.off)); return 0; }
 int rr_binning_layout(int64_t N, int W, int H, int64_t o[5]) { const BinLayout L = bin_layout(nullptr, N, W, H); memcpy(o, L.off, sizeof(L.off)); return 0; }
@@ -235,7 +235,7 @@ int rr_forward_geom(void* stream_, int P, int D, int M, int W, int H,
 	{ Stage st(stream, ST_DEPTH_SORT); which = sort_pairs<uint32_t>(stream, L.key_a, L.key_b, L.val_a, L.val_b, (size_t)P, 0, 32, L.sort_ws, true); }
 	if (which != 0) { if (which > 0) set_error("internal: depth sort landed in the wrong buffer"); return -1; }
 	if (debug && check_launch("depth sort", stream, true)) return -1;
-	{ Stage st(stream, ST_SCAN); if (launch_scan_tiles(stream, P, L.val_a, L.tiles_touched, L.offsets, L.dup_off, L.block_sums, L.num_rendered)) return -1; }
+	{ Stage st(stream, ST_SCAN); if (launch_scan_tiles(stream, P, L.val_a, L.tiles_touched, L.offsets, L.block_sums, L.num_rendered)) return -1; }
 	// num_rendered: u32 on the device, widened on the host side of the copy (the upper half was zeroed above)
 	cudaMemcpyAsync(num_rendered_host, L.num_rendered, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream);
 	return check_launch("forward_geom", stream, debug != 0);
@@ -257,10 +257,10 @@ int rr_forward_raster(void* stream_, int P, int W, int H, int64_t N, const float
 	const int grid_x = (W + TILE_X - 1) / TILE_X, grid_y = (H + TILE_Y - 1) / TILE_Y;
 
 	if (N > 0) {
-		{ Stage st(stream, ST_DUPLICATE); if (launch_duplicate(stream, P, G.val_a, G.offsets, G.rect, grid_x, B.key_a, B.emit_a, B.owner, G.dup_off)) return -1; }
+		{ Stage st(stream, ST_DUPLICATE); if (launch_duplicate(stream, P, G.val_a, G.offsets, G.rect, grid_x, B.key_a, B.val_a)) return -1; }
 		if (debug && check_launch("duplicate", stream, true)) return -1;
 		int which;
-		{ Stage st(stream, ST_TILE_SORT); which = sort_pairs<uint32_t>(stream, B.key_a, B.key_b, B.emit_a, B.emit_b, (size_t)N, 0, B.bits, B.sort_ws, false); }
+		{ Stage st(stream, ST_TILE_SORT); which = sort_pairs<uint32_t>(stream, B.key_a, B.key_b, B.val_a, B.val_b, (size_t)N, 0, B.bits, B.sort_ws, false); }
 		if (which < 0) return -1;
 		if ((which ? B.key_b : B.key_a) != B.keys_sorted) { set_error("internal: tile sort landed in the wrong buffer"); return -1; }
 		if (debug && check_launch("tile sort", stream, true)) return -1;
@@ -268,15 +268,14 @@ int rr_forward_raster(void* stream_, int P, int W, int H, int64_t N, const float
 	{
 		Stage st(stream, ST_RANGES_PACK);
 		const bool packed = (variant == 0 || variant == 1);    // the gather modes read rec[] through point_list: no pack pass
-		if (launch_tile_ranges(stream, (size_t)N, B.keys_sorted, I.ranges, grid_x * grid_y, packed ? nullptr : B.emit_sorted, B.owner,
-			packed ? nullptr : B.point_list)) return -1;
-		if (packed && launch_pack(stream, (size_t)N, B.emit_sorted, B.owner, G.rec, B.packed, B.point_list)) return -1;
+		if (launch_tile_ranges(stream, (size_t)N, B.keys_sorted, I.ranges, grid_x * grid_y)) return -1;
+		if (packed && launch_pack(stream, (size_t)N, B.point_list, G.rec, B.packed)) return -1;
 	}
 	if (debug && check_launch("ranges/pack", stream, true)) return -1;
 
 	RenderArgs r; memset(&r, 0, sizeof(r));
 	r.W = W; r.H = H; r.grid_x = grid_x; r.grid_y = grid_y;
-	r.ranges = I.ranges; r.packed = B.packed; r.rec = G.rec; r.point_list = B.point_list; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.tile_max_contrib = I.tile_max; r.pair_flags = B.flags;
+	r.ranges = I.ranges; r.packed = B.packed; r.rec = G.rec; r.point_list = B.point_list; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.warp_flags = B.warp_flags;
 	r.out_color = out_color; r.out_depth = out_depth; r.variant = variant;
 	{ Stage st(stream, ST_RENDER_FWD); if (launch_render_fwd(stream, r)) return -1; }
 	return check_launch("forward_raster", stream, debug != 0);
@@ -304,16 +303,19 @@ int rr_backward(void* stream_, int P, int D, int M, int W, int H, int64_t N, con
 	const GeomLayout G = geom_layout(geom, P);
 	const BinLayout B = bin_layout(binning, N, W, H);
 	const ImgLayout I = img_layout(image, W, H);
-	if (G.total > geom_bytes || B.total > binning_bytes || I.total > image_bytes || rr_backward_ws_bytes(N) > ws_bytes + 256) { set_error("scratch blob too small"); return -1; }
+	if (G.total > geom_bytes || B.total > binning_bytes || I.total > image_bytes || rr_backward_ws_bytes(P) > ws_bytes + 256) { set_error("scratch blob too small"); return -1; }
 	const int grid_x = (W + TILE_X - 1) / TILE_X, grid_y = (H + TILE_Y - 1) / TILE_Y;
-	float* partial = reinterpret_cast<float*>(ws);
+	float* grad_acc = reinterpret_cast<float*>(ws);
 
 	RenderArgs r; memset(&r, 0, sizeof(r));
 	r.W = W; r.H = H; r.grid_x = grid_x; r.grid_y = grid_y;
-	r.ranges = I.ranges; r.packed = B.packed; r.rec = G.rec; r.point_list = B.point_list; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.tile_max_contrib = I.tile_max; r.pair_flags = B.flags;
-	r.dL_dpix = dL_dpix; r.sorted_emit = B.emit_sorted; r.partial = partial; r.variant = variant;
-	if (N > 0) {
-		{ Stage st(stream, ST_RENDER_BWD); if (launch_render_bwd(stream, r)) return -1; }
+	r.ranges = I.ranges; r.packed = B.packed; r.rec = G.rec; r.point_list = B.point_list; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.warp_flags = B.warp_flags;
+	r.dL_dpix = dL_dpix; r.grad_acc = grad_acc; r.variant = variant;
+	{
+		// the accumulators start from zero (the fill is part of the render_bwd stage time)
+		Stage st(stream, ST_RENDER_BWD);
+		cudaMemsetAsync(grad_acc, 0, (size_t)P * ACC_FLOATS * sizeof(float), stream);
+		if (N > 0 && launch_render_bwd(stream, r)) return -1;
 		if (debug && check_launch("render_bwd", stream, true)) return -1;
 	}
 
@@ -324,7 +326,7 @@ int rr_backward(void* stream_, int P, int D, int M, int W, int H, int64_t N, con
 	a.means3D = means3D; a.scales = cov3D_precomp ? nullptr : scales; a.rotations = cov3D_precomp ? nullptr : rotations;
 	a.shs = use_sh ? shs : nullptr; a.cov3D = cov3D_precomp ? cov3D_precomp : G.cov3D;        // rasterizer_impl.cu:406
 	a.view = viewmatrix; a.proj = projmatrix; a.campos = campos; a.has_colors_precomp = colors_precomp != nullptr; a.accumulate = (flags & RR_BWD_ACCUMULATE) ? 1 : 0;
-	a.radii = radii; a.clamped = G.clamped; a.tiles_touched = G.tiles_touched; a.dup_off = G.dup_off; a.partial = partial;
+	a.radii = radii; a.clamped = G.clamped; a.rec = G.rec; a.grad_acc = grad_acc;
 	a.dL_dmean2D = dL_dmean2D; a.dL_dconic = dL_dconic; a.dL_dopacity = dL_dopacity; a.dL_dcolor = dL_dcolor; a.dL_dmean3D = dL_dmean3D;
 	a.dL_dcov3D = dL_dcov3D; a.dL_dsh = dL_dsh; a.dL_dscale = dL_dscale; a.dL_drot = dL_drot;
 	{ Stage st(stream, ST_PREPROCESS_BWD); if (launch_preprocess_bwd(stream, a)) return -1; }

@@ -35,65 +35,56 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* s
 	return pre + inc - v;
 }
 
-// Two prefix sums over tiles_touched are produced by the same three launches: one in DEPTH order (where each
-// Gaussian's duplicates go in the emission list) and one in INDEX order (where its gradient partials go, so that the
-// backward-preprocess kernel, which runs in index order, reads them as one contiguous stream).
-// block_sums layout: [0, nb) depth order, [nb, 2 nb) index order.
-__global__ void __launch_bounds__(SCAN_THREADS) scan_reduce_kernel(int P, int nb, const uint32_t* __restrict__ order, const uint32_t* __restrict__ tt, uint32_t* __restrict__ block_sums)
+// Inclusive prefix sum of tiles_touched in DEPTH order (where each Gaussian's duplicates go in the emission list):
+// reduce / scan-of-block-sums / final, three launches.
+__global__ void __launch_bounds__(SCAN_THREADS) scan_reduce_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ tt, uint32_t* __restrict__ block_sums)
 {
 	__shared__ uint32_t s_warp[SCAN_THREADS / 32];
-	uint32_t sum = 0, sum_i = 0;
+	uint32_t sum = 0;
 	#pragma unroll
 	for (int k = 0; k < SCAN_ITEMS; k++) {
 		const int i = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS + k;
-		if (i < P) { sum += tt[order[i]]; sum_i += tt[i]; }
+		if (i < P) sum += tt[order[i]];
 	}
-	uint32_t tot, tot_i;
+	uint32_t tot;
 	block_exclusive_scan(sum, s_warp, tot);
-	block_exclusive_scan(sum_i, s_warp, tot_i);
-	if (threadIdx.x == 0) { block_sums[blockIdx.x] = tot; block_sums[nb + blockIdx.x] = tot_i; }
+	if (threadIdx.x == 0) block_sums[blockIdx.x] = tot;
 }
 
 // single CTA: exclusive scan of the block sums in place, grand total to *total
 __global__ void __launch_bounds__(SCAN_THREADS) scan_blocksums_kernel(int nb, uint32_t* __restrict__ block_sums, uint32_t* __restrict__ total)
 {
 	__shared__ uint32_t s_warp[SCAN_THREADS / 32];
-	for (int which = 0; which < 2; which++) {
-		uint32_t* bs = block_sums + which * nb;
-		uint32_t carry = 0;
-		for (int base = 0; base < nb; base += SCAN_THREADS) {
-			const int i = base + threadIdx.x;
-			const uint32_t v = i < nb ? bs[i] : 0;
-			uint32_t tot;
-			const uint32_t ex = block_exclusive_scan(v, s_warp, tot);
-			if (i < nb) bs[i] = carry + ex;
-			carry += tot;
-		}
-		if (threadIdx.x == 0 && which == 0) *total = carry;
+	uint32_t carry = 0;
+	for (int base = 0; base < nb; base += SCAN_THREADS) {
+		const int i = base + threadIdx.x;
+		const uint32_t v = i < nb ? block_sums[i] : 0;
+		uint32_t tot;
+		const uint32_t ex = block_exclusive_scan(v, s_warp, tot);
+		if (i < nb) block_sums[i] = carry + ex;
+		carry += tot;
 	}
+	if (threadIdx.x == 0) *total = carry;
 }
 
-__global__ void __launch_bounds__(SCAN_THREADS) scan_final_kernel(int P, int nb, const uint32_t* __restrict__ order, const uint32_t* __restrict__ tt,
-	const uint32_t* __restrict__ block_excl, uint32_t* __restrict__ offsets /*inclusive, depth order*/, uint32_t* __restrict__ slot_off /*exclusive, index order*/)
+__global__ void __launch_bounds__(SCAN_THREADS) scan_final_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ tt,
+	const uint32_t* __restrict__ block_excl, uint32_t* __restrict__ offsets /*inclusive, depth order*/)
 {
 	__shared__ uint32_t s_warp[SCAN_THREADS / 32];
-	uint32_t v[SCAN_ITEMS], w[SCAN_ITEMS], sum = 0, sum_i = 0;
+	uint32_t v[SCAN_ITEMS], sum = 0;
 	#pragma unroll
 	for (int k = 0; k < SCAN_ITEMS; k++) {
 		const int i = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS + k;
 		v[k] = i < P ? tt[order[i]] : 0;
-		w[k] = i < P ? tt[i] : 0;
-		sum += v[k]; sum_i += w[k];
+		sum += v[k];
 	}
 	uint32_t tot;
 	uint32_t run = block_excl[blockIdx.x] + block_exclusive_scan(sum, s_warp, tot);
-	uint32_t run_i = block_excl[nb + blockIdx.x] + block_exclusive_scan(sum_i, s_warp, tot);
 	#pragma unroll
 	for (int k = 0; k < SCAN_ITEMS; k++) {
 		const int i = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS + k;
 		run += v[k];
-		if (i < P) { offsets[i] = run; slot_off[i] = run_i; }
-		run_i += w[k];
+		if (i < P) offsets[i] = run;
 	}
 }
 
@@ -101,14 +92,12 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_final_kernel(int P, int nb,
 // contiguous span is owned by the last lane whose exclusive offset is <= s (binary search over 32 shared values),
 // so writes are coalesced and a large splat does not serialise on one thread (reference: one thread per rect).
 __global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ offsets,
-	const uint2* __restrict__ rect, int grid_x, uint32_t* __restrict__ tile_keys, uint32_t* __restrict__ slots, uint32_t* __restrict__ owner,
-	const uint32_t* __restrict__ slot_off)
+	const uint2* __restrict__ rect, int grid_x, uint32_t* __restrict__ tile_keys, uint32_t* __restrict__ gaussian_ids)
 {
 	__shared__ uint32_t s_excl[8][32];
 	__shared__ uint32_t s_g[8][32];
 	__shared__ uint32_t s_xw[8][32];   // x0 | width<<16
 	__shared__ uint32_t s_y0[8][32];
-	__shared__ uint32_t s_slot[8][32];   // first partial slot of the Gaussian (index-order exclusive offset)
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	const int i = blockIdx.x * 256 + threadIdx.x;
 	uint32_t g = 0, excl = 0, incl = 0;
@@ -123,13 +112,11 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* _
 	const uint32_t end = __shfl_sync(FULL, incl, last_valid);
 	const uint32_t total = end - base;
 	const uint32_t tt = i < P ? incl - excl : 0u;
-	uint32_t x0 = 0, wdt = 1, y0 = 0, slot0 = 0;
+	uint32_t x0 = 0, wdt = 1, y0 = 0;
 	if (tt > 0) {
 		const uint2 r = rect[g];
 		x0 = r.x & 0xffffu; wdt = (r.x >> 16) - x0; y0 = r.y & 0xffffu;
-		slot0 = slot_off[g];
 	}
-	s_slot[warp][lane] = slot0;
 	s_excl[warp][lane] = i < P ? excl - base : total;
 	s_g[warp][lane] = g;
 	s_xw[warp][lane] = x0 | (wdt << 16);
@@ -145,19 +132,15 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* _
 		const uint32_t w = xw >> 16, xx0 = xw & 0xffffu;
 		const uint32_t ry = local / w, rx = local - ry * w;
 		tile_keys[base + s] = (s_y0[warp][lo] + ry) * (uint32_t)grid_x + xx0 + rx;
-		const uint32_t slot = s_slot[warp][lo] + local;
-		slots[base + s] = slot;             // the sort's value: where this pair's gradient partial goes
-		owner[slot] = s_g[warp][lo];        // runs of tiles_touched consecutive slots per Gaussian
+		gaussian_ids[base + s] = s_g[warp][lo];        // the sort's value, as in the reference (rasterizer_impl.cu:92)
 	}
 }
 
-// tile ranges from key changes; optionally also point_list[j] = owner[sorted_slot[j]] (the sorted Gaussian ids)
-__global__ void __launch_bounds__(256) tile_ranges_kernel(uint32_t N, const uint32_t* __restrict__ keys, uint2* __restrict__ ranges,
-	const uint32_t* __restrict__ sorted_slot, const uint32_t* __restrict__ owner, uint32_t* __restrict__ point_list)
+// tile ranges from key changes (identifyTileRanges, rasterizer_impl.cu:105-127)
+__global__ void __launch_bounds__(256) tile_ranges_kernel(uint32_t N, const uint32_t* __restrict__ keys, uint2* __restrict__ ranges)
 {
 	const uint32_t idx = blockIdx.x * 256 + threadIdx.x;
 	if (idx >= N) return;
-	if (point_list) point_list[idx] = __ldg(owner + __ldg(sorted_slot + idx));
 	const uint32_t cur = keys[idx];
 	if (idx == 0) ranges[cur].x = 0;
 	else {
@@ -167,16 +150,14 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(uint32_t N, const uint
 	if (idx == N - 1) ranges[cur].y = N;
 }
 
-// packed[j] = rec[owner[sorted_emit[j]]]; three threads move one 48-byte record (one float4 each)
-__global__ void __launch_bounds__(256) pack_kernel(uint32_t N, const uint32_t* __restrict__ sorted_emit, const uint32_t* __restrict__ owner,
-	const float4* __restrict__ rec, float4* __restrict__ packed, uint32_t* __restrict__ point_list)
+// packed[j] = rec[point_list[j]]; three threads move one 48-byte record (one float4 each)
+__global__ void __launch_bounds__(256) pack_kernel(uint32_t N, const uint32_t* __restrict__ point_list,
+	const float4* __restrict__ rec, float4* __restrict__ packed)
 {
 	const size_t t = (size_t)blockIdx.x * 256 + threadIdx.x;
 	if (t >= (size_t)N * 3) return;
 	const uint32_t j = (uint32_t)(t / 3), part = (uint32_t)(t - (size_t)j * 3);
-	const uint32_t g = owner[sorted_emit[j]];
-	packed[t] = __ldg(&rec[(size_t)g * 3 + part]);
-	if (part == 0) point_list[j] = g;
+	packed[t] = __ldg(&rec[(size_t)point_list[j] * 3 + part]);
 }
 
 __global__ void __launch_bounds__(256) export_keys_kernel(uint32_t N, const uint32_t* __restrict__ tile_keys, const uint32_t* __restrict__ point_list,
@@ -190,40 +171,39 @@ __global__ void __launch_bounds__(256) export_keys_kernel(uint32_t N, const uint
 
 }  // namespace
 
-size_t scan_ws_elems(int P) { return 2 * ((size_t)(P + SCAN_TILE - 1) / SCAN_TILE + 1); }
+size_t scan_ws_elems(int P) { return (size_t)(P + SCAN_TILE - 1) / SCAN_TILE + 1; }
 
-int launch_scan_tiles(cudaStream_t stream, int P, const uint32_t* order, const uint32_t* tt, uint32_t* offsets, uint32_t* slot_off, uint32_t* block_sums, uint32_t* num_rendered_dev)
+int launch_scan_tiles(cudaStream_t stream, int P, const uint32_t* order, const uint32_t* tt, uint32_t* offsets, uint32_t* block_sums, uint32_t* num_rendered_dev)
 {
 	if (P == 0) { cudaMemsetAsync(num_rendered_dev, 0, sizeof(uint32_t), stream); return 0; }
 	const int nb = (P + SCAN_TILE - 1) / SCAN_TILE;
-	count_launch(), scan_reduce_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, nb, order, tt, block_sums);
+	count_launch(), scan_reduce_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, order, tt, block_sums);
 	count_launch(), scan_blocksums_kernel<<<1, SCAN_THREADS, 0, stream>>>(nb, block_sums, num_rendered_dev);
-	count_launch(), scan_final_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, nb, order, tt, block_sums, offsets, slot_off);
+	count_launch(), scan_final_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, order, tt, block_sums, offsets);
 	return check_launch("scan_tiles", stream, false);
 }
 
 int launch_duplicate(cudaStream_t stream, int P, const uint32_t* order, const uint32_t* offsets, const uint2* rect, int grid_x,
-	uint32_t* tile_keys, uint32_t* slots, uint32_t* owner, const uint32_t* slot_off)
+	uint32_t* tile_keys, uint32_t* gaussian_ids)
 {
 	if (P == 0) return 0;
-	count_launch(), duplicate_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, order, offsets, rect, grid_x, tile_keys, slots, owner, slot_off);
+	count_launch(), duplicate_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, order, offsets, rect, grid_x, tile_keys, gaussian_ids);
 	return check_launch("duplicate", stream, false);
 }
 
-int launch_tile_ranges(cudaStream_t stream, size_t N, const uint32_t* keys, uint2* ranges, int num_tiles,
-	const uint32_t* sorted_slot, const uint32_t* owner, uint32_t* point_list)
+int launch_tile_ranges(cudaStream_t stream, size_t N, const uint32_t* keys, uint2* ranges, int num_tiles)
 {
 	cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)num_tiles, stream);
 	if (N == 0) return 0;
-	count_launch(), tile_ranges_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>((uint32_t)N, keys, ranges, sorted_slot, owner, point_list);
+	count_launch(), tile_ranges_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>((uint32_t)N, keys, ranges);
 	return check_launch("tile_ranges", stream, false);
 }
 
-int launch_pack(cudaStream_t stream, size_t N, const uint32_t* sorted_emit, const uint32_t* owner, const SplatRec* rec, SplatRec* packed, uint32_t* point_list)
+int launch_pack(cudaStream_t stream, size_t N, const uint32_t* point_list, const SplatRec* rec, SplatRec* packed)
 {
 	if (N == 0) return 0;
-	count_launch(), pack_kernel<<<(unsigned)((N * 3 + 255) / 256), 256, 0, stream>>>((uint32_t)N, sorted_emit, owner, reinterpret_cast<const float4*>(rec),
-		reinterpret_cast<float4*>(packed), point_list);
+	count_launch(), pack_kernel<<<(unsigned)((N * 3 + 255) / 256), 256, 0, stream>>>((uint32_t)N, point_list, reinterpret_cast<const float4*>(rec),
+		reinterpret_cast<float4*>(packed));
 	return check_launch("pack", stream, false);
 }
 

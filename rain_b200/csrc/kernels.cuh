@@ -22,16 +22,25 @@ int launch_mark_visible(cudaStream_t, int P, const float* means3D, const float* 
 // binning.cu
 size_t scan_ws_elems(int P);
 int launch_scan_tiles(cudaStream_t, int P, const uint32_t* order, const uint32_t* tiles_touched, uint32_t* offsets /*inclusive, depth order*/,
-	uint32_t* slot_off /*exclusive, index order*/, uint32_t* block_sums, uint32_t* num_rendered_dev);
+	uint32_t* block_sums, uint32_t* num_rendered_dev);
 int launch_duplicate(cudaStream_t, int P, const uint32_t* order, const uint32_t* offsets, const uint2* rect, int grid_x,
-	uint32_t* tile_keys /*[N] emission order*/, uint32_t* slots /*[N] emission order*/, uint32_t* owner /*[N] by slot*/, const uint32_t* slot_off /*[P]*/);
-int launch_tile_ranges(cudaStream_t, size_t N, const uint32_t* sorted_tile_keys, uint2* ranges, int num_tiles,
-	const uint32_t* sorted_slot /*nullable with point_list*/, const uint32_t* owner, uint32_t* point_list);
-int launch_pack(cudaStream_t, size_t N, const uint32_t* sorted_emit, const uint32_t* owner, const SplatRec* rec,
-	SplatRec* packed, uint32_t* point_list);
+	uint32_t* tile_keys /*[N] emission order*/, uint32_t* gaussian_ids /*[N] emission order*/);
+int launch_tile_ranges(cudaStream_t, size_t N, const uint32_t* sorted_tile_keys, uint2* ranges, int num_tiles);
+int launch_pack(cudaStream_t, size_t N, const uint32_t* point_list, const SplatRec* rec, SplatRec* packed);
 int launch_export_keys(cudaStream_t, size_t N, const uint32_t* sorted_tile_keys, const uint32_t* point_list, const uint32_t* rec_words, uint64_t* out);
 
 // render_fwd.cu / render_bwd.cu
+// Per-warp blend flags ("which list entries did warp w's 8x4 pixel block blend"), written by the forward and walked by
+// the backward.  One bit per (tile list entry, warp), stored as 32-bit words; the words of tile t start at
+// 8 * (ranges[t].x / 32 + t) and warp w owns the ceil(n / 32) consecutive words from + w * ceil(n / 32)
+// (n = list length of the tile; bit j % 32 of word j / 32 is list entry j).
+__host__ __device__ inline size_t warp_flag_words(size_t N, size_t tiles) { return 8 * (N / 32 + tiles + 2); }
+
+// Per-Gaussian gradient accumulator filled by the backward render (one RED.ADD per value and (warp, list entry) visit)
+// and consumed by the backward preprocess: 12 floats = 48 bytes,
+//   0..2 dL_dcolor   3 Su.dx  4 Su.dy  5 Su.dx^2  6 Su.dx.dy  7 Su.dy^2  8 Su   (u = G * dL_dalpha per pixel; d = centre - pixel)
+constexpr int ACC_FLOATS = 12;
+
 struct RenderArgs {
 	int W, H, grid_x, grid_y;
 	const uint2* ranges;        // [tiles]
@@ -41,14 +50,12 @@ struct RenderArgs {
 	const float* bg;            // [3]
 	float* final_T;             // [H*W]
 	uint32_t* n_contrib;        // [H*W]
-	uint32_t* tile_max_contrib; // [tiles] max n_contrib over the tile's pixels (written by forward, read by backward)
-	uint8_t* pair_flags;        // [N] sorted order: bit w set if warp w's 8x4 pixel block of the tile blended this pair (fwd writes, bwd reads)
+	uint32_t* warp_flags;       // [warp_flag_words(N, tiles)] fwd writes, bwd reads
 	float* out_color;           // [3,H,W]
 	float* out_depth;           // [H,W]
 	// backward only
 	const float* dL_dpix;       // [3,H,W]
-	const uint32_t* sorted_emit;// [N] emission index of each sorted entry
-	float* partial;             // [N, PARTIAL_FLOATS] indexed by emission index
+	float* grad_acc;            // [P, ACC_FLOATS], zero on entry
 	int variant;                // staging mode, see render_common.cuh
 };
 int launch_render_fwd(cudaStream_t, const RenderArgs&);
@@ -63,9 +70,8 @@ struct PreprocessBwdArgs {
 	int accumulate;           // 1: += into the parameter-gradient buffers, untouched where radii == 0
 	const int* radii;
 	const uint8_t* clamped;
-	const uint32_t* tiles_touched;
-	const uint32_t* dup_off;
-	const float* partial;
+	const SplatRec* rec;      // [P] projected records (conic, opacity)
+	const float* grad_acc;    // [P, ACC_FLOATS] from the backward render
 	float *dL_dmean2D /*[P,3]*/, *dL_dconic /*[P,4] or null*/, *dL_dopacity /*[P]*/, *dL_dcolor /*[P,3]*/, *dL_dmean3D /*[P,3]*/,
 		*dL_dcov3D /*[P,6]*/, *dL_dsh /*[P,M,3]*/, *dL_dscale /*[P,3]*/, *dL_drot /*[P,4]*/;
 };

@@ -1,12 +1,11 @@
-// Backward preprocess, fused: per-Gaussian gather of the render partials, conic -> 2D covariance -> 3D covariance /
-// mean gradient, projection gradient, SH gradient, scale / rotation gradient, and the zero fill of everything a
-// culled Gaussian does not touch.  Replaces computeCov2DCUDA (reference backward.cu:133-264), preprocessCUDA
+// Backward preprocess, fused: moments -> conic / screen-mean / opacity gradient, conic -> 2D covariance -> 3D
+// covariance / mean gradient, projection gradient, SH gradient, scale / rotation gradient, and the zero fill of
+// everything an untouched Gaussian leaves.  Replaces computeCov2DCUDA (reference backward.cu:133-264), preprocessCUDA
 // backward (:336-386) with its SH (:9-128) and cov3D (:268-331) device functions, and the nine torch::zeros fills of
 // rasterize_points.cu:145-153 (every output element is written exactly once here instead).
 //
-// One thread per Gaussian.  The partials of a Gaussian are contiguous (emission order), so the gather is a short
-// sequential read; there are no atomics, hence the result is deterministic.  Gradients only need 1e-4 relative
-// agreement with the reference (its own atomics are unordered), so this file uses plain float expressions.
+// One thread per Gaussian.  Gradients only need 1e-4 relative agreement with the reference (its own atomics are
+// unordered), so this file uses plain float expressions.
 #include "common.cuh"
 #include "kernels.cuh"
 
@@ -23,14 +22,15 @@ constexpr int PB_THREADS = 128;
 constexpr int PB_WARPS = PB_THREADS / 32;
 constexpr int SH_FLOATS = 48;            // 16 coefficients x 3 channels (the staged fast path needs M == 16)
 constexpr int SH_STRIDE = SH_FLOATS + 1; // +1 float: a lane walking its own row is bank-conflict free
-constexpr int PCHUNK = 128;              // (tile, Gaussian) partials staged per warp and round: 128 * 40 B = 5 KB
 
-// One warp handles 32 consecutive Gaussians.  Everything that is wide per Gaussian moves through a per-warp shared
-// buffer with fully coalesced global accesses:
-//   * the gradient partials of the warp's Gaussians are ONE contiguous span (slots are assigned in index order), read
-//     in chunks of PCHUNK entries, each lane then sums its own entries in slot order (deterministic);
-//   * the 32 SH rows (6 KB contiguous) are read as float4, each lane works on its row in shared memory, and the 32
-//     dL_dsh rows go back as float4 (STAGED; the plain per-thread path remains for M != 16 or unaligned pointers).
+// One warp handles 32 consecutive Gaussians.  The render gradients arrive as one 48-byte accumulator record per
+// Gaussian (kernels.cuh: colour sums and the moments of u = G * dL_dalpha), read as three float4; the conic / mean /
+// opacity gradients of reference backward.cu:519-544 are those moments times per-Gaussian constants.  A Gaussian
+// whose record is all zero received no gradient from any pixel: every output of it is zero (the reference computes
+// the same zeros the long way), so it is treated like a culled one — no SH row is read for it, and in accumulate mode
+// nothing is written.  The 32 SH rows (6 KB contiguous) are read as float4, each lane works on its row in shared
+// memory, and the 32 dL_dsh rows go back as float4 (STAGED; the plain per-thread path remains for M != 16 or
+// unaligned pointers).
 template <bool STAGED>
 __global__ void __launch_bounds__(PB_THREADS) preprocess_bwd_kernel(PreprocessBwdArgs a)
 {
@@ -43,36 +43,33 @@ __global__ void __launch_bounds__(PB_THREADS) preprocess_bwd_kernel(PreprocessBw
 	const bool valid = idx < a.P;
 	const int nvalid = min(32, a.P - warp_base);
 	const size_t i3 = 3 * (size_t)(valid ? idx : 0);
-	const bool visible = valid && a.radii[idx] > 0;
-	const unsigned vismask = __ballot_sync(FULL, visible);
 	// accumulate mode (multi-view batches, see rr_backward flags): parameter gradients are added to what the buffers
-	// hold and a Gaussian this view does not see is not touched at all; otherwise every element is overwritten.
+	// hold and a Gaussian this view does not touch is not touched at all; otherwise every element is overwritten.
 	const bool acc = a.accumulate != 0;
 	auto put1 = [acc](float* p, float v) { *p = acc ? *p + v : v; };
 
-	// ---- gather the (tile, Gaussian) partials ----
+	// ---- the render gradients of this Gaussian ----
 	float g[9];
 	#pragma unroll
 	for (int k = 0; k < 9; k++) g[k] = 0.0f;
-	if (vismask != 0) {
-		const uint32_t off = valid ? a.dup_off[idx] : 0u;
-		const uint32_t cnt = visible ? a.tiles_touched[idx] : 0u;
-		const uint32_t span0 = __shfl_sync(FULL, off, 0);
-		const uint32_t span1 = __shfl_sync(FULL, off + cnt, nvalid - 1);   // slot offsets are an exclusive scan in index order
-		for (uint32_t c0 = span0; c0 < span1; c0 += PCHUNK) {
-			const uint32_t nent = min((uint32_t)PCHUNK, span1 - c0);
-			const float2* __restrict__ src = reinterpret_cast<const float2*>(a.partial + (size_t)c0 * PARTIAL_FLOATS);
-			for (uint32_t i = lane; i < nent * (PARTIAL_FLOATS / 2); i += 32) reinterpret_cast<float2*>(sb)[i] = __ldg(src + i);
-			__syncwarp();
-			const uint32_t lo = max(off, c0), hi = min(off + cnt, c0 + nent);
-			for (uint32_t k = lo; k < hi; k++) {
-				const float2* __restrict__ p = reinterpret_cast<const float2*>(sb + (k - c0) * PARTIAL_FLOATS);
-				const float2 p0 = p[0], p1 = p[1], p2 = p[2], p3 = p[3], p4 = p[4];
-				g[0] += p0.x; g[1] += p0.y; g[2] += p1.x; g[3] += p1.y; g[4] += p2.x; g[5] += p2.y; g[6] += p3.x; g[7] += p3.y; g[8] += p4.x;
-			}
-			__syncwarp();
+	bool visible = valid && a.radii[idx] > 0;
+	if (visible) {
+		const float4* __restrict__ ap = reinterpret_cast<const float4*>(a.grad_acc) + (size_t)idx * (ACC_FLOATS / 4);
+		const float4 m0 = __ldg(ap), m1 = __ldg(ap + 1), m2 = __ldg(ap + 2);
+		visible = (m0.x != 0.0f) | (m0.y != 0.0f) | (m0.z != 0.0f) | (m0.w != 0.0f) | (m1.x != 0.0f) | (m1.y != 0.0f) | (m1.z != 0.0f) | (m1.w != 0.0f) | (m2.x != 0.0f);
+		if (visible) {
+			const float4* __restrict__ rp = reinterpret_cast<const float4*>(a.rec) + (size_t)idx * 3;
+			const float4 ra = __ldg(rp), rb = __ldg(rp + 1);         // ra = { pix.xy, conic.x, conic.y }, rb = { conic.z, opacity, .. }
+			const float A = ra.z, B = ra.w, C = rb.x, o = rb.y;
+			const float Sx = m0.w, Sy = m1.x, Sxx = m1.y, Sxy = m1.z, Syy = m1.w, S0 = m2.x;
+			g[0] = m0.x; g[1] = m0.y; g[2] = m0.z;
+			g[3] = -o * (0.5f * a.W) * (A * Sx + B * Sy);           // dL_dmean2D.x (backward.cu:519-527, 535)
+			g[4] = -o * (0.5f * a.H) * (C * Sy + B * Sx);           // dL_dmean2D.y
+			g[5] = -0.5f * o * Sxx; g[6] = -0.5f * o * Sxy; g[7] = -0.5f * o * Syy;   // dL_dconic .x .y .w (backward.cu:539-541)
+			g[8] = S0;                                               // dL_dopacity (backward.cu:544)
 		}
 	}
+	const unsigned vismask = __ballot_sync(FULL, visible);
 	if (valid) {
 		a.dL_dmean2D[i3] = g[3]; a.dL_dmean2D[i3 + 1] = g[4]; a.dL_dmean2D[i3 + 2] = 0.0f;
 		if (a.dL_dconic) reinterpret_cast<float4*>(a.dL_dconic)[idx] = make_float4(g[5], g[6], 0.0f, g[7]);

@@ -1,17 +1,21 @@
-// Backward tile renderer: back-to-front replay of each tile's list, producing one gradient partial per
-// (tile, Gaussian) duplicate.  Replaces renderCUDA<3> backward (reference backward.cu:389-547), whose 9 global float
-// atomics per contributing (pixel, Gaussian) pair serialise in L2 on a single address per Gaussian.
+// Backward tile renderer: each WARP independently replays, back to front, exactly the list entries its 8x4 pixel
+// block blended in the forward, and adds one warp-reduced gradient record per visit to the Gaussian's accumulator.
+// Replaces renderCUDA<3> backward (reference backward.cu:389-547), whose 9 global float atomics per contributing
+// (pixel, Gaussian) pair serialise in L2 on a single address per Gaussian.
 //
 // B200 design:
-//  * same TMA-staged list walk as the forward (render_fwd.cu), in reverse order, starting at the tile's deepest
-//    contributor (tile_max_contrib, recorded by the forward); each warp visits exactly the pairs its 8x4 pixels blended
-//    in the forward (one flag byte per pair written by the forward) — no culling arithmetic, no wasted pairs;
-//  * each lane forms the 9 per-pair terms for its pixel exactly as the reference does; the warp then reduces them with
-//    a halving butterfly (8 values in 4+2+1+1+1 shuffles, the 9th in 5) — skipped when no lane contributed;
-//  * the 8 warps' sums meet in a shared-memory slab (plain stores, a per-warp bitmask says which rows are live) and
-//    ONE 40-byte partial per (tile, Gaussian) is stored to global memory at the duplicate's emission index, so the
-//    partials of one Gaussian are contiguous for the per-Gaussian gather in preprocess_bwd.cu.
-//  No atomics anywhere: the backward is deterministic (bit-reproducible run to run), unlike the reference.
+//  * no CTA-wide coupling at all: the forward leaves one bit per (list entry, warp) ("this warp blended the entry",
+//    kernels.cuh); a warp reads its own bit words, turns them into a descending visit list, and walks it.  Warps that
+//    own saturated or empty pixel blocks finish at once; there is no __syncthreads in the kernel.
+//  * the 48-byte records of the next 32 visits are gathered straight from the per-Gaussian record array (L2 resident:
+//    48 MB at 1M Gaussians) by 32 per-lane 1-D TMA bulk copies onto a per-warp mbarrier, double buffered, while the
+//    current 32 visits are processed; Gaussian ids are prefetched one chunk further ahead.
+//  * each lane forms the terms of its pixel as the reference does (backward.cu:481-544), but accumulates the MOMENTS
+//    u, u.dx, u.dy, u.dx^2, u.dx.dy, u.dy^2 of u = G * dL_dalpha instead of the five conic / mean products — they are
+//    linear in the per-Gaussian constants (conic, opacity), which preprocess_bwd.cu applies once per Gaussian;
+//  * the warp reduces the 9 values with a halving butterfly (8 values in 4+2+1+1+1 shuffles, the 9th in 5) and issues
+//    ONE predicated RED.ADD.F32 (9 active lanes, one 48-byte accumulator record): a single global accumulation per
+//    (warp, Gaussian) visit instead of 9 atomics per pixel.
 #include "common.cuh"
 #include "kernels.cuh"
 #include "render_common.cuh"
@@ -20,8 +24,9 @@ namespace rr {
 
 namespace {
 
-constexpr int BWD_BATCH = 64;
 constexpr int NV = 9;
+constexpr int LIST_WORDS = 16;                  // flag words (of 32 list entries) turned into a visit list per round
+constexpr int LIST_CAP = LIST_WORDS * 32;
 
 // Sum v[0..8] over the 32 lanes.  On return lane L with (L & 3) == 0 holds in `y` the total of value
 // k = 4*bit4(L) + 2*bit3(L) + bit2(L); every lane holds the total of v[8] in `z`.
@@ -50,14 +55,13 @@ __device__ __forceinline__ void warp_reduce9(const float (&v)[NV], int lane, flo
 	for (int o = 16; o >= 1; o >>= 1) z += __shfl_xor_sync(FULL, z, o);
 }
 
-template <int MODE>
+template <bool USE_TMA>
 __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a)
 {
-	constexpr bool USE_TMA = StageMode<MODE>::tma;
-	__shared__ __align__(128) float4 s_rec[STAGES][BWD_BATCH * 3];
-	__shared__ __align__(8) uint64_t s_full[STAGES];
-	__shared__ float s_slab[RENDER_WARPS][BWD_BATCH * NV];
-	__shared__ uint8_t s_flags[2][BWD_BATCH];     // [batch parity] the forward's "which warps blended this pair" byte
+	__shared__ __align__(128) float4 s_rec[RENDER_WARPS][2][32 * 3];   // per warp, double buffered: 32 records of 48 B
+	__shared__ __align__(8) uint2 s_meta[RENDER_WARPS][2][32];         // { Gaussian id, list position } of each staged visit
+	__shared__ uint16_t s_pos[RENDER_WARPS][LIST_CAP];                  // visit list of the round (positions relative to the round's first entry, descending)
+	__shared__ __align__(8) uint64_t s_bar[RENDER_WARPS][2];
 
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 	const int tile = blockIdx.y * a.grid_x + blockIdx.x;
@@ -69,132 +73,119 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 
 	const uint2 range = a.ranges[tile];
 	const int n = (int)(range.y - range.x);
-	const int m = min(n, (int)a.tile_max_contrib[tile]);        // entries [m, n) contributed to no pixel
-	const int nbatches = (m + BWD_BATCH - 1) / BWD_BATCH;
-	const float4* __restrict__ src = reinterpret_cast<const float4*>(a.packed) + (size_t)range.x * 3;
-	const float4* __restrict__ grec = reinterpret_cast<const float4*>(a.rec);
-	const uint32_t* __restrict__ ids = a.point_list + range.x;
-	const uint32_t* __restrict__ emit = a.sorted_emit + range.x;
-	const uint8_t* __restrict__ flags = a.pair_flags + range.x;
-
-	// batch b covers local indices [lo_b, hi_b), hi_b = m - b*BWD_BATCH (back to front)
-	if (tid == 0 && USE_TMA) {
-		for (int s = 0; s < STAGES; s++) mbar_init(&s_full[s], 1);
-		mbar_fence_init();
-	}
-	if (tid < BWD_BATCH && nbatches > 0) {
-		const int lo0 = max(0, m - BWD_BATCH);
-		s_flags[0][tid] = (lo0 + tid < m) ? flags[lo0 + tid] : (uint8_t)0;
-	}
-	__syncthreads();
-	if (USE_TMA && warp == 0) {
-		for (int b = 0; b < STAGES && b < nbatches; b++) {
-			const int hi = m - b * BWD_BATCH, lo = max(0, hi - BWD_BATCH);
-			stage_fill_async<MODE>(&s_rec[b][0], &s_full[b], src, grec, ids, lo, hi - lo, lane);
-		}
-	}
-
-	// duplicates behind the deepest contributor get zero partials (one thread per pair: one slot load, five 8-byte stores)
-	for (int e = m + tid; e < n; e += RENDER_THREADS) {
-		float2* __restrict__ p = reinterpret_cast<float2*>(a.partial + (size_t)__ldg(emit + e) * PARTIAL_FLOATS);
-		#pragma unroll
-		for (int k = 0; k < PARTIAL_FLOATS / 2; k++) p[k] = make_float2(0.0f, 0.0f);
-	}
-
 	const size_t pid = (size_t)a.W * pix_y + pix_x, HW = (size_t)a.H * a.W;
+	const uint32_t last_contributor = inside ? a.n_contrib[pid] : 0u;
+	const uint32_t wmax = __reduce_max_sync(FULL, last_contributor);
+	if (wmax == 0 || n == 0) return;             // warp-uniform: nothing was blended into this warp's pixels
+
 	const float T_final = inside ? a.final_T[pid] : 0.0f;
 	float T = T_final;
-	const int last_contributor = inside ? (int)a.n_contrib[pid] : 0;
 	float dLp0 = 0, dLp1 = 0, dLp2 = 0;
 	if (inside) { dLp0 = a.dL_dpix[pid]; dLp1 = a.dL_dpix[HW + pid]; dLp2 = a.dL_dpix[2 * HW + pid]; }
 	float bg_dot_dpixel = 0;
 	bg_dot_dpixel += a.bg[0] * dLp0; bg_dot_dpixel += a.bg[1] * dLp1; bg_dot_dpixel += a.bg[2] * dLp2;
+	const float neg_Tf_bg = -T_final * bg_dot_dpixel;
 	float ar0 = 0, ar1 = 0, ar2 = 0, lc0 = 0, lc1 = 0, lc2 = 0, last_alpha = 0;
-	const float ddelx_dx = 0.5f * a.W, ddely_dy = 0.5f * a.H;
 
-	for (int b = 0; b < nbatches; b++) {
-		const int s = b % STAGES;
-		const int hi = m - b * BWD_BATCH, lo = max(0, hi - BWD_BATCH), cnt = hi - lo;
-		if (USE_TMA) {
-			mbar_wait(&s_full[s], (uint32_t)(b / STAGES) & 1u);
-		} else {
-			stage_fill_sync<MODE>(&s_rec[s][0], src, grec, ids, lo, cnt, tid);
-			__syncthreads();
-		}
-		const float4* __restrict__ rec = s_rec[s];
-		// the pairs this warp's 8x4 pixels blended in the forward, as a 64-bit mask over the batch
-		const uint8_t* __restrict__ fl = s_flags[b & 1];
-		uint64_t surv = (uint64_t)__ballot_sync(FULL, (fl[lane] >> warp) & 1) | ((uint64_t)__ballot_sync(FULL, (fl[lane + 32] >> warp) & 1) << 32);
-		while (surv) {
-			const int e = 63 - __clzll((long long)surv);
-			surv ^= 1ull << e;
-			const float4 ra = rec[e * 3], rb = rec[e * 3 + 1], rc = rec[e * 3 + 2];
-			float v[NV];
-			#pragma unroll
-			for (int i = 0; i < NV; i++) v[i] = 0.0f;
-			if (lo + e < last_contributor) {
+	uint64_t* bar = s_bar[warp];
+	if (USE_TMA) {
+		if (lane == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_fence_init(); }
+		__syncwarp();
+	}
+	// which lane adds which reduced value: lanes 0,4,..,28 hold values 0..7 (see warp_reduce9), lane 1 adds the 9th
+	const int kslot = (lane & 3) == 0 ? ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1) : (lane == 1 ? 8 : -1);
+
+	const int ngroups = (n + 31) >> 5;
+	const uint32_t* __restrict__ wf = a.warp_flags + 8ull * ((size_t)(range.x >> 5) + (size_t)tile) + (size_t)warp * ngroups;
+	const uint32_t* __restrict__ ids = a.point_list + range.x;
+	const float4* __restrict__ grec = reinterpret_cast<const float4*>(a.rec);
+	const int nwords = (int)((wmax + 31u) >> 5);
+	uint32_t q = 0;                               // chunks staged so far by this warp: buffer = q & 1, mbarrier parity = (q >> 1) & 1
+
+	for (int wbase = ((nwords - 1) / LIST_WORDS) * LIST_WORDS; wbase >= 0; wbase -= LIST_WORDS) {
+		// ---- visit list of this round: set bits of words [wbase, wbase + LIST_WORDS), highest list entry first ----
+		const int wi = wbase + lane;
+		uint32_t word = (lane < LIST_WORDS && wi < nwords) ? __ldg(wf + wi) : 0u;
+		const int cnt = __popc(word);
+		int inc = cnt;                             // inclusive sum over lanes >= this one
+		#pragma unroll
+		for (int o = 1; o < LIST_WORDS; o <<= 1) { const int t = __shfl_down_sync(FULL, inc, o); if (lane + o < 32) inc += t; }
+		const int total = __shfl_sync(FULL, inc, 0);
+		if (total == 0) continue;
+		int at = inc - cnt;
+		while (word) { const int bit = 31 - __clz(word); word ^= 1u << bit; s_pos[warp][at++] = (uint16_t)(lane * 32 + bit); }
+		__syncwarp();
+		const uint32_t ebase = (uint32_t)wbase * 32u;
+		const int nch = (total + 31) >> 5;
+
+		auto load_gid = [&](int k) -> uint32_t {
+			const int i = k * 32 + lane;
+			return i < total ? __ldg(ids + ebase + s_pos[warp][i]) : 0u;
+		};
+		// stage chunk k of the round into buffer qq & 1
+		auto issue = [&](int k, uint32_t qq, uint32_t gid) {
+			const int buf = (int)(qq & 1u);
+			const int cc = min(32, total - k * 32);
+			if (lane < cc) s_meta[warp][buf][lane] = make_uint2(gid, ebase + s_pos[warp][k * 32 + lane]);
+			if (USE_TMA) {
+				if (lane == 0) mbar_arrive_expect_tx(&bar[buf], (uint32_t)cc * (uint32_t)sizeof(SplatRec));
+				__syncwarp();
+				if (lane < cc) bulk_g2s(&s_rec[warp][buf][lane * 3], grec + (size_t)gid * 3, (uint32_t)sizeof(SplatRec), &bar[buf]);
+			} else if (lane < cc) {
+				const float4 r0 = __ldg(grec + (size_t)gid * 3), r1 = __ldg(grec + (size_t)gid * 3 + 1), r2 = __ldg(grec + (size_t)gid * 3 + 2);
+				s_rec[warp][buf][lane * 3] = r0; s_rec[warp][buf][lane * 3 + 1] = r1; s_rec[warp][buf][lane * 3 + 2] = r2;
+			}
+		};
+
+		uint32_t gid_next = load_gid(0);
+		issue(0, q, gid_next);
+		gid_next = nch > 1 ? load_gid(1) : 0u;
+		for (int k = 0; k < nch; k++, q++) {
+			if (k + 1 < nch) {
+				issue(k + 1, q + 1, gid_next);
+				if (k + 2 < nch) gid_next = load_gid(k + 2);
+			}
+			const int buf = (int)(q & 1u);
+			if (USE_TMA) mbar_wait(&bar[buf], (q >> 1) & 1u);
+			__syncwarp();
+			const float4* __restrict__ rec = s_rec[warp][buf];
+			const int cc = min(32, total - k * 32);
+			for (int kk = 0; kk < cc; kk++) {
+				const uint2 mt = s_meta[warp][buf][kk];
+				const float4 ra = rec[kk * 3], rb = rec[kk * 3 + 1], rc = rec[kk * 3 + 2];
 				const float dx = __fsub_rn(ra.x, pxf), dy = __fsub_rn(ra.y, pyf);
-				const float q = __fmaf_rn(dx, __fmul_rn(dx, ra.z), __fmul_rn(dy, __fmul_rn(dy, rb.x)));
-				const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(dy, __fmul_rn(dx, ra.w)));
-				if (!(power > 0.0f)) {
-					const float G = expf(power);
-					const float alpha = fminf(0.99f, __fmul_rn(rb.y, G));
-					if (!(alpha < 1.0f / 255.0f)) {
-						float inv_1ma;      // 1/(1-alpha), 1-alpha in [0.01, 1): the approximate reciprocal (1 ulp) is ample for 1e-4 gradients
-						asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv_1ma) : "f"(1.f - alpha));
-						T = T * inv_1ma;
-						const float dchannel_dcolor = alpha * T;
-						const float one_m_la = 1.f - last_alpha;
-						ar0 = last_alpha * lc0 + one_m_la * ar0; lc0 = rb.z;
-						ar1 = last_alpha * lc1 + one_m_la * ar1; lc1 = rb.w;
-						ar2 = last_alpha * lc2 + one_m_la * ar2; lc2 = rc.x;
-						float dL_dalpha = (rb.z - ar0) * dLp0;
-						dL_dalpha += (rb.w - ar1) * dLp1;
-						dL_dalpha += (rc.x - ar2) * dLp2;
-						v[0] = dchannel_dcolor * dLp0; v[1] = dchannel_dcolor * dLp1; v[2] = dchannel_dcolor * dLp2;
-						dL_dalpha *= T;
-						last_alpha = alpha;
-						dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
-						const float dL_dG = rb.y * dL_dalpha;
-						const float gdx = G * dx, gdy = G * dy;
-						const float dG_ddelx = -gdx * ra.z - gdy * ra.w;
-						const float dG_ddely = -gdy * rb.x - gdx * ra.w;
-						v[3] = dL_dG * dG_ddelx * ddelx_dx;
-						v[4] = dL_dG * dG_ddely * ddely_dy;
-						v[5] = -0.5f * gdx * dx * dL_dG;
-						v[6] = -0.5f * gdx * dy * dL_dG;
-						v[7] = -0.5f * gdy * dy * dL_dG;
-						v[8] = G * dL_dalpha;
-					}
+				const float qd = __fmaf_rn(dx, __fmul_rn(dx, ra.z), __fmul_rn(dy, __fmul_rn(dy, rb.x)));
+				const float power = __fmaf_rn(qd, -0.5f, -__fmul_rn(dy, __fmul_rn(dx, ra.w)));
+				const float G = expf(fminf(power, 0.0f));
+				const float alpha = fminf(0.99f, __fmul_rn(rb.y, G));
+				const bool live = !(power > 0.0f) && !(alpha < 1.0f / 255.0f) && mt.y < last_contributor;
+				float dcdc = 0.0f, u = 0.0f;
+				if (live) {
+					float inv_1ma;      // 1/(1-alpha), 1-alpha in [0.01, 1): the approximate reciprocal (1 ulp) is ample for 1e-4 gradients
+					asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv_1ma) : "f"(1.f - alpha));
+					T = T * inv_1ma;
+					dcdc = alpha * T;
+					const float one_m_la = 1.f - last_alpha;
+					ar0 = last_alpha * lc0 + one_m_la * ar0; lc0 = rb.z;
+					ar1 = last_alpha * lc1 + one_m_la * ar1; lc1 = rb.w;
+					ar2 = last_alpha * lc2 + one_m_la * ar2; lc2 = rc.x;
+					float dL_dalpha = (rb.z - ar0) * dLp0;
+					dL_dalpha += (rb.w - ar1) * dLp1;
+					dL_dalpha += (rc.x - ar2) * dLp2;
+					dL_dalpha = dL_dalpha * T + neg_Tf_bg * inv_1ma;
+					last_alpha = alpha;
+					u = G * dL_dalpha;
 				}
+				float v[NV];
+				v[0] = dcdc * dLp0; v[1] = dcdc * dLp1; v[2] = dcdc * dLp2;
+				v[3] = u * dx; v[4] = u * dy;
+				v[5] = v[3] * dx; v[6] = v[3] * dy; v[7] = v[4] * dy;
+				v[8] = u;
+				float y, z;
+				warp_reduce9(v, lane, y, z);
+				if (kslot >= 0) atomicAdd(a.grad_acc + (size_t)mt.x * ACC_FLOATS + kslot, lane == 1 ? z : y);
 			}
-			float y, z;
-			warp_reduce9(v, lane, y, z);
-			if ((lane & 3) == 0) s_slab[warp][e * NV + ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1)] = y;
-			if (lane == 1) s_slab[warp][e * NV + 8] = z;
-		}
-		__syncthreads();
-		// combine the warps that blended each pair and store one partial per (tile, Gaussian) at its slot
-		for (int t = tid; t < cnt * PARTIAL_FLOATS; t += RENDER_THREADS) {
-			const int e = t / PARTIAL_FLOATS, k = t - e * PARTIAL_FLOATS;
-			float sum = 0.0f;
-			if (k < NV) {
-				const uint32_t f = fl[e];
-				#pragma unroll
-				for (int w = 0; w < RENDER_WARPS; w++) if ((f >> w) & 1u) sum += s_slab[w][e * NV + k];
-			}
-			a.partial[(size_t)emit[lo + e] * PARTIAL_FLOATS + k] = sum;
-		}
-		// flags of the next batch
-		if (b + 1 < nbatches && tid < BWD_BATCH) {
-			const int nhi = m - (b + 1) * BWD_BATCH, nlo = max(0, nhi - BWD_BATCH);
-			s_flags[(b + 1) & 1][tid] = (nlo + tid < nhi) ? flags[nlo + tid] : (uint8_t)0;
-		}
-		__syncthreads();
-		if (USE_TMA && warp == 0 && b + STAGES < nbatches) {
-			const int nb = b + STAGES;
-			const int nhi = m - nb * BWD_BATCH, nlo = max(0, nhi - BWD_BATCH);
-			stage_fill_async<MODE>(&s_rec[s][0], &s_full[s], src, grec, ids, nlo, nhi - nlo, lane);
+			__syncwarp();      // every lane is done with this buffer before the next iteration refills it
 		}
 	}
 }
@@ -204,12 +195,8 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 int launch_render_bwd(cudaStream_t stream, const RenderArgs& a)
 {
 	const dim3 grid(a.grid_x, a.grid_y);
-	switch (a.variant) {
-	case MODE_PACKED_LDG: count_launch(), render_bwd_kernel<MODE_PACKED_LDG><<<grid, RENDER_THREADS, 0, stream>>>(a); break;
-	case MODE_PACKED_TMA: count_launch(), render_bwd_kernel<MODE_PACKED_TMA><<<grid, RENDER_THREADS, 0, stream>>>(a); break;
-	case MODE_GATHER_LDG: count_launch(), render_bwd_kernel<MODE_GATHER_LDG><<<grid, RENDER_THREADS, 0, stream>>>(a); break;
-	default: count_launch(), render_bwd_kernel<MODE_GATHER_TMA><<<grid, RENDER_THREADS, 0, stream>>>(a); break;
-	}
+	if (a.variant == MODE_PACKED_LDG || a.variant == MODE_GATHER_LDG) count_launch(), render_bwd_kernel<false><<<grid, RENDER_THREADS, 0, stream>>>(a);
+	else count_launch(), render_bwd_kernel<true><<<grid, RENDER_THREADS, 0, stream>>>(a);
 	return check_launch("render_bwd", stream, false);
 }
 

@@ -27,8 +27,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a
 	__shared__ __align__(128) float4 s_rec[STAGES][BATCH * 3];
 	__shared__ __align__(8) uint64_t s_full[STAGES];
 	__shared__ uint8_t s_list[RENDER_WARPS][BATCH];
-	__shared__ __align__(4) uint8_t s_used[2][RENDER_WARPS][BATCH];   // [batch parity]: 1 if the warp blended the entry into at least one pixel
-	__shared__ uint32_t s_max_contrib;
+	__shared__ __align__(4) uint8_t s_used[RENDER_WARPS][BATCH];      // 1 if the warp blended the entry into at least one of its pixels
 
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 	const int tile = blockIdx.y * a.grid_x + blockIdx.x;
@@ -48,13 +47,12 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a
 	const float4* __restrict__ grec = reinterpret_cast<const float4*>(a.rec);
 	const uint32_t* __restrict__ ids = a.point_list + range.x;
 
-	if (tid == 0) {
-		s_max_contrib = 0;
-		if (USE_TMA) {
-			for (int s = 0; s < STAGES; s++) mbar_init(&s_full[s], 1);
-			mbar_fence_init();
-		}
+	if (tid == 0 && USE_TMA) {
+		for (int s = 0; s < STAGES; s++) mbar_init(&s_full[s], 1);
+		mbar_fence_init();
 	}
+	// this warp's blend-flag words (kernels.cuh): bit j % 32 of word j / 32 = "list entry j was blended into one of my pixels"
+	uint32_t* __restrict__ wflags = a.warp_flags + 8ull * ((size_t)(range.x >> 5) + (size_t)tile) + (size_t)warp * ((n + 31) >> 5);
 	__syncthreads();
 	if (USE_TMA && warp == 0) {
 		for (int b = 0; b < STAGES && b < nbatches; b++)
@@ -70,8 +68,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a
 		const int s = b % STAGES;
 		const int cnt = min(BATCH, n - b * BATCH);
 		// this warp's "used" row for the batch starts from zero (one 4-byte store per lane covers the 128 entries)
-		// (double-buffered by batch parity: the other warps read the previous batch's rows after the barrier below)
-		reinterpret_cast<uint32_t*>(s_used[b & 1][warp])[lane] = 0u;
+		reinterpret_cast<uint32_t*>(s_used[warp])[lane] = 0u;
 		__syncwarp();
 		if (USE_TMA) {
 			mbar_wait(&s_full[s], (uint32_t)(b / STAGES) & 1u);
@@ -147,19 +144,21 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a
 					if ((kk & 7) == 7 && __all_sync(FULL, done)) { stop = true; break; }
 				}
 				const unsigned wbits = __reduce_or_sync(FULL, usedbits);
-				if ((wbits >> lane) & 1u) s_used[b & 1][warp][s_list[warp][kc + lane]] = 1;
+				if ((wbits >> lane) & 1u) s_used[warp][s_list[warp][kc + lane]] = 1;
 				if (stop || __all_sync(FULL, done)) break;
 			}
+			// the warp's flag words of this batch (4 words = 128 entries), one 16-byte store; the backward walks exactly these
+			__syncwarp();
+			uint32_t myword = 0;
+			#pragma unroll
+			for (int c = 0; c < BATCH / 32; c++) {
+				const uint32_t wd = __ballot_sync(FULL, s_used[warp][c * 32 + lane] != 0);
+				if (lane == c) myword = wd;
+			}
+			if (lane < BATCH / 32 && lane * 32 < cnt) wflags[b * (BATCH / 32) + lane] = myword;
 		}
 		// every warp is past this stage: it can be refilled; stop early when all 256 pixels are saturated
 		const int all_done = __syncthreads_and(done);
-		// one flag byte per (tile, entry): bit w = warp w blended it.  The backward walks exactly these.
-		if (tid < cnt) {
-			uint32_t f = 0;
-			#pragma unroll
-			for (int w = 0; w < RENDER_WARPS; w++) f |= (uint32_t)s_used[b & 1][w][tid] << w;
-			a.pair_flags[(size_t)range.x + (size_t)b * BATCH + tid] = (uint8_t)f;
-		}
 		if (all_done) { b_exit = b + 1; break; }
 		if (USE_TMA && warp == 0 && b + STAGES < nbatches) {
 			const int nb = b + STAGES;
@@ -181,10 +180,6 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a
 		a.out_color[2 * HW + pid] = __fmaf_rn(T, a.bg[2], C2);
 		a.out_depth[pid] = Dp;
 	}
-	const uint32_t wmax = __reduce_max_sync(FULL, inside ? last_contributor : 0u);
-	if (lane == 0) atomicMax(&s_max_contrib, wmax);
-	__syncthreads();
-	if (tid == 0) a.tile_max_contrib[tile] = s_max_contrib;
 }
 
 }  // namespace

@@ -65,7 +65,7 @@ def test_scratch_sizes_are_monotone_and_aligned(lib):
     assert lib.rr_image_bytes(1920, 1080) >= 8 * 1920 * 1080        # final_T + n_contrib
     n1, n2 = lib.rr_binning_bytes(1000, 1920, 1080), lib.rr_binning_bytes(4_000_000, 1920, 1080)
     assert n2 > n1 and n2 < 120 * 4_000_000
-    assert lib.rr_backward_ws_bytes(1000) >= 1000 * 40
+    assert lib.rr_backward_ws_bytes(1000) >= 1000 * 48
     assert lib.rr_dist2_ws_bytes(5_000_000) < 64 * 5_000_000
     assert lib.rr_sort_ws_bytes(1 << 20, 8, 0, 45) > 0
 
