@@ -1,15 +1,18 @@
 // Forward tile renderer: front-to-back alpha blending of each 16x16 tile's depth-sorted splat list.
 // Replaces renderCUDA<3> forward (reference forward.cu:251-369).
 //
-// B200 design:
-//  * the tile's list is a contiguous span of 48-byte records (packed by pack_kernel), so each batch of 128 splats
-//    is staged into shared memory with ONE cp.async.bulk (TMA) issued by one thread and tracked by an mbarrier,
-//    3 stages deep — no per-thread gathers, no register staging (variant 1; variant 0 uses plain cooperative
-//    float4 loads and exists as a cross-check);
-//  * each warp owns an 8x4 pixel block and first culls the staged batch against that block (one splat per lane,
-//    exact concave-maximum test, see render_common.cuh) and compacts the survivors with ballot/popc, so the blend
-//    loop only visits splats that can reach alpha >= 1/255 somewhere in the warp's pixels;
-//  * warps stop individually once their 32 pixels are saturated; the CTA stops when all 8 warps have.
+// B200 design (one CTA per tile, 8 consumer warps + 1 producer warp, no __syncthreads after the prologue):
+//  * the PRODUCER warp stages the tile's list into a ring of FWD_STAGES shared-memory stages of 128 records (48 B
+//    each) with TMA bulk copies — one 48-byte cp.async.bulk per record, gathered straight from the per-Gaussian record
+//    array (L2 resident) through point_list, 4 per lane and batch, all landing on the stage's `full` mbarrier
+//    (variant 2, default; variant 1 copies a packed span with ONE bulk copy; variants 0 / 3 fill with plain loads and
+//    exist as cross-checks).  A stage is refilled when all 8 consumer warps have arrived on its `empty` mbarrier;
+//  * each CONSUMER warp owns an 8x4 pixel block and runs through the ring at its own pace: it culls a staged batch
+//    against its block (one splat per lane: AABB, then the exact concave-maximum test of render_common.cuh), compacts
+//    the survivors with ballot/popc, and blends only those, so warps that own easy pixels do not wait for the others;
+//  * a warp whose 32 pixels are saturated stops blending and only keeps releasing stages until the producer, which
+//    stops filling once all 8 warps are saturated, raises the stop flag;
+//  * each warp leaves one bit per list entry ("blended into one of my pixels", kernels.cuh) for the backward.
 // The per-pair arithmetic (power, exp, alpha, T test, accumulation) is spelled with explicit-rounding intrinsics in
 // exactly the order of the reference build so final_T, n_contrib and the colours are reproduced bit for bit.
 #include "common.cuh"
@@ -20,17 +23,78 @@ namespace rr {
 
 namespace {
 
+constexpr int FWD_STAGES = 4;
+constexpr int FWD_THREADS = RENDER_THREADS + 32;      // 8 consumer warps + the producer warp
+
+// Producer: fill one stage with `cnt` records starting at list position `first`; completion is signalled on `bar`
+// (count 1: the arrive.expect_tx of lane 0 for the TMA modes, a plain arrive after the stores otherwise).
 template <int MODE>
-__global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a)
+__device__ __forceinline__ void producer_fill(float4* dst, uint64_t* bar, const float4* __restrict__ packed, const float4* __restrict__ rec,
+	const uint32_t* __restrict__ ids, int first, int cnt, int lane)
 {
-	constexpr bool USE_TMA = StageMode<MODE>::tma;
-	__shared__ __align__(128) float4 s_rec[STAGES][BATCH * 3];
-	__shared__ __align__(8) uint64_t s_full[STAGES];
+	if (StageMode<MODE>::tma) {
+		stage_fill_async<MODE>(dst, bar, packed, rec, ids, first, cnt, lane);
+	} else {
+		for (int i = lane; i < cnt * 3; i += 32) {
+			if (MODE == MODE_PACKED_LDG) dst[i] = __ldg(packed + (size_t)first * 3 + i);
+			else { const int e = i / 3; dst[i] = __ldg(rec + (size_t)__ldg(ids + first + e) * 3 + (i - e * 3)); }
+		}
+		__syncwarp();
+		if (lane == 0) mbar_arrive(bar);
+	}
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(FWD_THREADS) render_fwd_kernel(RenderArgs a)
+{
+	__shared__ __align__(128) float4 s_rec[FWD_STAGES][BATCH * 3];
+	__shared__ __align__(8) uint64_t s_full[FWD_STAGES];
+	__shared__ __align__(8) uint64_t s_empty[FWD_STAGES];
 	__shared__ uint8_t s_list[RENDER_WARPS][BATCH];
 	__shared__ __align__(4) uint8_t s_used[RENDER_WARPS][BATCH];      // 1 if the warp blended the entry into at least one of its pixels
+	__shared__ int s_ndone;        // consumer warps whose 32 pixels are all saturated
+	__shared__ int s_nissued;      // batches the producer filled (valid once s_stop is set)
+	__shared__ int s_stop;         // the producer will fill no more stages
 
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 	const int tile = blockIdx.y * a.grid_x + blockIdx.x;
+	const uint2 range = a.ranges[tile];
+	const int n = (int)(range.y - range.x);
+	const int nbatches = (n + BATCH - 1) / BATCH;
+
+	if (tid == 0) {
+		for (int s = 0; s < FWD_STAGES; s++) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], RENDER_WARPS); }
+		s_ndone = 0; s_nissued = 0; s_stop = 0;
+		mbar_fence_init();
+	}
+	__syncthreads();
+
+	if (warp == RENDER_WARPS) {
+		// ------------------------------------------------ producer ------------------------------------------------
+		const float4* __restrict__ src = reinterpret_cast<const float4*>(a.packed) + (size_t)range.x * 3;
+		const float4* __restrict__ grec = reinterpret_cast<const float4*>(a.rec);
+		const uint32_t* __restrict__ ids = a.point_list + range.x;
+		int b = 0;
+		for (; b < nbatches; b++) {
+			const int s = b % FWD_STAGES;
+			if (b >= FWD_STAGES) {
+				mbar_wait(&s_empty[s], (uint32_t)(b / FWD_STAGES - 1) & 1u);       // all 8 warps are past batch b - FWD_STAGES
+				if (*reinterpret_cast<volatile int*>(&s_ndone) == RENDER_WARPS) break;   // every pixel of the tile is saturated
+			}
+			producer_fill<MODE>(&s_rec[s][0], &s_full[s], src, grec, ids, b * BATCH, min(BATCH, n - b * BATCH), lane);
+		}
+		__syncwarp();
+		if (lane == 0) {
+			*reinterpret_cast<volatile int*>(&s_nissued) = b;
+			__threadfence_block();
+			*reinterpret_cast<volatile int*>(&s_stop) = 1;
+			// fills still in flight must land before the CTA (and its shared memory) retires
+			for (int bb = max(0, b - FWD_STAGES); bb < b; bb++) mbar_wait(&s_full[bb % FWD_STAGES], (uint32_t)(bb / FWD_STAGES) & 1u);
+		}
+		return;
+	}
+
+	// ---------------------------------------------------- consumers ----------------------------------------------------
 	int wx, wy, lx, ly;
 	warp_footprint(warp, lane, wx, wy, lx, ly);
 	const int pix_x = blockIdx.x * TILE_X + wx + lx, pix_y = blockIdx.y * TILE_Y + wy + ly;
@@ -39,47 +103,35 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a
 	// rectangle of the warp's pixel centres
 	const float X0 = (float)(blockIdx.x * TILE_X + wx), X1 = X0 + 7.0f;
 	const float Y0 = (float)(blockIdx.y * TILE_Y + wy), Y1 = Y0 + 3.0f;
-
-	const uint2 range = a.ranges[tile];
-	const int n = (int)(range.y - range.x);
-	const int nbatches = (n + BATCH - 1) / BATCH;
-	const float4* __restrict__ src = reinterpret_cast<const float4*>(a.packed) + (size_t)range.x * 3;
-	const float4* __restrict__ grec = reinterpret_cast<const float4*>(a.rec);
-	const uint32_t* __restrict__ ids = a.point_list + range.x;
-
-	if (tid == 0 && USE_TMA) {
-		for (int s = 0; s < STAGES; s++) mbar_init(&s_full[s], 1);
-		mbar_fence_init();
-	}
 	// this warp's blend-flag words (kernels.cuh): bit j % 32 of word j / 32 = "list entry j was blended into one of my pixels"
 	uint32_t* __restrict__ wflags = a.warp_flags + 8ull * ((size_t)(range.x >> 5) + (size_t)tile) + (size_t)warp * ((n + 31) >> 5);
-	__syncthreads();
-	if (USE_TMA && warp == 0) {
-		for (int b = 0; b < STAGES && b < nbatches; b++)
-			stage_fill_async<MODE>(&s_rec[b][0], &s_full[b], src, grec, ids, b * BATCH, min(BATCH, n - b * BATCH), lane);
-	}
+	uint8_t* __restrict__ list = s_list[warp];
+	uint8_t* __restrict__ used = s_used[warp];
 
 	float T = 1.0f, C0 = 0.0f, C1 = 0.0f, C2 = 0.0f, Dp = 0.0f;
 	uint32_t last_contributor = 0;
 	bool done = !inside;
-	int b_exit = nbatches;   // first batch index whose stage was never consumed
+	bool warp_done = __all_sync(FULL, done);
+	if (warp_done && lane == 0) atomicAdd(&s_ndone, 1);
 
 	for (int b = 0; b < nbatches; b++) {
-		const int s = b % STAGES;
-		const int cnt = min(BATCH, n - b * BATCH);
-		// this warp's "used" row for the batch starts from zero (one 4-byte store per lane covers the 128 entries)
-		reinterpret_cast<uint32_t*>(s_used[warp])[lane] = 0u;
-		__syncwarp();
-		if (USE_TMA) {
-			mbar_wait(&s_full[s], (uint32_t)(b / STAGES) & 1u);
-		} else {
-			__syncthreads();
-			stage_fill_sync<MODE>(&s_rec[s][0], src, grec, ids, b * BATCH, cnt, tid);
-			__syncthreads();
-		}
-		const float4* __restrict__ rec = s_rec[s];
-		const bool warp_done = __all_sync(FULL, done);
+		const int s = b % FWD_STAGES;
+		const uint32_t parity = (uint32_t)(b / FWD_STAGES) & 1u;
 		if (!warp_done) {
+			mbar_wait(&s_full[s], parity);       // an unsaturated warp keeps the producer filling
+		} else {
+			// saturated: only release stages, until the producer has stopped and this batch was never filled
+			bool got;
+			while (!(got = mbar_try_wait(&s_full[s], parity))) {
+				if (*reinterpret_cast<volatile int*>(&s_stop) && b >= *reinterpret_cast<volatile int*>(&s_nissued)) break;
+			}
+			if (!got) break;
+		}
+		if (!warp_done) {
+			const int cnt = min(BATCH, n - b * BATCH);
+			const float4* __restrict__ rec = s_rec[s];
+			// this warp's "used" row for the batch starts from zero (one 4-byte store per lane covers the 128 entries)
+			reinterpret_cast<uint32_t*>(used)[lane] = 0u;
 			// stage 1: cheap AABB cull against this warp's 8x4 pixels, one splat per lane, survivors compacted
 			int n1 = 0;
 			for (int c = 0; c < cnt; c += 32) {
@@ -90,7 +142,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a
 					pass = aabb_may_contribute(ra.x, ra.y, rc.z, rc.w, X0, X1, Y0, Y1);
 				}
 				const unsigned m = __ballot_sync(FULL, pass);
-				if (pass) s_list[warp][n1 + __popc(m & lanemask_lt())] = (uint8_t)e;
+				if (pass) list[n1 + __popc(m & lanemask_lt())] = (uint8_t)e;
 				n1 += __popc(m);
 			}
 			__syncwarp();
@@ -101,74 +153,64 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_fwd_kernel(RenderArgs a
 				bool pass = false;
 				int e = 0;
 				if (k < n1) {
-					e = s_list[warp][k];
+					e = list[k];
 					const float4 ra = rec[e * 3], rb = rec[e * 3 + 1];
 					pass = rect_may_contribute(ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, X0, X1, Y0, Y1);
 				}
-				const unsigned m = __ballot_sync(FULL, pass);     // all lanes have consumed their s_list[k] by now
-				if (pass) s_list[warp][nsurv + __popc(m & lanemask_lt())] = (uint8_t)e;
+				const unsigned m = __ballot_sync(FULL, pass);     // all lanes have consumed their list[k] by now
+				if (pass) list[nsurv + __popc(m & lanemask_lt())] = (uint8_t)e;
 				nsurv += __popc(m);
 			}
 			__syncwarp();
-			// blend the survivors, 32 at a time; each lane keeps one "I blended survivor kk" bit per chunk, OR-reduced once per
-			// chunk with redux.sync, and the saturation vote is taken every 8 survivors (a saturated pixel skips the math anyway)
-			for (int kc = 0; kc < nsurv; kc += 32) {
+			// blend the survivors, 32 at a time.  Each lane keeps one "I blended survivor kk" bit per chunk (OR-reduced once
+			// per chunk with redux.sync); the saturation vote is taken every 8 survivors (a saturated pixel is predicated
+			// off anyway).  The body is branch-free: done / culled lanes are masked by predicates.
+			const uint32_t pos1 = (uint32_t)(b * BATCH) + 1u;
+			for (int kc = 0; kc < nsurv && !warp_done; kc += 32) {
 				const int kn = min(32, nsurv - kc);
-				uint32_t usedbits = 0;
-				bool stop = false;
-				for (int kk = 0; kk < kn; kk++) {
-					const int e = s_list[warp][kc + kk];
-					const float4 ra = rec[e * 3], rb = rec[e * 3 + 1], rc = rec[e * 3 + 2];
-					if (!done) {
+				uint32_t usedbits = 0, bit = 1u;
+				for (int k8 = 0; k8 < kn; k8 += 8) {
+					const int n8 = min(8, kn - k8);
+					for (int j = 0; j < n8; j++, bit <<= 1) {
+						const int e = list[kc + k8 + j];
+						const float4 ra = rec[e * 3], rb = rec[e * 3 + 1], rc = rec[e * 3 + 2];
 						const float dx = __fsub_rn(ra.x, pxf), dy = __fsub_rn(ra.y, pyf);
 						const float q = __fmaf_rn(dx, __fmul_rn(dx, ra.z), __fmul_rn(dy, __fmul_rn(dy, rb.x)));
 						const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(dy, __fmul_rn(dx, ra.w)));
-						if (!(power > 0.0f)) {
-							const float alpha = fminf(0.99f, __fmul_rn(rb.y, expf(power)));
-							if (!(alpha < 1.0f / 255.0f)) {
-								const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
-								if (test_T < 0.0001f) {
-									done = true;
-								} else {
-									C0 = __fmaf_rn(T, __fmul_rn(alpha, rb.z), C0);
-									C1 = __fmaf_rn(T, __fmul_rn(alpha, rb.w), C1);
-									C2 = __fmaf_rn(T, __fmul_rn(alpha, rc.x), C2);
-									Dp = __fmaf_rn(T, __fmul_rn(alpha, rc.y), Dp);
-									T = test_T;
-									last_contributor = (uint32_t)(b * BATCH + e + 1);
-									usedbits |= 1u << kk;
-								}
-							}
+						const float alpha = fminf(0.99f, __fmul_rn(rb.y, expf(power)));
+						const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
+						const bool ok = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);     // forward.cu:330-340
+						const bool sat = ok && (test_T < 0.0001f);                               // forward.cu:341-346
+						done = done || sat;
+						if (ok && !sat) {
+							C0 = __fmaf_rn(T, __fmul_rn(alpha, rb.z), C0);
+							C1 = __fmaf_rn(T, __fmul_rn(alpha, rb.w), C1);
+							C2 = __fmaf_rn(T, __fmul_rn(alpha, rc.x), C2);
+							Dp = __fmaf_rn(T, __fmul_rn(alpha, rc.y), Dp);
+							T = test_T;
+							last_contributor = pos1 + (uint32_t)e;
+							usedbits |= bit;
 						}
 					}
-					if ((kk & 7) == 7 && __all_sync(FULL, done)) { stop = true; break; }
+					if (__all_sync(FULL, done)) { warp_done = true; break; }
 				}
 				const unsigned wbits = __reduce_or_sync(FULL, usedbits);
-				if ((wbits >> lane) & 1u) s_used[warp][s_list[warp][kc + lane]] = 1;
-				if (stop || __all_sync(FULL, done)) break;
+				if ((wbits >> lane) & 1u) used[list[kc + lane]] = 1;
 			}
 			// the warp's flag words of this batch (4 words = 128 entries), one 16-byte store; the backward walks exactly these
 			__syncwarp();
 			uint32_t myword = 0;
 			#pragma unroll
 			for (int c = 0; c < BATCH / 32; c++) {
-				const uint32_t wd = __ballot_sync(FULL, s_used[warp][c * 32 + lane] != 0);
+				const uint32_t wd = __ballot_sync(FULL, used[c * 32 + lane] != 0);
 				if (lane == c) myword = wd;
 			}
 			if (lane < BATCH / 32 && lane * 32 < cnt) wflags[b * (BATCH / 32) + lane] = myword;
+			if (warp_done && lane == 0) atomicAdd(&s_ndone, 1);
 		}
-		// every warp is past this stage: it can be refilled; stop early when all 256 pixels are saturated
-		const int all_done = __syncthreads_and(done);
-		if (all_done) { b_exit = b + 1; break; }
-		if (USE_TMA && warp == 0 && b + STAGES < nbatches) {
-			const int nb = b + STAGES;
-			stage_fill_async<MODE>(&s_rec[s][0], &s_full[s], src, grec, ids, nb * BATCH, min(BATCH, n - nb * BATCH), lane);
-		}
-	}
-
-	if (USE_TMA && tid == 0) {
-		// bulk copies already in flight for later stages must land before the CTA (and its shared memory) retires
-		for (int bb = b_exit; bb < nbatches && bb < b_exit + STAGES - 1; bb++) mbar_wait(&s_full[bb % STAGES], (uint32_t)(bb / STAGES) & 1u);
+		// this warp is past the stage: it can be refilled once all 8 have arrived
+		__syncwarp();
+		if (lane == 0) mbar_arrive(&s_empty[s]);
 	}
 
 	if (inside) {
@@ -188,10 +230,10 @@ int launch_render_fwd(cudaStream_t stream, const RenderArgs& a)
 {
 	const dim3 grid(a.grid_x, a.grid_y);
 	switch (a.variant) {
-	case MODE_PACKED_LDG: count_launch(), render_fwd_kernel<MODE_PACKED_LDG><<<grid, RENDER_THREADS, 0, stream>>>(a); break;
-	case MODE_PACKED_TMA: count_launch(), render_fwd_kernel<MODE_PACKED_TMA><<<grid, RENDER_THREADS, 0, stream>>>(a); break;
-	case MODE_GATHER_LDG: count_launch(), render_fwd_kernel<MODE_GATHER_LDG><<<grid, RENDER_THREADS, 0, stream>>>(a); break;
-	default: count_launch(), render_fwd_kernel<MODE_GATHER_TMA><<<grid, RENDER_THREADS, 0, stream>>>(a); break;
+	case MODE_PACKED_LDG: count_launch(), render_fwd_kernel<MODE_PACKED_LDG><<<grid, FWD_THREADS, 0, stream>>>(a); break;
+	case MODE_PACKED_TMA: count_launch(), render_fwd_kernel<MODE_PACKED_TMA><<<grid, FWD_THREADS, 0, stream>>>(a); break;
+	case MODE_GATHER_LDG: count_launch(), render_fwd_kernel<MODE_GATHER_LDG><<<grid, FWD_THREADS, 0, stream>>>(a); break;
+	default: count_launch(), render_fwd_kernel<MODE_GATHER_TMA><<<grid, FWD_THREADS, 0, stream>>>(a); break;
 	}
 	return check_launch("render_fwd", stream, false);
 }

@@ -260,7 +260,7 @@ def test_accumulate_mode_and_multiview_bucket(device):
     for v in range(V):
         fw = mine_forward(sc, cams[v], bg)
         g = mine_backward(fw, sc, cams[v], bg, dp[v])
-        assert eq(res[v].color, fw["color"]) and eq(res[v].dL_dmeans2D, g["dL_dmean2D"])
+        assert eq(res[v].color, fw["color"]) and rel_err(res[v].dL_dmeans2D, g["dL_dmean2D"])[0] < 2e-6
         cur = dict(means3D=g["dL_dmean3D"], sh=g["dL_dsh"], opacity=g["dL_dopacity"], scales=g["dL_dscale"], rotations=g["dL_drot"])
         tot = cur if tot is None else {k: tot[k] + cur[k] for k in cur}
     for k in mv.SEGMENTS:
