@@ -198,7 +198,7 @@ def run_ours(args, rank, world, local):
     # ---------------- end-to-end arm (host buffers -> public API -> host scalar) ----------------
     pinned = [dict(view=c.viewmatrix.pin_memory(), proj=c.projmatrix.pin_memory(), campos=c.campos.pin_memory()) for c in cams_h]
     dev_cam = [dict(view=torch.empty(4, 4, device=dev), proj=torch.empty(4, 4, device=dev), campos=torch.empty(3, device=dev)) for _ in range(VIEWS_PER_STEP)]
-    dev_tgt = [torch.empty(3, H, W, device=dev) for _ in range(VIEWS_PER_STEP)]
+    feed = mv.HostFeed([(3, H, W)] * VIEWS_PER_STEP, dev)     # target images: pinned host -> device on a side stream, overlapped with the renders
     loss_dev = torch.zeros(1, device=dev)
     loss_host = torch.zeros(1).pin_memory()
     h2d = VIEWS_PER_STEP * ((16 + 16 + 3) * 4 + 3 * H * W * 4)
@@ -208,16 +208,16 @@ def run_ours(args, rank, world, local):
     def step_e2e(s):
         ids = views_of(s)
         cams_step = {}
+        feed.stage(targets_h)
         for i, v in enumerate(ids):
             for k in ("view", "proj", "campos"):
                 dev_cam[i][k].copy_(pinned[v][k], non_blocking=True)
-            dev_tgt[i].copy_(targets_h[i], non_blocking=True)
             cams_step[v] = Camera(W, H, cams_h[v].tanfovx, cams_h[v].tanfovy, dev_cam[i]["view"], dev_cam[i]["proj"], dev_cam[i]["campos"])
         slot.clear(); slot.update({v: i for i, v in enumerate(ids)})
         loss_dev.zero_()
 
         def grad_e2e(v, color, depth):
-            d = torch.sub(color, dev_tgt[slot[v]])
+            d = torch.sub(color, feed.wait(slot[v]))
             loss_dev.add_(0.5 * (d * d).sum())
             return d
         bucket.filled = False

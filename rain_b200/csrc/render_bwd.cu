@@ -94,6 +94,8 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 	}
 	// which lane adds which reduced value: lanes 0,4,..,28 hold values 0..7 (see warp_reduce9), lane 1 adds the 9th
 	const int kslot = (lane & 3) == 0 ? ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1) : (lane == 1 ? 8 : -1);
+	const bool adder = kslot >= 0;
+	float* __restrict__ acc_lane = a.grad_acc + (adder ? kslot : 0);
 
 	const int ngroups = (n + 31) >> 5;
 	const uint32_t* __restrict__ wf = a.warp_flags + 8ull * ((size_t)(range.x >> 5) + (size_t)tile) + (size_t)warp * ngroups;
@@ -183,7 +185,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 				v[8] = u;
 				float y, z;
 				warp_reduce9(v, lane, y, z);
-				if (kslot >= 0) atomicAdd(a.grad_acc + (size_t)mt.x * ACC_FLOATS + kslot, lane == 1 ? z : y);
+				if (adder) atomicAdd(acc_lane + mt.x * (uint32_t)ACC_FLOATS, lane == 1 ? z : y);
 			}
 			__syncwarp();      // every lane is done with this buffer before the next iteration refills it
 		}

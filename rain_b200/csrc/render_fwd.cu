@@ -6,12 +6,13 @@
 //    each) with TMA bulk copies — one 48-byte cp.async.bulk per record, gathered straight from the per-Gaussian record
 //    array (L2 resident) through point_list, 4 per lane and batch, all landing on the stage's `full` mbarrier
 //    (variant 2, default; variant 1 copies a packed span with ONE bulk copy; variants 0 / 3 fill with plain loads and
-//    exist as cross-checks).  A stage is refilled when all 8 consumer warps have arrived on its `empty` mbarrier;
+//    exist as cross-checks).  A stage is refilled when every consumer warp has released it: each warp publishes the
+//    number of batches it is done with in a shared word (release store), the producer polls the minimum;
 //  * each CONSUMER warp owns an 8x4 pixel block and runs through the ring at its own pace: it culls a staged batch
 //    against its block (one splat per lane: AABB, then the exact concave-maximum test of render_common.cuh), compacts
 //    the survivors with ballot/popc, and blends only those, so warps that own easy pixels do not wait for the others;
-//  * a warp whose 32 pixels are saturated stops blending and only keeps releasing stages until the producer, which
-//    stops filling once all 8 warps are saturated, raises the stop flag;
+//  * a warp whose 32 pixels are saturated publishes "released everything" and leaves at once; the producer stops
+//    filling when all 8 warps have;
 //  * each warp leaves one bit per list entry ("blended into one of my pixels", kernels.cuh) for the backward.
 // The per-pair arithmetic (power, exp, alpha, T test, accumulation) is spelled with explicit-rounding intrinsics in
 // exactly the order of the reference build so final_T, n_contrib and the colours are reproduced bit for bit.
@@ -49,12 +50,9 @@ __global__ void __launch_bounds__(FWD_THREADS) render_fwd_kernel(RenderArgs a)
 {
 	__shared__ __align__(128) float4 s_rec[FWD_STAGES][BATCH * 3];
 	__shared__ __align__(8) uint64_t s_full[FWD_STAGES];
-	__shared__ __align__(8) uint64_t s_empty[FWD_STAGES];
+	__shared__ int s_released[RENDER_WARPS];                            // batches each consumer warp is done with (INT_MAX: saturated, gone)
 	__shared__ uint8_t s_list[RENDER_WARPS][BATCH];
 	__shared__ __align__(4) uint8_t s_used[RENDER_WARPS][BATCH];      // 1 if the warp blended the entry into at least one of its pixels
-	__shared__ int s_ndone;        // consumer warps whose 32 pixels are all saturated
-	__shared__ int s_nissued;      // batches the producer filled (valid once s_stop is set)
-	__shared__ int s_stop;         // the producer will fill no more stages
 
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 	const int tile = blockIdx.y * a.grid_x + blockIdx.x;
@@ -63,8 +61,8 @@ __global__ void __launch_bounds__(FWD_THREADS) render_fwd_kernel(RenderArgs a)
 	const int nbatches = (n + BATCH - 1) / BATCH;
 
 	if (tid == 0) {
-		for (int s = 0; s < FWD_STAGES; s++) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], RENDER_WARPS); }
-		s_ndone = 0; s_nissued = 0; s_stop = 0;
+		for (int s = 0; s < FWD_STAGES; s++) mbar_init(&s_full[s], 1);
+		for (int w = 0; w < RENDER_WARPS; w++) s_released[w] = 0;
 		mbar_fence_init();
 	}
 	__syncthreads();
@@ -78,19 +76,23 @@ __global__ void __launch_bounds__(FWD_THREADS) render_fwd_kernel(RenderArgs a)
 		for (; b < nbatches; b++) {
 			const int s = b % FWD_STAGES;
 			if (b >= FWD_STAGES) {
-				mbar_wait(&s_empty[s], (uint32_t)(b / FWD_STAGES - 1) & 1u);       // all 8 warps are past batch b - FWD_STAGES
-				if (*reinterpret_cast<volatile int*>(&s_ndone) == RENDER_WARPS) break;   // every pixel of the tile is saturated
+				// wait until every consumer warp is past batch b - FWD_STAGES; stop when all of them are saturated
+				int low;
+				for (;;) {
+					const int r = lane < RENDER_WARPS ? *reinterpret_cast<volatile int*>(&s_released[lane]) : 0x7fffffff;
+					low = __reduce_min_sync(FULL, r);
+					if (low > b - FWD_STAGES) break;
+					__nanosleep(32);
+				}
+				if (low == 0x7fffffff) break;
+				__threadfence_block();       // the consumers' reads of the stage are ordered before the refill below
 			}
 			producer_fill<MODE>(&s_rec[s][0], &s_full[s], src, grec, ids, b * BATCH, min(BATCH, n - b * BATCH), lane);
 		}
 		__syncwarp();
-		if (lane == 0) {
-			*reinterpret_cast<volatile int*>(&s_nissued) = b;
-			__threadfence_block();
-			*reinterpret_cast<volatile int*>(&s_stop) = 1;
-			// fills still in flight must land before the CTA (and its shared memory) retires
+		// fills still in flight must land before the CTA (and its shared memory) retires
+		if (lane == 0)
 			for (int bb = max(0, b - FWD_STAGES); bb < b; bb++) mbar_wait(&s_full[bb % FWD_STAGES], (uint32_t)(bb / FWD_STAGES) & 1u);
-		}
 		return;
 	}
 
@@ -112,22 +114,11 @@ __global__ void __launch_bounds__(FWD_THREADS) render_fwd_kernel(RenderArgs a)
 	uint32_t last_contributor = 0;
 	bool done = !inside;
 	bool warp_done = __all_sync(FULL, done);
-	if (warp_done && lane == 0) atomicAdd(&s_ndone, 1);
 
-	for (int b = 0; b < nbatches; b++) {
+	for (int b = 0; b < nbatches && !warp_done; b++) {
 		const int s = b % FWD_STAGES;
-		const uint32_t parity = (uint32_t)(b / FWD_STAGES) & 1u;
-		if (!warp_done) {
-			mbar_wait(&s_full[s], parity);       // an unsaturated warp keeps the producer filling
-		} else {
-			// saturated: only release stages, until the producer has stopped and this batch was never filled
-			bool got;
-			while (!(got = mbar_try_wait(&s_full[s], parity))) {
-				if (*reinterpret_cast<volatile int*>(&s_stop) && b >= *reinterpret_cast<volatile int*>(&s_nissued)) break;
-			}
-			if (!got) break;
-		}
-		if (!warp_done) {
+		mbar_wait(&s_full[s], (uint32_t)(b / FWD_STAGES) & 1u);       // an unsaturated warp keeps the producer filling
+		{
 			const int cnt = min(BATCH, n - b * BATCH);
 			const float4* __restrict__ rec = s_rec[s];
 			// this warp's "used" row for the batch starts from zero (one 4-byte store per lane covers the 128 entries)
@@ -206,12 +197,13 @@ __global__ void __launch_bounds__(FWD_THREADS) render_fwd_kernel(RenderArgs a)
 				if (lane == c) myword = wd;
 			}
 			if (lane < BATCH / 32 && lane * 32 < cnt) wflags[b * (BATCH / 32) + lane] = myword;
-			if (warp_done && lane == 0) atomicAdd(&s_ndone, 1);
 		}
-		// this warp is past the stage: it can be refilled once all 8 have arrived
+		// this warp is past the stage: publish it (release: the stage reads above come first)
 		__syncwarp();
-		if (lane == 0) mbar_arrive(&s_empty[s]);
+		if (lane == 0) { __threadfence_block(); *reinterpret_cast<volatile int*>(&s_released[warp]) = b + 1; }
 	}
+	// saturated or at the end of the list: nothing more will be read from the ring
+	if (lane == 0) { __threadfence_block(); *reinterpret_cast<volatile int*>(&s_released[warp]) = 0x7fffffff; }
 
 	if (inside) {
 		const size_t pid = (size_t)a.W * pix_y + pix_x, HW = (size_t)a.H * a.W;

@@ -107,6 +107,32 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
     return results
 
 
+class HostFeed:
+    """Per-view host inputs (target images in pinned memory) streamed to the device on a side stream so that the copy of
+    view i+1 overlaps the render of view i.  ``stage(step_tensors)`` enqueues the copies of one step after everything
+    already queued on the compute stream (the previous step may still read the staging buffers) and returns, per slot,
+    the device buffer; ``wait(slot)`` makes the compute stream wait for that slot's copy only."""
+
+    def __init__(self, shapes, device, dtype=torch.float32):
+        self.device = device
+        self.stream = torch.cuda.Stream(device=device)
+        self.buffers = [torch.empty(s, dtype=dtype, device=device) for s in shapes]
+        self.events = [torch.cuda.Event() for _ in shapes]
+
+    def stage(self, host_tensors):
+        main = torch.cuda.current_stream(self.device)
+        self.stream.wait_stream(main)
+        with torch.cuda.stream(self.stream):
+            for buf, ev, h in zip(self.buffers, self.events, host_tensors):
+                buf.copy_(h, non_blocking=True)
+                ev.record(self.stream)
+        return self.buffers
+
+    def wait(self, slot):
+        torch.cuda.current_stream(self.device).wait_event(self.events[slot])
+        return self.buffers[slot]
+
+
 def allreduce_bucket(bucket: GradientBucket, group=None, average: bool = False):
     """The single collective of a step: sum (or mean) of the flat bucket over all ranks, in place."""
     import torch.distributed as dist

@@ -265,7 +265,7 @@ def test_accumulate_mode_and_multiview_bucket(device):
         tot = cur if tot is None else {k: tot[k] + cur[k] for k in cur}
     for k in mv.SEGMENTS:
         assert torch.isfinite(bucket.views[k]).all()
-        assert rel_err(bucket.views[k], tot[k])[0] < 1e-6, k
+        assert rel_err(bucket.views[k], tot[k])[0] < 1e-5, k
 
 
 def _sort_case(device, n, key_bytes, b0, b1, seed, skew):
