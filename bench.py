@@ -31,7 +31,7 @@ import torch.distributed as dist  # noqa: E402
 
 from rain_b200.synthetic import CONFIGS, make_camera, make_grad, make_scene  # noqa: E402
 
-VIEWS_PER_STEP = 4          # views each rank renders per step
+VIEWS_PER_STEP = 8          # views each rank renders per step (BASELINE.json config 4: a 64-view batch over 8 GPUs)
 NUM_CAMERAS = 64            # the view pool (BASELINE.json config 4 uses a 64-view batch)
 METRIC = "fwd+bwd renders/sec (1M Gaussians, 1920x1080) at 1/2/4/8 B200"
 
@@ -86,12 +86,12 @@ def stage_bytes(name, P, V, N, X, M=16):
         "preprocess_fwd": 52 * P + (12 * M + 67) * V,                 # 44 in + 8 out always; SH row in + projected record out if visible
         "depth_sort": (4 + 4 * 16) * P,                                # histogram read + 4 passes x (key+value read, key+value write)
         "scan": 12 * P,                                                # order + tiles_touched in, offsets out
-        "duplicate": 20 * P + 8 * N,                                   # order/offsets/rect in, tile key + owner out
+        "duplicate": 16 * P + 8 * N,                                   # order/offsets/rect in, tile key + Gaussian id out
         "tile_sort": (4 + 2 * 16) * N,                                 # histogram read + 2 passes x 16 B
-        "ranges_pack": 4 * N + (8 + 48 + 48 + 4) * N,                  # key read; (emit, owner, record) in, record + point_list out
-        "render_fwd": 48 * N + 24 * X,                                 # staged records; colour 12 + depth 4 + final_T 4 + n_contrib 4 out
-        "render_bwd": 52 * N + 40 * N + 20 * X,                        # records + emission index in, one 40-B partial per pair out, dL_dpix/T/n in
-        "preprocess_bwd": 40 * N + (12 * M + 111) * V + (12 * M + 56) * P,   # partials + inputs in, every gradient element out
+        "ranges_pack": 4 * N,                                          # sorted tile keys in (ranges out: 8 B per tile); no pack pass in the gather variants
+        "render_fwd": 52 * N + N + 24 * X,                             # id + gathered record per list entry, 8 flag bits out; colour 12 + depth 4 + final_T 4 + n_contrib 4 out
+        "render_bwd": 52 * N + N + 20 * X + 96 * P,                    # id + record + flag bits in, dL_dpix/T/n in, accumulator zero fill + read-modify-write
+        "preprocess_bwd": 52 * P + (12 * M + 111) * V + (12 * M + 56) * P,   # accumulators + radii + inputs in, every gradient element out
     }.get(name)
 
 
@@ -317,6 +317,14 @@ def run_reference(args, rank, world, local):
 
 
 def main():
+    # stdout carries exactly ONE line, the JSON result: anything a library prints there meanwhile (e.g. the NCCL version
+    # banner) is sent to stderr instead
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+    def emit(obj):
+        real_stdout.write(json.dumps(obj) + "\n")
+        real_stdout.flush()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -331,7 +339,7 @@ def main():
         rank = int(os.environ.get("RANK", "0"))
         line = run_reference(args, rank, int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0")))
         if line is not None:
-            print(json.dumps(line), flush=True)
+            emit(line)
         return
 
     if not torch.cuda.is_available():
@@ -385,7 +393,7 @@ def main():
     }
     if world == 1 and args.cpu_renders > 0:
         line["cpu_baseline"] = cpu_oracle_sample(args.workload, args.cpu_renders)
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 if __name__ == "__main__":
