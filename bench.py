@@ -218,7 +218,8 @@ def run_ours(args, rank, world, local):
 
         def grad_e2e(v, color, depth):
             d = torch.sub(color, feed.wait(slot[v]))
-            loss_dev.add_(0.5 * (d * d).sum())
+            dv = d.view(-1)
+            loss_dev.add_(torch.dot(dv, dv), alpha=0.5)
             return d
         bucket.filled = False
         mv.render_views_fwd_bwd(params, cams_step, ids, bucket, grad_e2e, **kw)

@@ -37,11 +37,87 @@ def _f32c(t, dev):
     return t.contiguous()
 
 
-def _pinned_i64(dev):
+class _GeomPass:
+    """State between the two halves of the forward (rr_forward_geom / rr_forward_raster)."""
+    __slots__ = ("P", "H", "W", "dev", "bg", "debug", "out_color", "out_depth", "radii", "geom", "img", "nr", "event", "stream", "keep")
+
+
+def _pinned_slot(dev):
+    """a pinned int64 for num_rendered; two per device, used alternately, so that one forward may be in flight while the
+    previous one's count is still being read"""
     key = dev.index
     if key not in _pinned:
-        _pinned[key] = torch.zeros(1, dtype=torch.int64).pin_memory()
-    return _pinned[key]
+        _pinned[key] = [torch.zeros(1, dtype=torch.int64).pin_memory() for _ in range(2)] + [0]
+    slots = _pinned[key]
+    slots[2] ^= 1
+    return slots[slots[2]]
+
+
+def forward_geom(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                 viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
+                 prefiltered, debug, low_pass):
+    """First half of RasterizeGaussiansCUDA (preprocess, depth order, prefix sum; Rasterizer::forward up to the num_rendered
+    read-back, rasterizer_impl.cu:187-273), enqueued without waiting: returns the state ``forward_raster`` completes.
+    Splitting the forward lets a caller enqueue the next view's first half before the current view's backward, so the
+    device never idles on the num_rendered round trip (rain_b200.multiview)."""
+    lib = _lib.load()
+    if means3D.dim() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")  # rasterize_points.cu:47-49
+    if not means3D.is_cuda:
+        raise RuntimeError("rain_b200 has no CPU path: means3D must be a CUDA tensor")
+    dev = means3D.device
+    st = _GeomPass()
+    P, H, W = means3D.size(0), int(image_height), int(image_width)
+    st.P, st.H, st.W, st.dev, st.debug = P, H, W, dev, bool(debug)
+    byte = dict(dtype=torch.uint8, device=dev)
+    if P == 0:  # rasterize_points.cu:72
+        return st
+    means3D_c = _f32c(means3D, dev)
+    bg, colors_c, opac, scales_c, rots, cov_c = (_f32c(t, dev) for t in (background, colors, opacity, scales, rotations, cov3D_precomp))
+    view, proj, cam, sh_c = (_f32c(t, dev) for t in (viewmatrix, projmatrix, campos, sh))
+    M = sh.size(1) if (sh is not None and sh.numel() != 0) else 0  # rasterize_points.cu:75-78
+    st.bg = bg
+    st.out_color = torch.empty((NUM_CHANNELS, H, W), dtype=torch.float32, device=dev)
+    st.out_depth = torch.empty((1, H, W), dtype=torch.float32, device=dev)
+    st.radii = torch.empty((P,), dtype=torch.int32, device=dev)
+    st.geom = torch.empty(lib.rr_geom_bytes(P), **byte)
+    st.img = torch.empty(lib.rr_image_bytes(W, H), **byte)
+    st.nr = _pinned_slot(dev)
+    st.keep = (means3D_c, colors_c, opac, scales_c, rots, cov_c, view, proj, cam, sh_c)   # inputs stay alive until the kernels ran
+    with torch.cuda.device(dev):
+        st.stream = torch.cuda.current_stream()
+        _lib.check(lib.rr_forward_geom(st.stream.cuda_stream, P, int(degree), M, W, H,
+                                       _ptr(means3D_c), _ptr(sh_c), _ptr(colors_c), _ptr(opac),
+                                       _ptr(scales_c), float(scale_modifier), _ptr(rots), _ptr(cov_c),
+                                       _ptr(view), _ptr(proj), _ptr(cam),
+                                       float(tan_fovx), float(tan_fovy), float(low_pass), int(bool(prefiltered)), int(bool(debug)),
+                                       st.radii.data_ptr(), st.geom.data_ptr(), st.geom.numel(), st.nr.data_ptr()), "rr_forward_geom")
+        st.event = torch.cuda.Event()
+        st.event.record(st.stream)
+    return st
+
+
+def forward_raster(st):
+    """Second half of RasterizeGaussiansCUDA: waits for num_rendered (it sizes the binning blob; the reference blocks on a
+    cudaMemcpy here, rasterizer_impl.cu:273), then duplicate / tile sort / ranges / render.
+    Returns (num_rendered, out_color[3,H,W], radii i32[P], out_depth[1,H,W], geomBuffer, binningBuffer, imgBuffer)."""
+    lib = _lib.load()
+    dev, P, H, W = st.dev, st.P, st.H, st.W
+    byte = dict(dtype=torch.uint8, device=dev)
+    if P == 0:  # rasterize_points.cu:72
+        z = torch.zeros
+        return (0, z((NUM_CHANNELS, H, W), dtype=torch.float32, device=dev), z((0,), dtype=torch.int32, device=dev),
+                z((1, H, W), dtype=torch.float32, device=dev), torch.empty(0, **byte), torch.empty(0, **byte), torch.empty(0, **byte))
+    st.event.synchronize()
+    N = int(st.nr.item())
+    binning = torch.empty(lib.rr_binning_bytes(N, W, H), **byte)
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream()
+        _lib.check(lib.rr_forward_raster(stream.cuda_stream, P, W, H, N, _ptr(st.bg),
+                                         st.geom.data_ptr(), st.geom.numel(), binning.data_ptr(), binning.numel(), st.img.data_ptr(), st.img.numel(),
+                                         st.out_color.data_ptr(), st.out_depth.data_ptr(), _variant(), int(st.debug)), "rr_forward_raster")
+    st.keep = None
+    return N, st.out_color, st.radii, st.out_depth, st.geom, binning, st.img
 
 
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
@@ -49,43 +125,9 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
                         prefiltered, debug, low_pass):
     """RasterizeGaussiansCUDA (rasterize_points.cu:24-108).
     Returns (num_rendered, out_color[3,H,W], radii i32[P], out_depth[1,H,W], geomBuffer, binningBuffer, imgBuffer)."""
-    lib = _lib.load()
-    if means3D.dim() != 2 or means3D.size(1) != 3:
-        raise RuntimeError("means3D must have dimensions (num_points, 3)")  # rasterize_points.cu:47-49
-    if not means3D.is_cuda:
-        raise RuntimeError("rain_b200 has no CPU path: means3D must be a CUDA tensor")
-    dev = means3D.device
-    P, H, W = means3D.size(0), int(image_height), int(image_width)
-    byte = dict(dtype=torch.uint8, device=dev)
-    if P == 0:  # rasterize_points.cu:72
-        z = torch.zeros
-        return (0, z((NUM_CHANNELS, H, W), dtype=torch.float32, device=dev), z((0,), dtype=torch.int32, device=dev),
-                z((1, H, W), dtype=torch.float32, device=dev), torch.empty(0, **byte), torch.empty(0, **byte), torch.empty(0, **byte))
-    means3D_c = _f32c(means3D, dev)
-    bg, colors_c, opac, scales_c, rots, cov_c = (_f32c(t, dev) for t in (background, colors, opacity, scales, rotations, cov3D_precomp))
-    view, proj, cam, sh_c = (_f32c(t, dev) for t in (viewmatrix, projmatrix, campos, sh))
-    M = sh.size(1) if (sh is not None and sh.numel() != 0) else 0  # rasterize_points.cu:75-78
-    out_color = torch.empty((NUM_CHANNELS, H, W), dtype=torch.float32, device=dev)
-    out_depth = torch.empty((1, H, W), dtype=torch.float32, device=dev)
-    radii = torch.empty((P,), dtype=torch.int32, device=dev)
-    geom = torch.empty(lib.rr_geom_bytes(P), **byte)
-    img = torch.empty(lib.rr_image_bytes(W, H), **byte)
-    nr = _pinned_i64(dev)
-    with torch.cuda.device(dev):
-        stream = torch.cuda.current_stream()
-        _lib.check(lib.rr_forward_geom(stream.cuda_stream, P, int(degree), M, W, H,
-                                       _ptr(means3D_c), _ptr(sh_c), _ptr(colors_c), _ptr(opac),
-                                       _ptr(scales_c), float(scale_modifier), _ptr(rots), _ptr(cov_c),
-                                       _ptr(view), _ptr(proj), _ptr(cam),
-                                       float(tan_fovx), float(tan_fovy), float(low_pass), int(bool(prefiltered)), int(bool(debug)),
-                                       radii.data_ptr(), geom.data_ptr(), geom.numel(), nr.data_ptr()), "rr_forward_geom")
-        stream.synchronize()  # num_rendered sizes the binning blob (reference: blocking cudaMemcpy, rasterizer_impl.cu:273)
-        N = int(nr.item())
-        binning = torch.empty(lib.rr_binning_bytes(N, W, H), **byte)
-        _lib.check(lib.rr_forward_raster(stream.cuda_stream, P, W, H, N, _ptr(bg),
-                                         geom.data_ptr(), geom.numel(), binning.data_ptr(), binning.numel(), img.data_ptr(), img.numel(),
-                                         out_color.data_ptr(), out_depth.data_ptr(), _variant(), int(bool(debug))), "rr_forward_raster")
-    return N, out_color, radii, out_depth, geom, binning, img
+    return forward_raster(forward_geom(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                                       viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
+                                       prefiltered, debug, low_pass))
 
 
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,

@@ -83,25 +83,30 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
     dev = params["means3D"].device
     e = torch.empty(0, device=dev)
     results = []
-    for v in view_ids:
+    has_split = hasattr(backend, "forward_geom")
+
+    def geom_pass(v):
         cam = cameras[v]
-        N, color, radii, depth, geom, binning, img = backend.rasterize_gaussians(
-            bg, params["means3D"], e, params["opacities"], params["scales"], params["rotations"], scale_modifier, e,
-            cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, cam.height, cam.width, params["shs"], sh_degree, cam.campos,
-            False, debug, low_pass)
+        args = (bg, params["means3D"], e, params["opacities"], params["scales"], params["rotations"], scale_modifier, e,
+                cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, cam.height, cam.width, params["shs"], sh_degree, cam.campos,
+                False, debug, low_pass)
+        return backend.forward_geom(*args) if has_split else args
+
+    # software pipeline over the views: the first half of view i+1 (preprocess, depth sort, prefix sum) is enqueued BEFORE
+    # the backward of view i, so its num_rendered is on the host long before it is needed and the device never waits for
+    # the round trip that sizes the binning buffer
+    view_ids = list(view_ids)
+    pending = geom_pass(view_ids[0]) if view_ids else None
+    for i, v in enumerate(view_ids):
+        cam = cameras[v]
+        N, color, radii, depth, geom, binning, img = backend.forward_raster(pending) if has_split else backend.rasterize_gaussians(*pending)
+        pending = geom_pass(view_ids[i + 1]) if i + 1 < len(view_ids) else None
         dpix = grad_fn(v, color, depth)
-        if not bucket.filled:
-            # slots are overwritten by the first view; culled Gaussians get explicit zeros from the kernel
-            grads = backend.rasterize_gaussians_backward(
-                bg, params["means3D"], radii, e, params["scales"], params["rotations"], scale_modifier, e, cam.viewmatrix, cam.projmatrix,
-                cam.tanfovx, cam.tanfovy, dpix, params["shs"], sh_degree, cam.campos, geom, N, binning, img, debug, low_pass,
-                grads_out=bucket.grads_out(), accumulate=False)
-            bucket.filled = True
-        else:
-            grads = backend.rasterize_gaussians_backward(
-                bg, params["means3D"], radii, e, params["scales"], params["rotations"], scale_modifier, e, cam.viewmatrix, cam.projmatrix,
-                cam.tanfovx, cam.tanfovy, dpix, params["shs"], sh_degree, cam.campos, geom, N, binning, img, debug, low_pass,
-                grads_out=bucket.grads_out(), accumulate=True)
+        grads = backend.rasterize_gaussians_backward(
+            bg, params["means3D"], radii, e, params["scales"], params["rotations"], scale_modifier, e, cam.viewmatrix, cam.projmatrix,
+            cam.tanfovx, cam.tanfovy, dpix, params["shs"], sh_degree, cam.campos, geom, N, binning, img, debug, low_pass,
+            grads_out=bucket.grads_out(), accumulate=bucket.filled)       # the first view overwrites the bucket, later views add
+        bucket.filled = True
         results.append(ViewResult(v, color if keep_outputs else None, depth if keep_outputs else None, radii if keep_outputs else None,
                                   int(N), grads[0] if keep_outputs else None))
     return results
