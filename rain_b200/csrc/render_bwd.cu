@@ -7,15 +7,22 @@
 //  * no CTA-wide coupling at all: the forward leaves one bit per (list entry, warp) ("this warp blended the entry",
 //    kernels.cuh); a warp reads its own bit words, turns them into a descending visit list, and walks it.  Warps that
 //    own saturated or empty pixel blocks finish at once; there is no __syncthreads in the kernel.
-//  * the 48-byte records of the next 32 visits are gathered straight from the per-Gaussian record array (L2 resident:
-//    48 MB at 1M Gaussians) by 32 per-lane 1-D TMA bulk copies onto a per-warp mbarrier, double buffered, while the
-//    current 32 visits are processed; Gaussian ids are prefetched one chunk further ahead.
+//  * the 48-byte records of the next CHUNK (16) visits are gathered straight from the per-Gaussian record array (L2
+//    resident: 48 MB at 1M Gaussians) by per-lane 1-D TMA bulk copies onto a per-warp mbarrier, double buffered, while
+//    the current chunk is processed; Gaussian ids are prefetched one chunk further ahead.  Shared memory per CTA is
+//    17.5 KB static + 27 KB of transpose rows, so 4 CTAs (32 warps) stay resident per SM — measured: 3 CTAs/SM with
+//    32-visit chunks 0.534 ms, 4 CTAs/SM with 16-visit chunks 0.494 ms (C3, 8.4M pairs).
 //  * each lane forms the terms of its pixel as the reference does (backward.cu:481-544), but accumulates the MOMENTS
 //    u, u.dx, u.dy, u.dx^2, u.dx.dy, u.dy^2 of u = G * dL_dalpha instead of the five conic / mean products — they are
 //    linear in the per-Gaussian constants (conic, opacity), which preprocess_bwd.cu applies once per Gaussian;
-//  * the warp reduces the 9 values with a halving butterfly (8 values in 4+2+1+1+1 shuffles, the 9th in 5) and issues
-//    ONE predicated RED.ADD.F32 (9 active lanes, one 48-byte accumulator record): a single global accumulation per
-//    (warp, Gaussian) visit instead of 9 atomics per pixel.
+//  * the 9 values of GROUP consecutive visits are reduced across the warp by a TRANSPOSE through shared memory instead
+//    of shuffles: every lane stores its 9 terms of a visit as 9 conflict-free STS into rows [visit][value][lane];
+//    after GROUP visits lane r < 9*GROUP owns row r, reads its 32 floats as 8 LDS.128 (rotated by r so the 8 lanes of a
+//    quarter-warp hit 8 different bank groups) and sums them with packed add.rn.f32x2 (SASS FADD2), then issues its
+//    share of ONE predicated RED.ADD.F32 per group (9*GROUP active lanes).  Per visit this is 9 STS + ~10 issue
+//    slots of row work against 14 SHFL + 14 FADD + 14 FSEL for the halving butterfly it replaces (REDUCE_SHFL keeps
+//    the butterfly as the cross-check variant), and a third of the RED instructions.
+#include <cstdlib>
 #include "common.cuh"
 #include "kernels.cuh"
 #include "render_common.cuh"
@@ -25,8 +32,16 @@ namespace rr {
 namespace {
 
 constexpr int NV = 9;
-constexpr int LIST_WORDS = 16;                  // flag words (of 32 list entries) turned into a visit list per round
+constexpr int LIST_WORDS = 8;                   // flag words (of 32 list entries) turned into a visit list per round
 constexpr int LIST_CAP = LIST_WORDS * 32;
+constexpr int CHUNK = 16;                       // visits staged per buffer (16 x 48 B per warp and buffer keeps 4 CTAs per SM)
+
+__device__ __forceinline__ float2 add2(float2 a, float2 b) {
+	float2 r;
+	asm("{.reg .b64 ra, rb, rc; mov.b64 ra, {%2,%3}; mov.b64 rb, {%4,%5}; add.rn.f32x2 rc, ra, rb; mov.b64 {%0,%1}, rc;}"
+		: "=f"(r.x), "=f"(r.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+	return r;
+}
 
 // Sum v[0..8] over the 32 lanes.  On return lane L with (L & 3) == 0 holds in `y` the total of value
 // k = 4*bit4(L) + 2*bit3(L) + bit2(L); every lane holds the total of v[8] in `z`.
@@ -55,13 +70,19 @@ __device__ __forceinline__ void warp_reduce9(const float (&v)[NV], int lane, flo
 	for (int o = 16; o >= 1; o >>= 1) z += __shfl_xor_sync(FULL, z, o);
 }
 
-template <bool USE_TMA>
+// GROUP = visits reduced together through shared memory (0: shuffle butterfly, no transpose rows)
+template <bool USE_TMA, int GROUP>
 __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a)
 {
-	__shared__ __align__(128) float4 s_rec[RENDER_WARPS][2][32 * 3];   // per warp, double buffered: 32 records of 48 B
-	__shared__ __align__(8) uint2 s_meta[RENDER_WARPS][2][32];         // { Gaussian id, list position } of each staged visit
+	constexpr bool REDUCE_SHFL = GROUP == 0;
+	constexpr int RED_ROWS = GROUP * NV;         // rows of 32 floats per warp
+
+	__shared__ __align__(128) float4 s_rec[RENDER_WARPS][2][CHUNK * 3];   // per warp, double buffered: CHUNK records of 48 B
+	__shared__ uint32_t s_gid[RENDER_WARPS][2][CHUNK];                  // Gaussian id of each staged visit
 	__shared__ uint16_t s_pos[RENDER_WARPS][LIST_CAP];                  // visit list of the round (positions relative to the round's first entry, descending)
 	__shared__ __align__(8) uint64_t s_bar[RENDER_WARPS][2];
+	extern __shared__ __align__(16) float s_red_dyn[];                  // transpose rows [warp][visit in group][value][lane] (dynamic: static + this > 48 KB)
+	float* const s_red_w = s_red_dyn + (REDUCE_SHFL ? 0 : (threadIdx.x >> 5) * RED_ROWS * 32);
 
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 	const int tile = blockIdx.y * a.grid_x + blockIdx.x;
@@ -96,6 +117,10 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 	const int kslot = (lane & 3) == 0 ? ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1) : (lane == 1 ? 8 : -1);
 	const bool adder = kslot >= 0;
 	float* __restrict__ acc_lane = a.grad_acc + (adder ? kslot : 0);
+	// shared-memory transpose: lane r < 9 * GROUP owns row r = visit * 9 + value of the group
+	const int row_visit = lane / NV;
+	float* __restrict__ acc_row = a.grad_acc + (lane - row_visit * NV);
+	const float4* __restrict__ red_row = reinterpret_cast<const float4*>(s_red_w) + (REDUCE_SHFL ? 0 : lane * 8);
 
 	const int ngroups = (n + 31) >> 5;
 	const uint32_t* __restrict__ wf = a.warp_flags + 8ull * ((size_t)(range.x >> 5) + (size_t)tile) + (size_t)warp * ngroups;
@@ -118,17 +143,17 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 		while (word) { const int bit = 31 - __clz(word); word ^= 1u << bit; s_pos[warp][at++] = (uint16_t)(lane * 32 + bit); }
 		__syncwarp();
 		const uint32_t ebase = (uint32_t)wbase * 32u;
-		const int nch = (total + 31) >> 5;
+		const int nch = (total + CHUNK - 1) / CHUNK;
 
 		auto load_gid = [&](int k) -> uint32_t {
-			const int i = k * 32 + lane;
-			return i < total ? __ldg(ids + ebase + s_pos[warp][i]) : 0u;
+			const int i = k * CHUNK + lane;
+			return (lane < CHUNK && i < total) ? __ldg(ids + ebase + s_pos[warp][i]) : 0u;
 		};
 		// stage chunk k of the round into buffer qq & 1
 		auto issue = [&](int k, uint32_t qq, uint32_t gid) {
 			const int buf = (int)(qq & 1u);
-			const int cc = min(32, total - k * 32);
-			if (lane < cc) s_meta[warp][buf][lane] = make_uint2(gid, ebase + s_pos[warp][k * 32 + lane]);
+			const int cc = min(CHUNK, total - k * CHUNK);
+			if (lane < cc) s_gid[warp][buf][lane] = gid;
 			if (USE_TMA) {
 				if (lane == 0) mbar_arrive_expect_tx(&bar[buf], (uint32_t)cc * (uint32_t)sizeof(SplatRec));
 				__syncwarp();
@@ -151,18 +176,21 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 			if (USE_TMA) mbar_wait(&bar[buf], (q >> 1) & 1u);
 			__syncwarp();
 			const float4* __restrict__ rec = s_rec[warp][buf];
-			const int cc = min(32, total - k * 32);
-			for (int kk = 0; kk < cc; kk++) {
-				const uint2 mt = s_meta[warp][buf][kk];
-				const float4 ra = rec[kk * 3], rb = rec[kk * 3 + 1], rc = rec[kk * 3 + 2];
+			const int cc = min(CHUNK, total - k * CHUNK);
+			const uint16_t* __restrict__ cpos = s_pos[warp] + k * CHUNK;
+			// per-pixel terms of one visit (reference backward.cu:481-544, moments instead of conic / mean products)
+			auto visit = [&](int kk, float (&v)[NV]) {
+				const uint32_t pos = ebase + cpos[kk];
+				const float4 ra = rec[kk * 3], rb = rec[kk * 3 + 1];
 				const float dx = __fsub_rn(ra.x, pxf), dy = __fsub_rn(ra.y, pyf);
 				const float qd = __fmaf_rn(dx, __fmul_rn(dx, ra.z), __fmul_rn(dy, __fmul_rn(dy, rb.x)));
 				const float power = __fmaf_rn(qd, -0.5f, -__fmul_rn(dy, __fmul_rn(dx, ra.w)));
 				const float G = expf(fminf(power, 0.0f));
 				const float alpha = fminf(0.99f, __fmul_rn(rb.y, G));
-				const bool live = !(power > 0.0f) && !(alpha < 1.0f / 255.0f) && mt.y < last_contributor;
+				const bool live = !(power > 0.0f) && !(alpha < 1.0f / 255.0f) && pos < last_contributor;
 				float dcdc = 0.0f, u = 0.0f;
 				if (live) {
+					const float c2 = rec[kk * 3 + 2].x;
 					float inv_1ma;      // 1/(1-alpha), 1-alpha in [0.01, 1): the approximate reciprocal (1 ulp) is ample for 1e-4 gradients
 					asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv_1ma) : "f"(1.f - alpha));
 					T = T * inv_1ma;
@@ -170,22 +198,52 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 					const float one_m_la = 1.f - last_alpha;
 					ar0 = last_alpha * lc0 + one_m_la * ar0; lc0 = rb.z;
 					ar1 = last_alpha * lc1 + one_m_la * ar1; lc1 = rb.w;
-					ar2 = last_alpha * lc2 + one_m_la * ar2; lc2 = rc.x;
+					ar2 = last_alpha * lc2 + one_m_la * ar2; lc2 = c2;
 					float dL_dalpha = (rb.z - ar0) * dLp0;
 					dL_dalpha += (rb.w - ar1) * dLp1;
-					dL_dalpha += (rc.x - ar2) * dLp2;
+					dL_dalpha += (c2 - ar2) * dLp2;
 					dL_dalpha = dL_dalpha * T + neg_Tf_bg * inv_1ma;
 					last_alpha = alpha;
 					u = G * dL_dalpha;
 				}
-				float v[NV];
 				v[0] = dcdc * dLp0; v[1] = dcdc * dLp1; v[2] = dcdc * dLp2;
 				v[3] = u * dx; v[4] = u * dy;
 				v[5] = v[3] * dx; v[6] = v[3] * dy; v[7] = v[4] * dy;
 				v[8] = u;
-				float y, z;
-				warp_reduce9(v, lane, y, z);
-				if (adder) atomicAdd(acc_lane + mt.x * (uint32_t)ACC_FLOATS, lane == 1 ? z : y);
+			};
+			if (REDUCE_SHFL) {
+				for (int kk = 0; kk < cc; kk++) {
+					float v[NV], y, z;
+					visit(kk, v);
+					warp_reduce9(v, lane, y, z);
+					if (adder) atomicAdd(acc_lane + (size_t)s_gid[warp][buf][kk] * ACC_FLOATS, lane == 1 ? z : y);
+				}
+			} else {
+				float* __restrict__ red = s_red_w;
+				for (int g0 = 0; g0 < cc; g0 += GROUP) {
+					const int gn = min(GROUP, cc - g0);               // warp-uniform
+					#pragma unroll
+					for (int j = 0; j < GROUP; j++) {
+						if (j < gn) {
+							float v[NV];
+							visit(g0 + j, v);
+							#pragma unroll
+							for (int k = 0; k < NV; k++) red[(j * NV + k) * 32 + lane] = v[k];
+						}
+					}
+					__syncwarp();
+					if (lane < gn * NV) {
+						float2 s0 = make_float2(0.f, 0.f), s1 = make_float2(0.f, 0.f);
+						#pragma unroll
+						for (int i = 0; i < 8; i++) {
+							const float4 t = red_row[(i + lane) & 7];
+							s0 = add2(s0, make_float2(t.x, t.y)); s1 = add2(s1, make_float2(t.z, t.w));
+						}
+						s0 = add2(s0, s1);
+						atomicAdd(acc_row + (size_t)s_gid[warp][buf][g0 + row_visit] * ACC_FLOATS, s0.x + s0.y);
+					}
+					__syncwarp();      // rows are free again
+				}
 			}
 			__syncwarp();      // every lane is done with this buffer before the next iteration refills it
 		}
@@ -197,8 +255,23 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 int launch_render_bwd(cudaStream_t stream, const RenderArgs& a)
 {
 	const dim3 grid(a.grid_x, a.grid_y);
-	if (a.variant == MODE_PACKED_LDG || a.variant == MODE_GATHER_LDG) count_launch(), render_bwd_kernel<false><<<grid, RENDER_THREADS, 0, stream>>>(a);
-	else count_launch(), render_bwd_kernel<true><<<grid, RENDER_THREADS, 0, stream>>>(a);
+	// RAIN_BWD_REDUCE=s selects the shuffle-butterfly reduction (cross-check of the shared-memory transpose), 2 / 3 the group size
+	static const int group = []() { const char* e = getenv("RAIN_BWD_REDUCE"); return !e ? 3 : e[0] == 's' ? 0 : e[0] == '2' ? 2 : 3; }();
+	const bool ldg = a.variant == MODE_PACKED_LDG || a.variant == MODE_GATHER_LDG;
+	auto launch = [&](auto kern, int grp) -> int {
+		const int red_bytes = RENDER_WARPS * grp * NV * 32 * (int)sizeof(float);
+		if (red_bytes && cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, red_bytes) != cudaSuccess) {
+			set_error("render_bwd: cannot reserve %d bytes of dynamic shared memory", red_bytes); return -1;
+		}
+		count_launch();
+		kern<<<grid, RENDER_THREADS, red_bytes, stream>>>(a);
+		return 0;
+	};
+	int rc;
+	if (group == 0) rc = ldg ? launch(render_bwd_kernel<false, 0>, 0) : launch(render_bwd_kernel<true, 0>, 0);
+	else if (group == 2) rc = ldg ? launch(render_bwd_kernel<false, 2>, 2) : launch(render_bwd_kernel<true, 2>, 2);
+	else rc = ldg ? launch(render_bwd_kernel<false, 3>, 3) : launch(render_bwd_kernel<true, 3>, 3);
+	if (rc) return rc;
 	return check_launch("render_bwd", stream, false);
 }
 
