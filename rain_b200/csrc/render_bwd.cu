@@ -252,8 +252,13 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_bwd_kernel(RenderArgs a
 
 }  // namespace
 
+int launch_render_bwd2(cudaStream_t stream, const RenderArgs& a);   // render_bwd2.cu: two pixels per lane, packed f32x2 arithmetic
+
 int launch_render_bwd(cudaStream_t stream, const RenderArgs& a)
 {
+	// RAIN_BWD_KERNEL=1 selects the one-pixel-per-lane kernel of this file (cross-check); default: render_bwd2.cu
+	static const bool one_px = []() { const char* e = getenv("RAIN_BWD_KERNEL"); return e && e[0] == '1'; }();
+	if (!one_px) return launch_render_bwd2(stream, a);
 	const dim3 grid(a.grid_x, a.grid_y);
 	// RAIN_BWD_REDUCE=s selects the shuffle-butterfly reduction (cross-check of the shared-memory transpose), 2 / 3 the group size
 	static const int group = []() { const char* e = getenv("RAIN_BWD_REDUCE"); return !e ? 3 : e[0] == 's' ? 0 : e[0] == '2' ? 2 : 3; }();
