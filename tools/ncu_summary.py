@@ -1,13 +1,44 @@
-"""One line per captured launch of an ncu report: python tools/ncu_summary.py <rep>"""
-import csv, io, subprocess, sys
-M = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active",
-     "launch__registers_per_thread", "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__thread_inst_executed_per_inst_executed.ratio", "launch__grid_size",
-     "lts__t_bytes.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"]
-out = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "raw", "--csv", "--metrics", ",".join(M)], capture_output=True, text=True).stdout
-rows = list(csv.reader(io.StringIO(out)))
-h = rows[0]
-cols = [h.index("Kernel Name")] + [h.index(m) for m in M if m in h]
-print(",".join(["id"] + [h[c] for c in cols]))
-print(",".join([""] + [rows[1][c] for c in cols]))
-for i, r in enumerate(rows[2:]):
-    print(",".join([str(i)] + [r[c][:48].replace(",", ";") for c in cols]))
+"""Condense an `ncu --set full` report into the per-launch summary CSV kept under profiles/ and (optionally) refresh
+profiles/ncu_traffic.json, the per-stage DRAM traffic bench.py quotes in `roofline.traffic`.
+   python tools/ncu_summary.py <rep> <out.csv> [--traffic C3]"""
+import csv, io, json, os, subprocess, sys
+
+COLS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "smsp__inst_executed.sum",
+        "smsp__issue_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread",
+        "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__thread_inst_executed_per_inst_executed.ratio", "launch__grid_size",
+        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum"]
+STAGE_OF = [("render_bwd", "render_bwd"), ("render_fwd", "render_fwd"), ("preprocess_bwd", "preprocess_bwd"), ("preprocess_fwd", "preprocess_fwd"),
+            ("tile_ranges", "ranges_pack"), ("duplicate", "duplicate")]
+
+rep, out = sys.argv[1], sys.argv[2]
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(io.StringIO(raw)))
+hdr, units, data = rows[0], rows[1], rows[2:]
+ki = hdr.index("Kernel Name")
+idx = [hdr.index(c) for c in COLS if c in hdr]
+with open(out, "w", newline="") as f:
+    w = csv.writer(f)
+    w.writerow(["id", "Kernel Name"] + [hdr[i] for i in idx])
+    w.writerow(["", ""] + [units[i] for i in idx])
+    for n, r in enumerate(data):
+        w.writerow([n, r[ki].replace(",", ";")[:48]] + [r[i] for i in idx])
+print("wrote", out, len(data), "launches")
+
+if "--traffic" in sys.argv:
+    wl = sys.argv[sys.argv.index("--traffic") + 1]
+    tp = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "ncu_traffic.json")
+    tj = json.load(open(tp))
+    ri, wi = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+    scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    per = {}
+    for r in data:
+        for key, stage in STAGE_OF:
+            if key in r[ki]:
+                per.setdefault(stage, []).append(float(r[ri]) * scale[units[ri]] + float(r[wi]) * scale[units[wi]])
+                break
+    tj.setdefault(wl, {}).update({k: int(sum(v) / len(v)) for k, v in per.items()})
+    tj["_comment"] = "dram__bytes_read.sum + dram__bytes_write.sum per launch from ncu --set full captures (bytes); key = workload -> stage; source: " + os.path.basename(rep)
+    json.dump(tj, open(tp, "w"), indent=1)
+    print("traffic", tj[wl])
