@@ -86,6 +86,12 @@ int rr_backward(void* stream, int P, int D, int M, int W, int H, int64_t N, cons
 	int variant, int debug, int flags);
 
 /* replaces Rasterizer::markVisible / checkFrustum (rasterizer_impl.cu:43-55,130-142); present is uint8/bool [P] */
+/* Self test of the packed exponential the render kernels use (exp2x, csrc/render_common.cuh) against libdevice expf —
+ * the function the reference's forward.cu:336 / backward.cu:488 compile to — over the float bit patterns
+ * [first_bits, first_bits + count).  Adds the number of results that differ in any bit to *mismatches_dev (device, u64,
+ * zeroed by the caller).  The forward's bit-exact n_contrib / colour parity rests on this being 0 for all x <= 0. */
+int rr_selftest_exp(void* stream, uint32_t first_bits, uint32_t count, unsigned long long* mismatches_dev);
+
 int rr_mark_visible(void* stream, int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present);
 
 /* replaces distCUDA2 / SimpleKNN::knn (simple-knn/spatial.cu:4-15, simple_knn.cu:174-210); points f32[P,3] -> out f32[P] */

@@ -17,7 +17,7 @@ _pinned = {}
 
 
 def _variant():
-    return int(os.environ.get("RAIN_RAST_VARIANT", "2"))
+    return int(os.environ.get("RAIN_RAST_VARIANT", "4"))
 
 
 def _ptr(t):

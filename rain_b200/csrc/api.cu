@@ -333,6 +333,13 @@ int rr_backward(void* stream_, int P, int D, int M, int W, int H, int64_t N, con
 	return check_launch("backward", stream, debug != 0);
 }
 
+int rr_selftest_exp(void* stream_, uint32_t first_bits, uint32_t count, unsigned long long* mismatches_dev)
+{
+	if (bad_ptr(mismatches_dev, "mismatches_dev")) return -1;
+	if (count == 0) return 0;
+	return launch_exp_selftest(reinterpret_cast<cudaStream_t>(stream_), first_bits, count, mismatches_dev);
+}
+
 int rr_mark_visible(void* stream_, int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present)
 {
 	(void)projmatrix;   // in_frustum computes p_proj but only tests view-space z (auxiliary.h:137-143)

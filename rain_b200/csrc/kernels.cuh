@@ -60,6 +60,7 @@ struct RenderArgs {
 };
 int launch_render_fwd(cudaStream_t, const RenderArgs&);
 int launch_render_bwd(cudaStream_t, const RenderArgs&);
+int launch_exp_selftest(cudaStream_t, uint32_t first_bits, uint32_t count, unsigned long long* mismatches /*device, zeroed by the caller*/);
 
 // preprocess_bwd.cu
 struct PreprocessBwdArgs {

@@ -35,6 +35,12 @@ __device__ __forceinline__ void producer_fill(float4* dst, uint64_t* bar, const 
 {
 	if (StageMode<MODE>::tma) {
 		stage_fill_async<MODE>(dst, bar, packed, rec, ids, first, cnt, lane);
+	} else if (StageMode<MODE>::async_gather) {
+		for (int i = lane; i < cnt; i += 32) {
+			const float4* __restrict__ src = rec + (size_t)__ldg(ids + first + i) * 3;
+			cp_async16(dst + i * 3, src); cp_async16(dst + i * 3 + 1, src + 1); cp_async16(dst + i * 3 + 2, src + 2);
+		}
+		cp_async_arrive_noinc(bar);          // every lane: fires when this lane's copies (if any) have landed
 	} else {
 		for (int i = lane; i < cnt * 3; i += 32) {
 			if (MODE == MODE_PACKED_LDG) dst[i] = __ldg(packed + (size_t)first * 3 + i);
@@ -61,7 +67,7 @@ __global__ void __launch_bounds__(FWD_THREADS) render_fwd_kernel(RenderArgs a)
 	const int nbatches = (n + BATCH - 1) / BATCH;
 
 	if (tid == 0) {
-		for (int s = 0; s < FWD_STAGES; s++) mbar_init(&s_full[s], 1);
+		for (int s = 0; s < FWD_STAGES; s++) mbar_init(&s_full[s], StageMode<MODE>::full_count);
 		for (int w = 0; w < RENDER_WARPS; w++) s_released[w] = 0;
 		mbar_fence_init();
 	}
@@ -110,7 +116,9 @@ __global__ void __launch_bounds__(FWD_THREADS) render_fwd_kernel(RenderArgs a)
 	uint8_t* __restrict__ list = s_list[warp];
 	uint8_t* __restrict__ used = s_used[warp];
 
-	float T = 1.0f, C0 = 0.0f, C1 = 0.0f, C2 = 0.0f, Dp = 0.0f;
+	float T = 1.0f;
+	p2 C01 = pk(0.0f, 0.0f), C2D = C01;      // (C0, C1) and (C2, depth) accumulators
+	const p2 pxy2 = pk(pxf, pyf);
 	uint32_t last_contributor = 0;
 	bool done = !inside;
 	bool warp_done = __all_sync(FULL, done);
@@ -162,26 +170,40 @@ __global__ void __launch_bounds__(FWD_THREADS) render_fwd_kernel(RenderArgs a)
 				uint32_t usedbits = 0, bit = 1u;
 				for (int k8 = 0; k8 < kn; k8 += 8) {
 					const int n8 = min(8, kn - k8);
-					for (int j = 0; j < n8; j++, bit <<= 1) {
-						const int e = list[kc + k8 + j];
-						const float4 ra = rec[e * 3], rb = rec[e * 3 + 1], rc = rec[e * 3 + 2];
-						const float dx = __fsub_rn(ra.x, pxf), dy = __fsub_rn(ra.y, pyf);
-						const float q = __fmaf_rn(dx, __fmul_rn(dx, ra.z), __fmul_rn(dy, __fmul_rn(dy, rb.x)));
-						const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(dy, __fmul_rn(dx, ra.w)));
-						const float alpha = fminf(0.99f, __fmul_rn(rb.y, expf(power)));
-						const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
-						const bool ok = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);     // forward.cu:330-340
-						const bool sat = ok && (test_T < 0.0001f);                               // forward.cu:341-346
-						done = done || sat;
-						if (ok && !sat) {
-							C0 = __fmaf_rn(T, __fmul_rn(alpha, rb.z), C0);
-							C1 = __fmaf_rn(T, __fmul_rn(alpha, rb.w), C1);
-							C2 = __fmaf_rn(T, __fmul_rn(alpha, rc.x), C2);
-							Dp = __fmaf_rn(T, __fmul_rn(alpha, rc.y), Dp);
-							T = test_T;
-							last_contributor = pos1 + (uint32_t)e;
-							usedbits |= bit;
-						}
+					// two survivors per iteration: everything up to alpha is independent of the blend state, so the two
+					// exponentials share the packed steps of exp2x; the blend itself stays in list order
+					for (int j = 0; j < n8; j += 2, bit <<= 2) {
+						const bool two = j + 1 < n8;                                     // warp-uniform
+						const int e0 = list[kc + k8 + j], e1 = two ? list[kc + k8 + j + 1] : e0;
+						const float4 ra0 = rec[e0 * 3], rb0 = rec[e0 * 3 + 1], ra1 = rec[e1 * 3], rb1 = rec[e1 * 3 + 1];
+						float dx0, dy0, dx1, dy1;
+						up(sub2(pk(ra0.x, ra0.y), pxy2), dx0, dy0);
+						up(sub2(pk(ra1.x, ra1.y), pxy2), dx1, dy1);
+						const float q0 = __fmaf_rn(dx0, __fmul_rn(dx0, ra0.z), __fmul_rn(dy0, __fmul_rn(dy0, rb0.x)));
+						const float q1 = __fmaf_rn(dx1, __fmul_rn(dx1, ra1.z), __fmul_rn(dy1, __fmul_rn(dy1, rb1.x)));
+						const float power0 = __fmaf_rn(q0, -0.5f, -__fmul_rn(dy0, __fmul_rn(dx0, ra0.w)));
+						const float power1 = __fmaf_rn(q1, -0.5f, -__fmul_rn(dy1, __fmul_rn(dx1, ra1.w)));
+						float G0, G1;
+						exp2x(power0, power1, G0, G1);
+						const float alpha0 = fminf(0.99f, __fmul_rn(rb0.y, G0)), alpha1 = fminf(0.99f, __fmul_rn(rb1.y, G1));
+						// forward.cu:330-351 for one list entry; C01 = (C0, C1), C2D = (C2, depth): same roundings, packed
+						auto blend = [&](int e, float power, float alpha, const float4& rb, uint32_t ubit) {
+							const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
+							const bool ok = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);     // forward.cu:330-340
+							const bool sat = ok && (test_T < 0.0001f);                               // forward.cu:341-346
+							done = done || sat;
+							if (ok && !sat) {
+								const float4 rc = rec[e * 3 + 2];
+								const p2 a2 = pk1(alpha), T2 = pk1(T);
+								C01 = fma2(T2, mul2(a2, pk(rb.z, rb.w)), C01);
+								C2D = fma2(T2, mul2(a2, pk(rc.x, rc.y)), C2D);
+								T = test_T;
+								last_contributor = pos1 + (uint32_t)e;
+								usedbits |= ubit;
+							}
+						};
+						blend(e0, power0, alpha0, rb0, bit);
+						if (two) blend(e1, power1, alpha1, rb1, bit << 1);
 					}
 					if (__all_sync(FULL, done)) { warp_done = true; break; }
 				}
@@ -209,6 +231,8 @@ __global__ void __launch_bounds__(FWD_THREADS) render_fwd_kernel(RenderArgs a)
 		const size_t pid = (size_t)a.W * pix_y + pix_x, HW = (size_t)a.H * a.W;
 		a.final_T[pid] = T;
 		a.n_contrib[pid] = last_contributor;
+		float C0, C1, C2, Dp;
+		up(C01, C0, C1); up(C2D, C2, Dp);
 		a.out_color[pid] = __fmaf_rn(T, a.bg[0], C0);
 		a.out_color[HW + pid] = __fmaf_rn(T, a.bg[1], C1);
 		a.out_color[2 * HW + pid] = __fmaf_rn(T, a.bg[2], C2);
@@ -216,7 +240,26 @@ __global__ void __launch_bounds__(FWD_THREADS) render_fwd_kernel(RenderArgs a)
 	}
 }
 
+// exp2x (render_common.cuh) against libdevice expf over every float bit pattern in [first, first + count): counts lanes that differ
+__global__ void __launch_bounds__(256) exp_selftest_kernel(uint32_t first, uint32_t count, unsigned long long* __restrict__ mismatches)
+{
+	unsigned long long bad = 0;
+	for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < count; i += gridDim.x * 256u) {
+		const float xa = __uint_as_float(first + i), xb = __uint_as_float(first + (count - 1u - i));
+		float ea, eb;
+		exp2x(xa, xb, ea, eb);
+		bad += (__float_as_uint(ea) != __float_as_uint(expf(xa))) + (__float_as_uint(eb) != __float_as_uint(expf(xb)));
+	}
+	if (bad) atomicAdd(mismatches, bad);
+}
+
 }  // namespace
+
+int launch_exp_selftest(cudaStream_t stream, uint32_t first_bits, uint32_t count, unsigned long long* mismatches)
+{
+	count_launch(), exp_selftest_kernel<<<148 * 8, 256, 0, stream>>>(first_bits, count, mismatches);
+	return check_launch("exp_selftest", stream, false);
+}
 
 int launch_render_fwd(cudaStream_t stream, const RenderArgs& a)
 {
@@ -225,7 +268,8 @@ int launch_render_fwd(cudaStream_t stream, const RenderArgs& a)
 	case MODE_PACKED_LDG: count_launch(), render_fwd_kernel<MODE_PACKED_LDG><<<grid, FWD_THREADS, 0, stream>>>(a); break;
 	case MODE_PACKED_TMA: count_launch(), render_fwd_kernel<MODE_PACKED_TMA><<<grid, FWD_THREADS, 0, stream>>>(a); break;
 	case MODE_GATHER_LDG: count_launch(), render_fwd_kernel<MODE_GATHER_LDG><<<grid, FWD_THREADS, 0, stream>>>(a); break;
-	default: count_launch(), render_fwd_kernel<MODE_GATHER_TMA><<<grid, FWD_THREADS, 0, stream>>>(a); break;
+	case MODE_GATHER_TMA: count_launch(), render_fwd_kernel<MODE_GATHER_TMA><<<grid, FWD_THREADS, 0, stream>>>(a); break;
+	default: count_launch(), render_fwd_kernel<MODE_GATHER_ASYNC><<<grid, FWD_THREADS, 0, stream>>>(a); break;
 	}
 	return check_launch("render_fwd", stream, false);
 }

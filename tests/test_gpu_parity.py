@@ -63,11 +63,11 @@ def check_against_ref(fw, g, ref, N_r, color_r, radii_r, depth_r, g_r, dpix=None
         assert rel_err(a, b)[0] <= RTOL_GRAD
 
 
-@pytest.mark.parametrize("name,variant", [("C1", "2"), ("C1", "1"), ("C1", "3"), ("C1", "0"), ("C2", "2"), ("C2", "1"), ("C2", "3"), ("C2", "0"),
-                                          ("C3", "2"), ("C3", "1")])
+@pytest.mark.parametrize("name,variant", [("C1", "4"), ("C1", "2"), ("C1", "1"), ("C1", "3"), ("C1", "0"), ("C2", "4"), ("C2", "2"), ("C2", "1"), ("C2", "3"), ("C2", "0"),
+                                          ("C3", "4"), ("C3", "2"), ("C3", "1")])
 def test_configs_match_reference_cuda(device, refcuda, monkeypatch, name, variant):
     """BASELINE.json configs 1-3 at full size against the reference CUDA on the same GPU, in every staging mode
-    (2 = TMA gather, the default; 1 = packed TMA; 3 / 0 = their plain-load cross-checks)."""
+    (4 = cp.async gather, the default; 2 = TMA gather; 1 = packed TMA; 3 / 0 = their plain-load cross-checks)."""
     monkeypatch.setenv("RAIN_RAST_VARIANT", variant)
     cfg = CONFIGS[name]
     sc = make_scene(cfg["P"], cfg["D"]).to(device); cam = make_camera(0, 1, cfg["W"], cfg["H"]).to(device)
@@ -338,3 +338,18 @@ def test_golden_knn_vectors(device):
     for f in files:
         z = np.load(f)
         assert np.array_equal(_C.distCUDA2(torch.from_numpy(z["points"]).to(device)).cpu().numpy(), z["dist2"]), f
+
+
+def test_packed_exp_is_bit_identical_to_libdevice_expf(device):
+    """exp2x (csrc/render_common.cuh) restates the instruction sequence nvcc emits for the reference's expf
+    (forward.cu:336, backward.cu:488) with its packable steps packed; the forward's bit-exact n_contrib / final_T /
+    colour parity needs it to agree with libdevice expf in every bit for every x <= 0: checked exhaustively."""
+    import ctypes
+    lib = _lib.load()
+    bad = torch.zeros(1, dtype=torch.int64, device=device)
+    stream = torch.cuda.current_stream().cuda_stream
+    # +0, then every negative float from -0 through -inf (0x80000000 .. 0xFF800000)
+    _lib.check(lib.rr_selftest_exp(stream, 0, 1, bad.data_ptr()), "selftest")
+    _lib.check(lib.rr_selftest_exp(stream, 0x80000000, 0x7F800001, bad.data_ptr()), "selftest")
+    torch.cuda.synchronize()
+    assert int(bad.item()) == 0
