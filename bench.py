@@ -1,6 +1,6 @@
 """bench.py — fwd+bwd renders/sec of the splat rasterizer on B200 (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload C3|C2|C1]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload C3|C2|C1|C4]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
 
 A "step": every rank renders VIEWS_PER_STEP different camera views of the same synthetic scene forward + backward
@@ -331,7 +331,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="C3", choices=["C1", "C2", "C3"])
+    ap.add_argument("--workload", default="C3", choices=["C1", "C2", "C3", "C4"])
     ap.add_argument("--cpu-renders", type=int, default=2, help="renders of the workload timed on the host for cpu_baseline (0 = skip)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -378,10 +378,10 @@ def main():
         "metric": METRIC, "value": round(r["value"], 2), "unit": "renders/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": round(r["ms"] / args.steps, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": f"{args.workload}: {P} random Gaussians, {cfg['W']}x{cfg['H']}, SH degree {cfg['D']} (BASELINE.json configs[2])",
+        "config": {"workload": f"{args.workload}: {P} random Gaussians, {cfg['W']}x{cfg['H']}, SH degree {cfg['D']} (BASELINE.json configs[{int(args.workload[1]) - 1}])",
                    "views_per_step_per_gpu": VIEWS_PER_STEP, "global_views_per_step": VIEWS_PER_STEP * world, "num_rendered_per_view": N,
                    "parallelism": f"view-sharded dp{world}, one f32 all-reduce of {r['bucket_bytes']} B per step" if world > 1 else "single GPU",
-                   "l2": "inputs larger than L2: 236 MB of Gaussian parameters + 236 MB gradient bucket per render, different cameras every step"},
+                   "l2": f"inputs larger than L2: {P * 59 * 4 // 1000000} MB of Gaussian parameters + {P * 59 * 4 // 1000000} MB gradient bucket per render, different cameras every step"},
         "e2e": {"value": round(r["e2e_value"], 2), "unit": "renders/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
                 "ms_per_step": round(r["ms_e2e"] / args.steps, 4), "loss": r["loss"]},
         "gpu_launches": int(r["launches"]),
