@@ -133,6 +133,7 @@ def build_workload(name, dev, rank):
 
 def run_ours(args, rank, world, local):
     from rain_b200 import _lib, multiview as mv
+    from rain_b200.loss import l2_loss_grad
     dev = torch.device("cuda", local)
     lib = _lib.load()
     cfg, sc_h, cams_h, targets_h = build_workload(args.workload, dev, rank)
@@ -152,7 +153,7 @@ def run_ours(args, rank, world, local):
     slot = {}
 
     def grad_resident(v, color, depth):
-        return torch.sub(color, targets_d[slot[v]])
+        return l2_loss_grad(color, targets_d[slot[v]])            # dL/dcolor = colour - target, one fused pass (csrc/loss.cu)
 
     def step_resident(s):
         ids = views_of(s)
@@ -217,10 +218,7 @@ def run_ours(args, rank, world, local):
         loss_dev.zero_()
 
         def grad_e2e(v, color, depth):
-            d = torch.sub(color, feed.wait(slot[v]))
-            dv = d.view(-1)
-            loss_dev.add_(torch.dot(dv, dv), alpha=0.5)
-            return d
+            return l2_loss_grad(color, feed.wait(slot[v]), loss_dev)     # gradient + 0.5 * sum d^2 into the step's loss scalar
         bucket.filled = False
         mv.render_views_fwd_bwd(params, cams_step, ids, bucket, grad_e2e, **kw)
         mv.allreduce_bucket(bucket)

@@ -95,6 +95,18 @@ int rr_selftest_exp(void* stream, uint32_t first_bits, uint32_t count, unsigned 
 int rr_mark_visible(void* stream, int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present);
 
 /* replaces distCUDA2 / SimpleKNN::knn (simple-knn/spatial.cu:4-15, simple_knn.cu:174-210); points f32[P,3] -> out f32[P] */
+/* ---- image loss right after the render -------------------------------------------------------
+ * rr_loss_l1_ssim replaces, for the rendered image, utils/loss_utils.py:6-7 (l1_loss) and :23-51 (ssim / _ssim, window 11,
+ * sigma 1.5, zero padding, size_average=True) plus train.py:112-113 and their autograd backward:
+ *   out3 = { Ll1, ssim, (1 - lambda) * Ll1 + lambda * (1 - ssim) }            (device, 3 floats; may be null)
+ *   dL_dimage[C,H,W] = d loss / d image                                          (device; may be null: forward only)
+ * image and gt are [C,H,W] f32 device arrays; ws is rr_loss_ws_bytes(C,H,W) bytes of device scratch.
+ * rr_loss_l2: dL_dimage = image - gt and *loss_accum += 0.5 * sum (image - gt)^2 (loss_accum may be null) in one pass. */
+size_t rr_loss_ws_bytes(int C, int H, int W);
+int rr_loss_l1_ssim(void* stream, int C, int H, int W, const float* image, const float* gt, float lambda_dssim,
+	void* ws, size_t ws_bytes, float* out3, float* dL_dimage);
+int rr_loss_l2(void* stream, int64_t n, const float* image, const float* gt, float* dL_dimage, float* loss_accum);
+
 size_t rr_dist2_ws_bytes(int P);
 int rr_dist2(void* stream, int P, const float* points, float* out, void* ws, size_t ws_bytes);
 

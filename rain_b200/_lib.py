@@ -45,6 +45,9 @@ SIGNATURES = {
                          _i, _i, _i]),
     "rr_mark_visible": (_i, [_vp, _i, _vp, _vp, _vp, _vp]),
     "rr_selftest_exp": (_i, [_vp, _c.c_uint32, _c.c_uint32, _vp]),
+    "rr_loss_ws_bytes": (_sz, [_i, _i, _i]),
+    "rr_loss_l1_ssim": (_i, [_vp, _i, _i, _i, _vp, _vp, _c.c_float, _vp, _sz, _vp, _vp]),
+    "rr_loss_l2": (_i, [_vp, _i64, _vp, _vp, _vp, _vp]),
     "rr_dist2_ws_bytes": (_sz, [_i]),
     "rr_dist2": (_i, [_vp, _i, _vp, _vp, _vp, _sz]),
     "rr_sort_ws_bytes": (_sz, [_i64, _i, _i, _i]),

@@ -348,6 +348,26 @@ int rr_mark_visible(void* stream_, int P, const float* means3D, const float* vie
 	return launch_mark_visible(reinterpret_cast<cudaStream_t>(stream_), P, means3D, viewmatrix, present);
 }
 
+size_t rr_loss_ws_bytes(int C, int H, int W) { return (C > 0 && H > 0 && W > 0) ? loss_ws_bytes(C, H, W) : 256; }
+
+int rr_loss_l1_ssim(void* stream_, int C, int H, int W, const float* image, const float* gt, float lambda_dssim,
+	void* ws, size_t ws_bytes, float* out3, float* dL_dimage)
+{
+	if (C <= 0 || H <= 0 || W <= 0) { set_error("bad image size C=%d H=%d W=%d", C, H, W); return -1; }
+	if (bad_ptr(image, "image") || bad_ptr(gt, "gt") || bad_ptr(ws, "ws")) return -1;
+	if (!out3 && !dL_dimage) { set_error("nothing to compute: out3 and dL_dimage are both null"); return -1; }
+	if (ws_bytes < loss_ws_bytes(C, H, W)) { set_error("loss workspace too small: %zu < %zu", ws_bytes, loss_ws_bytes(C, H, W)); return -1; }
+	return launch_loss_l1_ssim(reinterpret_cast<cudaStream_t>(stream_), C, H, W, image, gt, lambda_dssim, ws, out3, dL_dimage);
+}
+
+int rr_loss_l2(void* stream_, int64_t n, const float* image, const float* gt, float* dL_dimage, float* loss_accum)
+{
+	if (n < 0) { set_error("bad element count %lld", (long long)n); return -1; }
+	if (n == 0) return 0;
+	if (bad_ptr(image, "image") || bad_ptr(gt, "gt") || bad_ptr(dL_dimage, "dL_dimage")) return -1;
+	return launch_loss_l2(reinterpret_cast<cudaStream_t>(stream_), (size_t)n, image, gt, dL_dimage, loss_accum);
+}
+
 size_t rr_dist2_ws_bytes(int P) { return knn_ws_bytes(P); }
 int rr_dist2(void* stream_, int P, const float* points, float* out, void* ws, size_t ws_bytes)
 {

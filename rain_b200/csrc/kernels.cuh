@@ -78,6 +78,11 @@ struct PreprocessBwdArgs {
 };
 int launch_preprocess_bwd(cudaStream_t, const PreprocessBwdArgs&);
 
+// loss.cu
+size_t loss_ws_bytes(int C, int H, int W);
+int launch_loss_l1_ssim(cudaStream_t, int C, int H, int W, const float* img, const float* gt, float lambda, void* ws, float* out3, float* dL_dimg);
+int launch_loss_l2(cudaStream_t, size_t n, const float* img, const float* gt, float* dL_dimg, float* loss_acc);
+
 // knn.cu
 size_t knn_ws_bytes(int P);
 int launch_dist2(cudaStream_t, int P, const float* points, float* out, void* ws, size_t ws_bytes);
