@@ -107,6 +107,22 @@ int rr_loss_l1_ssim(void* stream, int C, int H, int W, const float* image, const
 	void* ws, size_t ws_bytes, float* out3, float* dL_dimage);
 int rr_loss_l2(void* stream, int64_t n, const float* image, const float* gt, float* dL_dimage, float* loss_accum);
 
+/* ---- parameter step after the backward ------------------------------------------------
+ * One pass per Gaussian: chain rule through the caller-side activations of scene/gaussian_model.py:85-105 (exp, sigmoid,
+ * F.normalize, cat), torch.optim.Adam(..., eps=1e-15).step() over the six parameter groups of training_setup
+ * (scene/gaussian_model.py:139-157, train.py:146), and the activated inputs of the next render
+ * (gaussian_renderer/__init__.py:37-60).
+ *   xyz[P,3] f_dc[P,1,3] f_rest[P,M-1,3] opacity[P,1] scaling[P,3] rotation[P,4]: raw leaf tensors, updated in place
+ *   exp_avg, exp_avg_sq, grads: flat [P*(11+3M)] f32 in the gradient-bucket layout
+ *       means3D [P,3] | sh [P,M,3] | opacity [P] | scales [P,3] | rotations [P,4]
+ *     grads are w.r.t. the ACTIVATED values (what rr_backward writes / accumulates); the moments are updated in place
+ *   hyper: HOST array { lr_xyz, lr_f_dc, lr_f_rest, lr_opacity, lr_scaling, lr_rotation, beta1, beta2, eps }
+ *   step: 1-based Adam step count (bias correction 1 - beta^step)
+ *   shs_out[P,M,3], opacities_out[P,1], scales_out[P,3], rotations_out[P,4]: activated values after the update (each may be null) */
+int rr_param_step(void* stream, int P, int M, float* xyz, float* f_dc, float* f_rest, float* opacity, float* scaling, float* rotation,
+	float* exp_avg, float* exp_avg_sq, const float* grads, const float* hyper, int step,
+	float* shs_out, float* opacities_out, float* scales_out, float* rotations_out);
+
 size_t rr_dist2_ws_bytes(int P);
 int rr_dist2(void* stream, int P, const float* points, float* out, void* ws, size_t ws_bytes);
 

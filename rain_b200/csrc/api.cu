@@ -368,6 +368,20 @@ int rr_loss_l2(void* stream_, int64_t n, const float* image, const float* gt, fl
 	return launch_loss_l2(reinterpret_cast<cudaStream_t>(stream_), (size_t)n, image, gt, dL_dimage, loss_accum);
 }
 
+int rr_param_step(void* stream_, int P, int M, float* xyz, float* f_dc, float* f_rest, float* opacity, float* scaling, float* rotation,
+	float* exp_avg, float* exp_avg_sq, const float* grads, const float* hyper, int step,
+	float* shs_out, float* opacities_out, float* scales_out, float* rotations_out)
+{
+	if (P == 0) return 0;
+	if (P < 0 || M < 1) { set_error("bad sizes P=%d M=%d", P, M); return -1; }
+	if (step < 1) { set_error("Adam step count must be >= 1, got %d", step); return -1; }
+	if (bad_ptr(xyz, "xyz") || bad_ptr(f_dc, "f_dc") || bad_ptr(opacity, "opacity") || bad_ptr(scaling, "scaling") || bad_ptr(rotation, "rotation") ||
+		bad_ptr(exp_avg, "exp_avg") || bad_ptr(exp_avg_sq, "exp_avg_sq") || bad_ptr(grads, "grads") || bad_ptr(hyper, "hyper")) return -1;
+	if (M > 1 && bad_ptr(f_rest, "f_rest")) return -1;
+	return launch_param_step(reinterpret_cast<cudaStream_t>(stream_), P, M, xyz, f_dc, f_rest, opacity, scaling, rotation, exp_avg, exp_avg_sq, grads, hyper, step,
+		shs_out, opacities_out, scales_out, rotations_out);
+}
+
 size_t rr_dist2_ws_bytes(int P) { return knn_ws_bytes(P); }
 int rr_dist2(void* stream_, int P, const float* points, float* out, void* ws, size_t ws_bytes)
 {

@@ -83,6 +83,10 @@ size_t loss_ws_bytes(int C, int H, int W);
 int launch_loss_l1_ssim(cudaStream_t, int C, int H, int W, const float* img, const float* gt, float lambda, void* ws, float* out3, float* dL_dimg);
 int launch_loss_l2(cudaStream_t, size_t n, const float* img, const float* gt, float* dL_dimg, float* loss_acc);
 
+// param_step.cu
+int launch_param_step(cudaStream_t, int P, int M, float* xyz, float* f_dc, float* f_rest, float* opacity, float* scaling, float* rotation,
+	float* m, float* v, const float* grads, const float* hyper, int step, float* shs_out, float* opacities_out, float* scales_out, float* rotations_out);
+
 // knn.cu
 size_t knn_ws_bytes(int P);
 int launch_dist2(cudaStream_t, int P, const float* points, float* out, void* ws, size_t ws_bytes);

@@ -1,0 +1,126 @@
+// Parameter step after the (all-reduced) backward: the chain rule through the caller-side
+// activations, the Adam update of the six leaf tensors, and the re-activation for the next render, in one pass over the
+// 59 floats of a Gaussian.  Replaces, per training iteration of the reference:
+//   * autograd backward of scene/gaussian_model.py:85-105 — exp (get_scaling), sigmoid (get_opacity), F.normalize
+//     (get_rotation), torch.cat (get_features) — ~10 elementwise kernels and a 192 B/Gaussian cat copy each way;
+//   * torch.optim.Adam(l, lr=0.0, eps=1e-15).step() over the six parameter groups of training_setup
+//     (scene/gaussian_model.py:139-157; train.py:146): betas (0.9, 0.999), no weight decay, no amsgrad;
+//   * the forward activations of the next render() call (gaussian_renderer/__init__.py:37-60).
+// Gradients arrive in the flat bucket the backward accumulates into (multiview.py: means3D | sh | opacity | scales |
+// rotations, w.r.t. the ACTIVATED values); Adam moments use the same layout.  Every rank applies the same step to its
+// replica after the all-reduce, so replicas stay bit-identical without a parameter broadcast.
+// Traffic: 4 reads + 4 writes of 59 floats per Gaussian (1.9 KB): HBM bound, ~0.29 ms at 1M Gaussians.
+#include <cmath>
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace rr {
+
+namespace {
+
+struct AdamScalars { float lr[6]; float beta1, beta2, eps, inv_bc1, inv_sqrt_bc2; };   // groups: xyz, f_dc, f_rest, opacity, scaling, rotation
+
+// torch.optim.Adam single-tensor step (torch/optim/adam.py _single_tensor_adam, default flags):
+//   m = b1 m + (1-b1) g; v = b2 v + (1-b2) g^2; p -= (lr / bc1) * m / (sqrt(v) / sqrt(bc2) + eps)
+__device__ __forceinline__ float adam(float p, float g, float& m, float& v, float lr, const AdamScalars& h)
+{
+	m = fmaf(h.beta1, m, (1.0f - h.beta1) * g);
+	v = fmaf(h.beta2, v, (1.0f - h.beta2) * g * g);
+	const float denom = sqrtf(v) * h.inv_sqrt_bc2 + h.eps;
+	return p - lr * h.inv_bc1 * (m / denom);
+}
+
+// SH coefficients: element i of the [P, M, 3] gradient segment belongs to f_dc (coefficient 0) or f_rest; the updated
+// value also goes to the concatenated [P, M, 3] render input (torch.cat((f_dc, f_rest), dim=1)).
+__global__ void __launch_bounds__(256) param_step_sh_kernel(size_t n /*P*M*3*/, int M3 /*M*3*/, float* __restrict__ f_dc, float* __restrict__ f_rest,
+	float* __restrict__ m, float* __restrict__ v, const float* __restrict__ g, AdamScalars h, float* __restrict__ shs_out)
+{
+	for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (size_t)gridDim.x * 256) {
+		const size_t p = i / (size_t)M3;
+		const int j = (int)(i - p * (size_t)M3);
+		float* dst = j < 3 ? f_dc + p * 3 + j : f_rest + p * (size_t)(M3 - 3) + (j - 3);
+		float mm = m[i], vv = v[i];
+		const float out = adam(*dst, __ldg(g + i), mm, vv, j < 3 ? h.lr[1] : h.lr[2], h);
+		*dst = out; m[i] = mm; v[i] = vv;
+		if (shs_out) shs_out[i] = out;
+	}
+}
+
+// one thread per Gaussian: xyz (3), opacity (1), scaling (3), rotation (4)
+__global__ void __launch_bounds__(256) param_step_geom_kernel(int P, float* __restrict__ xyz, float* __restrict__ opacity, float* __restrict__ scaling,
+	float* __restrict__ rotation, float* __restrict__ m_xyz, float* __restrict__ v_xyz, float* __restrict__ m_op, float* __restrict__ v_op,
+	float* __restrict__ m_sc, float* __restrict__ v_sc, float* __restrict__ m_rot, float* __restrict__ v_rot,
+	const float* __restrict__ g_xyz, const float* __restrict__ g_op, const float* __restrict__ g_sc, const float* __restrict__ g_rot, AdamScalars h,
+	float* __restrict__ opacities_out, float* __restrict__ scales_out, float* __restrict__ rotations_out)
+{
+	const int p = blockIdx.x * 256 + threadIdx.x;
+	if (p >= P) return;
+	#pragma unroll
+	for (int c = 0; c < 3; c++) {                                   // xyz: identity activation
+		const size_t i = (size_t)p * 3 + c;
+		float mm = m_xyz[i], vv = v_xyz[i];
+		xyz[i] = adam(xyz[i], g_xyz[i], mm, vv, h.lr[0], h);
+		m_xyz[i] = mm; v_xyz[i] = vv;
+	}
+	{                                                               // opacity = sigmoid(o): d/do = s (1 - s)
+		const float o = opacity[p], s = 1.0f / (1.0f + expf(-o));
+		float mm = m_op[p], vv = v_op[p];
+		const float on = adam(o, g_op[p] * s * (1.0f - s), mm, vv, h.lr[3], h);
+		opacity[p] = on; m_op[p] = mm; v_op[p] = vv;
+		if (opacities_out) opacities_out[p] = 1.0f / (1.0f + expf(-on));
+	}
+	#pragma unroll
+	for (int c = 0; c < 3; c++) {                                   // scales = exp(s): d/ds = exp(s)
+		const size_t i = (size_t)p * 3 + c;
+		const float s = scaling[i];
+		float mm = m_sc[i], vv = v_sc[i];
+		const float sn = adam(s, g_sc[i] * expf(s), mm, vv, h.lr[4], h);
+		scaling[i] = sn; m_sc[i] = mm; v_sc[i] = vv;
+		if (scales_out) scales_out[i] = expf(sn);
+	}
+	{                                                               // rotations = q / max(|q|, 1e-12) (F.normalize): d/dq = (g - qh (qh.g)) / |q|
+		// the bucket segments start at 55 P floats: only the leaf tensor itself is known to be 16-byte aligned
+		const size_t r4 = (size_t)p * 4;
+		const float4 q = reinterpret_cast<const float4*>(rotation)[p], g = make_float4(g_rot[r4], g_rot[r4 + 1], g_rot[r4 + 2], g_rot[r4 + 3]);
+		const float nrm = fmaxf(sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w), 1e-12f), inv = 1.0f / nrm;
+		const float4 qh = make_float4(q.x * inv, q.y * inv, q.z * inv, q.w * inv);
+		const float dot = qh.x * g.x + qh.y * g.y + qh.z * g.z + qh.w * g.w;
+		const float4 d = make_float4((g.x - qh.x * dot) * inv, (g.y - qh.y * dot) * inv, (g.z - qh.z * dot) * inv, (g.w - qh.w * dot) * inv);
+		float4 mm = make_float4(m_rot[r4], m_rot[r4 + 1], m_rot[r4 + 2], m_rot[r4 + 3]), vv = make_float4(v_rot[r4], v_rot[r4 + 1], v_rot[r4 + 2], v_rot[r4 + 3]);
+		float4 qn;
+		qn.x = adam(q.x, d.x, mm.x, vv.x, h.lr[5], h); qn.y = adam(q.y, d.y, mm.y, vv.y, h.lr[5], h);
+		qn.z = adam(q.z, d.z, mm.z, vv.z, h.lr[5], h); qn.w = adam(q.w, d.w, mm.w, vv.w, h.lr[5], h);
+		reinterpret_cast<float4*>(rotation)[p] = qn;
+		m_rot[r4] = mm.x; m_rot[r4 + 1] = mm.y; m_rot[r4 + 2] = mm.z; m_rot[r4 + 3] = mm.w;
+		v_rot[r4] = vv.x; v_rot[r4 + 1] = vv.y; v_rot[r4 + 2] = vv.z; v_rot[r4 + 3] = vv.w;
+		if (rotations_out) {
+			const float i2 = 1.0f / fmaxf(sqrtf(qn.x * qn.x + qn.y * qn.y + qn.z * qn.z + qn.w * qn.w), 1e-12f);
+			reinterpret_cast<float4*>(rotations_out)[p] = make_float4(qn.x * i2, qn.y * i2, qn.z * i2, qn.w * i2);
+		}
+	}
+}
+
+}  // namespace
+
+int launch_param_step(cudaStream_t stream, int P, int M, float* xyz, float* f_dc, float* f_rest, float* opacity, float* scaling, float* rotation,
+	float* m, float* v, const float* grads, const float* hyper /*host: lr[6], beta1, beta2, eps*/, int step,
+	float* shs_out, float* opacities_out, float* scales_out, float* rotations_out)
+{
+	AdamScalars h;
+	for (int i = 0; i < 6; i++) h.lr[i] = hyper[i];
+	h.beta1 = hyper[6]; h.beta2 = hyper[7]; h.eps = hyper[8];
+	// bias corrections as torch computes them (python floats, i.e. double): 1 - beta ** step
+	h.inv_bc1 = (float)(1.0 / (1.0 - std::pow((double)hyper[6], (double)step)));
+	h.inv_sqrt_bc2 = (float)(1.0 / std::sqrt(1.0 - std::pow((double)hyper[7], (double)step)));
+	const size_t Pz = (size_t)P, nsh = Pz * M * 3;
+	// bucket layout: means3D [P,3] | sh [P,M,3] | opacity [P] | scales [P,3] | rotations [P,4]
+	const size_t o_sh = 3 * Pz, o_op = o_sh + nsh, o_sc = o_op + Pz, o_rot = o_sc + 3 * Pz;
+	const size_t blocks = (nsh + 255) / 256;
+	count_launch(), param_step_sh_kernel<<<(unsigned)(blocks < 148u * 16u ? blocks : 148u * 16u), 256, 0, stream>>>(nsh, M * 3, f_dc, f_rest, m + o_sh, v + o_sh,
+		grads + o_sh, h, shs_out);
+	count_launch(), param_step_geom_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, xyz, opacity, scaling, rotation, m, v, m + o_op, v + o_op, m + o_sc, v + o_sc,
+		m + o_rot, v + o_rot, grads, grads + o_op, grads + o_sc, grads + o_rot, h, opacities_out, scales_out, rotations_out);
+	return check_launch("param_step", stream, false);
+}
+
+}  // namespace rr

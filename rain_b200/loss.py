@@ -31,6 +31,13 @@ def _run(image, gt, lambda_dssim, want_grad):
     return out3, grad
 
 
+def loss_and_grad(image, gt, lambda_dssim=0.2):
+    """({Ll1, ssim, loss} as a 3-float device tensor, d loss / d image) without autograd bookkeeping — what a grad_fn of
+    rain_b200.multiview.render_views_fwd_bwd returns as dL/dcolor."""
+    image, gt = _check(image, gt)
+    return _run(image, gt, lambda_dssim, True)
+
+
 class _TrainingLoss(torch.autograd.Function):
     @staticmethod
     def forward(ctx, image, gt, lambda_dssim):

@@ -1,0 +1,51 @@
+"""Host side of the fused parameter step (csrc/param_step.cu, rr_param_step):
+activation backward + torch.optim.Adam semantics + re-activation for the next render in one pass per Gaussian, on the flat
+gradient bucket that rain_b200.multiview accumulates and all-reduces.  Mirrors GaussianModel.training_setup /
+optimizer.step() of the reference (scene/gaussian_model.py:139-157, train.py:146).  CUDA tensors only."""
+import ctypes
+
+import torch
+
+from . import _lib
+
+GROUPS = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")
+
+
+class GaussianParamStep:
+    """leaves: dict(xyz[P,3], f_dc[P,1,3], f_rest[P,M-1,3], opacity[P,1], scaling[P,3], rotation[P,4]) raw CUDA tensors
+    (updated in place); lrs: dict over GROUPS (scene/gaussian_model.py:144-151)."""
+
+    def __init__(self, leaves, lrs, betas=(0.9, 0.999), eps=1e-15):
+        self.leaves = {k: leaves[k] for k in GROUPS}
+        for k, t in self.leaves.items():
+            if not t.is_cuda:
+                raise RuntimeError(f"rain_b200 has no CPU path: leaf '{k}' must be a CUDA tensor")
+            if t.dtype != torch.float32 or not t.is_contiguous():
+                raise RuntimeError(f"leaf '{k}' must be contiguous float32")
+        self.P = int(self.leaves["xyz"].shape[0])
+        self.M = 1 + int(self.leaves["f_rest"].shape[1])
+        dev = self.leaves["xyz"].device
+        n = self.P * (11 + 3 * self.M)
+        self.exp_avg = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.lrs = dict(lrs)
+        self.betas, self.eps, self.steps = betas, eps, 0
+        P, M = self.P, self.M
+        self.activated = dict(means3D=self.leaves["xyz"], shs=torch.empty(P, M, 3, device=dev), opacities=torch.empty(P, 1, device=dev),
+                              scales=torch.empty(P, 3, device=dev), rotations=torch.empty(P, 4, device=dev))
+
+    def step(self, grads_flat):
+        """grads_flat: flat f32 [P*(11+3M)] in the bucket layout (w.r.t. the activated values).  Returns the activated
+        inputs of the next render: dict(means3D, shs, opacities, scales, rotations)."""
+        lib = _lib.load()
+        if not grads_flat.is_cuda or grads_flat.numel() != self.exp_avg.numel():
+            raise RuntimeError("grads_flat must be the CUDA gradient bucket of this parameter set")
+        self.steps += 1
+        hyper = (ctypes.c_float * 9)(*[float(self.lrs[k]) for k in GROUPS], float(self.betas[0]), float(self.betas[1]), float(self.eps))
+        L, A = self.leaves, self.activated
+        with torch.cuda.device(grads_flat.device):
+            _lib.check(lib.rr_param_step(torch.cuda.current_stream().cuda_stream, self.P, self.M, L["xyz"].data_ptr(), L["f_dc"].data_ptr(),
+                                         L["f_rest"].data_ptr() if self.M > 1 else None, L["opacity"].data_ptr(), L["scaling"].data_ptr(), L["rotation"].data_ptr(),
+                                         self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), grads_flat.data_ptr(), hyper, self.steps,
+                                         A["shs"].data_ptr(), A["opacities"].data_ptr(), A["scales"].data_ptr(), A["rotations"].data_ptr()), "rr_param_step")
+        return A
