@@ -31,6 +31,9 @@ import torch.distributed as dist  # noqa: E402
 
 from rain_b200.synthetic import CONFIGS, make_camera, make_grad, make_scene  # noqa: E402
 
+# diagnostics of the end-to-end arm only (never set for a reported number): skip the target-image H2D feed / the per-step host sync
+E2E_DIAG_NO_FEED = os.environ.get("RAIN_E2E_DIAG", "").find("nofeed") >= 0
+E2E_DIAG_NO_SYNC = os.environ.get("RAIN_E2E_DIAG", "").find("nosync") >= 0
 VIEWS_PER_STEP = 8          # views each rank renders per step (BASELINE.json config 4: a 64-view batch over 8 GPUs)
 NUM_CAMERAS = 64            # the view pool (BASELINE.json config 4 uses a 64-view batch)
 METRIC = "fwd+bwd renders/sec (1M Gaussians, 1920x1080) at 1/2/4/8 B200"
@@ -127,7 +130,9 @@ def build_workload(name, dev, rank):
     sc_h = make_scene(cfg["P"], cfg["D"], seed=0)
     cams_h = [make_camera(v, NUM_CAMERAS, cfg["W"], cfg["H"]) for v in range(NUM_CAMERAS)]
     # per-view target images: upstream gradient = colour - target (L2 loss); seeded, pinned on the host for the e2e arm
-    targets_h = [make_grad(cfg["W"], cfg["H"], seed=100 + v).mul_(0.1).add_(0.5).pin_memory() for v in range(VIEWS_PER_STEP)]
+    # stored as 8-bit images, the native form of training photographs (the kernel converts: target = byte / 255)
+    targets_h = [make_grad(cfg["W"], cfg["H"], seed=100 + v).mul_(0.1).add_(0.5).clamp_(0, 1).mul_(255).round_().to(torch.uint8).pin_memory()
+                 for v in range(VIEWS_PER_STEP)]
     return cfg, sc_h, cams_h, targets_h
 
 
@@ -199,17 +204,18 @@ def run_ours(args, rank, world, local):
     # ---------------- end-to-end arm (host buffers -> public API -> host scalar) ----------------
     pinned = [dict(view=c.viewmatrix.pin_memory(), proj=c.projmatrix.pin_memory(), campos=c.campos.pin_memory()) for c in cams_h]
     dev_cam = [dict(view=torch.empty(4, 4, device=dev), proj=torch.empty(4, 4, device=dev), campos=torch.empty(3, device=dev)) for _ in range(VIEWS_PER_STEP)]
-    feed = mv.HostFeed([(3, H, W)] * VIEWS_PER_STEP, dev)     # target images: pinned host -> device on a side stream, overlapped with the renders
+    feed = mv.HostFeed([(3, H, W)] * VIEWS_PER_STEP, dev, dtype=torch.uint8)     # target images: pinned host -> device on a side stream, overlapped with the renders
     loss_dev = torch.zeros(1, device=dev)
     loss_host = torch.zeros(1).pin_memory()
-    h2d = VIEWS_PER_STEP * ((16 + 16 + 3) * 4 + 3 * H * W * 4)
+    h2d = VIEWS_PER_STEP * ((16 + 16 + 3) * 4 + 3 * H * W)      # camera matrices + one 8-bit target image per view
     d2h = 4 + VIEWS_PER_STEP * 8          # loss scalar + num_rendered (8 B, read inside the forward) per view
     from rain_b200.synthetic import Camera
 
     def step_e2e(s):
         ids = views_of(s)
         cams_step = {}
-        feed.stage(targets_h)
+        if not E2E_DIAG_NO_FEED:
+            feed.stage_slot(0, targets_h[0])       # view i+1's image is staged when view i reaches its loss: one short transfer in flight
         for i, v in enumerate(ids):
             for k in ("view", "proj", "campos"):
                 dev_cam[i][k].copy_(pinned[v][k], non_blocking=True)
@@ -218,11 +224,16 @@ def run_ours(args, rank, world, local):
         loss_dev.zero_()
 
         def grad_e2e(v, color, depth):
-            return l2_loss_grad(color, feed.wait(slot[v]), loss_dev)     # gradient + 0.5 * sum d^2 into the step's loss scalar
+            if not E2E_DIAG_NO_FEED and slot[v] + 1 < VIEWS_PER_STEP:
+                feed.stage_slot(slot[v] + 1, targets_h[slot[v] + 1])
+            tgt = targets_d[slot[v]] if E2E_DIAG_NO_FEED else feed.wait(slot[v])
+            return l2_loss_grad(color, tgt, loss_dev)     # gradient + 0.5 * sum d^2 into the step's loss scalar
         bucket.filled = False
         mv.render_views_fwd_bwd(params, cams_step, ids, bucket, grad_e2e, **kw)
         mv.allreduce_bucket(bucket)
         loss_host.copy_(loss_dev, non_blocking=True)
+        if E2E_DIAG_NO_SYNC:
+            return 0.0
         torch.cuda.current_stream().synchronize()
         return float(loss_host.item())
 

@@ -106,6 +106,8 @@ size_t rr_loss_ws_bytes(int C, int H, int W);
 int rr_loss_l1_ssim(void* stream, int C, int H, int W, const float* image, const float* gt, float lambda_dssim,
 	void* ws, size_t ws_bytes, float* out3, float* dL_dimage);
 int rr_loss_l2(void* stream, int64_t n, const float* image, const float* gt, float* dL_dimage, float* loss_accum);
+/* same with the target kept as 8-bit samples (gt = gt_u8 * scale, e.g. scale = 1/255): a quarter of the host->device bytes per image */
+int rr_loss_l2_u8(void* stream, int64_t n, const float* image, const uint8_t* gt_u8, float scale, float* dL_dimage, float* loss_accum);
 
 /* ---- parameter step after the backward ------------------------------------------------
  * One pass per Gaussian: chain rule through the caller-side activations of scene/gaussian_model.py:85-105 (exp, sigmoid,

@@ -235,9 +235,18 @@ int rr_forward_geom(void* stream_, int P, int D, int M, int W, int H,
 	{ Stage st(stream, ST_DEPTH_SORT); which = sort_pairs<uint32_t>(stream, L.key_a, L.key_b, L.val_a, L.val_b, (size_t)P, 0, 32, L.sort_ws, true); }
 	if (which != 0) { if (which > 0) set_error("internal: depth sort landed in the wrong buffer"); return -1; }
 	if (debug && check_launch("depth sort", stream, true)) return -1;
-	{ Stage st(stream, ST_SCAN); if (launch_scan_tiles(stream, P, L.val_a, L.tiles_touched, L.offsets, L.block_sums, L.num_rendered)) return -1; }
-	// num_rendered: u32 on the device, widened on the host side of the copy (the upper half was zeroed above)
-	cudaMemcpyAsync(num_rendered_host, L.num_rendered, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream);
+	// num_rendered reaches the host as a u32 (the upper half of the int64 was zeroed above).  If the word is pinned host
+	// memory (device-addressable under unified addressing) the scan kernel stores it there directly: no copy-engine
+	// transfer that could queue behind the caller's own host->device traffic; otherwise a 4-byte async copy.
+	uint32_t* mapped = nullptr;
+	{
+		cudaPointerAttributes pa;
+		if (cudaPointerGetAttributes(&pa, num_rendered_host) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer)
+			mapped = reinterpret_cast<uint32_t*>(pa.devicePointer);
+		else (void)cudaGetLastError();
+	}
+	{ Stage st(stream, ST_SCAN); if (launch_scan_tiles(stream, P, L.val_a, L.tiles_touched, L.offsets, L.block_sums, L.num_rendered, mapped)) return -1; }
+	if (!mapped) cudaMemcpyAsync(num_rendered_host, L.num_rendered, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream);
 	return check_launch("forward_geom", stream, debug != 0);
 }
 
@@ -365,7 +374,15 @@ int rr_loss_l2(void* stream_, int64_t n, const float* image, const float* gt, fl
 	if (n < 0) { set_error("bad element count %lld", (long long)n); return -1; }
 	if (n == 0) return 0;
 	if (bad_ptr(image, "image") || bad_ptr(gt, "gt") || bad_ptr(dL_dimage, "dL_dimage")) return -1;
-	return launch_loss_l2(reinterpret_cast<cudaStream_t>(stream_), (size_t)n, image, gt, dL_dimage, loss_accum);
+	return launch_loss_l2(reinterpret_cast<cudaStream_t>(stream_), (size_t)n, image, gt, 0, 1.0f, dL_dimage, loss_accum);
+}
+
+int rr_loss_l2_u8(void* stream_, int64_t n, const float* image, const uint8_t* gt_u8, float scale, float* dL_dimage, float* loss_accum)
+{
+	if (n < 0) { set_error("bad element count %lld", (long long)n); return -1; }
+	if (n == 0) return 0;
+	if (bad_ptr(image, "image") || bad_ptr(gt_u8, "gt_u8") || bad_ptr(dL_dimage, "dL_dimage")) return -1;
+	return launch_loss_l2(reinterpret_cast<cudaStream_t>(stream_), (size_t)n, image, gt_u8, 1, scale, dL_dimage, loss_accum);
 }
 
 int rr_param_step(void* stream_, int P, int M, float* xyz, float* f_dc, float* f_rest, float* opacity, float* scaling, float* rotation,

@@ -52,7 +52,8 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_reduce_kernel(int P, const 
 }
 
 // single CTA: exclusive scan of the block sums in place, grand total to *total
-__global__ void __launch_bounds__(SCAN_THREADS) scan_blocksums_kernel(int nb, uint32_t* __restrict__ block_sums, uint32_t* __restrict__ total)
+__global__ void __launch_bounds__(SCAN_THREADS) scan_blocksums_kernel(int nb, uint32_t* __restrict__ block_sums, uint32_t* __restrict__ total,
+	uint32_t* __restrict__ total_host /*host-mapped pinned word or null: the count reaches the host without a copy-engine transfer*/)
 {
 	__shared__ uint32_t s_warp[SCAN_THREADS / 32];
 	uint32_t carry = 0;
@@ -64,7 +65,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_blocksums_kernel(int nb, ui
 		if (i < nb) block_sums[i] = carry + ex;
 		carry += tot;
 	}
-	if (threadIdx.x == 0) *total = carry;
+	if (threadIdx.x == 0) { *total = carry; if (total_host) { *total_host = carry; __threadfence_system(); } }
 }
 
 __global__ void __launch_bounds__(SCAN_THREADS) scan_final_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ tt,
@@ -173,12 +174,13 @@ __global__ void __launch_bounds__(256) export_keys_kernel(uint32_t N, const uint
 
 size_t scan_ws_elems(int P) { return (size_t)(P + SCAN_TILE - 1) / SCAN_TILE + 1; }
 
-int launch_scan_tiles(cudaStream_t stream, int P, const uint32_t* order, const uint32_t* tt, uint32_t* offsets, uint32_t* block_sums, uint32_t* num_rendered_dev)
+int launch_scan_tiles(cudaStream_t stream, int P, const uint32_t* order, const uint32_t* tt, uint32_t* offsets, uint32_t* block_sums, uint32_t* num_rendered_dev,
+	uint32_t* num_rendered_mapped)
 {
 	if (P == 0) { cudaMemsetAsync(num_rendered_dev, 0, sizeof(uint32_t), stream); return 0; }
 	const int nb = (P + SCAN_TILE - 1) / SCAN_TILE;
 	count_launch(), scan_reduce_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, order, tt, block_sums);
-	count_launch(), scan_blocksums_kernel<<<1, SCAN_THREADS, 0, stream>>>(nb, block_sums, num_rendered_dev);
+	count_launch(), scan_blocksums_kernel<<<1, SCAN_THREADS, 0, stream>>>(nb, block_sums, num_rendered_dev, num_rendered_mapped);
 	count_launch(), scan_final_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, order, tt, block_sums, offsets);
 	return check_launch("scan_tiles", stream, false);
 }

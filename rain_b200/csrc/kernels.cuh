@@ -22,7 +22,7 @@ int launch_mark_visible(cudaStream_t, int P, const float* means3D, const float* 
 // binning.cu
 size_t scan_ws_elems(int P);
 int launch_scan_tiles(cudaStream_t, int P, const uint32_t* order, const uint32_t* tiles_touched, uint32_t* offsets /*inclusive, depth order*/,
-	uint32_t* block_sums, uint32_t* num_rendered_dev);
+	uint32_t* block_sums, uint32_t* num_rendered_dev, uint32_t* num_rendered_mapped /*device-visible alias of a pinned host word, or null*/);
 int launch_duplicate(cudaStream_t, int P, const uint32_t* order, const uint32_t* offsets, const uint2* rect, int grid_x,
 	uint32_t* tile_keys /*[N] emission order*/, uint32_t* gaussian_ids /*[N] emission order*/);
 int launch_tile_ranges(cudaStream_t, size_t N, const uint32_t* sorted_tile_keys, uint2* ranges, int num_tiles);
@@ -81,7 +81,7 @@ int launch_preprocess_bwd(cudaStream_t, const PreprocessBwdArgs&);
 // loss.cu
 size_t loss_ws_bytes(int C, int H, int W);
 int launch_loss_l1_ssim(cudaStream_t, int C, int H, int W, const float* img, const float* gt, float lambda, void* ws, float* out3, float* dL_dimg);
-int launch_loss_l2(cudaStream_t, size_t n, const float* img, const float* gt, float* dL_dimg, float* loss_acc);
+int launch_loss_l2(cudaStream_t, size_t n, const float* img, const void* gt, int gt_is_u8, float scale, float* dL_dimg, float* loss_acc);
 
 // param_step.cu
 int launch_param_step(cudaStream_t, int P, int M, float* xyz, float* f_dc, float* f_rest, float* opacity, float* scaling, float* rotation,

@@ -153,23 +153,35 @@ __global__ void loss_finish_kernel(const double* __restrict__ acc, double n, flo
 	out3[0] = (float)l1; out3[1] = (float)s; out3[2] = (float)((1.0 - (double)lambda) * l1 + (double)lambda * (1.0 - s));
 }
 
-// dL = x - y, loss += 0.5 * sum (x - y)^2 in one pass (float4 body, scalar tail)
-__global__ void __launch_bounds__(256) l2_loss_grad_kernel(size_t n, const float* __restrict__ x, const float* __restrict__ y, float* __restrict__ d_out,
+// dL = x - y, loss += 0.5 * sum (x - y)^2 in one pass (4 elements per thread and iteration, scalar tail).  T = float, or
+// uint8_t for a target image kept in its native 8-bit form (y = byte * scale): a quarter of the host->device bytes.
+template <class T>
+__global__ void __launch_bounds__(256) l2_loss_grad_kernel(size_t n, const float* __restrict__ x, const T* __restrict__ y, float scale, float* __restrict__ d_out,
 	float* __restrict__ loss_acc)
 {
 	__shared__ float s_red[8];
 	float acc = 0.0f;
 	const size_t n4 = n / 4, stride = (size_t)gridDim.x * 256;
-	const bool vec = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(d_out)) & 15) == 0;
+	const bool vec = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(d_out)) & 15) == 0 && (reinterpret_cast<uintptr_t>(y) & (4 * sizeof(T) - 1)) == 0;
 	if (vec) {
 		for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += stride) {
-			const float4 a = __ldg(reinterpret_cast<const float4*>(x) + i), b = __ldg(reinterpret_cast<const float4*>(y) + i);
+			const float4 a = __ldg(reinterpret_cast<const float4*>(x) + i);
+			float4 b;
+			if (sizeof(T) == 1) {
+				const uchar4 u = __ldg(reinterpret_cast<const uchar4*>(y) + i);
+				b = make_float4(__fmul_rn(u.x, scale), __fmul_rn(u.y, scale), __fmul_rn(u.z, scale), __fmul_rn(u.w, scale));   // rounded product, not fused into the subtraction
+			} else {
+				b = __ldg(reinterpret_cast<const float4*>(y) + i);
+			}
 			const float4 d = make_float4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w);
 			reinterpret_cast<float4*>(d_out)[i] = d;
 			acc += d.x * d.x + d.y * d.y + d.z * d.z + d.w * d.w;
 		}
 	}
-	for (size_t i = (vec ? n4 * 4 : 0) + (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += stride) { const float d = x[i] - y[i]; d_out[i] = d; acc += d * d; }
+	for (size_t i = (vec ? n4 * 4 : 0) + (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += stride) {
+		const float d = x[i] - (sizeof(T) == 1 ? __fmul_rn((float)y[i], scale) : (float)y[i]);
+		d_out[i] = d; acc += d * d;
+	}
 	const float t = block_sum_256(acc, s_red);
 	if (threadIdx.x == 0 && loss_acc) atomicAdd(loss_acc, 0.5f * t);
 }
@@ -194,10 +206,13 @@ int launch_loss_l1_ssim(cudaStream_t stream, int C, int H, int W, const float* i
 	return check_launch("loss_l1_ssim", stream, false);
 }
 
-int launch_loss_l2(cudaStream_t stream, size_t n, const float* img, const float* gt, float* dL_dimg, float* loss_acc)
+int launch_loss_l2(cudaStream_t stream, size_t n, const float* img, const void* gt, int gt_is_u8, float scale, float* dL_dimg, float* loss_acc)
 {
 	const size_t blocks = (n / 4 + 255) / 256 + 1;
-	count_launch(), l2_loss_grad_kernel<<<(unsigned)(blocks < 148 * 8 ? blocks : 148 * 8), 256, 0, stream>>>(n, img, gt, dL_dimg, loss_acc);
+	const unsigned grid = (unsigned)(blocks < 148 * 8 ? blocks : 148 * 8);
+	count_launch();
+	if (gt_is_u8) l2_loss_grad_kernel<uint8_t><<<grid, 256, 0, stream>>>(n, img, reinterpret_cast<const uint8_t*>(gt), scale, dL_dimg, loss_acc);
+	else l2_loss_grad_kernel<float><<<grid, 256, 0, stream>>>(n, img, reinterpret_cast<const float*>(gt), 1.0f, dL_dimg, loss_acc);
 	return check_launch("loss_l2", stream, false);
 }
 

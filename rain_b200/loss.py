@@ -71,14 +71,19 @@ def ssim(img1, img2, window_size=11, size_average=True):
     return _run(a, b, 0.0, False)[0][1]
 
 
-def l2_loss_grad(image, gt, loss_accum=None, out=None):
-    """dL/dimage = image - gt for L = 0.5 * sum (image - gt)^2, and loss_accum[0] += L, fused in one pass."""
+def l2_loss_grad(image, gt, loss_accum=None, out=None, u8_scale=1.0 / 255.0):
+    """dL/dimage = image - gt for L = 0.5 * sum (image - gt)^2, and loss_accum[0] += L, fused in one pass.  gt is float32,
+    or uint8 (the image in its native 8-bit form, gt = byte * u8_scale, converted in the kernel)."""
     if not (image.is_cuda and gt.is_cuda):
         raise RuntimeError("rain_b200 has no CPU path: image and gt must be CUDA tensors")
     lib = _lib.load()
     image = image.contiguous(); gt = gt.contiguous()
     out = torch.empty_like(image) if out is None else out
     with torch.cuda.device(image.device):
-        _lib.check(lib.rr_loss_l2(torch.cuda.current_stream().cuda_stream, image.numel(), image.data_ptr(), gt.data_ptr(), out.data_ptr(),
-                                  loss_accum.data_ptr() if loss_accum is not None else None), "rr_loss_l2")
+        acc = loss_accum.data_ptr() if loss_accum is not None else None
+        if gt.dtype == torch.uint8:
+            _lib.check(lib.rr_loss_l2_u8(torch.cuda.current_stream().cuda_stream, image.numel(), image.data_ptr(), gt.data_ptr(), float(u8_scale),
+                                         out.data_ptr(), acc), "rr_loss_l2_u8")
+        else:
+            _lib.check(lib.rr_loss_l2(torch.cuda.current_stream().cuda_stream, image.numel(), image.data_ptr(), gt.data_ptr(), out.data_ptr(), acc), "rr_loss_l2")
     return out

@@ -133,6 +133,16 @@ class HostFeed:
                 ev.record(self.stream)
         return self.buffers
 
+    def stage_slot(self, slot, host_tensor):
+        """Enqueue the copy of ONE slot (after what is queued on the compute stream so far).  Staging view i+1 when view i
+        starts keeps a single short transfer in flight instead of a burst of all the step's images."""
+        main = torch.cuda.current_stream(self.device)
+        self.stream.wait_stream(main)
+        with torch.cuda.stream(self.stream):
+            self.buffers[slot].copy_(host_tensor, non_blocking=True)
+            self.events[slot].record(self.stream)
+        return self.buffers[slot]
+
     def wait(self, slot):
         torch.cuda.current_stream(self.device).wait_event(self.events[slot])
         return self.buffers[slot]

@@ -101,5 +101,11 @@ def test_l2_loss_grad_fused(device):
         assert torch.equal(d, a - b)
         ref = 0.5 * (a.double() - b.double()).pow(2).sum().item()
         assert abs(acc.item() - ref) <= 1e-5 * ref
+        u = torch.randint(0, 256, (n,), dtype=torch.uint8, device=device)
+        acc.zero_()
+        d = L.l2_loss_grad(a, u, acc)
+        assert torch.equal(d, a - u.float() * (1.0 / 255.0))
+        ref = 0.5 * (a.double() - (u.float() * (1.0 / 255.0)).double()).pow(2).sum().item()
+        assert abs(acc.item() - ref) <= 1e-5 * ref
     with pytest.raises(RuntimeError):
         L.l2_loss_grad(torch.zeros(4), torch.zeros(4))
