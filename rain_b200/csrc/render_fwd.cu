@@ -3,14 +3,18 @@
 //
 // B200 design (one CTA per tile, 8 consumer warps + 1 producer warp, no __syncthreads after the prologue):
 //  * the PRODUCER warp stages the tile's list into a ring of FWD_STAGES shared-memory stages of 128 records (48 B
-//    each) with TMA bulk copies — one 48-byte cp.async.bulk per record, gathered straight from the per-Gaussian record
-//    array (L2 resident) through point_list, 4 per lane and batch, all landing on the stage's `full` mbarrier
-//    (variant 2, default; variant 1 copies a packed span with ONE bulk copy; variants 0 / 3 fill with plain loads and
-//    exist as cross-checks).  A stage is refilled when every consumer warp has released it: each warp publishes the
-//    number of batches it is done with in a shared word (release store), the producer polls the minimum;
+//    each), gathered asynchronously straight from the per-Gaussian record array (L2 resident) through point_list, 4
+//    records per lane and batch, all landing on the stage's `full` mbarrier.  Staging modes (render_common.cuh):
+//    4 (default) three 16-byte cp.async per record with cp.async.mbarrier.arrive.noinc; 2 one 48-byte TMA bulk copy
+//    (cp.async.bulk) per record — measured slower here, because a per-lane bulk-copy address is issued lane by lane
+//    through the uniform datapath; 1 ONE bulk copy of a packed span (needs the pack pass); 0 / 3 plain loads
+//    (cross-checks).  A stage is refilled when every consumer warp has released it: each warp publishes the
+//    number of batches it is done with in a shared word (release store), the producer polls the minimum every
+//    FWD_POLL_NS;
 //  * each CONSUMER warp owns an 8x4 pixel block and runs through the ring at its own pace: it culls a staged batch
 //    against its block (one splat per lane: AABB, then the exact concave-maximum test of render_common.cuh), compacts
-//    the survivors with ballot/popc, and blends only those, so warps that own easy pixels do not wait for the others;
+//    the survivors with ballot/popc, and blends only those — two survivors per iteration, sharing the packed steps
+//    of the bit-exact exponential (exp2x) — so warps that own easy pixels do not wait for the others;
 //  * a warp whose 32 pixels are saturated publishes "released everything" and leaves at once; the producer stops
 //    filling when all 8 warps have;
 //  * each warp leaves one bit per list entry ("blended into one of my pixels", kernels.cuh) for the backward.
@@ -25,6 +29,9 @@ namespace rr {
 namespace {
 
 constexpr int FWD_STAGES = 4;
+#ifndef FWD_POLL_NS
+#define FWD_POLL_NS 256      // producer back-off between polls of the released counters (the ring keeps it 3 batches ahead; polling at 32 ns cost 9 % of the kernel's issue slots)
+#endif
 constexpr int FWD_THREADS = RENDER_THREADS + 32;      // 8 consumer warps + the producer warp
 
 // Producer: fill one stage with `cnt` records starting at list position `first`; completion is signalled on `bar`
@@ -88,7 +95,7 @@ __global__ void __launch_bounds__(FWD_THREADS) render_fwd_kernel(RenderArgs a)
 					const int r = lane < RENDER_WARPS ? *reinterpret_cast<volatile int*>(&s_released[lane]) : 0x7fffffff;
 					low = __reduce_min_sync(FULL, r);
 					if (low > b - FWD_STAGES) break;
-					__nanosleep(32);
+					__nanosleep(FWD_POLL_NS);
 				}
 				if (low == 0x7fffffff) break;
 				__threadfence_block();       // the consumers' reads of the stage are ordered before the refill below
