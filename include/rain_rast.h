@@ -125,6 +125,14 @@ int rr_param_step(void* stream, int P, int M, float* xyz, float* f_dc, float* f_
 	float* exp_avg, float* exp_avg_sq, const float* grads, const float* hyper, int step,
 	float* shs_out, float* opacities_out, float* scales_out, float* rotations_out);
 
+/* Densification statistics of one rendered view, fused (train.py:132-134 + GaussianModel.add_densification_stats,
+ * scene/gaussian_model.py:419-421): for every Gaussian with radii > 0 (the view's visibility_filter)
+ *   max_radii2D[p] = max(max_radii2D[p], radii[p]); xyz_gradient_accum[p] += |dL_dmean2D[p, 0:2]|; denom[p] += 1
+ * radii i32[P] and dL_dmean2D f32[P,3] are the view's outputs (viewspace_points.grad); the three f32[P] statistics are
+ * updated in place.  Per view and non-linear, so they are accumulated locally and summed / maxed across ranks separately
+ * from the gradient all-reduce. */
+int rr_densify_stats(void* stream, int P, const int* radii, const float* dL_dmean2D, float* max_radii2D, float* xyz_gradient_accum, float* denom);
+
 size_t rr_dist2_ws_bytes(int P);
 int rr_dist2(void* stream, int P, const float* points, float* out, void* ws, size_t ws_bytes);
 

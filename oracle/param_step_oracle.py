@@ -39,3 +39,11 @@ def adam_step(leaves, m, v, g_act, lrs, step, betas=(0.9, 0.999), eps=1e-15):
         v[k] *= b2; v[k] += (1 - b2) * g * g
         leaves[k] -= lrs[k] / (1 - b1 ** step) * m[k] / (np.sqrt(v[k]) / np.sqrt(1 - b2 ** step) + eps)
     return activate(leaves)
+
+
+def densify_stats(radii, dL_dmean2D, max_radii2D, xyz_gradient_accum, denom):
+    """train.py:132-134 and scene/gaussian_model.py:419-421, in place on float arrays of shape [P] (radii: int [P])."""
+    vis = radii > 0
+    max_radii2D[vis] = np.maximum(max_radii2D[vis], radii[vis].astype(max_radii2D.dtype))
+    xyz_gradient_accum[vis] += np.sqrt((dL_dmean2D[vis, :2].astype(np.float64) ** 2).sum(-1)).astype(xyz_gradient_accum.dtype)
+    denom[vis] += 1

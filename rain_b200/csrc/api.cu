@@ -399,6 +399,15 @@ int rr_param_step(void* stream_, int P, int M, float* xyz, float* f_dc, float* f
 		shs_out, opacities_out, scales_out, rotations_out);
 }
 
+int rr_densify_stats(void* stream_, int P, const int* radii, const float* dL_dmean2D, float* max_radii2D, float* xyz_gradient_accum, float* denom)
+{
+	if (P == 0) return 0;
+	if (P < 0) { set_error("bad size P=%d", P); return -1; }
+	if (bad_ptr(radii, "radii") || bad_ptr(dL_dmean2D, "dL_dmean2D") || bad_ptr(max_radii2D, "max_radii2D") ||
+		bad_ptr(xyz_gradient_accum, "xyz_gradient_accum") || bad_ptr(denom, "denom")) return -1;
+	return launch_densify_stats(reinterpret_cast<cudaStream_t>(stream_), P, radii, dL_dmean2D, max_radii2D, xyz_gradient_accum, denom);
+}
+
 size_t rr_dist2_ws_bytes(int P) { return knn_ws_bytes(P); }
 int rr_dist2(void* stream_, int P, const float* points, float* out, void* ws, size_t ws_bytes)
 {

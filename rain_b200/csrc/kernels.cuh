@@ -87,6 +87,8 @@ int launch_loss_l2(cudaStream_t, size_t n, const float* img, const void* gt, int
 int launch_param_step(cudaStream_t, int P, int M, float* xyz, float* f_dc, float* f_rest, float* opacity, float* scaling, float* rotation,
 	float* m, float* v, const float* grads, const float* hyper, int step, float* shs_out, float* opacities_out, float* scales_out, float* rotations_out);
 
+int launch_densify_stats(cudaStream_t, int P, const int* radii, const float* dL_dmean2D, float* max_radii2D, float* grad_accum, float* denom);
+
 // knn.cu
 size_t knn_ws_bytes(int P);
 int launch_dist2(cudaStream_t, int P, const float* points, float* out, void* ws, size_t ws_bytes);

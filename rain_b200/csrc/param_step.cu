@@ -100,7 +100,29 @@ __global__ void __launch_bounds__(256) param_step_geom_kernel(int P, float* __re
 	}
 }
 
+// Densification statistics of one rendered view (train.py:132-134, scene/gaussian_model.py:419-421), one thread per
+// Gaussian, for the Gaussians the view saw (visibility_filter = radii > 0):
+//   max_radii2D = max(max_radii2D, radii); xyz_gradient_accum += |dL/dmean2D.xy|; denom += 1
+__global__ void __launch_bounds__(256) densify_stats_kernel(int P, const int* __restrict__ radii, const float* __restrict__ dL_dmean2D /*[P,3]*/,
+	float* __restrict__ max_radii2D, float* __restrict__ grad_accum, float* __restrict__ denom)
+{
+	const int p = blockIdx.x * 256 + threadIdx.x;
+	if (p >= P) return;
+	const int r = radii[p];
+	if (r <= 0) return;
+	max_radii2D[p] = fmaxf(max_radii2D[p], (float)r);
+	const float gx = dL_dmean2D[(size_t)p * 3], gy = dL_dmean2D[(size_t)p * 3 + 1];
+	grad_accum[p] += sqrtf(gx * gx + gy * gy);          // torch.norm(grad[:, :2], dim=-1)
+	denom[p] += 1.0f;
+}
+
 }  // namespace
+
+int launch_densify_stats(cudaStream_t stream, int P, const int* radii, const float* dL_dmean2D, float* max_radii2D, float* grad_accum, float* denom)
+{
+	count_launch(), densify_stats_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, radii, dL_dmean2D, max_radii2D, grad_accum, denom);
+	return check_launch("densify_stats", stream, false);
+}
 
 int launch_param_step(cudaStream_t stream, int P, int M, float* xyz, float* f_dc, float* f_rest, float* opacity, float* scaling, float* rotation,
 	float* m, float* v, const float* grads, const float* hyper /*host: lr[6], beta1, beta2, eps*/, int step,

@@ -49,3 +49,21 @@ class GaussianParamStep:
                                          self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), grads_flat.data_ptr(), hyper, self.steps,
                                          A["shs"].data_ptr(), A["opacities"].data_ptr(), A["scales"].data_ptr(), A["rotations"].data_ptr()), "rr_param_step")
         return A
+
+
+def add_densification_stats(radii, dL_dmean2D, max_radii2D, xyz_gradient_accum, denom):
+    """train.py:132-134 + GaussianModel.add_densification_stats (scene/gaussian_model.py:419-421) for one rendered view, in one
+    kernel: radii i32[P], dL_dmean2D f32[P,3] (viewspace_points.grad); max_radii2D[P], xyz_gradient_accum[P,1], denom[P,1] f32
+    are updated in place for the Gaussians with radii > 0."""
+    lib = _lib.load()
+    for t in (radii, dL_dmean2D, max_radii2D, xyz_gradient_accum, denom):
+        if not t.is_cuda or not t.is_contiguous():
+            raise RuntimeError("rain_b200 has no CPU path: contiguous CUDA tensors required")
+    if radii.dtype != torch.int32 or any(t.dtype != torch.float32 for t in (dL_dmean2D, max_radii2D, xyz_gradient_accum, denom)):
+        raise RuntimeError("radii must be int32 and the statistics float32")
+    P = radii.numel()
+    if dL_dmean2D.numel() != 3 * P or max_radii2D.numel() != P or xyz_gradient_accum.numel() != P or denom.numel() != P:
+        raise RuntimeError("shape mismatch between radii and the statistics")
+    with torch.cuda.device(radii.device):
+        _lib.check(lib.rr_densify_stats(torch.cuda.current_stream().cuda_stream, P, radii.data_ptr(), dL_dmean2D.data_ptr(), max_radii2D.data_ptr(),
+                                        xyz_gradient_accum.data_ptr(), denom.data_ptr()), "rr_densify_stats")

@@ -136,3 +136,39 @@ def test_render_loss_step_loop_reduces_the_loss(device):
         params = opt.step(bucket.flat)
     loss = [float(torch.stack(h)[:, 2].mean().item()) for h in history]
     assert loss[-1] < 0.6 * loss[0], loss
+
+
+def test_densify_stats_oracle_matches_torch_restatement_of_the_reference():
+    from oracle.param_step_oracle import densify_stats
+    g = torch.Generator().manual_seed(5)
+    P = 501
+    radii = torch.randint(-1, 40, (P,), generator=g).clamp(min=0).int()
+    grad = torch.randn(P, 3, generator=g)
+    mx, acc, den = torch.rand(P, generator=g) * 30, torch.rand(P, 1, generator=g), torch.randint(0, 5, (P, 1), generator=g).float()
+    o = [t.numpy().copy().reshape(P) for t in (mx, acc, den)]
+    densify_stats(radii.numpy(), grad.numpy(), *o)
+    vis = radii > 0                                                      # gaussian_renderer/__init__.py: visibility_filter
+    mx[vis] = torch.max(mx[vis], radii[vis].float())                     # train.py:133
+    acc[vis] += torch.norm(grad[vis, :2], dim=-1, keepdim=True)          # gaussian_model.py:420
+    den[vis] += 1                                                        # :421
+    for a, b in zip(o, (mx, acc, den)):
+        assert np.allclose(a, b.numpy().reshape(P), rtol=1e-6, atol=0)
+
+
+@pytest.mark.gpu
+def test_densify_stats_kernel_matches_oracle(device):
+    from oracle.param_step_oracle import densify_stats
+    from rain_b200.optim import add_densification_stats
+    g = torch.Generator().manual_seed(6)
+    for P in (1, 257, 100_003):
+        radii = torch.randint(-1, 40, (P,), generator=g).clamp(min=0).int()
+        grad = torch.randn(P, 3, generator=g)
+        mx, acc, den = torch.rand(P, generator=g) * 30, torch.rand(P, 1, generator=g), torch.randint(0, 5, (P, 1), generator=g).float()
+        o = [t.numpy().copy().reshape(P) for t in (mx, acc, den)]
+        densify_stats(radii.numpy(), grad.numpy(), *o)
+        d = [t.to(device) for t in (mx, acc, den)]
+        add_densification_stats(radii.to(device), grad.to(device), *d)
+        for a, b in zip(o, d):
+            assert np.allclose(a, b.cpu().numpy().reshape(P), rtol=1e-6, atol=0)
+    with pytest.raises(RuntimeError):
+        add_densification_stats(radii, grad, mx, acc, den)
