@@ -155,7 +155,7 @@ int rr_geom_layout(int P, int64_t offsets_host[9]);
 int rr_binning_layout(int64_t N, int W, int H, int64_t offsets_host[5]);
 int rr_image_layout(int W, int H, int64_t offsets_host[4]);
 /* the 64-bit (tile<<32 | depth bits) key of every sorted duplicate, as the reference's point_list_keys holds them */
-int rr_export_sorted_keys(void* stream, int P, int64_t N, int W, int H, void* geom, void* binning, uint64_t* keys_out);
+int rr_export_sorted_keys(void* stream, int P, int64_t N, int W, int H, void* geom, void* binning, void* image, uint64_t* keys_out);
 
 #ifdef __cplusplus
 }

@@ -59,7 +59,7 @@ SIGNATURES = {
     "rr_geom_layout": (_i, [_i, _c.POINTER(_i64)]),
     "rr_binning_layout": (_i, [_i64, _i, _i, _c.POINTER(_i64)]),
     "rr_image_layout": (_i, [_i, _i, _c.POINTER(_i64)]),
-    "rr_export_sorted_keys": (_i, [_vp, _i, _i64, _i, _i, _vp, _vp, _vp]),
+    "rr_export_sorted_keys": (_i, [_vp, _i, _i64, _i, _i, _vp, _vp, _vp, _vp]),
 }
 
 _lib = None

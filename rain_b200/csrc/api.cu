@@ -2,6 +2,7 @@
 // Replaces CudaRasterizer::Rasterizer::forward/backward/markVisible (reference rasterizer_impl.cu:187-430) and the
 // torch binding RasterizeGaussiansCUDA / RasterizeGaussiansBackwardCUDA / markVisible (rasterize_points.cu) minus
 // tensor allocation, which stays in Python.
+#include <cstdlib>
 #include <cstdarg>
 #include <cstring>
 #include <atomic>
@@ -142,7 +143,10 @@ BinLayout bin_layout(void* blob, int64_t N, int W, int H)
 	return L;
 }
 
-struct ImgLayout { float* final_T; uint32_t* n_contrib; uint2* ranges; uint32_t* tile_max; size_t total; int64_t off[4]; };
+// RAIN_BINNING=count: opt-in sort-free binning (read once)
+bool count_binning_wanted() { static const bool on = []() { const char* e = getenv("RAIN_BINNING"); return e && e[0] == 'c'; }(); return on; }
+
+struct ImgLayout { float* final_T; uint32_t* n_contrib; uint2* ranges; uint32_t* tile_max; void* cb_ws; size_t total; int64_t off[4]; };
 ImgLayout img_layout(void* blob, int W, int H)
 {
 	ImgLayout L; Carver c(blob);
@@ -152,6 +156,8 @@ ImgLayout img_layout(void* blob, int W, int H)
 	L.n_contrib = c.take<uint32_t>(X < 1 ? 1 : X);
 	L.ranges = c.take<uint2>(tiles < 1 ? 1 : tiles);
 	L.tile_max = c.take<uint32_t>(tiles < 1 ? 1 : tiles);
+	// count / base matrices of the sort-free binning (binning_count.cu; opt-in, RAIN_BINNING=count); sized by the tile count only
+	L.cb_ws = (count_binning_wanted() && tiles <= (size_t)CB_MAX_TILES) ? (void*)c.take<char>(count_binning_ws_bytes((int)(tiles < 1 ? 1 : tiles))) : nullptr;
 	L.total = c.used();
 	char* b = reinterpret_cast<char*>(blob);
 	L.off[0] = (char*)L.final_T - b; L.off[1] = (char*)L.n_contrib - b; L.off[2] = (char*)L.ranges - b; L.off[3] = (char*)L.tile_max - b;
@@ -265,7 +271,15 @@ int rr_forward_raster(void* stream_, int P, int W, int H, int64_t N, const float
 	if (G.total > geom_bytes || B.total > binning_bytes || I.total > image_bytes) { set_error("scratch blob too small"); return -1; }
 	const int grid_x = (W + TILE_X - 1) / TILE_X, grid_y = (H + TILE_Y - 1) / TILE_Y;
 
-	if (N > 0) {
+	// default: duplicate + onesweep tile sort + ranges; RAIN_BINNING=count selects the sort-free counting placement
+	// (binning_count.cu: same lists bit for bit, measured slower on B200 — see its header)
+	const bool count_mode = I.cb_ws != nullptr;
+	if (count_mode) {
+		Stage st(stream, ST_TILE_SORT);
+		cudaMemsetAsync(I.ranges, 0, sizeof(uint2) * (size_t)(grid_x * grid_y), stream);
+		if (N > 0 && launch_count_binning(stream, P, grid_x * grid_y, grid_x, G.val_a, G.tiles_touched, G.rect, I.cb_ws, I.ranges, B.point_list)) return -1;
+		if (debug && check_launch("count binning", stream, true)) return -1;
+	} else if (N > 0) {
 		{ Stage st(stream, ST_DUPLICATE); if (launch_duplicate(stream, P, G.val_a, G.offsets, G.rect, grid_x, B.key_a, B.val_a)) return -1; }
 		if (debug && check_launch("duplicate", stream, true)) return -1;
 		int which;
@@ -277,7 +291,7 @@ int rr_forward_raster(void* stream_, int P, int W, int H, int64_t N, const float
 	{
 		Stage st(stream, ST_RANGES_PACK);
 		const bool packed = (variant == 0 || variant == 1);    // the gather modes read rec[] through point_list: no pack pass
-		if (launch_tile_ranges(stream, (size_t)N, B.keys_sorted, I.ranges, grid_x * grid_y)) return -1;
+		if (!count_mode && launch_tile_ranges(stream, (size_t)N, B.keys_sorted, I.ranges, grid_x * grid_y)) return -1;
 		if (packed && launch_pack(stream, (size_t)N, B.point_list, G.rec, B.packed)) return -1;
 	}
 	if (debug && check_launch("ranges/pack", stream, true)) return -1;
@@ -449,14 +463,15 @@ int rr_sort_pairs_u32(void* stream, int64_t n, uint32_t* keys_in, uint32_t* keys
 int rr_sort_pairs_u64(void* stream, int64_t n, uint64_t* keys_in, uint64_t* keys_out, uint32_t* vals_in, uint32_t* vals_out, int begin_bit, int end_bit, void* ws)
 { return sort_entry<uint64_t>(stream, n, keys_in, keys_out, vals_in, vals_out, begin_bit, end_bit, ws); }
 
-int rr_export_sorted_keys(void* stream_, int P, int64_t N, int W, int H, void* geom, void* binning, uint64_t* keys_out)
+int rr_export_sorted_keys(void* stream_, int P, int64_t N, int W, int H, void* geom, void* binning, void* image, uint64_t* keys_out)
 {
 	if (N == 0) return 0;
 	const GeomLayout G = geom_layout(geom, P);
 	const BinLayout B = bin_layout(binning, N, W, H);
-	// depth bits live in rec.c.y (float index 9 of the 12-float record)
-	return launch_export_keys(reinterpret_cast<cudaStream_t>(stream_), (size_t)N, B.keys_sorted, B.point_list,
-		reinterpret_cast<const uint32_t*>(G.rec), keys_out);
+	const ImgLayout I = img_layout(image, W, H);
+	// tile ids from the tile ranges, depth bits from rec.c.y (float index 9 of the 12-float record)
+	const int tiles = ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+	return launch_export_keys_ranges(reinterpret_cast<cudaStream_t>(stream_), tiles, I.ranges, B.point_list, reinterpret_cast<const uint32_t*>(G.rec), keys_out);
 }
 
 }  // extern "C"

@@ -29,6 +29,14 @@ int launch_tile_ranges(cudaStream_t, size_t N, const uint32_t* sorted_tile_keys,
 int launch_pack(cudaStream_t, size_t N, const uint32_t* point_list, const SplatRec* rec, SplatRec* packed);
 int launch_export_keys(cudaStream_t, size_t N, const uint32_t* sorted_tile_keys, const uint32_t* point_list, const uint32_t* rec_words, uint64_t* out);
 
+// binning_count.cu: sort-free tile binning (counting placement of the depth-ordered Gaussians)
+constexpr int CB_MAX_CHUNKS = 1024;      // >= one resident wave of placement CTAs (6 per SM)
+constexpr int CB_MAX_TILES = 12288;      // 48 KB of 32-bit positions in shared memory (8 160 tiles at 1920x1080)
+size_t count_binning_ws_bytes(int T);
+int launch_count_binning(cudaStream_t, int P, int T, int grid_x, const uint32_t* order, const uint32_t* tiles_touched, const uint2* rect,
+	void* ws, uint2* ranges, uint32_t* point_list);
+int launch_export_keys_ranges(cudaStream_t, int T, const uint2* ranges, const uint32_t* point_list, const uint32_t* rec_words, uint64_t* out);
+
 // render_fwd.cu / render_bwd.cu
 // Per-warp blend flags ("which list entries did warp w's 8x4 pixel block blend"), written by the forward and walked by
 // the backward.  One bit per (tile list entry, warp), stored as 32-bit words; the words of tile t start at

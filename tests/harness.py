@@ -48,7 +48,7 @@ def mine_forward(sc, cam, bg, *, colors_precomp=None, cov3D_precomp=None, use_sh
         bo = (ctypes.c_int64 * 5)(); lib.rr_binning_layout(N, W, H, bo)
         out.update(tile_keys=_view(binning, bo[0], N, torch.int32), point_list=_view(binning, bo[3], N, torch.int32))
         keys = torch.empty(N, dtype=torch.int64, device=dev)
-        _lib.check(lib.rr_export_sorted_keys(torch.cuda.current_stream().cuda_stream, P, N, W, H, geom.data_ptr(), binning.data_ptr(), keys.data_ptr()), "export")
+        _lib.check(lib.rr_export_sorted_keys(torch.cuda.current_stream().cuda_stream, P, N, W, H, geom.data_ptr(), binning.data_ptr(), img.data_ptr(), keys.data_ptr()), "export")
         out["keys"] = keys
     return out
 
