@@ -63,7 +63,10 @@ __device__ __forceinline__ void cov3d_from_scale_rot(float s0, float s1, float s
 	c[5] = sop3(M20, M20, M21, M21, M22, M22);
 }
 
-__global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreprocessArgs a)
+#ifndef PF_MIN_CTAS
+#define PF_MIN_CTAS 4      // 64 registers: 4 CTAs (32 warps) per SM instead of 3; 0.081 -> 0.078 ms
+#endif
+__global__ void __launch_bounds__(256, PF_MIN_CTAS) preprocess_fwd_kernel(PreprocessArgs a)
 {
 	const int idx = blockIdx.x * blockDim.x + threadIdx.x;
 	if (idx >= a.P) return;
