@@ -8,6 +8,7 @@
 // (tile, depth, index) order: ties in (tile, depth) keep ascending Gaussian index in both schemes, because both
 // sorts are stable and the depth sort starts from index order.  The 64-bit key list the reference would hold is
 // reconstructed on demand by export_keys_kernel for the parity tests.
+#include <cstdlib>
 #include "common.cuh"
 #include "kernels.cuh"
 
@@ -89,6 +90,64 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_final_kernel(int P, const u
 	}
 }
 
+// The same prefix sum in ONE launch: chained scan with decoupled look-back.  Blocks take tile ids from an atomic ticket (a
+// block's predecessors are therefore always running or done), publish their tile aggregate in a status word (flags in the
+// top two bits, as in radix_sort.cu), and warp 0 looks back over 32 predecessors per step until it meets an inclusive prefix.
+constexpr uint32_t SC_AGG = 1u << 30, SC_INC = 2u << 30, SC_MASK = (1u << 30) - 1;
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_chained_kernel(int P, int nb, const uint32_t* __restrict__ order, const uint32_t* __restrict__ tt,
+	volatile uint32_t* __restrict__ status /*[nb] + ticket at [nb], zero on entry*/, uint32_t* __restrict__ offsets /*inclusive, depth order*/,
+	uint32_t* __restrict__ total, uint32_t* __restrict__ total_host)
+{
+	__shared__ uint32_t s_warp[SCAN_THREADS / 32];
+	__shared__ uint32_t s_tile, s_excl;
+	if (threadIdx.x == 0) s_tile = atomicAdd(const_cast<uint32_t*>(status) + nb, 1u);
+	__syncthreads();
+	const int tile = (int)s_tile;
+	uint32_t v[SCAN_ITEMS], sum = 0;
+	#pragma unroll
+	for (int k = 0; k < SCAN_ITEMS; k++) {
+		const int i = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS + k;
+		v[k] = i < P ? tt[order[i]] : 0;
+		sum += v[k];
+	}
+	uint32_t tot;
+	const uint32_t ex = block_exclusive_scan(sum, s_warp, tot);
+	if (threadIdx.x < 32) {
+		const unsigned lane = threadIdx.x;
+		if (lane == 0) { status[tile] = tot | (tile == 0 ? SC_INC : SC_AGG); __threadfence(); }
+		uint32_t excl = 0;
+		int t = tile - 1;
+		while (t >= 0) {                                               // warp-uniform
+			const int idx = t - (int)lane;
+			uint32_t w = 2u << 30; if (idx >= 0) w = status[idx];       // before tile 0: inclusive prefix 0
+			const uint32_t f = w >> 30;
+			const unsigned not_ready = __ballot_sync(FULL, f == 0), inc = __ballot_sync(FULL, f == 2);
+			const int first_nr = not_ready ? __ffs(not_ready) - 1 : 32, first_inc = inc ? __ffs(inc) - 1 : 32;
+			const int take = min(first_nr, first_inc + 1);              // lanes [0, take): published, up to and including the first inclusive one
+			uint32_t c = (int)lane < take ? (w & SC_MASK) : 0u;
+			#pragma unroll
+			for (int o = 16; o >= 1; o >>= 1) c += __shfl_xor_sync(FULL, c, o);
+			excl += c;
+			if (first_inc < first_nr) break;
+			t -= take;
+		}
+		if (lane == 0) {
+			if (tile > 0) { status[tile] = (excl + tot) | SC_INC; __threadfence(); }
+			s_excl = excl;
+			if (tile == nb - 1) { *total = excl + tot; if (total_host) { *total_host = excl + tot; __threadfence_system(); } }
+		}
+	}
+	__syncthreads();
+	uint32_t run = s_excl + ex;
+	#pragma unroll
+	for (int k = 0; k < SCAN_ITEMS; k++) {
+		const int i = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS + k;
+		run += v[k];
+		if (i < P) offsets[i] = run;
+	}
+}
+
 // One warp emits the duplicates of 32 consecutive depth-sorted Gaussians cooperatively: output slot s of the warp's
 // contiguous span is owned by the last lane whose exclusive offset is <= s (binary search over 32 shared values),
 // so writes are coalesced and a large splat does not serialise on one thread (reference: one thread per rect).
@@ -137,18 +196,31 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* _
 	}
 }
 
-// tile ranges from key changes (identifyTileRanges, rasterizer_impl.cu:105-127)
+// tile ranges from key changes (identifyTileRanges, rasterizer_impl.cu:105-127); four consecutive keys per thread (one 16-byte load)
 __global__ void __launch_bounds__(256) tile_ranges_kernel(uint32_t N, const uint32_t* __restrict__ keys, uint2* __restrict__ ranges)
 {
-	const uint32_t idx = blockIdx.x * 256 + threadIdx.x;
-	if (idx >= N) return;
-	const uint32_t cur = keys[idx];
-	if (idx == 0) ranges[cur].x = 0;
-	else {
-		const uint32_t prev = keys[idx - 1];
-		if (cur != prev) { ranges[prev].y = idx; ranges[cur].x = idx; }
+	const uint32_t i4 = (blockIdx.x * 256u + threadIdx.x) * 4u;
+	if (i4 >= N) return;
+	uint32_t k[4];
+	if (i4 + 3u < N) {
+		const uint4 v = __ldg(reinterpret_cast<const uint4*>(keys) + (i4 >> 2));
+		k[0] = v.x; k[1] = v.y; k[2] = v.z; k[3] = v.w;
+	} else {
+		#pragma unroll
+		for (int j = 0; j < 4; j++) k[j] = i4 + j < N ? __ldg(keys + i4 + j) : 0u;
 	}
-	if (idx == N - 1) ranges[cur].y = N;
+	uint32_t prev = i4 ? __ldg(keys + i4 - 1) : 0u;
+	#pragma unroll
+	for (int j = 0; j < 4; j++) {
+		const uint32_t idx = i4 + j;
+		if (idx < N) {
+			const uint32_t cur = k[j];
+			if (idx == 0) ranges[cur].x = 0;
+			else if (cur != prev) { ranges[prev].y = idx; ranges[cur].x = idx; }
+			if (idx == N - 1) ranges[cur].y = N;
+			prev = cur;
+		}
+	}
 }
 
 // packed[j] = rec[point_list[j]]; three threads move one 48-byte record (one float4 each)
@@ -179,9 +251,16 @@ int launch_scan_tiles(cudaStream_t stream, int P, const uint32_t* order, const u
 {
 	if (P == 0) { cudaMemsetAsync(num_rendered_dev, 0, sizeof(uint32_t), stream); return 0; }
 	const int nb = (P + SCAN_TILE - 1) / SCAN_TILE;
-	count_launch(), scan_reduce_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, order, tt, block_sums);
-	count_launch(), scan_blocksums_kernel<<<1, SCAN_THREADS, 0, stream>>>(nb, block_sums, num_rendered_dev, num_rendered_mapped);
-	count_launch(), scan_final_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, order, tt, block_sums, offsets);
+	// RAIN_SCAN=3 selects the three-launch reduce / scan / final version (cross-check of the chained single-launch scan)
+	static const bool three = []() { const char* e = getenv("RAIN_SCAN"); return e && e[0] == '3'; }();
+	if (three) {
+		count_launch(), scan_reduce_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, order, tt, block_sums);
+		count_launch(), scan_blocksums_kernel<<<1, SCAN_THREADS, 0, stream>>>(nb, block_sums, num_rendered_dev, num_rendered_mapped);
+		count_launch(), scan_final_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, order, tt, block_sums, offsets);
+	} else {
+		cudaMemsetAsync(block_sums, 0, sizeof(uint32_t) * (size_t)(nb + 1), stream);
+		count_launch(), scan_chained_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, nb, order, tt, block_sums, offsets, num_rendered_dev, num_rendered_mapped);
+	}
 	return check_launch("scan_tiles", stream, false);
 }
 
@@ -197,7 +276,7 @@ int launch_tile_ranges(cudaStream_t stream, size_t N, const uint32_t* keys, uint
 {
 	cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)num_tiles, stream);
 	if (N == 0) return 0;
-	count_launch(), tile_ranges_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>((uint32_t)N, keys, ranges);
+	count_launch(), tile_ranges_kernel<<<(unsigned)((N + 1023) / 1024), 256, 0, stream>>>((uint32_t)N, keys, ranges);
 	return check_launch("tile_ranges", stream, false);
 }
 
