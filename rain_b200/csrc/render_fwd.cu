@@ -177,11 +177,8 @@ __global__ void __launch_bounds__(FWD_THREADS) render_fwd_kernel(RenderArgs a)
 				uint32_t usedbits = 0, bit = 1u;
 				for (int k8 = 0; k8 < kn; k8 += 8) {
 					const int n8 = min(8, kn - k8);
-					// two survivors per iteration: everything up to alpha is independent of the blend state, so the two
-					// exponentials share the packed steps of exp2x; the blend itself stays in list order
-					for (int j = 0; j < n8; j += 2, bit <<= 2) {
-						const bool two = j + 1 < n8;                                     // warp-uniform
-						const int e0 = list[kc + k8 + j], e1 = two ? list[kc + k8 + j + 1] : e0;
+					auto pair_step = [&](int li, bool two, uint32_t ubit) {
+						const int e0 = list[li], e1 = two ? list[li + 1] : e0;
 						const float4 ra0 = rec[e0 * 3], rb0 = rec[e0 * 3 + 1], ra1 = rec[e1 * 3], rb1 = rec[e1 * 3 + 1];
 						float dx0, dy0, dx1, dy1;
 						up(sub2(pk(ra0.x, ra0.y), pxy2), dx0, dy0);
@@ -193,24 +190,35 @@ __global__ void __launch_bounds__(FWD_THREADS) render_fwd_kernel(RenderArgs a)
 						float G0, G1;
 						exp2x(power0, power1, G0, G1);
 						const float alpha0 = fminf(0.99f, __fmul_rn(rb0.y, G0)), alpha1 = fminf(0.99f, __fmul_rn(rb1.y, G1));
-						// forward.cu:330-351 for one list entry; C01 = (C0, C1), C2D = (C2, depth): same roundings, packed
-						auto blend = [&](int e, float power, float alpha, const float4& rb, uint32_t ubit) {
+						// forward.cu:330-351 for one list entry, branch free: a pixel that does not blend the entry runs the same
+						// instructions with alpha = 0, which leaves the accumulators unchanged exactly (fma(T, +-0, C) = C) and keeps
+						// T; C01 = (C0, C1), C2D = (C2, depth): same roundings as the reference, packed
+						auto blend = [&](int e, float power, float alpha, const float4& rb, uint32_t b1) {
 							const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
 							const bool ok = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);     // forward.cu:330-340
 							const bool sat = ok && (test_T < 0.0001f);                               // forward.cu:341-346
 							done = done || sat;
-							if (ok && !sat) {
-								const float4 rc = rec[e * 3 + 2];
-								const p2 a2 = pk1(alpha), T2 = pk1(T);
-								C01 = fma2(T2, mul2(a2, pk(rb.z, rb.w)), C01);
-								C2D = fma2(T2, mul2(a2, pk(rc.x, rc.y)), C2D);
-								T = test_T;
-								last_contributor = pos1 + (uint32_t)e;
-								usedbits |= ubit;
-							}
+							const bool bl = ok && !sat;
+							const float4 rc = rec[e * 3 + 2];
+							const p2 a2 = pk1(bl ? alpha : 0.0f), T2 = pk1(T);
+							C01 = fma2(T2, mul2(a2, pk(rb.z, rb.w)), C01);
+							C2D = fma2(T2, mul2(a2, pk(rc.x, rc.y)), C2D);
+							T = bl ? test_T : T;
+							last_contributor = bl ? pos1 + (uint32_t)e : last_contributor;
+							usedbits |= bl ? b1 : 0u;
 						};
-						blend(e0, power0, alpha0, rb0, bit);
-						if (two) blend(e1, power1, alpha1, rb1, bit << 1);
+						blend(e0, power0, alpha0, rb0, ubit);
+						if (two) blend(e1, power1, alpha1, rb1, ubit << 1);
+					};
+					// two survivors per step: everything up to alpha is independent of the blend state, so the two exponentials
+					// share the packed steps of exp2x; the blend itself stays in list order.  A full group of 8 runs unguarded, so
+					// the four steps can be scheduled across each other.
+					if (n8 == 8) {
+						#pragma unroll
+						for (int j = 0; j < 8; j += 2) pair_step(kc + k8 + j, true, bit << j);
+						bit <<= 8;
+					} else {
+						for (int j = 0; j < n8; j += 2, bit <<= 2) pair_step(kc + k8 + j, j + 1 < n8, bit);
 					}
 					if (__all_sync(FULL, done)) { warp_done = true; break; }
 				}
