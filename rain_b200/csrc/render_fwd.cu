@@ -58,8 +58,11 @@ __device__ __forceinline__ void producer_fill(float4* dst, uint64_t* bar, const 
 	}
 }
 
+#ifndef FWD_MIN_CTAS
+#define FWD_MIN_CTAS 4      // CTAs per SM the register budget is held to (56 registers at 288 threads)
+#endif
 template <int MODE>
-__global__ void __launch_bounds__(FWD_THREADS) render_fwd_kernel(RenderArgs a)
+__global__ void __launch_bounds__(FWD_THREADS, FWD_MIN_CTAS) render_fwd_kernel(RenderArgs a)
 {
 	__shared__ __align__(128) float4 s_rec[FWD_STAGES][BATCH * 3];
 	__shared__ __align__(8) uint64_t s_full[FWD_STAGES];
