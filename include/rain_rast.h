@@ -66,6 +66,17 @@ int rr_forward_raster(void* stream, int P, int W, int H, int64_t N, const float*
 	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes,
 	float* out_color, float* out_depth, int variant, int debug);
 
+/* The two parts of rr_forward_raster as separate calls, so that a caller rendering a batch of views can run the binning of
+ * the next view (HBM bound) on a second stream beside the render kernels of the current one (issue bound):
+ *   rr_forward_bin     duplicateWithKeys + SortPairs + identifyTileRanges (rasterizer_impl.cu:275-318)
+ *   rr_forward_render  FORWARD::render (rasterizer_impl.cu:320-328); must be ordered after rr_forward_bin of the same blobs
+ * rr_forward_raster(...) == rr_forward_bin(...) then rr_forward_render(...) on one stream. */
+int rr_forward_bin(void* stream, int P, int W, int H, int64_t N,
+	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes, int variant, int debug);
+int rr_forward_render(void* stream, int P, int W, int H, int64_t N, const float* background,
+	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes,
+	float* out_color, float* out_depth, int variant, int debug);
+
 /* Backward — replaces Rasterizer::backward (rasterizer_impl.cu:334-430) and the torch::zeros fills of
  * RasterizeGaussiansBackwardCUDA (rasterize_points.cu:145-153): every element of every gradient buffer is written.
  * flags & RR_BWD_ACCUMULATE (view-sharded batches, no reference counterpart): the parameter gradients (dL_dmean3D,

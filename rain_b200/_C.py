@@ -39,7 +39,7 @@ def _f32c(t, dev):
 
 class _GeomPass:
     """State between the two halves of the forward (rr_forward_geom / rr_forward_raster)."""
-    __slots__ = ("P", "H", "W", "dev", "bg", "debug", "out_color", "out_depth", "radii", "geom", "img", "nr", "event", "stream", "keep")
+    __slots__ = ("P", "H", "W", "dev", "bg", "debug", "out_color", "out_depth", "radii", "geom", "img", "nr", "event", "stream", "keep", "N", "binning", "bin_event", "bin_stream")
 
 
 def _pinned_slot(dev):
@@ -55,11 +55,13 @@ def _pinned_slot(dev):
 
 def forward_geom(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                  viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
-                 prefiltered, debug, low_pass):
+                 prefiltered, debug, low_pass, stream=None):
     """First half of RasterizeGaussiansCUDA (preprocess, depth order, prefix sum; Rasterizer::forward up to the num_rendered
     read-back, rasterizer_impl.cu:187-273), enqueued without waiting: returns the state ``forward_raster`` completes.
     Splitting the forward lets a caller enqueue the next view's first half before the current view's backward, so the
-    device never idles on the num_rendered round trip (rain_b200.multiview)."""
+    device never idles on the num_rendered round trip (rain_b200.multiview).  ``stream``: launch on this stream instead of the
+    current one (buffers still come from the current stream's pool: the caller orders ``stream`` after the current stream
+    first, and forward_raster orders its stream after this half)."""
     lib = _lib.load()
     if means3D.dim() != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")  # rasterize_points.cu:47-49
@@ -85,7 +87,7 @@ def forward_geom(background, means3D, colors, opacity, scales, rotations, scale_
     st.nr = _pinned_slot(dev)
     st.keep = (means3D_c, colors_c, opac, scales_c, rots, cov_c, view, proj, cam, sh_c)   # inputs stay alive until the kernels ran
     with torch.cuda.device(dev):
-        st.stream = torch.cuda.current_stream()
+        st.stream = torch.cuda.current_stream() if stream is None else stream
         _lib.check(lib.rr_forward_geom(st.stream.cuda_stream, P, int(degree), M, W, H,
                                        _ptr(means3D_c), _ptr(sh_c), _ptr(colors_c), _ptr(opac),
                                        _ptr(scales_c), float(scale_modifier), _ptr(rots), _ptr(cov_c),
@@ -110,14 +112,54 @@ def forward_raster(st):
                 z((1, H, W), dtype=torch.float32, device=dev), torch.empty(0, **byte), torch.empty(0, **byte), torch.empty(0, **byte))
     st.event.synchronize()
     N = int(st.nr.item())
-    binning = torch.empty(lib.rr_binning_bytes(N, W, H), **byte)
     with torch.cuda.device(dev):
         stream = torch.cuda.current_stream()
+        if stream != st.stream:                  # first half ran on another stream (rain_b200.multiview's geometry stream)
+            stream.wait_event(st.event)
+    binning = torch.empty(lib.rr_binning_bytes(N, W, H), **byte)
+    with torch.cuda.device(dev):
         _lib.check(lib.rr_forward_raster(stream.cuda_stream, P, W, H, N, _ptr(st.bg),
                                          st.geom.data_ptr(), st.geom.numel(), binning.data_ptr(), binning.numel(), st.img.data_ptr(), st.img.numel(),
                                          st.out_color.data_ptr(), st.out_depth.data_ptr(), _variant(), int(st.debug)), "rr_forward_raster")
     st.keep = None
     return N, st.out_color, st.radii, st.out_depth, st.geom, binning, st.img
+
+
+def forward_bin(st, stream=None):
+    """forward_raster without the render kernel: waits for num_rendered, then duplicate / tile sort / ranges (rr_forward_bin),
+    on ``stream`` if given (same ordering contract as forward_geom's).  ``forward_render(st)`` completes the forward."""
+    lib = _lib.load()
+    if st.P == 0:
+        return st
+    st.event.synchronize()
+    st.N = int(st.nr.item())
+    st.binning = torch.empty(lib.rr_binning_bytes(st.N, st.W, st.H), dtype=torch.uint8, device=st.dev)
+    with torch.cuda.device(st.dev):
+        st.bin_stream = torch.cuda.current_stream() if stream is None else stream
+        if st.bin_stream != st.stream:
+            st.bin_stream.wait_event(st.event)
+        _lib.check(lib.rr_forward_bin(st.bin_stream.cuda_stream, st.P, st.W, st.H, st.N, st.geom.data_ptr(), st.geom.numel(),
+                                      st.binning.data_ptr(), st.binning.numel(), st.img.data_ptr(), st.img.numel(), _variant(), int(st.debug)), "rr_forward_bin")
+        st.bin_event = torch.cuda.Event()
+        st.bin_event.record(st.bin_stream)
+    return st
+
+
+def forward_render(st):
+    """The render kernel of a view whose forward_geom and forward_bin were enqueued (possibly on other streams); same return
+    value as forward_raster."""
+    lib = _lib.load()
+    if st.P == 0:
+        return forward_raster(st)
+    with torch.cuda.device(st.dev):
+        stream = torch.cuda.current_stream()
+        if stream != st.bin_stream:
+            stream.wait_event(st.bin_event)
+        _lib.check(lib.rr_forward_render(stream.cuda_stream, st.P, st.W, st.H, st.N, _ptr(st.bg),
+                                         st.geom.data_ptr(), st.geom.numel(), st.binning.data_ptr(), st.binning.numel(), st.img.data_ptr(), st.img.numel(),
+                                         st.out_color.data_ptr(), st.out_depth.data_ptr(), _variant(), int(st.debug)), "rr_forward_render")
+    st.keep = None
+    return st.N, st.out_color, st.radii, st.out_depth, st.geom, st.binning, st.img
 
 
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,

@@ -33,6 +33,11 @@ SIGNATURES = {
     "rr_forward_raster": (_i, [_vp, _i, _i, _i, _i64, _vp,
                                _vp, _sz, _vp, _sz, _vp, _sz,
                                _vp, _vp, _i, _i]),
+    "rr_forward_bin": (_i, [_vp, _i, _i, _i, _i64,
+                            _vp, _sz, _vp, _sz, _vp, _sz, _i, _i]),
+    "rr_forward_render": (_i, [_vp, _i, _i, _i, _i64, _vp,
+                               _vp, _sz, _vp, _sz, _vp, _sz,
+                               _vp, _vp, _i, _i]),
     "rr_backward": (_i, [_vp, _i, _i, _i, _i, _i, _i64, _vp,
                          _vp, _vp, _vp,
                          _vp, _f, _vp, _vp,

@@ -256,14 +256,12 @@ int rr_forward_geom(void* stream_, int P, int D, int M, int W, int H,
 	return check_launch("forward_geom", stream, debug != 0);
 }
 
-int rr_forward_raster(void* stream_, int P, int W, int H, int64_t N, const float* background,
-	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes,
-	float* out_color, float* out_depth, int variant, int debug)
+int rr_forward_bin(void* stream_, int P, int W, int H, int64_t N,
+	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes, int variant, int debug)
 {
 	cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
 	if (P == 0) return 0;
-	if (bad_ptr(background, "background") || bad_ptr(geom, "geom") || bad_ptr(binning, "binning") || bad_ptr(image, "image") ||
-		bad_ptr(out_color, "out_color") || bad_ptr(out_depth, "out_depth")) return -1;
+	if (bad_ptr(geom, "geom") || bad_ptr(binning, "binning") || bad_ptr(image, "image")) return -1;
 	if (N < 0 || N >= (1ll << 30)) { set_error("num_rendered=%lld out of range", (long long)N); return -1; }
 	const GeomLayout G = geom_layout(geom, P);
 	const BinLayout B = bin_layout(binning, N, W, H);
@@ -294,14 +292,40 @@ int rr_forward_raster(void* stream_, int P, int W, int H, int64_t N, const float
 		if (!count_mode && launch_tile_ranges(stream, (size_t)N, B.keys_sorted, I.ranges, grid_x * grid_y)) return -1;
 		if (packed && launch_pack(stream, (size_t)N, B.point_list, G.rec, B.packed)) return -1;
 	}
-	if (debug && check_launch("ranges/pack", stream, true)) return -1;
+	return check_launch("forward_bin", stream, debug != 0);
+}
+
+int rr_forward_render(void* stream_, int P, int W, int H, int64_t N, const float* background,
+	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes,
+	float* out_color, float* out_depth, int variant, int debug)
+{
+	cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+	if (P == 0) return 0;
+	if (bad_ptr(background, "background") || bad_ptr(geom, "geom") || bad_ptr(binning, "binning") || bad_ptr(image, "image") ||
+		bad_ptr(out_color, "out_color") || bad_ptr(out_depth, "out_depth")) return -1;
+	if (N < 0 || N >= (1ll << 30)) { set_error("num_rendered=%lld out of range", (long long)N); return -1; }
+	const GeomLayout G = geom_layout(geom, P);
+	const BinLayout B = bin_layout(binning, N, W, H);
+	const ImgLayout I = img_layout(image, W, H);
+	if (G.total > geom_bytes || B.total > binning_bytes || I.total > image_bytes) { set_error("scratch blob too small"); return -1; }
+	const int grid_x = (W + TILE_X - 1) / TILE_X, grid_y = (H + TILE_Y - 1) / TILE_Y;
 
 	RenderArgs r; memset(&r, 0, sizeof(r));
 	r.W = W; r.H = H; r.grid_x = grid_x; r.grid_y = grid_y;
 	r.ranges = I.ranges; r.packed = B.packed; r.rec = G.rec; r.point_list = B.point_list; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.warp_flags = B.warp_flags;
 	r.out_color = out_color; r.out_depth = out_depth; r.variant = variant;
 	{ Stage st(stream, ST_RENDER_FWD); if (launch_render_fwd(stream, r)) return -1; }
-	return check_launch("forward_raster", stream, debug != 0);
+	return check_launch("forward_render", stream, debug != 0);
+}
+
+int rr_forward_raster(void* stream, int P, int W, int H, int64_t N, const float* background,
+	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes,
+	float* out_color, float* out_depth, int variant, int debug)
+{
+	if (P == 0) return 0;
+	if (bad_ptr(background, "background") || bad_ptr(out_color, "out_color") || bad_ptr(out_depth, "out_depth")) return -1;
+	if (rr_forward_bin(stream, P, W, H, N, geom, geom_bytes, binning, binning_bytes, image, image_bytes, variant, debug)) return -1;
+	return rr_forward_render(stream, P, W, H, N, background, geom, geom_bytes, binning, binning_bytes, image, image_bytes, out_color, out_depth, variant, debug);
 }
 
 int rr_backward(void* stream_, int P, int D, int M, int W, int H, int64_t N, const float* background,

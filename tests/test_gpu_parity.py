@@ -254,9 +254,11 @@ def test_full_size_properties_config3(device):
     assert all(not v.any() for v in g0.values())
 
 
-def test_accumulate_mode_and_multiview_bucket(device):
+@pytest.mark.parametrize("two_stream", ["1", "0"])
+def test_accumulate_mode_and_multiview_bucket(device, two_stream, monkeypatch):
     from rain_b200 import multiview as mv
-    P, W, H, D, V = 30000, 160, 96, 3, 3
+    monkeypatch.setenv("RAIN_GEOM_STREAM", two_stream)          # both view pipelines: two streams (default) and one
+    P, W, H, D, V = 30000, 160, 96, 3, 5
     sc = make_scene(P, D, 8).to(device)
     cams = [make_camera(v, V, W, H).to(device) for v in range(V)]
     bg = torch.zeros(3, device=device)
