@@ -204,6 +204,11 @@ def run_ours(args, rank, world, local):
     torch.cuda.synchronize()
     st = _lib.stage_times(reset=True)
     lib.rr_prof_enable(0)
+    # Gaussians one view sees (radii > 0): the V of the per-stage byte model
+    v_probe = views_of(args.warmup + args.steps - 1)[-1]
+    slot[v_probe] = VIEWS_PER_STEP - 1
+    bucket.filled = False
+    V_seen = int((mv.render_views_fwd_bwd(params, cams_d, [v_probe], bucket, grad_resident, bg=bg, sh_degree=D, keep_outputs=True)[0].radii > 0).sum())
     os.environ["RAIN_GEOM_STREAM"] = two_stream
 
     # ---------------- end-to-end arm (host buffers -> public API -> host scalar) ----------------
@@ -256,7 +261,7 @@ def run_ours(args, rank, world, local):
     if rank != 0:
         return None
     return dict(cfg=cfg, value=value, ms=ms, e2e_value=e2e_value, ms_e2e=ms_e2e, h2d=h2d, d2h=d2h, launches=launches, stage=st, clocks=clocks,
-                N=N_last, loss=loss, bucket_bytes=bucket.nbytes())
+                N=N_last, V=V_seen, loss=loss, bucket_bytes=bucket.nbytes())
 
 
 def cpu_oracle_sample(workload, renders):
@@ -376,7 +381,7 @@ def main():
     for name, (ms, n) in r["stage"].items():
         if n == 0:
             continue
-        b = stage_bytes(name, P, P, N, X)
+        b = stage_bytes(name, P, r["V"], N, X)
         per = ms / n
         stages[name] = {"ms": round(per, 4), "share": None, "alg_bytes": b, "gbs": round(b / per / 1e6, 1) if b else None,
                         "frac_of_hbm": round(b / per / 1e6 / peak, 4) if b else None}
@@ -393,7 +398,7 @@ def main():
         "ms_per_step": round(r["ms"] / args.steps, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": {"workload": f"{args.workload}: {P} random Gaussians, {cfg['W']}x{cfg['H']}, SH degree {cfg['D']} (BASELINE.json configs[{int(args.workload[1]) - 1}])",
-                   "views_per_step_per_gpu": VIEWS_PER_STEP, "global_views_per_step": VIEWS_PER_STEP * world, "num_rendered_per_view": N,
+                   "views_per_step_per_gpu": VIEWS_PER_STEP, "global_views_per_step": VIEWS_PER_STEP * world, "num_rendered_per_view": N, "visible_per_view": r["V"],
                    "parallelism": f"view-sharded dp{world}, one f32 all-reduce of {r['bucket_bytes']} B per step" if world > 1 else "single GPU",
                    "pipeline": ("two streams: preprocess/sort/binning of the next view on a high-priority stream beside the render kernels of the current view; "
                                 "stages[] and roofline come from a one-stream pass over the same steps (a kernel's own duration), so their sum exceeds ms_per_step / views")

@@ -83,7 +83,8 @@ int rr_forward_render(void* stream, int P, int W, int H, int64_t N, const float*
  * dL_dsh / dL_dcolor, dL_dopacity, dL_dscale, dL_drot / dL_dcov3D) are ADDED to the buffers' contents and Gaussians
  * with radii == 0 are left untouched; the per-view outputs dL_dmean2D and dL_dconic are still overwritten.
  * dL_dconic may be null (the reference keeps it internal).  dL_dsh is [P,M,3] (unused when shs is null),
- * dL_dscale / dL_drot may be null when cov3D_precomp is given.  ws: rr_backward_ws_bytes(P) of scratch
+ * dL_dscale / dL_drot may be null when cov3D_precomp is given; dL_dcolor may be null when shs is used and dL_dcov3D when
+ * cov3D_precomp is not given (gradients of inputs the caller did not pass: intermediates, skipped).  ws: rr_backward_ws_bytes(P) of scratch
  * (the per-Gaussian gradient accumulators the backward render adds into; zero-filled inside). */
 int rr_backward(void* stream, int P, int D, int M, int W, int H, int64_t N, const float* background,
 	const float* means3D, const float* shs, const float* colors_precomp,

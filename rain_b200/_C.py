@@ -175,7 +175,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
                                  viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
                                  geomBuffer, R, binningBuffer, imageBuffer, debug, low_pass, return_conic=False,
-                                 grads_out=None, accumulate=False):
+                                 grads_out=None, accumulate=False, omit=()):
     """RasterizeGaussiansBackwardCUDA (rasterize_points.cu:110-191).
     Returns (dL_dmeans2D[P,3], dL_dcolors[P,3], dL_dopacity[P,1], dL_dmeans3D[P,3], dL_dcov3D[P,6], dL_dsh[P,M,3],
     dL_dscales[P,3], dL_drotations[P,4]).
@@ -183,7 +183,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     Extensions used by the view-sharded batch path (rain_b200.multiview), absent from the reference: ``grads_out`` maps
     any of "means3D", "sh", "colors", "opacity", "scales", "rotations", "cov3D" to caller-owned contiguous f32 tensors
     the kernel writes into (e.g. views of one flat allreduce bucket); ``accumulate`` adds to their contents instead
-    of overwriting (RR_BWD_ACCUMULATE)."""
+    of overwriting (RR_BWD_ACCUMULATE); ``omit`` names intermediates not to produce at all — "colors" (when ``sh`` is used)
+    and/or "cov3D" (when ``cov3D_precomp`` is not) — whose entries of the returned tuple are then None."""
     lib = _lib.load()
     dev = means3D.device
     P, H, W = means3D.size(0), dL_dout_color.size(1), dL_dout_color.size(2)
@@ -193,6 +194,11 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     dL_dmeans3D, dL_dmeans2D, dL_dcolors = new((P, 3), **f32), new((P, 3), **f32), new((P, NUM_CHANNELS), **f32)
     dL_dconic, dL_dopacity, dL_dcov3D = new((P, 2, 2), **f32), new((P, 1), **f32), new((P, 6), **f32)
     dL_dsh, dL_dscales, dL_drotations = new((P, M, 3), **f32), new((P, 3), **f32), new((P, 4), **f32)
+    has_sh = sh is not None and sh.numel() != 0 and (colors is None or colors.numel() == 0)
+    has_cov = cov3D_precomp is not None and cov3D_precomp.numel() != 0
+    for name in omit:
+        if name not in ("colors", "cov3D") or (name == "colors" and not has_sh) or (name == "cov3D" and has_cov):
+            raise RuntimeError(f"cannot omit {name!r}: it is the gradient of an input of this call")
     if grads_out is not None or accumulate:
         go = grads_out or {}
         own = dict(means3D=dL_dmeans3D, sh=dL_dsh, colors=dL_dcolors, opacity=dL_dopacity, scales=dL_dscales, rotations=dL_drotations,
@@ -205,7 +211,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
             own[k] = t
         if accumulate:
             for k, t in own.items():
-                if k not in go and t.numel():
+                if k not in go and k not in omit and t.numel():
                     t.zero_()        # slots the caller did not supply start from zero
         dL_dmeans3D, dL_dsh, dL_dcolors, dL_dopacity = own["means3D"], own["sh"], own["colors"], own["opacity"]
         dL_dscales, dL_drotations, dL_dcov3D = own["scales"], own["rotations"], own["cov3D"]
@@ -225,10 +231,10 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                                        geomBuffer.data_ptr(), geomBuffer.numel(), binningBuffer.data_ptr(), binningBuffer.numel(),
                                        imageBuffer.data_ptr(), imageBuffer.numel(),
                                        dpix.data_ptr(), ws.data_ptr(), ws.numel(),
-                                       dL_dmeans2D.data_ptr(), dL_dconic.data_ptr(), dL_dopacity.data_ptr(), dL_dcolors.data_ptr(),
-                                       dL_dmeans3D.data_ptr(), dL_dcov3D.data_ptr(), _ptr(dL_dsh), dL_dscales.data_ptr(), dL_drotations.data_ptr(),
+                                       dL_dmeans2D.data_ptr(), dL_dconic.data_ptr(), dL_dopacity.data_ptr(), None if "colors" in omit else dL_dcolors.data_ptr(),
+                                       dL_dmeans3D.data_ptr(), None if "cov3D" in omit else dL_dcov3D.data_ptr(), _ptr(dL_dsh), dL_dscales.data_ptr(), dL_drotations.data_ptr(),
                                        _variant(), int(bool(debug)), 1 if accumulate else 0), "rr_backward")
-    out = (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)
+    out = (dL_dmeans2D, None if "colors" in omit else dL_dcolors, dL_dopacity, dL_dmeans3D, None if "cov3D" in omit else dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)
     return out + (dL_dconic,) if return_conic else out
 
 

@@ -343,9 +343,11 @@ int rr_backward(void* stream_, int P, int D, int M, int W, int H, int64_t N, con
 	if (P == 0) return 0;                                                  // rasterize_points.cu:155
 	if (bad_ptr(background, "background") || bad_ptr(means3D, "means3D") || bad_ptr(radii, "radii") || bad_ptr(geom, "geom") ||
 		bad_ptr(binning, "binning") || bad_ptr(image, "image") || bad_ptr(dL_dpix, "dL_dpix") || bad_ptr(ws, "ws") ||
-		bad_ptr(dL_dmean2D, "dL_dmean2D") || bad_ptr(dL_dopacity, "dL_dopacity") || bad_ptr(dL_dcolor, "dL_dcolor") ||
-		bad_ptr(dL_dmean3D, "dL_dmean3D") || bad_ptr(dL_dcov3D, "dL_dcov3D")) return -1;
+		bad_ptr(dL_dmean2D, "dL_dmean2D") || bad_ptr(dL_dopacity, "dL_dopacity") || bad_ptr(dL_dmean3D, "dL_dmean3D")) return -1;
 	const bool use_sh = shs && !colors_precomp;
+	// the gradient of an input the caller did not pass is an intermediate: it may be omitted
+	if (!use_sh && bad_ptr(dL_dcolor, "dL_dcolor")) return -1;
+	if (cov3D_precomp && bad_ptr(dL_dcov3D, "dL_dcov3D")) return -1;
 	if (use_sh && bad_ptr(dL_dsh, "dL_dsh")) return -1;
 	const GeomLayout G = geom_layout(geom, P);
 	const BinLayout B = bin_layout(binning, N, W, H);

@@ -139,7 +139,8 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
         grads = backend.rasterize_gaussians_backward(
             bg, params["means3D"], radii, e, params["scales"], params["rotations"], scale_modifier, e, cam.viewmatrix, cam.projmatrix,
             cam.tanfovx, cam.tanfovy, dpix, params["shs"], sh_degree, cam.campos, geom, N, binning, img, debug, low_pass,
-            grads_out=bucket.grads_out(), accumulate=bucket.filled)       # the first view overwrites the bucket, later views add
+            grads_out=bucket.grads_out(), accumulate=bucket.filled,       # the first view overwrites the bucket, later views add
+            **({"omit": ("colors", "cov3D")} if backend is _native else {}))   # intermediates nobody reads (no zero fill, no read-modify-write)
         bucket.filled = True
         results.append(ViewResult(v, color if keep_outputs else None, depth if keep_outputs else None, radii if keep_outputs else None,
                                   int(N), grads[0] if keep_outputs else None))
