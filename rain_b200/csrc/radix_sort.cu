@@ -19,6 +19,9 @@ namespace rr {
 
 namespace {
 
+#ifndef SORT_BALANCED_DIGITS
+#define SORT_BALANCED_DIGITS 1
+#endif
 constexpr int RADIX_BITS = 8;
 constexpr int RADIX = 1 << RADIX_BITS;
 constexpr int SORT_THREADS = 256;
@@ -278,12 +281,26 @@ WsLayout ws_layout(void* ws, size_t n, int npass) {
 PassDesc make_passes(int begin_bit, int end_bit) {
 	PassDesc pd;
 	pd.npass = 0;
+#if SORT_BALANCED_DIGITS
+	// the bits are split evenly over the passes (13 tile bits: 7 + 6 instead of 8 + 5): a pass with fewer bins scatters in
+	// longer runs, and the wide pass is the slow one
+	const int total = (end_bit - begin_bit + RADIX_BITS - 1) / RADIX_BITS;
+	for (int b = begin_bit; b < end_bit && pd.npass < MAX_PASSES;) {
+		const int left = total - pd.npass;
+		const int nb = (end_bit - b + left - 1) / left;
+		pd.shift[pd.npass] = b;
+		pd.mask[pd.npass] = (1u << nb) - 1;
+		pd.npass++;
+		b += nb;
+	}
+#else
 	for (int b = begin_bit; b < end_bit && pd.npass < MAX_PASSES; b += RADIX_BITS) {
 		const int nb = (end_bit - b) < RADIX_BITS ? (end_bit - b) : RADIX_BITS;
 		pd.shift[pd.npass] = b;
 		pd.mask[pd.npass] = (1u << nb) - 1;
 		pd.npass++;
 	}
+#endif
 	return pd;
 }
 
