@@ -87,9 +87,14 @@ int tile_bits(int num_tiles) { int b = 0; while ((num_tiles >> b) != 0) b++; ret
 struct GeomLayout {
 	SplatRec* rec; float* cov3D; uint8_t* clamped; uint32_t* tiles_touched; uint2* rect;
 	uint32_t *key_a, *key_b, *val_a, *val_b, *offsets, *block_sums, *num_rendered; void* sort_ws;
+	unsigned long long* tile_mask;
 	size_t total;
 	int64_t off[9];
 };
+// opt-in tile culling (preprocess.cu): RAIN_TILE_CULL=1, read once; not combined with the counting binning
+bool count_binning_wanted();
+bool tile_cull_wanted() { static const bool on = []() { const char* e = getenv("RAIN_TILE_CULL"); return e && e[0] == '1' && !count_binning_wanted(); }(); return on; }
+
 GeomLayout geom_layout(void* blob, int P)
 {
 	GeomLayout L; Carver c(blob);
@@ -105,6 +110,7 @@ GeomLayout geom_layout(void* blob, int P)
 	L.block_sums = c.take<uint32_t>(scan_ws_elems((int)Pz));
 	L.num_rendered = c.take<uint32_t>(4);
 	L.sort_ws = c.take<char>(sort_ws_bytes<uint32_t>(Pz, 0, 32));
+	L.tile_mask = tile_cull_wanted() ? c.take<unsigned long long>(Pz) : nullptr;
 	L.total = c.used();
 	char* b = reinterpret_cast<char*>(blob);
 	// depth sort: 4 passes -> result back in the *_a buffers
@@ -234,6 +240,7 @@ int rr_forward_geom(void* stream_, int P, int D, int M, int W, int H,
 	a.means3D = means3D; a.scales = scales; a.rotations = rotations; a.opacities = opacities; a.shs = colors_precomp ? nullptr : shs;
 	a.cov3D_precomp = cov3D_precomp; a.colors_precomp = colors_precomp; a.view = viewmatrix; a.proj = projmatrix; a.campos = campos;
 	a.radii = radii; a.rec = L.rec; a.cov3D = L.cov3D; a.clamped = L.clamped; a.tiles_touched = L.tiles_touched; a.depth_key = L.key_a; a.rect = L.rect;
+	a.tile_mask = L.tile_mask; a.tile_cull = L.tile_mask != nullptr;
 	{ Stage st(stream, ST_PREPROCESS); if (launch_preprocess_fwd(stream, a)) return -1; }
 	if (debug && check_launch("preprocess_fwd", stream, true)) return -1;
 	// depth order of the Gaussians: 32-bit keys, 4 passes, result in the *_a buffers
@@ -278,7 +285,7 @@ int rr_forward_bin(void* stream_, int P, int W, int H, int64_t N,
 		if (N > 0 && launch_count_binning(stream, P, grid_x * grid_y, grid_x, G.val_a, G.tiles_touched, G.rect, I.cb_ws, I.ranges, B.point_list)) return -1;
 		if (debug && check_launch("count binning", stream, true)) return -1;
 	} else if (N > 0) {
-		{ Stage st(stream, ST_DUPLICATE); if (launch_duplicate(stream, P, G.val_a, G.offsets, G.rect, grid_x, B.key_a, B.val_a)) return -1; }
+		{ Stage st(stream, ST_DUPLICATE); if (launch_duplicate(stream, P, G.val_a, G.offsets, G.rect, G.tile_mask, grid_x, B.key_a, B.val_a)) return -1; }
 		if (debug && check_launch("duplicate", stream, true)) return -1;
 		int which;
 		{ Stage st(stream, ST_TILE_SORT); which = sort_pairs<uint32_t>(stream, B.key_a, B.key_b, B.val_a, B.val_b, (size_t)N, 0, B.bits, B.sort_ws, false); }

@@ -152,8 +152,10 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_chained_kernel(int P, int n
 // contiguous span is owned by the last lane whose exclusive offset is <= s (binary search over 32 shared values),
 // so writes are coalesced and a large splat does not serialise on one thread (reference: one thread per rect).
 __global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ offsets,
-	const uint2* __restrict__ rect, int grid_x, uint32_t* __restrict__ tile_keys, uint32_t* __restrict__ gaussian_ids)
+	const uint2* __restrict__ rect, const unsigned long long* __restrict__ tile_mask, int grid_x, uint32_t* __restrict__ tile_keys,
+	uint32_t* __restrict__ gaussian_ids)
 {
+	__shared__ unsigned long long s_mask[8][32];
 	__shared__ uint32_t s_excl[8][32];
 	__shared__ uint32_t s_g[8][32];
 	__shared__ uint32_t s_xw[8][32];   // x0 | width<<16
@@ -173,10 +175,13 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* _
 	const uint32_t total = end - base;
 	const uint32_t tt = i < P ? incl - excl : 0u;
 	uint32_t x0 = 0, wdt = 1, y0 = 0;
+	unsigned long long mask = ~0ull;
 	if (tt > 0) {
 		const uint2 r = rect[g];
 		x0 = r.x & 0xffffu; wdt = (r.x >> 16) - x0; y0 = r.y & 0xffffu;
+		if (tile_mask) mask = tile_mask[g];
 	}
+	s_mask[warp][lane] = mask;
 	s_excl[warp][lane] = i < P ? excl - base : total;
 	s_g[warp][lane] = g;
 	s_xw[warp][lane] = x0 | (wdt << 16);
@@ -187,7 +192,20 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* _
 		int lo = 0;
 		#pragma unroll
 		for (int step = 16; step >= 1; step >>= 1) if (s_excl[warp][lo + step] <= s) lo += step;
-		const uint32_t local = s - s_excl[warp][lo];
+		uint32_t local = s - s_excl[warp][lo];
+		const unsigned long long m = s_mask[warp][lo];
+		if (m != ~0ull) {
+			// culled rect (preprocess.cu): the local-th kept tile
+			const uint32_t mlo = (uint32_t)m, mhi = (uint32_t)(m >> 32), c = (uint32_t)__popc(mlo);
+			uint32_t word = mlo, n = local, pos = 0;
+			if (local >= c) { word = mhi; n = local - c; pos = 32; }
+			#pragma unroll
+			for (uint32_t wd = 16; wd >= 1; wd >>= 1) {          // position of the n-th set bit of word
+				const uint32_t below = (uint32_t)__popc(word & ((1u << wd) - 1u));
+				if (n >= below) { n -= below; word >>= wd; pos += wd; }
+			}
+			local = pos;
+		}
 		const uint32_t xw = s_xw[warp][lo];
 		const uint32_t w = xw >> 16, xx0 = xw & 0xffffu;
 		const uint32_t ry = local / w, rx = local - ry * w;
@@ -264,11 +282,11 @@ int launch_scan_tiles(cudaStream_t stream, int P, const uint32_t* order, const u
 	return check_launch("scan_tiles", stream, false);
 }
 
-int launch_duplicate(cudaStream_t stream, int P, const uint32_t* order, const uint32_t* offsets, const uint2* rect, int grid_x,
-	uint32_t* tile_keys, uint32_t* gaussian_ids)
+int launch_duplicate(cudaStream_t stream, int P, const uint32_t* order, const uint32_t* offsets, const uint2* rect, const unsigned long long* tile_mask,
+	int grid_x, uint32_t* tile_keys, uint32_t* gaussian_ids)
 {
 	if (P == 0) return 0;
-	count_launch(), duplicate_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, order, offsets, rect, grid_x, tile_keys, gaussian_ids);
+	count_launch(), duplicate_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, order, offsets, rect, tile_mask, grid_x, tile_keys, gaussian_ids);
 	return check_launch("duplicate", stream, false);
 }
 

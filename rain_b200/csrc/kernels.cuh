@@ -15,6 +15,8 @@ struct PreprocessArgs {
 	uint32_t* tiles_touched;  // [P]
 	uint32_t* depth_key;      // [P] float bits of view-space depth, 0xFFFFFFFF when culled
 	uint2* rect;              // [P] x0 | x1<<16, y0 | y1<<16
+	unsigned long long* tile_mask;   // [P] tile culling (opt-in): bit ry * w + rx of the rect is set if that tile can receive a contribution; ~0 = all
+	int tile_cull;
 };
 int launch_preprocess_fwd(cudaStream_t, const PreprocessArgs&);
 int launch_mark_visible(cudaStream_t, int P, const float* means3D, const float* view, uint8_t* present);
@@ -23,7 +25,7 @@ int launch_mark_visible(cudaStream_t, int P, const float* means3D, const float* 
 size_t scan_ws_elems(int P);
 int launch_scan_tiles(cudaStream_t, int P, const uint32_t* order, const uint32_t* tiles_touched, uint32_t* offsets /*inclusive, depth order*/,
 	uint32_t* block_sums, uint32_t* num_rendered_dev, uint32_t* num_rendered_mapped /*device-visible alias of a pinned host word, or null*/);
-int launch_duplicate(cudaStream_t, int P, const uint32_t* order, const uint32_t* offsets, const uint2* rect, int grid_x,
+int launch_duplicate(cudaStream_t, int P, const uint32_t* order, const uint32_t* offsets, const uint2* rect, const unsigned long long* tile_mask /*or null*/, int grid_x,
 	uint32_t* tile_keys /*[N] emission order*/, uint32_t* gaussian_ids /*[N] emission order*/);
 int launch_tile_ranges(cudaStream_t, size_t N, const uint32_t* sorted_tile_keys, uint2* ranges, int num_tiles);
 int launch_pack(cudaStream_t, size_t N, const uint32_t* point_list, const SplatRec* rec, SplatRec* packed);

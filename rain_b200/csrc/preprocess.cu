@@ -9,6 +9,7 @@
 // contract"); the compiler can neither contract nor reassociate these.
 #include "common.cuh"
 #include "kernels.cuh"
+#include "render_common.cuh"
 
 namespace rr {
 
@@ -66,15 +67,18 @@ __device__ __forceinline__ void cov3d_from_scale_rot(float s0, float s1, float s
 #ifndef PF_MIN_CTAS
 #define PF_MIN_CTAS 4      // 64 registers: 4 CTAs (32 warps) per SM instead of 3; 0.081 -> 0.078 ms
 #endif
+template <bool TILE_CULL>
 __global__ void __launch_bounds__(256, PF_MIN_CTAS) preprocess_fwd_kernel(PreprocessArgs a)
 {
 	const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-	if (idx >= a.P) return;
+	const bool live = idx < a.P;
+	if (!TILE_CULL && !live) return;            // the culling variant keeps whole warps for its cooperative pass
 	const float* __restrict__ V = a.view;
 	const float* __restrict__ Pm = a.proj;
 
-	const float px = a.means3D[3 * (size_t)idx], py = a.means3D[3 * (size_t)idx + 1], pz = a.means3D[3 * (size_t)idx + 2];
-	const float view_z = xform(V, 2, px, py, pz);
+	float px = 0, py = 0, pz = 0;
+	if (live) { px = a.means3D[3 * (size_t)idx]; py = a.means3D[3 * (size_t)idx + 1]; pz = a.means3D[3 * (size_t)idx + 2]; }
+	const float view_z = live ? xform(V, 2, px, py, pz) : 0.0f;
 
 	int radius = 0;
 	uint32_t tiles = 0, depth_key = 0xFFFFFFFFu;
@@ -82,7 +86,7 @@ __global__ void __launch_bounds__(256, PF_MIN_CTAS) preprocess_fwd_kernel(Prepro
 	bool visible = false;
 	float conx = 0, cony = 0, conz = 0, pix_x = 0, pix_y = 0;
 
-	if (!(view_z <= 0.2f)) {
+	if (live && !(view_z <= 0.2f)) {
 		const float hx = xform(Pm, 0, px, py, pz), hy = xform(Pm, 1, px, py, pz), hw = xform(Pm, 3, px, py, pz);
 		const float p_w = DIV(1.0f, ADD(hw, 0.0000001f));
 		const float projx = MUL(hx, p_w), projy = MUL(hy, p_w);
@@ -152,6 +156,52 @@ __global__ void __launch_bounds__(256, PF_MIN_CTAS) preprocess_fwd_kernel(Prepro
 		}
 	}
 
+	if (TILE_CULL) {
+		// opt-in (RAIN_TILE_CULL=1): drop the tiles of the rect in which the reference's own alpha test (power > 0 or
+		// alpha < 1/255 -> skip, forward.cu:330-340) rejects this Gaussian at every pixel — the same conservative test the
+		// render kernel applies per 8x4 block.  Images and gradients do not change; the internal lists and num_rendered
+		// get shorter.  Rects of more than 64 tiles are kept whole.  The warp tests the tiles of its 32 Gaussians
+		// together, one tile per lane and step (a per-thread loop runs as long as the largest rect of the warp).
+		__shared__ float s_par[8][32][8];
+		__shared__ uint32_t s_rc[8][32][2], s_ex[8][33];
+		__shared__ uint32_t s_mask[8][32][2];
+		const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+		const uint32_t x0 = rect.x & 0xffffu, w = (rect.x >> 16) - x0, y0 = rect.y & 0xffffu;
+		ContribTest ct = make_contrib_test(conx, cony, conz, visible ? a.opacities[idx] : 1.0f);
+		const uint32_t mine = (visible && tiles <= 64u && !ct.keep_all) ? tiles : 0u;
+		uint32_t incl = mine;
+		#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
+		const uint32_t total = __shfl_sync(FULL, incl, 31);
+		float* pr = s_par[warp][lane];
+		pr[0] = pix_x; pr[1] = pix_y; pr[2] = ct.A; pr[3] = ct.B; pr[4] = ct.C; pr[5] = ct.ia; pr[6] = ct.ic; pr[7] = ct.t;
+		s_rc[warp][lane][0] = x0 | (w << 16); s_rc[warp][lane][1] = y0;
+		s_ex[warp][lane] = incl - mine;
+		if (lane == 0) s_ex[warp][32] = total;
+		s_mask[warp][lane][0] = 0u; s_mask[warp][lane][1] = 0u;
+		__syncwarp();
+		for (uint32_t s = lane; s < total; s += 32) {
+			int lo = 0;                                      // last lane whose exclusive offset is <= s and that owns tiles
+			#pragma unroll
+			for (int step = 16; step >= 1; step >>= 1) if (s_ex[warp][lo + step] <= s) lo += step;
+			const uint32_t local = s - s_ex[warp][lo];
+			const float* q = s_par[warp][lo];
+			ContribTest c; c.A = q[2]; c.B = q[3]; c.C = q[4]; c.ia = q[5]; c.ic = q[6]; c.t = q[7]; c.keep_all = false;
+			const uint32_t xw = s_rc[warp][lo][0], ww = xw >> 16;
+			const uint32_t ry = local / ww, rx = local - ry * ww;
+			const float X0 = (float)(((xw & 0xffffu) + rx) * 16u), Y0 = (float)((s_rc[warp][lo][1] + ry) * 16u);
+			if (may_contribute(c, q[0], q[1], X0, X0 + 15.0f, Y0, Y0 + 15.0f)) atomicOr(&s_mask[warp][lo][local >> 5], 1u << (local & 31u));
+		}
+		__syncwarp();
+		if (!live) return;
+		unsigned long long mask = ~0ull;
+		if (mine) {
+			const unsigned long long m = (unsigned long long)s_mask[warp][lane][0] | ((unsigned long long)s_mask[warp][lane][1] << 32);
+			const uint32_t kept = (uint32_t)__popcll(m);
+			if (kept != tiles) { mask = m; tiles = kept; }
+		}
+		if (visible) a.tile_mask[idx] = mask;
+	}
 	a.radii[idx] = radius;
 	a.tiles_touched[idx] = tiles;
 	a.depth_key[idx] = depth_key;
@@ -282,7 +332,8 @@ __global__ void __launch_bounds__(256) mark_visible_kernel(int P, const float* _
 int launch_preprocess_fwd(cudaStream_t stream, const PreprocessArgs& a)
 {
 	if (a.P == 0) return 0;
-	count_launch(), preprocess_fwd_kernel<<<(a.P + 255) / 256, 256, 0, stream>>>(a);
+	if (a.tile_cull) count_launch(), preprocess_fwd_kernel<true><<<(a.P + 255) / 256, 256, 0, stream>>>(a);
+	else count_launch(), preprocess_fwd_kernel<false><<<(a.P + 255) / 256, 256, 0, stream>>>(a);
 	return check_launch("preprocess_fwd", stream, false);
 }
 
