@@ -8,15 +8,17 @@
 //    4 (default) three 16-byte cp.async per record with cp.async.mbarrier.arrive.noinc; 2 one 48-byte TMA bulk copy
 //    (cp.async.bulk) per record — measured slower here, because a per-lane bulk-copy address is issued lane by lane
 //    through the uniform datapath; 1 ONE bulk copy of a packed span (needs the pack pass); 0 / 3 plain loads
-//    (cross-checks).  A stage is refilled when every consumer warp has released it: each warp publishes the
-//    number of batches it is done with in a shared word (release store), the producer polls the minimum every
-//    FWD_POLL_NS;
+//    (cross-checks).  A stage is refilled when every consumer warp has released it: one arrival per warp and batch on
+//    the stage's `empty` mbarrier, on which the producer sleeps in hardware (an earlier version polled per-warp
+//    progress words every 256 ns: ~9 % of the kernel's warp instructions, all on the producer's scheduler);
 //  * each CONSUMER warp owns an 8x4 pixel block and runs through the ring at its own pace: it culls a staged batch
 //    against its block (one splat per lane: AABB, then the exact concave-maximum test of render_common.cuh), compacts
 //    the survivors with ballot/popc, and blends only those — two survivors per iteration, sharing the packed steps
 //    of the bit-exact exponential (exp2x) — so warps that own easy pixels do not wait for the others;
-//  * a warp whose 32 pixels are saturated publishes "released everything" and leaves at once; the producer stops
-//    filling when all 8 warps have;
+//  * a warp whose 32 pixels are saturated stops working but keeps the handshake going as a "ghost" (wait full, arrive
+//    empty: a few instructions per batch, asleep otherwise; its registers belong to the CTA until the CTA retires
+//    anyway); when all 8 warps are ghosts the producer stops filling, completes the next `full` phase without data
+//    and raises s_stop, on which the ghosts leave;
 //  * each warp leaves one bit per list entry ("blended into one of my pixels", kernels.cuh) for the backward.
 // The per-pair arithmetic (power, exp, alpha, T test, accumulation) is spelled with explicit-rounding intrinsics in
 // exactly the order of the reference build so final_T, n_contrib and the colours are reproduced bit for bit.
@@ -29,9 +31,6 @@ namespace rr {
 namespace {
 
 constexpr int FWD_STAGES = 4;
-#ifndef FWD_POLL_NS
-#define FWD_POLL_NS 256      // producer back-off between polls of the released counters (the ring keeps it 3 batches ahead; polling at 32 ns cost 9 % of the kernel's issue slots)
-#endif
 constexpr int FWD_THREADS = RENDER_THREADS + 32;      // 8 consumer warps + the producer warp
 
 // Producer: fill one stage with `cnt` records starting at list position `first`; completion is signalled on `bar`
@@ -66,7 +65,9 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MIN_CTAS) render_fwd_kernel(R
 {
 	__shared__ __align__(128) float4 s_rec[FWD_STAGES][BATCH * 3];
 	__shared__ __align__(8) uint64_t s_full[FWD_STAGES];
-	__shared__ int s_released[RENDER_WARPS];                            // batches each consumer warp is done with (INT_MAX: saturated, gone)
+	__shared__ __align__(8) uint64_t s_empty[FWD_STAGES];               // one arrival per consumer warp and batch: "I am past this stage"
+	__shared__ int s_gone;                                              // consumer warps whose 32 pixels are all saturated (or outside the image)
+	__shared__ int s_stop;                                              // the batch at which the producer stopped filling early (all warps gone); -1: it has not
 	__shared__ uint8_t s_list[RENDER_WARPS][BATCH];
 	__shared__ __align__(4) uint8_t s_used[RENDER_WARPS][BATCH];      // 1 if the warp blended the entry into at least one of its pixels
 
@@ -77,8 +78,8 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MIN_CTAS) render_fwd_kernel(R
 	const int nbatches = (n + BATCH - 1) / BATCH;
 
 	if (tid == 0) {
-		for (int s = 0; s < FWD_STAGES; s++) mbar_init(&s_full[s], StageMode<MODE>::full_count);
-		for (int w = 0; w < RENDER_WARPS; w++) s_released[w] = 0;
+		for (int s = 0; s < FWD_STAGES; s++) { mbar_init(&s_full[s], StageMode<MODE>::full_count); mbar_init(&s_empty[s], RENDER_WARPS); }
+		s_gone = 0; s_stop = -1;
 		mbar_fence_init();
 	}
 	__syncthreads();
@@ -88,27 +89,25 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MIN_CTAS) render_fwd_kernel(R
 		const float4* __restrict__ src = reinterpret_cast<const float4*>(a.packed) + (size_t)range.x * 3;
 		const float4* __restrict__ grec = reinterpret_cast<const float4*>(a.rec);
 		const uint32_t* __restrict__ ids = a.point_list + range.x;
-		int b = 0;
-		for (; b < nbatches; b++) {
+		for (int b = 0; b < nbatches; b++) {
 			const int s = b % FWD_STAGES;
 			if (b >= FWD_STAGES) {
-				// wait until every consumer warp is past batch b - FWD_STAGES; stop when all of them are saturated
-				int low;
-				for (;;) {
-					const int r = lane < RENDER_WARPS ? *reinterpret_cast<volatile int*>(&s_released[lane]) : 0x7fffffff;
-					low = __reduce_min_sync(FULL, r);
-					if (low > b - FWD_STAGES) break;
-					__nanosleep(FWD_POLL_NS);
+				// sleep (in hardware, no polling) until every consumer warp is past batch b - FWD_STAGES
+				mbar_wait(&s_empty[s], (uint32_t)(b / FWD_STAGES - 1) & 1u);
+				if (*reinterpret_cast<volatile int*>(&s_gone) == RENDER_WARPS) {
+					// every pixel of the tile is saturated: stop filling.  The warps are all ghosts by now and will reach
+					// batch b (the earlier ones are filled); complete its `full` phase without data so that they wake, see
+					// s_stop and leave.
+					if (lane == 0) *reinterpret_cast<volatile int*>(&s_stop) = b;
+					__syncwarp();
+					if (lane < (int)StageMode<MODE>::full_count) mbar_arrive(&s_full[s]);
+					return;
 				}
-				if (low == 0x7fffffff) break;
 				__threadfence_block();       // the consumers' reads of the stage are ordered before the refill below
 			}
 			producer_fill<MODE>(&s_rec[s][0], &s_full[s], src, grec, ids, b * BATCH, min(BATCH, n - b * BATCH), lane);
 		}
-		__syncwarp();
-		// fills still in flight must land before the CTA (and its shared memory) retires
-		if (lane == 0)
-			for (int bb = max(0, b - FWD_STAGES); bb < b; bb++) mbar_wait(&s_full[bb % FWD_STAGES], (uint32_t)(bb / FWD_STAGES) & 1u);
+		// every consumer warp waits on every filled batch before it leaves, so no fill is in flight when the CTA retires
 		return;
 	}
 
@@ -132,11 +131,18 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MIN_CTAS) render_fwd_kernel(R
 	uint32_t last_contributor = 0;
 	bool done = !inside;
 	bool warp_done = __all_sync(FULL, done);
+	if (warp_done && lane == 0) atomicAdd(&s_gone, 1);
 
-	for (int b = 0; b < nbatches && !warp_done; b++) {
+	// Every consumer warp walks every filled batch: wait for the stage, work on it (or not: a warp whose pixels are all
+	// saturated is a "ghost" that only keeps the handshake going, asleep in the barrier wait), release the stage.
+	for (int b = 0; b < nbatches; b++) {
 		const int s = b % FWD_STAGES;
-		mbar_wait(&s_full[s], (uint32_t)(b / FWD_STAGES) & 1u);       // an unsaturated warp keeps the producer filling
-		{
+		mbar_wait(&s_full[s], (uint32_t)(b / FWD_STAGES) & 1u);
+		if (warp_done) {
+			// the producer stopped at this batch: nothing was filled.  (Only at this batch: a ghost leaves after it has
+			// waited for every fill that was issued, so none is in flight when the CTA retires.)
+			if (*reinterpret_cast<volatile int*>(&s_stop) == b) break;
+		} else {
 			const int cnt = min(BATCH, n - b * BATCH);
 			const float4* __restrict__ rec = s_rec[s];
 			// this warp's "used" row for the batch starts from zero (one 4-byte store per lane covers the 128 entries)
@@ -237,13 +243,12 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MIN_CTAS) render_fwd_kernel(R
 				if (lane == c) myword = wd;
 			}
 			if (lane < BATCH / 32 && lane * 32 < cnt) wflags[b * (BATCH / 32) + lane] = myword;
+			if (warp_done && lane == 0) atomicAdd(&s_gone, 1);         // before the release below, so the producer sees it
 		}
-		// this warp is past the stage: publish it (release: the stage reads above come first)
+		// this warp is past the stage (mbarrier.arrive is a release: the stage reads above come first)
 		__syncwarp();
-		if (lane == 0) { __threadfence_block(); *reinterpret_cast<volatile int*>(&s_released[warp]) = b + 1; }
+		if (lane == 0) mbar_arrive(&s_empty[s]);
 	}
-	// saturated or at the end of the list: nothing more will be read from the ring
-	if (lane == 0) { __threadfence_block(); *reinterpret_cast<volatile int*>(&s_released[warp]) = 0x7fffffff; }
 
 	if (inside) {
 		const size_t pid = (size_t)a.W * pix_y + pix_x, HW = (size_t)a.H * a.W;
