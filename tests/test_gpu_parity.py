@@ -117,6 +117,27 @@ def test_shapes_and_settings_match_reference_cuda(device, refcuda, P, W, H, D, s
     check_against_ref(fw, g, refcuda, N_r, color_r, radii_r, depth_r, g_r, dpix)
 
 
+@pytest.mark.parametrize("P,W,H,opaque", [(200_000, 40, 24, True), (200_000, 40, 24, False), (60_000, 33, 50, True), (700, 40, 24, True)])
+def test_forward_ring_handshake_long_lists_early_saturation(device, refcuda, P, W, H, opaque):
+    """The forward's stage ring (csrc/render_fwd.cu: full / empty mbarriers, ghost warps, the producer's early stop): tile
+    lists of hundreds of batches whose pixels saturate within the first ones (opaque), or never (translucent: every batch is
+    walked), on images whose last tile row / column is partly outside (warps that are ghosts from the start), and lists that
+    end inside the first ring round (fewer than FWD_STAGES batches).  Everything against the reference CUDA."""
+    sc = make_scene(P, 1, seed=11, scale_mult=3.0).to(device); cam = make_camera(1, 4, W, H).to(device)
+    if opaque:
+        sc.opacities.fill_(0.999)
+    else:
+        sc.opacities.mul_(0.02)
+    bg = torch.tensor((0.1, 0.2, 0.3), device=device); dpix = make_grad(W, H, 5).to(device)
+    fw = mine_forward(sc, cam, bg)
+    g = mine_backward(fw, sc, cam, bg, dpix)
+    N_r, color_r, radii_r, depth_r = ref_forward(refcuda, sc, cam, bg)
+    g_r = refcuda.backward(dpix)
+    if P >= 60_000:
+        assert N_r > 128 * 8 * ((W + 15) // 16) * ((H + 15) // 16)      # more than two ring rounds per tile on average
+    check_against_ref(fw, g, refcuda, N_r, color_r, radii_r, depth_r, g_r, dpix)
+
+
 def test_precomputed_colour_and_covariance_modes(device, refcuda):
     P, W, H = 4000, 96, 80
     sc = make_scene(P, 0, 9, 1.5).to(device); cam = make_camera(1, 3, W, H).to(device)
