@@ -213,7 +213,6 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MIN_CTAS) render_fwd_kernel(R
 							C01 = fma2(T2, mul2(a2, pk(rb.z, rb.w)), C01);
 							C2D = fma2(T2, mul2(a2, pk(rc.x, rc.y)), C2D);
 							T = bl ? test_T : T;
-							last_contributor = bl ? pos1 + (uint32_t)e : last_contributor;
 							usedbits |= bl ? b1 : 0u;
 						};
 						blend(e0, power0, alpha0, rb0, ubit);
@@ -231,6 +230,9 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MIN_CTAS) render_fwd_kernel(R
 					}
 					if (__all_sync(FULL, done)) { warp_done = true; break; }
 				}
+				// n_contrib (forward.cu:353-355): the last entry this pixel blended is the highest bit of usedbits — looked up
+				// once per chunk instead of a select per survivor
+				if (usedbits) last_contributor = pos1 + (uint32_t)list[kc + 31 - __clz(usedbits)];
 				const unsigned wbits = __reduce_or_sync(FULL, usedbits);
 				if ((wbits >> lane) & 1u) used[list[kc + lane]] = 1;
 			}
