@@ -212,12 +212,19 @@ def run_ours(args, rank, world, local):
     os.environ["RAIN_GEOM_STREAM"] = two_stream
 
     # ---------------- end-to-end arm (host buffers -> public API -> host scalar) ----------------
-    pinned = [dict(view=c.viewmatrix.pin_memory(), proj=c.projmatrix.pin_memory(), campos=c.campos.pin_memory()) for c in cams_h]
-    dev_cam = [dict(view=torch.empty(4, 4, device=dev), proj=torch.empty(4, 4, device=dev), campos=torch.empty(3, device=dev)) for _ in range(VIEWS_PER_STEP)]
+    # cameras: one 48-float row per camera (view 16 | proj 16 | campos 3 | pad) in pinned host memory; the rows of a step's
+    # views are gathered into one pinned staging block and cross PCIe as ONE copy per step (24 small copies before)
+    cam_rows = torch.zeros(len(cams_h), 48)
+    for ci, c in enumerate(cams_h):
+        cam_rows[ci, :16] = c.viewmatrix.reshape(-1); cam_rows[ci, 16:32] = c.projmatrix.reshape(-1); cam_rows[ci, 32:35] = c.campos
+    cam_rows = cam_rows.pin_memory()
+    cam_stage = torch.zeros(VIEWS_PER_STEP, 48).pin_memory()
+    cam_dev = torch.zeros(VIEWS_PER_STEP, 48, device=dev)
+    dev_cam = [dict(view=cam_dev[i, :16].view(4, 4), proj=cam_dev[i, 16:32].view(4, 4), campos=cam_dev[i, 32:35]) for i in range(VIEWS_PER_STEP)]
     feed = mv.HostFeed([(3, H, W)] * VIEWS_PER_STEP, dev, dtype=torch.uint8)     # target images: pinned host -> device on a side stream, overlapped with the renders
     loss_dev = torch.zeros(1, device=dev)
     loss_host = torch.zeros(1).pin_memory()
-    h2d = VIEWS_PER_STEP * ((16 + 16 + 3) * 4 + 3 * H * W)      # camera matrices + one 8-bit target image per view
+    h2d = VIEWS_PER_STEP * (48 * 4 + 3 * H * W)      # one padded camera row + one 8-bit target image per view
     d2h = 4 + VIEWS_PER_STEP * 8          # loss scalar + num_rendered (8 B, read inside the forward) per view
     from rain_b200.synthetic import Camera
 
@@ -226,9 +233,9 @@ def run_ours(args, rank, world, local):
         cams_step = {}
         if not E2E_DIAG_NO_FEED:
             feed.stage_slot(0, targets_h[0])       # view i+1's image is staged when view i reaches its loss: one short transfer in flight
+        torch.index_select(cam_rows, 0, torch.as_tensor(ids), out=cam_stage)      # the previous step's copy has completed (per-step sync)
+        cam_dev.copy_(cam_stage, non_blocking=True)
         for i, v in enumerate(ids):
-            for k in ("view", "proj", "campos"):
-                dev_cam[i][k].copy_(pinned[v][k], non_blocking=True)
             cams_step[v] = Camera(W, H, cams_h[v].tanfovx, cams_h[v].tanfovy, dev_cam[i]["view"], dev_cam[i]["proj"], dev_cam[i]["campos"])
         slot.clear(); slot.update({v: i for i, v in enumerate(ids)})
         loss_dev.zero_()
