@@ -89,7 +89,7 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
 
     side = _geom_stream(dev) if hasattr(backend, "forward_bin") else None
 
-    def geom_pass(v):
+    def geom_pass(v, stream=None):
         cam = cameras[v]
         args = (bg, params["means3D"], e, params["opacities"], params["scales"], params["rotations"], scale_modifier, e,
                 cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, cam.height, cam.width, params["shs"], sh_degree, cam.campos,
@@ -98,8 +98,9 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
             return args
         if side is None:
             return backend.forward_geom(*args)
-        side.wait_stream(torch.cuda.current_stream(dev))
-        return backend.forward_geom(*args, stream=side)
+        stream = side if stream is None else stream
+        stream.wait_stream(torch.cuda.current_stream(dev))
+        return backend.forward_geom(*args, stream=stream)
 
     view_ids = list(view_ids)
     n = len(view_ids)
@@ -116,9 +117,15 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
 
         ahead = {}
         if n:
-            ahead[0] = bin_pass(geom_pass(view_ids[0]))
-        if n > 1:
-            ahead[1] = geom_pass(view_ids[1])
+            g0 = geom_pass(view_ids[0])
+            if n > 1 and _START_OVERLAP:
+                # step start: nothing runs beside view 0's front yet, so view 1's geometry half goes on a second side stream
+                # next to it (two latency-bound fronts overlap well); enqueued before the host blocks on view 0's num_rendered
+                side2 = _geom_stream(dev, 1)
+                ahead[1] = geom_pass(view_ids[1], stream=side2)
+            ahead[0] = bin_pass(g0)
+            if n > 1 and not _START_OVERLAP:
+                ahead[1] = geom_pass(view_ids[1])
     else:
         # software pipeline over the views: the first half of view i+1 (preprocess, depth sort, prefix sum) is enqueued BEFORE
         # the backward of view i, so its num_rendered is on the host long before it is needed and the device never waits for
@@ -153,12 +160,15 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
 _geom_streams = {}
 
 
-def _geom_stream(dev):
+_START_OVERLAP = os.environ.get("RAIN_START_OVERLAP", "1") == "1"
+
+
+def _geom_stream(dev, which=0):
     """The high-priority side stream of the two-stream view pipeline (render_views_fwd_bwd); RAIN_GEOM_STREAM=0 turns the
     pipeline back into the one-stream order (one B200, 8 views of 1M Gaussians at 1080p: 1.263 -> 1.173 ms per view)."""
     if os.environ.get("RAIN_GEOM_STREAM", "1") != "1":
         return None
-    key = torch.device(dev).index
+    key = (torch.device(dev).index, which)
     if key not in _geom_streams:
         _geom_streams[key] = torch.cuda.Stream(device=dev, priority=int(os.environ.get('RAIN_GEOM_PRIO', '-1')))
     return _geom_streams[key]
