@@ -30,7 +30,10 @@ namespace rr {
 
 namespace {
 
-constexpr int FWD_STAGES = 4;
+#ifndef RR_FWD_STAGES
+#define RR_FWD_STAGES 4
+#endif
+constexpr int FWD_STAGES = RR_FWD_STAGES;
 constexpr int FWD_THREADS = RENDER_THREADS + 32;      // 8 consumer warps + the producer warp
 
 // Producer: fill one stage with `cnt` records starting at list position `first`; completion is signalled on `bar`
@@ -146,7 +149,7 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MIN_CTAS) render_fwd_kernel(R
 			const int cnt = min(BATCH, n - b * BATCH);
 			const float4* __restrict__ rec = s_rec[s];
 			// this warp's "used" row for the batch starts from zero (one 4-byte store per lane covers the 128 entries)
-			reinterpret_cast<uint32_t*>(used)[lane] = 0u;
+			if (lane < BATCH / 4) reinterpret_cast<uint32_t*>(used)[lane] = 0u;
 			// stage 1: cheap AABB cull against this warp's 8x4 pixels, one splat per lane, survivors compacted
 			int n1 = 0;
 			for (int c = 0; c < cnt; c += 32) {
