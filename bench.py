@@ -3,14 +3,20 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload C3|C2|C1|C4]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
 
-A "step": every rank renders VIEWS_PER_STEP different camera views of the same synthetic scene forward + backward
-(default workload C3 = BASELINE.json configs[2], the one the metric is quoted on: 1M Gaussians, 1920x1080, SH degree 3),
+A "step": every rank renders its views of the step (different cameras of the same synthetic scene) forward + backward,
 accumulating the parameter gradients of its views into one flat bucket (59 floats per Gaussian), followed — for N > 1 — by
-ONE NCCL all-reduce of that bucket (view-sharded data parallelism).  Scaling is weak: per-GPU work is fixed.
-`value` = views rendered by all ranks / max-over-ranks device time, inputs resident in HBM.
-`e2e`   = the same step driven from HOST buffers through the public API: per view the camera matrices and the target
-          image are copied from pinned host memory, the loss gradient is formed on the device, and the loss scalar and
-          num_rendered are read back.
+ONE NCCL all-reduce of that bucket (view-sharded data parallelism).
+  * default workload C3 = BASELINE.json configs[2], the one the metric is quoted on (1M Gaussians, 1920x1080, SH degree 3):
+    8 views per rank and step; scaling is WEAK (per-GPU work fixed);
+  * workload C4 = BASELINE.json configs[3] (6M Gaussians, a 64-view batch): the 64 views of a step are SHARDED over the
+    ranks (64 / N each), one 1.42 GB all-reduce per step; scaling is STRONG (total work fixed).
+`value`  = views rendered by all ranks / max-over-ranks device time, inputs resident in HBM.
+`e2e`    = the same step driven from HOST buffers through the public API: per view the camera matrices and the target
+           image are copied from pinned host memory, the loss gradient is formed on the device, and the loss scalar and
+           num_rendered are read back.
+`dropin` = (N = 1) the metric exactly as SURVEY.md §8(d) defines it: ONE view at a time through the unchanged reference
+           API — GaussianRasterizationSettings + GaussianRasterizer(...)(...) + autograd backward, as
+           gaussian_renderer/__init__.py:20-64 drives it — no view pipeline, no gradient bucket.
 Prints ONE JSON line on rank 0.
 """
 import argparse
@@ -34,9 +40,35 @@ from rain_b200.synthetic import CONFIGS, make_camera, make_grad, make_scene  # n
 # diagnostics of the end-to-end arm only (never set for a reported number): skip the target-image H2D feed / the per-step host sync
 E2E_DIAG_NO_FEED = os.environ.get("RAIN_E2E_DIAG", "").find("nofeed") >= 0
 E2E_DIAG_NO_SYNC = os.environ.get("RAIN_E2E_DIAG", "").find("nosync") >= 0
-VIEWS_PER_STEP = 8          # views each rank renders per step (BASELINE.json config 4: a 64-view batch over 8 GPUs)
 NUM_CAMERAS = 64            # the view pool (BASELINE.json config 4 uses a 64-view batch)
+NUM_TARGETS = 8             # distinct target images (8-bit, pinned on the host); view slot i of a step uses image i % 8
 METRIC = "fwd+bwd renders/sec (1M Gaussians, 1920x1080) at 1/2/4/8 B200"
+# flops per evaluated (pixel, list entry) pair, SURVEY.md §8(d): the reference's forward spends ~15 flop on a pair its alpha
+# test rejects and ~26 on one it blends (forward.cu:325-351); its backward ~65 on a blended pair (backward.cu:481-544) and
+# the same ~15 on a rejected one
+FLOP_FWD_REJECT, FLOP_FWD_BLEND, FLOP_BWD_REJECT, FLOP_BWD_BLEND = 15, 26, 15, 65
+
+
+def views_per_rank(workload, world):
+    """views each rank renders per step: 8 (weak scaling) except for C4, whose 64-view batch is sharded over the ranks"""
+    if workload != "C4":
+        return 8
+    if 64 % world:
+        raise SystemExit("workload C4 shards a 64-view batch: --gpus must divide 64")
+    return 64 // world
+
+
+def views_of(step, rank, world, vps):
+    """camera ids of rank `rank` in step `step`: consecutive blocks of the 64-camera pool; successive steps start one block
+    further (and one more when the step's views are a multiple of the pool, so that a rank does not see the same cameras again)"""
+    per_step = world * vps
+    stride = per_step + (vps if per_step % NUM_CAMERAS == 0 else 0)
+    return [(step * stride + rank * vps + i) % NUM_CAMERAS for i in range(vps)]
+
+
+def load_json(name):
+    p = os.path.join(ROOT, "profiles", name)
+    return json.load(open(p)) if os.path.exists(p) else {}
 
 
 def load_peaks():
@@ -82,19 +114,26 @@ class ClockSampler:
                 "samples": len(rows), "reasons": reasons}
 
 
-def stage_bytes(name, P, V, N, X, M=16):
-    """ALGORITHMIC bytes of one launch group per render (SURVEY.md §8(d) per-unit figures adapted to this
-    library's data layout).  P Gaussians, V visible, N (tile, Gaussian) pairs, X pixels."""
+# stages whose roofline is HBM bandwidth; the two tile renderers are bound by instruction issue (FP32 / SFU / LSU slots)
+HBM_STAGES = ("preprocess_fwd", "depth_sort", "scan", "duplicate", "tile_sort", "ranges", "preprocess_bwd", "backward_views")
+
+
+def stage_bytes(name, P, V, N, X, M=16, views=1):
+    """ALGORITHMIC bytes of one launch group (SURVEY.md §8(d) per-unit figures adapted to this library's
+    data layout).  P Gaussians, V visible, N (tile, Gaussian) pairs, X pixels; per render unless stated."""
     return {
         "preprocess_fwd": 52 * P + (12 * M + 67) * V,                 # 44 in + 8 out always; SH row in + projected record out if visible
         "depth_sort": (4 + 4 * 16) * P,                                # histogram read + 4 passes x (key+value read, key+value write)
         "scan": 12 * P,                                                # order + tiles_touched in, offsets out
         "duplicate": 16 * P + 8 * N,                                   # order/offsets/rect in, tile key + Gaussian id out
         "tile_sort": (4 + 2 * 16) * N,                                 # histogram read + 2 passes x 16 B
-        "ranges_pack": 4 * N,                                          # sorted tile keys in (ranges out: 8 B per tile); no pack pass in the gather variants
+        "ranges": 4 * N,                                               # sorted tile keys in (ranges out: 8 B per tile)
         "render_fwd": 52 * N + N + 24 * X,                             # id + gathered record per list entry, 8 flag bits out; colour 12 + depth 4 + final_T 4 + n_contrib 4 out
         "render_bwd": 52 * N + N + 20 * X + 96 * P,                    # id + record + flag bits in, dL_dpix/T/n in, accumulator zero fill + read-modify-write
         "preprocess_bwd": 52 * P + (12 * M + 111) * V + (12 * M + 56) * P,   # accumulators + radii + inputs in, every gradient element out
+        # view-batched backward of a whole step: parameters in once, per view radii + accumulator (+ record, clamp flags of a
+        # visible Gaussian) in and dL_dmean2D out, the 59-float bucket row out once
+        "backward_views": (44 + 12 * M) * P + views * (52 * P + 37 * V + 12 * P) + (11 + 3 * M) * 4 * P,
     }.get(name)
 
 
@@ -125,15 +164,9 @@ def max_over_ranks(x, world, dev):
     return float(t.item())
 
 
-def build_workload(name, dev, rank):
-    cfg = CONFIGS[name]
-    sc_h = make_scene(cfg["P"], cfg["D"], seed=0)
-    cams_h = [make_camera(v, NUM_CAMERAS, cfg["W"], cfg["H"]) for v in range(NUM_CAMERAS)]
-    # per-view target images: upstream gradient = colour - target (L2 loss); seeded, pinned on the host for the e2e arm
-    # stored as 8-bit images, the native form of training photographs (the kernel converts: target = byte / 255)
-    targets_h = [make_grad(cfg["W"], cfg["H"], seed=100 + v).mul_(0.1).add_(0.5).clamp_(0, 1).mul_(255).round_().to(torch.uint8).pin_memory()
-                 for v in range(VIEWS_PER_STEP)]
-    return cfg, sc_h, cams_h, targets_h
+def make_target(W, H, slot):
+    """target image of view slot `slot`: seeded, 8-bit (the native form of training photographs; the loss kernel converts)"""
+    return make_grad(W, H, seed=100 + slot % NUM_TARGETS).mul_(0.1).add_(0.5).clamp_(0, 1).mul_(255).round_().to(torch.uint8)
 
 
 def run_ours(args, rank, world, local):
@@ -141,31 +174,37 @@ def run_ours(args, rank, world, local):
     from rain_b200.loss import l2_loss_grad
     dev = torch.device("cuda", local)
     lib = _lib.load()
-    cfg, sc_h, cams_h, targets_h = build_workload(args.workload, dev, rank)
+    cfg = CONFIGS[args.workload]
     P, W, H, D = cfg["P"], cfg["W"], cfg["H"], cfg["D"]
-    sc = sc_h.to(dev)
+    VPS = views_per_rank(args.workload, world)
+    sc = make_scene(P, D, seed=0).to(dev)
+    cams_h = [make_camera(v, NUM_CAMERAS, W, H) for v in range(NUM_CAMERAS)]
+    targets_h = [make_target(W, H, v).pin_memory() for v in range(NUM_TARGETS)]
     params = dict(means3D=sc.means3D, opacities=sc.opacities, shs=sc.shs, scales=sc.scales, rotations=sc.rotations)
     bg = torch.zeros(3, device=dev)
     bucket = mv.GradientBucket(P, 16, dev)
     kw = dict(bg=bg, sh_degree=D, keep_outputs=False)
 
-    def views_of(step):   # a different slice of the 64-camera pool for every (step, rank)
-        return [(step * world * VIEWS_PER_STEP + rank * VIEWS_PER_STEP + i) % NUM_CAMERAS for i in range(VIEWS_PER_STEP)]
-
     # ---------------- device-resident arm (`value`) ----------------
     cams_d = [c.to(dev) for c in cams_h]
     targets_d = [t.to(dev) for t in targets_h]
     slot = {}
+    ar_events = []
 
     def grad_resident(v, color, depth):
-        return l2_loss_grad(color, targets_d[slot[v]])            # dL/dcolor = colour - target, one fused pass (csrc/loss.cu)
+        return l2_loss_grad(color, targets_d[slot[v] % NUM_TARGETS])            # dL/dcolor = colour - target, one fused pass (csrc/loss.cu)
 
-    def step_resident(s):
-        ids = views_of(s)
+    def step_resident(s, pipeline="two_stream", time_allreduce=False):
+        ids = views_of(s, rank, world, VPS)
         slot.clear(); slot.update({v: i for i, v in enumerate(ids)})
         bucket.filled = False
-        res = mv.render_views_fwd_bwd(params, cams_d, ids, bucket, grad_resident, **kw)
-        mv.allreduce_bucket(bucket)
+        res = mv.render_views_fwd_bwd(params, cams_d, ids, bucket, grad_resident, pipeline=pipeline, **kw)
+        if time_allreduce and world > 1:
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record(); mv.allreduce_bucket(bucket); a1.record()
+            ar_events.append((a0, a1))
+        else:
+            mv.allreduce_bucket(bucket)
         return res
 
     for s in range(args.warmup):
@@ -180,56 +219,55 @@ def run_ours(args, rank, world, local):
     e0.record()
     N_last = 0
     for s in range(args.steps):
-        res = step_resident(args.warmup + s)
+        res = step_resident(args.warmup + s, time_allreduce=True)
         N_last = res[-1].num_rendered
     e1.record()
     barrier_sync(world)
     t1 = time.time()
     launches = lib.rr_launch_count() - launches0
     ms = max_over_ranks(e0.elapsed_time(e1), world, dev)
+    allreduce_ms = max_over_ranks(sum(a.elapsed_time(b) for a, b in ar_events) / max(1, len(ar_events)), world, dev) if world > 1 else 0.0
     clocks = sampler.stop(t0, t1) if rank == 0 else None
-    renders = world * VIEWS_PER_STEP * args.steps
+    renders = world * VPS * args.steps
     value = renders / (ms * 1e-3)
 
     # ---------------- per-stage device times (CUDA events on the launch stream, same steps) ----------------
     # one stream for this pass: in the timed region above the HBM-bound front of view i+1 runs beside the render kernels of
     # view i on a second stream, which stretches both; a kernel's own duration (the roofline numerator) is the serial one
-    two_stream = os.environ.get("RAIN_GEOM_STREAM", "1")
-    os.environ["RAIN_GEOM_STREAM"] = "0"
     lib.rr_prof_enable(1)
     _lib.stage_times(reset=True)
     torch.cuda.synchronize()
-    for s in range(args.steps):
-        step_resident(args.warmup + s)
+    for s in range(min(args.steps, max(1, 160 // VPS))):
+        step_resident(args.warmup + s, pipeline="one_stream")
     torch.cuda.synchronize()
     st = _lib.stage_times(reset=True)
     lib.rr_prof_enable(0)
     # Gaussians one view sees (radii > 0): the V of the per-stage byte model
-    v_probe = views_of(args.warmup + args.steps - 1)[-1]
-    slot[v_probe] = VIEWS_PER_STEP - 1
+    v_probe = views_of(args.warmup + args.steps - 1, rank, world, VPS)[-1]
+    slot[v_probe] = VPS - 1
     bucket.filled = False
-    V_seen = int((mv.render_views_fwd_bwd(params, cams_d, [v_probe], bucket, grad_resident, bg=bg, sh_degree=D, keep_outputs=True)[0].radii > 0).sum())
-    os.environ["RAIN_GEOM_STREAM"] = two_stream
+    V_seen = int((mv.render_views_fwd_bwd(params, cams_d, [v_probe], bucket, grad_resident, bg=bg, sh_degree=D, keep_outputs=True, pipeline="one_stream")[0].radii > 0).sum())
 
     # ---------------- end-to-end arm (host buffers -> public API -> host scalar) ----------------
     # cameras: one 48-float row per camera (view 16 | proj 16 | campos 3 | pad) in pinned host memory; the rows of a step's
-    # views are gathered into one pinned staging block and cross PCIe as ONE copy per step (24 small copies before)
+    # views are gathered into one pinned staging block and cross PCIe as ONE copy per step
     cam_rows = torch.zeros(len(cams_h), 48)
     for ci, c in enumerate(cams_h):
         cam_rows[ci, :16] = c.viewmatrix.reshape(-1); cam_rows[ci, 16:32] = c.projmatrix.reshape(-1); cam_rows[ci, 32:35] = c.campos
     cam_rows = cam_rows.pin_memory()
-    cam_stage = torch.zeros(VIEWS_PER_STEP, 48).pin_memory()
-    cam_dev = torch.zeros(VIEWS_PER_STEP, 48, device=dev)
-    dev_cam = [dict(view=cam_dev[i, :16].view(4, 4), proj=cam_dev[i, 16:32].view(4, 4), campos=cam_dev[i, 32:35]) for i in range(VIEWS_PER_STEP)]
-    feed = mv.HostFeed([(3, H, W)] * VIEWS_PER_STEP, dev, dtype=torch.uint8)     # target images: pinned host -> device on a side stream, overlapped with the renders
+    cam_stage = torch.zeros(VPS, 48).pin_memory()
+    cam_dev = torch.zeros(VPS, 48, device=dev)
+    dev_cam = [dict(view=cam_dev[i, :16].view(4, 4), proj=cam_dev[i, 16:32].view(4, 4), campos=cam_dev[i, 32:35]) for i in range(VPS)]
+    feed = mv.HostFeed([(3, H, W)] * min(VPS, NUM_TARGETS), dev, dtype=torch.uint8)     # target images: pinned host -> device on a side stream, overlapped with the renders
+    nbuf = len(feed.buffers)
     loss_dev = torch.zeros(1, device=dev)
     loss_host = torch.zeros(1).pin_memory()
-    h2d = VIEWS_PER_STEP * (48 * 4 + 3 * H * W)      # one padded camera row + one 8-bit target image per view
-    d2h = 4 + VIEWS_PER_STEP * 8          # loss scalar + num_rendered (8 B, read inside the forward) per view
+    h2d = VPS * (48 * 4 + 3 * H * W)      # one padded camera row + one 8-bit target image per view
+    d2h = 4 + VPS * 8                     # loss scalar + num_rendered (8 B, read inside the forward) per view
     from rain_b200.synthetic import Camera
 
     def step_e2e(s):
-        ids = views_of(s)
+        ids = views_of(s, rank, world, VPS)
         cams_step = {}
         if not E2E_DIAG_NO_FEED:
             feed.stage_slot(0, targets_h[0])       # view i+1's image is staged when view i reaches its loss: one short transfer in flight
@@ -241,9 +279,10 @@ def run_ours(args, rank, world, local):
         loss_dev.zero_()
 
         def grad_e2e(v, color, depth):
-            if not E2E_DIAG_NO_FEED and slot[v] + 1 < VIEWS_PER_STEP:
-                feed.stage_slot(slot[v] + 1, targets_h[slot[v] + 1])
-            tgt = targets_d[slot[v]] if E2E_DIAG_NO_FEED else feed.wait(slot[v])
+            i = slot[v]
+            if not E2E_DIAG_NO_FEED and i + 1 < VPS:
+                feed.stage_slot((i + 1) % nbuf, targets_h[(i + 1) % NUM_TARGETS])
+            tgt = targets_d[i % NUM_TARGETS] if E2E_DIAG_NO_FEED else feed.wait(i % nbuf)
             return l2_loss_grad(color, tgt, loss_dev)     # gradient + 0.5 * sum d^2 into the step's loss scalar
         bucket.filled = False
         mv.render_views_fwd_bwd(params, cams_step, ids, bucket, grad_e2e, **kw)
@@ -265,31 +304,76 @@ def run_ours(args, rank, world, local):
     ms_e2e = max_over_ranks(e0.elapsed_time(e1), world, dev)
     e2e_value = renders / (ms_e2e * 1e-3)
 
+    # ---------------- drop-in arm: one view at a time through the reference's own Python API ----------------
+    dropin = None
+    if world == 1 and rank == 0:
+        dropin = run_dropin(cfg, sc, cams_d, targets_d, bg, dev, iters=max(50, args.steps), warm=10)
+
     if rank != 0:
         return None
     return dict(cfg=cfg, value=value, ms=ms, e2e_value=e2e_value, ms_e2e=ms_e2e, h2d=h2d, d2h=d2h, launches=launches, stage=st, clocks=clocks,
-                N=N_last, V=V_seen, loss=loss, bucket_bytes=bucket.nbytes())
+                N=N_last, V=V_seen, loss=loss, bucket_bytes=bucket.nbytes(), vps=VPS, allreduce_ms=allreduce_ms, dropin=dropin)
+
+
+def run_dropin(cfg, sc, cams, targets, bg, dev, iters, warm):
+    """SURVEY.md §8(d)'s metric literally: 1 / (time of one _RasterizeGaussians.forward + .backward for one view), CUDA-event
+    timed, steady state, >= 50 iterations after 10 warm-ups, through the drop-in module path the unchanged
+    gaussian_renderer/__init__.py imports.  Per iteration, as render() + train.py do: a fresh zero screenspace tensor, the
+    settings tuple, the module call, the backward from dL/dcolor (= colour - target, the bench's L2 loss), grads set to None."""
+    from submodules.diff_gaussian_rasterization.diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    W, H, D = cfg["W"], cfg["H"], cfg["D"]
+    leaves = [t.detach().clone().requires_grad_(True) for t in (sc.means3D, sc.opacities, sc.shs, sc.scales, sc.rotations)]
+    tg = [t.float().div_(255.0) for t in targets]
+
+    def one(i):
+        cam = cams[i % NUM_CAMERAS]
+        screenspace = torch.zeros_like(leaves[0], requires_grad=True) + 0                 # gaussian_renderer/__init__.py:10
+        screenspace.retain_grad()
+        rs = GaussianRasterizationSettings(H, W, cam.tanfovx, cam.tanfovy, bg, 1.0, cam.viewmatrix, cam.projmatrix, D, cam.campos, False, False, 0.3)
+        color, radii, depth = GaussianRasterizer(raster_settings=rs)(means3D=leaves[0], means2D=screenspace, opacities=leaves[1], shs=leaves[2],
+                                                                     scales=leaves[3], rotations=leaves[4])
+        color.backward(gradient=torch.sub(color.detach(), tg[i % NUM_TARGETS]))
+        for t in leaves:
+            t.grad = None                                                                  # optimizer.zero_grad(set_to_none=True), train.py:147
+    for i in range(warm):
+        one(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(iters):
+        one(warm + i)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    return {"value": round(1e3 / ms, 2), "unit": "renders/s", "ms_per_render": round(ms, 4), "iterations": iters, "warmup": warm,
+            "api": "GaussianRasterizationSettings + GaussianRasterizer.forward + autograd backward, one view at a time "
+                   "(submodules.diff_gaussian_rasterization.diff_gaussian_rasterization, as gaussian_renderer/__init__.py:20-64 calls it)"}
 
 
 def cpu_oracle_sample(workload, renders):
     """The CPU baseline: the oracle port (scalar C++/OpenMP restatement of forward.cu / backward.cu, all host threads) timed
-    on `renders` fwd+bwd renders of the same workload.  Test infrastructure used here only as the measured baseline."""
+    on `renders` fwd+bwd renders of the same workload.  Test infrastructure used here only as the measured baseline.  Its
+    evaluated / blended (pixel, list entry) pair counts are the ALGORITHMIC work of one render."""
     from oracle.oracle_py import Oracle
     orc = Oracle()
     cfg = CONFIGS[workload]
     sc = make_scene(cfg["P"], cfg["D"], seed=0)
     bg = np.zeros(3, np.float32)
     arrs = [sc.means3D.numpy(), sc.opacities.numpy(), sc.scales.numpy(), sc.rotations.numpy()]
+    cnt = dict(fwd_evals=0, fwd_contribs=0, bwd_evals=0, bwd_contribs=0)
     t = time.time()
     for v in range(renders):
         cam = make_camera(v, NUM_CAMERAS, cfg["W"], cfg["H"])
         N, color, radii, depth = orc.forward(bg, *arrs, cam.viewmatrix.numpy(), cam.projmatrix.numpy(), cam.campos.numpy(), cam.tanfovx, cam.tanfovy,
                                              cam.height, cam.width, shs=sc.shs.numpy(), sh_degree=cfg["D"])
-        orc.backward(color - (make_grad(cfg["W"], cfg["H"], seed=100 + v % VIEWS_PER_STEP).numpy() * 0.1 + 0.5))
+        orc.backward(color - (make_target(cfg["W"], cfg["H"], v).float().numpy() / 255.0))
+        for k, x in orc.counters().items():
+            cnt[k] += x
     dt = time.time() - t
     return dict(value=renders / dt, unit="renders/s", cores=orc.num_threads(), kind="port",
                 sample=f"{renders} fwd+bwd renders of {workload} ({cfg['P']} Gaussians, {cfg['W']}x{cfg['H']}, SH degree {cfg['D']}) in {dt:.1f} s, "
-                       f"oracle/liboracle.so (g++ -O2 -fopenmp), host threads = {orc.num_threads()} of {os.cpu_count()} cores")
+                       f"oracle/liboracle.so (g++ -O2 -fopenmp), host threads = {orc.num_threads()} of {os.cpu_count()} cores",
+                pairs_per_render={k: x // renders for k, x in cnt.items()})
 
 
 def run_reference(args, rank, world, local):
@@ -300,12 +384,13 @@ def run_reference(args, rank, world, local):
         return None
     from oracle.oracle_py import REF_SO, RefCuda
     cfg = CONFIGS[args.workload]
+    VPS = views_per_rank(args.workload, 1)
     base = {"metric": METRIC, "unit": "renders/s", "impl": "reference", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic"}
+            "higher_is_better": True, "scaling": "strong" if args.workload == "C4" else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic"}
     if not os.path.exists(REF_SO) or not torch.cuda.is_available():
         # fall back to timing the host port, as the tier contract allows
         cb = cpu_oracle_sample(args.workload, max(1, min(3, args.steps)))
-        base.update(value=cb["value"], ms_per_step=1e3 * VIEWS_PER_STEP / cb["value"], cpu_baseline=cb,
+        base.update(value=cb["value"], ms_per_step=1e3 * VPS / cb["value"], cpu_baseline=cb,
                     config={"workload": f"{args.workload}: {cfg['P']} Gaussians, {cfg['W']}x{cfg['H']}, SH degree {cfg['D']}", "arm": "host port (oracle)"},
                     e2e={"value": cb["value"], "unit": "renders/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
         return base
@@ -314,15 +399,15 @@ def run_reference(args, rank, world, local):
     ref = RefCuda()
     sc = make_scene(cfg["P"], cfg["D"], seed=0).to(dev)
     cams = [make_camera(v, NUM_CAMERAS, cfg["W"], cfg["H"]).to(dev) for v in range(NUM_CAMERAS)]
-    targets = [make_grad(cfg["W"], cfg["H"], seed=100 + v).mul_(0.1).add_(0.5).to(dev) for v in range(VIEWS_PER_STEP)]
+    targets = [make_target(cfg["W"], cfg["H"], v).float().div_(255.0).to(dev) for v in range(NUM_TARGETS)]
     bg = torch.zeros(3, device=dev)
 
     def step(s):
-        for i in range(VIEWS_PER_STEP):
-            cam = cams[(s * VIEWS_PER_STEP + i) % NUM_CAMERAS]
+        for i, v in enumerate(views_of(s, 0, 1, VPS)):
+            cam = cams[v]
             N, color, radii, depth = ref.forward(bg, sc.means3D, sc.opacities, sc.scales, sc.rotations, cam.viewmatrix, cam.projmatrix, cam.campos,
                                                  cam.tanfovx, cam.tanfovy, cam.height, cam.width, shs=sc.shs, sh_degree=cfg["D"], sync=False)
-            ref.backward(torch.sub(color, targets[i]), sync=False)
+            ref.backward(torch.sub(color, targets[i % NUM_TARGETS]), sync=False)
     for s in range(args.warmup):
         step(s)
     torch.cuda.synchronize()
@@ -333,14 +418,21 @@ def run_reference(args, rank, world, local):
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
-    value = VIEWS_PER_STEP * args.steps / (ms * 1e-3)
+    value = VPS * args.steps / (ms * 1e-3)
     base.update(value=value, ms_per_step=ms / args.steps, n_gpus=1,
-                config={"workload": f"{args.workload}: {cfg['P']} Gaussians, {cfg['W']}x{cfg['H']}, SH degree {cfg['D']}, {VIEWS_PER_STEP} views per step",
+                config={"workload": f"{args.workload}: {cfg['P']} Gaussians, {cfg['W']}x{cfg['H']}, SH degree {cfg['D']}, {VPS} views per step",
                         "arm": "reference CUDA (unmodified sources, rebuilt for sm_100a) on the same B200, one GPU; no gradient accumulation or all-reduce"},
                 cpu_baseline={"value": value, "unit": "renders/s", "cores": 0, "kind": "reference",
-                              "sample": f"{args.steps} steps x {VIEWS_PER_STEP} views, oracle/_ref/libref_rast.so on cuda:{local} (the reference has no CPU path)"},
-                e2e={"value": value, "unit": "renders/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 4 * VIEWS_PER_STEP})
+                              "sample": f"{args.steps} steps x {VPS} views, oracle/_ref/libref_rast.so on cuda:{local} (the reference has no CPU path)"},
+                e2e={"value": value, "unit": "renders/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 4 * VPS})
     return base
+
+
+def fp32_peak_tflops(dev, clocks):
+    """FP32 peak of this GPU: SMs x 128 lanes x 2 flop x SM clock, read at run time"""
+    props = torch.cuda.get_device_properties(dev)
+    mhz = (clocks or {}).get("sm_max_mhz") or 1965.0
+    return props.multi_processor_count * 128 * 2 * mhz * 1e6 / 1e12, props.multi_processor_count, mhz
 
 
 def main():
@@ -380,49 +472,76 @@ def main():
     if rank != 0:
         return
     cfg = r["cfg"]
-    P, X, N = cfg["P"], cfg["W"] * cfg["H"], r["N"]
+    P, X, N, VPS = cfg["P"], cfg["W"] * cfg["H"], r["N"], r["vps"]
     peaks, peak_kind = load_peaks()
     peak = float(peaks["hbm_gbs"])
-    calls = max(1, r["stage"]["render_fwd"][1])
+    fp32_peak, sms, mhz = fp32_peak_tflops(torch.device("cuda", local), r["clocks"])
+    cpu = cpu_oracle_sample(args.workload, args.cpu_renders) if (world == 1 and args.cpu_renders > 0) else None
+    pairs = (cpu or {}).get("pairs_per_render") or load_json("pairs_per_render.json").get(args.workload)
+    ncu_render = load_json("ncu_render.json").get(args.workload, {})
+    live = load_json("live_lanes.json").get(args.workload, {})
+    traffic = load_json("ncu_traffic.json").get(args.workload, {})
     stages = {}
     for name, (ms, n) in r["stage"].items():
         if n == 0:
             continue
-        b = stage_bytes(name, P, r["V"], N, X)
         per = ms / n
-        stages[name] = {"ms": round(per, 4), "share": None, "alg_bytes": b, "gbs": round(b / per / 1e6, 1) if b else None,
-                        "frac_of_hbm": round(b / per / 1e6 / peak, 4) if b else None}
-    tot = sum(v["ms"] for v in stages.values())
-    for v in stages.values():
-        v["share"] = round(v["ms"] / tot, 4)
-    top = max(stages, key=lambda k: stages[k]["ms"])
-    traffic = None
-    tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")
-    if os.path.exists(tp):
-        traffic = json.load(open(tp)).get(args.workload, {}).get(top)
+        e = {"ms": round(per, 4), "share": None, "bound": "hbm" if name in HBM_STAGES else "issue"}
+        b = stage_bytes(name, P, r["V"], N, X, views=VPS)
+        if b:
+            e.update(alg_bytes=b, gbs=round(b / per / 1e6, 1), frac_of_hbm=round(b / per / 1e6 / peak, 4))
+        if name in ("render_fwd", "render_bwd") and pairs:
+            ev, co = (pairs["fwd_evals"], pairs["fwd_contribs"]) if name == "render_fwd" else (pairs["bwd_evals"], pairs["bwd_contribs"])
+            fl = (FLOP_FWD_REJECT * (ev - co) + FLOP_FWD_BLEND * co) if name == "render_fwd" else (FLOP_BWD_REJECT * (ev - co) + FLOP_BWD_BLEND * co)
+            e.update(alg_flops=fl, evaluated_pairs=ev, blended_pairs=co, tflops=round(fl / per / 1e9, 2), frac_of_fp32=round(fl / per / 1e9 / fp32_peak, 4))
+            e.update(ncu_render.get(name, {}))          # issue_active, pipe_fma, smem_wavefronts_per_clk_per_sm ... (ncu capture, committed under profiles/)
+            e.update(live.get(name, {}))                # live_lane_frac ... (cross-check build counters, committed under profiles/)
+        if name in traffic:
+            e["dram_traffic"] = traffic[name]
+        stages[name] = e
+    per_view = {k: (1.0 / VPS if k == "backward_views" else 1.0) for k in stages}      # launches per rendered view
+    tot = sum(v["ms"] * per_view[k] for k, v in stages.items())
+    for k, v in stages.items():
+        v["share"] = round(v["ms"] * per_view[k] / tot, 4)
+    top = max(stages, key=lambda k: stages[k]["ms"] * per_view[k])
+    t = stages[top]
+    if t["bound"] == "issue" and "tflops" in t:
+        roof = {"kernel": top, "bound": "issue", "achieved": t["tflops"], "peak": round(fp32_peak, 2), "unit": "TFLOP/s", "frac": t["frac_of_fp32"],
+                "peak_source": f"FP32 pipe: {sms} SMs x 128 lanes x 2 flop x {mhz:.0f} MHz (read at run time)",
+                "achieved_def": "oracle-counted evaluated / blended (pixel, list entry) pairs of one render x SURVEY 8(d) flop figures / kernel time",
+                "issue_active": t.get("issue_active"), "pipe_fma": t.get("pipe_fma"), "smem_wavefronts_per_clk_per_sm": t.get("smem_wavefronts_per_clk_per_sm"),
+                "live_lane_frac": t.get("live_lane_frac")}
+    else:
+        roof = {"kernel": top, "bound": "hbm", "achieved": t.get("gbs"), "peak": peak, "unit": "GB/s", "frac": t.get("frac_of_hbm"),
+                "peak_source": f"{peak_kind} (MEASURED_PEAKS.json hbm_gbs)" if peak_kind == "measured" else "fallback"}
+    roof.update(traffic=traffic.get(top), ms_per_launch=t["ms"], share_of_step=t["share"])
+    strong = args.workload == "C4"
     line = {
         "metric": METRIC, "value": round(r["value"], 2), "unit": "renders/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": round(r["ms"] / args.steps, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "ms_per_step": round(r["ms"] / args.steps, 4), "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": {"workload": f"{args.workload}: {P} random Gaussians, {cfg['W']}x{cfg['H']}, SH degree {cfg['D']} (BASELINE.json configs[{int(args.workload[1]) - 1}])",
-                   "views_per_step_per_gpu": VIEWS_PER_STEP, "global_views_per_step": VIEWS_PER_STEP * world, "num_rendered_per_view": N, "visible_per_view": r["V"],
-                   "parallelism": f"view-sharded dp{world}, one f32 all-reduce of {r['bucket_bytes']} B per step" if world > 1 else "single GPU",
+                   "views_per_step_per_gpu": VPS, "global_views_per_step": VPS * world, "num_rendered_per_view": N, "visible_per_view": r["V"],
+                   "parallelism": (f"view-sharded dp{world}, one f32 all-reduce of {r['bucket_bytes']} B per step ({r['allreduce_ms']:.3f} ms, "
+                                   f"{r['allreduce_ms'] / (r['ms'] / args.steps) * 100:.1f} % of the step)") if world > 1 else "single GPU",
                    "pipeline": ("two streams: preprocess/sort/binning of the next view on a high-priority stream beside the render kernels of the current view; "
-                                "stages[] and roofline come from a one-stream pass over the same steps (a kernel's own duration), so their sum exceeds ms_per_step / views")
-                   if os.environ.get("RAIN_GEOM_STREAM", "1") == "1" else "one stream",
-                   "l2": f"inputs larger than L2: {P * 59 * 4 // 1000000} MB of Gaussian parameters + {P * 59 * 4 // 1000000} MB gradient bucket per render, different cameras every step"},
+                                "stages[] and roofline come from a one-stream pass over the same steps (a kernel's own duration), so their sum exceeds ms_per_step / views"),
+                   "l2": f"inputs larger than L2: {P * 59 * 4 // 1000000} MB of Gaussian parameters + {P * 59 * 4 // 1000000} MB gradient bucket per render; "
+                         f"every step and rank takes the next block of the {NUM_CAMERAS}-camera pool"},
         "e2e": {"value": round(r["e2e_value"], 2), "unit": "renders/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
                 "ms_per_step": round(r["ms_e2e"] / args.steps, 4), "loss": r["loss"]},
         "gpu_launches": int(r["launches"]),
         "clocks": r["clocks"],
-        "roofline": {"kernel": top, "bound": "hbm", "achieved": stages[top]["gbs"], "peak": peak, "unit": "GB/s", "frac": stages[top]["frac_of_hbm"],
-                     "traffic": traffic, "peak_source": f"{peak_kind} (MEASURED_PEAKS.json hbm_gbs)" if peak_kind == "measured" else "fallback",
-                     "ms_per_launch": stages[top]["ms"], "share_of_step": stages[top]["share"],
-                     "note": "render kernels are FP32/SFU-issue bound, not HBM bound; see stages[] and DESIGN.md"},
+        "roofline": roof,
         "stages": stages,
     }
-    if world == 1 and args.cpu_renders > 0:
-        line["cpu_baseline"] = cpu_oracle_sample(args.workload, args.cpu_renders)
+    if world > 1:
+        line["allreduce"] = {"ms_per_step": round(r["allreduce_ms"], 4), "bytes": r["bucket_bytes"],
+                             "bus_gbs": round(2 * (world - 1) / world * r["bucket_bytes"] / max(r["allreduce_ms"], 1e-9) / 1e6, 1)}
+    if r["dropin"]:
+        line["dropin"] = r["dropin"]
+    if cpu:
+        line["cpu_baseline"] = cpu
     emit(line)
 
 

@@ -15,8 +15,9 @@
  *  - null `shs` / `colors_precomp` and null `scales`+`rotations` / `cov3D_precomp` select the modes exactly like the
  *    nullptr tests of the reference (forward.cu:195,231; backward.cu:380,384);
  *  - `debug != 0` makes each entry synchronise the stream and report asynchronous CUDA errors (CHECK_CUDA semantics,
- *    auxiliary.h:155-162);
- *  - `variant`: 1 = TMA bulk-copy staging in the tile renderers (default), 0 = cooperative float4 loads.
+ *    auxiliary.h:155-162).
+ * The library has one kernel per stage and no run-time kernel selection; its single environment switch is the opt-in
+ * RAIN_TILE_CULL=1 (read once per process), which shortens the internal tile lists and therefore is off by default.
  */
 #ifndef RAIN_RAST_H
 #define RAIN_RAST_H
@@ -31,12 +32,13 @@ extern "C" {
 const char* rr_last_error(void);
 int rr_version(void);
 
+/* number of CUDA kernels this library has launched in this process so far */
+int64_t rr_launch_count(void);
+
 /* Optional per-stage device timing: when enabled every entry point brackets each of its stages with CUDA events on the
  * caller's stream (no reference counterpart; the reference only has CHECK_CUDA syncs, auxiliary.h:155-162).
  * rr_prof_read synchronises the recorded events and returns accumulated milliseconds and call counts per stage
  * (arrays of rr_prof_num_stages() entries; either may be null), optionally resetting the accumulators. */
-/* number of CUDA kernels this library has launched in this process so far */
-int64_t rr_launch_count(void);
 int rr_prof_enable(int on);
 int rr_prof_num_stages(void);
 const char* rr_prof_stage_name(int i);
@@ -64,7 +66,7 @@ int rr_forward_geom(void* stream, int P, int D, int M, int W, int H,
  * (rasterizer_impl.cu:275-328).  out_color[3,H,W], out_depth[1,H,W]. */
 int rr_forward_raster(void* stream, int P, int W, int H, int64_t N, const float* background,
 	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes,
-	float* out_color, float* out_depth, int variant, int debug);
+	float* out_color, float* out_depth, int debug);
 
 /* The two parts of rr_forward_raster as separate calls, so that a caller rendering a batch of views can run the binning of
  * the next view (HBM bound) on a second stream beside the render kernels of the current one (issue bound):
@@ -72,10 +74,10 @@ int rr_forward_raster(void* stream, int P, int W, int H, int64_t N, const float*
  *   rr_forward_render  FORWARD::render (rasterizer_impl.cu:320-328); must be ordered after rr_forward_bin of the same blobs
  * rr_forward_raster(...) == rr_forward_bin(...) then rr_forward_render(...) on one stream. */
 int rr_forward_bin(void* stream, int P, int W, int H, int64_t N,
-	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes, int variant, int debug);
+	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes, int debug);
 int rr_forward_render(void* stream, int P, int W, int H, int64_t N, const float* background,
 	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes,
-	float* out_color, float* out_depth, int variant, int debug);
+	float* out_color, float* out_depth, int debug);
 
 /* Backward — replaces Rasterizer::backward (rasterizer_impl.cu:334-430) and the torch::zeros fills of
  * RasterizeGaussiansBackwardCUDA (rasterize_points.cu:145-153): every element of every gradient buffer is written.
@@ -95,18 +97,17 @@ int rr_backward(void* stream, int P, int D, int M, int W, int H, int64_t N, cons
 	const float* dL_dpix, void* ws, size_t ws_bytes,
 	float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
 	float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
-	int variant, int debug, int flags);
+	int debug, int flags);
 
-/* replaces Rasterizer::markVisible / checkFrustum (rasterizer_impl.cu:43-55,130-142); present is uint8/bool [P] */
 /* Self test of the packed exponential the render kernels use (exp2x, csrc/render_common.cuh) against libdevice expf —
  * the function the reference's forward.cu:336 / backward.cu:488 compile to — over the float bit patterns
  * [first_bits, first_bits + count).  Adds the number of results that differ in any bit to *mismatches_dev (device, u64,
  * zeroed by the caller).  The forward's bit-exact n_contrib / colour parity rests on this being 0 for all x <= 0. */
 int rr_selftest_exp(void* stream, uint32_t first_bits, uint32_t count, unsigned long long* mismatches_dev);
 
+/* replaces Rasterizer::markVisible / checkFrustum (rasterizer_impl.cu:43-55,130-142); present is uint8/bool [P] */
 int rr_mark_visible(void* stream, int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present);
 
-/* replaces distCUDA2 / SimpleKNN::knn (simple-knn/spatial.cu:4-15, simple_knn.cu:174-210); points f32[P,3] -> out f32[P] */
 /* ---- image loss right after the render -------------------------------------------------------
  * rr_loss_l1_ssim replaces, for the rendered image, utils/loss_utils.py:6-7 (l1_loss) and :23-51 (ssim / _ssim, window 11,
  * sigma 1.5, zero padding, size_average=True) plus train.py:112-113 and their autograd backward:
@@ -145,6 +146,8 @@ int rr_param_step(void* stream, int P, int M, float* xyz, float* f_dc, float* f_
  * from the gradient all-reduce. */
 int rr_densify_stats(void* stream, int P, const int* radii, const float* dL_dmean2D, float* max_radii2D, float* xyz_gradient_accum, float* denom);
 
+/* replaces distCUDA2 / SimpleKNN::knn (simple-knn/spatial.cu:4-15, simple_knn.cu:174-210); points f32[P,3] -> out f32[P];
+ * ws: rr_dist2_ws_bytes(P) bytes of device scratch */
 size_t rr_dist2_ws_bytes(int P);
 int rr_dist2(void* stream, int P, const float* points, float* out, void* ws, size_t ws_bytes);
 
@@ -160,8 +163,7 @@ int rr_sort_pairs_u64(void* stream, int64_t n, uint64_t* keys_in, uint64_t* keys
 /* byte offsets of the arrays inside the opaque blobs (for stage-wise diffing against the oracle / reference).
  * geom:    [0] rec f32[P,12]  [1] cov3D f32[P,6]  [2] clamped u8[P]  [3] tiles_touched u32[P]  [4] rect u32[P,2]
  *          [5] depth_order u32[P]  [6] offsets u32[P] (inclusive, in depth order)  [7] = [6]  [8] num_rendered u32
- * binning: [0] tile_keys_sorted u32[N]  [1] point_list u32[N]  [2] warp_flags u32[8*(N/32+T+2)]  [3] = [1]  [4] packed f32[N,12]
- *          (packed is only filled by the packed staging variants 0 / 1)
+ * binning: [0] tile_keys_sorted u32[N]  [1] point_list u32[N]  [2] warp_flags u32[8*(N/32+T+2)]  [3] = [1]  [4] reserved
  * image:   [0] final_T f32[H*W]  [1] n_contrib u32[H*W]  [2] ranges u32[T,2]  [3] reserved u32[T] */
 int rr_geom_layout(int P, int64_t offsets_host[9]);
 int rr_binning_layout(int64_t N, int W, int H, int64_t offsets_host[5]);

@@ -5,8 +5,6 @@ shapes and dtypes of rasterize_points.h:7-58, implemented on top of the C ABI of
 PyTorch is only plumbing here: it owns device memory (outputs, gradients, the three opaque scratch blobs) and the
 current stream.  All compute happens in the hand-written sm_100a kernels.
 """
-import os
-
 import torch
 
 from . import _lib
@@ -14,10 +12,6 @@ from . import _lib
 NUM_CHANNELS = 3  # config.h:4
 
 _pinned = {}
-
-
-def _variant():
-    return int(os.environ.get("RAIN_RAST_VARIANT", "4"))
 
 
 def _ptr(t):
@@ -42,15 +36,19 @@ class _GeomPass:
     __slots__ = ("P", "H", "W", "dev", "bg", "debug", "out_color", "out_depth", "radii", "geom", "img", "nr", "event", "stream", "keep", "N", "binning", "bin_event", "bin_stream")
 
 
-def _pinned_slot(dev):
-    """a pinned int64 for num_rendered; two per device, used alternately, so that one forward may be in flight while the
-    previous one's count is still being read"""
-    key = dev.index
-    if key not in _pinned:
-        _pinned[key] = [torch.zeros(1, dtype=torch.int64).pin_memory() for _ in range(2)] + [0]
-    slots = _pinned[key]
-    slots[2] ^= 1
-    return slots[slots[2]]
+def _take_slot(dev):
+    """A pinned int64 word for num_rendered, owned by ONE forward pass from forward_geom until its count has been read
+    (_read_count), then returned to the per-device pool: any number of first halves may be in flight."""
+    pool = _pinned.setdefault(dev.index, [])
+    return pool.pop() if pool else torch.zeros(1, dtype=torch.int64).pin_memory()
+
+
+def _read_count(st):
+    """num_rendered of a pass whose first half has completed (the caller synchronised st.event); releases the pinned word"""
+    N = int(st.nr.item())
+    _pinned.setdefault(st.dev.index, []).append(st.nr)
+    st.nr = None
+    return N
 
 
 def forward_geom(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
@@ -84,7 +82,7 @@ def forward_geom(background, means3D, colors, opacity, scales, rotations, scale_
     st.radii = torch.empty((P,), dtype=torch.int32, device=dev)
     st.geom = torch.empty(lib.rr_geom_bytes(P), **byte)
     st.img = torch.empty(lib.rr_image_bytes(W, H), **byte)
-    st.nr = _pinned_slot(dev)
+    st.nr = _take_slot(dev)
     st.keep = (means3D_c, colors_c, opac, scales_c, rots, cov_c, view, proj, cam, sh_c)   # inputs stay alive until the kernels ran
     with torch.cuda.device(dev):
         st.stream = torch.cuda.current_stream() if stream is None else stream
@@ -111,7 +109,7 @@ def forward_raster(st):
         return (0, z((NUM_CHANNELS, H, W), dtype=torch.float32, device=dev), z((0,), dtype=torch.int32, device=dev),
                 z((1, H, W), dtype=torch.float32, device=dev), torch.empty(0, **byte), torch.empty(0, **byte), torch.empty(0, **byte))
     st.event.synchronize()
-    N = int(st.nr.item())
+    N = _read_count(st)
     with torch.cuda.device(dev):
         stream = torch.cuda.current_stream()
         if stream != st.stream:                  # first half ran on another stream (rain_b200.multiview's geometry stream)
@@ -120,7 +118,7 @@ def forward_raster(st):
     with torch.cuda.device(dev):
         _lib.check(lib.rr_forward_raster(stream.cuda_stream, P, W, H, N, _ptr(st.bg),
                                          st.geom.data_ptr(), st.geom.numel(), binning.data_ptr(), binning.numel(), st.img.data_ptr(), st.img.numel(),
-                                         st.out_color.data_ptr(), st.out_depth.data_ptr(), _variant(), int(st.debug)), "rr_forward_raster")
+                                         st.out_color.data_ptr(), st.out_depth.data_ptr(), int(st.debug)), "rr_forward_raster")
     st.keep = None
     return N, st.out_color, st.radii, st.out_depth, st.geom, binning, st.img
 
@@ -132,14 +130,14 @@ def forward_bin(st, stream=None):
     if st.P == 0:
         return st
     st.event.synchronize()
-    st.N = int(st.nr.item())
+    st.N = _read_count(st)
     st.binning = torch.empty(lib.rr_binning_bytes(st.N, st.W, st.H), dtype=torch.uint8, device=st.dev)
     with torch.cuda.device(st.dev):
         st.bin_stream = torch.cuda.current_stream() if stream is None else stream
         if st.bin_stream != st.stream:
             st.bin_stream.wait_event(st.event)
         _lib.check(lib.rr_forward_bin(st.bin_stream.cuda_stream, st.P, st.W, st.H, st.N, st.geom.data_ptr(), st.geom.numel(),
-                                      st.binning.data_ptr(), st.binning.numel(), st.img.data_ptr(), st.img.numel(), _variant(), int(st.debug)), "rr_forward_bin")
+                                      st.binning.data_ptr(), st.binning.numel(), st.img.data_ptr(), st.img.numel(), int(st.debug)), "rr_forward_bin")
         st.bin_event = torch.cuda.Event()
         st.bin_event.record(st.bin_stream)
     return st
@@ -157,7 +155,7 @@ def forward_render(st):
             stream.wait_event(st.bin_event)
         _lib.check(lib.rr_forward_render(stream.cuda_stream, st.P, st.W, st.H, st.N, _ptr(st.bg),
                                          st.geom.data_ptr(), st.geom.numel(), st.binning.data_ptr(), st.binning.numel(), st.img.data_ptr(), st.img.numel(),
-                                         st.out_color.data_ptr(), st.out_depth.data_ptr(), _variant(), int(st.debug)), "rr_forward_render")
+                                         st.out_color.data_ptr(), st.out_depth.data_ptr(), int(st.debug)), "rr_forward_render")
     st.keep = None
     return st.N, st.out_color, st.radii, st.out_depth, st.geom, st.binning, st.img
 
@@ -233,7 +231,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                                        dpix.data_ptr(), ws.data_ptr(), ws.numel(),
                                        dL_dmeans2D.data_ptr(), dL_dconic.data_ptr(), dL_dopacity.data_ptr(), None if "colors" in omit else dL_dcolors.data_ptr(),
                                        dL_dmeans3D.data_ptr(), None if "cov3D" in omit else dL_dcov3D.data_ptr(), _ptr(dL_dsh), dL_dscales.data_ptr(), dL_drotations.data_ptr(),
-                                       _variant(), int(bool(debug)), 1 if accumulate else 0), "rr_backward")
+                                       int(bool(debug)), 1 if accumulate else 0), "rr_backward")
     out = (dL_dmeans2D, None if "colors" in omit else dL_dcolors, dL_dopacity, dL_dmeans3D, None if "cov3D" in omit else dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)
     return out + (dL_dconic,) if return_conic else out
 

@@ -32,12 +32,12 @@ SIGNATURES = {
                              _vp, _vp, _sz, _vp]),
     "rr_forward_raster": (_i, [_vp, _i, _i, _i, _i64, _vp,
                                _vp, _sz, _vp, _sz, _vp, _sz,
-                               _vp, _vp, _i, _i]),
+                               _vp, _vp, _i]),
     "rr_forward_bin": (_i, [_vp, _i, _i, _i, _i64,
-                            _vp, _sz, _vp, _sz, _vp, _sz, _i, _i]),
+                            _vp, _sz, _vp, _sz, _vp, _sz, _i]),
     "rr_forward_render": (_i, [_vp, _i, _i, _i, _i64, _vp,
                                _vp, _sz, _vp, _sz, _vp, _sz,
-                               _vp, _vp, _i, _i]),
+                               _vp, _vp, _i]),
     "rr_backward": (_i, [_vp, _i, _i, _i, _i, _i, _i64, _vp,
                          _vp, _vp, _vp,
                          _vp, _f, _vp, _vp,
@@ -47,7 +47,7 @@ SIGNATURES = {
                          _vp, _vp, _sz,
                          _vp, _vp, _vp, _vp,
                          _vp, _vp, _vp, _vp, _vp,
-                         _i, _i, _i]),
+                         _i, _i]),
     "rr_mark_visible": (_i, [_vp, _i, _vp, _vp, _vp, _vp]),
     "rr_selftest_exp": (_i, [_vp, _c.c_uint32, _c.c_uint32, _vp]),
     "rr_loss_ws_bytes": (_sz, [_i, _i, _i]),

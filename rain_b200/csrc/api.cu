@@ -35,12 +35,25 @@ int check_launch(const char* what, cudaStream_t stream, bool sync)
 	return 0;
 }
 
+#ifdef RR_CROSSCHECK
+// cross-check build only (make crosscheck): RAIN_XC_STAGING=tma stages the tile renderers with per-record TMA bulk copies
+int crosscheck_staging() { static const int m = []() { const char* e = getenv("RAIN_XC_STAGING"); return (e && e[0] == 't') ? 1 : 0; }(); return m; }
+// work counters of the tile renderers (render_common.cuh); the cross-check build may allocate, the product library never does
+static unsigned long long* xc_counters_dev() {
+	static unsigned long long* p = []() { unsigned long long* q = nullptr; if (cudaMalloc(&q, 16 * sizeof(unsigned long long)) != cudaSuccess) return (unsigned long long*)nullptr; cudaMemset(q, 0, 16 * sizeof(unsigned long long)); return q; }();
+	return p;
+}
+#define XC_COUNTERS xc_counters_dev()
+#else
+#define XC_COUNTERS nullptr
+#endif
+
 namespace {
 
 // ---- per-stage device timing (CUDA events on the caller's stream), off by default; used by bench.py -----------------
-enum StageId { ST_PREPROCESS = 0, ST_DEPTH_SORT, ST_SCAN, ST_DUPLICATE, ST_TILE_SORT, ST_RANGES_PACK, ST_RENDER_FWD,
+enum StageId { ST_PREPROCESS = 0, ST_DEPTH_SORT, ST_SCAN, ST_DUPLICATE, ST_TILE_SORT, ST_RANGES, ST_RENDER_FWD,
 	ST_RENDER_BWD, ST_PREPROCESS_BWD, ST_DIST2, ST_COUNT };
-const char* const kStageNames[ST_COUNT] = { "preprocess_fwd", "depth_sort", "scan", "duplicate", "tile_sort", "ranges_pack",
+const char* const kStageNames[ST_COUNT] = { "preprocess_fwd", "depth_sort", "scan", "duplicate", "tile_sort", "ranges",
 	"render_fwd", "render_bwd", "preprocess_bwd", "dist2" };
 struct Pending { int stage; cudaEvent_t a, b; };
 struct Prof {
@@ -91,9 +104,8 @@ struct GeomLayout {
 	size_t total;
 	int64_t off[9];
 };
-// opt-in tile culling (preprocess.cu): RAIN_TILE_CULL=1, read once; not combined with the counting binning
-bool count_binning_wanted();
-bool tile_cull_wanted() { static const bool on = []() { const char* e = getenv("RAIN_TILE_CULL"); return e && e[0] == '1' && !count_binning_wanted(); }(); return on; }
+// opt-in tile culling (preprocess.cu): RAIN_TILE_CULL=1, read once per process — the one run-time switch of the library
+bool tile_cull_wanted() { static const bool on = []() { const char* e = getenv("RAIN_TILE_CULL"); return e && e[0] == '1'; }(); return on; }
 
 GeomLayout geom_layout(void* blob, int P)
 {
@@ -121,7 +133,7 @@ GeomLayout geom_layout(void* blob, int P)
 }
 
 struct BinLayout {
-	uint32_t *key_a, *key_b, *val_a, *val_b, *warp_flags; SplatRec* packed; void* sort_ws;
+	uint32_t *key_a, *key_b, *val_a, *val_b, *warp_flags; void* sort_ws;
 	uint32_t *keys_sorted, *point_list;
 	int bits; size_t flag_words; size_t total; int64_t off[5];
 };
@@ -136,23 +148,17 @@ BinLayout bin_layout(void* blob, int64_t N, int W, int H)
 	L.flag_words = warp_flag_words(Nz, (size_t)tiles);
 	L.warp_flags = c.take<uint32_t>(L.flag_words);
 	L.sort_ws = c.take<char>(sort_ws_bytes<uint32_t>(Nz, 0, L.bits));
-	// the packed copy of the records in sorted order is only touched by the packed staging variants (0 / 1); it is carved
-	// last so that the working set of the gather variants stays compact
-	L.packed = c.take<SplatRec>(Nz);
 	L.total = c.used();
 	const bool in_b = (((L.bits + 7) / 8) & 1) != 0;
 	L.keys_sorted = in_b ? L.key_b : L.key_a;
 	L.point_list = in_b ? L.val_b : L.val_a;
 	char* b = reinterpret_cast<char*>(blob);
 	L.off[0] = (char*)L.keys_sorted - b; L.off[1] = (char*)L.point_list - b; L.off[2] = (char*)L.warp_flags - b;
-	L.off[3] = (char*)L.point_list - b; L.off[4] = (char*)L.packed - b;
+	L.off[3] = (char*)L.point_list - b; L.off[4] = 0;
 	return L;
 }
 
-// RAIN_BINNING=count: opt-in sort-free binning (read once)
-bool count_binning_wanted() { static const bool on = []() { const char* e = getenv("RAIN_BINNING"); return e && e[0] == 'c'; }(); return on; }
-
-struct ImgLayout { float* final_T; uint32_t* n_contrib; uint2* ranges; uint32_t* tile_max; void* cb_ws; size_t total; int64_t off[4]; };
+struct ImgLayout { float* final_T; uint32_t* n_contrib; uint2* ranges; uint32_t* tile_max; size_t total; int64_t off[4]; };
 ImgLayout img_layout(void* blob, int W, int H)
 {
 	ImgLayout L; Carver c(blob);
@@ -162,8 +168,6 @@ ImgLayout img_layout(void* blob, int W, int H)
 	L.n_contrib = c.take<uint32_t>(X < 1 ? 1 : X);
 	L.ranges = c.take<uint2>(tiles < 1 ? 1 : tiles);
 	L.tile_max = c.take<uint32_t>(tiles < 1 ? 1 : tiles);
-	// count / base matrices of the sort-free binning (binning_count.cu; opt-in, RAIN_BINNING=count); sized by the tile count only
-	L.cb_ws = (count_binning_wanted() && tiles <= (size_t)CB_MAX_TILES) ? (void*)c.take<char>(count_binning_ws_bytes((int)(tiles < 1 ? 1 : tiles))) : nullptr;
 	L.total = c.used();
 	char* b = reinterpret_cast<char*>(blob);
 	L.off[0] = (char*)L.final_T - b; L.off[1] = (char*)L.n_contrib - b; L.off[2] = (char*)L.ranges - b; L.off[3] = (char*)L.tile_max - b;
@@ -264,27 +268,19 @@ int rr_forward_geom(void* stream_, int P, int D, int M, int W, int H,
 }
 
 int rr_forward_bin(void* stream_, int P, int W, int H, int64_t N,
-	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes, int variant, int debug)
+	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes, int debug)
 {
 	cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
 	if (P == 0) return 0;
 	if (bad_ptr(geom, "geom") || bad_ptr(binning, "binning") || bad_ptr(image, "image")) return -1;
-	if (N < 0 || N >= (1ll << 30)) { set_error("num_rendered=%lld out of range", (long long)N); return -1; }
+	if (N < 0 || N >= (1ll << 30) - 1) { set_error("num_rendered=%lld out of range (the tile-duplicate count saturates at 2^30 - 1)", (long long)N); return -1; }
 	const GeomLayout G = geom_layout(geom, P);
 	const BinLayout B = bin_layout(binning, N, W, H);
 	const ImgLayout I = img_layout(image, W, H);
 	if (G.total > geom_bytes || B.total > binning_bytes || I.total > image_bytes) { set_error("scratch blob too small"); return -1; }
 	const int grid_x = (W + TILE_X - 1) / TILE_X, grid_y = (H + TILE_Y - 1) / TILE_Y;
 
-	// default: duplicate + onesweep tile sort + ranges; RAIN_BINNING=count selects the sort-free counting placement
-	// (binning_count.cu: same lists bit for bit, measured slower on B200 — see its header)
-	const bool count_mode = I.cb_ws != nullptr;
-	if (count_mode) {
-		Stage st(stream, ST_TILE_SORT);
-		cudaMemsetAsync(I.ranges, 0, sizeof(uint2) * (size_t)(grid_x * grid_y), stream);
-		if (N > 0 && launch_count_binning(stream, P, grid_x * grid_y, grid_x, G.val_a, G.tiles_touched, G.rect, I.cb_ws, I.ranges, B.point_list)) return -1;
-		if (debug && check_launch("count binning", stream, true)) return -1;
-	} else if (N > 0) {
+	if (N > 0) {
 		{ Stage st(stream, ST_DUPLICATE); if (launch_duplicate(stream, P, G.val_a, G.offsets, G.rect, G.tile_mask, grid_x, B.key_a, B.val_a)) return -1; }
 		if (debug && check_launch("duplicate", stream, true)) return -1;
 		int which;
@@ -293,24 +289,19 @@ int rr_forward_bin(void* stream_, int P, int W, int H, int64_t N,
 		if ((which ? B.key_b : B.key_a) != B.keys_sorted) { set_error("internal: tile sort landed in the wrong buffer"); return -1; }
 		if (debug && check_launch("tile sort", stream, true)) return -1;
 	}
-	{
-		Stage st(stream, ST_RANGES_PACK);
-		const bool packed = (variant == 0 || variant == 1);    // the gather modes read rec[] through point_list: no pack pass
-		if (!count_mode && launch_tile_ranges(stream, (size_t)N, B.keys_sorted, I.ranges, grid_x * grid_y)) return -1;
-		if (packed && launch_pack(stream, (size_t)N, B.point_list, G.rec, B.packed)) return -1;
-	}
+	{ Stage st(stream, ST_RANGES); if (launch_tile_ranges(stream, (size_t)N, B.keys_sorted, I.ranges, grid_x * grid_y)) return -1; }
 	return check_launch("forward_bin", stream, debug != 0);
 }
 
 int rr_forward_render(void* stream_, int P, int W, int H, int64_t N, const float* background,
 	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes,
-	float* out_color, float* out_depth, int variant, int debug)
+	float* out_color, float* out_depth, int debug)
 {
 	cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
 	if (P == 0) return 0;
 	if (bad_ptr(background, "background") || bad_ptr(geom, "geom") || bad_ptr(binning, "binning") || bad_ptr(image, "image") ||
 		bad_ptr(out_color, "out_color") || bad_ptr(out_depth, "out_depth")) return -1;
-	if (N < 0 || N >= (1ll << 30)) { set_error("num_rendered=%lld out of range", (long long)N); return -1; }
+	if (N < 0 || N >= (1ll << 30) - 1) { set_error("num_rendered=%lld out of range (the tile-duplicate count saturates at 2^30 - 1)", (long long)N); return -1; }
 	const GeomLayout G = geom_layout(geom, P);
 	const BinLayout B = bin_layout(binning, N, W, H);
 	const ImgLayout I = img_layout(image, W, H);
@@ -319,20 +310,20 @@ int rr_forward_render(void* stream_, int P, int W, int H, int64_t N, const float
 
 	RenderArgs r; memset(&r, 0, sizeof(r));
 	r.W = W; r.H = H; r.grid_x = grid_x; r.grid_y = grid_y;
-	r.ranges = I.ranges; r.packed = B.packed; r.rec = G.rec; r.point_list = B.point_list; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.warp_flags = B.warp_flags;
-	r.out_color = out_color; r.out_depth = out_depth; r.variant = variant;
+	r.ranges = I.ranges; r.rec = G.rec; r.point_list = B.point_list; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.warp_flags = B.warp_flags;
+	r.out_color = out_color; r.out_depth = out_depth; r.xc = XC_COUNTERS;
 	{ Stage st(stream, ST_RENDER_FWD); if (launch_render_fwd(stream, r)) return -1; }
 	return check_launch("forward_render", stream, debug != 0);
 }
 
 int rr_forward_raster(void* stream, int P, int W, int H, int64_t N, const float* background,
 	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes,
-	float* out_color, float* out_depth, int variant, int debug)
+	float* out_color, float* out_depth, int debug)
 {
 	if (P == 0) return 0;
 	if (bad_ptr(background, "background") || bad_ptr(out_color, "out_color") || bad_ptr(out_depth, "out_depth")) return -1;
-	if (rr_forward_bin(stream, P, W, H, N, geom, geom_bytes, binning, binning_bytes, image, image_bytes, variant, debug)) return -1;
-	return rr_forward_render(stream, P, W, H, N, background, geom, geom_bytes, binning, binning_bytes, image, image_bytes, out_color, out_depth, variant, debug);
+	if (rr_forward_bin(stream, P, W, H, N, geom, geom_bytes, binning, binning_bytes, image, image_bytes, debug)) return -1;
+	return rr_forward_render(stream, P, W, H, N, background, geom, geom_bytes, binning, binning_bytes, image, image_bytes, out_color, out_depth, debug);
 }
 
 int rr_backward(void* stream_, int P, int D, int M, int W, int H, int64_t N, const float* background,
@@ -344,7 +335,7 @@ int rr_backward(void* stream_, int P, int D, int M, int W, int H, int64_t N, con
 	const float* dL_dpix, void* ws, size_t ws_bytes,
 	float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
 	float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
-	int variant, int debug, int flags)
+	int debug, int flags)
 {
 	cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
 	if (P == 0) return 0;                                                  // rasterize_points.cu:155
@@ -365,8 +356,8 @@ int rr_backward(void* stream_, int P, int D, int M, int W, int H, int64_t N, con
 
 	RenderArgs r; memset(&r, 0, sizeof(r));
 	r.W = W; r.H = H; r.grid_x = grid_x; r.grid_y = grid_y;
-	r.ranges = I.ranges; r.packed = B.packed; r.rec = G.rec; r.point_list = B.point_list; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.warp_flags = B.warp_flags;
-	r.dL_dpix = dL_dpix; r.grad_acc = grad_acc; r.variant = variant;
+	r.ranges = I.ranges; r.rec = G.rec; r.point_list = B.point_list; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.warp_flags = B.warp_flags;
+	r.dL_dpix = dL_dpix; r.grad_acc = grad_acc; r.xc = XC_COUNTERS;
 	{
 		// the accumulators start from zero (the fill is part of the render_bwd stage time)
 		Stage st(stream, ST_RENDER_BWD);
@@ -388,6 +379,18 @@ int rr_backward(void* stream_, int P, int D, int M, int W, int H, int64_t N, con
 	{ Stage st(stream, ST_PREPROCESS_BWD); if (launch_preprocess_bwd(stream, a)) return -1; }
 	return check_launch("backward", stream, debug != 0);
 }
+
+#ifdef RR_CROSSCHECK
+/* cross-check build only (not declared in include/rain_rast.h): copy the 16 work counters to the host, optionally reset them */
+int rr_xc_counters(unsigned long long* out_host, int reset)
+{
+	unsigned long long* d = xc_counters_dev();
+	if (!d) { set_error("rr_xc_counters: no counter buffer"); return -1; }
+	if (cudaDeviceSynchronize() != cudaSuccess || cudaMemcpy(out_host, d, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost) != cudaSuccess) { set_error("rr_xc_counters: copy failed"); return -1; }
+	if (reset) cudaMemset(d, 0, 16 * sizeof(unsigned long long));
+	return 0;
+}
+#endif
 
 int rr_selftest_exp(void* stream_, uint32_t first_bits, uint32_t count, unsigned long long* mismatches_dev)
 {
@@ -504,7 +507,7 @@ int rr_export_sorted_keys(void* stream_, int P, int64_t N, int W, int H, void* g
 	const ImgLayout I = img_layout(image, W, H);
 	// tile ids from the tile ranges, depth bits from rec.c.y (float index 9 of the 12-float record)
 	const int tiles = ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
-	return launch_export_keys_ranges(reinterpret_cast<cudaStream_t>(stream_), tiles, I.ranges, B.point_list, reinterpret_cast<const uint32_t*>(G.rec), keys_out);
+	return launch_export_keys(reinterpret_cast<cudaStream_t>(stream_), tiles, I.ranges, B.point_list, reinterpret_cast<const uint32_t*>(G.rec), keys_out);
 }
 
 }  // extern "C"

@@ -1,4 +1,4 @@
-// Tile binning: prefix sum of tiles_touched, (tile, Gaussian) duplicate emission, tile ranges, record packing.
+// Tile binning: prefix sum of tiles_touched, (tile, Gaussian) duplicate emission, tile ranges.
 // Replaces cub::DeviceScan::InclusiveSum (reference rasterizer_impl.cu:269), duplicateWithKeys (:59-100),
 // identifyTileRanges (:105-127) and the cudaMemset of ranges (:302).
 //
@@ -8,7 +8,6 @@
 // (tile, depth, index) order: ties in (tile, depth) keep ascending Gaussian index in both schemes, because both
 // sorts are stable and the depth sort starts from index order.  The 64-bit key list the reference would hold is
 // reconstructed on demand by export_keys_kernel for the parity tests.
-#include <cstdlib>
 #include "common.cuh"
 #include "kernels.cuh"
 
@@ -20,81 +19,32 @@ constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_ITEMS = 4;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 
+// Status words of the chained scan: flags in the top two bits, a 30-bit payload.  All sums SATURATE at SC_MASK = 2^30 - 1
+// (operands are <= SC_MASK, so a + b cannot wrap 32 bits): a total that does not fit the payload reaches the host as
+// exactly SC_MASK, which rr_forward_bin rejects, instead of wrapping silently into a plausible small count.
+constexpr uint32_t SC_AGG = 1u << 30, SC_INC = 2u << 30, SC_MASK = (1u << 30) - 1;
+__device__ __forceinline__ uint32_t sat_add(uint32_t a, uint32_t b) { return min(a + b, SC_MASK); }
+
 __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* s_warp /*[8]*/, uint32_t& block_total)
 {
 	const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
 	uint32_t inc = v;
 	#pragma unroll
-	for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(FULL, inc, o); if (lane >= (unsigned)o) inc += t; }
+	for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(FULL, inc, o); if (lane >= (unsigned)o) inc = sat_add(inc, t); }
 	if (lane == 31) s_warp[warp] = inc;
 	__syncthreads();
 	uint32_t pre = 0, tot = 0;
 	#pragma unroll
-	for (int w = 0; w < SCAN_THREADS / 32; w++) { const uint32_t t = s_warp[w]; if (w < (int)warp) pre += t; tot += t; }
+	for (int w = 0; w < SCAN_THREADS / 32; w++) { const uint32_t t = s_warp[w]; if (w < (int)warp) pre = sat_add(pre, t); tot = sat_add(tot, t); }
 	block_total = tot;
 	__syncthreads();
-	return pre + inc - v;
+	return sat_add(pre, inc) - v;            // exact below saturation; garbage above it, where the host rejects the total
 }
 
-// Inclusive prefix sum of tiles_touched in DEPTH order (where each Gaussian's duplicates go in the emission list):
-// reduce / scan-of-block-sums / final, three launches.
-__global__ void __launch_bounds__(SCAN_THREADS) scan_reduce_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ tt, uint32_t* __restrict__ block_sums)
-{
-	__shared__ uint32_t s_warp[SCAN_THREADS / 32];
-	uint32_t sum = 0;
-	#pragma unroll
-	for (int k = 0; k < SCAN_ITEMS; k++) {
-		const int i = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS + k;
-		if (i < P) sum += tt[order[i]];
-	}
-	uint32_t tot;
-	block_exclusive_scan(sum, s_warp, tot);
-	if (threadIdx.x == 0) block_sums[blockIdx.x] = tot;
-}
-
-// single CTA: exclusive scan of the block sums in place, grand total to *total
-__global__ void __launch_bounds__(SCAN_THREADS) scan_blocksums_kernel(int nb, uint32_t* __restrict__ block_sums, uint32_t* __restrict__ total,
-	uint32_t* __restrict__ total_host /*host-mapped pinned word or null: the count reaches the host without a copy-engine transfer*/)
-{
-	__shared__ uint32_t s_warp[SCAN_THREADS / 32];
-	uint32_t carry = 0;
-	for (int base = 0; base < nb; base += SCAN_THREADS) {
-		const int i = base + threadIdx.x;
-		const uint32_t v = i < nb ? block_sums[i] : 0;
-		uint32_t tot;
-		const uint32_t ex = block_exclusive_scan(v, s_warp, tot);
-		if (i < nb) block_sums[i] = carry + ex;
-		carry += tot;
-	}
-	if (threadIdx.x == 0) { *total = carry; if (total_host) { *total_host = carry; __threadfence_system(); } }
-}
-
-__global__ void __launch_bounds__(SCAN_THREADS) scan_final_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ tt,
-	const uint32_t* __restrict__ block_excl, uint32_t* __restrict__ offsets /*inclusive, depth order*/)
-{
-	__shared__ uint32_t s_warp[SCAN_THREADS / 32];
-	uint32_t v[SCAN_ITEMS], sum = 0;
-	#pragma unroll
-	for (int k = 0; k < SCAN_ITEMS; k++) {
-		const int i = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS + k;
-		v[k] = i < P ? tt[order[i]] : 0;
-		sum += v[k];
-	}
-	uint32_t tot;
-	uint32_t run = block_excl[blockIdx.x] + block_exclusive_scan(sum, s_warp, tot);
-	#pragma unroll
-	for (int k = 0; k < SCAN_ITEMS; k++) {
-		const int i = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS + k;
-		run += v[k];
-		if (i < P) offsets[i] = run;
-	}
-}
-
-// The same prefix sum in ONE launch: chained scan with decoupled look-back.  Blocks take tile ids from an atomic ticket (a
-// block's predecessors are therefore always running or done), publish their tile aggregate in a status word (flags in the
-// top two bits, as in radix_sort.cu), and warp 0 looks back over 32 predecessors per step until it meets an inclusive prefix.
-constexpr uint32_t SC_AGG = 1u << 30, SC_INC = 2u << 30, SC_MASK = (1u << 30) - 1;
-
+// Inclusive prefix sum of tiles_touched in DEPTH order (where each Gaussian's duplicates go in the emission list), replacing
+// cub::DeviceScan::InclusiveSum (rasterizer_impl.cu:269), in ONE launch: chained scan with decoupled look-back.  Blocks
+// take tile ids from an atomic ticket (a block's predecessors are therefore always running or done), publish their tile
+// aggregate in a status word, and warp 0 looks back over 32 predecessors per step until it meets an inclusive prefix.
 __global__ void __launch_bounds__(SCAN_THREADS) scan_chained_kernel(int P, int nb, const uint32_t* __restrict__ order, const uint32_t* __restrict__ tt,
 	volatile uint32_t* __restrict__ status /*[nb] + ticket at [nb], zero on entry*/, uint32_t* __restrict__ offsets /*inclusive, depth order*/,
 	uint32_t* __restrict__ total, uint32_t* __restrict__ total_host)
@@ -108,8 +58,8 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_chained_kernel(int P, int n
 	#pragma unroll
 	for (int k = 0; k < SCAN_ITEMS; k++) {
 		const int i = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS + k;
-		v[k] = i < P ? tt[order[i]] : 0;
-		sum += v[k];
+		v[k] = i < P ? min(tt[order[i]], SC_MASK) : 0;
+		sum = sat_add(sum, v[k]);
 	}
 	uint32_t tot;
 	const uint32_t ex = block_exclusive_scan(sum, s_warp, tot);
@@ -127,15 +77,16 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_chained_kernel(int P, int n
 			const int take = min(first_nr, first_inc + 1);              // lanes [0, take): published, up to and including the first inclusive one
 			uint32_t c = (int)lane < take ? (w & SC_MASK) : 0u;
 			#pragma unroll
-			for (int o = 16; o >= 1; o >>= 1) c += __shfl_xor_sync(FULL, c, o);
-			excl += c;
+			for (int o = 16; o >= 1; o >>= 1) c = sat_add(c, __shfl_xor_sync(FULL, c, o));
+			excl = sat_add(excl, c);
 			if (first_inc < first_nr) break;
 			t -= take;
 		}
 		if (lane == 0) {
-			if (tile > 0) { status[tile] = (excl + tot) | SC_INC; __threadfence(); }
+			const uint32_t incl = sat_add(excl, tot);
+			if (tile > 0) { status[tile] = incl | SC_INC; __threadfence(); }
 			s_excl = excl;
-			if (tile == nb - 1) { *total = excl + tot; if (total_host) { *total_host = excl + tot; __threadfence_system(); } }
+			if (tile == nb - 1) { *total = incl; if (total_host) { *total_host = incl; __threadfence_system(); } }
 		}
 	}
 	__syncthreads();
@@ -241,23 +192,16 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(uint32_t N, const uint
 	}
 }
 
-// packed[j] = rec[point_list[j]]; three threads move one 48-byte record (one float4 each)
-__global__ void __launch_bounds__(256) pack_kernel(uint32_t N, const uint32_t* __restrict__ point_list,
-	const float4* __restrict__ rec, float4* __restrict__ packed)
-{
-	const size_t t = (size_t)blockIdx.x * 256 + threadIdx.x;
-	if (t >= (size_t)N * 3) return;
-	const uint32_t j = (uint32_t)(t / 3), part = (uint32_t)(t - (size_t)j * 3);
-	packed[t] = __ldg(&rec[(size_t)point_list[j] * 3 + part]);
-}
-
-__global__ void __launch_bounds__(256) export_keys_kernel(uint32_t N, const uint32_t* __restrict__ tile_keys, const uint32_t* __restrict__ point_list,
+// the 64-bit (tile << 32 | depth bits) key list the reference would hold (point_list_keys, rasterizer_impl.cu:92),
+// reconstructed from ranges + point_list for the parity tests; depth bits = float index 9 (c.y) of the 12-float record
+__global__ void __launch_bounds__(128) export_keys_kernel(int T, const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
 	const uint32_t* __restrict__ rec_words, uint64_t* __restrict__ out)
 {
-	const uint32_t j = blockIdx.x * 256 + threadIdx.x;
-	if (j >= N) return;
-	// depth bits = float index 9 (c.y) of the Gaussian's 12-float record
-	out[j] = ((uint64_t)tile_keys[j] << 32) | rec_words[(size_t)point_list[j] * 12 + 9];
+	const int t = blockIdx.x;
+	if (t >= T) return;
+	const uint2 r = ranges[t];
+	for (uint32_t j = r.x + threadIdx.x; j < r.y; j += 128)
+		out[j] = ((uint64_t)(uint32_t)t << 32) | rec_words[(size_t)point_list[j] * 12 + 9];
 }
 
 }  // namespace
@@ -269,16 +213,8 @@ int launch_scan_tiles(cudaStream_t stream, int P, const uint32_t* order, const u
 {
 	if (P == 0) { cudaMemsetAsync(num_rendered_dev, 0, sizeof(uint32_t), stream); return 0; }
 	const int nb = (P + SCAN_TILE - 1) / SCAN_TILE;
-	// RAIN_SCAN=3 selects the three-launch reduce / scan / final version (cross-check of the chained single-launch scan)
-	static const bool three = []() { const char* e = getenv("RAIN_SCAN"); return e && e[0] == '3'; }();
-	if (three) {
-		count_launch(), scan_reduce_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, order, tt, block_sums);
-		count_launch(), scan_blocksums_kernel<<<1, SCAN_THREADS, 0, stream>>>(nb, block_sums, num_rendered_dev, num_rendered_mapped);
-		count_launch(), scan_final_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, order, tt, block_sums, offsets);
-	} else {
-		cudaMemsetAsync(block_sums, 0, sizeof(uint32_t) * (size_t)(nb + 1), stream);
-		count_launch(), scan_chained_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, nb, order, tt, block_sums, offsets, num_rendered_dev, num_rendered_mapped);
-	}
+	cudaMemsetAsync(block_sums, 0, sizeof(uint32_t) * (size_t)(nb + 1), stream);
+	count_launch(), scan_chained_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, nb, order, tt, block_sums, offsets, num_rendered_dev, num_rendered_mapped);
 	return check_launch("scan_tiles", stream, false);
 }
 
@@ -298,18 +234,9 @@ int launch_tile_ranges(cudaStream_t stream, size_t N, const uint32_t* keys, uint
 	return check_launch("tile_ranges", stream, false);
 }
 
-int launch_pack(cudaStream_t stream, size_t N, const uint32_t* point_list, const SplatRec* rec, SplatRec* packed)
+int launch_export_keys(cudaStream_t stream, int T, const uint2* ranges, const uint32_t* point_list, const uint32_t* rec_words, uint64_t* out)
 {
-	if (N == 0) return 0;
-	count_launch(), pack_kernel<<<(unsigned)((N * 3 + 255) / 256), 256, 0, stream>>>((uint32_t)N, point_list, reinterpret_cast<const float4*>(rec),
-		reinterpret_cast<float4*>(packed));
-	return check_launch("pack", stream, false);
-}
-
-int launch_export_keys(cudaStream_t stream, size_t N, const uint32_t* tile_keys, const uint32_t* point_list, const uint32_t* rec_words, uint64_t* out)
-{
-	if (N == 0) return 0;
-	count_launch(), export_keys_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>((uint32_t)N, tile_keys, point_list, rec_words, out);
+	count_launch(), export_keys_kernel<<<T, 128, 0, stream>>>(T, ranges, point_list, rec_words, out);
 	return check_launch("export_keys", stream, false);
 }
 

@@ -44,6 +44,14 @@ void set_error(const char* fmt, ...);
 int check_launch(const char* what, cudaStream_t stream, bool sync);
 void count_launch();   // every kernel launch of the library is counted (rr_launch_count), bench.py reports it
 
+// element idx of a [n,4] float array as a float4: one 16-byte load when the base is 16-byte aligned (a tensor that is a view
+// at an odd offset of a larger buffer need not be), four scalar loads otherwise; the branch is uniform
+__device__ __forceinline__ float4 load_f4(const float* __restrict__ base, size_t idx) {
+	const float* p = base + 4 * idx;
+	if ((reinterpret_cast<uintptr_t>(base) & 15) == 0) return *reinterpret_cast<const float4*>(p);
+	return make_float4(p[0], p[1], p[2], p[3]);
+}
+
 __device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31u; }
 __device__ __forceinline__ unsigned lanemask_lt() { unsigned m; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m)); return m; }
 

@@ -28,16 +28,7 @@ int launch_scan_tiles(cudaStream_t, int P, const uint32_t* order, const uint32_t
 int launch_duplicate(cudaStream_t, int P, const uint32_t* order, const uint32_t* offsets, const uint2* rect, const unsigned long long* tile_mask /*or null*/, int grid_x,
 	uint32_t* tile_keys /*[N] emission order*/, uint32_t* gaussian_ids /*[N] emission order*/);
 int launch_tile_ranges(cudaStream_t, size_t N, const uint32_t* sorted_tile_keys, uint2* ranges, int num_tiles);
-int launch_pack(cudaStream_t, size_t N, const uint32_t* point_list, const SplatRec* rec, SplatRec* packed);
-int launch_export_keys(cudaStream_t, size_t N, const uint32_t* sorted_tile_keys, const uint32_t* point_list, const uint32_t* rec_words, uint64_t* out);
-
-// binning_count.cu: sort-free tile binning (counting placement of the depth-ordered Gaussians)
-constexpr int CB_MAX_CHUNKS = 1024;      // >= one resident wave of placement CTAs (6 per SM)
-constexpr int CB_MAX_TILES = 12288;      // 48 KB of 32-bit positions in shared memory (8 160 tiles at 1920x1080)
-size_t count_binning_ws_bytes(int T);
-int launch_count_binning(cudaStream_t, int P, int T, int grid_x, const uint32_t* order, const uint32_t* tiles_touched, const uint2* rect,
-	void* ws, uint2* ranges, uint32_t* point_list);
-int launch_export_keys_ranges(cudaStream_t, int T, const uint2* ranges, const uint32_t* point_list, const uint32_t* rec_words, uint64_t* out);
+int launch_export_keys(cudaStream_t, int T, const uint2* ranges, const uint32_t* point_list, const uint32_t* rec_words, uint64_t* out);
 
 // render_fwd.cu / render_bwd.cu
 // Per-warp blend flags ("which list entries did warp w's 8x4 pixel block blend"), written by the forward and walked by
@@ -54,8 +45,7 @@ constexpr int ACC_FLOATS = 12;
 struct RenderArgs {
 	int W, H, grid_x, grid_y;
 	const uint2* ranges;        // [tiles]
-	const SplatRec* packed;     // [N] in sorted (tile, depth) order (variants 0/1 only)
-	const SplatRec* rec;        // [P] per-Gaussian records (variants 2/3 gather from here)
+	const SplatRec* rec;        // [P] per-Gaussian records, gathered through point_list
 	const uint32_t* point_list; // [N] sorted Gaussian ids
 	const float* bg;            // [3]
 	float* final_T;             // [H*W]
@@ -66,7 +56,7 @@ struct RenderArgs {
 	// backward only
 	const float* dL_dpix;       // [3,H,W]
 	float* grad_acc;            // [P, ACC_FLOATS], zero on entry
-	int variant;                // staging mode, see render_common.cuh
+	unsigned long long* xc;     // cross-check build only (-DRR_CROSSCHECK): [16] work counters, see render_common.cuh; null in the product library
 };
 int launch_render_fwd(cudaStream_t, const RenderArgs&);
 int launch_render_bwd(cudaStream_t, const RenderArgs&);

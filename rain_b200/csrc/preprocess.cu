@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(256, PF_MIN_CTAS) preprocess_fwd_kernel(Prepro
 			#pragma unroll
 			for (int k = 0; k < 6; k++) c3[k] = a.cov3D_precomp[6 * (size_t)idx + k];
 		} else {
-			const float4 q = reinterpret_cast<const float4*>(a.rotations)[idx];
+			const float4 q = load_f4(a.rotations, (size_t)idx);
 			cov3d_from_scale_rot(a.scales[3 * (size_t)idx], a.scales[3 * (size_t)idx + 1], a.scales[3 * (size_t)idx + 2], a.scale_modifier, q, c3);
 			#pragma unroll
 			for (int k = 0; k < 6; k++) a.cov3D[6 * (size_t)idx + k] = c3[k];     // written even if culled below (forward.cu:201)

@@ -149,7 +149,7 @@ __device__ __forceinline__ void sh_grad(const PreprocessBwdArgs& a, int idx, flo
 // 3D covariance gradient -> scale and rotation gradient (reference computeCov3D backward, backward.cu:268-331)
 __device__ __forceinline__ void scale_rot_grad(const PreprocessBwdArgs& a, int idx, size_t i3, const float* dcov, float* ds, float4& dq)
 {
-	const float4 q = reinterpret_cast<const float4*>(a.rotations)[idx];
+	const float4 q = load_f4(a.rotations, (size_t)idx);
 	const float r = q.x, x = q.y, y = q.z, z = q.w;
 	// R in glm [col][row] indexing
 	const float R[3][3] = { { 1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y) },
@@ -313,9 +313,16 @@ __global__ void __launch_bounds__(PB_THREADS, PB_MIN_CTAS) preprocess_bwd_kernel
 	}
 	if (a.dL_dscale) { put1(a.dL_dscale + i3, ds[0]); put1(a.dL_dscale + i3 + 1, ds[1]); put1(a.dL_dscale + i3 + 2, ds[2]); }
 	if (a.dL_drot) {
-		float4* o = reinterpret_cast<float4*>(a.dL_drot) + idx;
-		if (acc) { const float4 c = *o; dq.x += c.x; dq.y += c.y; dq.z += c.z; dq.w += c.w; }
-		*o = dq;
+		// the rotations segment of a flat gradient bucket starts at float offset P * (7 + 3M): 16-byte aligned only when
+		// P % 4 == 0, so the float4 path is taken only for an aligned base (uniform branch)
+		if ((reinterpret_cast<uintptr_t>(a.dL_drot) & 15) == 0) {
+			float4* o = reinterpret_cast<float4*>(a.dL_drot) + idx;
+			if (acc) { const float4 c = *o; dq.x += c.x; dq.y += c.y; dq.z += c.z; dq.w += c.w; }
+			*o = dq;
+		} else {
+			float* o = a.dL_drot + 4 * (size_t)idx;
+			put1(o, dq.x); put1(o + 1, dq.y); put1(o + 2, dq.z); put1(o + 3, dq.w);
+		}
 	}
 }
 

@@ -11,7 +11,6 @@
 //      flags in the top two bits), reorders the tile through shared memory so the global scatter is written in runs,
 //      and writes keys and values to the other buffer.
 // Memory traffic per pass: read 1x + write 1x of (key,value); histogram: read keys once.
-#include <cstdlib>
 #include "common.cuh"
 #include "radix_sort.cuh"
 
@@ -326,8 +325,8 @@ int sort_pairs(cudaStream_t stream, K* keys_a, K* keys_b, uint32_t* vals_a, uint
 	const WsLayout L = ws_layout<K>(ws, n, pd.npass);
 	cudaMemsetAsync(ws, 0, L.zero_bytes, stream);
 	// ranking variant: shared-memory atomicOr match for large inputs (measured 0.196 vs 0.218 ms on the 8.4M-pair tile sort),
-	// ballot match for small ones (0.088 vs 0.096 ms on the 1M-key depth sort); RAIN_SORT_MATCH=b forces the ballot variant
-	static const bool match_or = []() { const char* e = getenv("RAIN_SORT_MATCH"); return !(e && e[0] == 'b'); }();
+	// ballot match for small ones (0.088 vs 0.096 ms on the 1M-key depth sort)
+	const bool match_or = true;
 	const uint32_t hgrid = (uint32_t)((n + SORT_THREADS * 16 - 1) / (SORT_THREADS * 16));
 	count_launch(), histogram_kernel<K><<<hgrid < 1184u ? hgrid : 1184u, SORT_THREADS, 0, stream>>>(keys_a, (uint32_t)n, pd, L.ghist);
 	count_launch(), digit_base_kernel<<<pd.npass, RADIX, 0, stream>>>(L.ghist);

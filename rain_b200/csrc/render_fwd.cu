@@ -4,11 +4,9 @@
 // B200 design (one CTA per tile, 8 consumer warps + 1 producer warp, no __syncthreads after the prologue):
 //  * the PRODUCER warp stages the tile's list into a ring of FWD_STAGES shared-memory stages of 128 records (48 B
 //    each), gathered asynchronously straight from the per-Gaussian record array (L2 resident) through point_list, 4
-//    records per lane and batch, all landing on the stage's `full` mbarrier.  Staging modes (render_common.cuh):
-//    4 (default) three 16-byte cp.async per record with cp.async.mbarrier.arrive.noinc; 2 one 48-byte TMA bulk copy
-//    (cp.async.bulk) per record — measured slower here, because a per-lane bulk-copy address is issued lane by lane
-//    through the uniform datapath; 1 ONE bulk copy of a packed span (needs the pack pass); 0 / 3 plain loads
-//    (cross-checks).  A stage is refilled when every consumer warp has released it: one arrival per warp and batch on
+//    records per lane and batch, all landing on the stage's `full` mbarrier (render_common.cuh: three 16-byte cp.async
+//    per record with cp.async.mbarrier.arrive.noinc; the 48-byte TMA bulk copy per record is the cross-check build's mode).
+//    A stage is refilled when every consumer warp has released it: one arrival per warp and batch on
 //    the stage's `empty` mbarrier, on which the producer sleeps in hardware (an earlier version polled per-warp
 //    progress words every 256 ns: ~9 % of the kernel's warp instructions, all on the producer's scheduler);
 //  * each CONSUMER warp owns an 8x4 pixel block and runs through the ring at its own pace: it culls a staged batch
@@ -35,30 +33,6 @@ namespace {
 #endif
 constexpr int FWD_STAGES = RR_FWD_STAGES;
 constexpr int FWD_THREADS = RENDER_THREADS + 32;      // 8 consumer warps + the producer warp
-
-// Producer: fill one stage with `cnt` records starting at list position `first`; completion is signalled on `bar`
-// (count 1: the arrive.expect_tx of lane 0 for the TMA modes, a plain arrive after the stores otherwise).
-template <int MODE>
-__device__ __forceinline__ void producer_fill(float4* dst, uint64_t* bar, const float4* __restrict__ packed, const float4* __restrict__ rec,
-	const uint32_t* __restrict__ ids, int first, int cnt, int lane)
-{
-	if (StageMode<MODE>::tma) {
-		stage_fill_async<MODE>(dst, bar, packed, rec, ids, first, cnt, lane);
-	} else if (StageMode<MODE>::async_gather) {
-		for (int i = lane; i < cnt; i += 32) {
-			const float4* __restrict__ src = rec + (size_t)__ldg(ids + first + i) * 3;
-			cp_async16(dst + i * 3, src); cp_async16(dst + i * 3 + 1, src + 1); cp_async16(dst + i * 3 + 2, src + 2);
-		}
-		cp_async_arrive_noinc(bar);          // every lane: fires when this lane's copies (if any) have landed
-	} else {
-		for (int i = lane; i < cnt * 3; i += 32) {
-			if (MODE == MODE_PACKED_LDG) dst[i] = __ldg(packed + (size_t)first * 3 + i);
-			else { const int e = i / 3; dst[i] = __ldg(rec + (size_t)__ldg(ids + first + e) * 3 + (i - e * 3)); }
-		}
-		__syncwarp();
-		if (lane == 0) mbar_arrive(bar);
-	}
-}
 
 #ifndef FWD_MIN_CTAS
 #define FWD_MIN_CTAS 4      // CTAs per SM the register budget is held to (56 registers at 288 threads)
@@ -89,7 +63,6 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MIN_CTAS) render_fwd_kernel(R
 
 	if (warp == RENDER_WARPS) {
 		// ------------------------------------------------ producer ------------------------------------------------
-		const float4* __restrict__ src = reinterpret_cast<const float4*>(a.packed) + (size_t)range.x * 3;
 		const float4* __restrict__ grec = reinterpret_cast<const float4*>(a.rec);
 		const uint32_t* __restrict__ ids = a.point_list + range.x;
 		for (int b = 0; b < nbatches; b++) {
@@ -108,7 +81,7 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MIN_CTAS) render_fwd_kernel(R
 				}
 				__threadfence_block();       // the consumers' reads of the stage are ordered before the refill below
 			}
-			producer_fill<MODE>(&s_rec[s][0], &s_full[s], src, grec, ids, b * BATCH, min(BATCH, n - b * BATCH), lane);
+			stage_fill_async<MODE>(&s_rec[s][0], &s_full[s], grec, ids, b * BATCH, min(BATCH, n - b * BATCH), lane);
 		}
 		// every consumer warp waits on every filled batch before it leaves, so no fill is in flight when the CTA retires
 		return;
@@ -135,6 +108,7 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MIN_CTAS) render_fwd_kernel(R
 	bool done = !inside;
 	bool warp_done = __all_sync(FULL, done);
 	if (warp_done && lane == 0) atomicAdd(&s_gone, 1);
+	XC(unsigned xc_batches = 0; unsigned xc_entries = 0; unsigned xc_aabb = 0; unsigned xc_blend = 0; unsigned xc_live = 0; unsigned xc_bl = 0;)
 
 	// Every consumer warp walks every filled batch: wait for the stage, work on it (or not: a warp whose pixels are all
 	// saturated is a "ghost" that only keeps the handshake going, asleep in the barrier wait), release the stage.
@@ -180,6 +154,7 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MIN_CTAS) render_fwd_kernel(R
 				nsurv += __popc(m);
 			}
 			__syncwarp();
+			XC(xc_batches++; xc_entries += cnt; xc_aabb += n1;)
 			// blend the survivors, 32 at a time.  Each lane keeps one "I blended survivor kk" bit per chunk (OR-reduced once
 			// per chunk with redux.sync); the saturation vote is taken every 8 survivors (a saturated pixel is predicated
 			// off anyway).  The body is branch-free: done / culled lanes are masked by predicates.
@@ -211,6 +186,7 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MIN_CTAS) render_fwd_kernel(R
 							const bool sat = ok && (test_T < 0.0001f);                               // forward.cu:341-346
 							done = done || sat;
 							const bool bl = ok && !sat;
+							XC(xc_live += ok; xc_bl += bl;)
 							const float4 rc = rec[e * 3 + 2];
 							const p2 a2 = pk1(bl ? alpha : 0.0f), T2 = pk1(T);
 							C01 = fma2(T2, mul2(a2, pk(rb.z, rb.w)), C01);
@@ -220,6 +196,7 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MIN_CTAS) render_fwd_kernel(R
 						};
 						blend(e0, power0, alpha0, rb0, ubit);
 						if (two) blend(e1, power1, alpha1, rb1, ubit << 1);
+						XC(xc_blend += two ? 2 : 1;)
 					};
 					// two survivors per step: everything up to alpha is independent of the blend state, so the two exponentials
 					// share the packed steps of exp2x; the blend itself stays in list order.  A full group of 8 runs unguarded, so
@@ -255,6 +232,10 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MIN_CTAS) render_fwd_kernel(R
 		if (lane == 0) mbar_arrive(&s_empty[s]);
 	}
 
+	XC({
+		const unsigned live = __reduce_add_sync(FULL, xc_live), bl = __reduce_add_sync(FULL, xc_bl);
+		if (lane == 0) { xc_add(a.xc, 0, xc_batches); xc_add(a.xc, 1, xc_entries); xc_add(a.xc, 2, xc_aabb); xc_add(a.xc, 3, xc_blend); xc_add(a.xc, 4, live); xc_add(a.xc, 5, bl); }
+	})
 	if (inside) {
 		const size_t pid = (size_t)a.W * pix_y + pix_x, HW = (size_t)a.H * a.W;
 		a.final_T[pid] = T;
@@ -292,13 +273,10 @@ int launch_exp_selftest(cudaStream_t stream, uint32_t first_bits, uint32_t count
 int launch_render_fwd(cudaStream_t stream, const RenderArgs& a)
 {
 	const dim3 grid(a.grid_x, a.grid_y);
-	switch (a.variant) {
-	case MODE_PACKED_LDG: count_launch(), render_fwd_kernel<MODE_PACKED_LDG><<<grid, FWD_THREADS, 0, stream>>>(a); break;
-	case MODE_PACKED_TMA: count_launch(), render_fwd_kernel<MODE_PACKED_TMA><<<grid, FWD_THREADS, 0, stream>>>(a); break;
-	case MODE_GATHER_LDG: count_launch(), render_fwd_kernel<MODE_GATHER_LDG><<<grid, FWD_THREADS, 0, stream>>>(a); break;
-	case MODE_GATHER_TMA: count_launch(), render_fwd_kernel<MODE_GATHER_TMA><<<grid, FWD_THREADS, 0, stream>>>(a); break;
-	default: count_launch(), render_fwd_kernel<MODE_GATHER_ASYNC><<<grid, FWD_THREADS, 0, stream>>>(a); break;
-	}
+#ifdef RR_CROSSCHECK
+	if (crosscheck_staging() == STAGE_TMA) { count_launch(), render_fwd_kernel<STAGE_TMA><<<grid, FWD_THREADS, 0, stream>>>(a); return check_launch("render_fwd", stream, false); }
+#endif
+	count_launch(), render_fwd_kernel<STAGE_CP_ASYNC><<<grid, FWD_THREADS, 0, stream>>>(a);
 	return check_launch("render_fwd", stream, false);
 }
 

@@ -15,8 +15,6 @@ from typing import Callable, List, Optional, Sequence
 
 import torch
 
-import os
-
 from . import _C as _native
 
 SEGMENTS = ("means3D", "sh", "opacity", "scales", "rotations")
@@ -74,20 +72,24 @@ class ViewResult:
 def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int], bucket: GradientBucket,
                          grad_fn: Callable[[int, torch.Tensor, torch.Tensor], torch.Tensor], *, bg: torch.Tensor, sh_degree: int,
                          scale_modifier: float = 1.0, low_pass: float = 0.3, debug: bool = False, keep_outputs: bool = True,
-                         backend=_native) -> List[ViewResult]:
+                         pipeline: str = "two_stream", backend=_native) -> List[ViewResult]:
     """Forward + backward of this rank's views; parameter gradients of all views are summed into ``bucket``.
 
     params: dict(means3D[P,3], opacities[P,1], shs[P,M,3], scales[P,3], rotations[P,4]) — activated values, as
     gaussian_renderer/__init__.py:37-60 passes them.  cameras[v] has width/height/tanfovx/tanfovy/viewmatrix/projmatrix/
     campos (rain_b200.synthetic.Camera or the reference's scene.cameras.Camera fields).  grad_fn(view, color, depth)
     returns dL/dcolor [3,H,W] (the loss backward of train.py:113-115).  The first view overwrites the bucket (no
-    zero-fill pass), later views accumulate."""
+    zero-fill pass), later views accumulate.  pipeline: "two_stream" (default: the front of the next view on a
+    high-priority side stream beside the render kernels of the current one) or "one_stream" (same work, serial order; used
+    for per-stage timing, where a kernel's own duration is wanted)."""
+    if pipeline not in ("two_stream", "one_stream"):
+        raise ValueError(f"unknown pipeline {pipeline!r}")
     dev = params["means3D"].device
     e = torch.empty(0, device=dev)
     results = []
     has_split = hasattr(backend, "forward_geom")
 
-    side = _geom_stream(dev) if hasattr(backend, "forward_bin") else None
+    side = _geom_stream(dev) if (pipeline == "two_stream" and hasattr(backend, "forward_bin")) else None
 
     def geom_pass(v, stream=None):
         cam = cameras[v]
@@ -118,14 +120,12 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
         ahead = {}
         if n:
             g0 = geom_pass(view_ids[0])
-            if n > 1 and _START_OVERLAP:
+            if n > 1:
                 # step start: nothing runs beside view 0's front yet, so view 1's geometry half goes on a second side stream
                 # next to it (two latency-bound fronts overlap well); enqueued before the host blocks on view 0's num_rendered
                 side2 = _geom_stream(dev, 1)
                 ahead[1] = geom_pass(view_ids[1], stream=side2)
             ahead[0] = bin_pass(g0)
-            if n > 1 and not _START_OVERLAP:
-                ahead[1] = geom_pass(view_ids[1])
     else:
         # software pipeline over the views: the first half of view i+1 (preprocess, depth sort, prefix sum) is enqueued BEFORE
         # the backward of view i, so its num_rendered is on the host long before it is needed and the device never waits for
@@ -160,17 +160,11 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
 _geom_streams = {}
 
 
-_START_OVERLAP = os.environ.get("RAIN_START_OVERLAP", "1") == "1"
-
-
 def _geom_stream(dev, which=0):
-    """The high-priority side stream of the two-stream view pipeline (render_views_fwd_bwd); RAIN_GEOM_STREAM=0 turns the
-    pipeline back into the one-stream order (one B200, 8 views of 1M Gaussians at 1080p: 1.263 -> 1.173 ms per view)."""
-    if os.environ.get("RAIN_GEOM_STREAM", "1") != "1":
-        return None
+    """The high-priority side streams of the two-stream view pipeline (render_views_fwd_bwd)."""
     key = (torch.device(dev).index, which)
     if key not in _geom_streams:
-        _geom_streams[key] = torch.cuda.Stream(device=dev, priority=int(os.environ.get('RAIN_GEOM_PRIO', '-1')))
+        _geom_streams[key] = torch.cuda.Stream(device=dev, priority=-1)
     return _geom_streams[key]
 
 
@@ -213,6 +207,8 @@ class HostFeed:
 def allreduce_bucket(bucket: GradientBucket, group=None, average: bool = False):
     """The single collective of a step: sum (or mean) of the flat bucket over all ranks, in place."""
     import torch.distributed as dist
+    if group == "skip":          # a single-rank step inside an initialised process group (tools/verify_multigpu.py)
+        return bucket
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(bucket.flat, op=dist.ReduceOp.SUM, group=group)
         if average:

@@ -67,3 +67,37 @@ def add_densification_stats(radii, dL_dmean2D, max_radii2D, xyz_gradient_accum, 
     with torch.cuda.device(radii.device):
         _lib.check(lib.rr_densify_stats(torch.cuda.current_stream().cuda_stream, P, radii.data_ptr(), dL_dmean2D.data_ptr(), max_radii2D.data_ptr(),
                                         xyz_gradient_accum.data_ptr(), denom.data_ptr()), "rr_densify_stats")
+
+
+class DensificationStats:
+    """Multi-GPU-consistent densification statistics (SURVEY.md 8(e) "caveat for callers", 8(f) rank 3): the three per-Gaussian
+    statistics of GaussianModel (scene/gaussian_model.py:419-421, train.py:132-134) kept identical on every replica of a
+    view-sharded step.  They are per view and non-linear (a norm, a max), so they cannot be derived from the all-reduced
+    gradients: each rank folds its views into a per-step DELTA (``add_view``), and ``sync`` combines the deltas across ranks —
+    ONE sum all-reduce over [xyz_gradient_accum | denom] (2P floats) and ONE max all-reduce over max_radii2D (P floats) —
+    and folds them into the replicated totals.  With one rank ``sync`` only folds."""
+
+    def __init__(self, P, device):
+        f = dict(dtype=torch.float32, device=device)
+        self.P = int(P)
+        self.max_radii2D = torch.zeros(self.P, **f)
+        self.xyz_gradient_accum = torch.zeros(self.P, 1, **f)
+        self.denom = torch.zeros(self.P, 1, **f)
+        self._sum = torch.zeros(2 * self.P, **f)          # [delta of xyz_gradient_accum | delta of denom]
+        self._max = torch.zeros(self.P, **f)              # max of radii over this rank's views of the step
+
+    def add_view(self, radii, dL_dmean2D):
+        """fold one rendered view (its radii and viewspace_points.grad) into this rank's delta of the step"""
+        add_densification_stats(radii, dL_dmean2D, self._max, self._sum[:self.P], self._sum[self.P:])
+
+    def sync(self, group=None):
+        """combine the step's deltas across the ranks of ``group`` and fold them into the replicated statistics"""
+        import torch.distributed as dist
+        if group != "skip" and dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+            dist.all_reduce(self._sum, op=dist.ReduceOp.SUM, group=group)
+            dist.all_reduce(self._max, op=dist.ReduceOp.MAX, group=group)
+        self.xyz_gradient_accum.view(-1).add_(self._sum[:self.P])
+        self.denom.view(-1).add_(self._sum[self.P:])
+        torch.maximum(self.max_radii2D, self._max, out=self.max_radii2D)
+        self._sum.zero_()
+        self._max.zero_()

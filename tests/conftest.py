@@ -10,6 +10,12 @@ if ROOT not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    # test infrastructure: RAIN_TEST_LIB points this test process at another build of the library (the cross-check build,
+    # rain_b200/librainrast_xc.so); the product never reads it
+    alt = os.environ.get("RAIN_TEST_LIB")
+    if alt:
+        from rain_b200 import _lib
+        _lib.LIB_PATH = alt
 
 
 @pytest.fixture(scope="session")

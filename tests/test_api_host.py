@@ -2,6 +2,7 @@
 keyword arguments and error behaviour as submodules/diff_gaussian_rasterization/diff_gaussian_rasterization/__init__.py
 and simple_knn._C of sharonal10/rain.  No kernel runs here."""
 import inspect
+import os
 
 import pytest
 import torch
@@ -91,3 +92,31 @@ def test_synthetic_camera_matches_reference_conventions():
     assert abs(cam.tanfovx / cam.tanfovy - 64 / 48) < 1e-6
     hom = torch.tensor([0.3, -0.2, 0.1, 1.0]) @ cam.projmatrix
     assert hom[3] > 0
+
+
+def test_unmodified_reference_callers_import_on_top_of_the_dropin_modules():
+    """SURVEY.md 8(b) last row, host half: the reference's unmodified gaussian_renderer/__init__.py and scene/gaussian_model.py
+    (staged verbatim into oracle/_ref/refpy by `make -f oracle/Makefile ref`) import with this repository first on sys.path,
+    and their `submodules.diff_gaussian_rasterization.diff_gaussian_rasterization` / `simple_knn._C` imports resolve to this
+    repository.  (The GPU half, tests/test_reference_callers.py, runs render() and create_from_pcd through them.)"""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    refpy = os.path.join(root, "oracle", "_ref", "refpy")
+    if not os.path.isdir(os.path.join(refpy, "gaussian_renderer")):
+        pytest.skip("oracle/_ref/refpy not staged (needs /root/reference at build time)")
+    code = (
+        "import sys, os, inspect\n"
+        f"sys.path[:0] = [{root!r}, {refpy!r}, {os.path.join(root, 'tests', 'stubs')!r}]\n"
+        "import gaussian_renderer\n"
+        "from scene.gaussian_model import GaussianModel, distCUDA2\n"
+        "from gaussian_renderer import GaussianRasterizationSettings, GaussianRasterizer\n"
+        "import rain_b200\n"
+        "assert GaussianRasterizer is rain_b200.GaussianRasterizer and GaussianRasterizationSettings is rain_b200.GaussianRasterizationSettings\n"
+        "assert distCUDA2 is rain_b200.distCUDA2\n"
+        f"assert os.path.abspath(gaussian_renderer.__file__).startswith({refpy!r})\n"
+        "assert list(inspect.signature(gaussian_renderer.render).parameters)[:4] == ['viewpoint_camera', 'pc', 'pipe', 'bg_color']\n"
+        "GaussianModel(3, 0.8)\n"
+        "print('ok')\n")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, cwd=root)
+    assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stderr[-2000:]

@@ -129,3 +129,35 @@ def test_two_ranks_allreduce_equals_single_rank_sum(tmp_path, V):
     for k in mv.SEGMENTS:
         ref.views[k].copy_(expected_sum(P, range(V), k).view(P, *([1] * (ref.views[k].dim() - 1))).expand_as(ref.views[k]))
     assert torch.equal(outs[0]["flat"], ref.flat)                                  # == the sum over ALL views (a rank with no view adds zeros)
+
+
+def _stats_worker(rank, world, port, P, out_dir):
+    from rain_b200.optim import DensificationStats
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        st = DensificationStats(P, "cpu")
+        st.max_radii2D.fill_(3.0); st.xyz_gradient_accum.fill_(1.0); st.denom.fill_(2.0)      # replicated totals of earlier steps
+        idx = torch.arange(P, dtype=torch.float32)
+        # this rank's delta of the step (what add_view's kernel leaves behind; the kernel itself needs a GPU)
+        st._sum[:P] = (rank + 1) * idx; st._sum[P:] = float(rank + 1); st._max.copy_(idx * (1 + rank) % 7)
+        st.sync()
+        assert not st._sum.any() and not st._max.any()                                        # deltas are consumed
+        torch.save(dict(m=st.max_radii2D, a=st.xyz_gradient_accum, d=st.denom), os.path.join(out_dir, f"s{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_densification_stats_are_summed_and_maxed_across_ranks(tmp_path):
+    """scene/gaussian_model.py:419-421 over a view-sharded step: xyz_gradient_accum / denom are sums over ALL ranks' views,
+    max_radii2D the max, and every replica ends up with the same totals (SURVEY.md 8(e) caveat)."""
+    P, world = 9, 2
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    mp.spawn(_stats_worker, args=(world, port, P, str(tmp_path)), nprocs=world, join=True)
+    a, b = (torch.load(os.path.join(str(tmp_path), f"s{r}.pt")) for r in range(world))
+    for k in "mad":
+        assert torch.equal(a[k], b[k])
+    idx = torch.arange(P, dtype=torch.float32)
+    assert torch.equal(a["a"].view(-1), 1.0 + 3 * idx) and torch.equal(a["d"].view(-1), torch.full((P,), 5.0))
+    assert torch.equal(a["m"], torch.maximum(torch.full((P,), 3.0), torch.maximum(idx % 7, idx * 2 % 7)))

@@ -1,0 +1,81 @@
+"""Hardware check of the view-sharded multi-GPU step: V views are rendered sharded over the ranks
+(one process per GPU, NCCL), the gradient bucket is all-reduced, and rank 0 also accumulates ALL V views alone; the two
+buckets must agree (1e-5 of max per segment), every replica must hold the same bits after the all-reduce, and the
+densification statistics combined across ranks (rain_b200.optim.DensificationStats.sync) must equal the single-rank ones.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/verify_multigpu.py [P W H V]
+
+Prints one JSON line on rank 0 and exits non-zero on any mismatch."""
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+from rain_b200 import multiview as mv  # noqa: E402
+from rain_b200.optim import DensificationStats  # noqa: E402
+from rain_b200.synthetic import make_camera, make_grad, make_scene  # noqa: E402
+
+
+def rel(a, b):
+    s = b.abs().max().item()
+    return (a - b).abs().max().item() / (s if s > 0 else 1.0)
+
+
+def main():
+    P, W, H, V = (int(x) for x in (sys.argv[1:5] if len(sys.argv) >= 5 else (30000, 160, 96, 8)))
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    D = 3
+    sc = make_scene(P, D, 8).to(dev)
+    cams = [make_camera(v, V, W, H).to(dev) for v in range(V)]
+    bg = torch.zeros(3, device=dev)
+    dp = [make_grad(W, H, 20 + v).to(dev) for v in range(V)]
+    params = dict(means3D=sc.means3D, opacities=sc.opacities, shs=sc.shs, scales=sc.scales, rotations=sc.rotations)
+
+    def step(r, w):
+        bucket = mv.GradientBucket(P, 16, dev)
+        bucket.flat.fill_(float("nan"))
+        stats = DensificationStats(P, dev)
+        res = mv.train_step_views(params, cams, V, bucket, lambda v, c, d: dp[v], rank=r, world_size=w, bg=bg, sh_degree=D,
+                                  group=None if w > 1 else "skip")
+        for x in res:
+            stats.add_view(x.radii, x.dL_dmeans2D)
+        return bucket, stats, res
+
+    bucket, stats, res = step(rank, world)
+    stats.sync()
+    torch.cuda.synchronize()
+    # replicas agree bit for bit after the all-reduce
+    lo, hi = bucket.flat.clone(), bucket.flat.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    same_bits = bool(torch.equal(lo, hi)) and bool(torch.isfinite(lo).all())
+    ok, report = same_bits, {"world": world, "P": P, "views": V, "replicas_bit_identical": same_bits, "views_per_rank": len(res)}
+    if rank == 0:
+        alone, stats1, _ = step(0, 1)             # all V views on this rank, no collective
+        stats1.sync("skip")
+        for k in mv.SEGMENTS:
+            e = rel(bucket.views[k], alone.views[k])
+            report[f"rel_err_{k}"] = e
+            ok = ok and e <= 1e-5
+        for k in ("max_radii2D", "xyz_gradient_accum", "denom"):
+            e = rel(getattr(stats, k), getattr(stats1, k))
+            report[f"rel_err_{k}"] = e
+            ok = ok and e <= (0.0 if k != "xyz_gradient_accum" else 1e-6)
+        report["ok"] = ok
+        print(json.dumps(report), flush=True)
+    flag = torch.tensor([0 if ok else 1], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+    dist.destroy_process_group()
+    sys.exit(int(flag.item()))
+
+
+if __name__ == "__main__":
+    main()
