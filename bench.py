@@ -306,8 +306,8 @@ def run_ours(args, rank, world, local):
 
     # ---------------- drop-in arm: one view at a time through the reference's own Python API ----------------
     dropin = None
-    if world == 1 and rank == 0:
-        dropin = run_dropin(cfg, sc, cams_d, targets_d, bg, dev, iters=max(50, args.steps), warm=10)
+    if world == 1 and rank == 0 and args.dropin_iters > 0:
+        dropin = run_dropin(cfg, sc, cams_d, targets_d, bg, dev, iters=args.dropin_iters, warm=10)
 
     if rank != 0:
         return None
@@ -451,6 +451,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C3", choices=["C1", "C2", "C3", "C4"])
     ap.add_argument("--cpu-renders", type=int, default=2, help="renders of the workload timed on the host for cpu_baseline (0 = skip)")
+    ap.add_argument("--dropin-iters", type=int, default=50, help="timed single-view iterations of the drop-in arm at N = 1 (0 = skip, e.g. under a profiler)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
