@@ -28,6 +28,7 @@ extern "C" {
 #endif
 
 #define RR_BWD_ACCUMULATE 1
+#define RR_BWD_LEAF 2        /* rr_backward_views: inputs are the raw leaf tensors, gradients w.r.t. them */
 
 const char* rr_last_error(void);
 int rr_version(void);
@@ -98,6 +99,33 @@ int rr_backward(void* stream, int P, int D, int M, int W, int H, int64_t N, cons
 	float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
 	float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
 	int debug, int flags);
+
+/* ---- view-batched backward (multi-view steps; no reference counterpart: the reference runs its whole backward once per view) ----
+ * rr_backward_render is the first half of rr_backward alone — BACKWARD::render (rasterizer_impl.cu:386-404, backward.cu:389-547):
+ * it zero-fills ws (rr_backward_ws_bytes(P)) and leaves there, per Gaussian, the 48-byte accumulator record of this view
+ * (colour gradient and the moments of G * dL_dalpha over the pixels that blended it).
+ * rr_backward_views is the second half — computeCov2DCUDA + preprocessCUDA backward (backward.cu:133-386) — for ALL nviews
+ * views of a step in ONE pass over the Gaussians: every array argument up to dL_dmean2D is a HOST array of nviews entries
+ * (device pointers, resp. floats); geom[v] / radii[v] / grad_acc[v] are view v's geometry blob, radii and the ws its
+ * rr_backward_render filled (all views share P, W, H, D, scale_modifier, low_pass).  Parameters are read once, the bucket row
+ * (59 floats per Gaussian with M = 16, the only supported M) is written once — overwritten, or added with RR_BWD_ACCUMULATE
+ * (rows no view touched are then left alone) — and dL_dmean2D[v] ([P,3] per view; the array or single entries may be null)
+ * receives each view's viewspace gradient.  stat_*: optional (all or none) f32[P] densification statistics updated in place
+ * for every view that saw the Gaussian (train.py:132-134, scene/gaussian_model.py:419-421).
+ *   flags without RR_BWD_LEAF: shs_or_f_dc = shs[P,16,3], f_rest = null, scales / rotations activated; gradients w.r.t. them:
+ *       dL_dmean3D[P,3], dL_dsh_or_f_dc = dL_dsh[P,16,3], dL_dopacity[P], dL_dscale[P,3], dL_drot[P,4]
+ *   with RR_BWD_LEAF: means3D = _xyz, shs_or_f_dc = _features_dc[P,1,3], f_rest = _features_rest[P,15,3], scales = _scaling (log),
+ *       rotations = _rotation (un-normalised) — the raw leaves of scene/gaussian_model.py:131-136; the activations of :85-105 and
+ *       their chain rule are applied inside; outputs dL_dxyz, dL_df_dc[P,3], dL_df_rest[P,45], dL_dopacity (raw), dL_dscaling, dL_drotation */
+int rr_backward_render(void* stream, int P, int W, int H, int64_t N, const float* background,
+	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes,
+	const float* dL_dpix, void* ws, size_t ws_bytes, int debug);
+int rr_backward_views(void* stream, int P, int D, int M, int W, int H, int nviews,
+	const float* const* viewmatrix, const float* const* projmatrix, const float* const* campos, const float* tan_fovx, const float* tan_fovy,
+	const int* const* radii, void* const* geom, const float* const* grad_acc, float* const* dL_dmean2D,
+	const float* means3D, const float* shs_or_f_dc, const float* f_rest, const float* scales, float scale_modifier, const float* rotations, float low_pass,
+	float* dL_dmean3D, float* dL_dsh_or_f_dc, float* dL_df_rest, float* dL_dopacity, float* dL_dscale, float* dL_drot,
+	float* stat_max_radii2D, float* stat_grad_accum, float* stat_denom, int flags, int debug);
 
 /* Self test of the packed exponential the render kernels use (exp2x, csrc/render_common.cuh) against libdevice expf —
  * the function the reference's forward.cu:336 / backward.cu:488 compile to — over the float bit patterns

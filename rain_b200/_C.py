@@ -236,6 +236,71 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     return out + (dL_dconic,) if return_conic else out
 
 
+def backward_render(background, dL_dout_color, geomBuffer, R, binningBuffer, imageBuffer, P, debug=False):
+    """First half of the backward alone (rr_backward_render: BACKWARD::render, rasterizer_impl.cu:386-404): returns the
+    per-Gaussian accumulator blob of this view, which ``backward_views`` consumes together with those of the step's other
+    views.  No reference counterpart as a separate op (the reference runs its whole backward per view)."""
+    lib = _lib.load()
+    dev = dL_dout_color.device
+    H, W = dL_dout_color.size(1), dL_dout_color.size(2)
+    ws = torch.empty(lib.rr_backward_ws_bytes(P), dtype=torch.uint8, device=dev)
+    if P != 0:
+        bg, dpix = _f32c(background, dev), _f32c(dL_dout_color, dev)
+        with torch.cuda.device(dev):
+            _lib.check(lib.rr_backward_render(torch.cuda.current_stream().cuda_stream, P, W, H, int(R), _ptr(bg),
+                                              geomBuffer.data_ptr(), geomBuffer.numel(), binningBuffer.data_ptr(), binningBuffer.numel(),
+                                              imageBuffer.data_ptr(), imageBuffer.numel(), dpix.data_ptr(), ws.data_ptr(), ws.numel(), int(bool(debug))), "rr_backward_render")
+    return ws
+
+
+def backward_views(views, means3D, sh, scales, rotations, scale_modifier, low_pass, degree, image_height, image_width, grads_out,
+                   accumulate=False, stats=None, leaf=False, f_rest=None, debug=False):
+    """Second half of the backward for ALL views of a batch in one pass over the Gaussians (rr_backward_views).
+    views: list of dicts with viewmatrix, projmatrix, campos (device tensors), tanfovx, tanfovy (floats), radii (i32[P]), geom (the
+    view's geometry blob), acc (the blob ``backward_render`` returned) and optionally dL_dmean2D (f32[P,3], written).
+    grads_out: the gradient bucket's segments — activated layout dict(means3D, sh, opacity, scales, rotations), or with
+    ``leaf=True`` dict(xyz, f_dc, f_rest, opacity, scaling, rotation); then means3D / sh / scales / rotations are the raw leaves
+    _xyz / _features_dc / _scaling / _rotation and ``f_rest`` is _features_rest (scene/gaussian_model.py:131-136).
+    stats: optional (max_radii2D, xyz_gradient_accum, denom) f32[P] tensors updated in place."""
+    import ctypes
+    lib = _lib.load()
+    dev = means3D.device
+    P, n = means3D.size(0), len(views)
+    if P == 0 or n == 0:
+        return
+    M = 16
+    if (leaf and (sh.numel() != P * 3 or f_rest is None or f_rest.numel() != P * 45)) or (not leaf and sh.numel() != P * 48):
+        raise RuntimeError("backward_views needs 16 SH coefficients per Gaussian")
+    keep = [_f32c(t, dev) for t in (means3D, sh, scales, rotations)] + ([_f32c(f_rest, dev)] if leaf else [])
+    names = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation") if leaf else ("means3D", "sh", "opacity", "scales", "rotations")
+    sizes = dict(xyz=3, means3D=3, f_dc=3, f_rest=45, sh=48, opacity=1, scaling=3, scales=3, rotation=4, rotations=4)
+    for k in names:
+        t = grads_out.get(k)
+        if t is None or t.dtype != torch.float32 or t.device != dev or not t.is_contiguous() or t.numel() != P * sizes[k]:
+            raise RuntimeError(f"grads_out[{k!r}] must be a contiguous float32 tensor of {P * sizes[k]} elements on {dev}")
+    vp = ctypes.c_void_p
+    arr = lambda xs: (vp * n)(*xs)
+    mats = [[_f32c(v[k], dev) for k in ("viewmatrix", "projmatrix", "campos")] for v in views]
+    radii = [v["radii"].contiguous() for v in views]
+    d2 = [v.get("dL_dmean2D") for v in views]
+    for t in d2:
+        if t is not None and (t.dtype != torch.float32 or not t.is_contiguous() or t.numel() != 3 * P):
+            raise RuntimeError("dL_dmean2D must be a contiguous float32 [P,3] tensor")
+    st = stats or (None, None, None)
+    g = grads_out
+    with torch.cuda.device(dev):
+        _lib.check(lib.rr_backward_views(
+            torch.cuda.current_stream().cuda_stream, P, int(degree), M, int(image_width), int(image_height), n,
+            arr([m[0].data_ptr() for m in mats]), arr([m[1].data_ptr() for m in mats]), arr([m[2].data_ptr() for m in mats]),
+            (ctypes.c_float * n)(*[float(v["tanfovx"]) for v in views]), (ctypes.c_float * n)(*[float(v["tanfovy"]) for v in views]),
+            arr([r.data_ptr() for r in radii]), arr([v["geom"].data_ptr() for v in views]), arr([v["acc"].data_ptr() for v in views]),
+            arr([t.data_ptr() if t is not None else None for t in d2]),
+            keep[0].data_ptr(), keep[1].data_ptr(), keep[4].data_ptr() if leaf else None, keep[2].data_ptr(), float(scale_modifier), keep[3].data_ptr(), float(low_pass),
+            g[names[0]].data_ptr(), g[names[1]].data_ptr(), g["f_rest"].data_ptr() if leaf else None,
+            g["opacity"].data_ptr(), g["scaling" if leaf else "scales"].data_ptr(), g["rotation" if leaf else "rotations"].data_ptr(),
+            _ptr(st[0]), _ptr(st[1]), _ptr(st[2]), (1 if accumulate else 0) | (2 if leaf else 0), int(bool(debug))), "rr_backward_views")
+
+
 def mark_visible(means3D, viewmatrix, projmatrix):
     """markVisible (rasterize_points.cu:193-212): bool[P], view-space z > 0.2."""
     lib = _lib.load()

@@ -48,6 +48,15 @@ SIGNATURES = {
                          _vp, _vp, _vp, _vp,
                          _vp, _vp, _vp, _vp, _vp,
                          _i, _i]),
+    "rr_backward_render": (_i, [_vp, _i, _i, _i, _i64, _vp,
+                                _vp, _sz, _vp, _sz, _vp, _sz,
+                                _vp, _vp, _sz, _i]),
+    "rr_backward_views": (_i, [_vp, _i, _i, _i, _i, _i, _i,
+                               _vp, _vp, _vp, _vp, _vp,
+                               _vp, _vp, _vp, _vp,
+                               _vp, _vp, _vp, _vp, _f, _vp, _f,
+                               _vp, _vp, _vp, _vp, _vp, _vp,
+                               _vp, _vp, _vp, _i, _i]),
     "rr_mark_visible": (_i, [_vp, _i, _vp, _vp, _vp, _vp]),
     "rr_selftest_exp": (_i, [_vp, _c.c_uint32, _c.c_uint32, _vp]),
     "rr_loss_ws_bytes": (_sz, [_i, _i, _i]),

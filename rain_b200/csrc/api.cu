@@ -52,9 +52,9 @@ namespace {
 
 // ---- per-stage device timing (CUDA events on the caller's stream), off by default; used by bench.py -----------------
 enum StageId { ST_PREPROCESS = 0, ST_DEPTH_SORT, ST_SCAN, ST_DUPLICATE, ST_TILE_SORT, ST_RANGES, ST_RENDER_FWD,
-	ST_RENDER_BWD, ST_PREPROCESS_BWD, ST_DIST2, ST_COUNT };
+	ST_RENDER_BWD, ST_PREPROCESS_BWD, ST_BACKWARD_VIEWS, ST_DIST2, ST_COUNT };
 const char* const kStageNames[ST_COUNT] = { "preprocess_fwd", "depth_sort", "scan", "duplicate", "tile_sort", "ranges",
-	"render_fwd", "render_bwd", "preprocess_bwd", "dist2" };
+	"render_fwd", "render_bwd", "preprocess_bwd", "backward_views", "dist2" };
 struct Pending { int stage; cudaEvent_t a, b; };
 struct Prof {
 	std::mutex mu;
@@ -326,6 +326,40 @@ int rr_forward_raster(void* stream, int P, int W, int H, int64_t N, const float*
 	return rr_forward_render(stream, P, W, H, N, background, geom, geom_bytes, binning, binning_bytes, image, image_bytes, out_color, out_depth, debug);
 }
 
+// B1: zero the per-Gaussian accumulators and run the backward tile renderer (shared by rr_backward and rr_backward_render)
+static int backward_render_impl(cudaStream_t stream, int P, int W, int H, int64_t N, const float* background,
+	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes,
+	const float* dL_dpix, void* ws, size_t ws_bytes, int debug)
+{
+	const GeomLayout G = geom_layout(geom, P);
+	const BinLayout B = bin_layout(binning, N, W, H);
+	const ImgLayout I = img_layout(image, W, H);
+	if (G.total > geom_bytes || B.total > binning_bytes || I.total > image_bytes || rr_backward_ws_bytes(P) > ws_bytes + 256) { set_error("scratch blob too small"); return -1; }
+	float* grad_acc = reinterpret_cast<float*>(ws);
+	RenderArgs r; memset(&r, 0, sizeof(r));
+	r.W = W; r.H = H; r.grid_x = (W + TILE_X - 1) / TILE_X; r.grid_y = (H + TILE_Y - 1) / TILE_Y;
+	r.ranges = I.ranges; r.rec = G.rec; r.point_list = B.point_list; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.warp_flags = B.warp_flags;
+	r.dL_dpix = dL_dpix; r.grad_acc = grad_acc; r.xc = XC_COUNTERS;
+	// the accumulators start from zero (the fill is part of the render_bwd stage time)
+	Stage st(stream, ST_RENDER_BWD);
+	cudaMemsetAsync(grad_acc, 0, (size_t)P * ACC_FLOATS * sizeof(float), stream);
+	if (N > 0 && launch_render_bwd(stream, r)) return -1;
+	if (debug && check_launch("render_bwd", stream, true)) return -1;
+	return 0;
+}
+
+int rr_backward_render(void* stream_, int P, int W, int H, int64_t N, const float* background,
+	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes,
+	const float* dL_dpix, void* ws, size_t ws_bytes, int debug)
+{
+	cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+	if (P == 0) return 0;
+	if (bad_ptr(background, "background") || bad_ptr(geom, "geom") || bad_ptr(binning, "binning") || bad_ptr(image, "image") ||
+		bad_ptr(dL_dpix, "dL_dpix") || bad_ptr(ws, "ws")) return -1;
+	if (backward_render_impl(stream, P, W, H, N, background, geom, geom_bytes, binning, binning_bytes, image, image_bytes, dL_dpix, ws, ws_bytes, debug)) return -1;
+	return check_launch("backward_render", stream, debug != 0);
+}
+
 int rr_backward(void* stream_, int P, int D, int M, int W, int H, int64_t N, const float* background,
 	const float* means3D, const float* shs, const float* colors_precomp,
 	const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
@@ -347,24 +381,8 @@ int rr_backward(void* stream_, int P, int D, int M, int W, int H, int64_t N, con
 	if (!use_sh && bad_ptr(dL_dcolor, "dL_dcolor")) return -1;
 	if (cov3D_precomp && bad_ptr(dL_dcov3D, "dL_dcov3D")) return -1;
 	if (use_sh && bad_ptr(dL_dsh, "dL_dsh")) return -1;
+	if (backward_render_impl(stream, P, W, H, N, background, geom, geom_bytes, binning, binning_bytes, image, image_bytes, dL_dpix, ws, ws_bytes, debug)) return -1;
 	const GeomLayout G = geom_layout(geom, P);
-	const BinLayout B = bin_layout(binning, N, W, H);
-	const ImgLayout I = img_layout(image, W, H);
-	if (G.total > geom_bytes || B.total > binning_bytes || I.total > image_bytes || rr_backward_ws_bytes(P) > ws_bytes + 256) { set_error("scratch blob too small"); return -1; }
-	const int grid_x = (W + TILE_X - 1) / TILE_X, grid_y = (H + TILE_Y - 1) / TILE_Y;
-	float* grad_acc = reinterpret_cast<float*>(ws);
-
-	RenderArgs r; memset(&r, 0, sizeof(r));
-	r.W = W; r.H = H; r.grid_x = grid_x; r.grid_y = grid_y;
-	r.ranges = I.ranges; r.rec = G.rec; r.point_list = B.point_list; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.warp_flags = B.warp_flags;
-	r.dL_dpix = dL_dpix; r.grad_acc = grad_acc; r.xc = XC_COUNTERS;
-	{
-		// the accumulators start from zero (the fill is part of the render_bwd stage time)
-		Stage st(stream, ST_RENDER_BWD);
-		cudaMemsetAsync(grad_acc, 0, (size_t)P * ACC_FLOATS * sizeof(float), stream);
-		if (N > 0 && launch_render_bwd(stream, r)) return -1;
-		if (debug && check_launch("render_bwd", stream, true)) return -1;
-	}
 
 	PreprocessBwdArgs a; memset(&a, 0, sizeof(a));
 	a.P = P; a.D = D; a.M = M; a.W = W; a.H = H;
@@ -373,11 +391,53 @@ int rr_backward(void* stream_, int P, int D, int M, int W, int H, int64_t N, con
 	a.means3D = means3D; a.scales = cov3D_precomp ? nullptr : scales; a.rotations = cov3D_precomp ? nullptr : rotations;
 	a.shs = use_sh ? shs : nullptr; a.cov3D = cov3D_precomp ? cov3D_precomp : G.cov3D;        // rasterizer_impl.cu:406
 	a.view = viewmatrix; a.proj = projmatrix; a.campos = campos; a.has_colors_precomp = colors_precomp != nullptr; a.accumulate = (flags & RR_BWD_ACCUMULATE) ? 1 : 0;
-	a.radii = radii; a.clamped = G.clamped; a.rec = G.rec; a.grad_acc = grad_acc;
+	a.radii = radii; a.clamped = G.clamped; a.rec = G.rec; a.grad_acc = reinterpret_cast<const float*>(ws);
 	a.dL_dmean2D = dL_dmean2D; a.dL_dconic = dL_dconic; a.dL_dopacity = dL_dopacity; a.dL_dcolor = dL_dcolor; a.dL_dmean3D = dL_dmean3D;
 	a.dL_dcov3D = dL_dcov3D; a.dL_dsh = dL_dsh; a.dL_dscale = dL_dscale; a.dL_drot = dL_drot;
 	{ Stage st(stream, ST_PREPROCESS_BWD); if (launch_preprocess_bwd(stream, a)) return -1; }
 	return check_launch("backward", stream, debug != 0);
+}
+
+int rr_backward_views(void* stream_, int P, int D, int M, int W, int H, int nviews,
+	const float* const* viewmatrix, const float* const* projmatrix, const float* const* campos, const float* tan_fovx, const float* tan_fovy,
+	const int* const* radii, void* const* geom, const float* const* grad_acc, float* const* dL_dmean2D,
+	const float* means3D, const float* shs_or_f_dc, const float* f_rest, const float* scales, float scale_modifier, const float* rotations, float low_pass,
+	float* dL_dmean3D, float* dL_dsh_or_f_dc, float* dL_df_rest, float* dL_dopacity, float* dL_dscale, float* dL_drot,
+	float* stat_max_radii2D, float* stat_grad_accum, float* stat_denom, int flags, int debug)
+{
+	cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+	if (P == 0 || nviews == 0) return 0;
+	if (P < 0 || nviews < 0 || W <= 0 || H <= 0) { set_error("bad sizes P=%d nviews=%d W=%d H=%d", P, nviews, W, H); return -1; }
+	const bool leaf = (flags & RR_BWD_LEAF) != 0;
+	if (M != 16 || D < 0 || D > 3) { set_error("rr_backward_views needs M = 16 SH coefficients and degree 0..3 (M=%d, D=%d)", M, D); return -1; }
+	if (bad_ptr(viewmatrix, "viewmatrix") || bad_ptr(projmatrix, "projmatrix") || bad_ptr(campos, "campos") || bad_ptr(tan_fovx, "tan_fovx") ||
+		bad_ptr(tan_fovy, "tan_fovy") || bad_ptr(radii, "radii") || bad_ptr(geom, "geom") || bad_ptr(grad_acc, "grad_acc") ||
+		bad_ptr(means3D, "means3D") || bad_ptr(shs_or_f_dc, leaf ? "f_dc" : "shs") || bad_ptr(scales, "scales") || bad_ptr(rotations, "rotations") ||
+		bad_ptr(dL_dmean3D, "dL_dmean3D") || bad_ptr(dL_dsh_or_f_dc, "dL_dsh") || bad_ptr(dL_dopacity, "dL_dopacity") || bad_ptr(dL_dscale, "dL_dscale") ||
+		bad_ptr(dL_drot, "dL_drot")) return -1;
+	if (leaf && (bad_ptr(f_rest, "f_rest") || bad_ptr(dL_df_rest, "dL_df_rest"))) return -1;
+	if ((stat_max_radii2D || stat_grad_accum || stat_denom) && !(stat_max_radii2D && stat_grad_accum && stat_denom)) { set_error("pass all three statistics or none"); return -1; }
+	Stage st(stream, ST_BACKWARD_VIEWS);
+	for (int v0 = 0; v0 < nviews; v0 += BV_MAX_VIEWS) {
+		BackwardViewsArgs a; memset(&a, 0, sizeof(a));
+		a.P = P; a.D = D; a.M = M; a.W = W; a.H = H; a.nviews = nviews - v0 < BV_MAX_VIEWS ? nviews - v0 : BV_MAX_VIEWS;
+		a.scale_modifier = scale_modifier; a.low_pass = low_pass; a.leaf = leaf ? 1 : 0;
+		a.accumulate = ((flags & RR_BWD_ACCUMULATE) || v0 > 0) ? 1 : 0;      // later chunks of a long batch add to the first one's rows
+		a.means3D = means3D; a.scales = scales; a.rotations = rotations; a.shs = leaf ? nullptr : shs_or_f_dc; a.f_dc = leaf ? shs_or_f_dc : nullptr; a.f_rest = f_rest;
+		for (int j = 0; j < a.nviews; j++) {
+			const int v = v0 + j;
+			if (bad_ptr(viewmatrix[v], "viewmatrix[v]") || bad_ptr(projmatrix[v], "projmatrix[v]") || bad_ptr(campos[v], "campos[v]") || bad_ptr(radii[v], "radii[v]") ||
+				bad_ptr(geom[v], "geom[v]") || bad_ptr(grad_acc[v], "grad_acc[v]")) return -1;
+			const GeomLayout G = geom_layout(geom[v], P);
+			a.view[j] = viewmatrix[v]; a.proj[j] = projmatrix[v]; a.campos[j] = campos[v]; a.tan_fovx[j] = tan_fovx[v]; a.tan_fovy[j] = tan_fovy[v];
+			a.radii[j] = radii[v]; a.rec[j] = G.rec; a.clamped[j] = G.clamped; a.grad_acc[j] = grad_acc[v];
+			a.dL_dmean2D[j] = dL_dmean2D ? dL_dmean2D[v] : nullptr;
+		}
+		a.dL_dmean3D = dL_dmean3D; a.dL_dsh = dL_dsh_or_f_dc; a.dL_dfrest = dL_df_rest; a.dL_dopacity = dL_dopacity; a.dL_dscale = dL_dscale; a.dL_drot = dL_drot;
+		a.stat_max_radii = stat_max_radii2D; a.stat_grad_accum = stat_grad_accum; a.stat_denom = stat_denom;
+		if (launch_backward_views(stream, a)) return -1;
+	}
+	return check_launch("backward_views", stream, debug != 0);
 }
 
 #ifdef RR_CROSSCHECK

@@ -78,6 +78,25 @@ struct PreprocessBwdArgs {
 };
 int launch_preprocess_bwd(cudaStream_t, const PreprocessBwdArgs&);
 
+// view-batched backward (preprocess_bwd.cu): the per-Gaussian half of the backward for up to BV_MAX_VIEWS views in one pass
+constexpr int BV_MAX_VIEWS = 16;
+struct BackwardViewsArgs {
+	int P, D, M, W, H, nviews;
+	float scale_modifier, low_pass;
+	int accumulate;           // 1: += into the bucket, rows no view of this batch touched are left alone
+	int leaf;                 // 1: inputs are the raw leaf tensors, gradients w.r.t. them (see the kernel's header)
+	const float *means3D, *scales, *rotations, *shs /*[P,16,3], leaf = 0*/, *f_dc /*[P,1,3]*/, *f_rest /*[P,15,3], leaf = 1*/;
+	// per view
+	const float* view[BV_MAX_VIEWS]; const float* proj[BV_MAX_VIEWS]; const float* campos[BV_MAX_VIEWS];
+	float tan_fovx[BV_MAX_VIEWS], tan_fovy[BV_MAX_VIEWS];
+	const int* radii[BV_MAX_VIEWS]; const SplatRec* rec[BV_MAX_VIEWS]; const uint8_t* clamped[BV_MAX_VIEWS]; const float* grad_acc[BV_MAX_VIEWS];
+	float* dL_dmean2D[BV_MAX_VIEWS];        // [P,3] per view, or null
+	// bucket segments (see the kernel's header for the two layouts); dL_dsh is the f_dc segment and dL_dfrest the f_rest one when leaf = 1
+	float *dL_dmean3D, *dL_dsh, *dL_dfrest, *dL_dopacity, *dL_dscale, *dL_drot;
+	float *stat_max_radii, *stat_grad_accum, *stat_denom;      // optional fused densification statistics ([P] each), or null
+};
+int launch_backward_views(cudaStream_t, const BackwardViewsArgs&);
+
 // loss.cu
 size_t loss_ws_bytes(int C, int H, int W);
 int launch_loss_l1_ssim(cudaStream_t, int C, int H, int W, const float* img, const float* gt, float lambda, void* ws, float* out3, float* dL_dimg);

@@ -10,59 +10,16 @@
 #include "common.cuh"
 #include "kernels.cuh"
 #include "render_common.cuh"
+#include "splat_math.cuh"
 
 namespace rr {
 
 namespace {
 
-#define FMA(a, b, c) __fmaf_rn((a), (b), (c))
-#define MUL(a, b) __fmul_rn((a), (b))
-#define ADD(a, b) __fadd_rn((a), (b))
-#define SUB(a, b) __fsub_rn((a), (b))
-#define DIV(a, b) __fdiv_rn((a), (b))
-
-__device__ __forceinline__ float sop3(float a, float b, float c, float d, float e, float f) { return FMA(e, f, FMA(a, b, MUL(c, d))); }
-// column `col` of the row-vector transform: m[col]*x + m[4+col]*y + m[8+col]*z + m[12+col]
-__device__ __forceinline__ float xform(const float* __restrict__ m, int col, float x, float y, float z) {
-	return ADD(m[12 + col], sop3(x, m[col], y, m[4 + col], z, m[8 + col]));
-}
-
 __constant__ float c_SH_C2[5] = { 1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f, -1.0925484305920792f, 0.5462742152960396f };
 __constant__ float c_SH_C3[7] = { -0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f, 0.3731763325901154f, -0.4570457994644658f, 1.445305721320277f, -0.5900435899266435f };
 constexpr float kSH_C0 = 0.28209479177387814f;
 constexpr float kSH_C1 = 0.4886025119029199f;
-
-__device__ __forceinline__ void cov3d_from_scale_rot(float s0, float s1, float s2, float mod, float4 q, float* c)
-{
-	const float sx = MUL(mod, s0), sy = MUL(mod, s1), sz = MUL(mod, s2);
-	const float r = q.x, x = q.y, y = q.z, z = q.w;
-	const float xz = MUL(x, z), A = FMA(r, y, xz), B = FMA(-r, y, xz);
-	const float rx = MUL(r, x), C = FMA(y, z, -rx), Dd = FMA(y, z, rx);
-	const float rz = MUL(r, z), E = FMA(x, y, -rz), F = FMA(x, y, rz);
-	const float yy = MUL(y, y), zz = MUL(z, z), G = FMA(x, x, yy), Hh = ADD(yy, zz), I = FMA(x, x, zz);
-	const float R00 = SUB(1.f, ADD(Hh, Hh)), R01 = ADD(E, E), R02 = ADD(A, A);
-	const float R10 = ADD(F, F), R11 = SUB(1.f, ADD(I, I)), R12 = ADD(C, C);
-	const float R20 = ADD(B, B), R21 = ADD(Dd, Dd), R22 = SUB(1.f, ADD(G, G));
-	const float z0 = 0.0f;
-	const float M00 = FMA(R02, z0, FMA(R01, z0, MUL(sx, R00)));
-	const float t0 = MUL(R00, z0);
-	const float M01 = FMA(R02, z0, FMA(sy, R01, t0));
-	const float M02 = FMA(sz, R02, FMA(R01, z0, t0));
-	const float t1 = MUL(R11, z0);
-	const float M10 = FMA(R12, z0, FMA(sx, R10, t1));
-	const float M11 = FMA(R12, z0, FMA(R10, z0, MUL(sy, R11)));
-	const float M12 = FMA(sz, R12, FMA(R10, z0, t1));
-	const float t2 = MUL(R21, z0);
-	const float M20 = FMA(R22, z0, FMA(sx, R20, t2));
-	const float M21 = FMA(R22, z0, FMA(R20, z0, MUL(sy, R21)));
-	const float M22 = FMA(sz, R22, FMA(R20, z0, t2));
-	c[0] = sop3(M00, M00, M01, M01, M02, M02);
-	c[1] = sop3(M10, M00, M11, M01, M12, M02);
-	c[2] = sop3(M20, M00, M21, M01, M22, M02);
-	c[3] = sop3(M10, M10, M11, M11, M12, M12);
-	c[4] = sop3(M20, M10, M21, M11, M22, M12);
-	c[5] = sop3(M20, M20, M21, M21, M22, M22);
-}
 
 #ifndef PF_MIN_CTAS
 #define PF_MIN_CTAS 4      // 64 registers: 4 CTAs (32 warps) per SM instead of 3; 0.081 -> 0.078 ms

@@ -8,6 +8,7 @@
 // unordered), so this file uses plain float expressions.
 #include "common.cuh"
 #include "kernels.cuh"
+#include "splat_math.cuh"
 
 namespace rr {
 
@@ -28,12 +29,13 @@ constexpr int SH_STRIDE = SH_FLOATS + 1; // +1 float: a lane walking its own row
 
 // conic / screen-mean gradient -> 2D covariance -> 3D covariance and mean gradient of one Gaussian that received gradient
 // (reference computeCov2DCUDA, backward.cu:133-264, and the projection part of preprocessCUDA, :360-377)
-__device__ __forceinline__ void cov2d_mean_grad(const PreprocessBwdArgs& a, int idx, float mx, float my, float mz, const float* g, float* dmean, float* dcov)
+// camera constants of one view as the per-Gaussian gradient functions need them; V / Pj may point to global or shared memory
+struct ViewCam { const float* V; const float* Pj; float cam[3]; float tan_fovx, tan_fovy, focal_x, focal_y, low_pass; };
+
+__device__ __forceinline__ void cov2d_mean_grad(const ViewCam& a, const float* S /*cov3D[6]*/, float mx, float my, float mz, const float* g, float* dmean, float* dcov)
 {
-	const float* __restrict__ V = a.view;
+	const float* V = a.V;
 	// ---- conic -> cov2D -> (cov3D, mean) : reference computeCov2DCUDA ----
-	const float* __restrict__ c3 = a.cov3D + 6 * (size_t)idx;
-	const float S[6] = { c3[0], c3[1], c3[2], c3[3], c3[4], c3[5] };
 	float tx = V[0] * mx + V[4] * my + V[8] * mz + V[12];
 	float ty = V[1] * mx + V[5] * my + V[9] * mz + V[13];
 	const float tz = V[2] * mx + V[6] * my + V[10] * mz + V[14];
@@ -87,7 +89,7 @@ __device__ __forceinline__ void cov2d_mean_grad(const PreprocessBwdArgs& a, int 
 	dmean[2] = V[8] * dtx + V[9] * dty + V[10] * dtz;
 
 	// ---- screen-space mean -> 3D mean through the projection (reference backward.cu:360-377) ----
-	const float* __restrict__ Pj = a.proj;
+	const float* Pj = a.Pj;
 	const float hw = Pj[3] * mx + Pj[7] * my + Pj[11] * mz + Pj[15];
 	const float m_w = 1.0f / (hw + 0.0000001f);
 	const float mul1 = (Pj[0] * mx + Pj[4] * my + Pj[8] * mz + Pj[12]) * m_w * m_w;
@@ -101,30 +103,29 @@ __device__ __forceinline__ void cov2d_mean_grad(const PreprocessBwdArgs& a, int 
 // store(ptr, r, g, b), and the view-direction part of the mean gradient added to dmean.  sh and dsh may alias (a staged
 // row is overwritten in place): every dot() of a band is taken before its put()s.
 template <class Store>
-__device__ __forceinline__ void sh_grad(const PreprocessBwdArgs& a, int idx, float mx, float my, float mz, const float* g, const float* __restrict__ sh,
-	float* __restrict__ dsh, float* dmean, Store store)
+__device__ __forceinline__ void sh_grad(int D, uint8_t cl /*clamped bits*/, const float* campos, float mx, float my, float mz, const float* g, const float* sh,
+	float* dsh, float* dmean, Store store)
 {
-	const uint8_t cl = a.clamped[idx];
 	const float dR[3] = { (cl & 1) ? 0.f : g[0], (cl & 2) ? 0.f : g[1], (cl & 4) ? 0.f : g[2] };
-	const float ox = mx - a.campos[0], oy = my - a.campos[1], oz = mz - a.campos[2];
+	const float ox = mx - campos[0], oy = my - campos[1], oz = mz - campos[2];
 	const float inv_len = 1.0f / sqrtf(ox * ox + oy * oy + oz * oz);
 	const float x = ox * inv_len, y = oy * inv_len, z = oz * inv_len;
 	float ddx = 0, ddy = 0, ddz = 0;   // dL/d(dir)
 	auto dot = [&](int k) { return sh[3 * k] * dR[0] + sh[3 * k + 1] * dR[1] + sh[3 * k + 2] * dR[2]; };
 	auto put = [&](int k, float wgt) { store(dsh + 3 * k, wgt * dR[0], wgt * dR[1], wgt * dR[2]); };
 	put(0, kC0);
-	if (a.D > 0) {
+	if (D > 0) {
 		const float s1 = dot(1), s2 = dot(2), s3 = dot(3);
 		put(1, -kC1 * y); put(2, kC1 * z); put(3, -kC1 * x);
 		ddx = -kC1 * s3; ddy = -kC1 * s1; ddz = kC1 * s2;
-		if (a.D > 1) {
+		if (D > 1) {
 			const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
 			const float s4 = dot(4), s5 = dot(5), s6 = dot(6), s7 = dot(7), s8 = dot(8);
 			put(4, b_SH_C2[0] * xy); put(5, b_SH_C2[1] * yz); put(6, b_SH_C2[2] * (2.f * zz - xx - yy)); put(7, b_SH_C2[3] * xz); put(8, b_SH_C2[4] * (xx - yy));
 			ddx += b_SH_C2[0] * y * s4 + b_SH_C2[2] * 2.f * -x * s6 + b_SH_C2[3] * z * s7 + b_SH_C2[4] * 2.f * x * s8;
 			ddy += b_SH_C2[0] * x * s4 + b_SH_C2[1] * z * s5 + b_SH_C2[2] * 2.f * -y * s6 + b_SH_C2[4] * 2.f * -y * s8;
 			ddz += b_SH_C2[1] * y * s5 + b_SH_C2[2] * 2.f * 2.f * z * s6 + b_SH_C2[3] * x * s7;
-			if (a.D > 2) {
+			if (D > 2) {
 				const float s9 = dot(9), s10 = dot(10), s11 = dot(11), s12 = dot(12), s13 = dot(13), s14 = dot(14), s15 = dot(15);
 				put(9, b_SH_C3[0] * y * (3.f * xx - yy)); put(10, b_SH_C3[1] * xy * z); put(11, b_SH_C3[2] * y * (4.f * zz - xx - yy));
 				put(12, b_SH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy)); put(13, b_SH_C3[4] * x * (4.f * zz - xx - yy));
@@ -147,15 +148,14 @@ __device__ __forceinline__ void sh_grad(const PreprocessBwdArgs& a, int idx, flo
 }
 
 // 3D covariance gradient -> scale and rotation gradient (reference computeCov3D backward, backward.cu:268-331)
-__device__ __forceinline__ void scale_rot_grad(const PreprocessBwdArgs& a, int idx, size_t i3, const float* dcov, float* ds, float4& dq)
+__device__ __forceinline__ void scale_rot_grad(float4 q, float s0, float s1, float s2, float scale_modifier, const float* dcov, float* ds, float4& dq)
 {
-	const float4 q = load_f4(a.rotations, (size_t)idx);
 	const float r = q.x, x = q.y, y = q.z, z = q.w;
 	// R in glm [col][row] indexing
 	const float R[3][3] = { { 1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y) },
 		{ 2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x) },
 		{ 2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y) } };
-	const float sv[3] = { a.scale_modifier * a.scales[i3], a.scale_modifier * a.scales[i3 + 1], a.scale_modifier * a.scales[i3 + 2] };
+	const float sv[3] = { scale_modifier * s0, scale_modifier * s1, scale_modifier * s2 };
 	const float dS[3][3] = { { dcov[0], 0.5f * dcov[1], 0.5f * dcov[2] }, { 0.5f * dcov[1], dcov[3], 0.5f * dcov[4] }, { 0.5f * dcov[2], 0.5f * dcov[4], dcov[5] } };
 	// dMt[k][j] = dL_dM[j][k] with M[c][r] = sv[r] * R[c][r], dL_dM = 2 M dSigma
 	float dMt[3][3];
@@ -256,10 +256,13 @@ __global__ void __launch_bounds__(PB_THREADS, PB_MIN_CTAS) preprocess_bwd_kernel
 
 	float dmean[3] = { 0, 0, 0 }, dcov[6] = { 0, 0, 0, 0, 0, 0 };
 	const float mx = a.means3D[i3], my = a.means3D[i3 + 1], mz = a.means3D[i3 + 2];
-	const float* __restrict__ V = a.view;
-
+	ViewCam vc;
+	vc.V = a.view; vc.Pj = a.proj; vc.cam[0] = a.campos[0]; vc.cam[1] = a.campos[1]; vc.cam[2] = a.campos[2];
+	vc.tan_fovx = a.tan_fovx; vc.tan_fovy = a.tan_fovy; vc.focal_x = a.focal_x; vc.focal_y = a.focal_y; vc.low_pass = a.low_pass;
 	if (visible) {
-		cov2d_mean_grad(a, idx, mx, my, mz, g, dmean, dcov);
+		const float* __restrict__ c3 = a.cov3D + 6 * (size_t)idx;
+		const float S[6] = { c3[0], c3[1], c3[2], c3[3], c3[4], c3[5] };
+		cov2d_mean_grad(vc, S, mx, my, mz, g, dmean, dcov);
 	}
 	#pragma unroll
 	for (int k = 0; k < 6; k++) if (wr && a.dL_dcov3D) put1(a.dL_dcov3D + 6 * (size_t)idx + k, dcov[k]);
@@ -271,7 +274,7 @@ __global__ void __launch_bounds__(PB_THREADS, PB_MIN_CTAS) preprocess_bwd_kernel
 		float* __restrict__ dsh = STAGED ? sb + lane * SH_STRIDE : a.dL_dsh + (size_t)(valid ? idx : 0) * a.M * 3;
 		const int nact = visible ? (a.D + 1) * (a.D + 1) : 0;
 		if (visible) {
-			sh_grad(a, idx, mx, my, mz, g, sh, dsh, dmean, [&](float* p, float r0, float r1, float r2) {
+			sh_grad(a.D, a.clamped[idx], vc.cam, mx, my, mz, g, sh, dsh, dmean, [&](float* p, float r0, float r1, float r2) {
 				if (STAGED) { p[0] = r0; p[1] = r1; p[2] = r2; }
 				else { put1(p, r0); put1(p + 1, r1); put1(p + 2, r2); }
 			});
@@ -309,7 +312,7 @@ __global__ void __launch_bounds__(PB_THREADS, PB_MIN_CTAS) preprocess_bwd_kernel
 	float ds[3] = { 0, 0, 0 };
 	float4 dq = make_float4(0, 0, 0, 0);
 	if (visible && a.scales) {
-		scale_rot_grad(a, idx, i3, dcov, ds, dq);
+		scale_rot_grad(load_f4(a.rotations, (size_t)idx), a.scales[i3], a.scales[i3 + 1], a.scales[i3 + 2], a.scale_modifier, dcov, ds, dq);
 	}
 	if (a.dL_dscale) { put1(a.dL_dscale + i3, ds[0]); put1(a.dL_dscale + i3 + 1, ds[1]); put1(a.dL_dscale + i3 + 2, ds[2]); }
 	if (a.dL_drot) {
@@ -327,6 +330,203 @@ __global__ void __launch_bounds__(PB_THREADS, PB_MIN_CTAS) preprocess_bwd_kernel
 }
 
 
+// ---- view-batched backward ------------------------------------------------------------------------------------------------
+// The per-Gaussian half of the backward for ALL views of a step in one pass (rr_backward_views; no reference counterpart: the
+// reference runs computeCov2DCUDA + preprocessCUDA once per view, backward.cu:133-386).  A multi-view step otherwise runs
+// preprocess_bwd once per view, each time re-reading the mean / scale / rotation / SH row of every touched Gaussian and
+// read-modify-writing its 59 gradient floats.  Here one thread owns one Gaussian: it reads its parameters ONCE, walks the
+// views of the batch (phase A: radii and accumulator records of all views, loads in flight four views at a time, giving the
+// set of views that touched it; phase B: only those views — projected record, clamp flags, the view's camera from shared
+// memory), sums the 3D-covariance gradient over the views (Sigma -> (scale, rotation) is linear in it, so that step runs once),
+// accumulates dL_dsh in a shared-memory row, and writes its bucket row ONCE.  Per-view outputs (dL_dmean2D = viewspace
+// gradients) are still written per view, and the densification statistics of the batch (train.py:132-134) can be folded in.
+//   LEAF = false: inputs are the activated tensors, gradients w.r.t. them, bucket layout  means3D | sh[P,16,3] | opacity | scales | rotations
+//   LEAF = true : inputs are the six RAW leaf tensors of scene/gaussian_model.py:131-136 (activations of :85-105 applied
+//                 here: splat_math.cuh), gradients w.r.t. the leaves (chain rule applied here), bucket layout
+//                 xyz | f_dc[P,1,3] | f_rest[P,15,3] | opacity | scaling | rotation
+constexpr int BV_THREADS = 128;
+constexpr int BV_WARPS = BV_THREADS / 32;
+constexpr int CAM_FLOATS = 40;           // V[16] Pj[16] campos[3] tan_fovx tan_fovy focal_x focal_y pad
+constexpr size_t BV_SMEM_BYTES = sizeof(float) * (2 * BV_WARPS * 32 * SH_STRIDE + BV_MAX_VIEWS * CAM_FLOATS);
+
+template <bool LEAF>
+__global__ void __launch_bounds__(BV_THREADS, 4) backward_views_kernel(BackwardViewsArgs a)
+{
+	// dynamic shared memory (BV_SMEM_BYTES > the 48 KB static limit): per warp 32 SH rows (coefficient-major, 3 channels each)
+	// and their gradient rows summed over the views, then the cameras of the batch
+	extern __shared__ __align__(16) float bv_smem[];
+	float (*s_sh)[32 * SH_STRIDE] = reinterpret_cast<float (*)[32 * SH_STRIDE]>(bv_smem);
+	float (*s_dsh)[32 * SH_STRIDE] = reinterpret_cast<float (*)[32 * SH_STRIDE]>(bv_smem + BV_WARPS * 32 * SH_STRIDE);
+	float (*s_cam)[CAM_FLOATS] = reinterpret_cast<float (*)[CAM_FLOATS]>(bv_smem + 2 * BV_WARPS * 32 * SH_STRIDE);
+	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+	const int nv = a.nviews;
+	for (int i = tid; i < nv * 35; i += BV_THREADS) {
+		const int v = i / 35, k = i - v * 35;
+		s_cam[v][k] = k < 16 ? a.view[v][k] : k < 32 ? a.proj[v][k - 16] : a.campos[v][k - 32];
+	}
+	if (tid < nv) {
+		s_cam[tid][35] = a.tan_fovx[tid]; s_cam[tid][36] = a.tan_fovy[tid];
+		s_cam[tid][37] = a.W / (2.0f * a.tan_fovx[tid]); s_cam[tid][38] = a.H / (2.0f * a.tan_fovy[tid]);       // rasterizer_impl.cu:213-214
+	}
+	__syncthreads();
+	const int warp_base = blockIdx.x * BV_THREADS + warp * 32;
+	if (warp_base >= a.P) return;                               // warp-uniform
+	const int idx = warp_base + lane;
+	const bool valid = idx < a.P;
+	const int nvalid = min(32, a.P - warp_base);
+	const size_t ii = (size_t)(valid ? idx : 0), i3 = 3 * ii;
+	float* __restrict__ sh = s_sh[warp] + lane * SH_STRIDE;
+	float* __restrict__ dsh = s_dsh[warp] + lane * SH_STRIDE;
+
+	// ---- stage the warp's 32 SH rows (coalesced) and clear the gradient rows ----
+	if (LEAF) {
+		// f_dc [P,1,3] and f_rest [P,15,3]: row r of the warp = 3 floats of f_dc then 45 of f_rest
+		const float* __restrict__ dc = a.f_dc + (size_t)warp_base * 3;
+		const float* __restrict__ rest = a.f_rest + (size_t)warp_base * 45;
+		for (int f = lane; f < nvalid * 3; f += 32) { const int row = f / 3; s_sh[warp][row * SH_STRIDE + (f - row * 3)] = __ldg(dc + f); }
+		for (int f = lane; f < nvalid * 45; f += 32) { const int row = f / 45; s_sh[warp][row * SH_STRIDE + 3 + (f - row * 45)] = __ldg(rest + f); }
+	} else {
+		const float* __restrict__ src = a.shs + (size_t)warp_base * SH_FLOATS;
+		if ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0) {
+			const float4* __restrict__ src4 = reinterpret_cast<const float4*>(src);
+			for (int f4 = lane; f4 < nvalid * (SH_FLOATS / 4); f4 += 32) {
+				const int row = f4 / (SH_FLOATS / 4), col = (f4 - row * (SH_FLOATS / 4)) * 4;
+				const float4 v = __ldg(src4 + f4);
+				float* d = s_sh[warp] + row * SH_STRIDE + col;
+				d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+			}
+		} else {
+			for (int f = lane; f < nvalid * SH_FLOATS; f += 32) { const int row = f / SH_FLOATS; s_sh[warp][row * SH_STRIDE + (f - row * SH_FLOATS)] = __ldg(src + f); }
+		}
+	}
+	#pragma unroll
+	for (int k = 0; k < SH_FLOATS; k++) dsh[k] = 0.0f;
+	__syncwarp();
+
+	// ---- phase A: which views touched this Gaussian (radii > 0 and a non-zero accumulator record) ----
+	unsigned touched = 0;
+	int nvis = 0, maxr = 0;
+	for (int v0 = 0; v0 < nv; v0 += 4) {
+		int r[4];
+		#pragma unroll
+		for (int j = 0; j < 4; j++) r[j] = (valid && v0 + j < nv) ? __ldg(a.radii[v0 + j] + ii) : 0;
+		float4 m[4][3];
+		#pragma unroll
+		for (int j = 0; j < 4; j++) {
+			if (r[j] > 0) {
+				const float4* __restrict__ ap = reinterpret_cast<const float4*>(a.grad_acc[v0 + j]) + ii * (ACC_FLOATS / 4);
+				m[j][0] = __ldg(ap); m[j][1] = __ldg(ap + 1); m[j][2] = __ldg(ap + 2);
+			} else { m[j][0] = m[j][1] = m[j][2] = make_float4(0.f, 0.f, 0.f, 0.f); }
+		}
+		#pragma unroll
+		for (int j = 0; j < 4; j++) {
+			const bool nz = (m[j][0].x != 0.0f) | (m[j][0].y != 0.0f) | (m[j][0].z != 0.0f) | (m[j][0].w != 0.0f) | (m[j][1].x != 0.0f) | (m[j][1].y != 0.0f) |
+				(m[j][1].z != 0.0f) | (m[j][1].w != 0.0f) | (m[j][2].x != 0.0f);
+			if (r[j] > 0) { nvis++; maxr = max(maxr, r[j]); }
+			if (nz) touched |= 1u << (v0 + j);
+			else if (valid && v0 + j < nv && a.dL_dmean2D[v0 + j]) {           // a view that left no gradient: its viewspace gradient row is zero
+				float* o = a.dL_dmean2D[v0 + j] + i3;
+				o[0] = 0.0f; o[1] = 0.0f; o[2] = 0.0f;
+			}
+		}
+	}
+	const unsigned anymask = __ballot_sync(FULL, touched != 0);
+	const bool acc = a.accumulate != 0;
+	if (acc && anymask == 0 && !a.stat_denom) return;          // warp-uniform: nothing to add anywhere
+
+	// ---- phase B: the views that touched it ----
+	float dmean[3] = { 0, 0, 0 }, dcov[6] = { 0, 0, 0, 0, 0, 0 }, dop = 0.0f, gnorm = 0.0f;
+	const float mx = a.means3D[i3], my = a.means3D[i3 + 1], mz = a.means3D[i3 + 2];
+	float S[6] = { 0, 0, 0, 0, 0, 0 };
+	float4 q = make_float4(1.f, 0.f, 0.f, 0.f), qraw = q;
+	float sc0 = 0, sc1 = 0, sc2 = 0, qinv = 1.0f;
+	if (touched) {
+		qraw = load_f4(a.rotations, ii);
+		sc0 = a.scales[i3]; sc1 = a.scales[i3 + 1]; sc2 = a.scales[i3 + 2];
+		if (LEAF) { qinv = rot_inv_norm(qraw); q = act_rot(qraw); sc0 = act_scale(sc0); sc1 = act_scale(sc1); sc2 = act_scale(sc2); }
+		else q = qraw;
+		cov3d_from_scale_rot(sc0, sc1, sc2, a.scale_modifier, q, S);         // the forward's Sigma, bit for bit (splat_math.cuh)
+	}
+	for (unsigned rest = touched; rest; rest &= rest - 1) {
+		const int v = __ffs(rest) - 1;
+		const float4* __restrict__ ap = reinterpret_cast<const float4*>(a.grad_acc[v]) + ii * (ACC_FLOATS / 4);
+		const float4 m0 = __ldg(ap), m1 = __ldg(ap + 1), m2 = __ldg(ap + 2);
+		const float4* __restrict__ rp = reinterpret_cast<const float4*>(a.rec[v]) + ii * 3;
+		const float4 ra = __ldg(rp), rb = __ldg(rp + 1);             // ra = { pix.xy, conic.x, conic.y }, rb = { conic.z, opacity, .. }
+		const float A = ra.z, B = ra.w, C = rb.x, o = rb.y;
+		const float Sx = m0.w, Sy = m1.x, Sxx = m1.y, Sxy = m1.z, Syy = m1.w, S0 = m2.x;
+		float g[9];
+		g[0] = m0.x; g[1] = m0.y; g[2] = m0.z;
+		g[3] = -o * (0.5f * a.W) * (A * Sx + B * Sy);               // dL_dmean2D.x (backward.cu:519-527, 535)
+		g[4] = -o * (0.5f * a.H) * (C * Sy + B * Sx);               // dL_dmean2D.y
+		g[5] = -0.5f * o * Sxx; g[6] = -0.5f * o * Sxy; g[7] = -0.5f * o * Syy;   // dL_dconic .x .y .w (backward.cu:539-541)
+		g[8] = S0;                                                   // dL_dopacity (backward.cu:544)
+		if (a.dL_dmean2D[v]) { float* out = a.dL_dmean2D[v] + i3; out[0] = g[3]; out[1] = g[4]; out[2] = 0.0f; }
+		gnorm += sqrtf(g[3] * g[3] + g[4] * g[4]);
+		dop += LEAF ? g[8] * o * (1.0f - o) : g[8];                 // d sigmoid: the forward's own opacity value
+		const float* cam = s_cam[v];
+		ViewCam vc;
+		vc.V = cam; vc.Pj = cam + 16; vc.cam[0] = cam[32]; vc.cam[1] = cam[33]; vc.cam[2] = cam[34];
+		vc.tan_fovx = cam[35]; vc.tan_fovy = cam[36]; vc.focal_x = cam[37]; vc.focal_y = cam[38]; vc.low_pass = a.low_pass;
+		float dm[3], dc[6] = { 0, 0, 0, 0, 0, 0 };
+		cov2d_mean_grad(vc, S, mx, my, mz, g, dm, dc);
+		#pragma unroll
+		for (int k = 0; k < 6; k++) dcov[k] += dc[k];
+		sh_grad(a.D, __ldg(a.clamped[v] + ii), vc.cam, mx, my, mz, g, sh, dsh, dm, [](float* p, float r0, float r1, float r2) { p[0] += r0; p[1] += r1; p[2] += r2; });
+		dmean[0] += dm[0]; dmean[1] += dm[1]; dmean[2] += dm[2];
+	}
+
+	// ---- densification statistics of the batch (scene/gaussian_model.py:419-421 over every view that saw the Gaussian) ----
+	if (a.stat_denom && valid && nvis > 0) {
+		a.stat_max_radii[ii] = fmaxf(a.stat_max_radii[ii], (float)maxr);
+		a.stat_grad_accum[ii] += gnorm;
+		a.stat_denom[ii] += (float)nvis;
+	}
+	if (acc && anymask == 0) return;
+
+	// ---- the bucket row: written once (added in accumulate mode, where rows nothing touched are left alone) ----
+	__syncwarp();
+	if (LEAF) {
+		float* __restrict__ o_dc = a.dL_dsh + (size_t)warp_base * 3;          // f_dc segment
+		float* __restrict__ o_rest = a.dL_dfrest + (size_t)warp_base * 45;
+		for (int f = lane; f < nvalid * 3; f += 32) {
+			const int row = f / 3;
+			const float v = s_dsh[warp][row * SH_STRIDE + (f - row * 3)];
+			if (!acc) o_dc[f] = v; else if ((anymask >> row) & 1u) o_dc[f] += v;
+		}
+		for (int f = lane; f < nvalid * 45; f += 32) {
+			const int row = f / 45;
+			const float v = s_dsh[warp][row * SH_STRIDE + 3 + (f - row * 45)];
+			if (!acc) o_rest[f] = v; else if ((anymask >> row) & 1u) o_rest[f] += v;
+		}
+	} else {
+		float* __restrict__ dst = a.dL_dsh + (size_t)warp_base * SH_FLOATS;
+		for (int f = lane; f < nvalid * SH_FLOATS; f += 32) {
+			const int row = f / SH_FLOATS;
+			const float v = s_dsh[warp][row * SH_STRIDE + (f - row * SH_FLOATS)];
+			if (!acc) dst[f] = v; else if ((anymask >> row) & 1u) dst[f] += v;
+		}
+	}
+	if (!valid || (acc && !touched)) return;
+	auto put1 = [acc](float* p, float v) { *p = acc ? *p + v : v; };
+	put1(a.dL_dmean3D + i3, dmean[0]); put1(a.dL_dmean3D + i3 + 1, dmean[1]); put1(a.dL_dmean3D + i3 + 2, dmean[2]);
+	put1(a.dL_dopacity + ii, dop);
+	float ds[3] = { 0, 0, 0 };
+	float4 dq = make_float4(0, 0, 0, 0);
+	if (touched) {
+		scale_rot_grad(q, sc0, sc1, sc2, a.scale_modifier, dcov, ds, dq);
+		if (LEAF) {
+			ds[0] *= sc0; ds[1] *= sc1; ds[2] *= sc2;                            // d exp(s) = exp(s)
+			const float dot = q.x * dq.x + q.y * dq.y + q.z * dq.z + q.w * dq.w;  // F.normalize backward: (g - qh (qh . g)) / |q|
+			dq = make_float4((dq.x - q.x * dot) * qinv, (dq.y - q.y * dot) * qinv, (dq.z - q.z * dot) * qinv, (dq.w - q.w * dot) * qinv);
+		}
+	}
+	put1(a.dL_dscale + i3, ds[0]); put1(a.dL_dscale + i3 + 1, ds[1]); put1(a.dL_dscale + i3 + 2, ds[2]);
+	float* orot = a.dL_drot + 4 * ii;                                          // bucket segments need not be 16-byte aligned: scalar
+	put1(orot, dq.x); put1(orot + 1, dq.y); put1(orot + 2, dq.z); put1(orot + 3, dq.w);
+}
+
+
 }  // namespace
 
 int launch_preprocess_bwd(cudaStream_t stream, const PreprocessBwdArgs& a)
@@ -337,6 +537,22 @@ int launch_preprocess_bwd(cudaStream_t stream, const PreprocessBwdArgs& a)
 	if (staged) count_launch(), preprocess_bwd_kernel<true><<<grid, PB_THREADS, 0, stream>>>(a);
 	else count_launch(), preprocess_bwd_kernel<false><<<grid, PB_THREADS, 0, stream>>>(a);
 	return check_launch("preprocess_bwd", stream, false);
+}
+
+int launch_backward_views(cudaStream_t stream, const BackwardViewsArgs& a)
+{
+	if (a.P == 0 || a.nviews == 0) return 0;
+	const unsigned grid = (unsigned)((a.P + BV_THREADS - 1) / BV_THREADS);
+	auto launch = [&](auto kern) -> int {
+		if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BV_SMEM_BYTES) != cudaSuccess) {
+			set_error("backward_views: cannot reserve %zu bytes of dynamic shared memory", BV_SMEM_BYTES); return -1;
+		}
+		count_launch();
+		kern<<<grid, BV_THREADS, BV_SMEM_BYTES, stream>>>(a);
+		return 0;
+	};
+	if (a.leaf ? launch(backward_views_kernel<true>) : launch(backward_views_kernel<false>)) return -1;
+	return check_launch("backward_views", stream, false);
 }
 
 }  // namespace rr

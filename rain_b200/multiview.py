@@ -18,6 +18,8 @@ import torch
 from . import _C as _native
 
 SEGMENTS = ("means3D", "sh", "opacity", "scales", "rotations")
+# the leaf layout: gradients w.r.t. the six raw leaf tensors, in the order of scene/gaussian_model.py:131-136
+LEAF_SEGMENTS = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")
 
 
 def shard_views(num_views: int, rank: int, world_size: int) -> List[int]:
@@ -33,13 +35,19 @@ def shard_views(num_views: int, rank: int, world_size: int) -> List[int]:
 class GradientBucket:
     """One flat f32 buffer holding the per-Gaussian parameter gradients of a rank, plus typed views of its segments."""
 
-    def __init__(self, P: int, M: int, device):
-        self.P, self.M = int(P), int(M)
+    def __init__(self, P: int, M: int, device, layout: str = "activated"):
+        self.P, self.M, self.layout = int(P), int(M), layout
         self.floats_per_gaussian = 3 + 3 * self.M + 1 + 3 + 4
         self.flat = torch.zeros(self.P * self.floats_per_gaussian, dtype=torch.float32, device=device)
-        shapes = dict(means3D=(self.P, 3), sh=(self.P, self.M, 3), opacity=(self.P, 1), scales=(self.P, 3), rotations=(self.P, 4))
+        if layout == "activated":      # gradients w.r.t. the activated tensors the drop-in API takes
+            shapes = dict(means3D=(self.P, 3), sh=(self.P, self.M, 3), opacity=(self.P, 1), scales=(self.P, 3), rotations=(self.P, 4))
+        elif layout == "leaf":         # gradients w.r.t. the raw leaves (view-batched backward in leaf mode)
+            shapes = dict(xyz=(self.P, 3), f_dc=(self.P, 1, 3), f_rest=(self.P, self.M - 1, 3), opacity=(self.P, 1), scaling=(self.P, 3), rotation=(self.P, 4))
+        else:
+            raise ValueError(f"unknown bucket layout {layout!r}")
+        self.segments = SEGMENTS if layout == "activated" else LEAF_SEGMENTS
         self.views, off = {}, 0
-        for name in SEGMENTS:
+        for name in self.segments:
             n = 1
             for d in shapes[name]:
                 n *= d
@@ -72,7 +80,7 @@ class ViewResult:
 def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int], bucket: GradientBucket,
                          grad_fn: Callable[[int, torch.Tensor, torch.Tensor], torch.Tensor], *, bg: torch.Tensor, sh_degree: int,
                          scale_modifier: float = 1.0, low_pass: float = 0.3, debug: bool = False, keep_outputs: bool = True,
-                         pipeline: str = "two_stream", backend=_native) -> List[ViewResult]:
+                         pipeline: str = "two_stream", batch_backward: int = 8, stats=None, backend=_native) -> List[ViewResult]:
     """Forward + backward of this rank's views; parameter gradients of all views are summed into ``bucket``.
 
     params: dict(means3D[P,3], opacities[P,1], shs[P,M,3], scales[P,3], rotations[P,4]) — activated values, as
@@ -81,9 +89,16 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
     returns dL/dcolor [3,H,W] (the loss backward of train.py:113-115).  The first view overwrites the bucket (no
     zero-fill pass), later views accumulate.  pipeline: "two_stream" (default: the front of the next view on a
     high-priority side stream beside the render kernels of the current one) or "one_stream" (same work, serial order; used
-    for per-stage timing, where a kernel's own duration is wanted)."""
+    for per-stage timing, where a kernel's own duration is wanted).
+
+    batch_backward = B > 0 (default 8): the per-Gaussian half of the backward runs ONCE per B views (rr_backward_views: parameters
+    read once, bucket row written once, the views' accumulator records summed in registers) instead of once per view; per view
+    only the backward tile renderer runs (rr_backward_render).  0 restores the per-view rr_backward with RR_BWD_ACCUMULATE.
+    stats: optional rain_b200.optim.DensificationStats; the batched backward folds the views' densification statistics into
+    its per-step delta in the same pass (otherwise call stats.add_view per view)."""
     if pipeline not in ("two_stream", "one_stream"):
         raise ValueError(f"unknown pipeline {pipeline!r}")
+    batched = batch_backward > 0 and hasattr(backend, "backward_views") and bucket.M == 16 and bucket.layout == "activated"
     dev = params["means3D"].device
     e = torch.empty(0, device=dev)
     results = []
@@ -131,6 +146,7 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
         # the backward of view i, so its num_rendered is on the host long before it is needed and the device never waits for
         # the round trip that sizes the binning buffer
         pending = geom_pass(view_ids[0]) if n else None
+    group = []
     for i, v in enumerate(view_ids):
         cam = cameras[v]
         if side is not None:
@@ -146,14 +162,32 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
                 bin_pass(ahead[i + 1])
             if i + 2 < n:
                 ahead[i + 2] = geom_pass(view_ids[i + 2])
-        grads = backend.rasterize_gaussians_backward(
-            bg, params["means3D"], radii, e, params["scales"], params["rotations"], scale_modifier, e, cam.viewmatrix, cam.projmatrix,
-            cam.tanfovx, cam.tanfovy, dpix, params["shs"], sh_degree, cam.campos, geom, N, binning, img, debug, low_pass,
-            grads_out=bucket.grads_out(), accumulate=bucket.filled,       # the first view overwrites the bucket, later views add
-            **({"omit": ("colors", "cov3D")} if backend is _native else {}))   # intermediates nobody reads (no zero fill, no read-modify-write)
-        bucket.filled = True
+        if batched:
+            # per view only the backward tile renderer; its accumulator blob, radii and geometry blob stay alive until the batch's
+            # single per-Gaussian pass
+            P = params["means3D"].shape[0]
+            acc = backend.backward_render(bg, dpix, geom, N, binning, img, P, debug)
+            d2 = torch.empty((P, 3), dtype=torch.float32, device=dev)
+            group.append(dict(viewmatrix=cam.viewmatrix, projmatrix=cam.projmatrix, campos=cam.campos, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
+                              radii=radii, geom=geom, acc=acc, dL_dmean2D=d2))
+            if len(group) == batch_backward or i + 1 == n:
+                backend.backward_views(group, params["means3D"], params["shs"], params["scales"], params["rotations"], scale_modifier, low_pass, sh_degree,
+                                       cam.height, cam.width, bucket.grads_out(), accumulate=bucket.filled,
+                                       stats=stats.delta_tensors() if stats is not None else None, debug=debug)
+                bucket.filled = True
+                group = []
+        else:
+            grads = backend.rasterize_gaussians_backward(
+                bg, params["means3D"], radii, e, params["scales"], params["rotations"], scale_modifier, e, cam.viewmatrix, cam.projmatrix,
+                cam.tanfovx, cam.tanfovy, dpix, params["shs"], sh_degree, cam.campos, geom, N, binning, img, debug, low_pass,
+                grads_out=bucket.grads_out(), accumulate=bucket.filled,       # the first view overwrites the bucket, later views add
+                **({"omit": ("colors", "cov3D")} if backend is _native else {}))   # intermediates nobody reads (no zero fill, no read-modify-write)
+            bucket.filled = True
+            d2 = grads[0]
+            if stats is not None:
+                stats.add_view(radii, d2)
         results.append(ViewResult(v, color if keep_outputs else None, depth if keep_outputs else None, radii if keep_outputs else None,
-                                  int(N), grads[0] if keep_outputs else None))
+                                  int(N), d2 if keep_outputs else None))
     return results
 
 

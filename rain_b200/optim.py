@@ -90,6 +90,11 @@ class DensificationStats:
         """fold one rendered view (its radii and viewspace_points.grad) into this rank's delta of the step"""
         add_densification_stats(radii, dL_dmean2D, self._max, self._sum[:self.P], self._sum[self.P:])
 
+    def delta_tensors(self):
+        """(max_radii2D, xyz_gradient_accum, denom) delta tensors of this rank's step, for kernels that fold views in directly
+        (rr_backward_views)"""
+        return self._max, self._sum[:self.P], self._sum[self.P:]
+
     def sync(self, group=None):
         """combine the step's deltas across the ranks of ``group`` and fold them into the replicated statistics"""
         import torch.distributed as dist
