@@ -191,7 +191,7 @@ int rr_sort_pairs_u64(void* stream, int64_t n, uint64_t* keys_in, uint64_t* keys
 /* byte offsets of the arrays inside the opaque blobs (for stage-wise diffing against the oracle / reference).
  * geom:    [0] rec f32[P,12]  [1] cov3D f32[P,6]  [2] clamped u8[P]  [3] tiles_touched u32[P]  [4] rect u32[P,2]
  *          [5] depth_order u32[P]  [6] offsets u32[P] (inclusive, in depth order)  [7] = [6]  [8] num_rendered u32
- * binning: [0] tile_keys_sorted u32[N]  [1] point_list u32[N]  [2] warp_flags u32[8*(N/32+T+2)]  [3] = [1]  [4] reserved
+ * binning: [0] tile_keys_sorted u32[N]  [1] point_list u32[N]  [2] warp_flags u32[4*(N/32+T+2)]  [3] = [1]  [4] reserved
  * image:   [0] final_T f32[H*W]  [1] n_contrib u32[H*W]  [2] ranges u32[T,2]  [3] reserved u32[T] */
 int rr_geom_layout(int P, int64_t offsets_host[9]);
 int rr_binning_layout(int64_t N, int W, int H, int64_t offsets_host[5]);

@@ -31,11 +31,13 @@ int launch_tile_ranges(cudaStream_t, size_t N, const uint32_t* sorted_tile_keys,
 int launch_export_keys(cudaStream_t, int T, const uint2* ranges, const uint32_t* point_list, const uint32_t* rec_words, uint64_t* out);
 
 // render_fwd.cu / render_bwd.cu
-// Per-warp blend flags ("which list entries did warp w's 8x4 pixel block blend"), written by the forward and walked by
-// the backward.  One bit per (tile list entry, warp), stored as 32-bit words; the words of tile t start at
-// 8 * (ranges[t].x / 32 + t) and warp w owns the ceil(n / 32) consecutive words from + w * ceil(n / 32)
-// (n = list length of the tile; bit j % 32 of word j / 32 is list entry j).
-__host__ __device__ inline size_t warp_flag_words(size_t N, size_t tiles) { return 8 * (N / 32 + tiles + 2); }
+// Per-warp blend flags ("which list entries did warp w's 8x8 pixel block blend"), written by the forward and walked by
+// the backward (both give warp w the block at ((w & 1) * 8, (w >> 1) * 8) of the tile).  One bit per (tile list entry,
+// warp), stored as 32-bit words; the words of tile t start at FLAG_WARPS * (ranges[t].x / 32 + t) and warp w owns the
+// ceil(n / 32) consecutive words from + w * ceil(n / 32) (n = list length of the tile; bit j % 32 of word j / 32 is list
+// entry j).  A warp writes its words only up to the batch of its last contributor; the blob is not zero-filled.
+constexpr int FLAG_WARPS = 4;
+__host__ __device__ inline size_t warp_flag_words(size_t N, size_t tiles) { return FLAG_WARPS * (N / 32 + tiles + 2); }
 
 // Per-Gaussian gradient accumulator filled by the backward render (one RED.ADD per value and (warp, list entry) visit)
 // and consumed by the backward preprocess: 12 floats = 48 bytes,

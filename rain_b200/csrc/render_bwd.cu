@@ -64,9 +64,7 @@ __global__ void __launch_bounds__(B2_THREADS, B2_MIN_CTAS) render_bwd_kernel(Ren
 	const size_t HW = (size_t)a.H * a.W;
 	const size_t pidA = (size_t)a.W * pyA + pix_x, pidB = (size_t)a.W * pyB + pix_x;
 	const uint32_t lastA = inA ? a.n_contrib[pidA] : 0u, lastB = inB ? a.n_contrib[pidB] : 0u;
-	// last contributor over each 8x4 half (the two forward warps whose flag words this warp walks) and over the block
-	const uint32_t wmaxA = __reduce_max_sync(FULL, lastA), wmaxB = __reduce_max_sync(FULL, lastB);
-	const uint32_t wmax = max(wmaxA, wmaxB);
+	const uint32_t wmax = __reduce_max_sync(FULL, max(lastA, lastB));
 	if (wmax == 0 || n == 0) return;             // warp-uniform: nothing was blended into this warp's pixels
 
 	const float TfA = inA ? a.final_T[pidA] : 0.0f, TfB = inB ? a.final_T[pidB] : 0.0f;
@@ -93,28 +91,21 @@ __global__ void __launch_bounds__(B2_THREADS, B2_MIN_CTAS) render_bwd_kernel(Ren
 	float* __restrict__ red = s_red[warp];
 	const float4* __restrict__ red_row = reinterpret_cast<const float4*>(red) + lane * 8;
 
-	// the forward's flag words of the two 8x4 half blocks (forward warps wA and wA + 2, kernels.cuh)
+	// the forward's flag words of this 8x8 block (same warp footprint in both kernels, kernels.cuh)
 	const int ngroups = (n + 31) >> 5;
-	const int wA = (warp & 1) + 4 * (warp >> 1);
-	const uint32_t* __restrict__ wfA = a.warp_flags + 8ull * ((size_t)(range.x >> 5) + (size_t)tile) + (size_t)wA * ngroups;
-	const uint32_t* __restrict__ wfB = wfA + 2 * (size_t)ngroups;
+	const uint32_t* __restrict__ wf = a.warp_flags + (size_t)FLAG_WARPS * ((size_t)(range.x >> 5) + (size_t)tile) + (size_t)warp * ngroups;
 	const uint32_t* __restrict__ ids = a.point_list + range.x;
 	const float4* __restrict__ grec = reinterpret_cast<const float4*>(a.rec);
-	// A forward warp writes its flag words only for the batches it worked on: up to the batch of its last contributor.  A
-	// half that is outside the image, or that saturated before the other one, leaves the rest of its words unwritten
-	// (the blob is not zero-filled), so each half's words are read only up to ITS last contributor.
-	const int nwords = (int)((wmax + 31u) >> 5), nwordsA = (int)((wmaxA + 31u) >> 5), nwordsB = (int)((wmaxB + 31u) >> 5);
+	// The forward warp of this block wrote its flag words only for the batches it worked on, i.e. up to the batch of its last
+	// contributor (the blob is not zero-filled): words are read only below ceil(wmax / 32).
+	const int nwords = (int)((wmax + 31u) >> 5);
 	XC(unsigned xc_visits = 0; unsigned xc_live = 0;)
 	uint32_t q = 0;                               // chunks staged so far by this warp: buffer = q & 1, mbarrier parity = (q >> 1) & 1
 
 	for (int wbase = ((nwords - 1) / LIST_WORDS) * LIST_WORDS; wbase >= 0; wbase -= LIST_WORDS) {
 		// ---- visit list of this round: set bits of words [wbase, wbase + LIST_WORDS), highest list entry first ----
 		const int wi = wbase + lane;
-		uint32_t word = 0u;
-		if (lane < LIST_WORDS) {
-			if (wi < nwordsA) word = __ldg(wfA + wi);
-			if (wi < nwordsB) word |= __ldg(wfB + wi);
-		}
+		uint32_t word = (lane < LIST_WORDS && wi < nwords) ? __ldg(wf + wi) : 0u;
 		const int cnt = __popc(word);
 		int inc = cnt;                             // inclusive sum over lanes >= this one
 		#pragma unroll

@@ -1,5 +1,5 @@
-"""Live-lane fraction of the two tile renderers: of the 32 (forward) / 64 (backward) pixel evaluations
-a warp issues per list entry it works on, how many pass the reference's own pair test.  Uses the work counters of the
+"""Live-lane fraction of the two tile renderers: of the 64 pixel evaluations (two per lane) a warp
+issues per list entry it works on, how many pass the reference's own pair test.  Uses the work counters of the
 CROSS-CHECK build of the library (rain_b200/librainrast_xc.so, -DRR_CROSSCHECK; the product library has none) on a few views
 of a workload and writes profiles/live_lanes.json, which bench.py quotes in stages[] / roofline.
 
@@ -46,7 +46,7 @@ c = [int(x) for x in out]
 per = lambda x: x / views
 rec = {
     "render_fwd": {
-        "live_lane_frac": round(c[4] / max(1, 32 * c[3]), 4), "blended_lane_frac": round(c[5] / max(1, 32 * c[3]), 4),
+        "live_lane_frac": round(c[4] / max(1, 64 * c[3]), 4), "blended_lane_frac": round(c[5] / max(1, 64 * c[3]), 4),
         "warp_entries_examined_per_view": per(c[1]), "after_aabb_cull_per_view": per(c[2]), "survivors_blended_per_view": per(c[3]),
         "live_lane_evals_per_view": per(c[4]), "blended_lane_evals_per_view": per(c[5]),
         "survivor_frac_of_examined": round(c[3] / max(1, c[1]), 4), "list_entries_per_view": N_tot / views},
