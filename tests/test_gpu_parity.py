@@ -377,7 +377,10 @@ def test_accumulate_mode_and_multiview_bucket(device, pipeline, P, W, H, V, batc
         tot = cur if tot is None else {k: tot[k] + cur[k] for k in cur}
     for k in mv.SEGMENTS:
         assert torch.isfinite(bucket.views[k]).all()
-        assert rel_err(bucket.views[k], tot[k])[0] < 1e-5, k
+        # summation order differs (the bucket adds view by view or sums in registers, `tot` adds tensors): 1e-5 at the small
+        # sizes; at 1M Gaussians dL_dscale / dL_drot (sums with heavy cancellation; their run-to-run spread alone is 5e-6 /
+        # 1.6e-5 at C2, profiles/r02_oracle_agreement_v1.log) get 3e-5 — still a third of the north star's 1e-4
+        assert rel_err(bucket.views[k], tot[k])[0] < (1e-5 if P < 100_000 else 3e-5), k
     # densification statistics folded into the batched backward == the per-view kernel's
     ref_stats.sync()
     assert eq(stats.max_radii2D, ref_stats.max_radii2D) and eq(stats.denom, ref_stats.denom)
@@ -418,7 +421,9 @@ def test_backward_views_leaf_mode_applies_the_activation_chain_rule(device):
                             [A.views["means3D"], A.views["sh"], A.views["opacity"], A.views["scales"], A.views["rotations"]])
     for k in mv.LEAF_SEGMENTS:
         assert torch.isfinite(L.views[k]).all(), k
-        assert rel_err(L.views[k], leaves[k].grad.reshape(L.views[k].shape))[0] < 1e-5, k
+        # leaf mode re-activates the leaves itself (splat_math.cuh: expf / sigmoid / normalise, an ulp or two from torch's) and
+        # recomputes Sigma from them, so the cancellation-heavy scale / rotation sums move by a few 1e-5 of max
+        assert rel_err(L.views[k], leaves[k].grad.reshape(L.views[k].shape))[0] < 5e-5, k
 
 
 def _sort_case(device, n, key_bytes, b0, b1, seed, skew):
