@@ -174,6 +174,18 @@ int rr_param_step(void* stream, int P, int M, float* xyz, float* f_dc, float* f_
  * from the gradient all-reduce. */
 int rr_densify_stats(void* stream, int P, const int* radii, const float* dL_dmean2D, float* max_radii2D, float* xyz_gradient_accum, float* denom);
 
+/* ---- gradient-bucket all-reduce over NVLink peer / multicast memory (no reference counterpart) -------------
+ * In-place sum of an f32 buffer of n floats that every rank holds in SYMMETRIC memory: buffers[r] / signals[r] (HOST arrays of
+ * `world` device pointers) are rank r's bucket and flag buffer as mapped into the calling rank's address space ([rank] = the
+ * local ones; flag buffers are rr_allreduce_signal_bytes() bytes, zero before the first call); multicast is the multicast
+ * address aliasing all buckets (in-switch reduction: multimem.ld_reduce + multimem.st), or null (peer loads / stores).  One
+ * kernel per rank, `ctas` CTAs (0 = one per SM; the same value on every rank), launched by every rank of the job on its own
+ * GPU; epoch must increase by 2 from call to call (same value on all ranks).  *error_flag (local device u32) is set if a
+ * cross-rank wait timed out.  Replaces ncclAllReduce for the view-sharded step; world <= 8. */
+size_t rr_allreduce_signal_bytes(void);
+int rr_allreduce_sum_f32(void* stream, int rank, int world, int64_t n, void* const* buffers, void* multicast, void* const* signals,
+	uint32_t* error_flag, uint32_t epoch, int ctas);
+
 /* replaces distCUDA2 / SimpleKNN::knn (simple-knn/spatial.cu:4-15, simple_knn.cu:174-210); points f32[P,3] -> out f32[P];
  * ws: rr_dist2_ws_bytes(P) bytes of device scratch */
 size_t rr_dist2_ws_bytes(int P);

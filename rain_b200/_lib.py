@@ -65,6 +65,8 @@ SIGNATURES = {
     "rr_loss_l2_u8": (_i, [_vp, _i64, _vp, _vp, _c.c_float, _vp, _vp]),
     "rr_param_step": (_i, [_vp, _i, _i] + [_vp] * 6 + [_vp, _vp, _vp, _c.POINTER(_c.c_float), _i] + [_vp] * 4),
     "rr_densify_stats": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp]),
+    "rr_allreduce_signal_bytes": (_sz, []),
+    "rr_allreduce_sum_f32": (_i, [_vp, _i, _i, _i64, _vp, _vp, _vp, _vp, _c.c_uint32, _i]),
     "rr_dist2_ws_bytes": (_sz, [_i]),
     "rr_dist2": (_i, [_vp, _i, _vp, _vp, _vp, _sz]),
     "rr_sort_ws_bytes": (_sz, [_i64, _i, _i, _i]),

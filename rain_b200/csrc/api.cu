@@ -518,6 +518,26 @@ int rr_densify_stats(void* stream_, int P, const int* radii, const float* dL_dme
 	return launch_densify_stats(reinterpret_cast<cudaStream_t>(stream_), P, radii, dL_dmean2D, max_radii2D, xyz_gradient_accum, denom);
 }
 
+size_t rr_allreduce_signal_bytes(void) { return sizeof(uint32_t) * AR_MAX_CTAS * AR_MAX_WORLD + 256; }
+
+int rr_allreduce_sum_f32(void* stream_, int rank, int world, int64_t n, void* const* buffers, void* multicast, void* const* signals,
+	uint32_t* error_flag, uint32_t epoch, int ctas)
+{
+	if (world <= 1 || n == 0) return 0;
+	if (world > AR_MAX_WORLD || rank < 0 || rank >= world || n < 0) { set_error("rr_allreduce_sum_f32: bad rank/world/n %d/%d/%lld (at most %d ranks)", rank, world, (long long)n, AR_MAX_WORLD); return -1; }
+	if (bad_ptr(buffers, "buffers") || bad_ptr(signals, "signals") || bad_ptr(error_flag, "error_flag")) return -1;
+	if (ctas <= 0) ctas = 148;
+	if (ctas > AR_MAX_CTAS) ctas = AR_MAX_CTAS;
+	AllReduceArgs a; memset(&a, 0, sizeof(a));
+	a.multicast = reinterpret_cast<float*>(multicast); a.error_flag = error_flag; a.n = n; a.rank = rank; a.world = world; a.epoch = epoch;
+	for (int r = 0; r < world; r++) {
+		if (bad_ptr(buffers[r], "buffers[r]") || bad_ptr(signals[r], "signals[r]")) return -1;
+		if (reinterpret_cast<uintptr_t>(buffers[r]) & 15) { set_error("rr_allreduce_sum_f32: buffers must be 16-byte aligned"); return -1; }
+		a.buffers[r] = reinterpret_cast<float*>(buffers[r]); a.signal[r] = reinterpret_cast<uint32_t*>(signals[r]);
+	}
+	return launch_allreduce(reinterpret_cast<cudaStream_t>(stream_), a, ctas);
+}
+
 size_t rr_dist2_ws_bytes(int P) { return knn_ws_bytes(P); }
 int rr_dist2(void* stream_, int P, const float* points, float* out, void* ws, size_t ws_bytes)
 {

@@ -110,6 +110,20 @@ int launch_param_step(cudaStream_t, int P, int M, float* xyz, float* f_dc, float
 
 int launch_densify_stats(cudaStream_t, int P, const int* radii, const float* dL_dmean2D, float* max_radii2D, float* grad_accum, float* denom);
 
+// allreduce.cu: one-kernel two-shot all-reduce of a symmetric f32 buffer over NVLink peer / multicast memory
+constexpr int AR_MAX_WORLD = 8;
+constexpr int AR_MAX_CTAS = 256;          // CTAs per rank; the signal buffer holds AR_MAX_CTAS * AR_MAX_WORLD flag words
+struct AllReduceArgs {
+	float* multicast;                     // multicast address of the symmetric buffer, or null (peer-pointer variant)
+	float* buffers[AR_MAX_WORLD];         // every rank's buffer as mapped into THIS rank's address space ([rank] = the local one)
+	uint32_t* signal[AR_MAX_WORLD];       // every rank's flag buffer (u32[AR_MAX_CTAS * world], zero before the first call), peer-mapped
+	uint32_t* error_flag;                 // local device word, set to 1 if a cross-rank wait timed out
+	int64_t n;                            // floats
+	int rank, world;
+	uint32_t epoch;                       // flag value of this call's first barrier; the second uses epoch + 1; strictly increasing across calls
+};
+int launch_allreduce(cudaStream_t, const AllReduceArgs&, int ctas);
+
 // knn.cu
 size_t knn_ws_bytes(int P);
 int launch_dist2(cudaStream_t, int P, const float* points, float* out, void* ws, size_t ws_bytes);

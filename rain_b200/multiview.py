@@ -35,10 +35,19 @@ def shard_views(num_views: int, rank: int, world_size: int) -> List[int]:
 class GradientBucket:
     """One flat f32 buffer holding the per-Gaussian parameter gradients of a rank, plus typed views of its segments."""
 
-    def __init__(self, P: int, M: int, device, layout: str = "activated"):
+    def __init__(self, P: int, M: int, device, layout: str = "activated", symmetric: bool = False, group=None):
+        """symmetric=True (collective: every rank of ``group`` constructs it): the buffer lives in symmetric memory and
+        ``allreduce_bucket`` runs the library's one-kernel NVLink all-reduce (rain_b200.collective) instead of ncclAllReduce."""
         self.P, self.M, self.layout = int(P), int(M), layout
         self.floats_per_gaussian = 3 + 3 * self.M + 1 + 3 + 4
-        self.flat = torch.zeros(self.P * self.floats_per_gaussian, dtype=torch.float32, device=device)
+        self.collective = None
+        if symmetric:
+            from .collective import SymmetricAllReduce
+            self.collective = SymmetricAllReduce(self.P * self.floats_per_gaussian, device, group)
+            self.flat = self.collective.flat
+            self.flat.zero_()
+        else:
+            self.flat = torch.zeros(self.P * self.floats_per_gaussian, dtype=torch.float32, device=device)
         if layout == "activated":      # gradients w.r.t. the activated tensors the drop-in API takes
             shapes = dict(means3D=(self.P, 3), sh=(self.P, self.M, 3), opacity=(self.P, 1), scales=(self.P, 3), rotations=(self.P, 4))
         elif layout == "leaf":         # gradients w.r.t. the raw leaves (view-batched backward in leaf mode)
@@ -244,7 +253,10 @@ def allreduce_bucket(bucket: GradientBucket, group=None, average: bool = False):
     if group == "skip":          # a single-rank step inside an initialised process group (tools/verify_multigpu.py)
         return bucket
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
-        dist.all_reduce(bucket.flat, op=dist.ReduceOp.SUM, group=group)
+        if bucket.collective is not None:
+            bucket.collective.allreduce()        # one kernel over NVLink peer / multicast memory (csrc/allreduce.cu)
+        else:
+            dist.all_reduce(bucket.flat, op=dist.ReduceOp.SUM, group=group)
         if average:
             bucket.flat.div_(dist.get_world_size(group))
     return bucket

@@ -3,6 +3,7 @@
 cd "$GRAFT_REPO_ROOT" || exit 1
 mkdir -p gpurun_out
 nvidia-smi topo -m > gpurun_out/c3_topo.txt 2>&1
+timeout 200 python tools/gpu_diag_callers.py > gpurun_out/c3_diag_callers.log 2>&1; tail -14 gpurun_out/c3_diag_callers.log
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1"
 NCCL_DEBUG=INFO NCCL_DEBUG_SUBSYS=INIT,TUNING,COLL timeout 200 $TR --master-port 29501 tools/probe_symm.py 1000000 > gpurun_out/c3_probe.json 2> gpurun_out/c3_probe_nccl.log; echo "probe rc=$?"
 grep -E "NVLS|Ring|Tree|Algo|algo|nvls" gpurun_out/c3_probe_nccl.log | head -40 > gpurun_out/c3_nccl_algo.txt

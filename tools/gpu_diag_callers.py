@@ -50,3 +50,20 @@ bad = (fw["rgb"] != st["rgb"]).any(1) & (radii_r > 0)
 if bad.any():
     i = int(bad.nonzero()[0])
     print("first rgb mismatch at", i, fw["rgb"][i].cpu().numpy(), st["rgb"][i].cpu().numpy(), "clamped", fw["clamped"][i].item(), st["clamped"][i].cpu().numpy())
+print("---- more")
+print("ref rgb[:3]", st["rgb"][:3].cpu().numpy())
+print("mine rgb[:3]", fw["rgb"][:3].cpu().numpy())
+for name, cp in (("view slice", cam.camera_center), ("clone", cam.camera_center.clone()), ("cpu-made", cam0.campos.to(dev))):
+    N2, c2, r2, d2 = ref.forward(bg, pc.get_xyz.detach(), det["opacity"], det["scales"], det["rotations"], cam.world_view_transform, cam.full_proj_transform,
+                                 cp, tanfovx, tanfovy, H, W, shs=det["shs"], sh_degree=D)
+    s2 = ref.state()
+    print(name, "ptr%256", cp.data_ptr() % 256, "ref rgb[0]", s2["rgb"][0].cpu().numpy(), "colour diff vs mine", int((c2 != fw["color"]).sum()))
+sh2 = sc.shs.to(dev)
+print("det shs == scene shs", bool(torch.equal(sh2, det["shs"])), det["shs"].shape, det["shs"].stride(), det["shs"].data_ptr() % 256)
+N2, c2, r2, d2 = ref.forward(bg, pc.get_xyz.detach(), det["opacity"], det["scales"], det["rotations"], cam.world_view_transform, cam.full_proj_transform,
+                             cam.camera_center.clone(), tanfovx, tanfovy, H, W, shs=sh2, sh_degree=D)
+print("scene shs tensor: ref rgb[0]", ref.state()["rgb"][0].cpu().numpy(), "colour diff vs mine", int((c2 != fw["color"]).sum()))
+for DD in range(4):
+    N2, c2, r2, d2 = ref.forward(bg, pc.get_xyz.detach(), det["opacity"], det["scales"], det["rotations"], cam.world_view_transform, cam.full_proj_transform,
+                                 cam.camera_center.clone(), tanfovx, tanfovy, H, W, shs=sh2, sh_degree=DD)
+    print("D", DD, ref.state()["rgb"][0].cpu().numpy())

@@ -62,6 +62,38 @@ try:
             out[name + "error"] = repr(ex)[:300]
 except Exception as ex:
     out["symm_mem_error"] = repr(ex)[:400]
+# this library's one-kernel all-reduce (csrc/allreduce.cu) on a symmetric bucket: correctness against NCCL's result, then time
+try:
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from rain_b200.collective import SymmetricAllReduce
+    for mc in (True, False):
+        tag = "rr_multimem_" if mc else "rr_peer_"
+        ar = SymmetricAllReduce(n, dev, use_multicast=mc)
+        if mc and not ar.multicast:
+            out[tag + "skipped"] = "no multicast address"
+            continue
+        g = torch.Generator(device=dev).manual_seed(1234 + rank)
+        src = torch.randn(n, device=dev, generator=g)
+        ar.flat.copy_(src)
+        ref = src.clone(); dist.all_reduce(ref)
+        torch.cuda.synchronize(); dist.barrier()
+        ar.allreduce()
+        torch.cuda.synchronize()
+        ar.check()
+        err = float((ar.flat - ref).abs().max() / ref.abs().max())
+        lo, hi = ar.flat.clone(), ar.flat.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        out[tag + "rel_err_vs_nccl"] = err
+        out[tag + "replicas_bit_identical"] = bool(torch.equal(lo, hi))
+        for ctas in (148, 256, 64):
+            ms = timeit(lambda: ar.allreduce(ctas))
+            out[tag + f"ms_ctas{ctas}"] = ms
+        ar.check()
+        best = min(out[tag + f"ms_ctas{c}"] for c in (148, 256, 64))
+        out[tag + "busbw_gbs"] = 2 * (world - 1) / world * n * 4 / best / 1e6
+except Exception as ex:
+    import traceback
+    out["rr_allreduce_error"] = traceback.format_exc()[-600:]
 if rank == 0:
     print(json.dumps(out), flush=True)
 dist.barrier()
