@@ -182,7 +182,9 @@ def run_ours(args, rank, world, local):
     targets_h = [make_target(W, H, v).pin_memory() for v in range(NUM_TARGETS)]
     params = dict(means3D=sc.means3D, opacities=sc.opacities, shs=sc.shs, scales=sc.scales, rotations=sc.rotations)
     bg = torch.zeros(3, device=dev)
-    bucket = mv.GradientBucket(P, 16, dev)
+    # N > 1: the bucket lives in symmetric memory and is reduced by the library's one-kernel NVLink all-reduce (csrc/allreduce.cu);
+    # `--collective nccl` keeps it a plain tensor reduced by ncclAllReduce
+    bucket = mv.GradientBucket(P, 16, dev, symmetric=(world > 1 and args.collective == "rr"))
     kw = dict(bg=bg, sh_degree=D, keep_outputs=False)
 
     # ---------------- device-resident arm (`value`) ----------------
@@ -312,7 +314,8 @@ def run_ours(args, rank, world, local):
     if rank != 0:
         return None
     return dict(cfg=cfg, value=value, ms=ms, e2e_value=e2e_value, ms_e2e=ms_e2e, h2d=h2d, d2h=d2h, launches=launches, stage=st, clocks=clocks,
-                N=N_last, V=V_seen, loss=loss, bucket_bytes=bucket.nbytes(), vps=VPS, allreduce_ms=allreduce_ms, dropin=dropin)
+                N=N_last, V=V_seen, loss=loss, bucket_bytes=bucket.nbytes(), vps=VPS, allreduce_ms=allreduce_ms, dropin=dropin,
+                collective=("rr_allreduce_sum_f32 " + json.dumps(bucket.collective.calibration)) if bucket.collective is not None else "ncclAllReduce")
 
 
 def run_dropin(cfg, sc, cams, targets, bg, dev, iters, warm):
@@ -451,6 +454,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C3", choices=["C1", "C2", "C3", "C4"])
     ap.add_argument("--cpu-renders", type=int, default=2, help="renders of the workload timed on the host for cpu_baseline (0 = skip)")
+    ap.add_argument("--collective", default="rr", choices=["rr", "nccl"], help="N > 1: rr = the library's one-kernel NVLink all-reduce on a symmetric bucket, nccl = ncclAllReduce")
     ap.add_argument("--dropin-iters", type=int, default=50, help="timed single-view iterations of the drop-in arm at N = 1 (0 = skip, e.g. under a profiler)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -537,7 +541,7 @@ def main():
         "stages": stages,
     }
     if world > 1:
-        line["allreduce"] = {"ms_per_step": round(r["allreduce_ms"], 4), "bytes": r["bucket_bytes"],
+        line["allreduce"] = {"impl": r["collective"], "ms_per_step": round(r["allreduce_ms"], 4), "bytes": r["bucket_bytes"],
                              "bus_gbs": round(2 * (world - 1) / world * r["bucket_bytes"] / max(r["allreduce_ms"], 1e-9) / 1e6, 1)}
     if r["dropin"]:
         line["dropin"] = r["dropin"]

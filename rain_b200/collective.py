@@ -17,7 +17,11 @@ class SymmetricAllReduce:
     """An f32 buffer of ``numel`` floats in symmetric memory plus what the one-kernel all-reduce needs (peer mappings, flag
     buffer, epoch).  Collective: every rank of ``group`` constructs it with the same arguments."""
 
-    def __init__(self, numel, device, group=None, use_multicast=True):
+    def __init__(self, numel, device, group=None, use_multicast="auto", ctas=0):
+        """use_multicast: True (in-switch multimem reduction; needs a multicast address), False (peer loads / stores), or "auto":
+        both variants are timed once on this buffer at construction and the faster one (max over ranks) is kept — at 2 GPUs
+        the peer variant wins (a GPU moves the same bytes either way and plain loads stream faster), with more ranks the
+        in-switch reduction moves ~1 bucket per GPU instead of 2 (world - 1) / world."""
         import torch.distributed._symmetric_memory as symm_mem
         lib = _lib.load()
         self.group = group if group is not None else dist.group.WORLD
@@ -36,19 +40,48 @@ class SymmetricAllReduce:
         vp = ctypes.c_void_p
         self._bufs = (vp * self.world)(*[int(p) + off for p in self._h.buffer_ptrs])
         self._sigs = (vp * self.world)(*[int(p) + soff for p in self._hs.buffer_ptrs])
-        mc = int(self._h.multicast_ptr) if use_multicast else 0
-        self.multicast = (mc + off) if mc else 0
+        mc = int(self._h.multicast_ptr)
+        self._multicast_addr = (mc + off) if mc else 0
+        self.multicast = self._multicast_addr if use_multicast else 0
+        self.ctas = int(ctas)
         assert int(self._bufs[self.rank]) == self.flat.data_ptr(), "symmetric memory: local mapping differs from the tensor's address"
         self.epoch = 1
+        self.calibration = None
         torch.cuda.synchronize(device)          # the zeroed flags are in memory before any peer can signal
         dist.barrier(self.group)
+        if use_multicast == "auto":
+            self._calibrate()
 
-    def allreduce(self, ctas=0):
+    def _calibrate(self, iters=4):
+        """time both variants on the (zero-filled) buffer and keep the faster; every rank takes the same decision"""
+        self.flat.zero_()
+        times = {}
+        for name, addr in (("peer", 0), ("multimem", self._multicast_addr)):
+            if name == "multimem" and not addr:
+                continue
+            self.multicast = addr
+            self.allreduce()                                            # warm-up
+            torch.cuda.synchronize(self.flat.device); dist.barrier(self.group)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(iters):
+                self.allreduce()
+            e1.record(); torch.cuda.synchronize(self.flat.device)
+            t = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64, device=self.flat.device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+            times[name] = float(t.item())
+        best = min(times, key=times.get)
+        self.multicast = self._multicast_addr if best == "multimem" else 0
+        self.calibration = dict(times_ms=times, chosen=best)
+        self.check()
+
+    def allreduce(self, ctas=None):
         """in-place sum over the ranks, on the current stream; every rank calls it once per step"""
         lib = _lib.load()
         with torch.cuda.device(self.flat.device):
             _lib.check(lib.rr_allreduce_sum_f32(torch.cuda.current_stream().cuda_stream, self.rank, self.world, self.numel, self._bufs,
-                                                self.multicast or None, self._sigs, self.error.data_ptr(), self.epoch, int(ctas)), "rr_allreduce_sum_f32")
+                                                self.multicast or None, self._sigs, self.error.data_ptr(), self.epoch,
+                                                self.ctas if ctas is None else int(ctas)), "rr_allreduce_sum_f32")
         self.epoch = (self.epoch + 2) & 0x7FFFFFFF
         return self.flat
 

@@ -19,6 +19,20 @@ struct PreprocessArgs {
 	int tile_cull;
 };
 int launch_preprocess_fwd(cudaStream_t, const PreprocessArgs&);
+
+// view-batched forward preprocess (preprocess.cu): SH colour + scale / rotation mode only, M = 16
+constexpr int PV_MAX_VIEWS = 16;
+struct PreprocessViewsArgs {
+	int P, D, W, H, grid_x, grid_y, nviews, write_cov3D;
+	float scale_modifier, low_pass;
+	const float *means3D, *scales, *rotations, *opacities, *shs;
+	const float* view[PV_MAX_VIEWS]; const float* proj[PV_MAX_VIEWS]; const float* campos[PV_MAX_VIEWS];
+	float tan_fovx[PV_MAX_VIEWS], tan_fovy[PV_MAX_VIEWS];
+	int* radii[PV_MAX_VIEWS];
+	char* geom[PV_MAX_VIEWS];             // each view's geometry blob; the arrays below sit at the same byte offsets in every one
+	size_t off_rec, off_cov3D, off_clamped, off_tiles, off_rect, off_key;
+};
+int launch_preprocess_views(cudaStream_t, const PreprocessViewsArgs&);
 int launch_mark_visible(cudaStream_t, int P, const float* means3D, const float* view, uint8_t* present);
 
 // binning.cu

@@ -111,9 +111,11 @@ def test_unmodified_render_matches_reference_cuda(device, refcuda, refmods, conv
     if compute_cov:
         cov = pc.get_covariance(1.0)
         kw["cov3D_precomp"] = cov.detach().contiguous()
+    # .contiguous() as the reference's own binding applies it (rasterize_points.cu:85-104): MiniCam.camera_center is a strided
+    # slice of torch.inverse's column-major result
     N_r, color_r, radii_r, depth_r = refcuda.forward(bg, pc.get_xyz.detach(), det["opacity"], None if compute_cov else det["scales"],
-                                                     None if compute_cov else det["rotations"], cam.world_view_transform, cam.full_proj_transform,
-                                                     cam.camera_center, tanfovx, tanfovy, H, W, sh_degree=D, **kw)
+                                                     None if compute_cov else det["rotations"], cam.world_view_transform.contiguous(), cam.full_proj_transform.contiguous(),
+                                                     cam.camera_center.contiguous(), tanfovx, tanfovy, H, W, sh_degree=D, **kw)
     g_r = refcuda.backward(dpix)
     again = refcuda.backward(dpix)
     assert N_r > 0
@@ -165,10 +167,10 @@ def test_unmodified_create_from_pcd_and_mark_visible(device, refcuda, refmods):
     bg = torch.zeros(3, device=device)
     out = refmods.render(cam, pc, pipe, bg)
     N_r, color_r, radii_r, depth_r = refcuda.forward(bg, pc.get_xyz.detach(), pc.get_opacity.detach(), pc.get_scaling.detach(), pc.get_rotation.detach(),
-                                                     cam.world_view_transform, cam.full_proj_transform, cam.camera_center, math.tan(fovx * 0.5), math.tan(fovy * 0.5),
-                                                     H, W, shs=pc.get_features.detach().contiguous(), sh_degree=0)
+                                                     cam.world_view_transform.contiguous(), cam.full_proj_transform.contiguous(), cam.camera_center.contiguous(),
+                                                     math.tan(fovx * 0.5), math.tan(fovy * 0.5), H, W, shs=pc.get_features.detach().contiguous(), sh_degree=0)
     assert torch.equal(out["radii"], radii_r) and torch.equal(out["render"].detach(), color_r)
     rs = refmods.dgr.GaussianRasterizationSettings(H, W, math.tan(fovx * 0.5), math.tan(fovy * 0.5), bg, 1.0, cam.world_view_transform, cam.full_proj_transform,
                                                    0, cam.camera_center, False, False, 0.3)
     vis = refmods.dgr.GaussianRasterizer(rs).markVisible(pc.get_xyz)
-    assert torch.equal(vis, refcuda.mark_visible(pc.get_xyz.detach(), cam.world_view_transform, cam.full_proj_transform))
+    assert torch.equal(vis, refcuda.mark_visible(pc.get_xyz.detach(), cam.world_view_transform.contiguous(), cam.full_proj_transform.contiguous()))

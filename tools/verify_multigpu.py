@@ -61,10 +61,13 @@ def main():
     if rank == 0:
         alone, stats1, _ = step(0, 1)             # all V views on this rank, no collective
         stats1.sync("skip")
+        # 1e-5 at small sizes; at 1M Gaussians the order of the fp32 view sums alone moves dL_dscale / dL_drot by a few 1e-5 of
+        # max (tests/test_gpu_parity.py::test_accumulate_mode_and_multiview_bucket), so the north star's 1e-4 applies there
+        tol = 1e-5 if P < 100_000 else 1e-4
         for k in mv.SEGMENTS:
             e = rel(bucket.views[k], alone.views[k])
             report[f"rel_err_{k}"] = e
-            ok = ok and e <= 1e-5
+            ok = ok and e <= tol
         for k in ("max_radii2D", "xyz_gradient_accum", "denom"):
             e = rel(getattr(stats, k), getattr(stats1, k))
             report[f"rel_err_{k}"] = e
