@@ -29,6 +29,7 @@ extern "C" {
 
 #define RR_BWD_ACCUMULATE 1
 #define RR_BWD_LEAF 2        /* rr_backward_views: inputs are the raw leaf tensors, gradients w.r.t. them */
+#define RR_GEOM_KEEP_COV3D 1 /* rr_forward_geom_views: also store the 3D covariance in every view's blob (the per-view rr_backward reads it) */
 
 const char* rr_last_error(void);
 int rr_version(void);
@@ -62,6 +63,18 @@ int rr_forward_geom(void* stream, int P, int D, int M, int W, int H,
 	const float* viewmatrix, const float* projmatrix, const float* campos,
 	float tan_fovx, float tan_fovy, float low_pass, int prefiltered, int debug,
 	int* radii, void* geom, size_t geom_bytes, int64_t* num_rendered_host);
+
+/* rr_forward_geom for ALL nviews views of a step in one set of launches (no reference counterpart: the reference runs its
+ * preprocess, scan and sort once per view): one pass over the Gaussians that reads the parameters once and projects them
+ * through every camera, the nviews depth sorts as one segmented onesweep, the nviews prefix sums as one launch.  Every array
+ * argument is a HOST array of nviews entries (viewmatrix / projmatrix / campos / radii / geom: device pointers; tan_fovx /
+ * tan_fovy: floats; num_rendered_host[v]: pinned host int64 receiving view v's count).  Each view's outputs (radii[v], its
+ * geometry blob) are bit-identical to rr_forward_geom's for that camera.  SH colours + scales / rotations only, M = 16,
+ * nviews <= 16; flags: RR_GEOM_KEEP_COV3D. */
+int rr_forward_geom_views(void* stream, int P, int D, int M, int W, int H, int nviews,
+	const float* const* viewmatrix, const float* const* projmatrix, const float* const* campos, const float* tan_fovx, const float* tan_fovy,
+	const float* means3D, const float* shs, const float* opacities, const float* scales, float scale_modifier, const float* rotations, float low_pass,
+	int* const* radii, void* const* geom, size_t geom_bytes, int64_t* const* num_rendered_host, int flags, int debug);
 
 /* Forward, second half — replaces duplicateWithKeys + cub SortPairs + identifyTileRanges + FORWARD::render
  * (rasterizer_impl.cu:275-328).  out_color[3,H,W], out_depth[1,H,W]. */

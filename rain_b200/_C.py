@@ -97,6 +97,58 @@ def forward_geom(background, means3D, colors, opacity, scales, rotations, scale_
     return st
 
 
+def forward_geom_views(background, means3D, opacity, scales, rotations, scale_modifier, cams, image_height, image_width, sh, degree,
+                       debug, low_pass, stream=None, keep_cov3D=False):
+    """forward_geom for ALL views of a batch in one set of launches (rr_forward_geom_views: one pass over the Gaussians for
+    every camera, one segmented depth sort, one segmented scan).  cams: list (at most 16) of objects with viewmatrix,
+    projmatrix, campos, tanfovx, tanfovy.  Returns one forward-pass state per view, each to be completed with forward_bin /
+    forward_render (or forward_raster) exactly like forward_geom's; their outputs are bit-identical to the per-view call's.
+    SH colours + scales / rotations only (M = 16).  keep_cov3D: also store the 3D covariance per view (needed only if the
+    per-view rasterize_gaussians_backward will be used on these states)."""
+    import ctypes
+    lib = _lib.load()
+    if not means3D.is_cuda:
+        raise RuntimeError("rain_b200 has no CPU path: means3D must be a CUDA tensor")
+    dev = means3D.device
+    P, H, W, n = means3D.size(0), int(image_height), int(image_width), len(cams)
+    byte = dict(dtype=torch.uint8, device=dev)
+    means3D_c, bg, opac, scales_c, rots, sh_c = (_f32c(t, dev) for t in (means3D, background, opacity, scales, rotations, sh))
+    M = sh.size(1) if (sh is not None and sh.numel() != 0) else 0
+    states = []
+    for cam in cams:
+        st = _GeomPass()
+        st.P, st.H, st.W, st.dev, st.debug, st.bg = P, H, W, dev, bool(debug), bg
+        states.append(st)
+    if P == 0 or n == 0:
+        return states
+    mats = [[_f32c(getattr(c, k), dev) for k in ("viewmatrix", "projmatrix", "campos")] for c in cams]
+    gbytes = lib.rr_geom_bytes(P)
+    for st in states:
+        st.out_color = torch.empty((NUM_CHANNELS, H, W), dtype=torch.float32, device=dev)
+        st.out_depth = torch.empty((1, H, W), dtype=torch.float32, device=dev)
+        st.radii = torch.empty((P,), dtype=torch.int32, device=dev)
+        st.geom = torch.empty(gbytes, **byte)
+        st.img = torch.empty(lib.rr_image_bytes(W, H), **byte)
+        st.nr = _take_slot(dev)
+        st.keep = (means3D_c, opac, scales_c, rots, sh_c, mats)
+    vp = ctypes.c_void_p
+    arr = lambda xs: (vp * n)(*xs)
+    with torch.cuda.device(dev):
+        s = torch.cuda.current_stream() if stream is None else stream
+        _lib.check(lib.rr_forward_geom_views(
+            s.cuda_stream, P, int(degree), M, W, H, n,
+            arr([m[0].data_ptr() for m in mats]), arr([m[1].data_ptr() for m in mats]), arr([m[2].data_ptr() for m in mats]),
+            (ctypes.c_float * n)(*[float(c.tanfovx) for c in cams]), (ctypes.c_float * n)(*[float(c.tanfovy) for c in cams]),
+            means3D_c.data_ptr(), sh_c.data_ptr(), opac.data_ptr(), scales_c.data_ptr(), float(scale_modifier), rots.data_ptr(), float(low_pass),
+            arr([st.radii.data_ptr() for st in states]), arr([st.geom.data_ptr() for st in states]), gbytes,
+            arr([st.nr.data_ptr() for st in states]), 1 if keep_cov3D else 0, int(bool(debug))), "rr_forward_geom_views")
+        ev = torch.cuda.Event()
+        ev.record(s)
+    for st in states:
+        st.stream, st.event = s, ev
+    return states
+
+
 def forward_raster(st):
     """Second half of RasterizeGaussiansCUDA: waits for num_rendered (it sizes the binning blob; the reference blocks on a
     cudaMemcpy here, rasterizer_impl.cu:273), then duplicate / tile sort / ranges / render.

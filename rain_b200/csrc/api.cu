@@ -267,6 +267,61 @@ int rr_forward_geom(void* stream_, int P, int D, int M, int W, int H,
 	return check_launch("forward_geom", stream, debug != 0);
 }
 
+int rr_forward_geom_views(void* stream_, int P, int D, int M, int W, int H, int nviews,
+	const float* const* viewmatrix, const float* const* projmatrix, const float* const* campos, const float* tan_fovx, const float* tan_fovy,
+	const float* means3D, const float* shs, const float* opacities, const float* scales, float scale_modifier, const float* rotations, float low_pass,
+	int* const* radii, void* const* geom, size_t geom_bytes, int64_t* const* num_rendered_host, int flags, int debug)
+{
+	cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+	if (nviews == 0) return 0;
+	if (nviews < 0 || nviews > PV_MAX_VIEWS) { set_error("rr_forward_geom_views: %d views (1..%d per call)", nviews, PV_MAX_VIEWS); return -1; }
+	if (bad_ptr(num_rendered_host, "num_rendered_host")) return -1;
+	for (int v = 0; v < nviews; v++) { if (bad_ptr(num_rendered_host[v], "num_rendered_host[v]")) return -1; *num_rendered_host[v] = 0; }
+	if (P == 0) return 0;
+	if (P < 0 || W <= 0 || H <= 0) { set_error("bad sizes P=%d W=%d H=%d", P, W, H); return -1; }
+	if (M != 16 || D < 0 || D > 3) { set_error("rr_forward_geom_views needs M = 16 SH coefficients and degree 0..3 (M=%d, D=%d)", M, D); return -1; }
+	if (tile_cull_wanted()) { set_error("rr_forward_geom_views does not support RAIN_TILE_CULL=1 (use rr_forward_geom per view)"); return -1; }
+	if (bad_ptr(viewmatrix, "viewmatrix") || bad_ptr(projmatrix, "projmatrix") || bad_ptr(campos, "campos") || bad_ptr(tan_fovx, "tan_fovx") || bad_ptr(tan_fovy, "tan_fovy") ||
+		bad_ptr(means3D, "means3D") || bad_ptr(shs, "shs") || bad_ptr(opacities, "opacities") || bad_ptr(scales, "scales") || bad_ptr(rotations, "rotations") ||
+		bad_ptr(radii, "radii") || bad_ptr(geom, "geom")) return -1;
+	const GeomLayout L0 = geom_layout(nullptr, P);
+	if (L0.total > geom_bytes) { set_error("geometry blob too small: %zu < %zu", geom_bytes, L0.total); return -1; }
+	PreprocessViewsArgs a; memset(&a, 0, sizeof(a));
+	a.P = P; a.D = D; a.W = W; a.H = H; a.grid_x = (W + TILE_X - 1) / TILE_X; a.grid_y = (H + TILE_Y - 1) / TILE_Y; a.nviews = nviews;
+	a.write_cov3D = (flags & RR_GEOM_KEEP_COV3D) ? 1 : 0;
+	a.scale_modifier = scale_modifier; a.low_pass = low_pass;
+	a.means3D = means3D; a.scales = scales; a.rotations = rotations; a.opacities = opacities; a.shs = shs;
+	// byte offsets of the arrays inside a geometry blob (the layout carved from a null base)
+	a.off_rec = reinterpret_cast<uintptr_t>(L0.rec); a.off_cov3D = reinterpret_cast<uintptr_t>(L0.cov3D); a.off_clamped = reinterpret_cast<uintptr_t>(L0.clamped);
+	a.off_tiles = reinterpret_cast<uintptr_t>(L0.tiles_touched); a.off_rect = reinterpret_cast<uintptr_t>(L0.rect); a.off_key = reinterpret_cast<uintptr_t>(L0.key_a);
+	uint32_t *ka[PV_MAX_VIEWS], *kb[PV_MAX_VIEWS], *va[PV_MAX_VIEWS], *vb[PV_MAX_VIEWS];
+	void* sws[PV_MAX_VIEWS];
+	ScanSegs sg; memset(&sg, 0, sizeof(sg));
+	for (int v = 0; v < nviews; v++) {
+		if (bad_ptr(viewmatrix[v], "viewmatrix[v]") || bad_ptr(projmatrix[v], "projmatrix[v]") || bad_ptr(campos[v], "campos[v]") || bad_ptr(radii[v], "radii[v]") ||
+			bad_ptr(geom[v], "geom[v]")) return -1;
+		a.view[v] = viewmatrix[v]; a.proj[v] = projmatrix[v]; a.campos[v] = campos[v]; a.tan_fovx[v] = tan_fovx[v]; a.tan_fovy[v] = tan_fovy[v];
+		a.radii[v] = radii[v]; a.geom[v] = reinterpret_cast<char*>(geom[v]);
+		const GeomLayout L = geom_layout(geom[v], P);
+		ka[v] = L.key_a; kb[v] = L.key_b; va[v] = L.val_a; vb[v] = L.val_b; sws[v] = L.sort_ws;
+		uint32_t* mapped = nullptr;
+		cudaPointerAttributes pa;
+		if (cudaPointerGetAttributes(&pa, num_rendered_host[v]) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer) mapped = reinterpret_cast<uint32_t*>(pa.devicePointer);
+		else (void)cudaGetLastError();
+		sg.order[v] = L.val_a; sg.tiles_touched[v] = L.tiles_touched; sg.status[v] = L.block_sums; sg.offsets[v] = L.offsets; sg.total[v] = L.num_rendered; sg.total_host[v] = mapped;
+	}
+	{ Stage st(stream, ST_PREPROCESS); if (launch_preprocess_views(stream, a)) return -1; }
+	if (debug && check_launch("preprocess_views", stream, true)) return -1;
+	int which;
+	{ Stage st(stream, ST_DEPTH_SORT); which = sort_pairs_segments<uint32_t>(stream, nviews, ka, kb, va, vb, (size_t)P, 0, 32, sws, true); }
+	if (which != 0) { if (which > 0) set_error("internal: depth sort landed in the wrong buffer"); return -1; }
+	if (debug && check_launch("depth sort", stream, true)) return -1;
+	{ Stage st(stream, ST_SCAN); if (launch_scan_tiles_segments(stream, P, nviews, sg)) return -1; }
+	for (int v = 0; v < nviews; v++)
+		if (!sg.total_host[v]) cudaMemcpyAsync(num_rendered_host[v], sg.total[v], sizeof(uint32_t), cudaMemcpyDeviceToHost, stream);
+	return check_launch("forward_geom_views", stream, debug != 0);
+}
+
 int rr_forward_bin(void* stream_, int P, int W, int H, int64_t N,
 	void* geom, size_t geom_bytes, void* binning, size_t binning_bytes, void* image, size_t image_bytes, int debug)
 {

@@ -8,6 +8,7 @@
 // (tile, depth, index) order: ties in (tile, depth) keep ascending Gaussian index in both schemes, because both
 // sorts are stable and the depth sort starts from index order.  The 64-bit key list the reference would hold is
 // reconstructed on demand by export_keys_kernel for the parity tests.
+#include <cstring>
 #include "common.cuh"
 #include "kernels.cuh"
 
@@ -45,10 +46,15 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* s
 // cub::DeviceScan::InclusiveSum (rasterizer_impl.cu:269), in ONE launch: chained scan with decoupled look-back.  Blocks
 // take tile ids from an atomic ticket (a block's predecessors are therefore always running or done), publish their tile
 // aggregate in a status word, and warp 0 looks back over 32 predecessors per step until it meets an inclusive prefix.
-__global__ void __launch_bounds__(SCAN_THREADS) scan_chained_kernel(int P, int nb, const uint32_t* __restrict__ order, const uint32_t* __restrict__ tt,
-	volatile uint32_t* __restrict__ status /*[nb] + ticket at [nb], zero on entry*/, uint32_t* __restrict__ offsets /*inclusive, depth order*/,
-	uint32_t* __restrict__ total, uint32_t* __restrict__ total_host)
+// blockIdx.y = segment: the scans of all views of a step run as one launch (ScanSegs, kernels.cuh).
+__global__ void __launch_bounds__(SCAN_THREADS) scan_chained_kernel(int P, int nb, ScanSegs sg)
 {
+	const uint32_t* __restrict__ order = sg.order[blockIdx.y];
+	const uint32_t* __restrict__ tt = sg.tiles_touched[blockIdx.y];
+	volatile uint32_t* __restrict__ status = sg.status[blockIdx.y];      // [nb] + ticket at [nb], zero on entry
+	uint32_t* __restrict__ offsets = sg.offsets[blockIdx.y];             // inclusive, depth order
+	uint32_t* __restrict__ total = sg.total[blockIdx.y];
+	uint32_t* __restrict__ total_host = sg.total_host[blockIdx.y];
 	__shared__ uint32_t s_warp[SCAN_THREADS / 32];
 	__shared__ uint32_t s_tile, s_excl;
 	if (threadIdx.x == 0) s_tile = atomicAdd(const_cast<uint32_t*>(status) + nb, 1u);
@@ -208,14 +214,22 @@ __global__ void __launch_bounds__(128) export_keys_kernel(int T, const uint2* __
 
 size_t scan_ws_elems(int P) { return (size_t)(P + SCAN_TILE - 1) / SCAN_TILE + 1; }
 
+int launch_scan_tiles_segments(cudaStream_t stream, int P, int nseg, const ScanSegs& sg)
+{
+	if (nseg == 0) return 0;
+	if (P == 0) { for (int g = 0; g < nseg; g++) cudaMemsetAsync(sg.total[g], 0, sizeof(uint32_t), stream); return 0; }
+	const int nb = (P + SCAN_TILE - 1) / SCAN_TILE;
+	for (int g = 0; g < nseg; g++) cudaMemsetAsync(sg.status[g], 0, sizeof(uint32_t) * (size_t)(nb + 1), stream);
+	count_launch(), scan_chained_kernel<<<dim3(nb, nseg), SCAN_THREADS, 0, stream>>>(P, nb, sg);
+	return check_launch("scan_tiles", stream, false);
+}
+
 int launch_scan_tiles(cudaStream_t stream, int P, const uint32_t* order, const uint32_t* tt, uint32_t* offsets, uint32_t* block_sums, uint32_t* num_rendered_dev,
 	uint32_t* num_rendered_mapped)
 {
-	if (P == 0) { cudaMemsetAsync(num_rendered_dev, 0, sizeof(uint32_t), stream); return 0; }
-	const int nb = (P + SCAN_TILE - 1) / SCAN_TILE;
-	cudaMemsetAsync(block_sums, 0, sizeof(uint32_t) * (size_t)(nb + 1), stream);
-	count_launch(), scan_chained_kernel<<<nb, SCAN_THREADS, 0, stream>>>(P, nb, order, tt, block_sums, offsets, num_rendered_dev, num_rendered_mapped);
-	return check_launch("scan_tiles", stream, false);
+	ScanSegs sg; memset(&sg, 0, sizeof(sg));
+	sg.order[0] = order; sg.tiles_touched[0] = tt; sg.status[0] = block_sums; sg.offsets[0] = offsets; sg.total[0] = num_rendered_dev; sg.total_host[0] = num_rendered_mapped;
+	return launch_scan_tiles_segments(stream, P, 1, sg);
 }
 
 int launch_duplicate(cudaStream_t stream, int P, const uint32_t* order, const uint32_t* offsets, const uint2* rect, const unsigned long long* tile_mask,

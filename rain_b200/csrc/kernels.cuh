@@ -39,6 +39,11 @@ int launch_mark_visible(cudaStream_t, int P, const float* means3D, const float* 
 size_t scan_ws_elems(int P);
 int launch_scan_tiles(cudaStream_t, int P, const uint32_t* order, const uint32_t* tiles_touched, uint32_t* offsets /*inclusive, depth order*/,
 	uint32_t* block_sums, uint32_t* num_rendered_dev, uint32_t* num_rendered_mapped /*device-visible alias of a pinned host word, or null*/);
+// the prefix sums of up to 16 views as one launch (blockIdx.y = view)
+struct ScanSegs {
+	const uint32_t* order[16]; const uint32_t* tiles_touched[16]; uint32_t* status[16]; uint32_t* offsets[16]; uint32_t* total[16]; uint32_t* total_host[16];
+};
+int launch_scan_tiles_segments(cudaStream_t, int P, int nseg, const ScanSegs&);
 int launch_duplicate(cudaStream_t, int P, const uint32_t* order, const uint32_t* offsets, const uint2* rect, const unsigned long long* tile_mask /*or null*/, int grid_x,
 	uint32_t* tile_keys /*[N] emission order*/, uint32_t* gaussian_ids /*[N] emission order*/);
 int launch_tile_ranges(cudaStream_t, size_t N, const uint32_t* sorted_tile_keys, uint2* ranges, int num_tiles);

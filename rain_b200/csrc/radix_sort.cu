@@ -11,6 +11,7 @@
 //      flags in the top two bits), reorders the tile through shared memory so the global scatter is written in runs,
 //      and writes keys and values to the other buffer.
 // Memory traffic per pass: read 1x + write 1x of (key,value); histogram: read keys once.
+#include <cstring>
 #include "common.cuh"
 #include "radix_sort.cuh"
 
@@ -41,6 +42,15 @@ template <class K> __device__ __forceinline__ uint32_t digit_of(K key, int shift
 
 struct PassDesc { int shift[MAX_PASSES]; uint32_t mask[MAX_PASSES]; int npass; };
 
+// Up to SORT_MAX_SEGS independent sorts of the same length and bit range run as ONE set of launches (blockIdx.y = segment):
+// the depth sorts of all views of a step (1M keys each are latency bound at 245 CTAs per pass; eight of them together fill
+// the GPU).  A plain sort is one segment.
+template <class K> struct SegPtrs {
+	K* keys_a[SORT_MAX_SEGS]; K* keys_b[SORT_MAX_SEGS];
+	uint32_t* vals_a[SORT_MAX_SEGS]; uint32_t* vals_b[SORT_MAX_SEGS];
+	uint32_t* ghist[SORT_MAX_SEGS]; uint32_t* tickets[SORT_MAX_SEGS]; uint32_t* status[SORT_MAX_SEGS];
+};
+
 // Lanes of the warp holding the same digit as this lane, built from one ballot per digit bit.  (match.any does this
 // in one instruction, but on sm_100a it is a slow MIO-queue operation: the first version of this kernel spent 58 % of
 // its stall samples waiting on MATCH results — profiles/r01_v0_ncu_full_summary.csv — whereas VOTE + LOP3 pipeline.)
@@ -60,8 +70,10 @@ __device__ __forceinline__ unsigned same_digit_lanes(uint32_t d, bool valid, int
 
 // ---- 1. histograms of all passes ------------------------------------------------------------------------------
 template <class K>
-__global__ void __launch_bounds__(SORT_THREADS) histogram_kernel(const K* __restrict__ keys, uint32_t n, PassDesc pd, uint32_t* __restrict__ ghist)
+__global__ void __launch_bounds__(SORT_THREADS) histogram_kernel(SegPtrs<K> sp, uint32_t n, PassDesc pd)
 {
+	const K* __restrict__ keys = sp.keys_a[blockIdx.y];
+	uint32_t* __restrict__ ghist = sp.ghist[blockIdx.y];
 	constexpr int HV = 4;                       // keys in flight per thread and iteration (independent loads)
 	__shared__ uint32_t sh[MAX_PASSES * RADIX];
 	for (int i = threadIdx.x; i < pd.npass * RADIX; i += SORT_THREADS) sh[i] = 0;
@@ -99,10 +111,11 @@ __global__ void __launch_bounds__(SORT_THREADS) histogram_kernel(const K* __rest
 }
 
 // ---- 2. exclusive scan of each 256-bin histogram (one CTA per pass) ---------------------------------------------
-__global__ void __launch_bounds__(RADIX) digit_base_kernel(uint32_t* __restrict__ ghist)
+template <class K>
+__global__ void __launch_bounds__(RADIX) digit_base_kernel(SegPtrs<K> sp)
 {
 	__shared__ uint32_t warp_tot[RADIX / 32];
-	uint32_t* h = ghist + blockIdx.x * RADIX;
+	uint32_t* h = sp.ghist[blockIdx.y] + blockIdx.x * RADIX;
 	const uint32_t v = h[threadIdx.x];
 	uint32_t inc = v;
 	#pragma unroll
@@ -116,14 +129,17 @@ __global__ void __launch_bounds__(RADIX) digit_base_kernel(uint32_t* __restrict_
 
 // ---- 3. one onesweep pass ---------------------------------------------------------------------------------------
 template <class K, int IPT, bool MATCH_OR>
-__global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(
-	const K* __restrict__ keys_in, K* __restrict__ keys_out,
-	const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
-	uint32_t n, int shift, uint32_t mask,
-	const uint32_t* __restrict__ digit_base,   // [RADIX] exclusive global base of each digit
-	uint32_t* __restrict__ ticket,             // dynamic tile id
-	volatile uint32_t* __restrict__ status)    // [ntiles][RADIX]
+__global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp, int pass, bool iota_vals, uint32_t n, uint32_t ntiles, int shift, uint32_t mask)
 {
+	// this segment's buffers: even passes read the *_a buffers and write *_b, odd passes the other way round
+	const int seg = blockIdx.y;
+	const K* __restrict__ keys_in = (pass & 1) ? sp.keys_b[seg] : sp.keys_a[seg];
+	K* __restrict__ keys_out = (pass & 1) ? sp.keys_a[seg] : sp.keys_b[seg];
+	const uint32_t* __restrict__ vals_in = (pass == 0 && iota_vals) ? nullptr : ((pass & 1) ? sp.vals_b[seg] : sp.vals_a[seg]);
+	uint32_t* __restrict__ vals_out = (pass & 1) ? sp.vals_a[seg] : sp.vals_b[seg];
+	const uint32_t* __restrict__ digit_base = sp.ghist[seg] + pass * RADIX;                       // [RADIX] exclusive global base of each digit
+	uint32_t* __restrict__ ticket = sp.tickets[seg] + pass;                                       // dynamic tile id
+	volatile uint32_t* __restrict__ status = sp.status[seg] + (size_t)pass * ntiles * RADIX;      // [ntiles][RADIX]
 	constexpr int TILE = SORT_THREADS * IPT;
 	constexpr int WARP_ITEMS = 32 * IPT;
 	__shared__ uint32_t s_tile;
@@ -312,41 +328,53 @@ size_t sort_ws_bytes(size_t n, int begin_bit, int end_bit) {
 }
 
 template <class K>
-int sort_pairs(cudaStream_t stream, K* keys_a, K* keys_b, uint32_t* vals_a, uint32_t* vals_b, size_t n,
-	int begin_bit, int end_bit, void* ws, bool iota_vals)
+int sort_pairs_segments(cudaStream_t stream, int nseg, K* const* keys_a, K* const* keys_b, uint32_t* const* vals_a, uint32_t* const* vals_b, size_t n,
+	int begin_bit, int end_bit, void* const* ws, bool iota_vals)
 {
-	if (n == 0) return 0;
+	if (n == 0 || nseg == 0) return 0;
+	if (nseg < 0 || nseg > SORT_MAX_SEGS) { set_error("sort_pairs: %d segments (at most %d)", nseg, SORT_MAX_SEGS); return -1; }
 	if (n >= (size_t)VALUE_MASK) { set_error("sort_pairs: n=%zu exceeds the 2^30-1 item limit of the look-back status word", n); return -1; }
 	if (end_bit <= begin_bit || end_bit > (int)sizeof(K) * 8 || (end_bit - begin_bit + RADIX_BITS - 1) / RADIX_BITS > MAX_PASSES) {
 		set_error("sort_pairs: bad bit range [%d,%d)", begin_bit, end_bit); return -1;
 	}
 	constexpr int IPT = Cfg<K>::IPT;
 	const PassDesc pd = make_passes(begin_bit, end_bit);
-	const WsLayout L = ws_layout<K>(ws, n, pd.npass);
-	cudaMemsetAsync(ws, 0, L.zero_bytes, stream);
+	SegPtrs<K> sp;
+	memset(&sp, 0, sizeof(sp));
+	uint32_t ntiles = 0;
+	for (int g = 0; g < nseg; g++) {
+		const WsLayout L = ws_layout<K>(ws[g], n, pd.npass);
+		cudaMemsetAsync(ws[g], 0, L.zero_bytes, stream);
+		sp.keys_a[g] = keys_a[g]; sp.keys_b[g] = keys_b[g]; sp.vals_a[g] = vals_a[g]; sp.vals_b[g] = vals_b[g];
+		sp.ghist[g] = L.ghist; sp.tickets[g] = L.tickets; sp.status[g] = L.status;
+		ntiles = L.ntiles;
+	}
 	// ranking variant: shared-memory atomicOr match for large inputs (measured 0.196 vs 0.218 ms on the 8.4M-pair tile sort),
 	// ballot match for small ones (0.088 vs 0.096 ms on the 1M-key depth sort)
-	const bool match_or = true;
+	const bool match_or = n >= (1u << 22);
 	const uint32_t hgrid = (uint32_t)((n + SORT_THREADS * 16 - 1) / (SORT_THREADS * 16));
-	count_launch(), histogram_kernel<K><<<hgrid < 1184u ? hgrid : 1184u, SORT_THREADS, 0, stream>>>(keys_a, (uint32_t)n, pd, L.ghist);
-	count_launch(), digit_base_kernel<<<pd.npass, RADIX, 0, stream>>>(L.ghist);
-	K* kin = keys_a; K* kout = keys_b;
-	uint32_t* vin = vals_a; uint32_t* vout = vals_b;
+	const uint32_t hcap = nseg > 1 ? (1184u + nseg - 1) / nseg : 1184u;
+	count_launch(), histogram_kernel<K><<<dim3(hgrid < hcap ? hgrid : hcap, nseg), SORT_THREADS, 0, stream>>>(sp, (uint32_t)n, pd);
+	count_launch(), digit_base_kernel<K><<<dim3(pd.npass, nseg), RADIX, 0, stream>>>(sp);
 	for (int p = 0; p < pd.npass; p++) {
-		if (match_or && n >= (1u << 22)) count_launch(), onesweep_kernel<K, IPT, true><<<L.ntiles, SORT_THREADS, 0, stream>>>(kin, kout, (p == 0 && iota_vals) ? nullptr : vin, vout,
-			(uint32_t)n, pd.shift[p], pd.mask[p], L.ghist + p * RADIX, L.tickets + p, L.status + (size_t)p * L.ntiles * RADIX);
-		else count_launch(), onesweep_kernel<K, IPT, false><<<L.ntiles, SORT_THREADS, 0, stream>>>(kin, kout, (p == 0 && iota_vals) ? nullptr : vin, vout,
-			(uint32_t)n, pd.shift[p], pd.mask[p], L.ghist + p * RADIX, L.tickets + p, L.status + (size_t)p * L.ntiles * RADIX);
-		K* tk = kin; kin = kout; kout = tk;
-		uint32_t* tv = vin; vin = vout; vout = tv;
+		if (match_or) count_launch(), onesweep_kernel<K, IPT, true><<<dim3(ntiles, nseg), SORT_THREADS, 0, stream>>>(sp, p, iota_vals, (uint32_t)n, ntiles, pd.shift[p], pd.mask[p]);
+		else count_launch(), onesweep_kernel<K, IPT, false><<<dim3(ntiles, nseg), SORT_THREADS, 0, stream>>>(sp, p, iota_vals, (uint32_t)n, ntiles, pd.shift[p], pd.mask[p]);
 	}
 	if (check_launch("sort_pairs", stream, false)) return -1;
 	return pd.npass & 1;   // odd number of passes -> result sits in the *_b buffers
+}
+
+template <class K>
+int sort_pairs(cudaStream_t stream, K* keys_a, K* keys_b, uint32_t* vals_a, uint32_t* vals_b, size_t n,
+	int begin_bit, int end_bit, void* ws, bool iota_vals)
+{
+	return sort_pairs_segments<K>(stream, 1, &keys_a, &keys_b, &vals_a, &vals_b, n, begin_bit, end_bit, &ws, iota_vals);
 }
 
 template size_t sort_ws_bytes<uint32_t>(size_t, int, int);
 template size_t sort_ws_bytes<uint64_t>(size_t, int, int);
 template int sort_pairs<uint32_t>(cudaStream_t, uint32_t*, uint32_t*, uint32_t*, uint32_t*, size_t, int, int, void*, bool);
 template int sort_pairs<uint64_t>(cudaStream_t, uint64_t*, uint64_t*, uint32_t*, uint32_t*, size_t, int, int, void*, bool);
+template int sort_pairs_segments<uint32_t>(cudaStream_t, int, uint32_t* const*, uint32_t* const*, uint32_t* const*, uint32_t* const*, size_t, int, int, void* const*, bool);
 
 }  // namespace rr

@@ -15,4 +15,11 @@ template <class K>
 int sort_pairs(cudaStream_t stream, K* keys_a, K* keys_b, uint32_t* vals_a, uint32_t* vals_b, size_t n,
 	int begin_bit, int end_bit, void* ws, bool iota_vals);
 
+// nseg independent sorts of the same length and bit range as ONE set of launches (blockIdx.y = segment); arrays of nseg
+// pointers (host memory); same return value as sort_pairs (all segments land in the same buffers).
+constexpr int SORT_MAX_SEGS = 16;
+template <class K>
+int sort_pairs_segments(cudaStream_t stream, int nseg, K* const* keys_a, K* const* keys_b, uint32_t* const* vals_a, uint32_t* const* vals_b, size_t n,
+	int begin_bit, int end_bit, void* const* ws, bool iota_vals);
+
 }  // namespace rr

@@ -89,7 +89,7 @@ class ViewResult:
 def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int], bucket: GradientBucket,
                          grad_fn: Callable[[int, torch.Tensor, torch.Tensor], torch.Tensor], *, bg: torch.Tensor, sh_degree: int,
                          scale_modifier: float = 1.0, low_pass: float = 0.3, debug: bool = False, keep_outputs: bool = True,
-                         pipeline: str = "two_stream", batch_backward: int = 8, stats=None, backend=_native) -> List[ViewResult]:
+                         pipeline: str = "two_stream", batch_backward: int = 8, batch_forward: int = 8, stats=None, backend=_native) -> List[ViewResult]:
     """Forward + backward of this rank's views; parameter gradients of all views are summed into ``bucket``.
 
     params: dict(means3D[P,3], opacities[P,1], shs[P,M,3], scales[P,3], rotations[P,4]) — activated values, as
@@ -103,74 +103,86 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
     batch_backward = B > 0 (default 8): the per-Gaussian half of the backward runs ONCE per B views (rr_backward_views: parameters
     read once, bucket row written once, the views' accumulator records summed in registers) instead of once per view; per view
     only the backward tile renderer runs (rr_backward_render).  0 restores the per-view rr_backward with RR_BWD_ACCUMULATE.
+    batch_forward = B > 0 (default 8): the per-Gaussian half of the forward — preprocess, depth sort, prefix sum — runs ONCE per
+    B views (rr_forward_geom_views: parameters read once and projected through every camera, one segmented sort, one segmented
+    scan; per-view outputs bit-identical to the per-view call's).  0 restores one rr_forward_geom per view.
     stats: optional rain_b200.optim.DensificationStats; the batched backward folds the views' densification statistics into
     its per-step delta in the same pass (otherwise call stats.add_view per view)."""
     if pipeline not in ("two_stream", "one_stream"):
         raise ValueError(f"unknown pipeline {pipeline!r}")
     batched = batch_backward > 0 and hasattr(backend, "backward_views") and bucket.M == 16 and bucket.layout == "activated"
+    fbatch = min(int(batch_forward), 16) if (batch_forward > 0 and hasattr(backend, "forward_geom_views") and bucket.M == 16) else 0
     dev = params["means3D"].device
     e = torch.empty(0, device=dev)
     results = []
     has_split = hasattr(backend, "forward_geom")
-
     side = _geom_stream(dev) if (pipeline == "two_stream" and hasattr(backend, "forward_bin")) else None
-
-    def geom_pass(v, stream=None):
-        cam = cameras[v]
-        args = (bg, params["means3D"], e, params["opacities"], params["scales"], params["rotations"], scale_modifier, e,
-                cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, cam.height, cam.width, params["shs"], sh_degree, cam.campos,
-                False, debug, low_pass)
-        if not has_split:
-            return args
-        if side is None:
-            return backend.forward_geom(*args)
-        stream = side if stream is None else stream
-        stream.wait_stream(torch.cuda.current_stream(dev))
-        return backend.forward_geom(*args, stream=stream)
-
     view_ids = list(view_ids)
     n = len(view_ids)
-    if side is not None:
+    main = torch.cuda.current_stream(dev) if dev.type == "cuda" else None
+
+    def raster_args(v):
+        cam = cameras[v]
+        return (bg, params["means3D"], e, params["opacities"], params["scales"], params["rotations"], scale_modifier, e,
+                cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, cam.height, cam.width, params["shs"], sh_degree, cam.campos,
+                False, debug, low_pass)
+
+    # ---- geometry half (preprocess, depth sort, prefix sum): per view, or per chunk of fbatch views -------------------------
+    states = {}                  # view position -> forward state whose geometry half is enqueued
+
+    def ensure_geom(pos, stream=None):
+        if pos >= n or pos in states:
+            return
+        if side is not None:
+            stream = side if stream is None else stream
+            stream.wait_stream(main)             # buffers come from the compute stream's pool: order after their previous users
+        if fbatch:
+            lo = (pos // fbatch) * fbatch
+            hi = min(n, lo + fbatch)
+            sts = backend.forward_geom_views(bg, params["means3D"], params["opacities"], params["scales"], params["rotations"], scale_modifier,
+                                             [cameras[view_ids[j]] for j in range(lo, hi)], cameras[view_ids[lo]].height, cameras[view_ids[lo]].width,
+                                             params["shs"], sh_degree, debug, low_pass, stream=stream, keep_cov3D=not batched)
+            states.update(zip(range(lo, hi), sts))
+        elif has_split:
+            states[pos] = backend.forward_geom(*raster_args(view_ids[pos]), **({"stream": stream} if stream is not None else {}))
+        else:
+            states[pos] = raster_args(view_ids[pos])
+
+    def bin_pass(pos):
+        side.wait_stream(main)
+        return backend.forward_bin(states[pos], stream=side)
+
+    if side is not None and n:
         # two-stream pipeline: the HBM-bound front of the forward (preprocess, depth sort, scan, duplicate, tile sort, ranges)
-        # runs on a high-priority side stream one view ahead of the issue-bound render / backward kernels on the compute
-        # stream, so its CTAs fill the SM slots those kernels release.  Buffers come from the compute stream's pool: every
-        # side-stream pass first waits for what is enqueued on the compute stream (the previous users of the memory).
-        main = torch.cuda.current_stream(dev)
-
-        def bin_pass(st):
-            side.wait_stream(main)
-            return backend.forward_bin(st, stream=side)
-
-        ahead = {}
-        if n:
-            g0 = geom_pass(view_ids[0])
-            if n > 1:
-                # step start: nothing runs beside view 0's front yet, so view 1's geometry half goes on a second side stream
-                # next to it (two latency-bound fronts overlap well); enqueued before the host blocks on view 0's num_rendered
-                side2 = _geom_stream(dev, 1)
-                ahead[1] = geom_pass(view_ids[1], stream=side2)
-            ahead[0] = bin_pass(g0)
-    else:
-        # software pipeline over the views: the first half of view i+1 (preprocess, depth sort, prefix sum) is enqueued BEFORE
-        # the backward of view i, so its num_rendered is on the host long before it is needed and the device never waits for
-        # the round trip that sizes the binning buffer
-        pending = geom_pass(view_ids[0]) if n else None
+        # runs on a high-priority side stream ahead of the issue-bound render / backward kernels on the compute stream, so its
+        # CTAs fill the SM slots those kernels release.
+        ensure_geom(0)
+        if n > 1 and not fbatch:
+            # step start: nothing runs beside view 0's front yet, so view 1's geometry half goes on a second side stream
+            # next to it (two latency-bound fronts overlap well); enqueued before the host blocks on view 0's num_rendered
+            ensure_geom(1, stream=_geom_stream(dev, 1))
+        bin_pass(0)
+    elif n:
+        # one stream: the geometry half of view i+1 is enqueued BEFORE the backward of view i, so its num_rendered is on the
+        # host long before it is needed and the device never waits for the round trip that sizes the binning buffer
+        ensure_geom(0)
     group = []
     for i, v in enumerate(view_ids):
         cam = cameras[v]
+        st = states.pop(i)
         if side is not None:
-            N, color, radii, depth, geom, binning, img = backend.forward_render(ahead.pop(i))
+            N, color, radii, depth, geom, binning, img = backend.forward_render(st)
         else:
-            N, color, radii, depth, geom, binning, img = backend.forward_raster(pending) if has_split else backend.rasterize_gaussians(*pending)
-            pending = geom_pass(view_ids[i + 1]) if i + 1 < n else None
+            N, color, radii, depth, geom, binning, img = backend.forward_raster(st) if has_split else backend.rasterize_gaussians(*st)
+            ensure_geom(i + 1)
         dpix = grad_fn(v, color, depth)
         if side is not None:
             # enqueued here, the side-stream passes wait for this view's render_fwd and loss and run beside its backward
             # (measured: before render_fwd 865, after it 871, after the loss 874 renders/s)
             if i + 1 < n:
-                bin_pass(ahead[i + 1])
-            if i + 2 < n:
-                ahead[i + 2] = geom_pass(view_ids[i + 2])
+                ensure_geom(i + 1)
+                bin_pass(i + 1)
+            ensure_geom(i + 2)
         if batched:
             # per view only the backward tile renderer; its accumulator blob, radii and geometry blob stay alive until the batch's
             # single per-Gaussian pass

@@ -343,13 +343,15 @@ def test_full_size_properties_config3(device):
     assert all(not v.any() for v in g0.values())
 
 
-@pytest.mark.parametrize("pipeline,P,W,H,V,batch", [("two_stream", 30000, 160, 96, 5, 8), ("one_stream", 30000, 160, 96, 5, 8), ("two_stream", 30000, 160, 96, 5, 2),
-                                                    ("two_stream", 30000, 160, 96, 5, 0), ("one_stream", 30000, 160, 96, 19, 19),
-                                                    ("two_stream", 30001, 160, 96, 3, 8), ("two_stream", 30002, 100, 52, 3, 2), ("one_stream", 29999, 160, 96, 2, 0),
-                                                    ("two_stream", 30001, 160, 96, 3, 0), ("two_stream", 1_000_000, 1920, 1080, 3, 8), ("two_stream", 1_000_000, 1920, 1080, 3, 0)])
-def test_accumulate_mode_and_multiview_bucket(device, pipeline, P, W, H, V, batch):
-    """The view-batch driver (both pipelines; the view-batched backward in groups of `batch` views — 19 views in one call span
-    two kernel launches — and the per-view accumulate path, batch = 0) against per-view forward + backward through the drop-in
+@pytest.mark.parametrize("pipeline,P,W,H,V,batch,fbatch", [
+    ("two_stream", 30000, 160, 96, 5, 8, 8), ("one_stream", 30000, 160, 96, 5, 8, 8), ("two_stream", 30000, 160, 96, 5, 2, 2), ("two_stream", 30000, 160, 96, 5, 0, 0),
+    ("two_stream", 30000, 160, 96, 5, 0, 3), ("two_stream", 30000, 160, 96, 5, 8, 0), ("one_stream", 30000, 160, 96, 19, 19, 16), ("two_stream", 30000, 160, 96, 19, 8, 8),
+    ("two_stream", 30001, 160, 96, 3, 8, 8), ("two_stream", 30002, 100, 52, 3, 2, 1), ("one_stream", 29999, 160, 96, 2, 0, 0), ("two_stream", 30001, 160, 96, 3, 0, 8),
+    ("two_stream", 1_000_000, 1920, 1080, 3, 8, 8), ("two_stream", 1_000_000, 1920, 1080, 3, 0, 0)])
+def test_accumulate_mode_and_multiview_bucket(device, pipeline, P, W, H, V, batch, fbatch):
+    """The view-batch driver (both pipelines; the view-batched geometry pass in chunks of `fbatch` views, 0 = per view; the
+    view-batched backward in groups of `batch` views — 19 views in one call span two kernel launches — and the per-view
+    accumulate path, batch = 0) against per-view forward + backward through the drop-in
     ops: images bit-identical, bucket = sum of the per-view gradients, per-view viewspace gradients equal.  P % 4 != 0 puts the
     segments of the flat bucket at addresses that are not 16-byte aligned; the last cases are BASELINE.json config 3's size."""
     from rain_b200 import multiview as mv
@@ -363,7 +365,7 @@ def test_accumulate_mode_and_multiview_bucket(device, pipeline, P, W, H, V, batc
     bucket.flat.fill_(float("nan"))                                        # the first view must overwrite everything
     from rain_b200.optim import DensificationStats
     stats = DensificationStats(P, device)
-    res = mv.train_step_views(params, cams, V, bucket, lambda v, c, d: dp[v], bg=bg, sh_degree=D, pipeline=pipeline, batch_backward=batch, stats=stats)
+    res = mv.train_step_views(params, cams, V, bucket, lambda v, c, d: dp[v], bg=bg, sh_degree=D, pipeline=pipeline, batch_backward=batch, batch_forward=fbatch, stats=stats)
     stats.sync()
     ref_stats = DensificationStats(P, device)
     tot = None
@@ -385,6 +387,38 @@ def test_accumulate_mode_and_multiview_bucket(device, pipeline, P, W, H, V, batc
     ref_stats.sync()
     assert eq(stats.max_radii2D, ref_stats.max_radii2D) and eq(stats.denom, ref_stats.denom)
     assert rel_err(stats.xyz_gradient_accum, ref_stats.xyz_gradient_accum)[0] < 1e-6
+
+
+@pytest.mark.parametrize("P,W,H,V", [(30001, 160, 96, 5), (20000, 100, 52, 16), (1_000_000, 1920, 1080, 3)])
+def test_batched_geometry_pass_is_bit_identical_to_the_per_view_one(device, P, W, H, V):
+    """rr_forward_geom_views (one pass over the Gaussians for all cameras, segmented depth sort, segmented scan) against
+    rr_forward_geom per view: radii, records, clamp flags, tile counts, depth order, offsets, num_rendered and — after the
+    binning / render half — images, tile lists and ranges, all bit for bit."""
+    import ctypes
+    lib = _lib.load()
+    D = 3
+    sc = make_scene(P, D, 13).to(device)
+    cams = [make_camera(v, V, W, H).to(device) for v in range(V)]
+    bg = torch.tensor([0.1, 0.2, 0.3], device=device)
+    sts = _C.forward_geom_views(bg, sc.means3D, sc.opacities, sc.scales, sc.rotations, 1.0, cams, H, W, sc.shs, D, False, 0.3, keep_cov3D=True)
+    go = (ctypes.c_int64 * 9)(); lib.rr_geom_layout(P, go)
+    view = lambda blob, off, cnt, dt: blob[off:off + cnt * torch.empty((), dtype=dt).element_size()].view(dt)
+    for v in range(V):
+        fw = mine_forward(sc, cams[v], bg)
+        N, color, radii, depth, geom, binning, img = _C.forward_raster(sts[v])
+        assert N == fw["N"] and eq(radii, fw["radii"]) and eq(color, fw["color"]) and eq(depth, fw["depth"])
+        vis = fw["radii"] > 0
+        assert eq(view(geom, go[0], P * 12, torch.int32).view(P, 12)[vis], fw["rec"].contiguous().view(torch.int32).view(P, 12)[vis])
+        assert eq(view(geom, go[2], P, torch.uint8)[vis], fw["clamped"][vis])
+        assert eq(view(geom, go[3], P, torch.int32), fw["tiles_touched"]) and eq(view(geom, go[5], P, torch.int32), fw["depth_order"])
+        assert eq(view(geom, go[6], P, torch.int32), view(fw["geom"], go[6], P, torch.int32))
+        assert eq(view(geom, go[1], P * 6, torch.float32).view(P, 6)[vis], fw["cov3D"][vis])
+        bo = (ctypes.c_int64 * 5)(); lib.rr_binning_layout(N, W, H, bo)
+        if N:
+            assert eq(view(binning, bo[1], N, torch.int32), fw["point_list"])
+        io = (ctypes.c_int64 * 4)(); lib.rr_image_layout(W, H, io)
+        T = ((W + 15) // 16) * ((H + 15) // 16)
+        assert eq(view(img, io[2], T * 2, torch.int32), fw["ranges"].reshape(-1)) and eq(view(img, io[1], H * W, torch.int32), fw["n_contrib"])
 
 
 def test_backward_views_leaf_mode_applies_the_activation_chain_rule(device):

@@ -40,8 +40,10 @@ def main():
     dp = [make_grad(W, H, 20 + v).to(dev) for v in range(V)]
     params = dict(means3D=sc.means3D, opacities=sc.opacities, shs=sc.shs, scales=sc.scales, rotations=sc.rotations)
 
+    symmetric = os.environ.get("RAIN_VERIFY_COLLECTIVE", "rr") == "rr"     # rr: the library's one-kernel all-reduce; nccl: ncclAllReduce
+
     def step(r, w):
-        bucket = mv.GradientBucket(P, 16, dev)
+        bucket = mv.GradientBucket(P, 16, dev, symmetric=(symmetric and w > 1))
         bucket.flat.fill_(float("nan"))
         stats = DensificationStats(P, dev)
         res = mv.train_step_views(params, cams, V, bucket, lambda v, c, d: dp[v], rank=r, world_size=w, bg=bg, sh_degree=D,
@@ -51,13 +53,15 @@ def main():
         return bucket, stats, res
 
     bucket, stats, res = step(rank, world)
+    if bucket.collective is not None:
+        bucket.collective.check()
     stats.sync()
     torch.cuda.synchronize()
     # replicas agree bit for bit after the all-reduce
     lo, hi = bucket.flat.clone(), bucket.flat.clone()
     dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
     same_bits = bool(torch.equal(lo, hi)) and bool(torch.isfinite(lo).all())
-    ok, report = same_bits, {"world": world, "P": P, "views": V, "replicas_bit_identical": same_bits, "views_per_rank": len(res)}
+    ok, report = same_bits, {"collective": ("rr_allreduce_sum_f32 " + json.dumps(bucket.collective.calibration)) if bucket.collective is not None else "ncclAllReduce", "world": world, "P": P, "views": V, "replicas_bit_identical": same_bits, "views_per_rank": len(res)}
     if rank == 0:
         alone, stats1, _ = step(0, 1)             # all V views on this rank, no collective
         stats1.sync("skip")
