@@ -36,6 +36,8 @@ int rr_version(void);
 
 /* number of CUDA kernels this library has launched in this process so far */
 int64_t rr_launch_count(void);
+/* 1 if the opt-in exact tile culling is on in this process (RAIN_TILE_CULL=1, read once; see the header comment) */
+int rr_tile_cull_enabled(void);
 
 /* Optional per-stage device timing: when enabled every entry point brackets each of its stages with CUDA events on the
  * caller's stream (no reference counterpart; the reference only has CHECK_CUDA syncs, auxiliary.h:155-162).

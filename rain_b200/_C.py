@@ -353,6 +353,11 @@ def backward_views(views, means3D, sh, scales, rotations, scale_modifier, low_pa
             _ptr(st[0]), _ptr(st[1]), _ptr(st[2]), (1 if accumulate else 0) | (2 if leaf else 0), int(bool(debug))), "rr_backward_views")
 
 
+def tile_cull_enabled():
+    """True if this process runs with the opt-in exact tile culling (RAIN_TILE_CULL=1, read once by the library)"""
+    return bool(_lib.load().rr_tile_cull_enabled())
+
+
 def mark_visible(means3D, viewmatrix, projmatrix):
     """markVisible (rasterize_points.cu:193-212): bool[P], view-space z > 0.2."""
     lib = _lib.load()

@@ -16,6 +16,7 @@ SIGNATURES = {
     "rr_last_error": (_c.c_char_p, []),
     "rr_version": (_i, []),
     "rr_launch_count": (_i64, []),
+    "rr_tile_cull_enabled": (_i, []),
     "rr_prof_enable": (_i, [_i]),
     "rr_prof_num_stages": (_i, []),
     "rr_prof_stage_name": (_c.c_char_p, [_i]),

@@ -187,6 +187,7 @@ const char* rr_last_error(void) { return g_error.c_str(); }
 int rr_version(void) { return 2; }
 
 int64_t rr_launch_count(void) { return (int64_t)g_launches.load(); }
+int rr_tile_cull_enabled(void) { return tile_cull_wanted() ? 1 : 0; }
 
 int rr_prof_enable(int on)
 {

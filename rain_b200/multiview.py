@@ -112,6 +112,8 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
         raise ValueError(f"unknown pipeline {pipeline!r}")
     batched = batch_backward > 0 and hasattr(backend, "backward_views") and bucket.M == 16 and bucket.layout == "activated"
     fbatch = min(int(batch_forward), 16) if (batch_forward > 0 and hasattr(backend, "forward_geom_views") and bucket.M == 16) else 0
+    if fbatch and backend is _native and _native.tile_cull_enabled():
+        fbatch = 0               # the opt-in tile culling lives in the per-view preprocess kernel only
     dev = params["means3D"].device
     e = torch.empty(0, device=dev)
     results = []
