@@ -29,6 +29,7 @@ extern "C" {
 
 #define RR_BWD_ACCUMULATE 1
 #define RR_BWD_LEAF 2        /* rr_backward_views: inputs are the raw leaf tensors, gradients w.r.t. them */
+#define RR_GEOM_LEAF 2       /* rr_forward_geom_views: inputs are the raw leaf tensors (activations applied in the kernel) */
 #define RR_GEOM_KEEP_COV3D 1 /* rr_forward_geom_views: also store the 3D covariance in every view's blob (the per-view rr_backward reads it) */
 
 const char* rr_last_error(void);
@@ -72,10 +73,14 @@ int rr_forward_geom(void* stream, int P, int D, int M, int W, int H,
  * argument is a HOST array of nviews entries (viewmatrix / projmatrix / campos / radii / geom: device pointers; tan_fovx /
  * tan_fovy: floats; num_rendered_host[v]: pinned host int64 receiving view v's count).  Each view's outputs (radii[v], its
  * geometry blob) are bit-identical to rr_forward_geom's for that camera.  SH colours + scales / rotations only, M = 16,
- * nviews <= 16; flags: RR_GEOM_KEEP_COV3D. */
+ * nviews <= 16; flags: RR_GEOM_KEEP_COV3D, RR_GEOM_LEAF.
+ * With RR_GEOM_LEAF the inputs are the six RAW leaf tensors of scene/gaussian_model.py:131-136 — means3D = _xyz, shs =
+ * _features_dc [P,1,3], f_rest = _features_rest [P,15,3], opacities / scales / rotations = _opacity / _scaling / _rotation before
+ * their activations — and sigmoid / exp / normalise (:85-105) are applied inside (f_rest is ignored otherwise; pass null).
+ * The outputs then equal rr_forward_geom's on the activated tensors rr_activate produces, bit for bit. */
 int rr_forward_geom_views(void* stream, int P, int D, int M, int W, int H, int nviews,
 	const float* const* viewmatrix, const float* const* projmatrix, const float* const* campos, const float* tan_fovx, const float* tan_fovy,
-	const float* means3D, const float* shs, const float* opacities, const float* scales, float scale_modifier, const float* rotations, float low_pass,
+	const float* means3D, const float* shs, const float* f_rest, const float* opacities, const float* scales, float scale_modifier, const float* rotations, float low_pass,
 	int* const* radii, void* const* geom, size_t geom_bytes, int64_t* const* num_rendered_host, int flags, int debug);
 
 /* Forward, second half — replaces duplicateWithKeys + cub SortPairs + identifyTileRanges + FORWARD::render
@@ -180,6 +185,17 @@ int rr_loss_l2_u8(void* stream, int64_t n, const float* image, const uint8_t* gt
 int rr_param_step(void* stream, int P, int M, float* xyz, float* f_dc, float* f_rest, float* opacity, float* scaling, float* rotation,
 	float* exp_avg, float* exp_avg_sq, const float* grads, const float* hyper, int step,
 	float* shs_out, float* opacities_out, float* scales_out, float* rotations_out);
+
+/* rr_param_step for LEAF gradients (the bucket the leaf mode of rr_backward_views fills: xyz | f_dc | f_rest | opacity | scaling |
+ * rotation, moments in the same layout): plain torch.optim.Adam semantics over the six leaf tensors in one flat pass — the chain
+ * rule already happened in the backward and the next render reads the leaves themselves, so nothing else is written. */
+int rr_param_step_leaf(void* stream, int P, int M, float* xyz, float* f_dc, float* f_rest, float* opacity, float* scaling, float* rotation,
+	float* exp_avg, float* exp_avg_sq, const float* grads, const float* hyper, int step);
+
+/* The caller-side activations of scene/gaussian_model.py:85-105 alone — opacities_out[P] = sigmoid(opacity), scales_out[P,3] =
+ * exp(scaling), rotations_out[P,4] = F.normalize(rotation) — computed with the same device functions as the leaf modes of
+ * rr_forward_geom_views / rr_backward_views and the re-activation of rr_param_step (identical bits in all of them). */
+int rr_activate(void* stream, int P, const float* opacity, const float* scaling, const float* rotation, float* opacities_out, float* scales_out, float* rotations_out);
 
 /* Densification statistics of one rendered view, fused (train.py:132-134 + GaussianModel.add_densification_stats,
  * scene/gaussian_model.py:419-421): for every Gaussian with radii > 0 (the view's visibility_filter)

@@ -97,14 +97,30 @@ def forward_geom(background, means3D, colors, opacity, scales, rotations, scale_
     return st
 
 
+def activate(opacity, scaling, rotation):
+    """sigmoid / exp / F.normalize of the raw leaf tensors (scene/gaussian_model.py:85-105) with the library's own device
+    functions (rr_activate): returns (opacities[P,1], scales[P,3], rotations[P,4])."""
+    lib = _lib.load()
+    dev = opacity.device
+    P = opacity.shape[0]
+    o, s, r = (_f32c(t, dev) if P else t for t in (opacity, scaling, rotation))
+    out = (torch.empty((P, 1), dtype=torch.float32, device=dev), torch.empty((P, 3), dtype=torch.float32, device=dev), torch.empty((P, 4), dtype=torch.float32, device=dev))
+    if P:
+        with torch.cuda.device(dev):
+            _lib.check(lib.rr_activate(torch.cuda.current_stream().cuda_stream, P, o.data_ptr(), s.data_ptr(), r.data_ptr(), out[0].data_ptr(), out[1].data_ptr(), out[2].data_ptr()), "rr_activate")
+    return out
+
+
 def forward_geom_views(background, means3D, opacity, scales, rotations, scale_modifier, cams, image_height, image_width, sh, degree,
-                       debug, low_pass, stream=None, keep_cov3D=False):
+                       debug, low_pass, stream=None, keep_cov3D=False, leaf=False, f_rest=None):
     """forward_geom for ALL views of a batch in one set of launches (rr_forward_geom_views: one pass over the Gaussians for
     every camera, one segmented depth sort, one segmented scan).  cams: list (at most 16) of objects with viewmatrix,
     projmatrix, campos, tanfovx, tanfovy.  Returns one forward-pass state per view, each to be completed with forward_bin /
     forward_render (or forward_raster) exactly like forward_geom's; their outputs are bit-identical to the per-view call's.
     SH colours + scales / rotations only (M = 16).  keep_cov3D: also store the 3D covariance per view (needed only if the
-    per-view rasterize_gaussians_backward will be used on these states)."""
+    per-view rasterize_gaussians_backward will be used on these states).  leaf=True: means3D / sh / opacity / scales / rotations
+    are the RAW leaves _xyz / _features_dc / _opacity / _scaling / _rotation and f_rest is _features_rest
+    (scene/gaussian_model.py:131-136); their activations are applied inside the kernel."""
     import ctypes
     lib = _lib.load()
     if not means3D.is_cuda:
@@ -113,7 +129,10 @@ def forward_geom_views(background, means3D, opacity, scales, rotations, scale_mo
     P, H, W, n = means3D.size(0), int(image_height), int(image_width), len(cams)
     byte = dict(dtype=torch.uint8, device=dev)
     means3D_c, bg, opac, scales_c, rots, sh_c = (_f32c(t, dev) for t in (means3D, background, opacity, scales, rotations, sh))
-    M = sh.size(1) if (sh is not None and sh.numel() != 0) else 0
+    frest_c = _f32c(f_rest, dev) if leaf else None
+    if leaf and (sh.numel() != P * 3 or f_rest is None or f_rest.numel() != P * 45):
+        raise RuntimeError("leaf mode needs _features_dc [P,1,3] and _features_rest [P,15,3]")
+    M = 16 if leaf else (sh.size(1) if (sh is not None and sh.numel() != 0) else 0)
     states = []
     for cam in cams:
         st = _GeomPass()
@@ -130,7 +149,7 @@ def forward_geom_views(background, means3D, opacity, scales, rotations, scale_mo
         st.geom = torch.empty(gbytes, **byte)
         st.img = torch.empty(lib.rr_image_bytes(W, H), **byte)
         st.nr = _take_slot(dev)
-        st.keep = (means3D_c, opac, scales_c, rots, sh_c, mats)
+        st.keep = (means3D_c, opac, scales_c, rots, sh_c, frest_c, mats)
     vp = ctypes.c_void_p
     arr = lambda xs: (vp * n)(*xs)
     with torch.cuda.device(dev):
@@ -139,9 +158,9 @@ def forward_geom_views(background, means3D, opacity, scales, rotations, scale_mo
             s.cuda_stream, P, int(degree), M, W, H, n,
             arr([m[0].data_ptr() for m in mats]), arr([m[1].data_ptr() for m in mats]), arr([m[2].data_ptr() for m in mats]),
             (ctypes.c_float * n)(*[float(c.tanfovx) for c in cams]), (ctypes.c_float * n)(*[float(c.tanfovy) for c in cams]),
-            means3D_c.data_ptr(), sh_c.data_ptr(), opac.data_ptr(), scales_c.data_ptr(), float(scale_modifier), rots.data_ptr(), float(low_pass),
+            means3D_c.data_ptr(), sh_c.data_ptr(), frest_c.data_ptr() if leaf else None, opac.data_ptr(), scales_c.data_ptr(), float(scale_modifier), rots.data_ptr(), float(low_pass),
             arr([st.radii.data_ptr() for st in states]), arr([st.geom.data_ptr() for st in states]), gbytes,
-            arr([st.nr.data_ptr() for st in states]), 1 if keep_cov3D else 0, int(bool(debug))), "rr_forward_geom_views")
+            arr([st.nr.data_ptr() for st in states]), (1 if keep_cov3D else 0) | (2 if leaf else 0), int(bool(debug))), "rr_forward_geom_views")
         ev = torch.cuda.Event()
         ev.record(s)
     for st in states:

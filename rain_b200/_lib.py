@@ -33,7 +33,7 @@ SIGNATURES = {
                              _vp, _vp, _sz, _vp]),
     "rr_forward_geom_views": (_i, [_vp, _i, _i, _i, _i, _i, _i,
                                    _vp, _vp, _vp, _vp, _vp,
-                                   _vp, _vp, _vp, _vp, _f, _vp, _f,
+                                   _vp, _vp, _vp, _vp, _vp, _f, _vp, _f,
                                    _vp, _vp, _sz, _vp, _i, _i]),
     "rr_forward_raster": (_i, [_vp, _i, _i, _i, _i64, _vp,
                                _vp, _sz, _vp, _sz, _vp, _sz,
@@ -69,6 +69,8 @@ SIGNATURES = {
     "rr_loss_l2": (_i, [_vp, _i64, _vp, _vp, _vp, _vp]),
     "rr_loss_l2_u8": (_i, [_vp, _i64, _vp, _vp, _c.c_float, _vp, _vp]),
     "rr_param_step": (_i, [_vp, _i, _i] + [_vp] * 6 + [_vp, _vp, _vp, _c.POINTER(_c.c_float), _i] + [_vp] * 4),
+    "rr_param_step_leaf": (_i, [_vp, _i, _i] + [_vp] * 6 + [_vp, _vp, _vp, _c.POINTER(_c.c_float), _i]),
+    "rr_activate": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "rr_densify_stats": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp]),
     "rr_allreduce_signal_bytes": (_sz, []),
     "rr_allreduce_sum_f32": (_i, [_vp, _i, _i, _i64, _vp, _vp, _vp, _vp, _c.c_uint32, _i]),

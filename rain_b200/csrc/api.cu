@@ -270,7 +270,7 @@ int rr_forward_geom(void* stream_, int P, int D, int M, int W, int H,
 
 int rr_forward_geom_views(void* stream_, int P, int D, int M, int W, int H, int nviews,
 	const float* const* viewmatrix, const float* const* projmatrix, const float* const* campos, const float* tan_fovx, const float* tan_fovy,
-	const float* means3D, const float* shs, const float* opacities, const float* scales, float scale_modifier, const float* rotations, float low_pass,
+	const float* means3D, const float* shs, const float* f_rest, const float* opacities, const float* scales, float scale_modifier, const float* rotations, float low_pass,
 	int* const* radii, void* const* geom, size_t geom_bytes, int64_t* const* num_rendered_host, int flags, int debug)
 {
 	cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
@@ -285,13 +285,16 @@ int rr_forward_geom_views(void* stream_, int P, int D, int M, int W, int H, int 
 	if (bad_ptr(viewmatrix, "viewmatrix") || bad_ptr(projmatrix, "projmatrix") || bad_ptr(campos, "campos") || bad_ptr(tan_fovx, "tan_fovx") || bad_ptr(tan_fovy, "tan_fovy") ||
 		bad_ptr(means3D, "means3D") || bad_ptr(shs, "shs") || bad_ptr(opacities, "opacities") || bad_ptr(scales, "scales") || bad_ptr(rotations, "rotations") ||
 		bad_ptr(radii, "radii") || bad_ptr(geom, "geom")) return -1;
+	const bool leaf = (flags & RR_GEOM_LEAF) != 0;
+	if (leaf && bad_ptr(f_rest, "f_rest")) return -1;
 	const GeomLayout L0 = geom_layout(nullptr, P);
 	if (L0.total > geom_bytes) { set_error("geometry blob too small: %zu < %zu", geom_bytes, L0.total); return -1; }
 	PreprocessViewsArgs a; memset(&a, 0, sizeof(a));
 	a.P = P; a.D = D; a.W = W; a.H = H; a.grid_x = (W + TILE_X - 1) / TILE_X; a.grid_y = (H + TILE_Y - 1) / TILE_Y; a.nviews = nviews;
 	a.write_cov3D = (flags & RR_GEOM_KEEP_COV3D) ? 1 : 0;
 	a.scale_modifier = scale_modifier; a.low_pass = low_pass;
-	a.means3D = means3D; a.scales = scales; a.rotations = rotations; a.opacities = opacities; a.shs = shs;
+	a.means3D = means3D; a.scales = scales; a.rotations = rotations; a.opacities = opacities;
+	a.leaf = leaf ? 1 : 0; a.shs = leaf ? nullptr : shs; a.f_dc = leaf ? shs : nullptr; a.f_rest = f_rest;
 	// byte offsets of the arrays inside a geometry blob (the layout carved from a null base)
 	a.off_rec = reinterpret_cast<uintptr_t>(L0.rec); a.off_cov3D = reinterpret_cast<uintptr_t>(L0.cov3D); a.off_clamped = reinterpret_cast<uintptr_t>(L0.clamped);
 	a.off_tiles = reinterpret_cast<uintptr_t>(L0.tiles_touched); a.off_rect = reinterpret_cast<uintptr_t>(L0.rect); a.off_key = reinterpret_cast<uintptr_t>(L0.key_a);
@@ -563,6 +566,27 @@ int rr_param_step(void* stream_, int P, int M, float* xyz, float* f_dc, float* f
 	if (M > 1 && bad_ptr(f_rest, "f_rest")) return -1;
 	return launch_param_step(reinterpret_cast<cudaStream_t>(stream_), P, M, xyz, f_dc, f_rest, opacity, scaling, rotation, exp_avg, exp_avg_sq, grads, hyper, step,
 		shs_out, opacities_out, scales_out, rotations_out);
+}
+
+int rr_param_step_leaf(void* stream_, int P, int M, float* xyz, float* f_dc, float* f_rest, float* opacity, float* scaling, float* rotation,
+	float* exp_avg, float* exp_avg_sq, const float* grads, const float* hyper, int step)
+{
+	if (P == 0) return 0;
+	if (P < 0 || M < 1) { set_error("bad sizes P=%d M=%d", P, M); return -1; }
+	if (step < 1) { set_error("Adam step count must be >= 1, got %d", step); return -1; }
+	if (bad_ptr(xyz, "xyz") || bad_ptr(f_dc, "f_dc") || bad_ptr(opacity, "opacity") || bad_ptr(scaling, "scaling") || bad_ptr(rotation, "rotation") ||
+		bad_ptr(exp_avg, "exp_avg") || bad_ptr(exp_avg_sq, "exp_avg_sq") || bad_ptr(grads, "grads") || bad_ptr(hyper, "hyper")) return -1;
+	if (M > 1 && bad_ptr(f_rest, "f_rest")) return -1;
+	return launch_param_step_leaf(reinterpret_cast<cudaStream_t>(stream_), P, M, xyz, f_dc, f_rest, opacity, scaling, rotation, exp_avg, exp_avg_sq, grads, hyper, step);
+}
+
+int rr_activate(void* stream_, int P, const float* opacity, const float* scaling, const float* rotation, float* opacities_out, float* scales_out, float* rotations_out)
+{
+	if (P == 0) return 0;
+	if (P < 0) { set_error("bad size P=%d", P); return -1; }
+	if (bad_ptr(opacity, "opacity") || bad_ptr(scaling, "scaling") || bad_ptr(rotation, "rotation") || bad_ptr(opacities_out, "opacities_out") ||
+		bad_ptr(scales_out, "scales_out") || bad_ptr(rotations_out, "rotations_out")) return -1;
+	return launch_activate(reinterpret_cast<cudaStream_t>(stream_), P, opacity, scaling, rotation, opacities_out, scales_out, rotations_out);
 }
 
 int rr_densify_stats(void* stream_, int P, const int* radii, const float* dL_dmean2D, float* max_radii2D, float* xyz_gradient_accum, float* denom)

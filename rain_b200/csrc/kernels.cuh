@@ -24,8 +24,9 @@ int launch_preprocess_fwd(cudaStream_t, const PreprocessArgs&);
 constexpr int PV_MAX_VIEWS = 16;
 struct PreprocessViewsArgs {
 	int P, D, W, H, grid_x, grid_y, nviews, write_cov3D;
+	int leaf;                             // 1: raw leaf tensors in (shs unused; f_dc [P,1,3] + f_rest [P,15,3]), activations applied in the kernel
 	float scale_modifier, low_pass;
-	const float *means3D, *scales, *rotations, *opacities, *shs;
+	const float *means3D, *scales, *rotations, *opacities, *shs, *f_dc, *f_rest;
 	const float* view[PV_MAX_VIEWS]; const float* proj[PV_MAX_VIEWS]; const float* campos[PV_MAX_VIEWS];
 	float tan_fovx[PV_MAX_VIEWS], tan_fovy[PV_MAX_VIEWS];
 	int* radii[PV_MAX_VIEWS];
@@ -127,6 +128,9 @@ int launch_loss_l2(cudaStream_t, size_t n, const float* img, const void* gt, int
 int launch_param_step(cudaStream_t, int P, int M, float* xyz, float* f_dc, float* f_rest, float* opacity, float* scaling, float* rotation,
 	float* m, float* v, const float* grads, const float* hyper, int step, float* shs_out, float* opacities_out, float* scales_out, float* rotations_out);
 
+int launch_param_step_leaf(cudaStream_t, int P, int M, float* xyz, float* f_dc, float* f_rest, float* opacity, float* scaling, float* rotation,
+	float* m, float* v, const float* grads, const float* hyper, int step);
+int launch_activate(cudaStream_t, int P, const float* opacity, const float* scaling, const float* rotation, float* opacities_out, float* scales_out, float* rotations_out);
 int launch_densify_stats(cudaStream_t, int P, const int* radii, const float* dL_dmean2D, float* max_radii2D, float* grad_accum, float* denom);
 
 // allreduce.cu: one-kernel two-shot all-reduce of a symmetric f32 buffer over NVLink peer / multicast memory

@@ -13,6 +13,7 @@
 #include <cmath>
 #include "common.cuh"
 #include "kernels.cuh"
+#include "splat_math.cuh"
 
 namespace rr {
 
@@ -63,11 +64,11 @@ __global__ void __launch_bounds__(256) param_step_geom_kernel(int P, float* __re
 		m_xyz[i] = mm; v_xyz[i] = vv;
 	}
 	{                                                               // opacity = sigmoid(o): d/do = s (1 - s)
-		const float o = opacity[p], s = 1.0f / (1.0f + expf(-o));
+		const float o = opacity[p], s = act_opacity(o);
 		float mm = m_op[p], vv = v_op[p];
 		const float on = adam(o, g_op[p] * s * (1.0f - s), mm, vv, h.lr[3], h);
 		opacity[p] = on; m_op[p] = mm; v_op[p] = vv;
-		if (opacities_out) opacities_out[p] = 1.0f / (1.0f + expf(-on));
+		if (opacities_out) opacities_out[p] = act_opacity(on);
 	}
 	#pragma unroll
 	for (int c = 0; c < 3; c++) {                                   // scales = exp(s): d/ds = exp(s)
@@ -76,7 +77,7 @@ __global__ void __launch_bounds__(256) param_step_geom_kernel(int P, float* __re
 		float mm = m_sc[i], vv = v_sc[i];
 		const float sn = adam(s, g_sc[i] * expf(s), mm, vv, h.lr[4], h);
 		scaling[i] = sn; m_sc[i] = mm; v_sc[i] = vv;
-		if (scales_out) scales_out[i] = expf(sn);
+		if (scales_out) scales_out[i] = act_scale(sn);
 	}
 	{                                                               // rotations = q / max(|q|, 1e-12) (F.normalize): d/dq = (g - qh (qh.g)) / |q|
 		// the bucket segments start at 55 P floats: only the leaf tensor itself is known to be 16-byte aligned
@@ -93,11 +94,40 @@ __global__ void __launch_bounds__(256) param_step_geom_kernel(int P, float* __re
 		reinterpret_cast<float4*>(rotation)[p] = qn;
 		m_rot[r4] = mm.x; m_rot[r4 + 1] = mm.y; m_rot[r4 + 2] = mm.z; m_rot[r4 + 3] = mm.w;
 		v_rot[r4] = vv.x; v_rot[r4 + 1] = vv.y; v_rot[r4 + 2] = vv.z; v_rot[r4 + 3] = vv.w;
-		if (rotations_out) {
-			const float i2 = 1.0f / fmaxf(sqrtf(qn.x * qn.x + qn.y * qn.y + qn.z * qn.z + qn.w * qn.w), 1e-12f);
-			reinterpret_cast<float4*>(rotations_out)[p] = make_float4(qn.x * i2, qn.y * i2, qn.z * i2, qn.w * i2);
-		}
+		if (rotations_out) reinterpret_cast<float4*>(rotations_out)[p] = act_rot(qn);
 	}
+}
+
+// Adam over the six raw leaf tensors with LEAF gradients (bucket layout xyz | f_dc | f_rest | opacity | scaling | rotation, what
+// the leaf mode of rr_backward_views writes): no chain rule, no re-activation, no activated copies — one flat pass; the segment
+// of a flat index selects the leaf tensor and its learning rate.
+struct LeafSegs { float* p[6]; size_t end[6]; };
+__global__ void __launch_bounds__(256) param_step_leaf_kernel(size_t n, LeafSegs sg, float* __restrict__ m, float* __restrict__ v, const float* __restrict__ g, AdamScalars h)
+{
+	for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (size_t)gridDim.x * 256) {
+		int k = 0;
+		#pragma unroll
+		for (int j = 0; j < 5; j++) k += i >= sg.end[j] ? 1 : 0;
+		float* dst = sg.p[k] + (i - (k ? sg.end[k - 1] : 0));
+		float mm = m[i], vv = v[i];
+		*dst = adam(*dst, __ldg(g + i), mm, vv, h.lr[k], h);
+		m[i] = mm; v[i] = vv;
+	}
+}
+
+// The caller-side activations alone (scene/gaussian_model.py:85-105: sigmoid, exp, F.normalize), with the same device functions
+// the leaf-mode rasterizer kernels and the parameter step use (splat_math.cuh): one thread per Gaussian.
+__global__ void __launch_bounds__(256) activate_kernel(int P, const float* __restrict__ opacity, const float* __restrict__ scaling, const float* __restrict__ rotation,
+	float* __restrict__ opacities_out, float* __restrict__ scales_out, float* __restrict__ rotations_out)
+{
+	const int p = blockIdx.x * 256 + threadIdx.x;
+	if (p >= P) return;
+	opacities_out[p] = act_opacity(opacity[p]);
+	#pragma unroll
+	for (int c = 0; c < 3; c++) scales_out[(size_t)p * 3 + c] = act_scale(scaling[(size_t)p * 3 + c]);
+	const float4 q = act_rot(load_f4(rotation, (size_t)p));
+	float* o = rotations_out + (size_t)p * 4;
+	o[0] = q.x; o[1] = q.y; o[2] = q.z; o[3] = q.w;
 }
 
 // Densification statistics of one rendered view (train.py:132-134, scene/gaussian_model.py:419-421), one thread per
@@ -118,15 +148,19 @@ __global__ void __launch_bounds__(256) densify_stats_kernel(int P, const int* __
 
 }  // namespace
 
+int launch_activate(cudaStream_t stream, int P, const float* opacity, const float* scaling, const float* rotation, float* opacities_out, float* scales_out, float* rotations_out)
+{
+	count_launch(), activate_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, opacity, scaling, rotation, opacities_out, scales_out, rotations_out);
+	return check_launch("activate", stream, false);
+}
+
 int launch_densify_stats(cudaStream_t stream, int P, const int* radii, const float* dL_dmean2D, float* max_radii2D, float* grad_accum, float* denom)
 {
 	count_launch(), densify_stats_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, radii, dL_dmean2D, max_radii2D, grad_accum, denom);
 	return check_launch("densify_stats", stream, false);
 }
 
-int launch_param_step(cudaStream_t stream, int P, int M, float* xyz, float* f_dc, float* f_rest, float* opacity, float* scaling, float* rotation,
-	float* m, float* v, const float* grads, const float* hyper /*host: lr[6], beta1, beta2, eps*/, int step,
-	float* shs_out, float* opacities_out, float* scales_out, float* rotations_out)
+static AdamScalars adam_scalars(const float* hyper, int step)
 {
 	AdamScalars h;
 	for (int i = 0; i < 6; i++) h.lr[i] = hyper[i];
@@ -134,6 +168,29 @@ int launch_param_step(cudaStream_t stream, int P, int M, float* xyz, float* f_dc
 	// bias corrections as torch computes them (python floats, i.e. double): 1 - beta ** step
 	h.inv_bc1 = (float)(1.0 / (1.0 - std::pow((double)hyper[6], (double)step)));
 	h.inv_sqrt_bc2 = (float)(1.0 / std::sqrt(1.0 - std::pow((double)hyper[7], (double)step)));
+	return h;
+}
+
+int launch_param_step_leaf(cudaStream_t stream, int P, int M, float* xyz, float* f_dc, float* f_rest, float* opacity, float* scaling, float* rotation,
+	float* m, float* v, const float* grads, const float* hyper, int step)
+{
+	const AdamScalars h = adam_scalars(hyper, step);
+	const size_t Pz = (size_t)P;
+	LeafSegs sg;
+	sg.p[0] = xyz; sg.p[1] = f_dc; sg.p[2] = f_rest; sg.p[3] = opacity; sg.p[4] = scaling; sg.p[5] = rotation;
+	const size_t len[6] = { 3 * Pz, 3 * Pz, (size_t)(M - 1) * 3 * Pz, Pz, 3 * Pz, 4 * Pz };
+	size_t acc = 0;
+	for (int k = 0; k < 6; k++) { acc += len[k]; sg.end[k] = acc; }
+	const size_t blocks = (acc + 255) / 256;
+	count_launch(), param_step_leaf_kernel<<<(unsigned)(blocks < 148u * 16u ? blocks : 148u * 16u), 256, 0, stream>>>(acc, sg, m, v, grads, h);
+	return check_launch("param_step_leaf", stream, false);
+}
+
+int launch_param_step(cudaStream_t stream, int P, int M, float* xyz, float* f_dc, float* f_rest, float* opacity, float* scaling, float* rotation,
+	float* m, float* v, const float* grads, const float* hyper /*host: lr[6], beta1, beta2, eps*/, int step,
+	float* shs_out, float* opacities_out, float* scales_out, float* rotations_out)
+{
+	const AdamScalars h = adam_scalars(hyper, step);
 	const size_t Pz = (size_t)P, nsh = Pz * M * 3;
 	// bucket layout: means3D [P,3] | sh [P,M,3] | opacity [P] | scales [P,3] | rotations [P,4]
 	const size_t o_sh = 3 * Pz, o_op = o_sh + nsh, o_sc = o_op + Pz, o_rot = o_sc + 3 * Pz;

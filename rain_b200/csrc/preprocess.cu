@@ -317,6 +317,10 @@ constexpr int PV_WARPS = PV_THREADS / 32;
 constexpr int PV_SH_STRIDE = 49;          // 48 floats + 1: a lane walking its own row is bank-conflict free
 constexpr int PV_CAM_FLOATS = 40;         // V[16] Pj[16] campos[3] tan_fovx tan_fovy focal_x focal_y pad
 
+// LEAF: the inputs are the six raw leaf tensors of scene/gaussian_model.py:131-136 (xyz, _features_dc [P,1,3], _features_rest
+// [P,15,3], raw opacity / scaling / rotation); sigmoid, exp and normalise (:85-105) are applied here (splat_math.cuh), so no
+// activated copy of the parameters is ever written or re-read.
+template <bool LEAF>
 __global__ void __launch_bounds__(PV_THREADS, 4) preprocess_views_kernel(PreprocessViewsArgs a)
 {
 	__shared__ __align__(16) float s_sh[PV_WARPS][32 * PV_SH_STRIDE];
@@ -338,9 +342,13 @@ __global__ void __launch_bounds__(PV_THREADS, 4) preprocess_views_kernel(Preproc
 	const bool live = idx < a.P;
 	const int nvalid = min(32, a.P - warp_base);
 	const size_t ii = (size_t)(live ? idx : 0);
-	// the warp's SH rows: (D+1)^2 * 3 floats of each 48-float row are needed; rows are 192 B, so the warp's span is 16-byte
-	// aligned whenever the array is
-	{
+	// the warp's SH rows (48 floats each), staged with coalesced loads
+	if (LEAF) {
+		const float* __restrict__ dc = a.f_dc + (size_t)warp_base * 3;
+		const float* __restrict__ rest = a.f_rest + (size_t)warp_base * 45;
+		for (int f = lane; f < nvalid * 3; f += 32) { const int row = f / 3; s_sh[warp][row * PV_SH_STRIDE + (f - row * 3)] = __ldg(dc + f); }
+		for (int f = lane; f < nvalid * 45; f += 32) { const int row = f / 45; s_sh[warp][row * PV_SH_STRIDE + 3 + (f - row * 45)] = __ldg(rest + f); }
+	} else {
 		const float* __restrict__ src = a.shs + (size_t)warp_base * 48;
 		if ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0) {
 			const float4* __restrict__ src4 = reinterpret_cast<const float4*>(src);
@@ -358,9 +366,12 @@ __global__ void __launch_bounds__(PV_THREADS, 4) preprocess_views_kernel(Preproc
 	if (!live) return;
 	const float* sh = s_sh[warp] + lane * PV_SH_STRIDE;
 	const float px = a.means3D[3 * ii], py = a.means3D[3 * ii + 1], pz = a.means3D[3 * ii + 2];
-	const float opacity = a.opacities[ii];
+	float opacity = a.opacities[ii];
+	float s0 = a.scales[3 * ii], s1 = a.scales[3 * ii + 1], s2 = a.scales[3 * ii + 2];
+	float4 q = load_f4(a.rotations, ii);
+	if (LEAF) { opacity = act_opacity(opacity); s0 = act_scale(s0); s1 = act_scale(s1); s2 = act_scale(s2); q = act_rot(q); }
 	float c3[6];
-	cov3d_from_scale_rot(a.scales[3 * ii], a.scales[3 * ii + 1], a.scales[3 * ii + 2], a.scale_modifier, load_f4(a.rotations, ii), c3);
+	cov3d_from_scale_rot(s0, s1, s2, a.scale_modifier, q, c3);
 
 	for (int v = 0; v < nv; v++) {
 		const float* cam = s_cam[v];
@@ -416,7 +427,9 @@ int launch_preprocess_fwd(cudaStream_t stream, const PreprocessArgs& a)
 int launch_preprocess_views(cudaStream_t stream, const PreprocessViewsArgs& a)
 {
 	if (a.P == 0 || a.nviews == 0) return 0;
-	count_launch(), preprocess_views_kernel<<<(a.P + PV_THREADS - 1) / PV_THREADS, PV_THREADS, 0, stream>>>(a);
+	count_launch();
+	if (a.leaf) preprocess_views_kernel<true><<<(a.P + PV_THREADS - 1) / PV_THREADS, PV_THREADS, 0, stream>>>(a);
+	else preprocess_views_kernel<false><<<(a.P + PV_THREADS - 1) / PV_THREADS, PV_THREADS, 0, stream>>>(a);
 	return check_launch("preprocess_views", stream, false);
 }
 

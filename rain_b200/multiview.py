@@ -89,7 +89,7 @@ class ViewResult:
 def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int], bucket: GradientBucket,
                          grad_fn: Callable[[int, torch.Tensor, torch.Tensor], torch.Tensor], *, bg: torch.Tensor, sh_degree: int,
                          scale_modifier: float = 1.0, low_pass: float = 0.3, debug: bool = False, keep_outputs: bool = True,
-                         pipeline: str = "two_stream", batch_backward: int = 8, batch_forward: int = 8, stats=None, backend=_native) -> List[ViewResult]:
+                         pipeline: str = "two_stream", batch_backward: int = 8, batch_forward: int = 8, stats=None, leaves: Optional[dict] = None, backend=_native) -> List[ViewResult]:
     """Forward + backward of this rank's views; parameter gradients of all views are summed into ``bucket``.
 
     params: dict(means3D[P,3], opacities[P,1], shs[P,M,3], scales[P,3], rotations[P,4]) — activated values, as
@@ -106,11 +106,20 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
     batch_forward = B > 0 (default 8): the per-Gaussian half of the forward — preprocess, depth sort, prefix sum — runs ONCE per
     B views (rr_forward_geom_views: parameters read once and projected through every camera, one segmented sort, one segmented
     scan; per-view outputs bit-identical to the per-view call's).  0 restores one rr_forward_geom per view.
+    leaves (opt-in fast path next to the unchanged API): dict(xyz, f_dc[P,1,3], f_rest[P,15,3], opacity,
+    scaling, rotation) — the six RAW leaf tensors of scene/gaussian_model.py:131-136.  ``params`` may then be None: the batched
+    geometry pass applies sigmoid / exp / normalise / cat itself, the batched backward applies their chain rule and writes LEAF
+    gradients into ``bucket`` (which must have layout="leaf"); no activated copy of the parameters exists anywhere.
     stats: optional rain_b200.optim.DensificationStats; the batched backward folds the views' densification statistics into
     its per-step delta in the same pass (otherwise call stats.add_view per view)."""
     if pipeline not in ("two_stream", "one_stream"):
         raise ValueError(f"unknown pipeline {pipeline!r}")
-    batched = batch_backward > 0 and hasattr(backend, "backward_views") and bucket.M == 16 and bucket.layout == "activated"
+    leaf = leaves is not None
+    if leaf:
+        if bucket.layout != "leaf" or batch_backward <= 0 or batch_forward <= 0 or backend is not _native or _native.tile_cull_enabled():
+            raise RuntimeError("the leaf fast path needs a layout='leaf' bucket and the view-batched forward and backward (batch sizes > 0, no tile culling)")
+        params = dict(means3D=leaves["xyz"], shs=leaves["f_dc"], opacities=leaves["opacity"], scales=leaves["scaling"], rotations=leaves["rotation"])
+    batched = batch_backward > 0 and hasattr(backend, "backward_views") and bucket.M == 16 and bucket.layout == ("leaf" if leaf else "activated")
     fbatch = min(int(batch_forward), 16) if (batch_forward > 0 and hasattr(backend, "forward_geom_views") and bucket.M == 16) else 0
     if fbatch and backend is _native and _native.tile_cull_enabled():
         fbatch = 0               # the opt-in tile culling lives in the per-view preprocess kernel only
@@ -143,7 +152,8 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
             hi = min(n, lo + fbatch)
             sts = backend.forward_geom_views(bg, params["means3D"], params["opacities"], params["scales"], params["rotations"], scale_modifier,
                                              [cameras[view_ids[j]] for j in range(lo, hi)], cameras[view_ids[lo]].height, cameras[view_ids[lo]].width,
-                                             params["shs"], sh_degree, debug, low_pass, stream=stream, keep_cov3D=not batched)
+                                             params["shs"], sh_degree, debug, low_pass, stream=stream, keep_cov3D=not batched,
+                                             **(dict(leaf=True, f_rest=leaves["f_rest"]) if leaf else {}))
             states.update(zip(range(lo, hi), sts))
         elif has_split:
             states[pos] = backend.forward_geom(*raster_args(view_ids[pos]), **({"stream": stream} if stream is not None else {}))
@@ -196,7 +206,8 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
             if len(group) == batch_backward or i + 1 == n:
                 backend.backward_views(group, params["means3D"], params["shs"], params["scales"], params["rotations"], scale_modifier, low_pass, sh_degree,
                                        cam.height, cam.width, bucket.grads_out(), accumulate=bucket.filled,
-                                       stats=stats.delta_tensors() if stats is not None else None, debug=debug)
+                                       stats=stats.delta_tensors() if stats is not None else None, debug=debug,
+                                       **(dict(leaf=True, f_rest=leaves["f_rest"]) if leaf else {}))
                 bucket.filled = True
                 group = []
         else:

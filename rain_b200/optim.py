@@ -34,6 +34,22 @@ class GaussianParamStep:
         self.activated = dict(means3D=self.leaves["xyz"], shs=torch.empty(P, M, 3, device=dev), opacities=torch.empty(P, 1, device=dev),
                               scales=torch.empty(P, 3, device=dev), rotations=torch.empty(P, 4, device=dev))
 
+    def step_leaf(self, grads_flat):
+        """grads_flat: flat f32 [P*(11+3M)] in the LEAF bucket layout (GradientBucket(layout="leaf"), gradients w.r.t. the raw leaves
+        as the leaf fast path of rain_b200.multiview produces them).  Plain Adam over the six leaves; returns the leaves dict, which
+        is what the next leaf-mode render reads (no activated copies)."""
+        lib = _lib.load()
+        if not grads_flat.is_cuda or grads_flat.numel() != self.exp_avg.numel():
+            raise RuntimeError("grads_flat must be the CUDA gradient bucket of this parameter set")
+        self.steps += 1
+        hyper = (ctypes.c_float * 9)(*[float(self.lrs[k]) for k in GROUPS], float(self.betas[0]), float(self.betas[1]), float(self.eps))
+        L = self.leaves
+        with torch.cuda.device(grads_flat.device):
+            _lib.check(lib.rr_param_step_leaf(torch.cuda.current_stream().cuda_stream, self.P, self.M, L["xyz"].data_ptr(), L["f_dc"].data_ptr(),
+                                              L["f_rest"].data_ptr() if self.M > 1 else None, L["opacity"].data_ptr(), L["scaling"].data_ptr(), L["rotation"].data_ptr(),
+                                              self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), grads_flat.data_ptr(), hyper, self.steps), "rr_param_step_leaf")
+        return L
+
     def step(self, grads_flat):
         """grads_flat: flat f32 [P*(11+3M)] in the bucket layout (w.r.t. the activated values).  Returns the activated
         inputs of the next render: dict(means3D, shs, opacities, scales, rotations)."""

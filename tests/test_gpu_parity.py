@@ -461,6 +461,50 @@ def test_backward_views_leaf_mode_applies_the_activation_chain_rule(device):
         assert rel_err(L.views[k], leaves[k].grad.reshape(L.views[k].shape))[0] < 5e-5, k
 
 
+def test_leaf_fast_path_forward_and_step(device):
+    """The opt-in leaf mode end to end: rr_forward_geom_views with RR_GEOM_LEAF on the raw leaves gives,
+    bit for bit, what the activated path gives on rr_activate's outputs (one set of activation device functions); rr_activate
+    agrees with torch's sigmoid / exp / F.normalize to a few ulp; and a whole multi-view step on the leaves fills a leaf-layout
+    bucket equal to torch's chain rule applied to the activated-path bucket."""
+    from rain_b200 import multiview as mv
+    P, W, H, D, V = 30001, 160, 96, 3, 4
+    sc = make_scene(P, D, 8)
+    gen = torch.Generator().manual_seed(3)
+    op = sc.opacities.clamp(1e-4, 1 - 1e-4)
+    leaves = dict(xyz=sc.means3D.clone(), f_dc=sc.shs[:, 0:1, :].contiguous(), f_rest=sc.shs[:, 1:, :].contiguous(), opacity=torch.log(op / (1 - op)),
+                  scaling=torch.log(sc.scales), rotation=sc.rotations * (0.5 + torch.rand(P, 1, generator=gen)))
+    leaves = {k: v.to(device).contiguous() for k, v in leaves.items()}
+    o_a, s_a, r_a = _C.activate(leaves["opacity"], leaves["scaling"], leaves["rotation"])
+    assert rel_err(o_a, torch.sigmoid(leaves["opacity"]))[0] < 1e-6 and rel_err(s_a, torch.exp(leaves["scaling"]))[0] < 1e-6
+    assert rel_err(r_a, torch.nn.functional.normalize(leaves["rotation"]))[0] < 1e-6
+    shs = torch.cat((leaves["f_dc"], leaves["f_rest"]), dim=1).contiguous()
+    cams = [make_camera(v, V, W, H).to(device) for v in range(V)]
+    bg = torch.zeros(3, device=device)
+    A = _C.forward_geom_views(bg, leaves["xyz"], o_a, s_a, r_a, 1.0, cams, H, W, shs, D, False, 0.3)
+    L = _C.forward_geom_views(bg, leaves["xyz"], leaves["opacity"], leaves["scaling"], leaves["rotation"], 1.0, cams, H, W, leaves["f_dc"], D, False, 0.3,
+                              leaf=True, f_rest=leaves["f_rest"])
+    for a, l in zip(A, L):
+        Na, ca, ra, da, *_ = _C.forward_raster(a)
+        Nl, cl, rl, dl, *_ = _C.forward_raster(l)
+        assert Na == Nl and eq(ra, rl) and eq(ca, cl) and eq(da, dl)
+    # a whole step on the leaves against the activated path + torch's chain rule
+    dp = [make_grad(W, H, 60 + v).to(device) for v in range(V)]
+    bl = mv.GradientBucket(P, 16, device, layout="leaf"); bl.flat.fill_(float("nan"))
+    res_l = mv.train_step_views(None, cams, V, bl, lambda v, c, d: dp[v], bg=bg, sh_degree=D, leaves=leaves)
+    req = {k: v.clone().requires_grad_(True) for k, v in leaves.items()}
+    act = dict(means3D=req["xyz"], shs=torch.cat((req["f_dc"], req["f_rest"]), dim=1), opacities=torch.sigmoid(req["opacity"]),
+               scales=torch.exp(req["scaling"]), rotations=torch.nn.functional.normalize(req["rotation"]))
+    ba = mv.GradientBucket(P, 16, device)
+    res_a = mv.train_step_views({k: v.detach().contiguous() for k, v in act.items()}, cams, V, ba, lambda v, c, d: dp[v], bg=bg, sh_degree=D)
+    torch.autograd.backward([act["means3D"], act["shs"], act["opacities"], act["scales"], act["rotations"]],
+                            [ba.views["means3D"], ba.views["sh"], ba.views["opacity"], ba.views["scales"], ba.views["rotations"]])
+    for a, l in zip(res_a, res_l):
+        assert rel_err(l.color, a.color)[0] < 1e-5 and (l.radii != a.radii).float().mean().item() < 1e-4      # torch's activations are an ulp or two away
+    for k in mv.LEAF_SEGMENTS:
+        assert torch.isfinite(bl.views[k]).all(), k
+        assert rel_err(bl.views[k], req[k].grad.reshape(bl.views[k].shape))[0] < 1e-4, k
+
+
 def _sort_case(device, n, key_bytes, b0, b1, seed, skew):
     lib = _lib.load()
     g = torch.Generator().manual_seed(seed)

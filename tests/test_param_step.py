@@ -172,3 +172,31 @@ def test_densify_stats_kernel_matches_oracle(device):
             assert np.allclose(a, b.cpu().numpy().reshape(P), rtol=1e-6, atol=0)
     with pytest.raises(RuntimeError):
         add_densification_stats(radii, grad, mx, acc, den)
+
+
+@pytest.mark.gpu
+def test_leaf_step_matches_torch_adam(device):
+    """rr_param_step_leaf (Adam over the six raw leaves from LEAF gradients in the leaf bucket layout) against torch.optim.Adam
+    with the reference's parameter groups (scene/gaussian_model.py:139-157: per-group lr, eps 1e-15) on the same gradients."""
+    from rain_b200.multiview import GradientBucket, LEAF_SEGMENTS
+    from rain_b200.optim import GaussianParamStep
+    gen = torch.Generator().manual_seed(7)
+    P = 1234
+    shapes = dict(xyz=(P, 3), f_dc=(P, 1, 3), f_rest=(P, 15, 3), opacity=(P, 1), scaling=(P, 3), rotation=(P, 4))
+    init = {k: torch.randn(*shp, generator=gen) for k, shp in shapes.items()}
+    lrs = dict(xyz=1.6e-4, f_dc=2.5e-3, f_rest=1.25e-4, opacity=0.05, scaling=5e-3, rotation=1e-3)
+    mine = {k: v.clone().to(device) for k, v in init.items()}
+    ref = {k: torch.nn.Parameter(v.clone().to(device)) for k, v in init.items()}
+    adam = torch.optim.Adam([{"params": [ref[k]], "lr": lrs[k]} for k in LEAF_SEGMENTS], lr=0.0, eps=1e-15)
+    opt = GaussianParamStep(mine, lrs)
+    bucket = GradientBucket(P, 16, device, layout="leaf")
+    for step in range(3):
+        for k in LEAF_SEGMENTS:
+            g = torch.randn(*shapes[k], generator=gen).to(device) * (10.0 ** (step - 1))
+            bucket.views[k].copy_(g)
+            ref[k].grad = g.clone()
+        adam.step()
+        out = opt.step_leaf(bucket.flat)
+        for k in LEAF_SEGMENTS:
+            assert rel(out[k].cpu().numpy(), ref[k].detach().cpu().numpy()) <= 2e-6, (step, k)
+            assert rel((out[k].cpu() - init[k]).numpy(), (ref[k].detach().cpu() - init[k]).numpy()) <= 2e-4, (step, k)
