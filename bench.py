@@ -126,7 +126,10 @@ def stage_bytes(name, P, V, N, X, M=16, views=1):
         "depth_sort": (4 + 4 * 16) * P,                                # histogram read + 4 passes x (key+value read, key+value write)
         "scan": 12 * P,                                                # order + tiles_touched in, offsets out
         "duplicate": 16 * P + 8 * N,                                   # order/offsets/rect in, tile key + Gaussian id out
-        "tile_sort": (4 + 2 * 16) * N,                                 # histogram read + 2 passes x 16 B
+        "tile_sort": (4 + 2 * 16) * N,                                 # (unfused fallback) histogram read + 2 passes x 16 B
+        # fused tile sort = duplicate + sort + ranges in one stage: order / offsets / rect in twice (tile plan, pair generation),
+        # pass 0 writes 2 B key + 4 B id per pair, pass 1 reads them and writes the 4 B id; ranges out
+        "tile_sort_fused": 24 * P + 16 * N,
         "ranges": 4 * N,                                               # sorted tile keys in (ranges out: 8 B per tile)
         "render_fwd": 52 * N + N + 24 * X,                             # id + gathered record per list entry, 8 flag bits out; colour 12 + depth 4 + final_T 4 + n_contrib 4 out
         "render_bwd": 52 * N + N + 20 * X + 96 * P,                    # id + record + flag bits in, dL_dpix/T/n in, accumulator zero fill + read-modify-write
@@ -494,7 +497,7 @@ def main():
             continue
         per = ms / n
         e = {"ms": round(per, 4), "share": None, "bound": "hbm" if name in HBM_STAGES else "issue"}
-        b = stage_bytes(name, P, r["V"], N, X, views=VPS)
+        b = stage_bytes("tile_sort_fused" if (name == "tile_sort" and r["stage"].get("duplicate", (0, 0))[1] == 0) else name, P, r["V"], N, X, views=VPS)
         if b:
             e.update(alg_bytes=b, gbs=round(b / per / 1e6, 1), frac_of_hbm=round(b / per / 1e6 / peak, 4))
         if name in ("render_fwd", "render_bwd") and pairs:

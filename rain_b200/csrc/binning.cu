@@ -55,6 +55,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_chained_kernel(int P, int n
 	uint32_t* __restrict__ offsets = sg.offsets[blockIdx.y];             // inclusive, depth order
 	uint32_t* __restrict__ total = sg.total[blockIdx.y];
 	uint32_t* __restrict__ total_host = sg.total_host[blockIdx.y];
+	uint32_t* __restrict__ tile_start = sg.tile_start[blockIdx.y];      // or null
 	__shared__ uint32_t s_warp[SCAN_THREADS / 32];
 	__shared__ uint32_t s_tile, s_excl;
 	if (threadIdx.x == 0) s_tile = atomicAdd(const_cast<uint32_t*>(status) + nb, 1u);
@@ -100,8 +101,15 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_chained_kernel(int P, int n
 	#pragma unroll
 	for (int k = 0; k < SCAN_ITEMS; k++) {
 		const int i = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS + k;
+		const uint32_t excl = run;
 		run += v[k];
-		if (i < P) offsets[i] = run;
+		if (i < P) {
+			offsets[i] = run;
+			// owner of the first slot of every PAIR_TILE-slot output tile that starts inside this Gaussian's span [excl, run): the
+			// fused expansion + first sort pass (radix_sort.cu) starts each tile from it
+			if (tile_start && v[k] && run < SC_MASK)
+				for (uint32_t b = (excl + PAIR_TILE - 1) / PAIR_TILE; b * PAIR_TILE < run; b++) tile_start[b] = (uint32_t)i;
+		}
 	}
 }
 
@@ -198,6 +206,88 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(uint32_t N, const uint
 	}
 }
 
+// ---- tile plan: per-tile pair counts -> ranges and the digit bases of the tile sort, without touching a pair ----------------
+// The pairs of tile t are exactly the visible Gaussians whose rect covers t, so count[t] follows from the rects alone: every
+// Gaussian adds +1 / -1 at the four corners of its rect in a (grid_x + 1) x (grid_y + 1) difference grid (four shared-memory
+// atomics per Gaussian, whatever the size of its rect), and the 2-D prefix sum of that grid is the count.  From the counts:
+// ranges[t] = [start, start + count) (identifyTileRanges, rasterizer_impl.cu:105-127, incl. the zero fill of :302 for empty
+// tiles) and the exclusive digit bases of both radix passes — so the tile sort needs no histogram pass over the 8-byte pairs,
+// no sorted key array, and no range-detection pass.
+constexpr int PLAN_MAX_CELLS = 11264;       // (grid_x + 1) * (grid_y + 1) ints in shared memory (44 KB); 1920x1080 needs 8 349
+
+__global__ void __launch_bounds__(256) tile_diff_kernel(int P, int cells, int gx1, const uint32_t* __restrict__ tiles_touched, const uint2* __restrict__ rect,
+	int* __restrict__ gdiff /*[cells], zero on entry*/)
+{
+	__shared__ int s_d[PLAN_MAX_CELLS];
+	for (int i = threadIdx.x; i < cells; i += 256) s_d[i] = 0;
+	__syncthreads();
+	for (int i = blockIdx.x * 256 + threadIdx.x; i < P; i += gridDim.x * 256) {
+		if (tiles_touched[i] == 0) continue;
+		const uint2 r = rect[i];
+		const int x0 = r.x & 0xffff, x1 = r.x >> 16, y0 = r.y & 0xffff, y1 = r.y >> 16;
+		atomicAdd(&s_d[y0 * gx1 + x0], 1); atomicAdd(&s_d[y0 * gx1 + x1], -1);
+		atomicAdd(&s_d[y1 * gx1 + x0], -1); atomicAdd(&s_d[y1 * gx1 + x1], 1);
+	}
+	__syncthreads();
+	for (int i = threadIdx.x; i < cells; i += 256) { const int v = s_d[i]; if (v) atomicAdd(&gdiff[i], v); }
+}
+
+constexpr int PLAN_THREADS = 1024;
+__global__ void __launch_bounds__(PLAN_THREADS) tile_plan_kernel(int grid_x, int grid_y, const int* __restrict__ gdiff, uint2* __restrict__ ranges,
+	uint32_t* __restrict__ ghist /*[npass][256] exclusive digit bases out*/, int npass, int shift0, uint32_t mask0, int shift1, uint32_t mask1)
+{
+	__shared__ int s_c[PLAN_MAX_CELLS];
+	__shared__ uint32_t s_h[2][256];
+	__shared__ uint32_t s_wsum[PLAN_THREADS / 32];
+	__shared__ uint32_t s_carry;
+	const int tid = threadIdx.x, gx1 = grid_x + 1, gy1 = grid_y + 1, T = grid_x * grid_y;
+	for (int i = tid; i < gx1 * gy1; i += PLAN_THREADS) s_c[i] = gdiff[i];
+	if (tid < 512) (&s_h[0][0])[tid] = 0;
+	if (tid == 0) s_carry = 0;
+	__syncthreads();
+	if (tid < gy1) { int run = 0; for (int x = 0; x < gx1; x++) { run += s_c[tid * gx1 + x]; s_c[tid * gx1 + x] = run; } }     // along rows
+	__syncthreads();
+	if (tid < gx1) { int run = 0; for (int y = 0; y < gy1; y++) { run += s_c[y * gx1 + tid]; s_c[y * gx1 + tid] = run; } }     // along columns
+	__syncthreads();
+	// exclusive scan of the counts in tile order (t = y * grid_x + x), PLAN_THREADS tiles per round
+	for (int base = 0; base < T; base += PLAN_THREADS) {
+		const int t = base + tid;
+		uint32_t c = 0;
+		if (t < T) { const int y = t / grid_x, x = t - y * grid_x; c = (uint32_t)s_c[y * gx1 + x]; }
+		uint32_t inc = c;
+		#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) { const uint32_t u = __shfl_up_sync(FULL, inc, o); if ((tid & 31) >= o) inc += u; }
+		if ((tid & 31) == 31) s_wsum[tid >> 5] = inc;
+		__syncthreads();
+		uint32_t pre = s_carry;
+		for (int w = 0; w < (tid >> 5); w++) pre += s_wsum[w];
+		const uint32_t start = pre + inc - c;
+		if (t < T) {
+			ranges[t] = c ? make_uint2(start, start + c) : make_uint2(0u, 0u);
+			if (c) {
+				atomicAdd(&s_h[0][((uint32_t)t >> shift0) & mask0], c);
+				if (npass > 1) atomicAdd(&s_h[1][((uint32_t)t >> shift1) & mask1], c);
+			}
+		}
+		__syncthreads();
+		if (tid == PLAN_THREADS - 1) s_carry = pre + inc;
+		__syncthreads();
+	}
+	// exclusive digit bases of each pass: warp p scans its 256 bins
+	if (tid < 32 * npass) {
+		const int p = tid >> 5, lane = tid & 31;
+		uint32_t carry = 0;
+		for (int b = 0; b < 256; b += 32) {
+			const uint32_t c = s_h[p][b + lane];
+			uint32_t inc = c;
+			#pragma unroll
+			for (int o = 1; o < 32; o <<= 1) { const uint32_t u = __shfl_up_sync(FULL, inc, o); if (lane >= o) inc += u; }
+			ghist[p * 256 + b + lane] = carry + inc - c;
+			carry += __shfl_sync(FULL, inc, 31);
+		}
+	}
+}
+
 // the 64-bit (tile << 32 | depth bits) key list the reference would hold (point_list_keys, rasterizer_impl.cu:92),
 // reconstructed from ranges + point_list for the parity tests; depth bits = float index 9 (c.y) of the 12-float record
 __global__ void __launch_bounds__(128) export_keys_kernel(int T, const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
@@ -225,9 +315,10 @@ int launch_scan_tiles_segments(cudaStream_t stream, int P, int nseg, const ScanS
 }
 
 int launch_scan_tiles(cudaStream_t stream, int P, const uint32_t* order, const uint32_t* tt, uint32_t* offsets, uint32_t* block_sums, uint32_t* num_rendered_dev,
-	uint32_t* num_rendered_mapped)
+	uint32_t* num_rendered_mapped, uint32_t* tile_start)
 {
 	ScanSegs sg; memset(&sg, 0, sizeof(sg));
+	sg.tile_start[0] = tile_start;
 	sg.order[0] = order; sg.tiles_touched[0] = tt; sg.status[0] = block_sums; sg.offsets[0] = offsets; sg.total[0] = num_rendered_dev; sg.total_host[0] = num_rendered_mapped;
 	return launch_scan_tiles_segments(stream, P, 1, sg);
 }
@@ -246,6 +337,20 @@ int launch_tile_ranges(cudaStream_t stream, size_t N, const uint32_t* keys, uint
 	if (N == 0) return 0;
 	count_launch(), tile_ranges_kernel<<<(unsigned)((N + 1023) / 1024), 256, 0, stream>>>((uint32_t)N, keys, ranges);
 	return check_launch("tile_ranges", stream, false);
+}
+
+bool tile_plan_supported(int grid_x, int grid_y) { return (grid_x + 1) * (grid_y + 1) <= PLAN_MAX_CELLS && grid_x < 65535 && grid_y < 65535; }
+size_t tile_plan_ws_bytes(int grid_x, int grid_y) { return sizeof(int) * (size_t)(grid_x + 1) * (grid_y + 1); }
+
+int launch_tile_plan(cudaStream_t stream, int P, int grid_x, int grid_y, const uint32_t* tiles_touched, const uint2* rect, int* gdiff, uint2* ranges,
+	uint32_t* ghist, int npass, const int* shift, const uint32_t* mask)
+{
+	const int cells = (grid_x + 1) * (grid_y + 1);
+	cudaMemsetAsync(gdiff, 0, sizeof(int) * (size_t)cells, stream);
+	const int ctas = min((P + 255) / 256, 148 * 2);
+	count_launch(), tile_diff_kernel<<<ctas, 256, 0, stream>>>(P, cells, grid_x + 1, tiles_touched, rect, gdiff);
+	count_launch(), tile_plan_kernel<<<1, PLAN_THREADS, 0, stream>>>(grid_x, grid_y, gdiff, ranges, ghist, npass, shift[0], mask[0], npass > 1 ? shift[1] : 0, npass > 1 ? mask[1] : 0u);
+	return check_launch("tile_plan", stream, false);
 }
 
 int launch_export_keys(cudaStream_t stream, int T, const uint2* ranges, const uint32_t* point_list, const uint32_t* rec_words, uint64_t* out)
