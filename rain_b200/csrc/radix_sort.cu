@@ -164,9 +164,9 @@ __global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp
 	__shared__ uint32_t s_dstart[RADIX];
 	__shared__ uint32_t s_goff[RADIX];
 	__shared__ uint32_t s_wtot[SORT_WARPS];
-	__shared__ K s_keys[TILE];
-	__shared__ uint32_t s_vals[TILE];
-	__shared__ uint16_t s_head[EXPAND ? TILE : 2];      // EXPAND: rank (relative to the tile's first owner) of the Gaussian whose span starts at a slot, 0 = none
+	__shared__ __align__(16) K s_keys[TILE];          // also viewed as 32-bit words (match table)
+	__shared__ __align__(16) uint32_t s_vals[TILE];
+	__shared__ __align__(16) uint16_t s_head[EXPAND ? TILE : 8];      // EXPAND: rank (relative to the tile's first owner) of the Gaussian whose span starts at a slot, 0 = none
 
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 	const int nbits = __popc(mask);
