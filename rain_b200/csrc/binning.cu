@@ -215,21 +215,32 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(uint32_t N, const uint
 // no sorted key array, and no range-detection pass.
 constexpr int PLAN_MAX_CELLS = 11264;       // (grid_x + 1) * (grid_y + 1) ints in shared memory (44 KB); 1920x1080 needs 8 349
 
-__global__ void __launch_bounds__(256) tile_diff_kernel(int P, int cells, int gx1, const uint32_t* __restrict__ tiles_touched, const uint2* __restrict__ rect,
+constexpr int DIFF_THREADS = 512;
+__global__ void __launch_bounds__(DIFF_THREADS) tile_diff_kernel(int P, int cells, int gx1, const uint32_t* __restrict__ tiles_touched, const uint2* __restrict__ rect,
 	int* __restrict__ gdiff /*[cells], zero on entry*/)
 {
 	__shared__ int s_d[PLAN_MAX_CELLS];
-	for (int i = threadIdx.x; i < cells; i += 256) s_d[i] = 0;
+	for (int i = threadIdx.x; i < cells; i += DIFF_THREADS) s_d[i] = 0;
 	__syncthreads();
-	for (int i = blockIdx.x * 256 + threadIdx.x; i < P; i += gridDim.x * 256) {
-		if (tiles_touched[i] == 0) continue;
-		const uint2 r = rect[i];
-		const int x0 = r.x & 0xffff, x1 = r.x >> 16, y0 = r.y & 0xffff, y1 = r.y >> 16;
-		atomicAdd(&s_d[y0 * gx1 + x0], 1); atomicAdd(&s_d[y0 * gx1 + x1], -1);
-		atomicAdd(&s_d[y1 * gx1 + x0], -1); atomicAdd(&s_d[y1 * gx1 + x1], 1);
+	// one CTA per SM, four Gaussians in flight per thread: few CTAs keep the flush below small (cells atomics per CTA)
+	const int stride = gridDim.x * DIFF_THREADS;
+	for (int i0 = blockIdx.x * DIFF_THREADS + threadIdx.x; i0 < P; i0 += 4 * stride) {
+		uint32_t tt[4];
+		uint2 r[4];
+		#pragma unroll
+		for (int u = 0; u < 4; u++) { const int i = i0 + u * stride; tt[u] = i < P ? __ldg(tiles_touched + i) : 0u; }
+		#pragma unroll
+		for (int u = 0; u < 4; u++) { const int i = i0 + u * stride; r[u] = tt[u] ? __ldg(rect + i) : make_uint2(0u, 0u); }
+		#pragma unroll
+		for (int u = 0; u < 4; u++) {
+			if (tt[u] == 0) continue;
+			const int x0 = r[u].x & 0xffff, x1 = r[u].x >> 16, y0 = r[u].y & 0xffff, y1 = r[u].y >> 16;
+			atomicAdd(&s_d[y0 * gx1 + x0], 1); atomicAdd(&s_d[y0 * gx1 + x1], -1);
+			atomicAdd(&s_d[y1 * gx1 + x0], -1); atomicAdd(&s_d[y1 * gx1 + x1], 1);
+		}
 	}
 	__syncthreads();
-	for (int i = threadIdx.x; i < cells; i += 256) { const int v = s_d[i]; if (v) atomicAdd(&gdiff[i], v); }
+	for (int i = threadIdx.x; i < cells; i += DIFF_THREADS) { const int v = s_d[i]; if (v) atomicAdd(&gdiff[i], v); }
 }
 
 constexpr int PLAN_THREADS = 1024;
@@ -245,7 +256,17 @@ __global__ void __launch_bounds__(PLAN_THREADS) tile_plan_kernel(int grid_x, int
 	if (tid < 512) (&s_h[0][0])[tid] = 0;
 	if (tid == 0) s_carry = 0;
 	__syncthreads();
-	if (tid < gy1) { int run = 0; for (int x = 0; x < gx1; x++) { run += s_c[tid * gx1 + x]; s_c[tid * gx1 + x] = run; } }     // along rows
+	for (int y = tid >> 5; y < gy1; y += PLAN_THREADS / 32) {                                                                 // along rows: one warp per row
+		int carry = 0;
+		for (int xb = 0; xb < gx1; xb += 32) {
+			const int x = xb + (tid & 31);
+			int v = x < gx1 ? s_c[y * gx1 + x] : 0;
+			#pragma unroll
+			for (int o = 1; o < 32; o <<= 1) { const int u = __shfl_up_sync(FULL, v, o); if ((tid & 31) >= o) v += u; }
+			if (x < gx1) s_c[y * gx1 + x] = v + carry;
+			carry += __shfl_sync(FULL, v, 31);
+		}
+	}
 	__syncthreads();
 	if (tid < gx1) { int run = 0; for (int y = 0; y < gy1; y++) { run += s_c[y * gx1 + tid]; s_c[y * gx1 + tid] = run; } }     // along columns
 	__syncthreads();
@@ -347,8 +368,8 @@ int launch_tile_plan(cudaStream_t stream, int P, int grid_x, int grid_y, const u
 {
 	const int cells = (grid_x + 1) * (grid_y + 1);
 	cudaMemsetAsync(gdiff, 0, sizeof(int) * (size_t)cells, stream);
-	const int ctas = min((P + 255) / 256, 148 * 2);
-	count_launch(), tile_diff_kernel<<<ctas, 256, 0, stream>>>(P, cells, grid_x + 1, tiles_touched, rect, gdiff);
+	const int ctas = min((P + DIFF_THREADS * 4 - 1) / (DIFF_THREADS * 4), 148);
+	count_launch(), tile_diff_kernel<<<ctas, DIFF_THREADS, 0, stream>>>(P, cells, grid_x + 1, tiles_touched, rect, gdiff);
 	count_launch(), tile_plan_kernel<<<1, PLAN_THREADS, 0, stream>>>(grid_x, grid_y, gdiff, ranges, ghist, npass, shift[0], mask[0], npass > 1 ? shift[1] : 0, npass > 1 ? mask[1] : 0u);
 	return check_launch("tile_plan", stream, false);
 }

@@ -185,14 +185,12 @@ __global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp
 		static_assert(!EXPAND || (TILE == (int)PAIR_TILE && sizeof(K) == 2), "the fused first pass works on PAIR_TILE slots with 16-bit tile ids");
 		// ---- generate the tile's pairs in slot order into s_keys (tile ids) / s_vals (Gaussian ids) ----
 		const uint32_t j0 = ex.tile_start[tile], end = tile_base + tile_count;
-		// every later Gaussian of the tile marks the slot its span starts at (each owns >= 1 slot, so at most tile_count of them)
-		for (uint32_t base = 0; base < tile_count; base += SORT_THREADS) {
-			const uint32_t lj = base + tid + 1, j = j0 + lj;
-			uint32_t excl = 0xFFFFFFFFu;
-			if (lj <= tile_count && j < (uint32_t)ex.P) excl = ex.offsets[j - 1];
-			const bool in = excl < end;
-			if (in) s_head[excl - tile_base] = (uint16_t)lj;       // excl >= inclusive offset of j0 > tile_base
-			if (__syncthreads_and(!in)) break;                      // spans start in rank order: nothing further can start inside the tile
+		// every later Gaussian of the tile marks the slot its span starts at: ranks j0 + 1 .. the first owner of the next tile
+		// (each owns >= 1 slot, so at most tile_count of them); independent loads, no votes
+		const uint32_t jlast = (tile + 1 < ntiles) ? ex.tile_start[tile + 1] : min((uint32_t)ex.P - 1u, j0 + tile_count);
+		for (uint32_t lj = tid + 1; j0 + lj <= jlast; lj += SORT_THREADS) {
+			const uint32_t excl = ex.offsets[j0 + lj - 1];
+			if (excl < end) s_head[excl - tile_base] = (uint16_t)lj;       // excl >= inclusive offset of j0 > tile_base
 		}
 		__syncthreads();
 		// owner of each slot = the largest mark at or before it: blocked max-scan, thread t owns slots [16 t, 16 t + 16)
@@ -216,24 +214,37 @@ __global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp
 			__syncthreads();                                        // s_wtot is reused below
 		}
 		// tile id of each slot: row-major walk of the owner's rect (rasterizer_impl.cu:87-98), continued incrementally while
-		// consecutive slots stay with the same owner
-		uint32_t cur = 0xFFFFFFFFu, g = 0, x0 = 0, wdt = 1, rx = 0, ry = 0, y0 = 0;
+		// consecutive slots stay with the same owner.  The owners' ids / offsets / rects are fetched for 8 slots at a time with
+		// independent loads (two round trips per 8 slots, not two per change of owner; repeated owners hit L1).
+		uint32_t cur = 0xFFFFFFFFu, wdt = 1, rx = 0, ry = 0, xb = 0;
 		#pragma unroll
-		for (int k = 0; k < IPT; k++) {
-			const uint32_t sl = (uint32_t)tid * IPT + k;
-			if (sl < tile_count) {
-				if (own[k] != cur) {
-					cur = own[k];
-					const uint32_t j = j0 + cur;
-					g = ex.order[j];
-					const uint32_t excl = j ? ex.offsets[j - 1] : 0u;
-					const uint2 r = ex.rect[g];
-					x0 = r.x & 0xffffu; wdt = (r.x >> 16) - x0; y0 = r.y & 0xffffu;
-					const uint32_t local = tile_base + sl - excl;
-					ry = local / wdt; rx = local - ry * wdt;
-				} else if (++rx == wdt) { rx = 0; ry++; }
-				s_keys[sl] = (K)((y0 + ry) * (uint32_t)ex.grid_x + x0 + rx);
-				s_vals[sl] = g;                                     // the sort's value, as in the reference (rasterizer_impl.cu:92)
+		for (int h = 0; h < IPT; h += 8) {
+			uint32_t gg[8], ee[8];
+			uint2 rr[8];
+			#pragma unroll
+			for (int k = 0; k < 8; k++) {
+				const uint32_t sl = (uint32_t)tid * IPT + h + k, j = j0 + own[h + k];
+				const bool valid = sl < tile_count;
+				gg[k] = valid ? __ldg(ex.order + j) : 0u;
+				ee[k] = (valid && j) ? __ldg(ex.offsets + j - 1) : 0u;
+			}
+			#pragma unroll
+			for (int k = 0; k < 8; k++) rr[k] = __ldg(ex.rect + gg[k]);
+			#pragma unroll
+			for (int k = 0; k < 8; k++) {
+				const uint32_t sl = (uint32_t)tid * IPT + h + k;
+				if (sl < tile_count) {
+					if (own[h + k] != cur) {
+						cur = own[h + k];
+						const uint32_t x0 = rr[k].x & 0xffffu;
+						wdt = (rr[k].x >> 16) - x0;
+						const uint32_t local = tile_base + sl - ee[k];
+						ry = local / wdt; rx = local - ry * wdt;
+						xb = (rr[k].y & 0xffffu) * (uint32_t)ex.grid_x + x0;         // tile id of the rect's first tile
+					} else if (++rx == wdt) { rx = 0; ry++; }
+					s_keys[sl] = (K)(xb + ry * (uint32_t)ex.grid_x + rx);
+					s_vals[sl] = gg[k];                                 // the sort's value, as in the reference (rasterizer_impl.cu:92)
+				}
 			}
 		}
 		__syncthreads();
