@@ -97,13 +97,9 @@ struct Stage {
 // bit length, the reference's getHigherMsb (rasterizer_impl.cu:24-39)
 int tile_bits(int num_tiles) { int b = 0; while ((num_tiles >> b) != 0) b++; return b < 1 ? 1 : b; }
 
-// entries of GeomLayout::tile_start: num_rendered < 2^30 (rr_forward_bin's limit)
-static size_t tile_start_entries() { return (size_t)((1u << 30) / PAIR_TILE + 2); }
-
 struct GeomLayout {
 	SplatRec* rec; float* cov3D; uint8_t* clamped; uint32_t* tiles_touched; uint2* rect;
 	uint32_t *key_a, *key_b, *val_a, *val_b, *offsets, *block_sums, *num_rendered; void* sort_ws;
-	uint32_t* tile_start;
 	unsigned long long* tile_mask;
 	size_t total;
 	int64_t off[9];
@@ -127,8 +123,6 @@ GeomLayout geom_layout(void* blob, int P)
 	L.num_rendered = c.take<uint32_t>(4);
 	L.sort_ws = c.take<char>(sort_ws_bytes<uint32_t>(Pz, 0, 32));
 	L.tile_mask = tile_cull_wanted() ? c.take<unsigned long long>(Pz) : nullptr;
-	// first-owner table of the fused tile sort: one entry per PAIR_TILE emission slots, sized for the num_rendered limit (1 MB)
-	L.tile_start = c.take<uint32_t>(tile_start_entries());
 	L.total = c.used();
 	char* b = reinterpret_cast<char*>(blob);
 	// depth sort: 4 passes -> result back in the *_a buffers
@@ -273,7 +267,7 @@ int rr_forward_geom(void* stream_, int P, int D, int M, int W, int H,
 			mapped = reinterpret_cast<uint32_t*>(pa.devicePointer);
 		else (void)cudaGetLastError();
 	}
-	{ Stage st(stream, ST_SCAN); if (launch_scan_tiles(stream, P, L.val_a, L.tiles_touched, L.offsets, L.block_sums, L.num_rendered, mapped, L.tile_start)) return -1; }
+	{ Stage st(stream, ST_SCAN); if (launch_scan_tiles(stream, P, L.val_a, L.tiles_touched, L.offsets, L.block_sums, L.num_rendered, mapped)) return -1; }
 	if (!mapped) cudaMemcpyAsync(num_rendered_host, L.num_rendered, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream);
 	return check_launch("forward_geom", stream, debug != 0);
 }
@@ -322,7 +316,7 @@ int rr_forward_geom_views(void* stream_, int P, int D, int M, int W, int H, int 
 		cudaPointerAttributes pa;
 		if (cudaPointerGetAttributes(&pa, num_rendered_host[v]) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer) mapped = reinterpret_cast<uint32_t*>(pa.devicePointer);
 		else (void)cudaGetLastError();
-		sg.order[v] = L.val_a; sg.tiles_touched[v] = L.tiles_touched; sg.status[v] = L.block_sums; sg.offsets[v] = L.offsets; sg.total[v] = L.num_rendered; sg.total_host[v] = mapped; sg.tile_start[v] = L.tile_start;
+		sg.order[v] = L.val_a; sg.tiles_touched[v] = L.tiles_touched; sg.status[v] = L.block_sums; sg.offsets[v] = L.offsets; sg.total[v] = L.num_rendered; sg.total_host[v] = mapped;
 	}
 	{ Stage st(stream, ST_PREPROCESS); if (launch_preprocess_views(stream, a)) return -1; }
 	if (debug && check_launch("preprocess_views", stream, true)) return -1;
@@ -349,13 +343,13 @@ int rr_forward_bin(void* stream_, int P, int W, int H, int64_t N,
 	if (G.total > geom_bytes || B.total > binning_bytes || I.total > image_bytes) { set_error("scratch blob too small"); return -1; }
 	const int grid_x = (W + TILE_X - 1) / TILE_X, grid_y = (H + TILE_Y - 1) / TILE_Y;
 
-	// Default: the fused tile sort (radix_sort.cu::tile_sort_fused — ranges and digit bases from the rects, pair generation fused
-	// into the first radix pass, value-only last pass).  The separate duplicate / sort / ranges kernels remain for what it does
-	// not cover: the opt-in tile culling (per-Gaussian tile masks) and grids beyond the tile plan's shared-memory budget.
+	// Default: 16-bit tile ids, ranges and digit bases from the tile plan, value-only last pass (radix_sort.cu::tile_sort16).  The
+	// 32-bit-key kernels below remain for what it does not cover: the opt-in tile culling (per-Gaussian tile masks) and grids
+	// beyond the tile plan's shared-memory budget.
 	if (I.plan_ws && !G.tile_mask && B.bits <= 16) {
 		Stage st(stream, ST_TILE_SORT);
-		const int which = tile_sort_fused(stream, P, (size_t)N, B.bits, grid_x, grid_y, G.val_a, G.offsets, G.rect, G.tiles_touched, G.tile_start,
-			reinterpret_cast<uint16_t*>(B.key_a), B.val_a, B.val_b, I.ranges, I.plan_ws, B.sort_ws);
+		const int which = tile_sort16(stream, P, (size_t)N, B.bits, grid_x, grid_y, G.val_a, G.offsets, G.rect, G.tiles_touched,
+			reinterpret_cast<uint16_t*>(B.key_a), reinterpret_cast<uint16_t*>(B.key_b), B.val_a, B.val_b, I.ranges, I.plan_ws, B.sort_ws);
 		if (which < 0) return -1;
 		if ((which ? B.val_b : B.val_a) != B.point_list) { set_error("internal: tile sort landed in the wrong buffer"); return -1; }
 		return check_launch("forward_bin", stream, debug != 0);

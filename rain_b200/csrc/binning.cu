@@ -55,7 +55,6 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_chained_kernel(int P, int n
 	uint32_t* __restrict__ offsets = sg.offsets[blockIdx.y];             // inclusive, depth order
 	uint32_t* __restrict__ total = sg.total[blockIdx.y];
 	uint32_t* __restrict__ total_host = sg.total_host[blockIdx.y];
-	uint32_t* __restrict__ tile_start = sg.tile_start[blockIdx.y];      // or null
 	__shared__ uint32_t s_warp[SCAN_THREADS / 32];
 	__shared__ uint32_t s_tile, s_excl;
 	if (threadIdx.x == 0) s_tile = atomicAdd(const_cast<uint32_t*>(status) + nb, 1u);
@@ -101,23 +100,17 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_chained_kernel(int P, int n
 	#pragma unroll
 	for (int k = 0; k < SCAN_ITEMS; k++) {
 		const int i = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS + k;
-		const uint32_t excl = run;
 		run += v[k];
-		if (i < P) {
-			offsets[i] = run;
-			// owner of the first slot of every PAIR_TILE-slot output tile that starts inside this Gaussian's span [excl, run): the
-			// fused expansion + first sort pass (radix_sort.cu) starts each tile from it
-			if (tile_start && v[k] && run < SC_MASK)
-				for (uint32_t b = (excl + PAIR_TILE - 1) / PAIR_TILE; b * PAIR_TILE < run; b++) tile_start[b] = (uint32_t)i;
-		}
+		if (i < P) offsets[i] = run;
 	}
 }
 
 // One warp emits the duplicates of 32 consecutive depth-sorted Gaussians cooperatively: output slot s of the warp's
 // contiguous span is owned by the last lane whose exclusive offset is <= s (binary search over 32 shared values),
 // so writes are coalesced and a large splat does not serialise on one thread (reference: one thread per rect).
+template <class K>
 __global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ offsets,
-	const uint2* __restrict__ rect, const unsigned long long* __restrict__ tile_mask, int grid_x, uint32_t* __restrict__ tile_keys,
+	const uint2* __restrict__ rect, const unsigned long long* __restrict__ tile_mask, int grid_x, K* __restrict__ tile_keys,
 	uint32_t* __restrict__ gaussian_ids)
 {
 	__shared__ unsigned long long s_mask[8][32];
@@ -174,7 +167,7 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* _
 		const uint32_t xw = s_xw[warp][lo];
 		const uint32_t w = xw >> 16, xx0 = xw & 0xffffu;
 		const uint32_t ry = local / w, rx = local - ry * w;
-		tile_keys[base + s] = (s_y0[warp][lo] + ry) * (uint32_t)grid_x + xx0 + rx;
+		tile_keys[base + s] = (K)((s_y0[warp][lo] + ry) * (uint32_t)grid_x + xx0 + rx);
 		gaussian_ids[base + s] = s_g[warp][lo];        // the sort's value, as in the reference (rasterizer_impl.cu:92)
 	}
 }
@@ -336,10 +329,9 @@ int launch_scan_tiles_segments(cudaStream_t stream, int P, int nseg, const ScanS
 }
 
 int launch_scan_tiles(cudaStream_t stream, int P, const uint32_t* order, const uint32_t* tt, uint32_t* offsets, uint32_t* block_sums, uint32_t* num_rendered_dev,
-	uint32_t* num_rendered_mapped, uint32_t* tile_start)
+	uint32_t* num_rendered_mapped)
 {
 	ScanSegs sg; memset(&sg, 0, sizeof(sg));
-	sg.tile_start[0] = tile_start;
 	sg.order[0] = order; sg.tiles_touched[0] = tt; sg.status[0] = block_sums; sg.offsets[0] = offsets; sg.total[0] = num_rendered_dev; sg.total_host[0] = num_rendered_mapped;
 	return launch_scan_tiles_segments(stream, P, 1, sg);
 }
@@ -348,7 +340,14 @@ int launch_duplicate(cudaStream_t stream, int P, const uint32_t* order, const ui
 	int grid_x, uint32_t* tile_keys, uint32_t* gaussian_ids)
 {
 	if (P == 0) return 0;
-	count_launch(), duplicate_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, order, offsets, rect, tile_mask, grid_x, tile_keys, gaussian_ids);
+	count_launch(), duplicate_kernel<uint32_t><<<(P + 255) / 256, 256, 0, stream>>>(P, order, offsets, rect, tile_mask, grid_x, tile_keys, gaussian_ids);
+	return check_launch("duplicate", stream, false);
+}
+
+int launch_duplicate16(cudaStream_t stream, int P, const uint32_t* order, const uint32_t* offsets, const uint2* rect, int grid_x, uint16_t* tile_keys, uint32_t* gaussian_ids)
+{
+	if (P == 0) return 0;
+	count_launch(), duplicate_kernel<uint16_t><<<(P + 255) / 256, 256, 0, stream>>>(P, order, offsets, rect, nullptr, grid_x, tile_keys, gaussian_ids);
 	return check_launch("duplicate", stream, false);
 }
 

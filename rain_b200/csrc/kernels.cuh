@@ -39,13 +39,10 @@ int launch_mark_visible(cudaStream_t, int P, const float* means3D, const float* 
 // binning.cu
 size_t scan_ws_elems(int P);
 int launch_scan_tiles(cudaStream_t, int P, const uint32_t* order, const uint32_t* tiles_touched, uint32_t* offsets /*inclusive, depth order*/,
-	uint32_t* block_sums, uint32_t* num_rendered_dev, uint32_t* num_rendered_mapped /*device-visible alias of a pinned host word, or null*/,
-	uint32_t* tile_start /*see ScanSegs, or null*/);
+	uint32_t* block_sums, uint32_t* num_rendered_dev, uint32_t* num_rendered_mapped /*device-visible alias of a pinned host word, or null*/);
 // the prefix sums of up to 16 views as one launch (blockIdx.y = view)
-constexpr uint32_t PAIR_TILE = 4096;      // (tile, Gaussian) pairs per CTA of the tile sort's first pass (256 threads x 16), see radix_sort.cu
 struct ScanSegs {
 	const uint32_t* order[16]; const uint32_t* tiles_touched[16]; uint32_t* status[16]; uint32_t* offsets[16]; uint32_t* total[16]; uint32_t* total_host[16];
-	uint32_t* tile_start[16];             // [2^30 / PAIR_TILE + 2] depth rank of the Gaussian that owns slot b * PAIR_TILE of the emission list, or null
 };
 int launch_scan_tiles_segments(cudaStream_t, int P, int nseg, const ScanSegs&);
 int launch_duplicate(cudaStream_t, int P, const uint32_t* order, const uint32_t* offsets, const uint2* rect, const unsigned long long* tile_mask /*or null*/, int grid_x,
@@ -55,6 +52,7 @@ bool tile_plan_supported(int grid_x, int grid_y);
 size_t tile_plan_ws_bytes(int grid_x, int grid_y);
 int launch_tile_plan(cudaStream_t, int P, int grid_x, int grid_y, const uint32_t* tiles_touched, const uint2* rect, int* gdiff /*tile_plan_ws_bytes scratch*/,
 	uint2* ranges, uint32_t* ghist /*[npass][256] out*/, int npass, const int* shift, const uint32_t* mask);
+int launch_duplicate16(cudaStream_t, int P, const uint32_t* order, const uint32_t* offsets, const uint2* rect, int grid_x, uint16_t* tile_keys, uint32_t* gaussian_ids);
 int launch_tile_ranges(cudaStream_t, size_t N, const uint32_t* sorted_tile_keys, uint2* ranges, int num_tiles);
 int launch_export_keys(cudaStream_t, int T, const uint2* ranges, const uint32_t* point_list, const uint32_t* rec_words, uint64_t* out);
 

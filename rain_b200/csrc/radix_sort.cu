@@ -36,7 +36,7 @@ constexpr uint32_t VALUE_MASK = (1u << FLAG_SHIFT) - 1;
 template <class K> struct Cfg;
 template <> struct Cfg<uint32_t> { static constexpr int IPT = 16; };
 template <> struct Cfg<uint64_t> { static constexpr int IPT = 12; };
-template <> struct Cfg<uint16_t> { static constexpr int IPT = 16; };      // tile ids of the fused tile sort (PAIR_TILE = 256 x 16)
+template <> struct Cfg<uint16_t> { static constexpr int IPT = 16; };      // tile ids of the binning stage's sort
 
 template <class K> __device__ __forceinline__ uint32_t digit_of(K key, int shift, uint32_t mask) {
 	return (uint32_t)(key >> shift) & mask;
@@ -130,23 +130,8 @@ __global__ void __launch_bounds__(RADIX) digit_base_kernel(SegPtrs<K> sp)
 }
 
 // ---- 3. one onesweep pass ---------------------------------------------------------------------------------------
-// EXPAND (first pass of the fused tile sort, K = uint16_t): the tile's (tile id, Gaussian id) pairs are not read from memory
-// but GENERATED here from the depth-ordered Gaussians' rects — duplicateWithKeys (rasterizer_impl.cu:59-100) fused into the
-// sort's first pass, so the pair list is written once (this pass's scatter) instead of written by a duplicate kernel, read by
-// a histogram pass and read again by the first sort pass.  Slot s of the emission list belongs to the last depth rank j with
-// exclusive offset <= s; the tile's first owner comes from the scan kernel's tile_start table, the others mark their first
-// slot in shared memory and a blocked max-scan spreads the owners over the slots.
-struct ExpandArgs {
-	const uint32_t* order;        // [P] Gaussian ids in depth order
-	const uint32_t* offsets;      // [P] inclusive prefix sum of tiles_touched in depth order
-	const uint2* rect;            // [P] by Gaussian id: x0 | x1 << 16, y0 | y1 << 16
-	const uint32_t* tile_start;   // [ceil(N / PAIR_TILE)] depth rank of the owner of slot b * PAIR_TILE
-	int P, grid_x;
-};
-
-template <class K, int IPT, bool MATCH_OR, bool EXPAND>
-__global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp, int pass, bool iota_vals, bool write_keys, uint32_t n, uint32_t ntiles, int shift, uint32_t mask,
-	ExpandArgs ex)
+template <class K, int IPT, bool MATCH_OR>
+__global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp, int pass, bool iota_vals, bool write_keys, uint32_t n, uint32_t ntiles, int shift, uint32_t mask)
 {
 	// this segment's buffers: even passes read the *_a buffers and write *_b, odd passes the other way round
 	const int seg = blockIdx.y;
@@ -166,7 +151,6 @@ __global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp
 	__shared__ uint32_t s_wtot[SORT_WARPS];
 	__shared__ __align__(16) K s_keys[TILE];          // also viewed as 32-bit words (match table)
 	__shared__ __align__(16) uint32_t s_vals[TILE];
-	__shared__ __align__(16) uint16_t s_head[EXPAND ? TILE : 8];      // EXPAND: rank (relative to the tile's first owner) of the Gaussian whose span starts at a slot, 0 = none
 
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 	const int nbits = __popc(mask);
@@ -174,83 +158,14 @@ __global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp
 	uint32_t* s_match = reinterpret_cast<uint32_t*>(s_keys) + warp * RADIX;
 	static_assert(sizeof(K) * TILE >= sizeof(uint32_t) * SORT_WARPS * RADIX, "s_match does not fit into s_keys");
 	if (tid == 0) s_tile = atomicAdd(ticket, 1u);
-	for (int i = tid; i < SORT_WARPS * RADIX; i += SORT_THREADS) { (&s_whist[0][0])[i] = 0; if (MATCH_OR && !EXPAND) reinterpret_cast<uint32_t*>(s_keys)[i] = 0; }
-	if (EXPAND) for (int i = tid; i < TILE / 2; i += SORT_THREADS) reinterpret_cast<uint32_t*>(s_head)[i] = 0;
+	for (int i = tid; i < SORT_WARPS * RADIX; i += SORT_THREADS) { (&s_whist[0][0])[i] = 0; if (MATCH_OR) reinterpret_cast<uint32_t*>(s_keys)[i] = 0; }
 	__syncthreads();
 	const uint32_t tile = s_tile;
 	const uint32_t tile_base = tile * (uint32_t)TILE;
 	const uint32_t tile_count = min((uint32_t)TILE, n - tile_base);
 
-	if (EXPAND) {
-		static_assert(!EXPAND || (TILE == (int)PAIR_TILE && sizeof(K) == 2), "the fused first pass works on PAIR_TILE slots with 16-bit tile ids");
-		// ---- generate the tile's pairs in slot order into s_keys (tile ids) / s_vals (Gaussian ids) ----
-		const uint32_t j0 = ex.tile_start[tile], end = tile_base + tile_count;
-		// every later Gaussian of the tile marks the slot its span starts at: ranks j0 + 1 .. the first owner of the next tile
-		// (each owns >= 1 slot, so at most tile_count of them); independent loads, no votes
-		const uint32_t jlast = (tile + 1 < ntiles) ? ex.tile_start[tile + 1] : min((uint32_t)ex.P - 1u, j0 + tile_count);
-		for (uint32_t lj = tid + 1; j0 + lj <= jlast; lj += SORT_THREADS) {
-			const uint32_t excl = ex.offsets[j0 + lj - 1];
-			if (excl < end) s_head[excl - tile_base] = (uint16_t)lj;       // excl >= inclusive offset of j0 > tile_base
-		}
-		__syncthreads();
-		// owner of each slot = the largest mark at or before it: blocked max-scan, thread t owns slots [16 t, 16 t + 16)
-		uint32_t own[IPT];
-		{
-			const uint4 h0 = reinterpret_cast<const uint4*>(s_head)[tid * 2], h1 = reinterpret_cast<const uint4*>(s_head)[tid * 2 + 1];
-			const uint32_t w[8] = { h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w };
-			uint32_t run = 0;
-			#pragma unroll
-			for (int k = 0; k < IPT; k++) { const uint32_t h = (w[k >> 1] >> ((k & 1) * 16)) & 0xffffu; run = max(run, h); own[k] = run; }
-			uint32_t inc = run;                                     // inclusive max over the threads of the warp
-			#pragma unroll
-			for (int o = 1; o < 32; o <<= 1) { const uint32_t u = __shfl_up_sync(FULL, inc, o); if (lane >= o) inc = max(inc, u); }
-			if (lane == 31) s_wtot[warp] = inc;
-			__syncthreads();
-			uint32_t carry = __shfl_up_sync(FULL, inc, 1);
-			if (lane == 0) carry = 0;
-			for (int w2 = 0; w2 < warp; w2++) carry = max(carry, s_wtot[w2]);
-			#pragma unroll
-			for (int k = 0; k < IPT; k++) own[k] = max(own[k], carry);
-			__syncthreads();                                        // s_wtot is reused below
-		}
-		// tile id of each slot: row-major walk of the owner's rect (rasterizer_impl.cu:87-98), continued incrementally while
-		// consecutive slots stay with the same owner.  The owners' ids / offsets / rects are fetched for 8 slots at a time with
-		// independent loads (two round trips per 8 slots, not two per change of owner; repeated owners hit L1).
-		uint32_t cur = 0xFFFFFFFFu, wdt = 1, rx = 0, ry = 0, xb = 0;
-		#pragma unroll
-		for (int h = 0; h < IPT; h += 8) {
-			uint32_t gg[8], ee[8];
-			uint2 rr[8];
-			#pragma unroll
-			for (int k = 0; k < 8; k++) {
-				const uint32_t sl = (uint32_t)tid * IPT + h + k, j = j0 + own[h + k];
-				const bool valid = sl < tile_count;
-				gg[k] = valid ? __ldg(ex.order + j) : 0u;
-				ee[k] = (valid && j) ? __ldg(ex.offsets + j - 1) : 0u;
-			}
-			#pragma unroll
-			for (int k = 0; k < 8; k++) rr[k] = __ldg(ex.rect + gg[k]);
-			#pragma unroll
-			for (int k = 0; k < 8; k++) {
-				const uint32_t sl = (uint32_t)tid * IPT + h + k;
-				if (sl < tile_count) {
-					if (own[h + k] != cur) {
-						cur = own[h + k];
-						const uint32_t x0 = rr[k].x & 0xffffu;
-						wdt = (rr[k].x >> 16) - x0;
-						const uint32_t local = tile_base + sl - ee[k];
-						ry = local / wdt; rx = local - ry * wdt;
-						xb = (rr[k].y & 0xffffu) * (uint32_t)ex.grid_x + x0;         // tile id of the rect's first tile
-					} else if (++rx == wdt) { rx = 0; ry++; }
-					s_keys[sl] = (K)(xb + ry * (uint32_t)ex.grid_x + rx);
-					s_vals[sl] = gg[k];                                 // the sort's value, as in the reference (rasterizer_impl.cu:92)
-				}
-			}
-		}
-		__syncthreads();
-	}
 	// the values are only fetched after the ranking (registers); pull their lines into L2 now (one 128-byte line per thread)
-	if (!EXPAND && vals_in) {
+	if (vals_in) {
 		const uint32_t line = (uint32_t)tid * 32u;
 		if (line < tile_count) asm volatile("prefetch.global.L2 [%0];" ::"l"(vals_in + tile_base + line));
 	}
@@ -260,12 +175,7 @@ __global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp
 	#pragma unroll
 	for (int k = 0; k < IPT; k++) {
 		const uint32_t li = warp * WARP_ITEMS + k * 32 + lane;
-		key[k] = (li < tile_count) ? (EXPAND ? s_keys[li] : keys_in[tile_base + li]) : (K)0;
-	}
-	if (EXPAND) {
-		// s_keys now becomes the match table of the ranking (and later the reorder buffer): every thread holds its keys
-		__syncthreads();
-		if (MATCH_OR) { for (int i = tid; i < SORT_WARPS * RADIX; i += SORT_THREADS) reinterpret_cast<uint32_t*>(s_keys)[i] = 0; __syncthreads(); }
+		key[k] = (li < tile_count) ? keys_in[tile_base + li] : (K)0;
 	}
 	// per-warp stable ranking
 	#pragma unroll
@@ -343,9 +253,8 @@ __global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp
 	for (int k = 0; k < IPT; k++) {
 		const uint32_t li = warp * WARP_ITEMS + k * 32 + lane;
 		val[k] = 0;
-		if (li < tile_count) val[k] = EXPAND ? s_vals[li] : (vals_in ? vals_in[tile_base + li] : tile_base + li);
+		if (li < tile_count) val[k] = vals_in ? vals_in[tile_base + li] : tile_base + li;
 	}
-	if (EXPAND) __syncthreads();       // s_vals turns from the generated ids (slot order) into the reorder buffer
 	// reorder through shared memory into tile-local sorted order
 	#pragma unroll
 	for (int k = 0; k < IPT; k++) {
@@ -450,44 +359,42 @@ int sort_pairs_segments(cudaStream_t stream, int nseg, K* const* keys_a, K* cons
 	count_launch(), histogram_kernel<K><<<dim3(hgrid < hcap ? hgrid : hcap, nseg), SORT_THREADS, 0, stream>>>(sp, (uint32_t)n, pd);
 	count_launch(), digit_base_kernel<K><<<dim3(pd.npass, nseg), RADIX, 0, stream>>>(sp);
 	for (int p = 0; p < pd.npass; p++) {
-		if (match_or) count_launch(), onesweep_kernel<K, IPT, true, false><<<dim3(ntiles, nseg), SORT_THREADS, 0, stream>>>(sp, p, iota_vals, true, (uint32_t)n, ntiles, pd.shift[p], pd.mask[p], ExpandArgs());
-		else count_launch(), onesweep_kernel<K, IPT, false, false><<<dim3(ntiles, nseg), SORT_THREADS, 0, stream>>>(sp, p, iota_vals, true, (uint32_t)n, ntiles, pd.shift[p], pd.mask[p], ExpandArgs());
+		if (match_or) count_launch(), onesweep_kernel<K, IPT, true><<<dim3(ntiles, nseg), SORT_THREADS, 0, stream>>>(sp, p, iota_vals, true, (uint32_t)n, ntiles, pd.shift[p], pd.mask[p]);
+		else count_launch(), onesweep_kernel<K, IPT, false><<<dim3(ntiles, nseg), SORT_THREADS, 0, stream>>>(sp, p, iota_vals, true, (uint32_t)n, ntiles, pd.shift[p], pd.mask[p]);
 	}
 	if (check_launch("sort_pairs", stream, false)) return -1;
 	return pd.npass & 1;   // odd number of passes -> result sits in the *_b buffers
 }
 
-// ---- the fused tile sort: tile plan (digit bases, ranges) + expansion fused into pass 0 + a value-only last pass ------------
+// ---- the tile sort of the binning stage: 16-bit tile ids, digit bases and ranges from the tile plan, value-only last pass ----
 size_t tile_sort_ws_bytes(size_t n, int bits) { return sort_ws_bytes<uint16_t>(n, 0, bits); }
 
-int tile_sort_fused(cudaStream_t stream, int P, size_t N, int bits, int grid_x, int grid_y, const uint32_t* order, const uint32_t* offsets, const uint2* rect,
-	const uint32_t* tiles_touched, const uint32_t* tile_start, uint16_t* keys_tmp, uint32_t* vals_a, uint32_t* vals_b, uint2* ranges, int* plan_ws, void* ws)
+int tile_sort16(cudaStream_t stream, int P, size_t N, int bits, int grid_x, int grid_y, const uint32_t* order, const uint32_t* offsets, const uint2* rect,
+	const uint32_t* tiles_touched, uint16_t* keys_a, uint16_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, uint2* ranges, int* plan_ws, void* ws)
 {
-	if (bits < 1 || bits > 16) { set_error("tile_sort_fused: %d tile-id bits (1..16)", bits); return -1; }
-	if (N >= (size_t)VALUE_MASK) { set_error("tile_sort_fused: N=%zu exceeds the 2^30-1 item limit", N); return -1; }
+	if (bits < 1 || bits > 16) { set_error("tile_sort16: %d tile-id bits (1..16)", bits); return -1; }
+	if (N >= (size_t)VALUE_MASK) { set_error("tile_sort16: N=%zu exceeds the 2^30-1 item limit", N); return -1; }
 	const PassDesc pd = make_passes(0, bits);                       // 1 or 2 passes
 	const WsLayout L = ws_layout<uint16_t>(ws, N, pd.npass);
 	cudaMemsetAsync(ws, 0, L.zero_bytes, stream);
-	// ranges and the exclusive digit bases of both passes straight from the rects (binning.cu)
+	// ranges and the exclusive digit bases of both passes straight from the rects (binning.cu): no histogram pass over the pairs,
+	// no sorted key array, no range-detection pass
 	if (launch_tile_plan(stream, P, grid_x, grid_y, tiles_touched, rect, plan_ws, ranges, L.ghist, pd.npass, pd.shift, pd.mask)) return -1;
 	if (N == 0) return pd.npass & 1;
+	// duplicateWithKeys (rasterizer_impl.cu:59-100) in depth order with 2-byte tile ids: 6 bytes per pair instead of 12
+	if (launch_duplicate16(stream, P, order, offsets, rect, grid_x, keys_a, vals_a)) return -1;
 	SegPtrs<uint16_t> sp;
 	memset(&sp, 0, sizeof(sp));
-	// pass 0 generates its input and writes (keys_tmp, vals_b); pass 1 reads them and writes vals_a only
-	sp.keys_a[0] = keys_tmp; sp.keys_b[0] = keys_tmp; sp.vals_a[0] = vals_a; sp.vals_b[0] = vals_b;
+	sp.keys_a[0] = keys_a; sp.keys_b[0] = keys_b; sp.vals_a[0] = vals_a; sp.vals_b[0] = vals_b;
 	sp.ghist[0] = L.ghist; sp.tickets[0] = L.tickets; sp.status[0] = L.status;
-	ExpandArgs ex;
-	ex.order = order; ex.offsets = offsets; ex.rect = rect; ex.tile_start = tile_start; ex.P = P; ex.grid_x = grid_x;
 	constexpr int IPT = Cfg<uint16_t>::IPT;
 	const bool match_or = N >= (1u << 22);
-	const bool last0 = pd.npass == 1;
-	if (match_or) count_launch(), onesweep_kernel<uint16_t, IPT, true, true><<<dim3(L.ntiles, 1), SORT_THREADS, 0, stream>>>(sp, 0, false, !last0, (uint32_t)N, L.ntiles, pd.shift[0], pd.mask[0], ex);
-	else count_launch(), onesweep_kernel<uint16_t, IPT, false, true><<<dim3(L.ntiles, 1), SORT_THREADS, 0, stream>>>(sp, 0, false, !last0, (uint32_t)N, L.ntiles, pd.shift[0], pd.mask[0], ex);
-	if (pd.npass > 1) {
-		if (match_or) count_launch(), onesweep_kernel<uint16_t, IPT, true, false><<<dim3(L.ntiles, 1), SORT_THREADS, 0, stream>>>(sp, 1, false, false, (uint32_t)N, L.ntiles, pd.shift[1], pd.mask[1], ExpandArgs());
-		else count_launch(), onesweep_kernel<uint16_t, IPT, false, false><<<dim3(L.ntiles, 1), SORT_THREADS, 0, stream>>>(sp, 1, false, false, (uint32_t)N, L.ntiles, pd.shift[1], pd.mask[1], ExpandArgs());
+	for (int p = 0; p < pd.npass; p++) {
+		const bool wk = p + 1 < pd.npass;                             // the last pass writes the Gaussian ids (point_list) only
+		if (match_or) count_launch(), onesweep_kernel<uint16_t, IPT, true><<<dim3(L.ntiles, 1), SORT_THREADS, 0, stream>>>(sp, p, false, wk, (uint32_t)N, L.ntiles, pd.shift[p], pd.mask[p]);
+		else count_launch(), onesweep_kernel<uint16_t, IPT, false><<<dim3(L.ntiles, 1), SORT_THREADS, 0, stream>>>(sp, p, false, wk, (uint32_t)N, L.ntiles, pd.shift[p], pd.mask[p]);
 	}
-	if (check_launch("tile_sort_fused", stream, false)) return -1;
+	if (check_launch("tile_sort16", stream, false)) return -1;
 	return pd.npass & 1;   // 1: the sorted ids are in vals_b, 0: in vals_a
 }
 
