@@ -59,13 +59,15 @@ size_t rr_backward_ws_bytes(int P);
 /* Forward, first half — replaces FORWARD::preprocess + cub InclusiveSum + the blocking cudaMemcpy of num_rendered
  * (Rasterizer::forward, rasterizer_impl.cu:187-273).  Writes radii[P] and the geometry blob, and enqueues an async
  * copy of num_rendered into *num_rendered_host (pinned host memory); the caller synchronises the stream before
- * reading it and sizing the binning blob. */
+ * reading it and sizing the binning blob.  The image blob (rr_image_bytes) already receives the tile ranges here: the "tile
+ * plan" derives them, and the digit bases of the later tile sort, from the tile rects alone (replacing identifyTileRanges and
+ * the sort's histogram pass, rasterizer_impl.cu:302-318). */
 int rr_forward_geom(void* stream, int P, int D, int M, int W, int H,
 	const float* means3D, const float* shs, const float* colors_precomp, const float* opacities,
 	const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
 	const float* viewmatrix, const float* projmatrix, const float* campos,
 	float tan_fovx, float tan_fovy, float low_pass, int prefiltered, int debug,
-	int* radii, void* geom, size_t geom_bytes, int64_t* num_rendered_host);
+	int* radii, void* geom, size_t geom_bytes, void* image, size_t image_bytes, int64_t* num_rendered_host);
 
 /* rr_forward_geom for ALL nviews views of a step in one set of launches (no reference counterpart: the reference runs its
  * preprocess, scan and sort once per view): one pass over the Gaussians that reads the parameters once and projects them
@@ -81,7 +83,7 @@ int rr_forward_geom(void* stream, int P, int D, int M, int W, int H,
 int rr_forward_geom_views(void* stream, int P, int D, int M, int W, int H, int nviews,
 	const float* const* viewmatrix, const float* const* projmatrix, const float* const* campos, const float* tan_fovx, const float* tan_fovy,
 	const float* means3D, const float* shs, const float* f_rest, const float* opacities, const float* scales, float scale_modifier, const float* rotations, float low_pass,
-	int* const* radii, void* const* geom, size_t geom_bytes, int64_t* const* num_rendered_host, int flags, int debug);
+	int* const* radii, void* const* geom, size_t geom_bytes, void* const* image, size_t image_bytes, int64_t* const* num_rendered_host, int flags, int debug);
 
 /* Forward, second half — replaces duplicateWithKeys + cub SortPairs + identifyTileRanges + FORWARD::render
  * (rasterizer_impl.cu:275-328).  out_color[3,H,W], out_depth[1,H,W]. */

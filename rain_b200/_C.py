@@ -91,7 +91,7 @@ def forward_geom(background, means3D, colors, opacity, scales, rotations, scale_
                                        _ptr(scales_c), float(scale_modifier), _ptr(rots), _ptr(cov_c),
                                        _ptr(view), _ptr(proj), _ptr(cam),
                                        float(tan_fovx), float(tan_fovy), float(low_pass), int(bool(prefiltered)), int(bool(debug)),
-                                       st.radii.data_ptr(), st.geom.data_ptr(), st.geom.numel(), st.nr.data_ptr()), "rr_forward_geom")
+                                       st.radii.data_ptr(), st.geom.data_ptr(), st.geom.numel(), st.img.data_ptr(), st.img.numel(), st.nr.data_ptr()), "rr_forward_geom")
         st.event = torch.cuda.Event()
         st.event.record(st.stream)
     return st
@@ -160,7 +160,7 @@ def forward_geom_views(background, means3D, opacity, scales, rotations, scale_mo
             (ctypes.c_float * n)(*[float(c.tanfovx) for c in cams]), (ctypes.c_float * n)(*[float(c.tanfovy) for c in cams]),
             means3D_c.data_ptr(), sh_c.data_ptr(), frest_c.data_ptr() if leaf else None, opac.data_ptr(), scales_c.data_ptr(), float(scale_modifier), rots.data_ptr(), float(low_pass),
             arr([st.radii.data_ptr() for st in states]), arr([st.geom.data_ptr() for st in states]), gbytes,
-            arr([st.nr.data_ptr() for st in states]), (1 if keep_cov3D else 0) | (2 if leaf else 0), int(bool(debug))), "rr_forward_geom_views")
+            arr([st.img.data_ptr() for st in states]), states[0].img.numel(), arr([st.nr.data_ptr() for st in states]), (1 if keep_cov3D else 0) | (2 if leaf else 0), int(bool(debug))), "rr_forward_geom_views")
         ev = torch.cuda.Event()
         ev.record(s)
     for st in states:

@@ -30,11 +30,11 @@ SIGNATURES = {
                              _vp, _f, _vp, _vp,
                              _vp, _vp, _vp,
                              _f, _f, _f, _i, _i,
-                             _vp, _vp, _sz, _vp]),
+                             _vp, _vp, _sz, _vp, _sz, _vp]),
     "rr_forward_geom_views": (_i, [_vp, _i, _i, _i, _i, _i, _i,
                                    _vp, _vp, _vp, _vp, _vp,
                                    _vp, _vp, _vp, _vp, _vp, _f, _vp, _f,
-                                   _vp, _vp, _sz, _vp, _i, _i]),
+                                   _vp, _vp, _sz, _vp, _sz, _vp, _i, _i]),
     "rr_forward_raster": (_i, [_vp, _i, _i, _i, _i64, _vp,
                                _vp, _sz, _vp, _sz, _vp, _sz,
                                _vp, _vp, _i]),

@@ -51,9 +51,9 @@ static unsigned long long* xc_counters_dev() {
 namespace {
 
 // ---- per-stage device timing (CUDA events on the caller's stream), off by default; used by bench.py -----------------
-enum StageId { ST_PREPROCESS = 0, ST_DEPTH_SORT, ST_SCAN, ST_DUPLICATE, ST_TILE_SORT, ST_RANGES, ST_RENDER_FWD,
+enum StageId { ST_PREPROCESS = 0, ST_TILE_PLAN, ST_DEPTH_SORT, ST_SCAN, ST_DUPLICATE, ST_TILE_SORT, ST_RANGES, ST_RENDER_FWD,
 	ST_RENDER_BWD, ST_PREPROCESS_BWD, ST_BACKWARD_VIEWS, ST_DIST2, ST_COUNT };
-const char* const kStageNames[ST_COUNT] = { "preprocess_fwd", "depth_sort", "scan", "duplicate", "tile_sort", "ranges",
+const char* const kStageNames[ST_COUNT] = { "preprocess_fwd", "tile_plan", "depth_sort", "scan", "duplicate", "tile_sort", "ranges",
 	"render_fwd", "render_bwd", "preprocess_bwd", "backward_views", "dist2" };
 struct Pending { int stage; cudaEvent_t a, b; };
 struct Prof {
@@ -158,7 +158,7 @@ BinLayout bin_layout(void* blob, int64_t N, int W, int H)
 	return L;
 }
 
-struct ImgLayout { float* final_T; uint32_t* n_contrib; uint2* ranges; uint32_t* tile_max; int* plan_ws; size_t total; int64_t off[4]; };
+struct ImgLayout { float* final_T; uint32_t* n_contrib; uint2* ranges; uint32_t* tile_max; int* plan_ws; uint32_t* plan_bases; size_t total; int64_t off[4]; };
 ImgLayout img_layout(void* blob, int W, int H)
 {
 	ImgLayout L; Carver c(blob);
@@ -171,11 +171,20 @@ ImgLayout img_layout(void* blob, int W, int H)
 	{	// difference grid of the tile plan (binning.cu)
 		const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
 		L.plan_ws = tile_plan_supported(gx, gy) ? c.take<int>(tile_plan_ws_bytes(gx, gy) / sizeof(int)) : nullptr;
+		L.plan_bases = c.take<uint32_t>(2 * 256);            // exclusive digit bases of the tile sort's passes
 	}
 	L.total = c.used();
 	char* b = reinterpret_cast<char*>(blob);
 	L.off[0] = (char*)L.final_T - b; L.off[1] = (char*)L.n_contrib - b; L.off[2] = (char*)L.ranges - b; L.off[3] = (char*)L.tile_max - b;
 	return L;
+}
+
+// the tile plan (ranges + digit bases from the rects, run in the geometry half) covers everything but the opt-in tile culling
+// and grids beyond its shared-memory budget / 16-bit tile ids
+bool plan_in_use(const GeomLayout& G, const ImgLayout& I, int W, int H)
+{
+	const int tiles = ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+	return I.plan_ws && !G.tile_mask && tile_bits(tiles) <= 16;
 }
 
 bool bad_ptr(const void* p, const char* name) { if (!p) { set_error("%s must not be null", name); return true; } return false; }
@@ -224,7 +233,7 @@ int rr_forward_geom(void* stream_, int P, int D, int M, int W, int H,
 	const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
 	const float* viewmatrix, const float* projmatrix, const float* campos,
 	float tan_fovx, float tan_fovy, float low_pass, int prefiltered, int debug,
-	int* radii, void* geom, size_t geom_bytes, int64_t* num_rendered_host)
+	int* radii, void* geom, size_t geom_bytes, void* image, size_t image_bytes, int64_t* num_rendered_host)
 {
 	(void)prefiltered;   // the reference only uses it to trap on an inconsistent caller (auxiliary.h:145-149)
 	cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
@@ -239,6 +248,9 @@ int rr_forward_geom(void* stream_, int P, int D, int M, int W, int H,
 	if (shs && !colors_precomp && (D < 0 || D > 3 || (D + 1) * (D + 1) > M)) { set_error("SH degree %d needs %d coefficients, M=%d", D, (D + 1) * (D + 1), M); return -1; }
 	const GeomLayout L = geom_layout(geom, P);
 	if (L.total > geom_bytes) { set_error("geometry blob too small: %zu < %zu", geom_bytes, L.total); return -1; }
+	if (bad_ptr(image, "image")) return -1;
+	const ImgLayout I = img_layout(image, W, H);
+	if (I.total > image_bytes) { set_error("image blob too small: %zu < %zu", image_bytes, I.total); return -1; }
 
 	PreprocessArgs a;
 	a.P = P; a.D = D; a.M = M; a.W = W; a.H = H;
@@ -252,6 +264,15 @@ int rr_forward_geom(void* stream_, int P, int D, int M, int W, int H,
 	a.tile_mask = L.tile_mask; a.tile_cull = L.tile_mask != nullptr;
 	{ Stage st(stream, ST_PREPROCESS); if (launch_preprocess_fwd(stream, a)) return -1; }
 	if (debug && check_launch("preprocess_fwd", stream, true)) return -1;
+	if (plan_in_use(L, I, W, H)) {
+		// tile plan: ranges and the tile sort's digit bases from the rects (needs nothing but the preprocess outputs)
+		Stage st(stream, ST_TILE_PLAN);
+		PlanSegs ps; memset(&ps, 0, sizeof(ps));
+		ps.tiles_touched[0] = L.tiles_touched; ps.rect[0] = L.rect; ps.gdiff[0] = I.plan_ws; ps.ranges[0] = I.ranges; ps.ghist[0] = I.plan_bases;
+		int shift[2] = { 0, 0 }; uint32_t mask[2] = { 0, 0 };
+		const int npass = tile_sort_passes(tile_bits(a.grid_x * a.grid_y), shift, mask);
+		if (launch_tile_plan(stream, P, a.grid_x, a.grid_y, 1, ps, npass, shift, mask)) return -1;
+	}
 	// depth order of the Gaussians: 32-bit keys, 4 passes, result in the *_a buffers
 	int which;
 	{ Stage st(stream, ST_DEPTH_SORT); which = sort_pairs<uint32_t>(stream, L.key_a, L.key_b, L.val_a, L.val_b, (size_t)P, 0, 32, L.sort_ws, true); }
@@ -275,7 +296,7 @@ int rr_forward_geom(void* stream_, int P, int D, int M, int W, int H,
 int rr_forward_geom_views(void* stream_, int P, int D, int M, int W, int H, int nviews,
 	const float* const* viewmatrix, const float* const* projmatrix, const float* const* campos, const float* tan_fovx, const float* tan_fovy,
 	const float* means3D, const float* shs, const float* f_rest, const float* opacities, const float* scales, float scale_modifier, const float* rotations, float low_pass,
-	int* const* radii, void* const* geom, size_t geom_bytes, int64_t* const* num_rendered_host, int flags, int debug)
+	int* const* radii, void* const* geom, size_t geom_bytes, void* const* image, size_t image_bytes, int64_t* const* num_rendered_host, int flags, int debug)
 {
 	cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
 	if (nviews == 0) return 0;
@@ -288,7 +309,8 @@ int rr_forward_geom_views(void* stream_, int P, int D, int M, int W, int H, int 
 	if (tile_cull_wanted()) { set_error("rr_forward_geom_views does not support RAIN_TILE_CULL=1 (use rr_forward_geom per view)"); return -1; }
 	if (bad_ptr(viewmatrix, "viewmatrix") || bad_ptr(projmatrix, "projmatrix") || bad_ptr(campos, "campos") || bad_ptr(tan_fovx, "tan_fovx") || bad_ptr(tan_fovy, "tan_fovy") ||
 		bad_ptr(means3D, "means3D") || bad_ptr(shs, "shs") || bad_ptr(opacities, "opacities") || bad_ptr(scales, "scales") || bad_ptr(rotations, "rotations") ||
-		bad_ptr(radii, "radii") || bad_ptr(geom, "geom")) return -1;
+		bad_ptr(radii, "radii") || bad_ptr(geom, "geom") || bad_ptr(image, "image")) return -1;
+	if (img_layout(nullptr, W, H).total > image_bytes) { set_error("image blob too small"); return -1; }
 	const bool leaf = (flags & RR_GEOM_LEAF) != 0;
 	if (leaf && bad_ptr(f_rest, "f_rest")) return -1;
 	const GeomLayout L0 = geom_layout(nullptr, P);
@@ -305,6 +327,8 @@ int rr_forward_geom_views(void* stream_, int P, int D, int M, int W, int H, int 
 	uint32_t *ka[PV_MAX_VIEWS], *kb[PV_MAX_VIEWS], *va[PV_MAX_VIEWS], *vb[PV_MAX_VIEWS];
 	void* sws[PV_MAX_VIEWS];
 	ScanSegs sg; memset(&sg, 0, sizeof(sg));
+	PlanSegs ps; memset(&ps, 0, sizeof(ps));
+	bool use_plan = true;
 	for (int v = 0; v < nviews; v++) {
 		if (bad_ptr(viewmatrix[v], "viewmatrix[v]") || bad_ptr(projmatrix[v], "projmatrix[v]") || bad_ptr(campos[v], "campos[v]") || bad_ptr(radii[v], "radii[v]") ||
 			bad_ptr(geom[v], "geom[v]")) return -1;
@@ -312,6 +336,10 @@ int rr_forward_geom_views(void* stream_, int P, int D, int M, int W, int H, int 
 		a.radii[v] = radii[v]; a.geom[v] = reinterpret_cast<char*>(geom[v]);
 		const GeomLayout L = geom_layout(geom[v], P);
 		ka[v] = L.key_a; kb[v] = L.key_b; va[v] = L.val_a; vb[v] = L.val_b; sws[v] = L.sort_ws;
+		if (bad_ptr(image[v], "image[v]")) return -1;
+		const ImgLayout I = img_layout(image[v], W, H);
+		use_plan = use_plan && plan_in_use(L, I, W, H);
+		ps.tiles_touched[v] = L.tiles_touched; ps.rect[v] = L.rect; ps.gdiff[v] = I.plan_ws; ps.ranges[v] = I.ranges; ps.ghist[v] = I.plan_bases;
 		uint32_t* mapped = nullptr;
 		cudaPointerAttributes pa;
 		if (cudaPointerGetAttributes(&pa, num_rendered_host[v]) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer) mapped = reinterpret_cast<uint32_t*>(pa.devicePointer);
@@ -320,6 +348,12 @@ int rr_forward_geom_views(void* stream_, int P, int D, int M, int W, int H, int 
 	}
 	{ Stage st(stream, ST_PREPROCESS); if (launch_preprocess_views(stream, a)) return -1; }
 	if (debug && check_launch("preprocess_views", stream, true)) return -1;
+	if (use_plan) {
+		Stage st(stream, ST_TILE_PLAN);
+		int shift[2] = { 0, 0 }; uint32_t mask[2] = { 0, 0 };
+		const int npass = tile_sort_passes(tile_bits(a.grid_x * a.grid_y), shift, mask);
+		if (launch_tile_plan(stream, P, a.grid_x, a.grid_y, nviews, ps, npass, shift, mask)) return -1;
+	}
 	int which;
 	{ Stage st(stream, ST_DEPTH_SORT); which = sort_pairs_segments<uint32_t>(stream, nviews, ka, kb, va, vb, (size_t)P, 0, 32, sws, true); }
 	if (which != 0) { if (which > 0) set_error("internal: depth sort landed in the wrong buffer"); return -1; }
@@ -343,13 +377,13 @@ int rr_forward_bin(void* stream_, int P, int W, int H, int64_t N,
 	if (G.total > geom_bytes || B.total > binning_bytes || I.total > image_bytes) { set_error("scratch blob too small"); return -1; }
 	const int grid_x = (W + TILE_X - 1) / TILE_X, grid_y = (H + TILE_Y - 1) / TILE_Y;
 
-	// Default: 16-bit tile ids, ranges and digit bases from the tile plan, value-only last pass (radix_sort.cu::tile_sort16).  The
+	// Default: 16-bit tile ids, digit bases (and ranges) from the geometry half's tile plan, value-only last pass (tile_sort16).  The
 	// 32-bit-key kernels below remain for what it does not cover: the opt-in tile culling (per-Gaussian tile masks) and grids
 	// beyond the tile plan's shared-memory budget.
-	if (I.plan_ws && !G.tile_mask && B.bits <= 16) {
+	if (plan_in_use(G, I, W, H)) {
 		Stage st(stream, ST_TILE_SORT);
-		const int which = tile_sort16(stream, P, (size_t)N, B.bits, grid_x, grid_y, G.val_a, G.offsets, G.rect, G.tiles_touched,
-			reinterpret_cast<uint16_t*>(B.key_a), reinterpret_cast<uint16_t*>(B.key_b), B.val_a, B.val_b, I.ranges, I.plan_ws, B.sort_ws);
+		const int which = tile_sort16(stream, P, (size_t)N, B.bits, grid_x, G.val_a, G.offsets, G.rect, I.plan_bases,
+			reinterpret_cast<uint16_t*>(B.key_a), reinterpret_cast<uint16_t*>(B.key_b), B.val_a, B.val_b, B.sort_ws);
 		if (which < 0) return -1;
 		if ((which ? B.val_b : B.val_a) != B.point_list) { set_error("internal: tile sort landed in the wrong buffer"); return -1; }
 		return check_launch("forward_bin", stream, debug != 0);

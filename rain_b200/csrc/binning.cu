@@ -209,9 +209,12 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(uint32_t N, const uint
 constexpr int PLAN_MAX_CELLS = 11264;       // (grid_x + 1) * (grid_y + 1) ints in shared memory (44 KB); 1920x1080 needs 8 349
 
 constexpr int DIFF_THREADS = 512;
-__global__ void __launch_bounds__(DIFF_THREADS) tile_diff_kernel(int P, int cells, int gx1, const uint32_t* __restrict__ tiles_touched, const uint2* __restrict__ rect,
-	int* __restrict__ gdiff /*[cells], zero on entry*/)
+// blockIdx.y = view: the plans of all views of a batched geometry pass run as one pair of launches (PlanSegs, kernels.cuh)
+__global__ void __launch_bounds__(DIFF_THREADS) tile_diff_kernel(int P, int cells, int gx1, PlanSegs sg)
 {
+	const uint32_t* __restrict__ tiles_touched = sg.tiles_touched[blockIdx.y];
+	const uint2* __restrict__ rect = sg.rect[blockIdx.y];
+	int* __restrict__ gdiff = sg.gdiff[blockIdx.y];          // [cells], zero on entry
 	__shared__ int s_d[PLAN_MAX_CELLS];
 	for (int i = threadIdx.x; i < cells; i += DIFF_THREADS) s_d[i] = 0;
 	__syncthreads();
@@ -237,9 +240,11 @@ __global__ void __launch_bounds__(DIFF_THREADS) tile_diff_kernel(int P, int cell
 }
 
 constexpr int PLAN_THREADS = 1024;
-__global__ void __launch_bounds__(PLAN_THREADS) tile_plan_kernel(int grid_x, int grid_y, const int* __restrict__ gdiff, uint2* __restrict__ ranges,
-	uint32_t* __restrict__ ghist /*[npass][256] exclusive digit bases out*/, int npass, int shift0, uint32_t mask0, int shift1, uint32_t mask1)
+__global__ void __launch_bounds__(PLAN_THREADS) tile_plan_kernel(int grid_x, int grid_y, PlanSegs sg, int npass, int shift0, uint32_t mask0, int shift1, uint32_t mask1)
 {
+	const int* __restrict__ gdiff = sg.gdiff[blockIdx.x];
+	uint2* __restrict__ ranges = sg.ranges[blockIdx.x];
+	uint32_t* __restrict__ ghist = sg.ghist[blockIdx.x];     // [npass][256] exclusive digit bases out
 	__shared__ int s_c[PLAN_MAX_CELLS];
 	__shared__ uint32_t s_h[2][256];
 	__shared__ uint32_t s_wsum[PLAN_THREADS / 32];
@@ -362,14 +367,14 @@ int launch_tile_ranges(cudaStream_t stream, size_t N, const uint32_t* keys, uint
 bool tile_plan_supported(int grid_x, int grid_y) { return (grid_x + 1) * (grid_y + 1) <= PLAN_MAX_CELLS && grid_x < 65535 && grid_y < 65535; }
 size_t tile_plan_ws_bytes(int grid_x, int grid_y) { return sizeof(int) * (size_t)(grid_x + 1) * (grid_y + 1); }
 
-int launch_tile_plan(cudaStream_t stream, int P, int grid_x, int grid_y, const uint32_t* tiles_touched, const uint2* rect, int* gdiff, uint2* ranges,
-	uint32_t* ghist, int npass, const int* shift, const uint32_t* mask)
+int launch_tile_plan(cudaStream_t stream, int P, int grid_x, int grid_y, int nseg, const PlanSegs& sg, int npass, const int* shift, const uint32_t* mask)
 {
+	if (nseg == 0) return 0;
 	const int cells = (grid_x + 1) * (grid_y + 1);
-	cudaMemsetAsync(gdiff, 0, sizeof(int) * (size_t)cells, stream);
-	const int ctas = min((P + DIFF_THREADS * 4 - 1) / (DIFF_THREADS * 4), 148);
-	count_launch(), tile_diff_kernel<<<ctas, DIFF_THREADS, 0, stream>>>(P, cells, grid_x + 1, tiles_touched, rect, gdiff);
-	count_launch(), tile_plan_kernel<<<1, PLAN_THREADS, 0, stream>>>(grid_x, grid_y, gdiff, ranges, ghist, npass, shift[0], mask[0], npass > 1 ? shift[1] : 0, npass > 1 ? mask[1] : 0u);
+	for (int g = 0; g < nseg; g++) cudaMemsetAsync(sg.gdiff[g], 0, sizeof(int) * (size_t)cells, stream);
+	const int ctas = max(1, min((P + DIFF_THREADS * 4 - 1) / (DIFF_THREADS * 4), 148));
+	count_launch(), tile_diff_kernel<<<dim3(ctas, nseg), DIFF_THREADS, 0, stream>>>(P, cells, grid_x + 1, sg);
+	count_launch(), tile_plan_kernel<<<nseg, PLAN_THREADS, 0, stream>>>(grid_x, grid_y, sg, npass, shift[0], mask[0], npass > 1 ? shift[1] : 0, npass > 1 ? mask[1] : 0u);
 	return check_launch("tile_plan", stream, false);
 }
 

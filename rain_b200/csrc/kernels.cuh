@@ -47,11 +47,11 @@ struct ScanSegs {
 int launch_scan_tiles_segments(cudaStream_t, int P, int nseg, const ScanSegs&);
 int launch_duplicate(cudaStream_t, int P, const uint32_t* order, const uint32_t* offsets, const uint2* rect, const unsigned long long* tile_mask /*or null*/, int grid_x,
 	uint32_t* tile_keys /*[N] emission order*/, uint32_t* gaussian_ids /*[N] emission order*/);
-// tile plan (binning.cu): ranges and the tile sort's digit bases from the rects alone
+// tile plan (binning.cu): ranges and the tile sort's digit bases from the rects alone, for up to 16 views per launch pair
 bool tile_plan_supported(int grid_x, int grid_y);
 size_t tile_plan_ws_bytes(int grid_x, int grid_y);
-int launch_tile_plan(cudaStream_t, int P, int grid_x, int grid_y, const uint32_t* tiles_touched, const uint2* rect, int* gdiff /*tile_plan_ws_bytes scratch*/,
-	uint2* ranges, uint32_t* ghist /*[npass][256] out*/, int npass, const int* shift, const uint32_t* mask);
+struct PlanSegs { const uint32_t* tiles_touched[16]; const uint2* rect[16]; int* gdiff[16] /*tile_plan_ws_bytes scratch*/; uint2* ranges[16]; uint32_t* ghist[16] /*[2][256] out*/; };
+int launch_tile_plan(cudaStream_t, int P, int grid_x, int grid_y, int nseg, const PlanSegs&, int npass, const int* shift, const uint32_t* mask);
 int launch_duplicate16(cudaStream_t, int P, const uint32_t* order, const uint32_t* offsets, const uint2* rect, int grid_x, uint16_t* tile_keys, uint32_t* gaussian_ids);
 int launch_tile_ranges(cudaStream_t, size_t N, const uint32_t* sorted_tile_keys, uint2* ranges, int num_tiles);
 int launch_export_keys(cudaStream_t, int T, const uint2* ranges, const uint32_t* point_list, const uint32_t* rec_words, uint64_t* out);

@@ -369,24 +369,30 @@ int sort_pairs_segments(cudaStream_t stream, int nseg, K* const* keys_a, K* cons
 // ---- the tile sort of the binning stage: 16-bit tile ids, digit bases and ranges from the tile plan, value-only last pass ----
 size_t tile_sort_ws_bytes(size_t n, int bits) { return sort_ws_bytes<uint16_t>(n, 0, bits); }
 
-int tile_sort16(cudaStream_t stream, int P, size_t N, int bits, int grid_x, int grid_y, const uint32_t* order, const uint32_t* offsets, const uint2* rect,
-	const uint32_t* tiles_touched, uint16_t* keys_a, uint16_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, uint2* ranges, int* plan_ws, void* ws)
+int tile_sort_passes(int bits, int* shift, uint32_t* mask)
+{
+	const PassDesc pd = make_passes(0, bits);
+	for (int p = 0; p < pd.npass && p < 2; p++) { shift[p] = pd.shift[p]; mask[p] = pd.mask[p]; }
+	return pd.npass;
+}
+
+int tile_sort16(cudaStream_t stream, int P, size_t N, int bits, int grid_x, const uint32_t* order, const uint32_t* offsets, const uint2* rect,
+	const uint32_t* digit_bases, uint16_t* keys_a, uint16_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, void* ws)
 {
 	if (bits < 1 || bits > 16) { set_error("tile_sort16: %d tile-id bits (1..16)", bits); return -1; }
 	if (N >= (size_t)VALUE_MASK) { set_error("tile_sort16: N=%zu exceeds the 2^30-1 item limit", N); return -1; }
 	const PassDesc pd = make_passes(0, bits);                       // 1 or 2 passes
 	const WsLayout L = ws_layout<uint16_t>(ws, N, pd.npass);
 	cudaMemsetAsync(ws, 0, L.zero_bytes, stream);
-	// ranges and the exclusive digit bases of both passes straight from the rects (binning.cu): no histogram pass over the pairs,
-	// no sorted key array, no range-detection pass
-	if (launch_tile_plan(stream, P, grid_x, grid_y, tiles_touched, rect, plan_ws, ranges, L.ghist, pd.npass, pd.shift, pd.mask)) return -1;
+	// the exclusive digit bases of both passes (and the ranges) come from the tile plan of the geometry half (binning.cu): no
+	// histogram pass over the pairs, no sorted key array, no range-detection pass
 	if (N == 0) return pd.npass & 1;
 	// duplicateWithKeys (rasterizer_impl.cu:59-100) in depth order with 2-byte tile ids: 6 bytes per pair instead of 12
 	if (launch_duplicate16(stream, P, order, offsets, rect, grid_x, keys_a, vals_a)) return -1;
 	SegPtrs<uint16_t> sp;
 	memset(&sp, 0, sizeof(sp));
 	sp.keys_a[0] = keys_a; sp.keys_b[0] = keys_b; sp.vals_a[0] = vals_a; sp.vals_b[0] = vals_b;
-	sp.ghist[0] = L.ghist; sp.tickets[0] = L.tickets; sp.status[0] = L.status;
+	sp.ghist[0] = const_cast<uint32_t*>(digit_bases); sp.tickets[0] = L.tickets; sp.status[0] = L.status;
 	constexpr int IPT = Cfg<uint16_t>::IPT;
 	const bool match_or = N >= (1u << 22);
 	for (int p = 0; p < pd.npass; p++) {

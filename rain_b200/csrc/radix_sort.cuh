@@ -22,13 +22,14 @@ template <class K>
 int sort_pairs_segments(cudaStream_t stream, int nseg, K* const* keys_a, K* const* keys_b, uint32_t* const* vals_a, uint32_t* const* vals_b, size_t n,
 	int begin_bit, int end_bit, void* const* ws, bool iota_vals);
 
-// The whole tile binning after the prefix sum (replaces duplicateWithKeys + SortPairs + identifyTileRanges,
-// rasterizer_impl.cu:275-318): ranges and the sort's digit bases from the rects (tile plan, binning.cu), pair emission with
-// 16-bit tile ids, two 16-bit-key radix passes of which the last writes the Gaussian ids only.  keys_a / keys_b: N uint16 each;
-// vals_a / vals_b: N uint32 each; returns 1 if the sorted ids (point_list) are in vals_b, 0 if in vals_a, -1 on error.  Needs
-// tile_plan_supported(grid_x, grid_y) and bits <= 16.
+// The tile binning after the prefix sum (replaces duplicateWithKeys + SortPairs, rasterizer_impl.cu:275-300): pair emission with
+// 16-bit tile ids and two 16-bit-key radix passes of which the last writes the Gaussian ids only.  digit_bases [npass][256] are
+// the exclusive digit bases the tile plan of the geometry half computed from the rects (binning.cu; it also wrote the ranges,
+// so there is no identifyTileRanges pass).  keys_a / keys_b: N uint16 each; vals_a / vals_b: N uint32 each; returns 1 if the
+// sorted ids (point_list) are in vals_b, 0 if in vals_a, -1 on error.  bits <= 16.
 size_t tile_sort_ws_bytes(size_t n, int bits);
-int tile_sort16(cudaStream_t stream, int P, size_t N, int bits, int grid_x, int grid_y, const uint32_t* order, const uint32_t* offsets, const uint2* rect,
-	const uint32_t* tiles_touched, uint16_t* keys_a, uint16_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, uint2* ranges, int* plan_ws, void* ws);
+int tile_sort_passes(int bits, int* shift /*[2]*/, uint32_t* mask /*[2]*/);      // the sort's digit split: returns the number of passes (1 or 2)
+int tile_sort16(cudaStream_t stream, int P, size_t N, int bits, int grid_x, const uint32_t* order, const uint32_t* offsets, const uint2* rect,
+	const uint32_t* digit_bases, uint16_t* keys_a, uint16_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, void* ws);
 
 }  // namespace rr

@@ -86,15 +86,15 @@ def test_argument_validation_happens_before_any_cuda_call(lib):
     nr = ctypes.c_int64(77)
     # P == 0 short-circuit (rasterize_points.cu:72)
     assert lib.rr_forward_geom(None, 0, 0, 0, 16, 16, None, None, None, None, None, 1.0, None, None, None, None, None,
-                               1.0, 1.0, 0.3, 0, 0, None, None, 0, ctypes.byref(nr)) == 0
+                               1.0, 1.0, 0.3, 0, 0, None, None, 0, None, 0, ctypes.byref(nr)) == 0
     assert nr.value == 0
     # bad sizes
     assert lib.rr_forward_geom(None, 5, 0, 0, 0, 16, None, None, None, None, None, 1.0, None, None, None, None, None,
-                               1.0, 1.0, 0.3, 0, 0, None, None, 0, ctypes.byref(nr)) != 0
+                               1.0, 1.0, 0.3, 0, 0, None, None, 0, None, 0, ctypes.byref(nr)) != 0
     assert "bad sizes" in _lib.last_error()
     # null inputs
     assert lib.rr_forward_geom(None, 5, 0, 0, 16, 16, None, None, None, None, None, 1.0, None, None, None, None, None,
-                               1.0, 1.0, 0.3, 0, 0, None, None, 0, ctypes.byref(nr)) != 0
+                               1.0, 1.0, 0.3, 0, 0, None, None, 0, None, 0, ctypes.byref(nr)) != 0
     assert "must not be null" in _lib.last_error()
     assert lib.rr_mark_visible(None, 0, None, None, None, None) == 0
     assert lib.rr_dist2(None, 0, None, None, None, 0) == 0
