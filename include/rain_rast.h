@@ -28,6 +28,7 @@ extern "C" {
 #endif
 
 #define RR_BWD_ACCUMULATE 1
+#define RR_BWD_LEAVE_ROOM 4  /* rr_backward_views: cap the kernel at 3 CTAs per SM so that a CTA of a concurrent rr_allreduce fits beside it */
 #define RR_BWD_LEAF 2        /* rr_backward_views: inputs are the raw leaf tensors, gradients w.r.t. them */
 #define RR_GEOM_LEAF 2       /* rr_forward_geom_views: inputs are the raw leaf tensors (activations applied in the kernel) */
 #define RR_GEOM_KEEP_COV3D 1 /* rr_forward_geom_views: also store the 3D covariance in every view's blob (the per-view rr_backward reads it) */
@@ -133,7 +134,9 @@ int rr_backward(void* stream, int P, int D, int M, int W, int H, int64_t N, cons
  * (59 floats per Gaussian with M = 16, the only supported M) is written once — overwritten, or added with RR_BWD_ACCUMULATE
  * (rows no view touched are then left alone) — and dL_dmean2D[v] ([P,3] per view; the array or single entries may be null)
  * receives each view's viewspace gradient.  stat_*: optional (all or none) f32[P] densification statistics updated in place
- * for every view that saw the Gaussian (train.py:132-134, scene/gaussian_model.py:419-421).
+ * for every view that saw the Gaussian (train.py:132-134, scene/gaussian_model.py:419-421).  [first, first + count) is the
+ * range of Gaussians this call covers (0, P for all): a caller may run the pass chunk by chunk and all-reduce the finished
+ * chunk's bucket rows (rr_allreduce_sum_f32_ranges) on another stream while the next chunk is computed.
  *   flags without RR_BWD_LEAF: shs_or_f_dc = shs[P,16,3], f_rest = null, scales / rotations activated; gradients w.r.t. them:
  *       dL_dmean3D[P,3], dL_dsh_or_f_dc = dL_dsh[P,16,3], dL_dopacity[P], dL_dscale[P,3], dL_drot[P,4]
  *   with RR_BWD_LEAF: means3D = _xyz, shs_or_f_dc = _features_dc[P,1,3], f_rest = _features_rest[P,15,3], scales = _scaling (log),
@@ -147,7 +150,7 @@ int rr_backward_views(void* stream, int P, int D, int M, int W, int H, int nview
 	const int* const* radii, void* const* geom, const float* const* grad_acc, float* const* dL_dmean2D,
 	const float* means3D, const float* shs_or_f_dc, const float* f_rest, const float* scales, float scale_modifier, const float* rotations, float low_pass,
 	float* dL_dmean3D, float* dL_dsh_or_f_dc, float* dL_df_rest, float* dL_dopacity, float* dL_dscale, float* dL_drot,
-	float* stat_max_radii2D, float* stat_grad_accum, float* stat_denom, int flags, int debug);
+	float* stat_max_radii2D, float* stat_grad_accum, float* stat_denom, int first, int count, int flags, int debug);
 
 /* Self test of the packed exponential the render kernels use (exp2x, csrc/render_common.cuh) against libdevice expf —
  * the function the reference's forward.cu:336 / backward.cu:488 compile to — over the float bit patterns
@@ -214,8 +217,13 @@ int rr_densify_stats(void* stream, int P, const int* radii, const float* dL_dmea
  * address aliasing all buckets (in-switch reduction: multimem.ld_reduce + multimem.st), or null (peer loads / stores).  One
  * kernel per rank, `ctas` CTAs (0 = one per SM; the same value on every rank), launched by every rank of the job on its own
  * GPU; epoch must increase by 2 from call to call (same value on all ranks).  *error_flag (local device u32) is set if a
- * cross-rank wait timed out.  Replaces ncclAllReduce for the view-sharded step; world <= 8. */
+ * cross-rank wait timed out.  Replaces ncclAllReduce for the view-sharded step; world <= 8.
+ * rr_allreduce_sum_f32_ranges reduces nranges (<= 8) sub-ranges [offsets[i], offsets[i] + lengths[i]) of the buffer (floats; HOST
+ * arrays; all multiples of 4 when nranges > 1) in one kernel — e.g. the rows of one chunk of Gaussians in each of the bucket's
+ * segments; threads = CTA size (0 = 512). */
 size_t rr_allreduce_signal_bytes(void);
+int rr_allreduce_sum_f32_ranges(void* stream, int rank, int world, int nranges, const int64_t* offsets, const int64_t* lengths, void* const* buffers, void* multicast,
+	void* const* signals, uint32_t* error_flag, uint32_t epoch, int ctas, int threads);
 int rr_allreduce_sum_f32(void* stream, int rank, int world, int64_t n, void* const* buffers, void* multicast, void* const* signals,
 	uint32_t* error_flag, uint32_t epoch, int ctas);
 

@@ -325,14 +325,16 @@ def backward_render(background, dL_dout_color, geomBuffer, R, binningBuffer, ima
 
 
 def backward_views(views, means3D, sh, scales, rotations, scale_modifier, low_pass, degree, image_height, image_width, grads_out,
-                   accumulate=False, stats=None, leaf=False, f_rest=None, debug=False):
+                   accumulate=False, stats=None, leaf=False, f_rest=None, debug=False, first=0, count=None, leave_room=False):
     """Second half of the backward for ALL views of a batch in one pass over the Gaussians (rr_backward_views).
     views: list of dicts with viewmatrix, projmatrix, campos (device tensors), tanfovx, tanfovy (floats), radii (i32[P]), geom (the
     view's geometry blob), acc (the blob ``backward_render`` returned) and optionally dL_dmean2D (f32[P,3], written).
     grads_out: the gradient bucket's segments — activated layout dict(means3D, sh, opacity, scales, rotations), or with
     ``leaf=True`` dict(xyz, f_dc, f_rest, opacity, scaling, rotation); then means3D / sh / scales / rotations are the raw leaves
     _xyz / _features_dc / _scaling / _rotation and ``f_rest`` is _features_rest (scene/gaussian_model.py:131-136).
-    stats: optional (max_radii2D, xyz_gradient_accum, denom) f32[P] tensors updated in place."""
+    stats: optional (max_radii2D, xyz_gradient_accum, denom) f32[P] tensors updated in place.
+    first / count: the range of Gaussians this call covers (default all); leave_room: cap the kernel's occupancy so that a
+    concurrently running all-reduce kernel fits on every SM (rain_b200.multiview overlaps the two chunk by chunk)."""
     import ctypes
     lib = _lib.load()
     dev = means3D.device
@@ -369,7 +371,8 @@ def backward_views(views, means3D, sh, scales, rotations, scale_modifier, low_pa
             keep[0].data_ptr(), keep[1].data_ptr(), keep[4].data_ptr() if leaf else None, keep[2].data_ptr(), float(scale_modifier), keep[3].data_ptr(), float(low_pass),
             g[names[0]].data_ptr(), g[names[1]].data_ptr(), g["f_rest"].data_ptr() if leaf else None,
             g["opacity"].data_ptr(), g["scaling" if leaf else "scales"].data_ptr(), g["rotation" if leaf else "rotations"].data_ptr(),
-            _ptr(st[0]), _ptr(st[1]), _ptr(st[2]), (1 if accumulate else 0) | (2 if leaf else 0), int(bool(debug))), "rr_backward_views")
+            _ptr(st[0]), _ptr(st[1]), _ptr(st[2]), int(first), int(P - first if count is None else count),
+            (1 if accumulate else 0) | (2 if leaf else 0) | (4 if leave_room else 0), int(bool(debug))), "rr_backward_views")
 
 
 def tile_cull_enabled():

@@ -61,7 +61,7 @@ SIGNATURES = {
                                _vp, _vp, _vp, _vp,
                                _vp, _vp, _vp, _vp, _f, _vp, _f,
                                _vp, _vp, _vp, _vp, _vp, _vp,
-                               _vp, _vp, _vp, _i, _i]),
+                               _vp, _vp, _vp, _i, _i, _i, _i]),
     "rr_mark_visible": (_i, [_vp, _i, _vp, _vp, _vp, _vp]),
     "rr_selftest_exp": (_i, [_vp, _c.c_uint32, _c.c_uint32, _vp]),
     "rr_loss_ws_bytes": (_sz, [_i, _i, _i]),
@@ -73,6 +73,7 @@ SIGNATURES = {
     "rr_activate": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "rr_densify_stats": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp]),
     "rr_allreduce_signal_bytes": (_sz, []),
+    "rr_allreduce_sum_f32_ranges": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _c.c_uint32, _i, _i]),
     "rr_allreduce_sum_f32": (_i, [_vp, _i, _i, _i64, _vp, _vp, _vp, _vp, _c.c_uint32, _i]),
     "rr_dist2_ws_bytes": (_sz, [_i]),
     "rr_dist2": (_i, [_vp, _i, _vp, _vp, _vp, _sz]),

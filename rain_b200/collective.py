@@ -85,6 +85,20 @@ class SymmetricAllReduce:
         self.epoch = (self.epoch + 2) & 0x7FFFFFFF
         return self.flat
 
+    def allreduce_ranges(self, ranges, ctas=None, threads=256):
+        """in-place sum of the sub-ranges [(offset, length), ...] (floats, multiples of 4, at most 8) of the buffer in one kernel,
+        on the current stream; every rank calls it with the same ranges.  Smaller CTAs (256 threads) so that one fits on every
+        SM beside a co-running kernel that left room for it."""
+        lib = _lib.load()
+        n = len(ranges)
+        offs = (ctypes.c_int64 * n)(*[int(o) for o, _ in ranges])
+        lens = (ctypes.c_int64 * n)(*[int(l) for _, l in ranges])
+        with torch.cuda.device(self.flat.device):
+            _lib.check(lib.rr_allreduce_sum_f32_ranges(torch.cuda.current_stream().cuda_stream, self.rank, self.world, n, offs, lens, self._bufs,
+                                                       self.multicast or None, self._sigs, self.error.data_ptr(), self.epoch,
+                                                       self.ctas if ctas is None else int(ctas), int(threads)), "rr_allreduce_sum_f32_ranges")
+        self.epoch = (self.epoch + 2) & 0x7FFFFFFF
+
     def check(self):
         """raise if a cross-rank wait of an earlier all-reduce timed out (synchronises)"""
         if int(self.error.item()) != 0:

@@ -68,57 +68,62 @@ __device__ __forceinline__ void mm_st(float* mc, float4 v) {
 template <bool MULTIMEM>
 __global__ void __launch_bounds__(AR_THREADS) allreduce_kernel(AllReduceArgs a)
 {
-	cross_rank_barrier(a, a.epoch);                         // every rank's bucket is final
-	// float4 vectors [lo, hi) of this rank's slice; CTA b takes a contiguous share, its threads stride through it
-	const int64_t n4 = a.n / 4;
-	const int64_t lo = n4 * a.rank / a.world, hi = n4 * (a.rank + 1) / a.world;
-	const int64_t per = (hi - lo + gridDim.x - 1) / gridDim.x;
-	const int64_t b0 = lo + per * blockIdx.x, b1 = min(hi, b0 + per);
+	cross_rank_barrier(a, a.epoch);                         // every rank's bucket (these ranges of it) is final
 	constexpr int U = 4;                                    // independent vectors in flight per thread
-	for (int64_t i = b0 + threadIdx.x; i < b1; i += (int64_t)AR_THREADS * U) {
-		float4 v[U];
-		#pragma unroll
-		for (int u = 0; u < U; u++) {
-			const int64_t j = i + (int64_t)u * AR_THREADS;
-			if (j < b1) {
-				if (MULTIMEM) v[u] = mm_ld_reduce(a.multicast + 4 * j);
-				else {
-					float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-					for (int r = 0; r < a.world; r++) {           // rank order: the same sum on every replica of the job
-						const float4 t = ld_peer4(a.buffers[r] + 4 * j);
-						s.x += t.x; s.y += t.y; s.z += t.z; s.w += t.w;
+	const int nthreads = blockDim.x;
+	for (int rg = 0; rg < a.nranges; rg++) {
+		// float4 vectors [lo, hi) of this rank's slice of the range; CTA b takes a contiguous share, its threads stride through it
+		const int64_t v0 = a.off[rg] / 4, n4 = a.len[rg] / 4;
+		const int64_t lo = v0 + n4 * a.rank / a.world, hi = v0 + n4 * (a.rank + 1) / a.world;
+		const int64_t per = (hi - lo + gridDim.x - 1) / gridDim.x;
+		const int64_t b0 = lo + per * blockIdx.x, b1 = min(hi, b0 + per);
+		for (int64_t i = b0 + threadIdx.x; i < b1; i += (int64_t)nthreads * U) {
+			float4 v[U];
+			#pragma unroll
+			for (int u = 0; u < U; u++) {
+				const int64_t j = i + (int64_t)u * nthreads;
+				if (j < b1) {
+					if (MULTIMEM) v[u] = mm_ld_reduce(a.multicast + 4 * j);
+					else {
+						float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+						for (int r = 0; r < a.world; r++) {           // rank order: the same sum on every replica of the job
+							const float4 t = ld_peer4(a.buffers[r] + 4 * j);
+							s.x += t.x; s.y += t.y; s.z += t.z; s.w += t.w;
+						}
+						v[u] = s;
 					}
-					v[u] = s;
+				}
+			}
+			#pragma unroll
+			for (int u = 0; u < U; u++) {
+				const int64_t j = i + (int64_t)u * nthreads;
+				if (j < b1) {
+					if (MULTIMEM) mm_st(a.multicast + 4 * j, v[u]);
+					else for (int r = 0; r < a.world; r++) st_peer4(a.buffers[r] + 4 * j, v[u]);
 				}
 			}
 		}
-		#pragma unroll
-		for (int u = 0; u < U; u++) {
-			const int64_t j = i + (int64_t)u * AR_THREADS;
-			if (j < b1) {
-				if (MULTIMEM) mm_st(a.multicast + 4 * j, v[u]);
-				else for (int r = 0; r < a.world; r++) st_peer4(a.buffers[r] + 4 * j, v[u]);
-			}
+		// the len % 4 tail floats of the range (single-range calls only): rank 0, CTA 0, through the peer pointers
+		if (a.rank == 0 && blockIdx.x == 0 && threadIdx.x < (unsigned)(a.len[rg] & 3)) {
+			const int64_t j = a.off[rg] + (a.len[rg] & ~(int64_t)3) + threadIdx.x;
+			float s = 0.f;
+			for (int r = 0; r < a.world; r++) s += ld_peer1(a.buffers[r] + j);
+			for (int r = 0; r < a.world; r++) st_peer1(a.buffers[r] + j, s);
 		}
-	}
-	// the n % 4 tail floats: rank 0, CTA 0, through the peer pointers
-	if (a.rank == 0 && blockIdx.x == 0 && threadIdx.x < (unsigned)(a.n & 3)) {
-		const int64_t j = (a.n & ~(int64_t)3) + threadIdx.x;
-		float s = 0.f;
-		for (int r = 0; r < a.world; r++) s += ld_peer1(a.buffers[r] + j);
-		for (int r = 0; r < a.world; r++) st_peer1(a.buffers[r] + j, s);
 	}
 	cross_rank_barrier(a, a.epoch + 1);                     // every slice has been broadcast: the bucket may be read
 }
 
 }  // namespace
 
-int launch_allreduce(cudaStream_t stream, const AllReduceArgs& a, int ctas)
+int launch_allreduce(cudaStream_t stream, const AllReduceArgs& a, int ctas, int threads)
 {
-	if (a.n == 0 || a.world <= 1) return 0;
+	if (a.world <= 1) return 0;
+	if (threads <= 0 || threads > AR_THREADS) threads = AR_THREADS;
+	threads = (threads + 31) / 32 * 32;
 	count_launch();
-	if (a.multicast) allreduce_kernel<true><<<ctas, AR_THREADS, 0, stream>>>(a);
-	else allreduce_kernel<false><<<ctas, AR_THREADS, 0, stream>>>(a);
+	if (a.multicast) allreduce_kernel<true><<<ctas, threads, 0, stream>>>(a);
+	else allreduce_kernel<false><<<ctas, threads, 0, stream>>>(a);
 	return check_launch("allreduce", stream, false);
 }
 

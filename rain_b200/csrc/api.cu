@@ -511,10 +511,11 @@ int rr_backward_views(void* stream_, int P, int D, int M, int W, int H, int nvie
 	const int* const* radii, void* const* geom, const float* const* grad_acc, float* const* dL_dmean2D,
 	const float* means3D, const float* shs_or_f_dc, const float* f_rest, const float* scales, float scale_modifier, const float* rotations, float low_pass,
 	float* dL_dmean3D, float* dL_dsh_or_f_dc, float* dL_df_rest, float* dL_dopacity, float* dL_dscale, float* dL_drot,
-	float* stat_max_radii2D, float* stat_grad_accum, float* stat_denom, int flags, int debug)
+	float* stat_max_radii2D, float* stat_grad_accum, float* stat_denom, int first, int count, int flags, int debug)
 {
 	cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
-	if (P == 0 || nviews == 0) return 0;
+	if (P == 0 || nviews == 0 || count == 0) return 0;
+	if (first < 0 || count < 0 || (int64_t)first + count > P) { set_error("bad Gaussian range [%d, %d + %d) of %d", first, first, count, P); return -1; }
 	if (P < 0 || nviews < 0 || W <= 0 || H <= 0) { set_error("bad sizes P=%d nviews=%d W=%d H=%d", P, nviews, W, H); return -1; }
 	const bool leaf = (flags & RR_BWD_LEAF) != 0;
 	if (M != 16 || D < 0 || D > 3) { set_error("rr_backward_views needs M = 16 SH coefficients and degree 0..3 (M=%d, D=%d)", M, D); return -1; }
@@ -529,6 +530,7 @@ int rr_backward_views(void* stream_, int P, int D, int M, int W, int H, int nvie
 	for (int v0 = 0; v0 < nviews; v0 += BV_MAX_VIEWS) {
 		BackwardViewsArgs a; memset(&a, 0, sizeof(a));
 		a.P = P; a.D = D; a.M = M; a.W = W; a.H = H; a.nviews = nviews - v0 < BV_MAX_VIEWS ? nviews - v0 : BV_MAX_VIEWS;
+		a.first = first; a.count = count; a.leave_room = (flags & RR_BWD_LEAVE_ROOM) ? 1 : 0;
 		a.scale_modifier = scale_modifier; a.low_pass = low_pass; a.leaf = leaf ? 1 : 0;
 		a.accumulate = ((flags & RR_BWD_ACCUMULATE) || v0 > 0) ? 1 : 0;      // later chunks of a long batch add to the first one's rows
 		a.means3D = means3D; a.scales = scales; a.rotations = rotations; a.shs = leaf ? nullptr : shs_or_f_dc; a.f_dc = leaf ? shs_or_f_dc : nullptr; a.f_rest = f_rest;
@@ -652,19 +654,36 @@ size_t rr_allreduce_signal_bytes(void) { return sizeof(uint32_t) * AR_MAX_CTAS *
 int rr_allreduce_sum_f32(void* stream_, int rank, int world, int64_t n, void* const* buffers, void* multicast, void* const* signals,
 	uint32_t* error_flag, uint32_t epoch, int ctas)
 {
-	if (world <= 1 || n == 0) return 0;
-	if (world > AR_MAX_WORLD || rank < 0 || rank >= world || n < 0) { set_error("rr_allreduce_sum_f32: bad rank/world/n %d/%d/%lld (at most %d ranks)", rank, world, (long long)n, AR_MAX_WORLD); return -1; }
-	if (bad_ptr(buffers, "buffers") || bad_ptr(signals, "signals") || bad_ptr(error_flag, "error_flag")) return -1;
+	const int64_t off = 0;
+	return rr_allreduce_sum_f32_ranges(stream_, rank, world, 1, &off, &n, buffers, multicast, signals, error_flag, epoch, ctas, 0);
+}
+
+int rr_allreduce_sum_f32_ranges(void* stream_, int rank, int world, int nranges, const int64_t* offsets, const int64_t* lengths, void* const* buffers, void* multicast,
+	void* const* signals, uint32_t* error_flag, uint32_t epoch, int ctas, int threads)
+{
+	if (world <= 1 || nranges == 0) return 0;
+	if (world > AR_MAX_WORLD || rank < 0 || rank >= world || nranges < 0 || nranges > AR_MAX_RANGES) {
+		set_error("rr_allreduce_sum_f32: bad rank/world/ranges %d/%d/%d (at most %d ranks, %d ranges)", rank, world, nranges, AR_MAX_WORLD, AR_MAX_RANGES); return -1;
+	}
+	if (bad_ptr(offsets, "offsets") || bad_ptr(lengths, "lengths") || bad_ptr(buffers, "buffers") || bad_ptr(signals, "signals") || bad_ptr(error_flag, "error_flag")) return -1;
 	if (ctas <= 0) ctas = 148;
 	if (ctas > AR_MAX_CTAS) ctas = AR_MAX_CTAS;
 	AllReduceArgs a; memset(&a, 0, sizeof(a));
-	a.multicast = reinterpret_cast<float*>(multicast); a.error_flag = error_flag; a.n = n; a.rank = rank; a.world = world; a.epoch = epoch;
+	a.multicast = reinterpret_cast<float*>(multicast); a.error_flag = error_flag; a.rank = rank; a.world = world; a.epoch = epoch;
+	a.nranges = nranges;
+	int64_t total = 0;
+	for (int r = 0; r < nranges; r++) {
+		if (offsets[r] < 0 || lengths[r] < 0 || (nranges > 1 && ((offsets[r] | lengths[r]) & 3))) { set_error("rr_allreduce_sum_f32: ranges must be non-negative and, if several, multiples of 4 floats"); return -1; }
+		if (offsets[r] & 3) { set_error("rr_allreduce_sum_f32: range offsets must be multiples of 4 floats"); return -1; }
+		a.off[r] = offsets[r]; a.len[r] = lengths[r]; total += lengths[r];
+	}
+	if (total == 0) return 0;
 	for (int r = 0; r < world; r++) {
 		if (bad_ptr(buffers[r], "buffers[r]") || bad_ptr(signals[r], "signals[r]")) return -1;
 		if (reinterpret_cast<uintptr_t>(buffers[r]) & 15) { set_error("rr_allreduce_sum_f32: buffers must be 16-byte aligned"); return -1; }
 		a.buffers[r] = reinterpret_cast<float*>(buffers[r]); a.signal[r] = reinterpret_cast<uint32_t*>(signals[r]);
 	}
-	return launch_allreduce(reinterpret_cast<cudaStream_t>(stream_), a, ctas);
+	return launch_allreduce(reinterpret_cast<cudaStream_t>(stream_), a, ctas, threads);
 }
 
 size_t rr_dist2_ws_bytes(int P) { return knn_ws_bytes(P); }

@@ -110,6 +110,8 @@ int launch_preprocess_bwd(cudaStream_t, const PreprocessBwdArgs&);
 constexpr int BV_MAX_VIEWS = 16;
 struct BackwardViewsArgs {
 	int P, D, M, W, H, nviews;
+	int first, count;         // the Gaussians [first, first + count) this launch covers
+	int leave_room;           // 1: cap the kernel at 3 CTAs per SM so a co-running all-reduce CTA fits on every SM
 	float scale_modifier, low_pass;
 	int accumulate;           // 1: += into the bucket, rows no view of this batch touched are left alone
 	int leaf;                 // 1: inputs are the raw leaf tensors, gradients w.r.t. them (see the kernel's header)
@@ -141,17 +143,18 @@ int launch_densify_stats(cudaStream_t, int P, const int* radii, const float* dL_
 
 // allreduce.cu: one-kernel two-shot all-reduce of a symmetric f32 buffer over NVLink peer / multicast memory
 constexpr int AR_MAX_WORLD = 8;
+constexpr int AR_MAX_RANGES = 8;
 constexpr int AR_MAX_CTAS = 256;          // CTAs per rank; the signal buffer holds AR_MAX_CTAS * AR_MAX_WORLD flag words
 struct AllReduceArgs {
 	float* multicast;                     // multicast address of the symmetric buffer, or null (peer-pointer variant)
 	float* buffers[AR_MAX_WORLD];         // every rank's buffer as mapped into THIS rank's address space ([rank] = the local one)
 	uint32_t* signal[AR_MAX_WORLD];       // every rank's flag buffer (u32[AR_MAX_CTAS * world], zero before the first call), peer-mapped
 	uint32_t* error_flag;                 // local device word, set to 1 if a cross-rank wait timed out
-	int64_t n;                            // floats
+	int nranges; int64_t off[AR_MAX_RANGES], len[AR_MAX_RANGES];      // sub-ranges of the buffer (floats) reduced by this launch
 	int rank, world;
 	uint32_t epoch;                       // flag value of this call's first barrier; the second uses epoch + 1; strictly increasing across calls
 };
-int launch_allreduce(cudaStream_t, const AllReduceArgs&, int ctas);
+int launch_allreduce(cudaStream_t, const AllReduceArgs&, int ctas, int threads /*0 = default*/);
 
 // knn.cu
 size_t knn_ws_bytes(int P);

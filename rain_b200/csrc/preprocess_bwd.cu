@@ -369,12 +369,15 @@ __global__ void __launch_bounds__(BV_THREADS, 4) backward_views_kernel(BackwardV
 		s_cam[tid][37] = a.W / (2.0f * a.tan_fovx[tid]); s_cam[tid][38] = a.H / (2.0f * a.tan_fovy[tid]);       // rasterizer_impl.cu:213-214
 	}
 	__syncthreads();
-	const int warp_base = blockIdx.x * BV_THREADS + warp * 32;
-	if (warp_base >= a.P) return;                               // warp-uniform
+	// this launch covers the Gaussians [first, last) (the whole set, or one chunk of it when the caller overlaps the all-reduce of
+	// finished chunks with the backward of the next one)
+	const int last = a.first + a.count;
+	const int warp_base = a.first + blockIdx.x * BV_THREADS + warp * 32;
+	if (warp_base >= last) return;                              // warp-uniform
 	const int idx = warp_base + lane;
-	const bool valid = idx < a.P;
-	const int nvalid = min(32, a.P - warp_base);
-	const size_t ii = (size_t)(valid ? idx : 0), i3 = 3 * ii;
+	const bool valid = idx < last;
+	const int nvalid = min(32, last - warp_base);
+	const size_t ii = (size_t)(valid ? idx : a.first), i3 = 3 * ii;
 	float* __restrict__ sh = s_sh[warp] + lane * SH_STRIDE;
 	float* __restrict__ dsh = s_dsh[warp] + lane * SH_STRIDE;
 
@@ -541,14 +544,16 @@ int launch_preprocess_bwd(cudaStream_t stream, const PreprocessBwdArgs& a)
 
 int launch_backward_views(cudaStream_t stream, const BackwardViewsArgs& a)
 {
-	if (a.P == 0 || a.nviews == 0) return 0;
-	const unsigned grid = (unsigned)((a.P + BV_THREADS - 1) / BV_THREADS);
+	if (a.P == 0 || a.nviews == 0 || a.count == 0) return 0;
+	const unsigned grid = (unsigned)((a.count + BV_THREADS - 1) / BV_THREADS);
+	// leave_room: at most 3 CTAs per SM (by shared memory), so that one CTA of the all-reduce kernel of an earlier chunk fits beside
+	const size_t smem = a.leave_room ? (BV_SMEM_BYTES > 59392 ? BV_SMEM_BYTES : (size_t)59392) : BV_SMEM_BYTES;
 	auto launch = [&](auto kern) -> int {
-		if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BV_SMEM_BYTES) != cudaSuccess) {
-			set_error("backward_views: cannot reserve %zu bytes of dynamic shared memory", BV_SMEM_BYTES); return -1;
+		if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 59392) != cudaSuccess) {
+			set_error("backward_views: cannot reserve %d bytes of dynamic shared memory", 59392); return -1;
 		}
 		count_launch();
-		kern<<<grid, BV_THREADS, BV_SMEM_BYTES, stream>>>(a);
+		kern<<<grid, BV_THREADS, smem, stream>>>(a);
 		return 0;
 	};
 	if (a.leaf ? launch(backward_views_kernel<true>) : launch(backward_views_kernel<false>)) return -1;

@@ -55,12 +55,15 @@ class GradientBucket:
         else:
             raise ValueError(f"unknown bucket layout {layout!r}")
         self.segments = SEGMENTS if layout == "activated" else LEAF_SEGMENTS
+        self.reduced = False         # the step's all-reduce already happened inside render_views_fwd_bwd (overlapped with the backward)
         self.views, off = {}, 0
         for name in self.segments:
             n = 1
             for d in shapes[name]:
                 n *= d
             self.views[name] = self.flat[off:off + n].view(shapes[name])
+            self.seg_offsets = getattr(self, "seg_offsets", {})
+            self.seg_offsets[name] = (off, n // self.P if self.P else 0)      # (float offset of the segment, floats per Gaussian)
             off += n
         assert off == self.flat.numel()
         self.filled = False
@@ -71,6 +74,11 @@ class GradientBucket:
     def zero_(self):
         self.flat.zero_()
         self.filled = False
+        self.reduced = False
+
+    def chunk_ranges(self, g0, g1):
+        """(float offset, length) of the rows of Gaussians [g0, g1) in every segment of the flat buffer"""
+        return [(off + g0 * per, (g1 - g0) * per) for off, per in (self.seg_offsets[k] for k in self.segments)]
 
     def nbytes(self):
         return self.flat.numel() * 4
@@ -89,7 +97,8 @@ class ViewResult:
 def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int], bucket: GradientBucket,
                          grad_fn: Callable[[int, torch.Tensor, torch.Tensor], torch.Tensor], *, bg: torch.Tensor, sh_degree: int,
                          scale_modifier: float = 1.0, low_pass: float = 0.3, debug: bool = False, keep_outputs: bool = True,
-                         pipeline: str = "two_stream", batch_backward: int = 8, batch_forward: int = 8, stats=None, leaves: Optional[dict] = None, backend=_native) -> List[ViewResult]:
+                         pipeline: str = "two_stream", batch_backward: int = 8, batch_forward: int = 8, stats=None, leaves: Optional[dict] = None, overlap_allreduce: bool = True,
+                         backend=_native) -> List[ViewResult]:
     """Forward + backward of this rank's views; parameter gradients of all views are summed into ``bucket``.
 
     params: dict(means3D[P,3], opacities[P,1], shs[P,M,3], scales[P,3], rotations[P,4]) — activated values, as
@@ -110,6 +119,8 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
     scaling, rotation) — the six RAW leaf tensors of scene/gaussian_model.py:131-136.  ``params`` may then be None: the batched
     geometry pass applies sigmoid / exp / normalise / cat itself, the batched backward applies their chain rule and writes LEAF
     gradients into ``bucket`` (which must have layout="leaf"); no activated copy of the parameters exists anywhere.
+    overlap_allreduce (N > 1, symmetric bucket): the step's all-reduce runs chunk by chunk beside the last batched backward and
+    ``bucket.reduced`` is set, so the ``allreduce_bucket`` call that follows is a no-op.
     stats: optional rain_b200.optim.DensificationStats; the batched backward folds the views' densification statistics into
     its per-step delta in the same pass (otherwise call stats.add_view per view)."""
     if pipeline not in ("two_stream", "one_stream"):
@@ -178,6 +189,13 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
         # one stream: the geometry half of view i+1 is enqueued BEFORE the backward of view i, so its num_rendered is on the
         # host long before it is needed and the device never waits for the round trip that sizes the binning buffer
         ensure_geom(0)
+    # overlap the step's all-reduce with its last batched backward (N > 1, symmetric bucket, P a multiple of 4 so that every chunk's
+    # rows are 16-byte aligned in every segment)
+    P = params["means3D"].shape[0]
+    overlap_chunks = 0
+    if batched and overlap_allreduce and bucket.collective is not None and bucket.collective.world > 1 and P % 4 == 0 and P >= 4096:
+        overlap_chunks = 4
+    bucket.reduced = False
     group = []
     for i, v in enumerate(view_ids):
         cam = cameras[v]
@@ -198,16 +216,31 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
         if batched:
             # per view only the backward tile renderer; its accumulator blob, radii and geometry blob stay alive until the batch's
             # single per-Gaussian pass
-            P = params["means3D"].shape[0]
             acc = backend.backward_render(bg, dpix, geom, N, binning, img, P, debug)
             d2 = torch.empty((P, 3), dtype=torch.float32, device=dev)
             group.append(dict(viewmatrix=cam.viewmatrix, projmatrix=cam.projmatrix, campos=cam.campos, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
                               radii=radii, geom=geom, acc=acc, dL_dmean2D=d2))
             if len(group) == batch_backward or i + 1 == n:
-                backend.backward_views(group, params["means3D"], params["shs"], params["scales"], params["rotations"], scale_modifier, low_pass, sh_degree,
-                                       cam.height, cam.width, bucket.grads_out(), accumulate=bucket.filled,
-                                       stats=stats.delta_tensors() if stats is not None else None, debug=debug,
-                                       **(dict(leaf=True, f_rest=leaves["f_rest"]) if leaf else {}))
+                bv = lambda **kx: backend.backward_views(group, params["means3D"], params["shs"], params["scales"], params["rotations"], scale_modifier, low_pass,
+                                                         sh_degree, cam.height, cam.width, bucket.grads_out(), accumulate=bucket.filled,
+                                                         stats=stats.delta_tensors() if stats is not None else None, debug=debug,
+                                                         **(dict(leaf=True, f_rest=leaves["f_rest"]) if leaf else {}), **kx)
+                if i + 1 == n and overlap_chunks > 1:
+                    # last pass of the step on N > 1 GPUs: the Gaussians are walked in chunks, and while chunk k + 1 is computed the
+                    # finished bucket rows of chunk k are all-reduced by the one-kernel NVLink all-reduce on a second stream (the
+                    # backward is capped at 3 CTAs per SM so that one all-reduce CTA fits on every SM beside it)
+                    comm = _geom_stream(dev, 2)
+                    step_g = ((P + overlap_chunks - 1) // overlap_chunks + 3) // 4 * 4
+                    for g0 in range(0, P, step_g):
+                        g1 = min(P, g0 + step_g)
+                        bv(first=g0, count=g1 - g0, leave_room=True)
+                        comm.wait_stream(main)
+                        with torch.cuda.stream(comm):
+                            bucket.collective.allreduce_ranges(bucket.chunk_ranges(g0, g1))
+                    main.wait_stream(comm)
+                    bucket.reduced = True
+                else:
+                    bv()
                 bucket.filled = True
                 group = []
         else:
@@ -276,6 +309,11 @@ def allreduce_bucket(bucket: GradientBucket, group=None, average: bool = False):
     """The single collective of a step: sum (or mean) of the flat bucket over all ranks, in place."""
     import torch.distributed as dist
     if group == "skip":          # a single-rank step inside an initialised process group (tools/verify_multigpu.py)
+        return bucket
+    if bucket.reduced:           # already summed, chunk by chunk beside the step's last backward pass
+        bucket.reduced = False
+        if average:
+            bucket.flat.div_(dist.get_world_size(group))
         return bucket
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         if bucket.collective is not None:
