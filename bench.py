@@ -188,7 +188,7 @@ def run_ours(args, rank, world, local):
     # N > 1: the bucket lives in symmetric memory and is reduced by the library's one-kernel NVLink all-reduce (csrc/allreduce.cu);
     # `--collective nccl` keeps it a plain tensor reduced by ncclAllReduce
     bucket = mv.GradientBucket(P, 16, dev, symmetric=(world > 1 and args.collective == "rr"))
-    kw = dict(bg=bg, sh_degree=D, keep_outputs=False)
+    kw = dict(bg=bg, sh_degree=D, keep_outputs=False, overlap_allreduce=args.overlap_chunks, overlap_leave_room=not args.overlap_no_room)
 
     # ---------------- device-resident arm (`value`) ----------------
     cams_d = [c.to(dev) for c in cams_h]
@@ -460,6 +460,8 @@ def main():
     ap.add_argument("--workload", default="C3", choices=["C1", "C2", "C3", "C4"])
     ap.add_argument("--cpu-renders", type=int, default=2, help="renders of the workload timed on the host for cpu_baseline (0 = skip)")
     ap.add_argument("--collective", default="rr", choices=["rr", "nccl"], help="N > 1: rr = the library's one-kernel NVLink all-reduce on a symmetric bucket, nccl = ncclAllReduce")
+    ap.add_argument("--overlap-chunks", type=int, default=0, help="experiment: all-reduce in K chunks beside the last batched backward (0 = off, the default)")
+    ap.add_argument("--overlap-no-room", action="store_true", help="experiment: do not cap the backward's occupancy while overlapping")
     ap.add_argument("--dropin-iters", type=int, default=50, help="timed single-view iterations of the drop-in arm at N = 1 (0 = skip, e.g. under a profiler)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

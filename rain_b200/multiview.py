@@ -97,7 +97,7 @@ class ViewResult:
 def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int], bucket: GradientBucket,
                          grad_fn: Callable[[int, torch.Tensor, torch.Tensor], torch.Tensor], *, bg: torch.Tensor, sh_degree: int,
                          scale_modifier: float = 1.0, low_pass: float = 0.3, debug: bool = False, keep_outputs: bool = True,
-                         pipeline: str = "two_stream", batch_backward: int = 8, batch_forward: int = 8, stats=None, leaves: Optional[dict] = None, overlap_allreduce: bool = True,
+                         pipeline: str = "two_stream", batch_backward: int = 8, batch_forward: int = 8, stats=None, leaves: Optional[dict] = None, overlap_allreduce: int = 0, overlap_leave_room: bool = True,
                          backend=_native) -> List[ViewResult]:
     """Forward + backward of this rank's views; parameter gradients of all views are summed into ``bucket``.
 
@@ -119,8 +119,10 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
     scaling, rotation) — the six RAW leaf tensors of scene/gaussian_model.py:131-136.  ``params`` may then be None: the batched
     geometry pass applies sigmoid / exp / normalise / cat itself, the batched backward applies their chain rule and writes LEAF
     gradients into ``bucket`` (which must have layout="leaf"); no activated copy of the parameters exists anywhere.
-    overlap_allreduce (N > 1, symmetric bucket): the step's all-reduce runs chunk by chunk beside the last batched backward and
-    ``bucket.reduced`` is set, so the ``allreduce_bucket`` call that follows is a no-op.
+    overlap_allreduce = K > 1 (N > 1, symmetric bucket; default off): the step's all-reduce runs in K chunks of Gaussians beside the
+    last batched backward and ``bucket.reduced`` is set, so the ``allreduce_bucket`` call that follows is a no-op.  Measured
+    SLOWER than the plain all-reduce after the backward on B200 (both kernels are HBM bound: 8.33 vs 8.08 ms per step at 2 GPUs,
+    profiles/r02_n2_overlap.txt), hence off.
     stats: optional rain_b200.optim.DensificationStats; the batched backward folds the views' densification statistics into
     its per-step delta in the same pass (otherwise call stats.add_view per view)."""
     if pipeline not in ("two_stream", "one_stream"):
@@ -193,8 +195,8 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
     # rows are 16-byte aligned in every segment)
     P = params["means3D"].shape[0]
     overlap_chunks = 0
-    if batched and overlap_allreduce and bucket.collective is not None and bucket.collective.world > 1 and P % 4 == 0 and P >= 4096:
-        overlap_chunks = 4
+    if batched and overlap_allreduce > 1 and bucket.collective is not None and bucket.collective.world > 1 and P % 4 == 0 and P >= 4096:
+        overlap_chunks = int(overlap_allreduce)
     bucket.reduced = False
     group = []
     for i, v in enumerate(view_ids):
@@ -233,7 +235,7 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
                     step_g = ((P + overlap_chunks - 1) // overlap_chunks + 3) // 4 * 4
                     for g0 in range(0, P, step_g):
                         g1 = min(P, g0 + step_g)
-                        bv(first=g0, count=g1 - g0, leave_room=True)
+                        bv(first=g0, count=g1 - g0, leave_room=overlap_leave_room)
                         comm.wait_stream(main)
                         with torch.cuda.stream(comm):
                             bucket.collective.allreduce_ranges(bucket.chunk_ranges(g0, g1))

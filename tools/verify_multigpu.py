@@ -47,7 +47,7 @@ def main():
         bucket.flat.fill_(float("nan"))
         stats = DensificationStats(P, dev)
         res = mv.train_step_views(params, cams, V, bucket, lambda v, c, d: dp[v], rank=r, world_size=w, bg=bg, sh_degree=D,
-                                  group=None if w > 1 else "skip")
+                                  group=None if w > 1 else "skip", overlap_allreduce=int(os.environ.get("RAIN_VERIFY_OVERLAP", "0")))
         for x in res:
             stats.add_view(x.radii, x.dL_dmeans2D)
         return bucket, stats, res
