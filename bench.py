@@ -205,6 +205,8 @@ def run_ours(args, rank, world, local):
         bucket.filled = False
         res = mv.render_views_fwd_bwd(params, cams_d, ids, bucket, grad_resident, pipeline=pipeline, **kw)
         if time_allreduce and world > 1:
+            if os.environ.get("RAIN_BENCH_DIAG", "") == "arsync":      # diagnostic only: remove the rank skew from the all-reduce's time
+                torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
             a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a0.record(); mv.allreduce_bucket(bucket); a1.record()
             ar_events.append((a0, a1))
@@ -231,6 +233,10 @@ def run_ours(args, rank, world, local):
     t1 = time.time()
     launches = lib.rr_launch_count() - launches0
     ms = max_over_ranks(e0.elapsed_time(e1), world, dev)
+    if os.environ.get("RAIN_BENCH_DIAG", "") == "artrace" and world > 1:      # diagnostic only: per-step all-reduce time of every rank
+        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+        with open(os.path.join(ROOT, "gpurun_out", f"artrace_{args.collective}_r{rank}.txt"), "w") as f:
+            f.write(" ".join(f"{a.elapsed_time(b):.3f}" for a, b in ar_events) + "\n")
     allreduce_ms = max_over_ranks(sum(a.elapsed_time(b) for a, b in ar_events) / max(1, len(ar_events)), world, dev) if world > 1 else 0.0
     clocks = sampler.stop(t0, t1) if rank == 0 else None
     renders = world * VPS * args.steps
