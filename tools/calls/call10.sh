@@ -14,7 +14,7 @@ timeout 200 python tools/live_lanes.py C3 4 > gpurun_out/live_lanes_$T.log 2>&1;
 timeout 100 python bench.py --steps 2 --warmup 3 --cpu-renders 0 --dropin-iters 4 > gpurun_out/plain_$T.log 2>&1 &&
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/ncu_launches_$T.csv python bench.py --steps 2 --warmup 3 --cpu-renders 0 --dropin-iters 4 > gpurun_out/ncu1_$T.log 2>&1
 echo "ncu launches rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'render_|onesweep|preprocess|duplicate|scan_chained|tile_|histogram|backward_views|loss' -s 120 -c 60 -o gpurun_out/ncu_full_$T python bench.py --steps 2 --warmup 3 --cpu-renders 0 --dropin-iters 4 > gpurun_out/ncu2_$T.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'render_|onesweep|preprocess|duplicate|scan_chained|tile_|histogram|backward_views|loss' -s 120 -c 28 -o gpurun_out/ncu_full_$T python bench.py --steps 2 --warmup 3 --cpu-renders 0 --dropin-iters 4 > gpurun_out/ncu2_$T.log 2>&1
 echo "ncu full rc=$?"
 for f in ours reference c2 c2_ref c4_n1 c4_ref; do python -c "
 import json

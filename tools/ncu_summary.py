@@ -11,8 +11,8 @@ COLS = ["gpu__time_duration.sum", "sm__cycles_elapsed.max", "dram__bytes_read.su
         "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
         "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
         "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum"]
-STAGE_OF = [("render_bwd", "render_bwd"), ("render_fwd", "render_fwd"), ("preprocess_bwd", "preprocess_bwd"), ("preprocess_fwd", "preprocess_fwd"),
-            ("tile_ranges", "ranges"), ("duplicate", "duplicate")]
+STAGE_OF = [("render_bwd", "render_bwd"), ("render_fwd", "render_fwd"), ("backward_views", "backward_views"), ("preprocess_bwd", "preprocess_bwd"),
+            ("preprocess_views", "preprocess_views"), ("preprocess_fwd", "preprocess_fwd")]
 
 rep, out = sys.argv[1], sys.argv[2]
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
