@@ -115,21 +115,28 @@ class ClockSampler:
 
 
 # stages whose roofline is HBM bandwidth; the two tile renderers are bound by instruction issue (FP32 / SFU / LSU slots)
-HBM_STAGES = ("preprocess_fwd", "depth_sort", "scan", "duplicate", "tile_sort", "ranges", "preprocess_bwd", "backward_views")
+HBM_STAGES = ("preprocess_fwd", "tile_plan", "depth_sort", "scan", "duplicate", "tile_sort", "ranges", "preprocess_bwd", "backward_views")
 
 
 def stage_bytes(name, P, V, N, X, M=16, views=1):
     """ALGORITHMIC bytes of one launch group (SURVEY.md §8(d) per-unit figures adapted to this library's
     data layout).  P Gaussians, V visible, N (tile, Gaussian) pairs, X pixels; per render unless stated."""
+    if views > 1 and name == "preprocess_fwd":
+        # view-batched geometry pass: parameters (44 B + the SH row) in once, per view radii / tile count / depth key out always and
+        # rect + clamp flags + the 48-byte record out if visible
+        return (44 + 12 * M) * P + views * (12 * P + 67 * V)
+    if views > 1 and name in ("depth_sort", "scan", "tile_plan"):
+        return views * stage_bytes(name, P, V, N, X, M, 1)
     return {
         "preprocess_fwd": 52 * P + (12 * M + 67) * V,                 # 44 in + 8 out always; SH row in + projected record out if visible
+        "tile_plan": 12 * P,                                           # tiles_touched + rect in (ranges and digit bases out: a few KB)
         "depth_sort": (4 + 4 * 16) * P,                                # histogram read + 4 passes x (key+value read, key+value write)
         "scan": 12 * P,                                                # order + tiles_touched in, offsets out
         "duplicate": 16 * P + 8 * N,                                   # order/offsets/rect in, tile key + Gaussian id out
         "tile_sort": (4 + 2 * 16) * N,                                 # (unfused fallback) histogram read + 2 passes x 16 B
-        # fused tile sort = duplicate + sort + ranges in one stage: order / offsets / rect in twice (tile plan, pair generation),
-        # pass 0 writes 2 B key + 4 B id per pair, pass 1 reads them and writes the 4 B id; ranges out
-        "tile_sort_fused": 24 * P + 16 * N,
+        # 16-bit tile sort = duplicate + the two radix passes in one stage: order / offsets / rect in, 6-byte pairs out (duplicate),
+        # in and out (pass 0), in (pass 1), 4-byte ids out (pass 1)
+        "tile_sort_fused": 16 * P + 28 * N,
         "ranges": 4 * N,                                               # sorted tile keys in (ranges out: 8 B per tile)
         "render_fwd": 52 * N + N + 24 * X,                             # id + gathered record per list entry, 8 flag bits out; colour 12 + depth 4 + final_T 4 + n_contrib 4 out
         "render_bwd": 52 * N + N + 20 * X + 96 * P,                    # id + record + flag bits in, dL_dpix/T/n in, accumulator zero fill + read-modify-write
@@ -500,12 +507,15 @@ def main():
     live = load_json("live_lanes.json").get(args.workload, {})
     traffic = load_json("ncu_traffic.json").get(args.workload, {})
     stages = {}
+    n_render = max(1, r["stage"]["render_fwd"][1])
+    views_per_launch = {}
     for name, (ms, n) in r["stage"].items():
         if n == 0:
             continue
         per = ms / n
-        e = {"ms": round(per, 4), "share": None, "bound": "hbm" if name in HBM_STAGES else "issue"}
-        b = stage_bytes("tile_sort_fused" if (name == "tile_sort" and r["stage"].get("duplicate", (0, 0))[1] == 0) else name, P, r["V"], N, X, views=VPS)
+        vpl = views_per_launch[name] = max(1, round(n_render / n))      # the view-batched stages run once per batch of views
+        e = {"ms": round(per, 4), "views_per_launch": vpl, "share": None, "bound": "hbm" if name in HBM_STAGES else "issue"}
+        b = stage_bytes("tile_sort_fused" if (name == "tile_sort" and r["stage"].get("duplicate", (0, 0))[1] == 0) else name, P, r["V"], N, X, views=vpl)
         if b:
             e.update(alg_bytes=b, gbs=round(b / per / 1e6, 1), frac_of_hbm=round(b / per / 1e6 / peak, 4))
         if name in ("render_fwd", "render_bwd") and pairs:
@@ -517,7 +527,7 @@ def main():
         if name in traffic:
             e["dram_traffic"] = traffic[name]
         stages[name] = e
-    per_view = {k: (1.0 / VPS if k == "backward_views" else 1.0) for k in stages}      # launches per rendered view
+    per_view = {k: 1.0 / views_per_launch[k] for k in stages}                           # launches per rendered view
     tot = sum(v["ms"] * per_view[k] for k, v in stages.items())
     for k, v in stages.items():
         v["share"] = round(v["ms"] * per_view[k] / tot, 4)
