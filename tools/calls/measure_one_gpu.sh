@@ -2,7 +2,7 @@
 # round 2: single-GPU measurement set of the current build (bench C3 / C2 / C4, reference arm, dist2, live lanes, ncu)
 cd "$GRAFT_REPO_ROOT" || exit 1
 mkdir -p gpurun_out
-T=${1:-v8}
+T=${1:-v9}
 timeout 300 python bench.py --steps 20 --warmup 3 > gpurun_out/bench_ours_$T.json 2> gpurun_out/bench_ours_$T.err; echo "bench rc=$?"
 timeout 200 python bench.py --impl reference --steps 5 --warmup 2 > gpurun_out/bench_reference_$T.json 2> gpurun_out/bench_ref_$T.err; echo "ref rc=$?"
 timeout 200 python bench.py --workload C2 --steps 20 --warmup 3 > gpurun_out/bench_c2_$T.json 2> gpurun_out/bench_c2_$T.err; echo "c2 rc=$?"

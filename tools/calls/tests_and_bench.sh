@@ -1,5 +1,5 @@
 #!/bin/bash
-# round 2, GPU call 5: full parity suite with the batched geometry pass, bench
+# full GPU parity suite, then the default bench line: gpurun --timeout 1500 -- "bash tools/calls/tests_and_bench.sh"
 cd "$GRAFT_REPO_ROOT" || exit 1
 mkdir -p gpurun_out
 timeout 1200 python -m pytest tests -m gpu -q > gpurun_out/c5_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/c5_pytest.log
