@@ -234,12 +234,23 @@ int rr_dist2(void* stream, int P, const float* points, float* out, void* ws, siz
 
 /* ---- stage-level entry points used by the parity tests ---- */
 /* stable ascending sort of (key,value) pairs on key bits [begin_bit,end_bit); result is written to keys_out/vals_out;
- * keys_in/vals_in are clobbered (they are the ping-pong partners).  vals_in == NULL sorts the identity 0..n-1. */
+ * keys_in/vals_in are clobbered (they are the ping-pong partners; vals_in must be a real buffer). */
 size_t rr_sort_ws_bytes(int64_t n, int key_bytes, int begin_bit, int end_bit);
 int rr_sort_pairs_u32(void* stream, int64_t n, uint32_t* keys_in, uint32_t* keys_out, uint32_t* vals_in, uint32_t* vals_out,
 	int begin_bit, int end_bit, void* ws);
 int rr_sort_pairs_u64(void* stream, int64_t n, uint64_t* keys_in, uint64_t* keys_out, uint32_t* vals_in, uint32_t* vals_out,
 	int begin_bit, int end_bit, void* ws);
+
+/* rr_sort_pairs_u32 for callers that cannot allocate device memory (code under CUDA graph capture, serving loops, harnesses
+ * that forbid cudaMalloc).  No counterpart in the reference.  Same sort, same
+ * arguments minus ws: the workspace is a 4.06 MiB array inside the library's device image (every GPU that loads the library
+ * holds it until exit), so n is limited to rr_sort_noalloc_max_pairs() = 4 194 304 pairs — a larger n is rejected with -1 and
+ * a message.  The call makes no cudaMalloc / cudaFree / allocating library call.  All calls on a device share the one array
+ * (each call clears the words it needs on its stream first): calls that overlap on the same GPU — two streams, two host
+ * threads — race; order them on one stream or with events.  vals_in must be a real buffer (it is a ping-pong partner). */
+size_t rr_sort_noalloc_max_pairs(void);
+int rr_sort_pairs_u32_noalloc(void* stream, int64_t n, uint32_t* keys_in, uint32_t* keys_out, uint32_t* vals_in, uint32_t* vals_out,
+	int begin_bit, int end_bit);
 
 /* byte offsets of the arrays inside the opaque blobs (for stage-wise diffing against the oracle / reference).
  * geom:    [0] rec f32[P,12]  [1] cov3D f32[P,6]  [2] clamped u8[P]  [3] tiles_touched u32[P]  [4] rect u32[P,2]

@@ -80,6 +80,8 @@ SIGNATURES = {
     "rr_sort_ws_bytes": (_sz, [_i64, _i, _i, _i]),
     "rr_sort_pairs_u32": (_i, [_vp, _i64, _vp, _vp, _vp, _vp, _i, _i, _vp]),
     "rr_sort_pairs_u64": (_i, [_vp, _i64, _vp, _vp, _vp, _vp, _i, _i, _vp]),
+    "rr_sort_noalloc_max_pairs": (_sz, []),
+    "rr_sort_pairs_u32_noalloc": (_i, [_vp, _i64, _vp, _vp, _vp, _vp, _i, _i]),
     "rr_geom_layout": (_i, [_i, _c.POINTER(_i64)]),
     "rr_binning_layout": (_i, [_i64, _i, _i, _c.POINTER(_i64)]),
     "rr_image_layout": (_i, [_i, _i, _c.POINTER(_i64)]),

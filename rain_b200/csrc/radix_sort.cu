@@ -418,3 +418,69 @@ template int sort_pairs<uint64_t>(cudaStream_t, uint64_t*, uint64_t*, uint32_t*,
 template int sort_pairs_segments<uint32_t>(cudaStream_t, int, uint32_t* const*, uint32_t* const*, uint32_t* const*, uint32_t* const*, size_t, int, int, void* const*, bool);
 
 }  // namespace rr
+
+// ---- rr_sort_pairs_u32_noalloc: the u32 pair sort with its workspace in a library-owned device array ----------------------
+// For callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc): the same kernels as
+// rr_sort_pairs_u32, handed a file-scope device array instead of a caller-supplied workspace.  The array's name is only a
+// host-side handle here: its device address is looked up once per device with cudaGetSymbolAddress (the device current at the
+// call) and that address is what the kernels get.  No cudaMalloc / cudaFree / allocating library call on this path.
+namespace rr {
+namespace {
+
+constexpr size_t NOALLOC_MAX_PAIRS = (size_t)1 << 22;                      // 4 194 304 pairs
+// histograms + tickets (MAX_PASSES x 256 words, padded) + one 256-word status row per 4096-key tile and pass (4 passes of a
+// 32-bit key): 4 MiB + 16 KiB, rounded up; sort_noalloc checks the real figure against sizeof at every call
+constexpr size_t NOALLOC_WS_BYTES = 4 * (NOALLOC_MAX_PAIRS / 4096) * RADIX * sizeof(uint32_t) + (64u << 10);
+static __device__ __align__(256) unsigned char g_noalloc_ws[NOALLOC_WS_BYTES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+void* g_noalloc_ptr[NOALLOC_MAX_DEVICES];       // device address of g_noalloc_ws on device i (null: not looked up yet)
+
+void* noalloc_ws_of_current_device()
+{
+	int dev = -1;
+	cudaError_t e = cudaGetDevice(&dev);
+	if (e != cudaSuccess) { set_error("sort_noalloc: cudaGetDevice: %s", cudaGetErrorString(e)); return nullptr; }
+	if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) { set_error("sort_noalloc: device %d (at most %d devices)", dev, NOALLOC_MAX_DEVICES); return nullptr; }
+	void* p = __atomic_load_n(&g_noalloc_ptr[dev], __ATOMIC_ACQUIRE);
+	if (p) return p;
+	e = cudaGetSymbolAddress(&p, g_noalloc_ws);           // this device's instance of the array; same answer from every thread
+	if (e != cudaSuccess || !p) { set_error("sort_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e)); return nullptr; }
+	__atomic_store_n(&g_noalloc_ptr[dev], p, __ATOMIC_RELEASE);
+	return p;
+}
+
+}  // namespace
+}  // namespace rr
+
+extern "C" size_t rr_sort_noalloc_max_pairs(void) { return rr::NOALLOC_MAX_PAIRS; }
+
+extern "C" int rr_sort_pairs_u32_noalloc(void* stream_, int64_t n, uint32_t* keys_in, uint32_t* keys_out, uint32_t* vals_in, uint32_t* vals_out,
+	int begin_bit, int end_bit)
+{
+	using namespace rr;
+	cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+	if (n < 0) { set_error("sort_noalloc: bad pair count %lld", (long long)n); return -1; }
+	if (n == 0) return 0;
+	if ((size_t)n > NOALLOC_MAX_PAIRS) {
+		set_error("sort_noalloc: %lld pairs exceed the %zu-pair limit of the built-in workspace (use rr_sort_pairs_u32 with your own)", (long long)n, NOALLOC_MAX_PAIRS);
+		return -1;
+	}
+	if (!keys_in || !keys_out || !vals_in || !vals_out) { set_error("sort_noalloc: keys_in, keys_out, vals_in and vals_out must not be null"); return -1; }
+	if (end_bit <= begin_bit || begin_bit < 0 || end_bit > 32) { set_error("sort_noalloc: bad bit range [%d,%d)", begin_bit, end_bit); return -1; }
+	if (sort_ws_bytes<uint32_t>((size_t)n, begin_bit, end_bit) > NOALLOC_WS_BYTES) {
+		set_error("sort_noalloc: workspace of %zu bytes exceeds the built-in %zu", sort_ws_bytes<uint32_t>((size_t)n, begin_bit, end_bit), NOALLOC_WS_BYTES);
+		return -1;
+	}
+	void* ws = noalloc_ws_of_current_device();
+	if (!ws) return -1;
+	// sort_pairs clears the histogram / ticket / status words of this call on the stream before its first kernel, so what the
+	// previous call left in the array does not matter
+	const int which = sort_pairs<uint32_t>(stream, keys_in, keys_out, vals_in, vals_out, (size_t)n, begin_bit, end_bit, ws, false);
+	if (which < 0) return -1;
+	if (which == 0) {
+		cudaMemcpyAsync(keys_out, keys_in, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToDevice, stream);
+		cudaMemcpyAsync(vals_out, vals_in, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToDevice, stream);
+	}
+	return check_launch("sort_pairs_noalloc", stream, false);
+}
