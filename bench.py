@@ -565,8 +565,8 @@ def main():
     }
     if world > 1:
         line["allreduce"] = {"impl": r["collective"], "ms_per_step": round(r["allreduce_ms"], 4), "bytes": r["bucket_bytes"],
-                             "note": "with the one-kernel all-reduce the reduction runs chunk by chunk beside the step's last backward pass; ms_per_step is only "
-                                     "what remains after it (the allreduce_bucket call itself)" if r["collective"].startswith("rr_") else "exposed: issued after the last backward pass",
+                             "note": (f"--overlap-chunks {args.overlap_chunks}: the reduction runs chunk by chunk beside the step's last backward pass; ms_per_step is "
+                                      "only what remains after it") if args.overlap_chunks else "exposed: issued after the step's last backward pass",
                              "bus_gbs": round(2 * (world - 1) / world * r["bucket_bytes"] / max(r["allreduce_ms"], 1e-9) / 1e6, 1)}
     if r["dropin"]:
         line["dropin"] = r["dropin"]

@@ -39,15 +39,31 @@ def ref_forward(ref, sc, cam, bg, **kw):
                        cam.height, cam.width, shs=sc.shs, sh_degree=sc.sh_degree, **kw)
 
 
-def check_against_ref(fw, g, ref, N_r, color_r, radii_r, depth_r, g_r, dpix=None):
+def oracle_grads_of(oracle, sc, cam, bg, dpix, **kw):
+    """the deterministic CPU oracle's gradients for the same inputs, computed only if asked for (check_against_ref)"""
+    def run():
+        c = lambda t: t.detach().cpu().numpy()
+        oracle.forward(c(bg), c(sc.means3D), c(sc.opacities), c(sc.scales), c(sc.rotations), c(cam.viewmatrix), c(cam.projmatrix), c(cam.campos),
+                       cam.tanfovx, cam.tanfovy, cam.height, cam.width, shs=c(sc.shs), sh_degree=sc.sh_degree, **kw)
+        return oracle.backward(c(dpix))
+    return run
+
+
+def check_against_ref(fw, g, ref, N_r, color_r, radii_r, depth_r, g_r, dpix=None, oracle_grads=None):
     """Integer outputs bit-exact, colour/depth 1e-5, gradients 1e-4 PLUS the reference's own run-to-run spread: its
     backward adds per pixel with unordered atomics, and on gradients with heavy cancellation (dL_drot, dL_dscale) two of
     its own runs differ by 1e-5 .. 3e-4 of max (tools/gpu_diag_bwd.py), so a fixed 1e-4 against ONE of its runs is a coin
-    flip there.  The spread is measured here from two more reference backward runs on the same state."""
+    flip there.  The spread is measured here from three more reference backward runs on the same state.
+    oracle_grads (optional, a callable): the spread of a few runs does not show the part of the reference's rounding error
+    that repeats from run to run (its atomics arrive in much the same order every time: on the dense-tile case its dL_dcov3D
+    sits 1e-5 from the deterministic oracle while two of its runs differ by 2e-6, and dL_drot amplifies that tenfold —
+    tools/gpu_diag_bwd.py).  A gradient that misses the reference run by more than the tolerance must then be within a plain
+    1e-4 of the ORACLE, the deterministic restatement of the same algorithm; without oracle_grads it fails."""
     st = ref.state()
     spread = {}
+    g_o = None
     if g is not None and dpix is not None:
-        again = [ref.backward(dpix) for _ in range(2)]
+        again = [ref.backward(dpix) for _ in range(3)]
         spread = {k: max(rel_err(x[k], g_r[k])[0] for x in again) for k in GRAD_KEYS}
     assert eq(fw["radii"], radii_r)
     if TILE_CULL:
@@ -77,6 +93,11 @@ def check_against_ref(fw, g, ref, N_r, color_r, radii_r, depth_r, g_r, dpix=None
     if g is not None:
         for k in GRAD_KEYS:
             err = rel_err(g[k], g_r[k])[0]
+            if err > RTOL_GRAD + 2.0 * spread.get(k, 0.0) and oracle_grads is not None:
+                g_o = g_o if g_o is not None else oracle_grads()
+                err_o = rel_err(g[k], g_o[k].reshape(g[k].shape))[0]
+                assert err_o <= RTOL_GRAD, f"{k}: {err:.3e} vs the reference run (its spread {spread.get(k, 0.0):.3e}) and {err_o:.3e} vs the oracle"
+                continue
             assert err <= RTOL_GRAD + 2.0 * spread.get(k, 0.0), f"{k}: {err:.3e} vs the reference run; the reference's own run-to-run spread here is {spread.get(k, 0.0):.3e}"
         a = g["dL_dconic"].reshape(-1, 4)[:, [0, 1, 3]]; b = g_r["dL_dconic"].reshape(-1, 4)[:, [0, 1, 3]]
         assert rel_err(a, b)[0] <= RTOL_GRAD
@@ -111,7 +132,7 @@ def test_configs_match_reference_cuda(device, refcuda, name):
     (6000, 90, 41, 2, 8, 2, (0.0, 0.0, 0.0), 0.3, 1.0, 3.0),          # H % 16 == 9: one pixel row of the lower 8x8 blocks is inside
     (30000, 72, 36, 1, 9, 0, (0.3, 0.3, 0.3), 0.3, 1.0, 5.0),         # H % 16 == 4 with long, early-saturating lists (flag words of a half that stops early)
 ])
-def test_shapes_and_settings_match_reference_cuda(device, refcuda, P, W, H, D, seed, view, bgc, low_pass, smod, smult):
+def test_shapes_and_settings_match_reference_cuda(device, refcuda, oracle, P, W, H, D, seed, view, bgc, low_pass, smod, smult):
     sc = make_scene(P, D, seed, smult).to(device); cam = make_camera(view, 4, W, H).to(device)
     if P == 1:
         sc.means3D.zero_()
@@ -120,7 +141,8 @@ def test_shapes_and_settings_match_reference_cuda(device, refcuda, P, W, H, D, s
     g = mine_backward(fw, sc, cam, bg, dpix)
     N_r, color_r, radii_r, depth_r = ref_forward(refcuda, sc, cam, bg, low_pass=low_pass, scale_modifier=smod)
     g_r = refcuda.backward(dpix)
-    check_against_ref(fw, g, refcuda, N_r, color_r, radii_r, depth_r, g_r, dpix)
+    check_against_ref(fw, g, refcuda, N_r, color_r, radii_r, depth_r, g_r, dpix,
+                      oracle_grads=oracle_grads_of(oracle, sc, cam, bg, dpix, low_pass=low_pass, scale_modifier=smod))
 
 
 @pytest.mark.parametrize("P,W,H,opaque", [(200_000, 40, 24, True), (200_000, 40, 24, False), (60_000, 33, 50, True), (700, 40, 24, True),
