@@ -56,9 +56,9 @@ template <class K> struct SegPtrs {
 // Lanes of the warp holding the same digit as this lane, built from one ballot per digit bit.  (match.any does this
 // in one instruction, but on sm_100a it is a slow MIO-queue operation: the first version of this kernel spent 58 % of
 // its stall samples waiting on MATCH results — profiles/r01_v0_ncu_full_summary.csv — whereas VOTE + LOP3 pipeline.)
-__device__ __forceinline__ unsigned same_digit_lanes(uint32_t d, bool valid, int nbits)
+__device__ __forceinline__ unsigned same_digit_lanes(uint32_t d, int nbits)
 {
-	unsigned peers = __ballot_sync(FULL, valid);
+	unsigned peers = FULL;
 	#pragma unroll
 	for (int b = 0; b < RADIX_BITS; b++) {
 		if (b < nbits) {
@@ -130,6 +130,10 @@ __global__ void __launch_bounds__(RADIX) digit_base_kernel(SegPtrs<K> sp)
 }
 
 // ---- 3. one onesweep pass ---------------------------------------------------------------------------------------
+// The kernel is bound by instruction issue, not by HBM (ncu: 65 % issue-active at 11 % of the DRAM rate), so it is written
+// for a short instruction stream: no per-item validity tests (a partial tile — only the last one — is padded with all-ones
+// keys, which rank behind every real key of the highest digit and are dropped at the scatter), digit and rank packed into one
+// register per item, one shared-memory table lookup per item at the reorder.
 template <class K, int IPT, bool MATCH_OR>
 __global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp, int pass, bool iota_vals, bool write_keys, uint32_t n, uint32_t ntiles, int shift, uint32_t mask)
 {
@@ -144,25 +148,34 @@ __global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp
 	volatile uint32_t* __restrict__ status = sp.status[seg] + (size_t)pass * ntiles * RADIX;      // [ntiles][RADIX]
 	constexpr int TILE = SORT_THREADS * IPT;
 	constexpr int WARP_ITEMS = 32 * IPT;
+	constexpr int MATCH_WORDS = 2 * SORT_WARPS * RADIX;      // two digit -> lane-mask tables per warp (even / odd items)
 	__shared__ uint32_t s_tile;
-	__shared__ uint32_t s_whist[SORT_WARPS][RADIX];
-	__shared__ uint32_t s_dstart[RADIX];
+	__shared__ __align__(16) uint32_t s_whist[SORT_WARPS * RADIX];   // ranking: per-warp digit counts; afterwards: tile-local start of (warp, digit)
 	__shared__ uint32_t s_goff[RADIX];
 	__shared__ uint32_t s_wtot[SORT_WARPS];
-	__shared__ __align__(16) K s_keys[TILE];          // also viewed as 32-bit words (match table)
-	__shared__ __align__(16) uint32_t s_vals[TILE];
+	// the tile's keys, then its values, in tile-local sorted order; during the ranking the match tables live here
+	__shared__ __align__(16) unsigned char s_buf[TILE * (sizeof(K) + sizeof(uint32_t))];
+	static_assert(sizeof(s_buf) >= sizeof(uint32_t) * MATCH_WORDS, "the match tables do not fit into the reorder buffer");
+	K* const s_keys = reinterpret_cast<K*>(s_buf);
+	uint32_t* const s_vals = reinterpret_cast<uint32_t*>(s_buf + TILE * sizeof(K));
 
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-	const int nbits = __popc(mask);
-	// per-warp digit -> lane-mask table of the atomicOr ranking; aliases s_keys (the ranking is over before the reorder)
-	uint32_t* s_match = reinterpret_cast<uint32_t*>(s_keys) + warp * RADIX;
-	static_assert(sizeof(K) * TILE >= sizeof(uint32_t) * SORT_WARPS * RADIX, "s_match does not fit into s_keys");
 	if (tid == 0) s_tile = atomicAdd(ticket, 1u);
-	for (int i = tid; i < SORT_WARPS * RADIX; i += SORT_THREADS) { (&s_whist[0][0])[i] = 0; if (MATCH_OR) reinterpret_cast<uint32_t*>(s_keys)[i] = 0; }
+	{
+		const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+		#pragma unroll
+		for (int i = tid; i < SORT_WARPS * RADIX / 4; i += SORT_THREADS) reinterpret_cast<uint4*>(s_whist)[i] = z;
+		if (MATCH_OR) {
+			#pragma unroll
+			for (int i = tid; i < MATCH_WORDS / 4; i += SORT_THREADS) reinterpret_cast<uint4*>(s_buf)[i] = z;
+		}
+	}
 	__syncthreads();
 	const uint32_t tile = s_tile;
 	const uint32_t tile_base = tile * (uint32_t)TILE;
 	const uint32_t tile_count = min((uint32_t)TILE, n - tile_base);
+	const bool full = tile_count == (uint32_t)TILE;
+	const uint32_t my0 = (uint32_t)(warp * WARP_ITEMS + lane);       // tile-local index of this lane's item 0; item k is 32 k further
 
 	// the values are only fetched after the ranking (registers); pull their lines into L2 now (one 128-byte line per thread)
 	if (vals_in) {
@@ -171,43 +184,62 @@ __global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp
 	}
 	// load (warp-striped: item k of lane l of warp w sits at w*WARP_ITEMS + k*32 + l, i.e. memory order within the warp)
 	K key[IPT];
-	uint32_t pos[IPT];
-	#pragma unroll
-	for (int k = 0; k < IPT; k++) {
-		const uint32_t li = warp * WARP_ITEMS + k * 32 + lane;
-		key[k] = (li < tile_count) ? keys_in[tile_base + li] : (K)0;
-	}
-	// per-warp stable ranking
-	#pragma unroll
-	for (int k = 0; k < IPT; k++) {
-		const uint32_t li = warp * WARP_ITEMS + k * 32 + lane;
-		const bool valid = li < tile_count;
-		const uint32_t d = valid ? digit_of(key[k], shift, mask) : 0u;
-		unsigned peers;
-		if (MATCH_OR) {
-			// lanes holding the same digit meet in one shared word (atomicOr of the lane bit); its first lane clears it again
-			if (valid) atomicOr(&s_match[d], 1u << lane);
-			__syncwarp();
-			peers = valid ? s_match[d] : 0u;
-			__syncwarp();
+	{
+		const K* __restrict__ kin = keys_in + tile_base + my0;
+		if (full) {
+			#pragma unroll
+			for (int k = 0; k < IPT; k++) key[k] = kin[k * 32];
 		} else {
-			peers = same_digit_lanes(d, valid, nbits);
+			#pragma unroll
+			for (int k = 0; k < IPT; k++) key[k] = (my0 + k * 32 < tile_count) ? kin[k * 32] : (K) ~(K)0;
 		}
-		const int leader = valid ? __ffs(peers) - 1 : lane;
-		uint32_t old = 0;
-		if (valid && lane == leader) { if (MATCH_OR) s_match[d] = 0; old = s_whist[warp][d]; s_whist[warp][d] = old + __popc(peers); }
-		__syncwarp();
-		old = __shfl_sync(FULL, old, leader);
-		pos[k] = old + __popc(peers & lanemask_lt());
+	}
+	// per-warp stable ranking: pd[k] = (digit << 16) | rank of the item among the warp's items of the same digit
+	uint32_t pd[IPT];
+	{
+		uint32_t* const wh = s_whist + warp * RADIX;
+		const uint32_t lt = lanemask_lt();
+		if (MATCH_OR) {
+			// lanes holding the same digit meet in one shared word (atomicOr of the lane bit).  Items alternate between two
+			// tables, so the word an item's first lane clears is not one the next item's lanes are setting bits in.
+			uint32_t* const t0 = reinterpret_cast<uint32_t*>(s_buf) + warp * RADIX;
+			const uint32_t lanebit = 1u << lane;
+			#pragma unroll
+			for (int k = 0; k < IPT; k++) {
+				const uint32_t d = digit_of(key[k], shift, mask);
+				uint32_t* const t = t0 + (k & 1) * (SORT_WARPS * RADIX);
+				atomicOr(&t[d], lanebit);
+				__syncwarp();
+				const uint32_t peers = t[d], old = wh[d];
+				__syncwarp();
+				const uint32_t below = peers & lt;
+				if (below == 0) { t[d] = 0; wh[d] = old + __popc(peers); }       // the first lane of the group
+				pd[k] = (old + __popc(below)) | (d << 16);
+			}
+		} else {
+			const int nbits = __popc(mask);
+			#pragma unroll
+			for (int k = 0; k < IPT; k++) {
+				const uint32_t d = digit_of(key[k], shift, mask);
+				const uint32_t peers = same_digit_lanes(d, nbits);
+				const uint32_t old = wh[d];
+				__syncwarp();
+				const uint32_t below = peers & lt;
+				if (below == 0) wh[d] = old + __popc(peers);
+				__syncwarp();
+				pd[k] = (old + __popc(below)) | (d << 16);
+			}
+		}
 	}
 	__syncthreads();
 
-	// thread d owns digit d: warp-exclusive offsets, tile count, look-back
+	// thread d owns digit d: tile count, look-back, tile-local start of every (warp, digit) group
 	{
 		const int d = tid;
+		uint32_t cnt[SORT_WARPS];
 		uint32_t sum = 0;
 		#pragma unroll
-		for (int w = 0; w < SORT_WARPS; w++) { const uint32_t t = s_whist[w][d]; s_whist[w][d] = sum; sum += t; }
+		for (int w = 0; w < SORT_WARPS; w++) { cnt[w] = s_whist[w * RADIX + d]; sum += cnt[w]; }
 		status[(size_t)tile * RADIX + d] = sum | (tile == 0 ? FLAG_INC : FLAG_AGG);
 		// exclusive scan of the tile's digit counts -> start of each digit in tile-local sorted order
 		uint32_t inc = sum;
@@ -218,7 +250,11 @@ __global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp
 		uint32_t pre = 0;
 		for (int w = 0; w < warp; w++) pre += s_wtot[w];
 		const uint32_t dstart = pre + inc - sum;
-		s_dstart[d] = dstart;
+		{
+			uint32_t run = dstart;
+			#pragma unroll
+			for (int w = 0; w < SORT_WARPS; w++) { s_whist[w * RADIX + d] = run; run += cnt[w]; }
+		}
 		// decoupled look-back, LB predecessors per round: the status words of a round are loaded with independent loads
 		// (one L2 round trip per round instead of one per predecessor — a tile of the first wave has to walk over every
 		// tile in flight, ~3 per SM), then consumed in order; the walk restarts at the first word not yet published.
@@ -247,34 +283,54 @@ __global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp
 	}
 	__syncthreads();
 
-	// values are fetched only now so they do not occupy registers during the ranking
-	uint32_t val[IPT];
-	#pragma unroll
-	for (int k = 0; k < IPT; k++) {
-		const uint32_t li = warp * WARP_ITEMS + k * 32 + lane;
-		val[k] = 0;
-		if (li < tile_count) val[k] = vals_in ? vals_in[tile_base + li] : tile_base + li;
-	}
-	// reorder through shared memory into tile-local sorted order
-	#pragma unroll
-	for (int k = 0; k < IPT; k++) {
-		const uint32_t li = warp * WARP_ITEMS + k * 32 + lane;
-		if (li < tile_count) {
-			const uint32_t d = digit_of(key[k], shift, mask);
-			const uint32_t p = s_dstart[d] + s_whist[warp][d] + pos[k];
+	// reorder through shared memory into tile-local sorted order: keys first (their registers are free afterwards), then the
+	// values, which are fetched only now
+	{
+		const uint32_t* const wh = s_whist + warp * RADIX;
+		#pragma unroll
+		for (int k = 0; k < IPT; k++) {
+			const uint32_t p = wh[pd[k] >> 16] + (pd[k] & 0xffffu);
+			pd[k] = p;
 			s_keys[p] = key[k];
-			s_vals[p] = val[k];
 		}
+		uint32_t val[IPT];
+		if (vals_in) {
+			const uint32_t* __restrict__ vin = vals_in + tile_base + my0;
+			if (full) {
+				#pragma unroll
+				for (int k = 0; k < IPT; k++) val[k] = vin[k * 32];
+			} else {
+				#pragma unroll
+				for (int k = 0; k < IPT; k++) val[k] = (my0 + k * 32 < tile_count) ? vin[k * 32] : 0u;
+			}
+		} else {
+			#pragma unroll
+			for (int k = 0; k < IPT; k++) val[k] = tile_base + my0 + k * 32;
+		}
+		#pragma unroll
+		for (int k = 0; k < IPT; k++) s_vals[pd[k]] = val[k];
 	}
 	__syncthreads();
-	#pragma unroll
-	for (int k = 0; k < IPT; k++) {
-		const uint32_t p = k * SORT_THREADS + tid;
-		if (p < tile_count) {
+	// scatter: consecutive threads hold consecutive items of the sorted tile, so every digit's run is written contiguously
+	if (full) {
+		#pragma unroll
+		for (int k = 0; k < IPT; k++) {
+			const uint32_t p = k * SORT_THREADS + tid;
 			const K kk = s_keys[p];
 			const uint32_t g = s_goff[digit_of(kk, shift, mask)] + p;
 			if (write_keys) keys_out[g] = kk;
 			vals_out[g] = s_vals[p];
+		}
+	} else {
+		#pragma unroll
+		for (int k = 0; k < IPT; k++) {
+			const uint32_t p = k * SORT_THREADS + tid;
+			if (p < tile_count) {
+				const K kk = s_keys[p];
+				const uint32_t g = s_goff[digit_of(kk, shift, mask)] + p;
+				if (write_keys) keys_out[g] = kk;
+				vals_out[g] = s_vals[p];
+			}
 		}
 	}
 }
