@@ -233,11 +233,13 @@ __global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp
 	}
 	__syncthreads();
 
-	// thread d owns digit d: tile count, look-back, tile-local start of every (warp, digit) group
+	// thread d owns digit d: the tile's digit count is published at once (AGG), the tile-local start of every (warp, digit)
+	// group follows from a block scan.  The look-back itself comes only after the reorder below, which does not need it: by
+	// then the tiles just ahead of this one have published their counts too, so it polls less.
+	const int d = tid;
+	uint32_t sum = 0, dstart;
 	{
-		const int d = tid;
 		uint32_t cnt[SORT_WARPS];
-		uint32_t sum = 0;
 		#pragma unroll
 		for (int w = 0; w < SORT_WARPS; w++) { cnt[w] = s_whist[w * RADIX + d]; sum += cnt[w]; }
 		status[(size_t)tile * RADIX + d] = sum | (tile == 0 ? FLAG_INC : FLAG_AGG);
@@ -249,37 +251,10 @@ __global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp
 		__syncthreads();
 		uint32_t pre = 0;
 		for (int w = 0; w < warp; w++) pre += s_wtot[w];
-		const uint32_t dstart = pre + inc - sum;
-		{
-			uint32_t run = dstart;
-			#pragma unroll
-			for (int w = 0; w < SORT_WARPS; w++) { s_whist[w * RADIX + d] = run; run += cnt[w]; }
-		}
-		// decoupled look-back, LB predecessors per round: the status words of a round are loaded with independent loads
-		// (one L2 round trip per round instead of one per predecessor — a tile of the first wave has to walk over every
-		// tile in flight, ~3 per SM), then consumed in order; the walk restarts at the first word not yet published.
-		uint32_t excl = 0;
-		if (tile > 0) {
-			constexpr int LB = 8;
-			int64_t t = (int64_t)tile - 1;
-			bool found = false;
-			while (!found) {
-				uint32_t v[LB];
-				#pragma unroll
-				for (int j = 0; j < LB; j++) { v[j] = 2u << FLAG_SHIFT; if (t - j >= 0) v[j] = status[(size_t)(t - j) * RADIX + d]; }   // before tile 0: inclusive 0
-				#pragma unroll
-				for (int j = 0; j < LB; j++) {
-					if (found) break;
-					const uint32_t f = v[j] >> FLAG_SHIFT;
-					if (f == 0) { t -= j; break; }          // not published yet: retry from here
-					excl += v[j] & VALUE_MASK;
-					if (f == 2) found = true;
-					else if (j == LB - 1) t -= LB;
-				}
-			}
-			status[(size_t)tile * RADIX + d] = (excl + sum) | FLAG_INC;
-		}
-		s_goff[d] = digit_base[d] + excl - dstart;
+		dstart = pre + inc - sum;
+		uint32_t run = dstart;
+		#pragma unroll
+		for (int w = 0; w < SORT_WARPS; w++) { s_whist[w * RADIX + d] = run; run += cnt[w]; }
 	}
 	__syncthreads();
 
@@ -309,6 +284,37 @@ __global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp
 		}
 		#pragma unroll
 		for (int k = 0; k < IPT; k++) s_vals[pd[k]] = val[k];
+	}
+	// decoupled look-back, LB predecessors per round: the status words of a round are loaded with independent loads (one L2
+	// round trip per round instead of one per predecessor), then consumed in order; at a word that is not published yet the
+	// thread polls that one word (with a pause, so that it does not take issue slots from the warps it waits for) and
+	// resumes from there.
+	{
+		uint32_t excl = 0;
+		if (tile > 0) {
+			constexpr int LB = 8;
+			int64_t t = (int64_t)tile - 1;
+			bool found = false;
+			while (!found) {
+				uint32_t v[LB];
+				#pragma unroll
+				for (int j = 0; j < LB; j++) { v[j] = 2u << FLAG_SHIFT; if (t - j >= 0) v[j] = status[(size_t)(t - j) * RADIX + d]; }   // before tile 0: inclusive 0
+				int used = LB;
+				#pragma unroll
+				for (int j = 0; j < LB; j++) {
+					const uint32_t f = v[j] >> FLAG_SHIFT;
+					if (f == 0) { used = j; break; }
+					excl += v[j] & VALUE_MASK;
+					if (f == 2) { found = true; break; }
+				}
+				t -= used;
+				if (!found && used < LB) {
+					while ((status[(size_t)t * RADIX + d] >> FLAG_SHIFT) == 0) __nanosleep(100);
+				}
+			}
+			status[(size_t)tile * RADIX + d] = (excl + sum) | FLAG_INC;
+		}
+		s_goff[d] = digit_base[d] + excl - dstart;
 	}
 	__syncthreads();
 	// scatter: consecutive threads hold consecutive items of the sorted tile, so every digit's run is written contiguously
