@@ -84,7 +84,7 @@ class ClockSampler:
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.ready = index, [], None, threading.Event()
 
     def start(self):
         try:
@@ -98,6 +98,12 @@ class ClockSampler:
     def _read(self):
         for line in self.proc.stdout:
             self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
+            self.ready.set()
+
+    def wait_ready(self, timeout=5.0):
+        """returns once the first sample has arrived (nvidia-smi is up and polling)"""
+        if self.proc is not None:
+            self.ready.wait(timeout)
 
     def stop(self, t0, t1):
         if self.proc is None:
@@ -221,12 +227,16 @@ def run_ours(args, rank, world, local):
             mv.allreduce_bucket(bucket)
         return res
 
-    for s in range(args.warmup):
-        step_resident(s)
+    # the clock sampler (an nvidia-smi process polling every 50 ms) is started before the warm-up: its start-up (process launch,
+    # NVML initialisation) would otherwise fall into the first timed steps and stall them; only the samples taken inside the
+    # timed region [t0, t1] are used
     sampler = ClockSampler(local)
-    barrier_sync(world)
     if rank == 0:
         sampler.start()
+        sampler.wait_ready()
+    for s in range(args.warmup):
+        step_resident(s)
+    barrier_sync(world)
     launches0 = lib.rr_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.time()

@@ -108,9 +108,8 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_chained_kernel(int P, int n
 // One warp emits the duplicates of 32 consecutive depth-sorted Gaussians cooperatively: output slot s of the warp's
 // contiguous span is owned by the last lane whose exclusive offset is <= s (binary search over 32 shared values),
 // so writes are coalesced and a large splat does not serialise on one thread (reference: one thread per rect).
-template <class K>
 __global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ offsets,
-	const uint2* __restrict__ rect, const unsigned long long* __restrict__ tile_mask, int grid_x, K* __restrict__ tile_keys,
+	const uint2* __restrict__ rect, const unsigned long long* __restrict__ tile_mask, int grid_x, uint32_t* __restrict__ tile_keys,
 	uint32_t* __restrict__ gaussian_ids)
 {
 	__shared__ unsigned long long s_mask[8][32];
@@ -167,8 +166,66 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* _
 		const uint32_t xw = s_xw[warp][lo];
 		const uint32_t w = xw >> 16, xx0 = xw & 0xffffu;
 		const uint32_t ry = local / w, rx = local - ry * w;
-		tile_keys[base + s] = (K)((s_y0[warp][lo] + ry) * (uint32_t)grid_x + xx0 + rx);
+		tile_keys[base + s] = (s_y0[warp][lo] + ry) * (uint32_t)grid_x + xx0 + rx;
 		gaussian_ids[base + s] = s_g[warp][lo];        // the sort's value, as in the reference (rasterizer_impl.cu:92)
+	}
+}
+
+// The pair emission of the 16-bit tile sort (radix_sort.cu::tile_sort16; no tile masks on that path), written for a short
+// instruction stream — the kernel is bound by instruction issue, its 6 bytes per pair are far from the HBM rate.  A warp
+// takes 32 Gaussians of the depth order, keeps those that touch tiles, and emits their pairs 32 at a time:
+//  * which Gaussian owns output slot s is found without a search: every Gaussian whose first pair falls into the current
+//    32 slots sets the bit of that slot (one redux.or over the warp); the owner of slot l is then (Gaussians started before
+//    the window) + popc(bits up to l) - 1;
+//  * tile y / x inside the rect without a division per pair: local / width = umulhi(local, ceil(2^32 / width)), exact for
+//    local, width < 2^16 (tile ids are 16-bit on this path); one division per Gaussian.
+__global__ void __launch_bounds__(256) duplicate16_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ offsets,
+	const uint2* __restrict__ rect, int grid_x, uint16_t* __restrict__ tile_keys, uint32_t* __restrict__ gaussian_ids)
+{
+	__shared__ uint4 s_a[8][32];       // { first pair (relative to the warp's first), Gaussian, x0 | y0 << 16, ceil(2^32 / width) (0: width 1) }
+	__shared__ uint32_t s_w[8][32];    // rect width in tiles
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const int i = blockIdx.x * 256 + threadIdx.x;
+	uint32_t g = 0, excl = 0, incl = 0;
+	if (i < P) {
+		g = order[i];
+		incl = offsets[i];
+		excl = i == 0 ? 0u : offsets[i - 1];
+	}
+	const int last_valid = min(31, P - 1 - (blockIdx.x * 256 + warp * 32));   // >= 0 for any warp that has work
+	if (last_valid < 0) return;                                                 // warp-uniform
+	const uint32_t base = __shfl_sync(FULL, excl, 0);
+	const uint32_t total = __shfl_sync(FULL, incl, last_valid) - base;
+	const bool touches = i < P && incl > excl;
+	const unsigned has = __ballot_sync(FULL, touches);
+	if (touches) {
+		const uint2 r = rect[g];
+		const uint32_t x0 = r.x & 0xffffu, w = (r.x >> 16) - x0, y0 = r.y & 0xffffu;
+		const int slot = __popc(has & lanemask_lt());
+		s_a[warp][slot] = make_uint4(excl - base, g, x0 | (y0 << 16), 0xffffffffu / w + 1u);       // (w == 1 wraps to 0)
+		s_w[warp][slot] = w;
+	}
+	__syncwarp();
+	const uint32_t my_start = lane < __popc(has) ? s_a[warp][lane].x : 0xffffffffu;
+	const uint32_t le = 0xffffffffu >> (31 - lane);                             // lanes up to and including mine
+	uint16_t* __restrict__ kout = tile_keys + base;
+	uint32_t* __restrict__ vout = gaussian_ids + base;
+	uint32_t started = 0;                                                        // Gaussians whose first pair lies before the window
+	for (uint32_t s0 = 0; s0 < total; s0 += 32) {
+		const uint32_t rel = my_start - s0;                                      // (wraps to a huge value for a start before the window)
+		const uint32_t starts = __reduce_or_sync(FULL, rel < 32u ? 1u << rel : 0u);
+		const uint32_t s = s0 + lane;
+		const uint32_t lo = started + __popc(starts & le) - 1u;
+		started += __popc(starts);
+		if (s < total) {
+			const uint4 a = s_a[warp][lo];
+			const uint32_t w = s_w[warp][lo];
+			const uint32_t local = s - a.x;
+			const uint32_t ry = a.w ? __umulhi(local, a.w) : local;
+			const uint32_t rx = local - ry * w;
+			kout[s] = (uint16_t)(((a.z >> 16) + ry) * (uint32_t)grid_x + (a.z & 0xffffu) + rx);
+			vout[s] = a.y;                                                       // the sort's value, as in the reference (rasterizer_impl.cu:92)
+		}
 	}
 }
 
@@ -345,14 +402,14 @@ int launch_duplicate(cudaStream_t stream, int P, const uint32_t* order, const ui
 	int grid_x, uint32_t* tile_keys, uint32_t* gaussian_ids)
 {
 	if (P == 0) return 0;
-	count_launch(), duplicate_kernel<uint32_t><<<(P + 255) / 256, 256, 0, stream>>>(P, order, offsets, rect, tile_mask, grid_x, tile_keys, gaussian_ids);
+	count_launch(), duplicate_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, order, offsets, rect, tile_mask, grid_x, tile_keys, gaussian_ids);
 	return check_launch("duplicate", stream, false);
 }
 
 int launch_duplicate16(cudaStream_t stream, int P, const uint32_t* order, const uint32_t* offsets, const uint2* rect, int grid_x, uint16_t* tile_keys, uint32_t* gaussian_ids)
 {
 	if (P == 0) return 0;
-	count_launch(), duplicate_kernel<uint16_t><<<(P + 255) / 256, 256, 0, stream>>>(P, order, offsets, rect, nullptr, grid_x, tile_keys, gaussian_ids);
+	count_launch(), duplicate16_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, order, offsets, rect, grid_x, tile_keys, gaussian_ids);
 	return check_launch("duplicate", stream, false);
 }
 

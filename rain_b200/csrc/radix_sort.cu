@@ -5,11 +5,11 @@
 //   1. one histogram kernel builds the 256-bin digit histograms of ALL passes in a single read of the keys;
 //   2. a tiny kernel turns them into exclusive digit bases;
 //   3. one kernel per 8-bit pass ("onesweep"): every CTA takes a tile of keys (tile ids are handed out by an atomic
-//      ticket so a CTA's predecessors are always already running), ranks its keys per warp with
-//      __match_any_sync + popc (stable: items are visited in memory order), combines the warp histograms,
-//      resolves its global digit offsets by DECOUPLED LOOK-BACK over per-tile status words (aggregate / inclusive
-//      flags in the top two bits), reorders the tile through shared memory so the global scatter is written in runs,
-//      and writes keys and values to the other buffer.
+//      ticket so a CTA's predecessors are always already running), ranks its keys per warp (lanes with the same digit
+//      meet in a shared-memory word through atomicOr; stable: items are visited in memory order), combines the warp
+//      histograms, reorders the tile through shared memory so the global scatter is written in runs, resolves its
+//      global digit offsets by DECOUPLED LOOK-BACK over per-tile status words (aggregate / inclusive flags in the top
+//      two bits), and writes keys and values to the other buffer.
 // Memory traffic per pass: read 1x + write 1x of (key,value); histogram: read keys once.
 #include <cstring>
 #include "common.cuh"
@@ -22,6 +22,12 @@ namespace {
 
 #ifndef SORT_BALANCED_DIGITS
 #define SORT_BALANCED_DIGITS 1
+#endif
+#ifndef SORT_LOOKBACK
+#define SORT_LOOKBACK 8         // status words a look-back round loads at once
+#endif
+#ifndef SORT_MIN_CTAS
+#define SORT_MIN_CTAS 4         // resident CTAs per SM the onesweep pass is compiled for (registers: 64 at 4)
 #endif
 constexpr int RADIX_BITS = 8;
 constexpr int RADIX = 1 << RADIX_BITS;
@@ -52,23 +58,6 @@ template <class K> struct SegPtrs {
 	uint32_t* vals_a[SORT_MAX_SEGS]; uint32_t* vals_b[SORT_MAX_SEGS];
 	uint32_t* ghist[SORT_MAX_SEGS]; uint32_t* tickets[SORT_MAX_SEGS]; uint32_t* status[SORT_MAX_SEGS];
 };
-
-// Lanes of the warp holding the same digit as this lane, built from one ballot per digit bit.  (match.any does this
-// in one instruction, but on sm_100a it is a slow MIO-queue operation: the first version of this kernel spent 58 % of
-// its stall samples waiting on MATCH results — profiles/r01_v0_ncu_full_summary.csv — whereas VOTE + LOP3 pipeline.)
-__device__ __forceinline__ unsigned same_digit_lanes(uint32_t d, int nbits)
-{
-	unsigned peers = FULL;
-	#pragma unroll
-	for (int b = 0; b < RADIX_BITS; b++) {
-		if (b < nbits) {
-			const bool bit = (d >> b) & 1u;
-			const unsigned bal = __ballot_sync(FULL, bit);
-			peers &= bit ? bal : ~bal;
-		}
-	}
-	return peers;
-}
 
 // ---- 1. histograms of all passes ------------------------------------------------------------------------------
 template <class K>
@@ -134,8 +123,8 @@ __global__ void __launch_bounds__(RADIX) digit_base_kernel(SegPtrs<K> sp)
 // for a short instruction stream: no per-item validity tests (a partial tile — only the last one — is padded with all-ones
 // keys, which rank behind every real key of the highest digit and are dropped at the scatter), digit and rank packed into one
 // register per item, one shared-memory table lookup per item at the reorder.
-template <class K, int IPT, bool MATCH_OR>
-__global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp, int pass, bool iota_vals, bool write_keys, uint32_t n, uint32_t ntiles, int shift, uint32_t mask)
+template <class K, int IPT>
+__global__ void __launch_bounds__(SORT_THREADS, SORT_MIN_CTAS) onesweep_kernel(SegPtrs<K> sp, int pass, bool iota_vals, bool write_keys, uint32_t n, uint32_t ntiles, int shift, uint32_t mask)
 {
 	// this segment's buffers: even passes read the *_a buffers and write *_b, odd passes the other way round
 	const int seg = blockIdx.y;
@@ -165,10 +154,8 @@ __global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp
 		const uint4 z = make_uint4(0u, 0u, 0u, 0u);
 		#pragma unroll
 		for (int i = tid; i < SORT_WARPS * RADIX / 4; i += SORT_THREADS) reinterpret_cast<uint4*>(s_whist)[i] = z;
-		if (MATCH_OR) {
-			#pragma unroll
-			for (int i = tid; i < MATCH_WORDS / 4; i += SORT_THREADS) reinterpret_cast<uint4*>(s_buf)[i] = z;
-		}
+		#pragma unroll
+		for (int i = tid; i < MATCH_WORDS / 4; i += SORT_THREADS) reinterpret_cast<uint4*>(s_buf)[i] = z;
 	}
 	__syncthreads();
 	const uint32_t tile = s_tile;
@@ -199,36 +186,23 @@ __global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp
 	{
 		uint32_t* const wh = s_whist + warp * RADIX;
 		const uint32_t lt = lanemask_lt();
-		if (MATCH_OR) {
-			// lanes holding the same digit meet in one shared word (atomicOr of the lane bit).  Items alternate between two
-			// tables, so the word an item's first lane clears is not one the next item's lanes are setting bits in.
-			uint32_t* const t0 = reinterpret_cast<uint32_t*>(s_buf) + warp * RADIX;
-			const uint32_t lanebit = 1u << lane;
-			#pragma unroll
-			for (int k = 0; k < IPT; k++) {
-				const uint32_t d = digit_of(key[k], shift, mask);
-				uint32_t* const t = t0 + (k & 1) * (SORT_WARPS * RADIX);
-				atomicOr(&t[d], lanebit);
-				__syncwarp();
-				const uint32_t peers = t[d], old = wh[d];
-				__syncwarp();
-				const uint32_t below = peers & lt;
-				if (below == 0) { t[d] = 0; wh[d] = old + __popc(peers); }       // the first lane of the group
-				pd[k] = (old + __popc(below)) | (d << 16);
-			}
-		} else {
-			const int nbits = __popc(mask);
-			#pragma unroll
-			for (int k = 0; k < IPT; k++) {
-				const uint32_t d = digit_of(key[k], shift, mask);
-				const uint32_t peers = same_digit_lanes(d, nbits);
-				const uint32_t old = wh[d];
-				__syncwarp();
-				const uint32_t below = peers & lt;
-				if (below == 0) wh[d] = old + __popc(peers);
-				__syncwarp();
-				pd[k] = (old + __popc(below)) | (d << 16);
-			}
+		// lanes holding the same digit meet in one shared word (atomicOr of the lane bit; match.any is a slow MIO-queue
+		// operation on sm_100a and a ballot per digit bit costs more issue slots and latency than it saves shared-memory
+		// traffic — both measured).  Items alternate between two tables, so the word an item's first lane clears is not one
+		// the next item's lanes are setting bits in.
+		uint32_t* const t0 = reinterpret_cast<uint32_t*>(s_buf) + warp * RADIX;
+		const uint32_t lanebit = 1u << lane;
+		#pragma unroll
+		for (int k = 0; k < IPT; k++) {
+			const uint32_t d = digit_of(key[k], shift, mask);
+			uint32_t* const t = t0 + (k & 1) * (SORT_WARPS * RADIX);
+			atomicOr(&t[d], lanebit);
+			__syncwarp();
+			const uint32_t peers = t[d], old = wh[d];
+			__syncwarp();
+			const uint32_t below = peers & lt;
+			if (below == 0) { t[d] = 0; wh[d] = old + __popc(peers); }       // the first lane of the group
+			pd[k] = (old + __popc(below)) | (d << 16);
 		}
 	}
 	__syncthreads();
@@ -291,8 +265,8 @@ __global__ void __launch_bounds__(SORT_THREADS, 4) onesweep_kernel(SegPtrs<K> sp
 	// resumes from there.
 	{
 		uint32_t excl = 0;
-		if (tile > 0) {
-			constexpr int LB = 8;
+		if (tile > 0 && (uint32_t)d <= mask) {                 // digits above the mask do not occur
+			constexpr int LB = SORT_LOOKBACK;
 			int64_t t = (int64_t)tile - 1;
 			bool found = false;
 			while (!found) {
@@ -413,16 +387,12 @@ int sort_pairs_segments(cudaStream_t stream, int nseg, K* const* keys_a, K* cons
 		sp.ghist[g] = L.ghist; sp.tickets[g] = L.tickets; sp.status[g] = L.status;
 		ntiles = L.ntiles;
 	}
-	// ranking variant: shared-memory atomicOr match for large inputs (measured 0.196 vs 0.218 ms on the 8.4M-pair tile sort),
-	// ballot match for small ones (0.088 vs 0.096 ms on the 1M-key depth sort)
-	const bool match_or = n >= (1u << 22);
 	const uint32_t hgrid = (uint32_t)((n + SORT_THREADS * 16 - 1) / (SORT_THREADS * 16));
 	const uint32_t hcap = nseg > 1 ? (1184u + nseg - 1) / nseg : 1184u;
 	count_launch(), histogram_kernel<K><<<dim3(hgrid < hcap ? hgrid : hcap, nseg), SORT_THREADS, 0, stream>>>(sp, (uint32_t)n, pd);
 	count_launch(), digit_base_kernel<K><<<dim3(pd.npass, nseg), RADIX, 0, stream>>>(sp);
 	for (int p = 0; p < pd.npass; p++) {
-		if (match_or) count_launch(), onesweep_kernel<K, IPT, true><<<dim3(ntiles, nseg), SORT_THREADS, 0, stream>>>(sp, p, iota_vals, true, (uint32_t)n, ntiles, pd.shift[p], pd.mask[p]);
-		else count_launch(), onesweep_kernel<K, IPT, false><<<dim3(ntiles, nseg), SORT_THREADS, 0, stream>>>(sp, p, iota_vals, true, (uint32_t)n, ntiles, pd.shift[p], pd.mask[p]);
+		count_launch(), onesweep_kernel<K, IPT><<<dim3(ntiles, nseg), SORT_THREADS, 0, stream>>>(sp, p, iota_vals, true, (uint32_t)n, ntiles, pd.shift[p], pd.mask[p]);
 	}
 	if (check_launch("sort_pairs", stream, false)) return -1;
 	return pd.npass & 1;   // odd number of passes -> result sits in the *_b buffers
@@ -456,11 +426,9 @@ int tile_sort16(cudaStream_t stream, int P, size_t N, int bits, int grid_x, cons
 	sp.keys_a[0] = keys_a; sp.keys_b[0] = keys_b; sp.vals_a[0] = vals_a; sp.vals_b[0] = vals_b;
 	sp.ghist[0] = const_cast<uint32_t*>(digit_bases); sp.tickets[0] = L.tickets; sp.status[0] = L.status;
 	constexpr int IPT = Cfg<uint16_t>::IPT;
-	const bool match_or = N >= (1u << 22);
 	for (int p = 0; p < pd.npass; p++) {
 		const bool wk = p + 1 < pd.npass;                             // the last pass writes the Gaussian ids (point_list) only
-		if (match_or) count_launch(), onesweep_kernel<uint16_t, IPT, true><<<dim3(L.ntiles, 1), SORT_THREADS, 0, stream>>>(sp, p, false, wk, (uint32_t)N, L.ntiles, pd.shift[p], pd.mask[p]);
-		else count_launch(), onesweep_kernel<uint16_t, IPT, false><<<dim3(L.ntiles, 1), SORT_THREADS, 0, stream>>>(sp, p, false, wk, (uint32_t)N, L.ntiles, pd.shift[p], pd.mask[p]);
+		count_launch(), onesweep_kernel<uint16_t, IPT><<<dim3(L.ntiles, 1), SORT_THREADS, 0, stream>>>(sp, p, false, wk, (uint32_t)N, L.ntiles, pd.shift[p], pd.mask[p]);
 	}
 	if (check_launch("tile_sort16", stream, false)) return -1;
 	return pd.npass & 1;   // 1: the sorted ids are in vals_b, 0: in vals_a
