@@ -9,6 +9,7 @@
 // sorts are stable and the depth sort starts from index order.  The 64-bit key list the reference would hold is
 // reconstructed on demand by export_keys_kernel for the parity tests.
 #include <cstring>
+#include <algorithm>
 #include "common.cuh"
 #include "kernels.cuh"
 
@@ -17,7 +18,7 @@ namespace rr {
 namespace {
 
 constexpr int SCAN_THREADS = 256;
-constexpr int SCAN_ITEMS = 4;
+constexpr int SCAN_ITEMS = 16;        // per thread, consecutive: 4096 per CTA (the look-back walks over 4 x fewer tiles than at 4)
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 
 // Status words of the chained scan: flags in the top two bits, a 30-bit payload.  All sums SATURATE at SC_MASK = 2^30 - 1
@@ -42,6 +43,13 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* s
 	return sat_add(pre, inc) - v;            // exact below saturation; garbage above it, where the host rejects the total
 }
 
+struct ZeroSegs { uint4* p[16]; };
+__global__ void __launch_bounds__(256) zero_segments_kernel(ZeroSegs z, size_t n16)
+{
+	uint4* __restrict__ p = z.p[blockIdx.y];
+	for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n16; i += (size_t)gridDim.x * 256) p[i] = make_uint4(0u, 0u, 0u, 0u);
+}
+
 // Inclusive prefix sum of tiles_touched in DEPTH order (where each Gaussian's duplicates go in the emission list), replacing
 // cub::DeviceScan::InclusiveSum (rasterizer_impl.cu:269), in ONE launch: chained scan with decoupled look-back.  Blocks
 // take tile ids from an atomic ticket (a block's predecessors are therefore always running or done), publish their tile
@@ -61,12 +69,24 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_chained_kernel(int P, int n
 	__syncthreads();
 	const int tile = (int)s_tile;
 	uint32_t v[SCAN_ITEMS], sum = 0;
-	#pragma unroll
-	for (int k = 0; k < SCAN_ITEMS; k++) {
-		const int i = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS + k;
-		v[k] = i < P ? min(tt[order[i]], SC_MASK) : 0;
-		sum = sat_add(sum, v[k]);
+	const int i0 = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+	const bool full = tile * SCAN_TILE + SCAN_TILE <= P;                // warp- and CTA-uniform
+	if (full) {
+		// the thread's 16 depth-order entries as four 16-byte loads, then 16 independent gathers
+		uint32_t g[SCAN_ITEMS];
+		#pragma unroll
+		for (int k = 0; k < SCAN_ITEMS; k += 4) {
+			const uint4 o = *reinterpret_cast<const uint4*>(order + i0 + k);
+			g[k] = o.x; g[k + 1] = o.y; g[k + 2] = o.z; g[k + 3] = o.w;
+		}
+		#pragma unroll
+		for (int k = 0; k < SCAN_ITEMS; k++) v[k] = min(__ldg(tt + g[k]), SC_MASK);
+	} else {
+		#pragma unroll
+		for (int k = 0; k < SCAN_ITEMS; k++) v[k] = i0 + k < P ? min(tt[order[i0 + k]], SC_MASK) : 0;
 	}
+	#pragma unroll
+	for (int k = 0; k < SCAN_ITEMS; k++) sum = sat_add(sum, v[k]);
 	uint32_t tot;
 	const uint32_t ex = block_exclusive_scan(sum, s_warp, tot);
 	if (threadIdx.x < 32) {
@@ -97,11 +117,19 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_chained_kernel(int P, int n
 	}
 	__syncthreads();
 	uint32_t run = s_excl + ex;
-	#pragma unroll
-	for (int k = 0; k < SCAN_ITEMS; k++) {
-		const int i = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS + k;
-		run += v[k];
-		if (i < P) offsets[i] = run;
+	if (full) {
+		#pragma unroll
+		for (int k = 0; k < SCAN_ITEMS; k += 4) {
+			uint4 o;
+			run += v[k]; o.x = run; run += v[k + 1]; o.y = run; run += v[k + 2]; o.z = run; run += v[k + 3]; o.w = run;
+			*reinterpret_cast<uint4*>(offsets + i0 + k) = o;
+		}
+	} else {
+		#pragma unroll
+		for (int k = 0; k < SCAN_ITEMS; k++) {
+			run += v[k];
+			if (i0 + k < P) offsets[i0 + k] = run;
+		}
 	}
 }
 
@@ -380,12 +408,25 @@ __global__ void __launch_bounds__(128) export_keys_kernel(int T, const uint2* __
 
 size_t scan_ws_elems(int P) { return (size_t)(P + SCAN_TILE - 1) / SCAN_TILE + 1; }
 
+int launch_zero_segments(cudaStream_t stream, int nseg, void* const* ptrs, size_t bytes)
+{
+	if (nseg <= 0 || bytes == 0) return 0;
+	if (nseg == 1) { cudaMemsetAsync(ptrs[0], 0, bytes, stream); return 0; }
+	if (nseg > 16) { set_error("zero_segments: %d regions (at most 16)", nseg); return -1; }
+	ZeroSegs z;
+	for (int g = 0; g < 16; g++) z.p[g] = reinterpret_cast<uint4*>(ptrs[g < nseg ? g : 0]);
+	const size_t n16 = (bytes + 15) / 16;
+	const unsigned gx = (unsigned)std::min<size_t>((n16 + 255) / 256, 64);
+	count_launch(), zero_segments_kernel<<<dim3(gx, nseg), 256, 0, stream>>>(z, n16);
+	return check_launch("zero_segments", stream, false);
+}
+
 int launch_scan_tiles_segments(cudaStream_t stream, int P, int nseg, const ScanSegs& sg)
 {
 	if (nseg == 0) return 0;
 	if (P == 0) { for (int g = 0; g < nseg; g++) cudaMemsetAsync(sg.total[g], 0, sizeof(uint32_t), stream); return 0; }
 	const int nb = (P + SCAN_TILE - 1) / SCAN_TILE;
-	for (int g = 0; g < nseg; g++) cudaMemsetAsync(sg.status[g], 0, sizeof(uint32_t) * (size_t)(nb + 1), stream);
+	{ void* zp[16]; for (int g = 0; g < nseg; g++) zp[g] = sg.status[g]; if (launch_zero_segments(stream, nseg, zp, sizeof(uint32_t) * (size_t)(nb + 1))) return -1; }
 	count_launch(), scan_chained_kernel<<<dim3(nb, nseg), SCAN_THREADS, 0, stream>>>(P, nb, sg);
 	return check_launch("scan_tiles", stream, false);
 }
@@ -428,7 +469,7 @@ int launch_tile_plan(cudaStream_t stream, int P, int grid_x, int grid_y, int nse
 {
 	if (nseg == 0) return 0;
 	const int cells = (grid_x + 1) * (grid_y + 1);
-	for (int g = 0; g < nseg; g++) cudaMemsetAsync(sg.gdiff[g], 0, sizeof(int) * (size_t)cells, stream);
+	{ void* zp[16]; for (int g = 0; g < nseg; g++) zp[g] = sg.gdiff[g]; if (launch_zero_segments(stream, nseg, zp, sizeof(int) * (size_t)cells)) return -1; }
 	const int ctas = max(1, min((P + DIFF_THREADS * 4 - 1) / (DIFF_THREADS * 4), 148));
 	count_launch(), tile_diff_kernel<<<dim3(ctas, nseg), DIFF_THREADS, 0, stream>>>(P, cells, grid_x + 1, sg);
 	count_launch(), tile_plan_kernel<<<nseg, PLAN_THREADS, 0, stream>>>(grid_x, grid_y, sg, npass, shift[0], mask[0], npass > 1 ? shift[1] : 0, npass > 1 ? mask[1] : 0u);

@@ -42,6 +42,9 @@ struct Carver {
 
 void set_error(const char* fmt, ...);
 int check_launch(const char* what, cudaStream_t stream, bool sync);
+// zero `bytes` (rounded up to 16; the regions are 256-byte-aligned carvings with room to the next one) at each of nseg device
+// pointers (host array): one memset for a single region, ONE kernel for several (instead of a memset launch per region)
+int launch_zero_segments(cudaStream_t stream, int nseg, void* const* ptrs, size_t bytes);
 void count_launch();   // every kernel launch of the library is counted (rr_launch_count), bench.py reports it
 
 // element idx of a [n,4] float array as a float4: one 16-byte load when the base is 16-byte aligned (a tensor that is a view

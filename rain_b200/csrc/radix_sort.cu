@@ -380,13 +380,15 @@ int sort_pairs_segments(cudaStream_t stream, int nseg, K* const* keys_a, K* cons
 	SegPtrs<K> sp;
 	memset(&sp, 0, sizeof(sp));
 	uint32_t ntiles = 0;
+	size_t zero_bytes = 0;
 	for (int g = 0; g < nseg; g++) {
 		const WsLayout L = ws_layout<K>(ws[g], n, pd.npass);
-		cudaMemsetAsync(ws[g], 0, L.zero_bytes, stream);
+		zero_bytes = L.zero_bytes;
 		sp.keys_a[g] = keys_a[g]; sp.keys_b[g] = keys_b[g]; sp.vals_a[g] = vals_a[g]; sp.vals_b[g] = vals_b[g];
 		sp.ghist[g] = L.ghist; sp.tickets[g] = L.tickets; sp.status[g] = L.status;
 		ntiles = L.ntiles;
 	}
+	if (launch_zero_segments(stream, nseg, ws, zero_bytes)) return -1;
 	const uint32_t hgrid = (uint32_t)((n + SORT_THREADS * 16 - 1) / (SORT_THREADS * 16));
 	const uint32_t hcap = nseg > 1 ? (1184u + nseg - 1) / nseg : 1184u;
 	count_launch(), histogram_kernel<K><<<dim3(hgrid < hcap ? hgrid : hcap, nseg), SORT_THREADS, 0, stream>>>(sp, (uint32_t)n, pd);
