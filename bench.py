@@ -534,8 +534,9 @@ def main():
             e.update(alg_flops=fl, evaluated_pairs=ev, blended_pairs=co, tflops=round(fl / per / 1e9, 2), frac_of_fp32=round(fl / per / 1e9 / fp32_peak, 4))
             e.update(ncu_render.get(name, {}))          # issue_active, pipe_fma, smem_wavefronts_per_clk_per_sm ... (ncu capture, committed under profiles/)
             e.update(live.get(name, {}))                # live_lane_frac ... (cross-check build counters, committed under profiles/)
-        if name in traffic:
-            e["dram_traffic"] = traffic[name]
+        tkey = "preprocess_views" if (name == "preprocess_fwd" and vpl > 1) else name      # the view-batched geometry pass is its own kernel
+        if tkey in traffic:
+            e["dram_traffic"] = traffic[tkey]
         stages[name] = e
     per_view = {k: 1.0 / views_per_launch[k] for k in stages}                           # launches per rendered view
     tot = sum(v["ms"] * per_view[k] for k, v in stages.items())
