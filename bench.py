@@ -20,6 +20,7 @@ ONE NCCL all-reduce of that bucket (view-sharded data parallelism, SURVEY.md §8
 Prints ONE JSON line on rank 0.
 """
 import argparse
+import gc
 import json
 import os
 import subprocess
@@ -79,17 +80,25 @@ def load_peaks():
 
 
 class ClockSampler:
-    """samples nvidia-smi clocks / throttle reasons of one GPU during the timed region"""
-    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+    """samples nvidia-smi clocks / throttle reasons of one GPU during the timed region.  The polled query is kept light (SM clock
+    and the four throttle reasons, every SMI_MS ms): polling the full recipe line every 50 ms stalled the timed steps in about one
+    run out of five (profiles/r02_smi_polling.txt); the maximum clock and the power draw are read once, right after the region."""
+    Q = "clocks.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    Q_FULL = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    SMI_MS = os.environ.get("RAIN_BENCH_SMI_MS", "100")                 # diagnostics: polling period; "0" = no polling process at all
+    FULL = os.environ.get("RAIN_BENCH_SMI_FULL", "0") == "1"            # diagnostics: poll the full line (incl. clocks.max.sm, power.draw)
 
     def __init__(self, index):
         self.index, self.rows, self.proc, self.ready = index, [], None, threading.Event()
 
     def start(self):
+        if self.SMI_MS == "0":
+            return
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50", "-i", str(self.index)],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q_FULL if self.FULL else self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", self.SMI_MS, "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
         except Exception:
@@ -97,7 +106,10 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
+            r = [x.strip() for x in line.split(",")]
+            if self.FULL and len(r) >= 7:
+                r = [r[0]] + r[3:7]
+            self.rows.append((time.time(), r))
             self.ready.set()
 
     def wait_ready(self, timeout=5.0):
@@ -107,17 +119,23 @@ class ClockSampler:
 
     def stop(self, t0, t1):
         if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable" if self.SMI_MS != "0" else "polling disabled (diagnostic run)"]}
         time.sleep(0.12)
         self.proc.terminate()
-        rows = [r for t, r in self.rows if t0 - 0.05 <= t <= t1 + 0.1 and len(r) >= 7] or [r for _, r in self.rows if len(r) >= 7]
+        rows = [r for t, r in self.rows if t0 - 0.05 <= t <= t1 + 0.1 and len(r) >= 5] or [r for _, r in self.rows if len(r) >= 5]
         if not rows:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
         sm = sorted(float(r[0]) for r in rows)
-        reasons = [n for i, n in ((3, "hw_slowdown"), (4, "hw_thermal_slowdown"), (5, "sw_thermal_slowdown"), (6, "sw_power_cap"))
+        reasons = [n for i, n in ((1, "hw_slowdown"), (2, "hw_thermal_slowdown"), (3, "sw_thermal_slowdown"), (4, "sw_power_cap"))
                    if any(r[i].lower().startswith("active") for r in rows)]
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][1]), "power_w_max": max(float(r[2]) for r in rows),
-                "samples": len(rows), "reasons": reasons}
+        out = {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": None, "samples": len(rows), "period_ms": int(self.SMI_MS), "reasons": reasons}
+        try:       # one query outside the timed region
+            one = subprocess.run(["nvidia-smi", "--query-gpu=clocks.max.sm,power.draw", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                                 capture_output=True, text=True, timeout=10).stdout.strip().split(",")
+            out["sm_max_mhz"] = float(one[0]); out["power_w_after"] = float(one[1])
+        except Exception:
+            pass
+        return out
 
 
 # stages whose roofline is HBM bandwidth; the two tile renderers are bound by instruction issue (FP32 / SFU / LSU slots)
@@ -234,6 +252,11 @@ def run_ours(args, rank, world, local):
     if rank == 0:
         sampler.start()
         sampler.wait_ready()
+    # Python's cyclic collector: a full collection over everything torch has imported takes tens of ms of host time and, landing
+    # in a step, drains the GPU (every view waits for its num_rendered on the host) — seen as one slow step in one run out of
+    # five (profiles/r02_steptimes.txt).  Collect now and move the survivors out of the collector's reach; it stays enabled.
+    gc.collect()
+    gc.freeze()
     for s in range(args.warmup):
         step_resident(s)
     barrier_sync(world)
@@ -242,14 +265,20 @@ def run_ours(args, rank, world, local):
     t0 = time.time()
     e0.record()
     N_last = 0
+    step_marks = []                                  # diagnostic only (RAIN_BENCH_DIAG=steptimes): an event after every timed step
     for s in range(args.steps):
         res = step_resident(args.warmup + s, time_allreduce=True)
         N_last = res[-1].num_rendered
+        if os.environ.get("RAIN_BENCH_DIAG", "") == "steptimes":
+            step_marks.append(torch.cuda.Event(enable_timing=True)); step_marks[-1].record()
     e1.record()
     barrier_sync(world)
     t1 = time.time()
     launches = lib.rr_launch_count() - launches0
     ms = max_over_ranks(e0.elapsed_time(e1), world, dev)
+    if step_marks:
+        marks = [e0] + step_marks
+        print("steptimes_ms " + " ".join(f"{marks[i].elapsed_time(marks[i + 1]):.2f}" for i in range(len(step_marks))), file=sys.stderr)
     if os.environ.get("RAIN_BENCH_DIAG", "") == "artrace" and world > 1:      # diagnostic only: per-step all-reduce time of every rank
         os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
         with open(os.path.join(ROOT, "gpurun_out", f"artrace_{args.collective}_r{rank}.txt"), "w") as f:
@@ -439,6 +468,8 @@ def run_reference(args, rank, world, local):
             N, color, radii, depth = ref.forward(bg, sc.means3D, sc.opacities, sc.scales, sc.rotations, cam.viewmatrix, cam.projmatrix, cam.campos,
                                                  cam.tanfovx, cam.tanfovy, cam.height, cam.width, shs=sc.shs, sh_degree=cfg["D"], sync=False)
             ref.backward(torch.sub(color, targets[i % NUM_TARGETS]), sync=False)
+    gc.collect()
+    gc.freeze()          # same treatment as our arm: no full cyclic collection inside the timed steps
     for s in range(args.warmup):
         step(s)
     torch.cuda.synchronize()

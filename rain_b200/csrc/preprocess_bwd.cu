@@ -344,6 +344,9 @@ __global__ void __launch_bounds__(PB_THREADS, PB_MIN_CTAS) preprocess_bwd_kernel
 //   LEAF = true : inputs are the six RAW leaf tensors of scene/gaussian_model.py:131-136 (activations of :85-105 applied
 //                 here: splat_math.cuh), gradients w.r.t. the leaves (chain rule applied here), bucket layout
 //                 xyz | f_dc[P,1,3] | f_rest[P,15,3] | opacity | scaling | rotation
+#ifndef BV_PREFETCH
+#define BV_PREFETCH 1
+#endif
 constexpr int BV_THREADS = 128;
 constexpr int BV_WARPS = BV_THREADS / 32;
 constexpr int CAM_FLOATS = 40;           // V[16] Pj[16] campos[3] tan_fovx tan_fovy focal_x focal_y pad
@@ -426,7 +429,17 @@ __global__ void __launch_bounds__(BV_THREADS, 4) backward_views_kernel(BackwardV
 			const bool nz = (m[j][0].x != 0.0f) | (m[j][0].y != 0.0f) | (m[j][0].z != 0.0f) | (m[j][0].w != 0.0f) | (m[j][1].x != 0.0f) | (m[j][1].y != 0.0f) |
 				(m[j][1].z != 0.0f) | (m[j][1].w != 0.0f) | (m[j][2].x != 0.0f);
 			if (r[j] > 0) { nvis++; maxr = max(maxr, r[j]); }
-			if (nz) touched |= 1u << (v0 + j);
+			if (nz) {
+				touched |= 1u << (v0 + j);
+#if BV_PREFETCH
+				// phase B reads this view's projected record and clamp flags one view at a time, with its arithmetic in between:
+				// start those lines on their way now
+				const float4* rp = reinterpret_cast<const float4*>(a.rec[v0 + j]) + ii * 3;
+				asm volatile("prefetch.global.L2 [%0];" ::"l"(rp));
+				asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + 1));
+				asm volatile("prefetch.global.L2 [%0];" ::"l"(a.clamped[v0 + j] + ii));
+#endif
+			}
 			else if (valid && v0 + j < nv && a.dL_dmean2D[v0 + j]) {           // a view that left no gradient: its viewspace gradient row is zero
 				float* o = a.dL_dmean2D[v0 + j] + i3;
 				o[0] = 0.0f; o[1] = 0.0f; o[2] = 0.0f;
