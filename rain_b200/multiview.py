@@ -124,7 +124,11 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
     SLOWER than the plain all-reduce after the backward on B200 (both kernels are HBM bound: 8.33 vs 8.08 ms per step at 2 GPUs,
     profiles/r02_n2_overlap.txt), hence off.
     stats: optional rain_b200.optim.DensificationStats; the batched backward folds the views' densification statistics into
-    its per-step delta in the same pass (otherwise call stats.add_view per view)."""
+    its per-step delta in the same pass (otherwise call stats.add_view per view).
+    Host side: every view's forward blocks the host until its num_rendered has arrived, so host stalls drain the GPU.  A long-running
+    loop should call ``gc.collect(); gc.freeze()`` once after set-up: a full pass of Python's cyclic collector over torch's objects
+    takes tens of ms and was measured as one 8-40 ms step in a five-step-old process.
+    """
     if pipeline not in ("two_stream", "one_stream"):
         raise ValueError(f"unknown pipeline {pipeline!r}")
     leaf = leaves is not None
