@@ -395,7 +395,9 @@ def test_accumulate_mode_and_multiview_bucket(device, pipeline, P, W, H, V, batc
         fw = mine_forward(sc, cams[v], bg)
         g = mine_backward(fw, sc, cams[v], bg, dp[v])
         assert eq(res[v].color, fw["color"]) and eq(res[v].radii, fw["radii"]) and res[v].num_rendered == fw["N"]
-        assert rel_err(res[v].dL_dmeans2D, g["dL_dmean2D"])[0] < 2e-6
+        # two runs of the same backward tile renderer: its per-Gaussian sums arrive through unordered fp32 atomics, and over a
+        # million Gaussians the largest of the differences reaches a few 1e-6 of max (3.0e-6 seen); small scenes stay below 2e-6
+        assert rel_err(res[v].dL_dmeans2D, g["dL_dmean2D"])[0] < (2e-6 if P < 100_000 else 1e-5)
         ref_stats.add_view(fw["radii"], g["dL_dmean2D"])                  # rr_densify_stats per view (train.py:132-134)
         cur = dict(means3D=g["dL_dmean3D"], sh=g["dL_dsh"], opacity=g["dL_dopacity"], scales=g["dL_dscale"], rotations=g["dL_drot"])
         tot = cur if tot is None else {k: tot[k] + cur[k] for k in cur}
