@@ -410,7 +410,7 @@ def test_accumulate_mode_and_multiview_bucket(device, pipeline, P, W, H, V, batc
     # densification statistics folded into the batched backward == the per-view kernel's
     ref_stats.sync()
     assert eq(stats.max_radii2D, ref_stats.max_radii2D) and eq(stats.denom, ref_stats.denom)
-    assert rel_err(stats.xyz_gradient_accum, ref_stats.xyz_gradient_accum)[0] < 5e-6
+    assert rel_err(stats.xyz_gradient_accum, ref_stats.xyz_gradient_accum)[0] < (5e-6 if P < 100_000 else 2e-5)      # sums of the norms bounded above
 
 
 @pytest.mark.skipif(TILE_CULL, reason="the view-batched geometry pass has no tile culling")
