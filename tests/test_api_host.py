@@ -4,6 +4,7 @@ and simple_knn._C of sharonal10/rain.  No kernel runs here."""
 import inspect
 import os
 
+import numpy as np
 import pytest
 import torch
 
@@ -120,3 +121,19 @@ def test_unmodified_reference_callers_import_on_top_of_the_dropin_modules():
         "print('ok')\n")
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, cwd=root)
     assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stderr[-2000:]
+
+
+def test_pair_emission_division_identity():
+    """csrc/binning.cu::duplicate16_kernel replaces `local / width` (tile row inside a Gaussian's rect) by
+    umulhi(local, 0xffffffff / width + 1); claimed exact for local, width < 2^16 (tile ids are 16-bit on that path).  Checked on the
+    host for every width at the multiples of the width, their neighbours and random points (width 1 wraps the factor to 0 and is
+    special-cased in the kernel)."""
+    rng = np.random.default_rng(0)
+    for w in range(2, 65536):
+        inv = np.uint64(0xffffffff // w + 1)
+        assert inv < 2 ** 32
+        k = np.arange(0, 65536 // w + 1, dtype=np.uint64)
+        loc = np.concatenate([k * np.uint64(w), k * np.uint64(w) + np.uint64(w - 1), k * np.uint64(w) + np.uint64(1), rng.integers(0, 65536, 16).astype(np.uint64)])
+        loc = loc[loc < 65536]
+        assert np.array_equal((loc * inv) >> np.uint64(32), loc // np.uint64(w)), w
+    assert (0xffffffff // 1 + 1) & 0xffffffff == 0
