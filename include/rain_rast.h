@@ -56,6 +56,7 @@ size_t rr_geom_bytes(int P);
 size_t rr_image_bytes(int W, int H);
 size_t rr_binning_bytes(int64_t N, int W, int H);
 size_t rr_backward_ws_bytes(int P);
+size_t rr_geom_acc_offset(int P);      /* byte offset of the backward accumulator region inside the geometry blob (rr_backward_render) */
 
 /* Forward, first half — replaces FORWARD::preprocess + cub InclusiveSum + the blocking cudaMemcpy of num_rendered
  * (Rasterizer::forward, rasterizer_impl.cu:187-273).  Writes radii[P] and the geometry blob, and enqueues an async
@@ -110,7 +111,7 @@ int rr_forward_render(void* stream, int P, int W, int H, int64_t N, const float*
  * with radii == 0 are left untouched; the per-view outputs dL_dmean2D and dL_dconic are still overwritten.
  * dL_dconic may be null (the reference keeps it internal).  dL_dsh is [P,M,3] (unused when shs is null),
  * dL_dscale / dL_drot may be null when cov3D_precomp is given; dL_dcolor may be null when shs is used and dL_dcov3D when
- * cov3D_precomp is not given (gradients of inputs the caller did not pass: intermediates, skipped).  ws: rr_backward_ws_bytes(P) of scratch
+ * cov3D_precomp is not given (gradients of inputs the caller did not pass: intermediates, skipped).  ws: rr_backward_ws_bytes(P) of scratch, or NULL for the geometry blob's own accumulator region (first backward after a forward only, see rr_backward_render)
  * (the per-Gaussian gradient accumulators the backward render adds into; zero-filled inside). */
 int rr_backward(void* stream, int P, int D, int M, int W, int H, int64_t N, const float* background,
 	const float* means3D, const float* shs, const float* colors_precomp,
@@ -126,7 +127,10 @@ int rr_backward(void* stream, int P, int D, int M, int W, int H, int64_t N, cons
 /* ---- view-batched backward (multi-view steps; no reference counterpart: the reference runs its whole backward once per view) ----
  * rr_backward_render is the first half of rr_backward alone — BACKWARD::render (rasterizer_impl.cu:386-404, backward.cu:389-547):
  * it zero-fills ws (rr_backward_ws_bytes(P)) and leaves there, per Gaussian, the 48-byte accumulator record of this view
- * (colour gradient and the moments of G * dL_dalpha over the pixels that blended it).
+ * (colour gradient and the moments of G * dL_dalpha over the pixels that blended it).  ws == NULL (ws_bytes 0): the records go
+ * to the accumulator region of the view's geometry blob (byte offset rr_geom_acc_offset(P), rr_backward_ws_bytes(P) - 256 bytes),
+ * which rr_forward_render / rr_forward_raster of the same view cleared while it rendered (its stores ride on idle HBM
+ * bandwidth; a separate fill costs 13 us per million Gaussians): valid for ONE rr_backward_render per forward of the view.
  * rr_backward_views is the second half — computeCov2DCUDA + preprocessCUDA backward (backward.cu:133-386) — for ALL nviews
  * views of a step in ONE pass over the Gaussians: every array argument up to dL_dmean2D is a HOST array of nviews entries
  * (device pointers, resp. floats); geom[v] / radii[v] / grad_acc[v] are view v's geometry blob, radii and the ws its

@@ -244,7 +244,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
                                  viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
                                  geomBuffer, R, binningBuffer, imageBuffer, debug, low_pass, return_conic=False,
-                                 grads_out=None, accumulate=False, omit=()):
+                                 grads_out=None, accumulate=False, omit=(), acc_in_geom=False):
     """RasterizeGaussiansBackwardCUDA (rasterize_points.cu:110-191).
     Returns (dL_dmeans2D[P,3], dL_dcolors[P,3], dL_dopacity[P,1], dL_dmeans3D[P,3], dL_dcov3D[P,6], dL_dsh[P,M,3],
     dL_dscales[P,3], dL_drotations[P,4]).
@@ -253,7 +253,9 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     any of "means3D", "sh", "colors", "opacity", "scales", "rotations", "cov3D" to caller-owned contiguous f32 tensors
     the kernel writes into (e.g. views of one flat allreduce bucket); ``accumulate`` adds to their contents instead
     of overwriting (RR_BWD_ACCUMULATE); ``omit`` names intermediates not to produce at all — "colors" (when ``sh`` is used)
-    and/or "cov3D" (when ``cov3D_precomp`` is not) — whose entries of the returned tuple are then None."""
+    and/or "cov3D" (when ``cov3D_precomp`` is not) — whose entries of the returned tuple are then None.
+    ``acc_in_geom``: the backward tile renderer accumulates into the region of the geometry blob that the forward cleared while
+    it rendered (no fill pass); only the FIRST backward after a forward may ask for it (the autograd function does)."""
     lib = _lib.load()
     dev = means3D.device
     P, H, W = means3D.size(0), dL_dout_color.size(1), dL_dout_color.size(2)
@@ -289,7 +291,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         bg, colors_c, scales_c, rots, cov_c = (_f32c(t, dev) for t in (background, colors, scales, rotations, cov3D_precomp))
         view, proj, cam, sh_c, dpix = (_f32c(t, dev) for t in (viewmatrix, projmatrix, campos, sh, dL_dout_color))
         radii_c = radii.contiguous()
-        ws = torch.empty(lib.rr_backward_ws_bytes(P), dtype=torch.uint8, device=dev)
+        ws = None if acc_in_geom else torch.empty(lib.rr_backward_ws_bytes(P), dtype=torch.uint8, device=dev)
         with torch.cuda.device(dev):
             stream = torch.cuda.current_stream()
             _lib.check(lib.rr_backward(stream.cuda_stream, P, int(degree), M, W, H, int(R), _ptr(bg),
@@ -299,7 +301,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                                        float(tan_fovx), float(tan_fovy), float(low_pass), radii_c.data_ptr(),
                                        geomBuffer.data_ptr(), geomBuffer.numel(), binningBuffer.data_ptr(), binningBuffer.numel(),
                                        imageBuffer.data_ptr(), imageBuffer.numel(),
-                                       dpix.data_ptr(), ws.data_ptr(), ws.numel(),
+                                       dpix.data_ptr(), None if ws is None else ws.data_ptr(), 0 if ws is None else ws.numel(),
                                        dL_dmeans2D.data_ptr(), dL_dconic.data_ptr(), dL_dopacity.data_ptr(), None if "colors" in omit else dL_dcolors.data_ptr(),
                                        dL_dmeans3D.data_ptr(), None if "cov3D" in omit else dL_dcov3D.data_ptr(), _ptr(dL_dsh), dL_dscales.data_ptr(), dL_drotations.data_ptr(),
                                        int(bool(debug)), 1 if accumulate else 0), "rr_backward")
@@ -307,20 +309,29 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     return out + (dL_dconic,) if return_conic else out
 
 
-def backward_render(background, dL_dout_color, geomBuffer, R, binningBuffer, imageBuffer, P, debug=False):
+def backward_render(background, dL_dout_color, geomBuffer, R, binningBuffer, imageBuffer, P, debug=False, in_geom=False):
     """First half of the backward alone (rr_backward_render: BACKWARD::render, rasterizer_impl.cu:386-404): returns the
     per-Gaussian accumulator blob of this view, which ``backward_views`` consumes together with those of the step's other
-    views.  No reference counterpart as a separate op (the reference runs its whole backward per view)."""
+    views.  No reference counterpart as a separate op (the reference runs its whole backward per view).
+    in_geom: keep the accumulators in the geometry blob (see below) instead of a fresh scratch tensor."""
     lib = _lib.load()
     dev = dL_dout_color.device
     H, W = dL_dout_color.size(1), dL_dout_color.size(2)
-    ws = torch.empty(lib.rr_backward_ws_bytes(P), dtype=torch.uint8, device=dev)
+    if in_geom:
+        # the accumulator region of the view's geometry blob, which the forward cleared while it rendered: no fill pass here.
+        # Valid for ONE backward_render per forward of the view (rain_b200.multiview calls it exactly once).
+        off = lib.rr_geom_acc_offset(P)
+        ws = geomBuffer[off:off + lib.rr_backward_ws_bytes(P) - 256]
+        ws_ptr, ws_len = None, 0
+    else:
+        ws = torch.empty(lib.rr_backward_ws_bytes(P), dtype=torch.uint8, device=dev)
+        ws_ptr, ws_len = ws.data_ptr(), ws.numel()
     if P != 0:
         bg, dpix = _f32c(background, dev), _f32c(dL_dout_color, dev)
         with torch.cuda.device(dev):
             _lib.check(lib.rr_backward_render(torch.cuda.current_stream().cuda_stream, P, W, H, int(R), _ptr(bg),
                                               geomBuffer.data_ptr(), geomBuffer.numel(), binningBuffer.data_ptr(), binningBuffer.numel(),
-                                              imageBuffer.data_ptr(), imageBuffer.numel(), dpix.data_ptr(), ws.data_ptr(), ws.numel(), int(bool(debug))), "rr_backward_render")
+                                              imageBuffer.data_ptr(), imageBuffer.numel(), dpix.data_ptr(), ws_ptr, ws_len, int(bool(debug))), "rr_backward_render")
     return ws
 
 

@@ -25,6 +25,7 @@ SIGNATURES = {
     "rr_image_bytes": (_sz, [_i, _i]),
     "rr_binning_bytes": (_sz, [_i64, _i, _i]),
     "rr_backward_ws_bytes": (_sz, [_i]),
+    "rr_geom_acc_offset": (_sz, [_i]),
     "rr_forward_geom": (_i, [_vp, _i, _i, _i, _i, _i,
                              _vp, _vp, _vp, _vp,
                              _vp, _f, _vp, _vp,

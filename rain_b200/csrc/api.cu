@@ -101,8 +101,10 @@ struct GeomLayout {
 	SplatRec* rec; float* cov3D; uint8_t* clamped; uint32_t* tiles_touched; uint2* rect;
 	uint32_t *key_a, *key_b, *val_a, *val_b, *offsets, *block_sums, *num_rendered; void* sort_ws;
 	unsigned long long* tile_mask;
+	float* acc;                 // [P, ACC_FLOATS] accumulators of this view's backward tile renderer; rr_forward_render leaves them zero
 	size_t total;
 	int64_t off[9];
+	int64_t acc_off;
 };
 // opt-in tile culling (preprocess.cu): RAIN_TILE_CULL=1, read once per process — the one run-time switch of the library
 bool tile_cull_wanted() { static const bool on = []() { const char* e = getenv("RAIN_TILE_CULL"); return e && e[0] == '1'; }(); return on; }
@@ -123,8 +125,10 @@ GeomLayout geom_layout(void* blob, int P)
 	L.num_rendered = c.take<uint32_t>(4);
 	L.sort_ws = c.take<char>(sort_ws_bytes<uint32_t>(Pz, 0, 32));
 	L.tile_mask = tile_cull_wanted() ? c.take<unsigned long long>(Pz) : nullptr;
+	L.acc = c.take<float>(Pz * ACC_FLOATS);
 	L.total = c.used();
 	char* b = reinterpret_cast<char*>(blob);
+	L.acc_off = (char*)L.acc - b;
 	// depth sort: 4 passes -> result back in the *_a buffers
 	L.off[0] = (char*)L.rec - b; L.off[1] = (char*)L.cov3D - b; L.off[2] = (char*)L.clamped - b; L.off[3] = (char*)L.tiles_touched - b;
 	L.off[4] = (char*)L.rect - b; L.off[5] = (char*)L.val_a - b; L.off[6] = (char*)L.offsets - b; L.off[7] = L.off[6];
@@ -222,6 +226,7 @@ int rr_prof_read(double* ms, int64_t* calls, int reset)
 size_t rr_geom_bytes(int P) { return geom_layout(nullptr, P).total + 256; }
 size_t rr_image_bytes(int W, int H) { return img_layout(nullptr, W, H).total + 256; }
 size_t rr_binning_bytes(int64_t N, int W, int H) { return bin_layout(nullptr, N, W, H).total + 256; }
+size_t rr_geom_acc_offset(int P) { return (size_t)geom_layout(nullptr, P).acc_off; }
 size_t rr_backward_ws_bytes(int P) { return (size_t)(P < 1 ? 1 : P) * ACC_FLOATS * sizeof(float) + 256; }
 
 int rr_geom_layout(int P, int64_t o[9]) { const GeomLayout L = geom_layout(nullptr, P); memcpy(o, L.off, sizeof(L.off)); return 0; }
@@ -420,6 +425,7 @@ int rr_forward_render(void* stream_, int P, int W, int H, int64_t N, const float
 	r.W = W; r.H = H; r.grid_x = grid_x; r.grid_y = grid_y;
 	r.ranges = I.ranges; r.rec = G.rec; r.point_list = B.point_list; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.warp_flags = B.warp_flags;
 	r.out_color = out_color; r.out_depth = out_depth; r.xc = XC_COUNTERS;
+	r.zero = reinterpret_cast<float4*>(G.acc); r.zero_n16 = (uint32_t)((size_t)P * ACC_FLOATS / 4);
 	{ Stage st(stream, ST_RENDER_FWD); if (launch_render_fwd(stream, r)) return -1; }
 	return check_launch("forward_render", stream, debug != 0);
 }
@@ -442,15 +448,17 @@ static int backward_render_impl(cudaStream_t stream, int P, int W, int H, int64_
 	const GeomLayout G = geom_layout(geom, P);
 	const BinLayout B = bin_layout(binning, N, W, H);
 	const ImgLayout I = img_layout(image, W, H);
-	if (G.total > geom_bytes || B.total > binning_bytes || I.total > image_bytes || rr_backward_ws_bytes(P) > ws_bytes + 256) { set_error("scratch blob too small"); return -1; }
-	float* grad_acc = reinterpret_cast<float*>(ws);
+	if (G.total > geom_bytes || B.total > binning_bytes || I.total > image_bytes || (ws && rr_backward_ws_bytes(P) > ws_bytes + 256)) { set_error("scratch blob too small"); return -1; }
+	// ws == null: the accumulator region of the geometry blob, which rr_forward_render of this view zero-filled while it rendered
+	// (valid for ONE backward per forward); otherwise the caller's scratch, zero-filled here
+	float* grad_acc = ws ? reinterpret_cast<float*>(ws) : G.acc;
 	RenderArgs r; memset(&r, 0, sizeof(r));
 	r.W = W; r.H = H; r.grid_x = (W + TILE_X - 1) / TILE_X; r.grid_y = (H + TILE_Y - 1) / TILE_Y;
 	r.ranges = I.ranges; r.rec = G.rec; r.point_list = B.point_list; r.bg = background; r.final_T = I.final_T; r.n_contrib = I.n_contrib; r.warp_flags = B.warp_flags;
 	r.dL_dpix = dL_dpix; r.grad_acc = grad_acc; r.xc = XC_COUNTERS;
 	// the accumulators start from zero (the fill is part of the render_bwd stage time)
 	Stage st(stream, ST_RENDER_BWD);
-	cudaMemsetAsync(grad_acc, 0, (size_t)P * ACC_FLOATS * sizeof(float), stream);
+	if (ws) cudaMemsetAsync(grad_acc, 0, (size_t)P * ACC_FLOATS * sizeof(float), stream);
 	if (N > 0 && launch_render_bwd(stream, r)) return -1;
 	if (debug && check_launch("render_bwd", stream, true)) return -1;
 	return 0;
@@ -463,7 +471,7 @@ int rr_backward_render(void* stream_, int P, int W, int H, int64_t N, const floa
 	cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
 	if (P == 0) return 0;
 	if (bad_ptr(background, "background") || bad_ptr(geom, "geom") || bad_ptr(binning, "binning") || bad_ptr(image, "image") ||
-		bad_ptr(dL_dpix, "dL_dpix") || bad_ptr(ws, "ws")) return -1;
+		bad_ptr(dL_dpix, "dL_dpix")) return -1;
 	if (backward_render_impl(stream, P, W, H, N, background, geom, geom_bytes, binning, binning_bytes, image, image_bytes, dL_dpix, ws, ws_bytes, debug)) return -1;
 	return check_launch("backward_render", stream, debug != 0);
 }
@@ -482,7 +490,7 @@ int rr_backward(void* stream_, int P, int D, int M, int W, int H, int64_t N, con
 	cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
 	if (P == 0) return 0;                                                  // rasterize_points.cu:155
 	if (bad_ptr(background, "background") || bad_ptr(means3D, "means3D") || bad_ptr(radii, "radii") || bad_ptr(geom, "geom") ||
-		bad_ptr(binning, "binning") || bad_ptr(image, "image") || bad_ptr(dL_dpix, "dL_dpix") || bad_ptr(ws, "ws") ||
+		bad_ptr(binning, "binning") || bad_ptr(image, "image") || bad_ptr(dL_dpix, "dL_dpix") ||
 		bad_ptr(dL_dmean2D, "dL_dmean2D") || bad_ptr(dL_dopacity, "dL_dopacity") || bad_ptr(dL_dmean3D, "dL_dmean3D")) return -1;
 	const bool use_sh = shs && !colors_precomp;
 	// the gradient of an input the caller did not pass is an intermediate: it may be omitted
@@ -499,7 +507,7 @@ int rr_backward(void* stream_, int P, int D, int M, int W, int H, int64_t N, con
 	a.means3D = means3D; a.scales = cov3D_precomp ? nullptr : scales; a.rotations = cov3D_precomp ? nullptr : rotations;
 	a.shs = use_sh ? shs : nullptr; a.cov3D = cov3D_precomp ? cov3D_precomp : G.cov3D;        // rasterizer_impl.cu:406
 	a.view = viewmatrix; a.proj = projmatrix; a.campos = campos; a.has_colors_precomp = colors_precomp != nullptr; a.accumulate = (flags & RR_BWD_ACCUMULATE) ? 1 : 0;
-	a.radii = radii; a.clamped = G.clamped; a.rec = G.rec; a.grad_acc = reinterpret_cast<const float*>(ws);
+	a.radii = radii; a.clamped = G.clamped; a.rec = G.rec; a.grad_acc = ws ? reinterpret_cast<const float*>(ws) : G.acc;      // (ws == null: see rr_backward_render)
 	a.dL_dmean2D = dL_dmean2D; a.dL_dconic = dL_dconic; a.dL_dopacity = dL_dopacity; a.dL_dcolor = dL_dcolor; a.dL_dmean3D = dL_dmean3D;
 	a.dL_dcov3D = dL_dcov3D; a.dL_dsh = dL_dsh; a.dL_dscale = dL_dscale; a.dL_drot = dL_drot;
 	{ Stage st(stream, ST_PREPROCESS_BWD); if (launch_preprocess_bwd(stream, a)) return -1; }

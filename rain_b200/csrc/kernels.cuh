@@ -81,6 +81,8 @@ struct RenderArgs {
 	uint32_t* warp_flags;       // [warp_flag_words(N, tiles)] fwd writes, bwd reads
 	float* out_color;           // [3,H,W]
 	float* out_depth;           // [H,W]
+	float4* zero;               // forward only: zero_n16 16-byte units the CTAs clear while they render (the geometry blob's accumulator
+	uint32_t zero_n16;          // region of this view's backward; the kernel is issue bound, the stores ride on idle HBM bandwidth)
 	// backward only
 	const float* dL_dpix;       // [3,H,W]
 	float* grad_acc;            // [P, ACC_FLOATS], zero on entry

@@ -55,6 +55,11 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MIN_CTAS) render_fwd_kernel(R
 
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 	const int tile = blockIdx.y * a.grid_x + blockIdx.x;
+	// this CTA's share of the zero fill of the view's backward accumulators (api.cu: GeomLayout::acc): a few 16-byte stores per thread
+	if (a.zero) {
+		const uint32_t stride = (uint32_t)(a.grid_x * a.grid_y) * FWD_THREADS;
+		for (uint32_t i = (uint32_t)tile * FWD_THREADS + tid; i < a.zero_n16; i += stride) a.zero[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+	}
 	const uint2 range = a.ranges[tile];
 	const int n = (int)(range.y - range.x);
 	const int nbatches = (n + BATCH - 1) / BATCH;

@@ -222,7 +222,8 @@ def render_views_fwd_bwd(params: dict, cameras: Sequence, view_ids: Sequence[int
         if batched:
             # per view only the backward tile renderer; its accumulator blob, radii and geometry blob stay alive until the batch's
             # single per-Gaussian pass
-            acc = backend.backward_render(bg, dpix, geom, N, binning, img, P, debug)
+            # (native backend: the accumulators live in the view's geometry blob, cleared by its forward render — no fill pass)
+            acc = backend.backward_render(bg, dpix, geom, N, binning, img, P, debug, **({"in_geom": True} if backend is _native else {}))
             d2 = torch.empty((P, 3), dtype=torch.float32, device=dev)
             group.append(dict(viewmatrix=cam.viewmatrix, projmatrix=cam.projmatrix, campos=cam.campos, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
                               radii=radii, geom=geom, acc=acc, dL_dmean2D=d2))

@@ -55,6 +55,7 @@ class _RasterizeGaussians(torch.autograd.Function):
             num_rendered, color, radii, depth, geomBuffer, binningBuffer, imgBuffer = _C.rasterize_gaussians(*args)
         ctx.raster_settings = rs
         ctx.num_rendered = num_rendered
+        ctx.acc_clean = True          # the forward left the geometry blob's backward accumulators zero: the first backward needs no fill pass
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer, binningBuffer, imgBuffer)
         ctx.mark_non_differentiable(radii)
         return color, radii, depth
@@ -67,16 +68,17 @@ class _RasterizeGaussians(torch.autograd.Function):
         args = (rs.bg, means3D, radii, colors_precomp, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
                 rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_out_color, sh, rs.sh_degree, rs.campos,
                 geomBuffer, ctx.num_rendered, binningBuffer, imgBuffer, rs.debug, rs.low_pass)
+        first, ctx.acc_clean = getattr(ctx, "acc_clean", False), False      # a second backward of the same forward (retain_graph) fills its own scratch
         if rs.debug:
             cpu_args = cpu_deep_copy_tuple(args)
             try:
-                grads = _C.rasterize_gaussians_backward(*args)
+                grads = _C.rasterize_gaussians_backward(*args, acc_in_geom=first)
             except Exception as ex:
                 torch.save(cpu_args, "snapshot_bw.dump")
                 print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
                 raise ex
         else:
-            grads = _C.rasterize_gaussians_backward(*args)
+            grads = _C.rasterize_gaussians_backward(*args, acc_in_geom=first)
         grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh, grad_scales, grad_rotations = grads
         # one slot per forward input, in input order (reference __init__.py:134-144)
         return (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities, grad_scales, grad_rotations,

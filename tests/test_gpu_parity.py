@@ -335,6 +335,19 @@ def test_autograd_api_equals_direct_backward_and_is_reproducible(device):
     g = mine_backward(fw, sc, cam, bg, dpix)
     for a, k in zip(outs[0][3:], ["dL_dmean2D", "dL_dmean3D", "dL_dopacity", "dL_dsh", "dL_dscale", "dL_drot"]):
         assert rel_err(a, g[k])[0] < 5e-5, k
+    # two backward passes of ONE forward (retain_graph): the first accumulates in the geometry blob's region that the forward
+    # cleared while it rendered, the second must not trust that region again (it fills its own scratch) — same gradients both times
+    leaves = [t.clone().requires_grad_(True) for t in (sc.means3D, sc.opacities, sc.shs, sc.scales, sc.rotations)]
+    m2d = torch.zeros_like(sc.means3D, requires_grad=True)
+    color, radii, depth = GaussianRasterizer(rs)(means3D=leaves[0], means2D=m2d, opacities=leaves[1], shs=leaves[2], scales=leaves[3], rotations=leaves[4])
+    loss = (color * dpix).sum()
+    loss.backward(retain_graph=True)
+    first = [m2d.grad.clone()] + [t.grad.clone() for t in leaves]
+    for t in [m2d] + leaves:
+        t.grad = None
+    loss.backward()
+    for a, b, c in zip(first, [m2d.grad] + [t.grad for t in leaves], outs[0][3:]):
+        assert rel_err(a, b)[0] < 5e-5 and rel_err(a, c)[0] < 5e-5
 
 
 def test_full_size_properties_config3(device):
